@@ -1,0 +1,216 @@
+// TEST INFRASTRUCTURE (oracle/_ref). Drives the UNMODIFIED reference integrator
+// (mimi::integrators::NonlinearSolid, /root/reference/src/mimi/integrators/nonlinear_solid.cpp)
+// exactly the way PyNonlinearSolid::Setup wires it (/root/reference/src/mimi/py/py_nonlinear_solid.cpp:57-217)
+// and dumps / times what it computes. Nothing in the product links or executes this file.
+//
+//   mimi_ref dump <mesh> <elevate> <refine> <material> <nthreads> <gf> <u.bin|-> <outdir> [lite]
+//   mimi_ref time <mesh> <elevate> <refine> <material> <nthreads> <reps>
+// material: neohookean | stvk  (E=2100, nu=0.3, rho=1: tests/test_nonlinear_solid.py:59-62)
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <mfem.hpp>
+
+#include "mimi/integrators/nonlinear_solid.hpp"
+#include "mimi/materials/materials.hpp"
+#include "mimi/utils/precomputed.hpp"
+
+// The only splinepy *library* symbol the reference's contact integrator pulls in
+// (coefficients/nearest_distance.hpp:259-281, NearestDistanceToSplines). The harness never builds a
+// NearestDistanceToSplines (rigid bodies are analytic NearestDistanceBase subclasses), so it must never run.
+namespace splinepy::py {
+PySpline::CoreSpline_& PySpline::Core() { throw std::runtime_error("splinepy core is not linked into oracle/_ref"); }
+}  // namespace splinepy::py
+
+namespace {
+
+uint64_t splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+// u_i = 1e-3 (U_i - 0.5), U_i from splitmix64(seed + i): SURVEY.md section 8(d)
+double synth_u(uint64_t seed, uint64_t i) {
+  const double U = (double)(splitmix64(seed + i) >> 11) * (1.0 / 9007199254740992.0);
+  return 1.0e-3 * (U - 0.5);
+}
+
+template <typename T>
+void dump(const std::string& dir, const char* name, const T* p, size_t n) {
+  std::ofstream f(dir + "/" + name, std::ios::binary);
+  f.write(reinterpret_cast<const char*>(p), sizeof(T) * n);
+}
+
+struct Setup {
+  std::unique_ptr<mfem::Mesh> mesh;
+  std::unique_ptr<mfem::FiniteElementSpace> fes;
+  std::shared_ptr<mimi::utils::PrecomputedData> pre;
+  std::shared_ptr<mimi::materials::MaterialBase> mat;
+  std::shared_ptr<mimi::integrators::NonlinearSolid> integ;
+  std::unique_ptr<mfem::BilinearForm> mass;
+  double t_precompute = 0.0;
+};
+
+Setup build(const char* mesh_file, int elevate, int refine, const std::string& material, int nthreads,
+            bool with_mass) {
+  Setup s;
+  s.mesh = std::make_unique<mfem::Mesh>(mesh_file, 1, 1);  // py_solid.cpp:76
+  if (elevate > 0) s.mesh->DegreeElevate(elevate, 50);     // py_solid.cpp:155
+  for (int i = 0; i < refine; ++i) s.mesh->UniformRefinement();  // py_solid.cpp:177
+  auto* fec = s.mesh->GetNodes()->OwnFEC();
+  s.fes = std::make_unique<mfem::FiniteElementSpace>(s.mesh.get(), nullptr, fec, s.mesh->Dimension(),
+                                                     mfem::Ordering::byVDIM);
+  if (material == "neohookean") s.mat = std::make_shared<mimi::materials::CompressibleOgdenNeoHookean>();
+  else if (material == "stvk") s.mat = std::make_shared<mimi::materials::StVenantKirchhoff>();
+  else { std::fprintf(stderr, "unknown material %s\n", material.c_str()); std::exit(2); }
+  s.mat->density_ = 1.0;
+  s.mat->viscosity_ = -1.0;
+  s.mat->SetYoungPoisson(2100.0, 0.3);
+
+  auto t0 = std::chrono::steady_clock::now();
+  s.pre = std::make_shared<mimi::utils::PrecomputedData>();
+  s.pre->PrepareThreadSafety(*s.fes, nthreads);
+  s.pre->PrepareElementData();
+  s.pre->PrepareSparsity();
+  s.pre->CreateElementQuadData("domain", nullptr);
+  if (with_mass) {
+    s.mass = std::make_unique<mfem::BilinearForm>(s.fes.get());
+    mfem::ConstantCoefficient rho(s.mat->density_);
+    s.mass->AddDomainIntegrator(new mfem::VectorMassIntegrator(rho));
+    s.mass->Assemble(0);
+    s.mass->Finalize(0);
+    s.mass->SpMat().SortColumnIndices();  // operators/nonlinear_solid.cpp:86-122 expects sorted CSR
+  }
+  s.integ = std::make_shared<mimi::integrators::NonlinearSolid>(s.mat->Name() + "-NonlinearSolid", s.mat, s.pre);
+  s.pre->PrecomputeElementQuadData("domain", -1, true);
+  s.integ->Prepare();
+  s.t_precompute = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  return s;
+}
+
+void fill_u(mfem::Vector& u, const char* u_file) {
+  if (std::strcmp(u_file, "-") == 0) {
+    for (int i = 0; i < u.Size(); ++i) u[i] = synth_u(12345, (uint64_t)i);
+  } else {
+    std::ifstream f(u_file, std::ios::binary);
+    f.read(reinterpret_cast<char*>(u.GetData()), sizeof(double) * u.Size());
+    if (!f) { std::fprintf(stderr, "short read of %s\n", u_file); std::exit(2); }
+  }
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  if (argc < 8) { std::fprintf(stderr, "usage: see header of oracle/ref_harness.cpp\n"); return 2; }
+  const std::string mode = argv[1];
+  const char* mesh_file = argv[2];
+  const int elevate = std::atoi(argv[3]), refine = std::atoi(argv[4]);
+  const std::string material = argv[5];
+  const int nthreads = std::atoi(argv[6]);
+  std::cout.setstate(std::ios_base::failbit);  // silence the reference's PrintInfo chatter
+
+  if (mode == "dump") {
+    const double gf = std::atof(argv[7]);
+    const char* u_file = argv[8];
+    const std::string out = argv[9];
+    const bool lite = argc > 10 && std::strcmp(argv[10], "lite") == 0;
+    Setup s = build(mesh_file, elevate, refine, material, nthreads, true);
+    auto& pre = *s.pre;
+    const int NV = pre.n_v_dofs_, NE = pre.n_elements_;
+    mfem::SparseMatrix& sp = *pre.sparsity_pattern_;
+    const int nnz = sp.NumNonZeroElems();
+    dump(out, "I.i32", sp.GetI(), (size_t)NV + 1);
+    dump(out, "J.i32", sp.GetJ(), (size_t)nnz);
+    auto& eqd = pre.GetElementQuadData("domain");
+    const int tdof = eqd[0].GetElementData().n_tdof, nd = eqd[0].GetElementData().n_dof, nq = eqd[0].n_quad;
+    const int dim = pre.dim_;
+    std::vector<int> vd((size_t)NE * tdof), aid;
+    std::vector<double> w((size_t)NE * nq), dj((size_t)NE * nq), N, dxi, dX((size_t)NE * nq * nd * dim);
+    if (!lite) { aid.resize((size_t)NE * tdof * tdof); N.resize((size_t)NE * nq * nd); dxi.resize((size_t)NE * nq * nd * dim); }
+    for (int e = 0; e < NE; ++e) {
+      const auto& ed = eqd[e].GetElementData();
+      std::memcpy(&vd[(size_t)e * tdof], ed.v_dofs.GetData(), sizeof(int) * tdof);
+      if (!lite) std::memcpy(&aid[(size_t)e * tdof * tdof], ed.A_ids.data(), sizeof(int) * tdof * tdof);
+      for (int q = 0; q < nq; ++q) {
+        const auto& qd = eqd[e].GetQuadData()[q];
+        const size_t eq = (size_t)e * nq + q;
+        w[eq] = qd.integration_weight; dj[eq] = qd.det_dX_dxi;
+        std::memcpy(&dX[eq * nd * dim], qd.dN_dX.GetData(), sizeof(double) * nd * dim);
+        if (!lite) {
+          std::memcpy(&N[eq * nd], qd.N.GetData(), sizeof(double) * nd);
+          std::memcpy(&dxi[eq * nd * dim], qd.dN_dxi.GetData(), sizeof(double) * nd * dim);
+        }
+      }
+    }
+    dump(out, "v_dofs.i32", vd.data(), vd.size());
+    dump(out, "w.f64", w.data(), w.size());
+    dump(out, "detJ.f64", dj.data(), dj.size());
+    dump(out, "dN_dX.f64", dX.data(), dX.size());
+    if (!lite) {
+      dump(out, "A_ids.i32", aid.data(), aid.size());
+      dump(out, "N.f64", N.data(), N.size());
+      dump(out, "dN_dxi.f64", dxi.data(), dxi.size());
+    }
+    // nodes (x_ref) in the FE space's byVDIM ordering
+    mfem::GridFunction& nodes = *s.mesh->GetNodes();
+    dump(out, "x_ref.f64", nodes.GetData(), (size_t)nodes.Size());
+
+    mfem::Vector u(NV), r(NV), r2(NV);
+    fill_u(u, u_file);
+    dump(out, "u.f64", u.GetData(), (size_t)NV);
+    r = 0.0;
+    s.integ->AddDomainResidual(u, r);
+    dump(out, "r.f64", r.GetData(), (size_t)NV);
+    // Jacobian = copy of the mass CSR (operators/nonlinear_solid.cpp:114-121,257) + gf * K
+    mfem::SparseMatrix A(s.mass->SpMat());
+    if (A.NumNonZeroElems() != nnz) { std::fprintf(stderr, "mass pattern != sparsity pattern\n"); return 3; }
+    dump(out, "mass.f64", A.GetData(), (size_t)nnz);
+    r2 = 0.0;
+    s.integ->AddDomainResidualAndGrad(u, gf, r2, A);
+    dump(out, "r2.f64", r2.GetData(), (size_t)NV);
+    dump(out, "A.f64", A.GetData(), (size_t)nnz);
+    std::ofstream m(out + "/meta.json");
+    m << "{\"NV\": " << NV << ", \"NE\": " << NE << ", \"nnz\": " << nnz << ", \"nd\": " << nd << ", \"nq\": " << nq
+      << ", \"dim\": " << dim << ", \"tdof\": " << tdof << ", \"gf\": " << gf << ", \"nthreads\": " << nthreads
+      << ", \"material\": \"" << material << "\", \"lambda\": " << std::hexfloat << s.mat->lambda_ << ", \"mu\": "
+      << s.mat->mu_ << std::defaultfloat << ", \"lite\": " << (lite ? 1 : 0) << "}\n";
+    return 0;
+  }
+  if (mode == "time") {
+    const int reps = std::atoi(argv[7]);
+    Setup s = build(mesh_file, elevate, refine, material, nthreads, false);
+    auto& pre = *s.pre;
+    const int NV = pre.n_v_dofs_, NE = pre.n_elements_;
+    const int nq = pre.GetElementQuadData("domain")[0].n_quad;
+    mfem::Vector u(NV), r(NV);
+    fill_u(u, "-");
+    mfem::SparseMatrix A(*pre.sparsity_pattern_);
+    double best_rg = 1e300, best_r = 1e300, sum_rg = 0;
+    for (int i = 0; i < reps; ++i) {
+      r = 0.0; A = 0.0;
+      auto t0 = std::chrono::steady_clock::now();
+      s.integ->AddDomainResidualAndGrad(u, 1.0, r, A);
+      double t = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+      best_rg = std::min(best_rg, t); sum_rg += t;
+      r = 0.0;
+      t0 = std::chrono::steady_clock::now();
+      s.integ->AddDomainResidual(u, r);
+      t = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+      best_r = std::min(best_r, t);
+    }
+    std::fprintf(stderr,
+                 "{\"NE\": %d, \"nq\": %d, \"NV\": %d, \"nnz\": %d, \"nthreads\": %d, \"reps\": %d, "
+                 "\"t_res_grad_best\": %.6f, \"t_res_grad_mean\": %.6f, \"t_res_best\": %.6f, \"t_precompute\": %.3f}\n",
+                 NE, nq, NV, A.NumNonZeroElems(), nthreads, reps, best_rg, sum_rg / reps, best_r, s.t_precompute);
+    return 0;
+  }
+  std::fprintf(stderr, "unknown mode\n");
+  return 2;
+}
