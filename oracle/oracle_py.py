@@ -1,0 +1,144 @@
+"""TEST INFRASTRUCTURE: ctypes loader for the plain-C oracle (oracle/mimi_oracle.c) and a runner for the
+compiled reference (oracle/_ref/mimi_ref). Imported only by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs -- never by mimi_b200/."""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "libmimi_oracle.so")
+REF_BIN = os.path.join(HERE, "_ref", "mimi_ref")
+
+NEOHOOKEAN, STVK = 0, 1
+
+
+class Material(C.Structure):
+    _fields_ = [("kind", C.c_int), ("lam", C.c_double), ("mu", C.c_double)]
+
+
+def lame(young=2100.0, poisson=0.3):
+    """MaterialBase::SetYoungPoisson, src/mimi/materials/materials.cpp:7-14 (same expression order)."""
+    lam = young * poisson / ((1 + poisson) * (1 - 2 * poisson))
+    mu = young / (2.0 * (1.0 + poisson))
+    return lam, mu
+
+
+def build_oracle(force=False):
+    src = os.path.join(HERE, "mimi_oracle.c")
+    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(src):
+        subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", LIB, src, "-lm"])
+    return LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build_oracle()
+        _lib = C.CDLL(LIB)
+        _lib.orc_build_pattern.restype = C.c_int64
+    return _lib
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def mat(kind, young=2100.0, poisson=0.3):
+    lam, mu = lame(young, poisson)
+    return Material(kind, lam, mu)
+
+
+def assemble_residual(dim, nd, nq, m, v_dofs, dN_dX, w, detJ, u):
+    NE = v_dofs.shape[0]
+    r = np.zeros_like(u)
+    rc = lib().orc_assemble_residual(C.c_int(dim), C.c_int(nd), C.c_int(nq), C.c_int64(NE), C.c_int64(u.size),
+                                     C.byref(m), _p(v_dofs, C.c_int32), _p(dN_dX, C.c_double), _p(w, C.c_double),
+                                     _p(detJ, C.c_double), _p(u, C.c_double), _p(r, C.c_double))
+    assert rc == 0
+    return r
+
+
+def assemble_residual_and_grad(dim, nd, nq, m, v_dofs, A_ids, dN_dX, w, detJ, u, gf, A0):
+    NE = v_dofs.shape[0]
+    r = np.zeros_like(u)
+    A = A0.copy()
+    rc = lib().orc_assemble_residual_and_grad(C.c_int(dim), C.c_int(nd), C.c_int(nq), C.c_int64(NE), C.c_int64(u.size),
+                                              C.c_int64(A.size), C.byref(m), _p(v_dofs, C.c_int32),
+                                              _p(A_ids, C.c_int32), _p(dN_dX, C.c_double), _p(w, C.c_double),
+                                              _p(detJ, C.c_double), _p(u, C.c_double), C.c_double(gf),
+                                              _p(r, C.c_double), _p(A, C.c_double))
+    assert rc == 0
+    return r, A
+
+
+def build_pattern(tdof, v_dofs, NV):
+    NE = v_dofs.shape[0]
+    I = np.zeros(NV + 1, np.int32)
+    nnz = lib().orc_build_pattern(C.c_int(tdof), C.c_int64(NE), C.c_int64(NV), _p(v_dofs, C.c_int32),
+                                  _p(I, C.c_int32), None)
+    J = np.zeros(nnz, np.int32)
+    lib().orc_build_pattern(C.c_int(tdof), C.c_int64(NE), C.c_int64(NV), _p(v_dofs, C.c_int32), _p(I, C.c_int32),
+                            _p(J, C.c_int32))
+    return I, J
+
+
+def build_A_ids(tdof, v_dofs, I, J):
+    NE = v_dofs.shape[0]
+    A_ids = np.zeros((NE, tdof * tdof), np.int32)
+    lib().orc_build_A_ids(C.c_int(tdof), C.c_int64(NE), _p(v_dofs, C.c_int32), _p(I, C.c_int32), _p(J, C.c_int32),
+                          _p(A_ids, C.c_int32))
+    return A_ids
+
+
+# ---------------------------------------------------------------- compiled reference (oracle/_ref)
+def have_ref():
+    return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
+
+
+def load_dump(d):
+    meta = json.load(open(os.path.join(d, "meta.json")))
+    NE, nd, nq, dim, tdof = meta["NE"], meta["nd"], meta["nq"], meta["dim"], meta["tdof"]
+    out = dict(meta)
+
+    def rd(name, dt, shape=None):
+        p = os.path.join(d, name)
+        if not os.path.exists(p):
+            return None
+        a = np.fromfile(p, dtype=dt)
+        return a.reshape(shape) if shape else a
+
+    out["I"] = rd("I.i32", np.int32)
+    out["J"] = rd("J.i32", np.int32)
+    out["v_dofs"] = rd("v_dofs.i32", np.int32, (NE, tdof))
+    out["A_ids"] = rd("A_ids.i32", np.int32, (NE, tdof * tdof))
+    out["w"] = rd("w.f64", np.float64, (NE, nq))
+    out["detJ"] = rd("detJ.f64", np.float64, (NE, nq))
+    out["dN_dX"] = rd("dN_dX.f64", np.float64, (NE, nq, dim, nd))
+    out["dN_dxi"] = rd("dN_dxi.f64", np.float64, (NE, nq, dim, nd))
+    out["N"] = rd("N.f64", np.float64, (NE, nq, nd))
+    for k in ("x_ref", "u", "r", "r2", "mass", "A"):
+        out[k] = rd(k + ".f64", np.float64)
+    return out
+
+
+def run_ref_dump(mesh, elevate, refine, material, outdir, gf=1.0, nthreads=1, u_file="-", lite=False):
+    os.makedirs(outdir, exist_ok=True)
+    cmd = [REF_BIN, "dump", mesh, str(elevate), str(refine), material, str(nthreads), repr(gf), u_file, outdir]
+    if lite:
+        cmd.append("lite")
+    subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+    return load_dump(outdir)
+
+
+def run_ref_time(mesh, elevate, refine, material, nthreads, reps):
+    cmd = [REF_BIN, "time", mesh, str(elevate), str(refine), material, str(nthreads), str(reps)]
+    p = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, check=True, text=True)
+    return json.loads(p.stderr.strip().splitlines()[-1])

@@ -179,8 +179,8 @@ int main(int argc, char** argv) {
     std::ofstream m(out + "/meta.json");
     m << "{\"NV\": " << NV << ", \"NE\": " << NE << ", \"nnz\": " << nnz << ", \"nd\": " << nd << ", \"nq\": " << nq
       << ", \"dim\": " << dim << ", \"tdof\": " << tdof << ", \"gf\": " << gf << ", \"nthreads\": " << nthreads
-      << ", \"material\": \"" << material << "\", \"lambda\": " << std::hexfloat << s.mat->lambda_ << ", \"mu\": "
-      << s.mat->mu_ << std::defaultfloat << ", \"lite\": " << (lite ? 1 : 0) << "}\n";
+      << ", \"material\": \"" << material << "\", \"lambda\": \"" << std::hexfloat << s.mat->lambda_ << "\", \"mu\": \""
+      << s.mat->mu_ << std::defaultfloat << "\", \"lite\": " << (lite ? 1 : 0) << "}\n";
     return 0;
   }
   if (mode == "time") {
