@@ -1,0 +1,131 @@
+/*
+ * mimi_b200 -- C ABI of the B200-native residual + tangent CSR assembly path of j042/mimi.
+ *
+ * This is the drop-in boundary: plain C types, caller-owned host buffers, library-owned device
+ * buffers, 0 = success / non-zero = error (message via mb2_last_error). A maintainer of the
+ * reference binds these from a `mimi::integrators::NonlinearBase` subclass;
+ * each entry cites the reference interface it replaces. There is NO CPU fallback: every compute
+ * entry fails with MB2_ERR_CUDA when no sm_100a device / CUDA runtime is usable.
+ *
+ * Conventions shared with the reference:
+ *  - all matrices column-major (mfem::DenseMatrix); FP64 throughout;
+ *  - vdof ordering is mfem::Ordering::byVDIM (src/mimi/py/py_nonlinear_solid.cpp:63,74): global
+ *    vdof = dim*node + component; element vdofs are component-major: v_dofs[c*nd + a];
+ *  - entries ADD into the residual and into the CSR values they are given
+ *    (src/mimi/integrators/nonlinear_base.hpp:90-151).
+ */
+#ifndef MIMI_B200_H
+#define MIMI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mb2_ctx mb2_ctx;
+
+enum {
+  MB2_OK = 0,
+  MB2_ERR_ARG = 1,      /* bad argument / call order */
+  MB2_ERR_CUDA = 2,     /* CUDA runtime error or no device */
+  MB2_ERR_UNSUPPORTED = 3,
+  MB2_ERR_NUMERIC = 4   /* device-side failure flag (det F <= 0, scalar solve not converged) */
+};
+
+/* material ids: src/mimi/materials/materials.hpp (Name()) */
+enum {
+  MB2_MAT_NEOHOOKEAN = 0, /* CompressibleOgdenNeoHookean, materials.cpp:96-118; params {lambda, mu} */
+  MB2_MAT_STVK = 1        /* StVenantKirchhoff,           materials.cpp:73-94;  params {lambda, mu} */
+};
+
+/* tangent modes */
+enum {
+  MB2_TANGENT_FD_PARITY = 0 /* forward finite difference in the reference's exact operation order
+                               (src/mimi/integrators/nonlinear_solid.cpp:48-76), no FMA */
+};
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+/* device: CUDA ordinal. stream: a cudaStream_t cast to void* (NULL = the library creates its own).
+ * Replaces: construction of mimi::integrators::NonlinearSolid (nonlinear_solid.hpp:45-50). */
+int mb2_create(mb2_ctx** out, int device, void* stream);
+int mb2_destroy(mb2_ctx* ctx);
+/* Error text of the last failing call on ctx (ctx may be NULL for create failures). */
+const char* mb2_last_error(const mb2_ctx* ctx);
+/* Library/ABI version, for the loader check. */
+int mb2_version(void);
+
+/* ---- setup: what PrecomputedData holds (src/mimi/utils/precomputed.hpp:58-130) ------------------ */
+/* Element connectivity. v_dofs: NE x (dim*nd) int32, component-major per element, byVDIM global ids
+ * (ElementData::v_dofs, precomputed.cpp:86). NV = number of vdofs = dim * number of nodes.
+ * elem_offset: global id of this rank's first element (0 on one GPU); elements must be passed in
+ * ascending global order -- the deterministic scatter adds contributions in that order. */
+int mb2_set_connectivity(mb2_ctx* ctx, int dim, int nd, int nq, int64_t NE, int64_t NV, const int32_t* v_dofs);
+
+/* Flat per-quadrature-point tables exactly as the reference precomputes them
+ * (PrecomputeElementQuadData, precomputed.cpp:264-330): dN_dX NE x nq x (nd x dim col-major),
+ * w and detJ NE x nq (QuadData::integration_weight, det_dX_dxi). Host pointers. */
+int mb2_upload_quad_tables(mb2_ctx* ctx, const double* dN_dX, const double* w, const double* detJ);
+
+/* Device-side regeneration of the same tables for one tensor-product NURBS patch from its knot
+ * vectors, weights and control net, in MFEM's arithmetic order (third_party/mfem/mesh/nurbs.cpp:297-322,
+ * fem/fe/fe_nurbs.cpp:243-311, precomputed.cpp:289-321). knots[d] has ncp[d]+p+1 entries; el_ijk is
+ * NE x dim (knot-span index of every element); x_ref / weights are indexed by node (x_ref byVDIM).
+ * quad_order < 0 selects the reference default 2p+3. */
+int mb2_generate_patch_tables(mb2_ctx* ctx, int p, const int32_t* ncp, const double* const* knots,
+                              const int32_t* el_ijk, const double* x_ref, const double* weights,
+                              int quad_order);
+
+/* Copies the device tables back (tests). Any pointer may be NULL. */
+int mb2_download_quad_tables(mb2_ctx* ctx, double* dN_dX, double* w_detJ);
+
+/* Sparsity pattern built ON DEVICE from the connectivity (replaces PrepareSparsity,
+ * precomputed.cpp:151-218): rows = vdofs, columns ascending. Returns nnz. */
+int mb2_build_pattern(mb2_ctx* ctx, int64_t* nnz);
+/* Pattern hand-back. I: NV+1 row offsets, J: nnz columns. The 32-bit form fails with
+ * MB2_ERR_UNSUPPORTED when nnz does not fit int (the reference's own limit, precomputed.cpp:196-199). */
+int mb2_get_pattern_i32(mb2_ctx* ctx, int32_t* I, int32_t* J);
+int mb2_get_pattern_i64(mb2_ctx* ctx, int64_t* I, int32_t* J);
+/* Element -> CSR value index map in the reference's layout (ElementData::A_ids, precomputed.cpp:183-199),
+ * expanded on device from the factored map; for parity tests. A_ids: NE x tdof^2 int32. */
+int mb2_get_A_ids_i32(mb2_ctx* ctx, int32_t* A_ids);
+
+/* MaterialBase parameters (materials.hpp:24-40). */
+int mb2_set_material(mb2_ctx* ctx, int kind, const double* params, int nparams);
+
+/* ---- the hot path, host-buffer form (what the integrator virtuals forward to) ------------------- */
+/* r += R(u).  Replaces NonlinearSolid::AddDomainResidual (nonlinear_solid.cpp:151-160). */
+int mb2_add_domain_residual(mb2_ctx* ctx, const double* u, double* r);
+/* r += R(u); A_values += grad_factor * K_fd(u), in the reference's accumulation order.
+ * Replaces NonlinearSolid::AddDomainResidualAndGrad (nonlinear_solid.cpp:162-177). A_values holds
+ * the nnz values of the CSR whose pattern is mb2_build_pattern's (already containing the mass). */
+int mb2_add_domain_residual_and_grad(mb2_ctx* ctx, const double* u, double grad_factor, double* r,
+                                     double* A_values);
+
+/* ---- the hot path, device-resident form (solver-on-device callers, bench) ------------------------ */
+int mb2_set_u(mb2_ctx* ctx, const double* u_host);                 /* H2D into the resident u */
+int mb2_set_r(mb2_ctx* ctx, const double* r_host);                 /* NULL = zero */
+int mb2_set_A(mb2_ctx* ctx, const double* A_host);                 /* NULL = zero */
+int mb2_get_r(mb2_ctx* ctx, double* r_host);
+int mb2_get_A(mb2_ctx* ctx, double* A_host);
+int mb2_assemble_residual_device(mb2_ctx* ctx);                    /* r_dev += R(u_dev) */
+int mb2_assemble_residual_and_grad_device(mb2_ctx* ctx, double grad_factor);
+/* Raw device pointers of the resident arrays (u: NV, r: NV, A: nnz doubles). */
+int mb2_device_pointers(mb2_ctx* ctx, void** u, void** r, void** A);
+
+/* Milliseconds of the kernels of the last assemble call, from CUDA events on ctx's stream:
+ * out[0] = element kernel (FD tangent or residual), out[1] = CSR/residual gather-scatter, out[2] = total. */
+int mb2_last_timing_ms(mb2_ctx* ctx, float* out3);
+/* Kernel launches issued by the last assemble call. */
+int mb2_last_launch_count(mb2_ctx* ctx);
+/* Synchronise ctx's stream. */
+int mb2_sync(mb2_ctx* ctx);
+
+/* FP64 pipe micro-benchmark used for the roofline denominator: runs `iters` dependent-chain-free
+ * DMUL+DADD pairs (fma = 0) or DFMA (fma = 1) per thread on a full grid; returns TFLOP/s. */
+int mb2_measure_fp64_peak(mb2_ctx* ctx, int fma, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIMI_B200_H */

@@ -1,0 +1,163 @@
+"""ctypes binding of the C ABI in include/mimi_b200.h (the same symbols a cgo/pybind caller binds).
+
+There is no CPU fallback: importing works anywhere, but every call needs libmimi_b200.so (built by
+``__graft_entry__.build()`` / ``make -C mimi_b200/csrc``) and, for compute, an sm_100a GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmimi_b200.so")
+
+MB2_MAT_NEOHOOKEAN, MB2_MAT_STVK = 0, 1
+
+# every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
+SYMBOLS = [
+    "mb2_create", "mb2_destroy", "mb2_last_error", "mb2_version", "mb2_set_connectivity",
+    "mb2_upload_quad_tables", "mb2_generate_patch_tables", "mb2_download_quad_tables", "mb2_build_pattern",
+    "mb2_get_pattern_i32", "mb2_get_pattern_i64", "mb2_get_A_ids_i32", "mb2_set_material",
+    "mb2_add_domain_residual", "mb2_add_domain_residual_and_grad", "mb2_set_u", "mb2_set_r", "mb2_set_A",
+    "mb2_get_r", "mb2_get_A", "mb2_assemble_residual_device", "mb2_assemble_residual_and_grad_device",
+    "mb2_device_pointers", "mb2_last_timing_ms", "mb2_last_launch_count", "mb2_sync", "mb2_measure_fp64_peak",
+]
+
+
+class Mb2Error(RuntimeError):
+    """Mirrors mimi::utils::PrintAndThrowError -> std::runtime_error -> Python RuntimeError
+    (src/mimi/utils/print.hpp:49-56)."""
+
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise Mb2Error("libmimi_b200.so is not built (run __graft_entry__.build()); there is no CPU fallback")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.mb2_last_error.restype = C.c_char_p
+        _lib.mb2_last_error.argtypes = [C.c_void_p]
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class Context:
+    """Thin owner of an mb2_ctx*."""
+
+    def __init__(self, device=0, stream=None):
+        self.lib = load()
+        self.h = C.c_void_p()
+        rc = self.lib.mb2_create(C.byref(self.h), C.c_int(device), C.c_void_p(stream or 0))
+        if rc:
+            raise Mb2Error(self.lib.mb2_last_error(None).decode())
+
+    def _ck(self, rc):
+        if rc:
+            raise Mb2Error("mb2 error %d: %s" % (rc, self.lib.mb2_last_error(self.h).decode()))
+
+    def close(self):
+        if self.h:
+            self.lib.mb2_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- setup
+    def set_connectivity(self, dim, nd, nq, NV, v_dofs):
+        v = np.ascontiguousarray(v_dofs, np.int32)
+        self.dim, self.nd, self.nq, self.tdof, self.NE, self.NV = dim, nd, nq, dim * nd, v.shape[0], NV
+        self._ck(self.lib.mb2_set_connectivity(self.h, dim, nd, nq, C.c_int64(self.NE), C.c_int64(NV), _dp(v)))
+
+    def upload_quad_tables(self, dN_dX, w, detJ):
+        a, b, c = (np.ascontiguousarray(x, np.float64) for x in (dN_dX, w, detJ))
+        assert a.size == self.NE * self.nq * self.tdof and b.size == self.NE * self.nq == c.size
+        self._ck(self.lib.mb2_upload_quad_tables(self.h, _dp(a), _dp(b), _dp(c)))
+
+    def download_quad_tables(self):
+        dN = np.empty((self.NE, self.nq, self.dim, self.nd))
+        wd = np.empty((self.NE, self.nq))
+        self._ck(self.lib.mb2_download_quad_tables(self.h, _dp(dN), _dp(wd)))
+        return dN, wd
+
+    def build_pattern(self):
+        nnz = C.c_int64()
+        self._ck(self.lib.mb2_build_pattern(self.h, C.byref(nnz)))
+        self.nnz = nnz.value
+        return self.nnz
+
+    def get_pattern(self, i64=False):
+        I = np.empty(self.NV + 1, np.int64 if i64 else np.int32)
+        J = np.empty(self.nnz, np.int32)
+        f = self.lib.mb2_get_pattern_i64 if i64 else self.lib.mb2_get_pattern_i32
+        self._ck(f(self.h, _dp(I), _dp(J)))
+        return I, J
+
+    def get_A_ids(self):
+        A = np.empty((self.NE, self.tdof * self.tdof), np.int32)
+        self._ck(self.lib.mb2_get_A_ids_i32(self.h, _dp(A)))
+        return A
+
+    def set_material(self, kind, params):
+        p = np.ascontiguousarray(params, np.float64)
+        self._ck(self.lib.mb2_set_material(self.h, kind, _dp(p), p.size))
+
+    # ---- host-buffer hot path
+    def add_domain_residual(self, u, r):
+        self._ck(self.lib.mb2_add_domain_residual(self.h, _dp(u), _dp(r)))
+
+    def add_domain_residual_and_grad(self, u, gf, r, A):
+        self._ck(self.lib.mb2_add_domain_residual_and_grad(self.h, _dp(u), C.c_double(gf), _dp(r), _dp(A)))
+
+    # ---- device-resident hot path
+    def set_u(self, u):
+        self._ck(self.lib.mb2_set_u(self.h, _dp(u)))
+
+    def set_r(self, r=None):
+        self._ck(self.lib.mb2_set_r(self.h, _dp(r)))
+
+    def set_A(self, A=None):
+        self._ck(self.lib.mb2_set_A(self.h, _dp(A)))
+
+    def get_r(self):
+        r = np.empty(self.NV)
+        self._ck(self.lib.mb2_get_r(self.h, _dp(r)))
+        return r
+
+    def get_A(self):
+        A = np.empty(self.nnz)
+        self._ck(self.lib.mb2_get_A(self.h, _dp(A)))
+        return A
+
+    def assemble_residual_device(self):
+        self._ck(self.lib.mb2_assemble_residual_device(self.h))
+
+    def assemble_residual_and_grad_device(self, gf):
+        self._ck(self.lib.mb2_assemble_residual_and_grad_device(self.h, C.c_double(gf)))
+
+    def last_timing_ms(self):
+        t = (C.c_float * 3)()
+        self._ck(self.lib.mb2_last_timing_ms(self.h, t))
+        return list(t)
+
+    def last_launch_count(self):
+        return self.lib.mb2_last_launch_count(self.h)
+
+    def sync(self):
+        self._ck(self.lib.mb2_sync(self.h))
+
+    def measure_fp64_peak(self, fma):
+        t = C.c_double()
+        self._ck(self.lib.mb2_measure_fp64_peak(self.h, int(fma), C.byref(t)))
+        return t.value

@@ -1,0 +1,333 @@
+// C ABI of libmimi_b200 (include/mimi_b200.h): context lifetime, uploads, hand-backs and the
+// host-buffer forms of the integrator entry points.
+#include <cstring>
+#include <new>
+
+#include "mb2_ctx.h"
+
+static thread_local std::string g_create_err;
+
+#define CHECK_CTX(c)          \
+  if (!(c)) return MB2_ERR_ARG
+#define REQUIRE(cond, msg)    \
+  if (!(cond)) {              \
+    c->err = (msg);           \
+    return MB2_ERR_ARG;       \
+  }
+
+template <typename T>
+static void dfree(T*& p) {
+  if (p) cudaFree(p);
+  p = nullptr;
+}
+
+static void free_problem(mb2_ctx* c) {
+  dfree(c->d_vdofs); dfree(c->d_enodes); dfree(c->d_dNdX); dfree(c->d_wdetJ);
+  dfree(c->d_n2e_ptr); dfree(c->d_n2e_elem); dfree(c->d_n2e_loc); dfree(c->d_nnbr); dfree(c->d_nodeptr);
+  dfree(c->d_nbr); dfree(c->d_rank); dfree(c->d_I); dfree(c->d_J);
+  dfree(c->d_u); dfree(c->d_r); dfree(c->d_A); dfree(c->d_Re); dfree(c->d_KeT);
+  c->have_pattern = false;
+  c->nnz = 0;
+}
+
+extern "C" {
+
+int mb2_version(void) { return 100; }
+
+const char* mb2_last_error(const mb2_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int mb2_create(mb2_ctx** out, int device, void* stream) {
+  if (!out) return MB2_ERR_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= device || device < 0) {
+    g_create_err = std::string("no usable CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "bad ordinal") +
+                   " (libmimi_b200 has no CPU fallback)";
+    return MB2_ERR_CUDA;
+  }
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess || prop.major < 10) {
+    g_create_err = "device is not sm_100-class; this library is built for sm_100a only";
+    return MB2_ERR_CUDA;
+  }
+  mb2_ctx* c = new (std::nothrow) mb2_ctx();
+  if (!c) return MB2_ERR_ARG;
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  cudaSetDevice(device);
+  if (stream) {
+    c->stream = (cudaStream_t)stream;
+  } else {
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+      g_create_err = "cudaStreamCreate failed";
+      delete c;
+      return MB2_ERR_CUDA;
+    }
+    c->own_stream = true;
+  }
+  for (auto& ev : c->ev) cudaEventCreate(&ev);
+  cudaMalloc(&c->d_flag, sizeof(int));
+  *out = c;
+  return MB2_OK;
+}
+
+int mb2_destroy(mb2_ctx* c) {
+  CHECK_CTX(c);
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  free_problem(c);
+  dfree(c->d_flag);
+  for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  if (c->own_stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return MB2_OK;
+}
+
+int mb2_set_connectivity(mb2_ctx* c, int dim, int nd, int nq, int64_t NE, int64_t NV, const int32_t* v_dofs) {
+  CHECK_CTX(c);
+  REQUIRE(dim == 2 || dim == 3, "dim must be 2 or 3");
+  REQUIRE(nd > 0 && nq > 0 && NE > 0 && NV > 0 && v_dofs, "bad connectivity arguments");
+  REQUIRE(NV % dim == 0, "NV must be dim * number of nodes");
+  MB2_CUDA(cudaSetDevice(c->device));
+  free_problem(c);
+  c->dim = dim; c->nd = nd; c->nq = nq; c->tdof = dim * nd; c->NE = NE; c->NV = NV; c->Nn = NV / dim;
+  MB2_CUDA(cudaMalloc(&c->d_vdofs, sizeof(int32_t) * NE * c->tdof));
+  MB2_CUDA(cudaMemcpyAsync(c->d_vdofs, v_dofs, sizeof(int32_t) * NE * c->tdof, cudaMemcpyHostToDevice, c->stream));
+  MB2_CUDA(cudaMalloc(&c->d_u, sizeof(double) * NV));
+  MB2_CUDA(cudaMalloc(&c->d_r, sizeof(double) * NV));
+  MB2_CUDA(cudaMalloc(&c->d_Re, sizeof(double) * NE * c->tdof));
+  MB2_CUDA(cudaMemsetAsync(c->d_u, 0, sizeof(double) * NV, c->stream));
+  MB2_CUDA(cudaMemsetAsync(c->d_r, 0, sizeof(double) * NV, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+
+__global__ void k_wdetj(int64_t n, const double* __restrict__ w, const double* __restrict__ dj, double* __restrict__ o) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) o[i] = w[i] * dj[i];  // q.integration_weight * q.det_dX_dxi, nonlinear_solid.hpp:79
+}
+
+int mb2_upload_quad_tables(mb2_ctx* c, const double* dN_dX, const double* w, const double* detJ) {
+  CHECK_CTX(c);
+  REQUIRE(c->NE > 0, "call mb2_set_connectivity first");
+  REQUIRE(dN_dX && w && detJ, "null table pointer");
+  MB2_CUDA(cudaSetDevice(c->device));
+  const int64_t nqp = c->NE * c->nq;
+  if (!c->d_dNdX) MB2_CUDA(cudaMalloc(&c->d_dNdX, sizeof(double) * nqp * c->tdof));
+  if (!c->d_wdetJ) MB2_CUDA(cudaMalloc(&c->d_wdetJ, sizeof(double) * nqp));
+  double *d_w = nullptr, *d_dj = nullptr;
+  MB2_CUDA(cudaMalloc(&d_w, sizeof(double) * nqp));
+  MB2_CUDA(cudaMalloc(&d_dj, sizeof(double) * nqp));
+  MB2_CUDA(cudaMemcpyAsync(c->d_dNdX, dN_dX, sizeof(double) * nqp * c->tdof, cudaMemcpyHostToDevice, c->stream));
+  MB2_CUDA(cudaMemcpyAsync(d_w, w, sizeof(double) * nqp, cudaMemcpyHostToDevice, c->stream));
+  MB2_CUDA(cudaMemcpyAsync(d_dj, detJ, sizeof(double) * nqp, cudaMemcpyHostToDevice, c->stream));
+  k_wdetj<<<(unsigned)((nqp + 255) / 256), 256, 0, c->stream>>>(nqp, d_w, d_dj, c->d_wdetJ);
+  MB2_CUDA(cudaGetLastError());
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  cudaFree(d_w);
+  cudaFree(d_dj);
+  return MB2_OK;
+}
+
+int mb2_download_quad_tables(mb2_ctx* c, double* dN_dX, double* w_detJ) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_dNdX && c->d_wdetJ, "no tables on device");
+  const int64_t nqp = c->NE * c->nq;
+  if (dN_dX) MB2_CUDA(cudaMemcpyAsync(dN_dX, c->d_dNdX, sizeof(double) * nqp * c->tdof, cudaMemcpyDeviceToHost, c->stream));
+  if (w_detJ) MB2_CUDA(cudaMemcpyAsync(w_detJ, c->d_wdetJ, sizeof(double) * nqp, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+
+int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
+  CHECK_CTX(c);
+  REQUIRE(kind == MB2_MAT_NEOHOOKEAN || kind == MB2_MAT_STVK, "unknown material kind");
+  REQUIRE(params && nparams >= 2, "material needs {lambda, mu}");
+  c->mat_kind = kind;
+  c->lambda = params[0];
+  c->mu = params[1];
+  return MB2_OK;
+}
+
+int mb2_build_pattern(mb2_ctx* c, int64_t* nnz) {
+  CHECK_CTX(c);
+  REQUIRE(c->NE > 0, "call mb2_set_connectivity first");
+  MB2_CUDA(cudaSetDevice(c->device));
+  if (!c->have_pattern) {
+    int rc = mb2::build_pattern(c);
+    if (rc) return rc;
+    MB2_CUDA(cudaMalloc(&c->d_A, sizeof(double) * c->nnz));
+    MB2_CUDA(cudaMemsetAsync(c->d_A, 0, sizeof(double) * c->nnz, c->stream));
+  }
+  if (nnz) *nnz = c->nnz;
+  return MB2_OK;
+}
+
+__global__ void k_i64_to_i32(int64_t n, const int64_t* __restrict__ in, int32_t* __restrict__ out) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (int32_t)in[i];
+}
+
+int mb2_get_pattern_i64(mb2_ctx* c, int64_t* I, int32_t* J) {
+  CHECK_CTX(c);
+  REQUIRE(c->have_pattern, "call mb2_build_pattern first");
+  if (I) MB2_CUDA(cudaMemcpyAsync(I, c->d_I, sizeof(int64_t) * (c->NV + 1), cudaMemcpyDeviceToHost, c->stream));
+  if (J) MB2_CUDA(cudaMemcpyAsync(J, c->d_J, sizeof(int32_t) * c->nnz, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+
+int mb2_get_pattern_i32(mb2_ctx* c, int32_t* I, int32_t* J) {
+  CHECK_CTX(c);
+  REQUIRE(c->have_pattern, "call mb2_build_pattern first");
+  if (c->nnz > 2147483647LL) {
+    c->err = "nnz does not fit a 32-bit int (the reference's own limit); use mb2_get_pattern_i64";
+    return MB2_ERR_UNSUPPORTED;
+  }
+  if (I) {
+    int32_t* d_tmp = nullptr;
+    MB2_CUDA(cudaMalloc(&d_tmp, sizeof(int32_t) * (c->NV + 1)));
+    k_i64_to_i32<<<(unsigned)((c->NV + 256) / 256), 256, 0, c->stream>>>(c->NV + 1, c->d_I, d_tmp);
+    MB2_CUDA(cudaMemcpyAsync(I, d_tmp, sizeof(int32_t) * (c->NV + 1), cudaMemcpyDeviceToHost, c->stream));
+    MB2_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(d_tmp);
+  }
+  if (J) MB2_CUDA(cudaMemcpyAsync(J, c->d_J, sizeof(int32_t) * c->nnz, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+
+int mb2_get_A_ids_i32(mb2_ctx* c, int32_t* A_ids) {
+  CHECK_CTX(c);
+  REQUIRE(c->have_pattern && A_ids, "call mb2_build_pattern first");
+  REQUIRE(c->nnz <= 2147483647LL, "nnz does not fit int");
+  const int64_t n = c->NE * c->tdof * c->tdof;
+  int32_t* d_tmp = nullptr;
+  MB2_CUDA(cudaMalloc(&d_tmp, sizeof(int32_t) * n));
+  int rc = mb2::expand_A_ids(c, d_tmp);
+  if (rc) return rc;
+  MB2_CUDA(cudaMemcpyAsync(A_ids, d_tmp, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  cudaFree(d_tmp);
+  return MB2_OK;
+}
+
+// ---- resident state ----
+int mb2_set_u(mb2_ctx* c, const double* u) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_u && u, "no problem set");
+  MB2_CUDA(cudaMemcpyAsync(c->d_u, u, sizeof(double) * c->NV, cudaMemcpyHostToDevice, c->stream));
+  return MB2_OK;
+}
+int mb2_set_r(mb2_ctx* c, const double* r) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_r, "no problem set");
+  if (r) MB2_CUDA(cudaMemcpyAsync(c->d_r, r, sizeof(double) * c->NV, cudaMemcpyHostToDevice, c->stream));
+  else MB2_CUDA(cudaMemsetAsync(c->d_r, 0, sizeof(double) * c->NV, c->stream));
+  return MB2_OK;
+}
+int mb2_set_A(mb2_ctx* c, const double* A) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_A, "call mb2_build_pattern first");
+  if (A) MB2_CUDA(cudaMemcpyAsync(c->d_A, A, sizeof(double) * c->nnz, cudaMemcpyHostToDevice, c->stream));
+  else MB2_CUDA(cudaMemsetAsync(c->d_A, 0, sizeof(double) * c->nnz, c->stream));
+  return MB2_OK;
+}
+int mb2_get_r(mb2_ctx* c, double* r) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_r && r, "no problem set");
+  MB2_CUDA(cudaMemcpyAsync(r, c->d_r, sizeof(double) * c->NV, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+int mb2_get_A(mb2_ctx* c, double* A) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_A && A, "call mb2_build_pattern first");
+  MB2_CUDA(cudaMemcpyAsync(A, c->d_A, sizeof(double) * c->nnz, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+int mb2_device_pointers(mb2_ctx* c, void** u, void** r, void** A) {
+  CHECK_CTX(c);
+  if (u) *u = c->d_u;
+  if (r) *r = c->d_r;
+  if (A) *A = c->d_A;
+  return MB2_OK;
+}
+
+static int ready(mb2_ctx* c, bool grad) {
+  REQUIRE(c->d_dNdX && c->d_wdetJ, "quadrature tables missing (mb2_upload_quad_tables / mb2_generate_patch_tables)");
+  REQUIRE(c->mat_kind >= 0, "material not set");
+  REQUIRE(c->have_pattern, "call mb2_build_pattern first");
+  (void)grad;
+  return MB2_OK;
+}
+
+int mb2_assemble_residual_device(mb2_ctx* c) {
+  CHECK_CTX(c);
+  int rc = ready(c, false);
+  if (rc) return rc;
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::launch_residual(c);
+}
+int mb2_assemble_residual_and_grad_device(mb2_ctx* c, double gf) {
+  CHECK_CTX(c);
+  int rc = ready(c, true);
+  if (rc) return rc;
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::launch_residual_and_grad(c, gf);
+}
+
+int mb2_add_domain_residual(mb2_ctx* c, const double* u, double* r) {
+  CHECK_CTX(c);
+  REQUIRE(u && r, "null vector");
+  int rc;
+  if ((rc = mb2_set_u(c, u))) return rc;
+  if ((rc = mb2_set_r(c, r))) return rc;
+  if ((rc = mb2_assemble_residual_device(c))) return rc;
+  return mb2_get_r(c, r);
+}
+int mb2_add_domain_residual_and_grad(mb2_ctx* c, const double* u, double gf, double* r, double* A) {
+  CHECK_CTX(c);
+  REQUIRE(u && r && A, "null vector");
+  int rc;
+  if ((rc = mb2_set_u(c, u))) return rc;
+  if ((rc = mb2_set_r(c, r))) return rc;
+  if ((rc = mb2_set_A(c, A))) return rc;
+  if ((rc = mb2_assemble_residual_and_grad_device(c, gf))) return rc;
+  if ((rc = mb2_get_r(c, r))) return rc;
+  return mb2_get_A(c, A);
+}
+
+int mb2_last_timing_ms(mb2_ctx* c, float* out3) {
+  CHECK_CTX(c);
+  REQUIRE(out3, "null");
+  MB2_CUDA(cudaEventSynchronize(c->ev[2]));
+  MB2_CUDA(cudaEventElapsedTime(&out3[0], c->ev[0], c->ev[1]));
+  MB2_CUDA(cudaEventElapsedTime(&out3[1], c->ev[1], c->ev[2]));
+  MB2_CUDA(cudaEventElapsedTime(&out3[2], c->ev[0], c->ev[2]));
+  return MB2_OK;
+}
+int mb2_last_launch_count(mb2_ctx* c) { return c ? c->last_launches : 0; }
+int mb2_sync(mb2_ctx* c) {
+  CHECK_CTX(c);
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+int mb2_measure_fp64_peak(mb2_ctx* c, int fma, double* tflops) {
+  CHECK_CTX(c);
+  REQUIRE(tflops, "null");
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::launch_fp64_peak(c, fma, tflops);
+}
+
+int mb2_generate_patch_tables(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                              const double* x_ref, const double* weights, int quad_order) {
+  CHECK_CTX(c);
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::generate_patch_tables(c, p, ncp, knots, el_ijk, x_ref, weights, quad_order);
+}
+
+}  // extern "C"

@@ -1,0 +1,384 @@
+// Element quadrature kernels (residual, finite-difference tangent) and the deterministic,
+// atomic-free scatter into the residual vector and the CSR value array.
+//
+// Reference path replaced: NonlinearSolid::ThreadLocalResidual[AndGrad] + ElementResidual[AndGrad]
+// (src/mimi/integrators/nonlinear_solid.cpp:48-149, nonlinear_solid.hpp:65-87) and
+// NonlinearBase::AddThreadLocalResidual[AndGrad] (src/mimi/integrators/nonlinear_base.hpp:90-151).
+//
+// Compiled -fmad=false: every value is produced by the reference's operation sequence, so results
+// are bit-identical to the reference at nthreads=1.
+#include <cstdio>
+
+#include "mb2_ctx.h"
+#include "mb2_math.cuh"
+
+namespace mb2 {
+
+struct ElemArgs {
+  int64_t NE;
+  const int32_t* __restrict__ vdofs;
+  const double* __restrict__ dNdX;
+  const double* __restrict__ wdetJ;
+  const double* __restrict__ u;
+  double* __restrict__ Re;
+  double* __restrict__ KeT;
+  double lambda, mu;
+};
+
+template <int DIM, int ND, int NQ>
+struct ElemCfg {
+  static constexpr int TD = DIM * ND;
+  static constexpr int DD = DIM * DIM;
+  static constexpr int NT = ((TD > NQ ? TD : NQ) + 31) / 32 * 32;
+  // shared memory carve-up (doubles)
+  static constexpr int OFF_DN = 0;
+  static constexpr int OFF_FB = OFF_DN + NQ * TD;
+  static constexpr int OFF_BQ = OFF_FB + NQ * DD;
+  static constexpr int OFF_WD = OFF_BQ + NQ * DD;
+  static constexpr int OFF_UE = OFF_WD + NQ;
+  static constexpr int OFF_RB = OFF_UE + TD;
+  static constexpr int SMEM_DOUBLES = OFF_RB + TD;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
+};
+
+// One CTA per element (grid-stride). Thread t < TD owns residual entry t = i + j*ND in the base pass
+// and perturbed dof t (component c = t/ND, node a = t%ND) in the finite-difference pass.
+template <int DIM, int ND, int NQ, int MAT, bool GRAD, int MINB>
+__global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel(const ElemArgs g) {
+  using Cfg = ElemCfg<DIM, ND, NQ>;
+  constexpr int TD = Cfg::TD, DD = Cfg::DD, NT = Cfg::NT;
+  extern __shared__ __align__(16) double smem[];
+  double* sdN = smem + Cfg::OFF_DN;
+  double* sFb = smem + Cfg::OFF_FB;
+  double* sbq = smem + Cfg::OFF_BQ;
+  double* swd = smem + Cfg::OFF_WD;
+  double* sue = smem + Cfg::OFF_UE;
+  double* sRb = smem + Cfg::OFF_RB;
+  const int t = threadIdx.x;
+
+  for (int64_t e = blockIdx.x; e < g.NE; e += gridDim.x) {
+    // ---- stage the element: gathered dofs (Vector::GetSubVector), weights, dN_dX tables
+    if (t < TD) sue[t] = g.u[g.vdofs[e * TD + t]];
+    if (t < NQ) swd[t] = g.wdetJ[e * NQ + t];
+    {
+      const double2* src = reinterpret_cast<const double2*>(g.dNdX + e * (int64_t)(NQ * TD));
+      double2* dst = reinterpret_cast<double2*>(sdN);
+      constexpr int N2 = NQ * TD / 2;
+      for (int i = t; i < N2; i += NT) dst[i] = src[i];
+      if ((NQ * TD) % 2) {
+        if (t == 0) sdN[NQ * TD - 1] = g.dNdX[e * (int64_t)(NQ * TD) + NQ * TD - 1];
+      }
+    }
+    __syncthreads();
+
+    // ---- base pass A: one thread per quadrature point: F, P, b = (w detJ) P
+    if (t < NQ) {
+      const double* dN = sdN + t * TD;
+      double F[DD], P[DD];
+      // mfem::MultAtB(element_x_mat_, dN_dX, F_) then AddDiagonal(1.0)  (integrator_utils.cpp:33-40)
+#pragma unroll
+      for (int j = 0; j < DIM; j++)
+#pragma unroll
+        for (int i = 0; i < DIM; i++) {
+          double d = 0.0;
+          for (int k = 0; k < ND; k++) d += sue[k + i * ND] * dN[k + j * ND];
+          F[i + DIM * j] = d;
+        }
+#pragma unroll
+      for (int i = 0; i < DIM; i++) F[i + DIM * i] += 1.0;
+      material_pk1<DIM, MAT>(g.lambda, g.mu, F, P);
+      const double aq = swd[t];
+#pragma unroll
+      for (int n = 0; n < DD; n++) {
+        sFb[t * DD + n] = F[n];
+        sbq[t * DD + n] = aq * P[n];  // bjk = a * P(j,k), densemat.cpp:3008
+      }
+    }
+    __syncthreads();
+
+    // ---- base pass B: one thread per residual entry, (q,k) summed in the reference's order
+    if (t < TD) {
+      const int i = t % ND, j = t / ND;
+      double r = 0.0;
+      for (int q = 0; q < NQ; q++) {
+#pragma unroll
+        for (int k = 0; k < DIM; k++) r += sdN[q * TD + i + k * ND] * sbq[q * DD + j + DIM * k];
+      }
+      sRb[t] = r;
+      g.Re[e * TD + t] = r;
+    }
+    __syncthreads();
+
+    if (GRAD) {
+      if (t < TD) {
+        // forward difference wrt dof t (nonlinear_solid.cpp:57-75)
+        const int c = t / ND, a = t % ND;
+        const double orig = sue[t];
+        const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
+        const double hinv = 1. / h;
+        const double up = orig + h;
+        double R[TD];
+#pragma unroll
+        for (int n = 0; n < TD; n++) R[n] = 0.0;
+        const double* uc = sue + c * ND;
+#pragma unroll 1
+        for (int q = 0; q < NQ; q++) {
+          const double* dN = sdN + q * TD;
+          // Only row c of F depends on the perturbed dof; rows != c are bit-identical to the base F.
+          double drow[DIM];
+#pragma unroll
+          for (int j = 0; j < DIM; j++) drow[j] = 0.0;
+          for (int k = 0; k < ND; k++) {
+            const double uk = (k == a) ? up : uc[k];
+#pragma unroll
+            for (int j = 0; j < DIM; j++) drow[j] += uk * dN[k + j * ND];
+          }
+          double F[DD], P[DD];
+#pragma unroll
+          for (int j = 0; j < DIM; j++)
+#pragma unroll
+            for (int i = 0; i < DIM; i++) {
+              const double fnew = (i == j) ? drow[j] + 1.0 : drow[j];
+              F[i + DIM * j] = (i == c) ? fnew : sFb[q * DD + i + DIM * j];
+            }
+          material_pk1<DIM, MAT>(g.lambda, g.mu, F, P);
+          const double aq = swd[q];
+          // mfem::AddMult_a_ABt(a, dN_dX, P, R)  (densemat.cpp:3002-3015)
+#pragma unroll
+          for (int k = 0; k < DIM; k++)
+#pragma unroll
+            for (int j = 0; j < DIM; j++) {
+              const double bjk = aq * P[j + DIM * k];
+#pragma unroll
+              for (int i = 0; i < ND; i++) R[i + j * ND] += dN[i + k * ND] * bjk;
+            }
+        }
+        double* out = g.KeT + e * (int64_t)(TD * TD) + t;
+#pragma unroll
+        for (int j = 0; j < TD; j++) out[(int64_t)j * TD] = (R[j] - sRb[j]) * hinv;
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Deterministic scatter, written as a gather: every output entry is owned by exactly one thread,
+// which adds its element contributions in ascending element id -- the order in which the
+// reference's single thread pushes them (nonlinear_solid.cpp:126-143) -- so no atomics are needed
+// and the sums are bit-identical.
+// ---------------------------------------------------------------------------------------------
+
+// r[dim*I + c] += ((0 + R_e1) + R_e2) + ...   (thread_local_residual_ then nonlinear_base.hpp:96-105)
+__global__ void residual_gather_kernel(int dim, int nd, int64_t Nn, const int64_t* __restrict__ n2e_ptr,
+                                       const int32_t* __restrict__ n2e_elem, const uint8_t* __restrict__ n2e_loc,
+                                       const double* __restrict__ Re, double* __restrict__ r) {
+  const int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (v >= Nn * dim) return;
+  const int64_t I = v / dim;
+  const int c = (int)(v % dim);
+  const int tdof = dim * nd;
+  double acc = 0.0;
+  for (int64_t p = n2e_ptr[I]; p < n2e_ptr[I + 1]; p++)
+    acc += Re[(int64_t)n2e_elem[p] * tdof + n2e_loc[p] + c * nd];
+  r[v] += acc;
+}
+
+// One CTA per node I (block row of dim rows). Thread (ci, cj, b) adds K_e(a + ci*nd, b + cj*nd) into
+// the block-row accumulator slot rank[e][a][b]; elements visited in ascending id with a barrier in
+// between. Finally A[row, col] += grad_factor * acc  (nonlinear_base.hpp:141-144).
+template <int DIM>
+__global__ void csr_gather_kernel(int nd, int64_t Nn, const int64_t* __restrict__ n2e_ptr,
+                                  const int32_t* __restrict__ n2e_elem, const uint8_t* __restrict__ n2e_loc,
+                                  const uint16_t* __restrict__ rank, const int32_t* __restrict__ nnbr,
+                                  const int64_t* __restrict__ nodeptr, const double* __restrict__ KeT,
+                                  double grad_factor, double* __restrict__ A) {
+  constexpr int DD = DIM * DIM;
+  extern __shared__ double acc[];  // nnbr(I) x DIM(ci) x DIM(cj)
+  const int tdof = DIM * nd;
+  const int t = threadIdx.x;
+  for (int64_t I = blockIdx.x; I < Nn; I += gridDim.x) {
+    const int nn = nnbr[I];
+    for (int i = t; i < nn * DD; i += blockDim.x) acc[i] = 0.0;
+    __syncthreads();
+    const int ci = t / tdof, col = t % tdof;  // col = b + cj*nd
+    const int cj = col / nd, b = col % nd;
+    for (int64_t p = n2e_ptr[I]; p < n2e_ptr[I + 1]; p++) {
+      const int64_t e = n2e_elem[p];
+      const int a = n2e_loc[p];
+      if (t < DIM * tdof) {
+        const int s = rank[(e * nd + a) * nd + b];
+        acc[(s * DIM + ci) * DIM + cj] += KeT[e * (int64_t)(tdof * tdof) + (int64_t)(a + ci * nd) * tdof + col];
+      }
+      __syncthreads();
+    }
+    // row dim*I + ci starts at DD*nodeptr[I] + ci*DIM*nn; entry (s, cj) at + DIM*s + cj
+    const int64_t base = (int64_t)DD * nodeptr[I];
+    for (int i = t; i < nn * DD; i += blockDim.x) {
+      const int rci = i / (nn * DIM), rem = i % (nn * DIM);
+      const int s = rem / DIM, rcj = rem % DIM;
+      A[base + i] += grad_factor * acc[(s * DIM + rci) * DIM + rcj];
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------------
+template <int DIM, int ND, int NQ, int MAT, bool GRAD, int MINB>
+static int launch_element(mb2_ctx* c, const ElemArgs& a) {
+  using Cfg = ElemCfg<DIM, ND, NQ>;
+  auto kern = element_kernel<DIM, ND, NQ, MAT, GRAD, MINB>;
+  MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+  int per_sm = 0;
+  MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::NT, Cfg::SMEM_BYTES));
+  if (per_sm < 1) per_sm = 1;
+  // persistent grid: a whole number of resident CTAs per SM
+  int64_t grid = (int64_t)c->sm_count * per_sm;
+  if (grid > a.NE) grid = a.NE;
+  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, c->stream>>>(a);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
+template <int DIM, int ND, int NQ, bool GRAD, int MINB>
+static int launch_element_mat(mb2_ctx* c, const ElemArgs& a) {
+  switch (c->mat_kind) {
+    case MAT_NEOHOOKEAN: return launch_element<DIM, ND, NQ, MAT_NEOHOOKEAN, GRAD, MINB>(c, a);
+    case MAT_STVK: return launch_element<DIM, ND, NQ, MAT_STVK, GRAD, MINB>(c, a);
+  }
+  c->err = "material not set or unsupported";
+  return MB2_ERR_UNSUPPORTED;
+}
+
+template <bool GRAD>
+static int dispatch_element(mb2_ctx* c, const ElemArgs& a) {
+  const int dim = c->dim, nd = c->nd, nq = c->nq;
+  if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a);
+  if (dim == 3 && nd == 8 && nq == 27) return launch_element_mat<3, 8, 27, GRAD, 4>(c, a);
+  if (dim == 2 && nd == 16 && nq == 25) return launch_element_mat<2, 16, 25, GRAD, 4>(c, a);
+  if (dim == 2 && nd == 9 && nq == 16) return launch_element_mat<2, 9, 16, GRAD, 4>(c, a);
+  if (dim == 2 && nd == 4 && nq == 9) return launch_element_mat<2, 4, 9, GRAD, 4>(c, a);
+  c->err = "no kernel instantiated for (dim, nd, nq) = (" + std::to_string(dim) + ", " + std::to_string(nd) + ", " +
+           std::to_string(nq) + ")";
+  return MB2_ERR_UNSUPPORTED;
+}
+
+static ElemArgs make_args(mb2_ctx* c) {
+  ElemArgs a;
+  a.NE = c->NE;
+  a.vdofs = c->d_vdofs;
+  a.dNdX = c->d_dNdX;
+  a.wdetJ = c->d_wdetJ;
+  a.u = c->d_u;
+  a.Re = c->d_Re;
+  a.KeT = c->d_KeT;
+  a.lambda = c->lambda;
+  a.mu = c->mu;
+  return a;
+}
+
+static int launch_residual_gather(mb2_ctx* c) {
+  const int64_t n = c->Nn * c->dim;
+  residual_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->dim, c->nd, c->Nn, c->d_n2e_ptr,
+                                                                              c->d_n2e_elem, c->d_n2e_loc, c->d_Re,
+                                                                              c->d_r);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
+int launch_residual(mb2_ctx* c) {
+  c->last_launches = 0;
+  MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
+  int rc = dispatch_element<false>(c, make_args(c));
+  if (rc) return rc;
+  MB2_CUDA(cudaEventRecord(c->ev[1], c->stream));
+  rc = launch_residual_gather(c);
+  if (rc) return rc;
+  MB2_CUDA(cudaEventRecord(c->ev[2], c->stream));
+  c->last_launches = 2;
+  return MB2_OK;
+}
+
+int launch_residual_and_grad(mb2_ctx* c, double gf) {
+  c->last_launches = 0;
+  if (!c->d_KeT) {
+    const size_t bytes = sizeof(double) * (size_t)c->NE * c->tdof * c->tdof;
+    MB2_CUDA(cudaMalloc(&c->d_KeT, bytes));
+  }
+  MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
+  int rc = dispatch_element<true>(c, make_args(c));
+  if (rc) return rc;
+  MB2_CUDA(cudaEventRecord(c->ev[1], c->stream));
+  rc = launch_residual_gather(c);
+  if (rc) return rc;
+  {
+    const int threads = (c->dim * c->tdof + 31) / 32 * 32;
+    const int dd = c->dim * c->dim;
+    const int maxnbr = 1;  // placeholder, replaced below
+    (void)maxnbr;
+    int mx = 1;
+    for (int d = 0; d < c->dim; d++) mx *= 2 * 3 + 1;  // (2p+1)^dim for p <= 3
+    const size_t smem = sizeof(double) * (size_t)mx * dd;
+    int64_t grid = c->Nn < (int64_t)c->sm_count * 64 ? c->Nn : (int64_t)c->sm_count * 64;
+    if (c->dim == 3) {
+      MB2_CUDA(cudaFuncSetAttribute(csr_gather_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      csr_gather_kernel<3><<<(unsigned)grid, threads, smem, c->stream>>>(c->nd, c->Nn, c->d_n2e_ptr, c->d_n2e_elem,
+                                                                         c->d_n2e_loc, c->d_rank, c->d_nnbr,
+                                                                         c->d_nodeptr, c->d_KeT, gf, c->d_A);
+    } else {
+      csr_gather_kernel<2><<<(unsigned)grid, threads, smem, c->stream>>>(c->nd, c->Nn, c->d_n2e_ptr, c->d_n2e_elem,
+                                                                         c->d_n2e_loc, c->d_rank, c->d_nnbr,
+                                                                         c->d_nodeptr, c->d_KeT, gf, c->d_A);
+    }
+    MB2_CUDA(cudaGetLastError());
+  }
+  MB2_CUDA(cudaEventRecord(c->ev[2], c->stream));
+  c->last_launches = 3;
+  return MB2_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// FP64 pipe micro-benchmark: the roofline denominator MEASURED_PEAKS.json does not carry.
+// ---------------------------------------------------------------------------------------------
+template <int FMA>
+__global__ void __launch_bounds__(256) fp64_peak_kernel(int iters, double a, double b, double* out) {
+  double x[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) x[i] = (double)(threadIdx.x + i) * 1e-3;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+      if (FMA) x[i] = __fma_rn(x[i], a, b);
+      else x[i] = __dadd_rn(__dmul_rn(x[i], a), b);
+    }
+  }
+  double s = 0;
+#pragma unroll
+  for (int i = 0; i < 16; i++) s += x[i];
+  if (s == 123.456) out[0] = s;  // keep the result live
+}
+
+int launch_fp64_peak(mb2_ctx* c, int fma, double* tflops) {
+  double* d_out = nullptr;
+  MB2_CUDA(cudaMalloc(&d_out, 8));
+  const int iters = 4096, threads = 256, blocks = c->sm_count * 8;
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; rep++) {
+    MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
+    if (fma) fp64_peak_kernel<1><<<blocks, threads, 0, c->stream>>>(iters, 0.999999, 1e-9, d_out);
+    else fp64_peak_kernel<0><<<blocks, threads, 0, c->stream>>>(iters, 0.999999, 1e-9, d_out);
+    MB2_CUDA(cudaEventRecord(c->ev[1], c->stream));
+    MB2_CUDA(cudaEventSynchronize(c->ev[1]));
+    float ms = 0;
+    MB2_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    if (rep > 0 && ms < best) best = ms;
+  }
+  MB2_CUDA(cudaFree(d_out));
+  const double flops = 2.0 * 16.0 * iters * (double)threads * blocks;
+  *tflops = flops / (best * 1e-3) / 1e12;
+  return MB2_OK;
+}
+
+}  // namespace mb2

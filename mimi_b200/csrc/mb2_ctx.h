@@ -1,0 +1,81 @@
+// Internal context of libmimi_b200 (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+
+#include "../../include/mimi_b200.h"
+
+struct mb2_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  std::string err;
+  int sm_count = 148;
+
+  // problem shape
+  int dim = 0, nd = 0, nq = 0, tdof = 0;
+  int64_t NE = 0, NV = 0, Nn = 0, nnz = 0;
+
+  // material
+  int mat_kind = -1;
+  double lambda = 0, mu = 0;
+
+  // connectivity
+  int32_t* d_vdofs = nullptr;   // NE x tdof (reference layout)
+  int32_t* d_enodes = nullptr;  // NE x nd   node ids
+
+  // tables
+  double* d_dNdX = nullptr;  // NE x nq x (nd x dim col-major)
+  double* d_wdetJ = nullptr; // NE x nq   (integration_weight * det_dX_dxi)
+
+  // node -> element adjacency (ascending element id) and pattern
+  int64_t* d_n2e_ptr = nullptr;  // Nn+1
+  int32_t* d_n2e_elem = nullptr; // sum
+  uint8_t* d_n2e_loc = nullptr;  // local node index inside that element
+  int32_t* d_nnbr = nullptr;     // Nn   neighbours per node
+  int64_t* d_nodeptr = nullptr;  // Nn+1 prefix sum of nnbr
+  int32_t* d_nbr = nullptr;      // nodeptr[Nn] sorted neighbour nodes
+  uint16_t* d_rank = nullptr;    // NE x nd x nd  rank of node b in nbr list of node a
+  int64_t* d_I = nullptr;        // NV+1
+  int32_t* d_J = nullptr;        // nnz
+  bool have_pattern = false;
+
+  // resident state
+  double* d_u = nullptr;  // NV
+  double* d_r = nullptr;  // NV
+  double* d_A = nullptr;  // nnz
+
+  // per-element results
+  double* d_Re = nullptr;  // NE x tdof
+  double* d_KeT = nullptr; // NE x tdof x tdof, [residual row j][perturbed dof i], i fastest
+  int* d_flag = nullptr;   // device failure flag
+
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  float last_ms[3] = {0, 0, 0};
+  int last_launches = 0;
+};
+
+namespace mb2 {
+// mb2_pattern.cu
+int build_pattern(mb2_ctx* c);
+int expand_A_ids(mb2_ctx* c, int32_t* d_out);
+// mb2_assembly.cu
+int launch_residual(mb2_ctx* c);
+int launch_residual_and_grad(mb2_ctx* c, double gf);
+int launch_fp64_peak(mb2_ctx* c, int fma, double* tflops);
+// mb2_tables.cu
+int generate_patch_tables(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                          const double* x_ref, const double* weights, int quad_order);
+}  // namespace mb2
+
+#define MB2_CUDA(call)                                                                      \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) {                                                                \
+      c->err = std::string(#call) + ": " + cudaGetErrorString(e_) + " (" + __FILE__ + ":" + \
+               std::to_string(__LINE__) + ")";                                              \
+      return MB2_ERR_CUDA;                                                                  \
+    }                                                                                       \
+  } while (0)

@@ -1,0 +1,51 @@
+"""TEST INFRASTRUCTURE. Regenerates tests/golden/*.npz by running the UNMODIFIED reference
+(oracle/_ref/mimi_ref, built by `make -f oracle/Makefile.ref`) at nthreads=1 on small meshes.
+Run from the repo root where /root/reference exists:  python oracle/make_golden.py
+"""
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from mimi_b200 import meshgen  # noqa: E402
+from oracle import oracle_py as O  # noqa: E402
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+# name: (mesh writer, elevate, refine, gf)
+CASES = {
+    "cube_p2_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 1, 1, 1.0),
+    "cube_p1_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 0, 1, 0.5),
+    "beam2d_p3_n2": (lambda f: meshgen.write_box_p1(f, (5.0, 1.0)), 2, 1, 0.0125),  # tests/test_nonlinear_solid.py mesh
+    "quad_p2_n4": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 1, 2, 1.0),
+    "cube_p2_n3_patch": (lambda f: meshgen.write_box_patch(f, 2, (3, 2, 2), (1.5, 1.0, 1.0)), 0, 0, 2.0),
+}
+
+
+def main():
+    assert O.have_ref(), "build oracle/_ref first: make -f oracle/Makefile.ref -j8"
+    os.makedirs(OUT, exist_ok=True)
+    for name, (writer, elevate, refine, gf) in CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            mesh = os.path.join(tmp, "m.mesh")
+            writer(mesh)
+            out = {}
+            for mat in ("neohookean", "stvk"):
+                D = O.run_ref_dump(mesh, elevate, refine, mat, os.path.join(tmp, mat), gf=gf)
+                if not out:
+                    for k in ("I", "J", "v_dofs", "A_ids", "w", "detJ", "dN_dX", "N", "dN_dxi", "x_ref", "u", "mass"):
+                        out[k] = D[k]
+                    out["meta"] = np.array([D["dim"], D["nd"], D["nq"], D["NE"], D["NV"], D["nnz"]], np.int64)
+                    out["gf"] = np.float64(gf)
+                    out["lambda_mu"] = np.array([float.fromhex(D["lambda"]), float.fromhex(D["mu"])])
+                out["r_" + mat] = D["r"]
+                out["r2_" + mat] = D["r2"]
+                out["A_" + mat] = D["A"]
+            np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+            print(name, {k: int(v) for k, v in zip(("dim", "nd", "nq", "NE", "NV", "nnz"), out["meta"])})
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,46 @@
+"""Shared helpers: golden fixtures (tests/golden/*.npz, written by oracle/make_golden.py from the
+unmodified reference) and live runs of oracle/_ref/mimi_ref on generated meshes."""
+import os
+import tempfile
+
+import numpy as np
+
+from mimi_b200 import meshgen
+from oracle import oracle_py as O
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "quad_p2_n4", "cube_p2_n3_patch"]
+MATS = {"neohookean": 0, "stvk": 1}
+
+
+def load_golden(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    D = {k: z[k] for k in z.files}
+    dim, nd, nq, NE, NV, nnz = (int(x) for x in D["meta"])
+    D.update(dim=dim, nd=nd, nq=nq, NE=NE, NV=NV, nnz=nnz, tdof=dim * nd, gf=float(D["gf"]))
+    return D
+
+
+def ref_case(kind, p, n, material, gf=1.0):
+    """Live reference run (nthreads=1). kind: 'refine' (p1 cube + DegreeElevate(p-1) + log2(n) refinements)
+    or 'patch' (direct p, n spans)."""
+    tmp = tempfile.mkdtemp(prefix="mb2case_")
+    mesh = os.path.join(tmp, "m.mesh")
+    if kind == "refine":
+        meshgen.write_box_p1(mesh, (1.0, 1.0, 1.0))
+        ref = int(round(np.log2(n)))
+        assert 2 ** ref == n
+        D = O.run_ref_dump(mesh, p - 1, ref, material, os.path.join(tmp, "d"), gf=gf, lite=True)
+    else:
+        meshgen.write_box_patch(mesh, p, (n, n, n))
+        D = O.run_ref_dump(mesh, 0, 0, material, os.path.join(tmp, "d"), gf=gf, lite=True)
+    return D
+
+
+def setup_ctx(ctx, D, material):
+    ctx.set_connectivity(D["dim"], D["nd"], D["nq"], D["NV"], D["v_dofs"])
+    ctx.upload_quad_tables(D["dN_dX"], D["w"], D["detJ"])
+    ctx.build_pattern()
+    lam, mu = O.lame()
+    ctx.set_material(MATS[material], [lam, mu])
+    return ctx

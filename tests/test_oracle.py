@@ -1,0 +1,42 @@
+"""CPU: the plain-C oracle against the golden vectors dumped from the unmodified reference (bit-exact)."""
+import numpy as np
+import pytest
+
+from oracle import oracle_py as O
+from tests.cases import GOLDEN_CASES, MATS, load_golden
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_pattern_and_index_map(name):
+    D = load_golden(name)
+    I, J = O.build_pattern(D["tdof"], D["v_dofs"], D["NV"])
+    assert np.array_equal(I, D["I"]) and np.array_equal(J, D["J"])
+    assert np.array_equal(O.build_A_ids(D["tdof"], D["v_dofs"], I, J), D["A_ids"])
+
+
+@pytest.mark.parametrize("material", ["neohookean", "stvk"])
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_residual_and_tangent_bit_exact(name, material):
+    D = load_golden(name)
+    m = O.mat(MATS[material])
+    assert [m.lam, m.mu] == list(D["lambda_mu"])
+    r = O.assemble_residual(D["dim"], D["nd"], D["nq"], m, D["v_dofs"], D["dN_dX"], D["w"], D["detJ"], D["u"])
+    assert np.array_equal(r, D["r_" + material])
+    r2, A = O.assemble_residual_and_grad(D["dim"], D["nd"], D["nq"], m, D["v_dofs"], D["A_ids"], D["dN_dX"], D["w"],
+                                         D["detJ"], D["u"], D["gf"], D["mass"])
+    assert np.array_equal(r2, D["r2_" + material])
+    assert np.array_equal(A, D["A_" + material])
+
+
+@pytest.mark.skipif(not O.have_ref(), reason="oracle/_ref not built")
+def test_oracle_vs_live_reference_4096_free():
+    """A mesh no fixture covers (n=4 via DegreeElevate+2 refinements), straight from the compiled reference."""
+    from tests.cases import ref_case
+    D = ref_case("refine", 2, 4, "neohookean", gf=0.7)
+    m = O.mat(0)
+    I, J = O.build_pattern(D["tdof"], D["v_dofs"], D["NV"])
+    assert np.array_equal(I, D["I"]) and np.array_equal(J, D["J"])
+    aid = O.build_A_ids(D["tdof"], D["v_dofs"], I, J)
+    r2, A = O.assemble_residual_and_grad(3, 27, 64, m, D["v_dofs"], aid, D["dN_dX"], D["w"], D["detJ"], D["u"], 0.7,
+                                         D["mass"])
+    assert np.array_equal(r2, D["r2"]) and np.array_equal(A, D["A"])
