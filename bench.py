@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""bench.py -- quadrature points / second of one residual + tangent CSR assembly (BASELINE.json metric).
+
+Workload at N=1: configs[2] of BASELINE.json = C3 of SURVEY.md section 8: single-patch unit cube, B-spline p=2,
+100^3 = 1e6 elements, 64 qp each, compressible NeoHookean (E=2100, nu=0.3), u_i = 1e-3 (U_i - 0.5) from
+splitmix64(12345 + i), grad_factor = 1. A "step" is one AddDomainResidualAndGrad-equivalent:
+element FD-tangent kernel + deterministic gather into r[NV] and the CSR values A[nnz].
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--n SPANS] [--impl reference]
+
+Contract keys: value = device-resident step (u, tables, CSR in HBM); e2e = the host-buffer C-ABI call
+mb2_add_domain_residual_and_grad (u H2D, r and A D2H from pinned host memory inside the timed region);
+roofline = FP64 CUDA-core pipe of the element kernel; cpu_baseline = the unmodified reference
+(oracle/_ref/mimi_ref, OpenMP, all host cores) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = json.load(open(os.path.join(ROOT, "BASELINE.json")))["metric"] if os.path.exists(os.path.join(ROOT, "BASELINE.json")) else \
+    "quadrature pts/sec for residual+tangent CSR assembly (3D p=2 NeoHookean) @1/2/4/8 GPU"
+UNIT = "qp/s"
+
+
+# flops per quadrature point, counted mul/add/div = 1 each
+def flops_per_qp(p, dim=3):
+    nd = (p + 1) ** dim
+    tdof = dim * nd
+    F = 2 * dim * dim * nd + dim           # MultAtB + AddDiagonal
+    stress = 204                           # NeoHookean: det 14, mu/J 1, FF^T 54, coeff 3, axpby 27, inverse 42, sigma F^-T 54, J* 9
+    acc = dim * dim * (1 + 2 * nd) + 1     # AddMult_a_ABt + (w * detJ)
+    algorithmic = (tdof + 1) * (F + stress + acc)
+    # executed by the CUDA kernel: a perturbed dof only changes one row of F (the others are bit-identical
+    # to the base F and are re-used), and w*detJ is folded into the tables at setup.
+    F_row = 2 * dim * nd + 1
+    executed = (F + stress + acc - 1) + tdof * (F_row + stress + acc - 1)
+    fd = 2 * tdof * tdof                   # (R+ - R) * (1/h), per element -> caller divides by nq
+    return algorithmic, executed, fd
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, pw, reasons = [], [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        # under load = samples at or above the median power draw
+        med_p = float(np.median(pw))
+        load = [s for s, p_ in zip(sm, pw) if p_ >= med_p] or sm
+        return {"sm_mhz": float(np.median(load)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the UNMODIFIED reference compiled into oracle/_ref/mimi_ref (test
+# infrastructure; this is the one place bench.py executes anything under oracle/).
+# ----------------------------------------------------------------------------------------------------
+def run_reference_sample(n, reps, nthreads, warmup=0, p=2, material="neohookean"):
+    from mimi_b200 import meshgen
+    from oracle import oracle_py as O
+    if not O.have_ref():
+        raise RuntimeError("oracle/_ref/mimi_ref is not present (build it with `make -f oracle/Makefile.ref` "
+                           "where /root/reference exists; it ships to the GPU box with the snapshot)")
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        meshgen.write_box_patch(mesh, p, (n, n, n))
+        T = O.run_ref_time(mesh, 0, 0, material, nthreads, reps, warmup)
+    qp = T["NE"] * T["nq"]
+    return {"qp": qp, "NE": T["NE"], "t_mean": T["t_res_grad_mean"], "t_best": T["t_res_grad_best"],
+            "t_res_best": T["t_res_best"], "value_mean": qp / T["t_res_grad_mean"], "value_best": qp / T["t_res_grad_best"],
+            "t_precompute": T["t_precompute"]}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = host_cores()
+    n = args.ref_n
+    reps = args.steps
+    t0 = time.time()
+    S = run_reference_sample(n, reps, cores, warmup=args.warmup)
+    value = S["qp"] / S["t_mean"]
+    sample = ("unmodified reference AddDomainResidualAndGrad (MFEM 4.7.1 + mimi integrators, OpenMP, -O3), "
+              "p=2 unit cube %d^3 = %d elements (%d qp) per step, %d threads; mean of %d steps after %d warm-up" % (n, S["NE"], S["qp"], cores, reps, args.warmup))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": S["t_mean"] * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C3 sample: p=2 NeoHookean unit cube %d^3 (bounded sample of the 100^3 workload)" % n,
+                       "elements": S["NE"], "qp": S["qp"]},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.time() - t0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------------
+def build_problem(ctx, n, p, rank=0):
+    """Synthetic C3-style block in MFEM's numbering; tables regenerated on the device."""
+    from mimi_b200 import capi, meshgen
+    t0 = time.time()
+    M = meshgen.patch_connectivity(p, (n, n, n))
+    nq1 = (2 * p + 3) // 2 + 1
+    ctx.set_connectivity(3, M["nd"], nq1 ** 3, M["NV"], M["v_dofs"])
+    ctx.set_nodes(M["x_ref"], None)
+    ctx.generate_patch_tables(p, M["ncp"], M["knots"], M["el_ijk"])
+    nnz = ctx.build_pattern()
+    young, poisson = 2100.0, 0.3
+    lam = young * poisson / ((1 + poisson) * (1 - 2 * poisson))
+    mu = young / (2.0 * (1.0 + poisson))
+    ctx.set_material(capi.MB2_MAT_NEOHOOKEAN, [lam, mu])
+    u = meshgen.synth_u(M["NV"])
+    # face x = 0 clamped: exactly 0 (h = 1e-10 branch of the FD rule)
+    x = M["x_ref"].reshape(-1, 3)
+    u.reshape(-1, 3)[x[:, 0] == 0.0, :] = 0.0
+    M.update(u=u, nnz=nnz, nq=nq1 ** 3, setup_s=time.time() - t0)
+    return M
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    from mimi_b200 import capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: libmimi_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n, p = args.n, 2
+    stream = torch.cuda.Stream()            # the library launches on this stream, so torch events see its work
+    ctx = capi.Context(local, stream=stream.cuda_stream)
+    M = build_problem(ctx, n, p, rank)
+    NE, nq, NV, nnz = M["NE"], M["nq"], M["NV"], M["nnz"]
+    ctx.set_u(M["u"])
+    ctx.set_r(None)
+    ctx.set_A(None)
+    ctx.sync()
+
+    # FP64 pipe peak of this very GPU (MEASURED_PEAKS.json carries no FP64 figure): DMUL+DADD pairs, the
+    # instruction mix a bit-exact (non-FMA) kernel is allowed to issue.
+    peak_nofma = ctx.measure_fp64_peak(0)
+    peak_fma = ctx.measure_fp64_peak(1)
+
+    # ---- device-resident steps ----
+    for _ in range(args.warmup):
+        ctx.assemble_residual_and_grad_device(1.0)
+    ctx.sync()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    t_el, t_sc, launches = [], [], 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        ctx.assemble_residual_and_grad_device(1.0)
+        el, sc, tot = ctx.last_timing_ms()      # CUDA events on the library's stream (synchronises on the last)
+        t_el.append(el); t_sc.append(sc)
+        launches += ctx.last_launch_count()
+    ev1.record(stream)
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    dev_ms = float(ev0.elapsed_time(ev1))         # device time of the K steps, CUDA events on the launching stream
+    if world > 1:
+        tt = torch.tensor([dev_ms, wall], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dev_ms, wall = float(tt[0]), float(tt[1])
+    ms_per_step = dev_ms / args.steps
+    total_qp = float(NE) * nq * world
+    value = total_qp / (ms_per_step * 1e-3)
+
+    # ---- end to end through the host-buffer C-ABI call (pinned host memory) ----
+    e2e = None
+    if not args.no_e2e:
+        u_h = torch.from_numpy(M["u"]).pin_memory()
+        r_h = torch.zeros(NV, dtype=torch.float64).pin_memory()
+        A_h = torch.zeros(nnz, dtype=torch.float64).pin_memory()
+        up, rp, Ap = (C_void(t) for t in (u_h, r_h, A_h))
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        ctx._ck(ctx.lib.mb2_add_domain_residual_and_grad(ctx.h, up, capi.C.c_double(1.0), rp, Ap))  # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            ctx._ck(ctx.lib.mb2_add_domain_residual_and_grad(ctx.h, up, capi.C.c_double(1.0), rp, Ap))
+        barrier()
+        e2e_s = (time.perf_counter() - t0) / e2e_steps
+        if world > 1:
+            tt = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            e2e_s = float(tt[0])
+        e2e = {"value": total_qp / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * (2 * NV + nnz),
+               "d2h_bytes_per_step": 8 * (NV + nnz), "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
+               "call": "mb2_add_domain_residual_and_grad(u, 1.0, r, A) with pinned host buffers"}
+
+    if rank == 0:
+        alg, exe, fd = flops_per_qp(p)
+        el_ms = float(np.mean(t_el))
+        qp_rate_kernel = float(NE) * nq / (el_ms * 1e-3)
+        exe_qp = exe + fd / nq
+        achieved = qp_rate_kernel * exe_qp / 1e12
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        tdof = 3 * M["nd"]
+        bytes_el = NE * (8.0 * nq * (tdof + 1) + 4 * tdof + 8 * tdof + 8 * tdof * tdof + 8 * tdof)
+        roofline = {"bound": "fp64", "kernel": "element_kernel<3,27,64,NeoHookean,GRAD>", "achieved": achieved, "peak": peak_nofma,
+                    "unit": "TFLOP/s", "frac": achieved / peak_nofma, "traffic": None,
+                    "peak_source": "mb2_measure_fp64_peak(fma=0) on this GPU in this run: DMUL+DADD pairs = the only "
+                                   "mix a bit-exact non-FMA kernel may issue (DFMA peak %.2f; MEASURED_PEAKS.json has no FP64 entry)" % peak_fma,
+                    "flop_per_qp_executed": exe_qp, "flop_per_qp_algorithmic": alg + fd / nq,
+                    "achieved_algorithmic": qp_rate_kernel * (alg + fd / nq) / 1e12,
+                    "kernel_ms": el_ms, "scatter_ms": float(np.mean(t_sc)),
+                    "hbm_secondary": {"algorithmic_gb": bytes_el / 1e9, "achieved_gbs": bytes_el / 1e9 / (el_ms * 1e-3),
+                                      "peak_gbs": hbm_peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback"}}
+        cpu = None
+        if not args.no_cpu:
+            try:
+                cores = host_cores()
+                S = run_reference_sample(args.ref_n, 2, cores, warmup=1)
+                cpu = {"value": S["value_mean"], "unit": UNIT, "cores": cores, "kind": "reference",
+                       "sample": "unmodified reference (oracle/_ref/mimi_ref, OpenMP %d threads) on p=2 NeoHookean cube %d^3 = %d el, "
+                                 "mean of 2 steps after 1 warm-up; residual-only best %.3e qp/s" % (
+                                     cores, args.ref_n, S["NE"], S["qp"] / S["t_res_best"])}
+            except Exception as ex:  # the checker binary is absent: report that, never substitute
+                cpu = {"value": None, "unit": UNIT, "cores": host_cores(), "kind": "reference", "sample": "unavailable: %s" % ex}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic",
+                "config": {"workload": "C3: 3D unit-cube B-spline patch p=2, %d^3 = %d elements x %d qp per GPU, compressible NeoHookean, "
+                                       "one residual+tangent assembly into CSR (nnz=%d per GPU), MFEM dof numbering" % (n, NE, nq, nnz),
+                           "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "nnz_per_gpu": nnz, "tangent": "FD parity (bit-exact vs reference)",
+                           "l2": "inputs larger than L2 (tables %.1f GB, K_e %.1f GB per step)" % (8e-9 * NE * nq * (tdof + 1), 8e-9 * NE * tdof * tdof),
+                           "parallelism": "1 GPU" if world == 1 else "independent blocks per GPU (interface exchange: see DESIGN.md)",
+                           "setup_s": M["setup_s"]},
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "wall_s_timed_region": wall}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def C_void(t):
+    import ctypes
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=100, help="knot spans per direction (per GPU)")
+    ap.add_argument("--ref-n", type=int, default=24, help="spans per direction of the CPU reference sample")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = max(args.warmup, 3) if not os.environ.get("MB2_BENCH_ALLOW_SHORT") else args.warmup
+    if args.impl == "reference":
+        return reference_arm(args)
+    return gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

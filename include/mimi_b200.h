@@ -67,14 +67,21 @@ int mb2_set_connectivity(mb2_ctx* ctx, int dim, int nd, int nq, int64_t NE, int6
  * w and detJ NE x nq (QuadData::integration_weight, det_dX_dxi). Host pointers. */
 int mb2_upload_quad_tables(mb2_ctx* ctx, const double* dN_dX, const double* w, const double* detJ);
 
-/* Device-side regeneration of the same tables for one tensor-product NURBS patch from its knot
- * vectors, weights and control net, in MFEM's arithmetic order (third_party/mfem/mesh/nurbs.cpp:297-322,
- * fem/fe/fe_nurbs.cpp:243-311, precomputed.cpp:289-321). knots[d] has ncp[d]+p+1 entries; el_ijk is
- * NE x dim (knot-span index of every element); x_ref / weights are indexed by node (x_ref byVDIM).
- * quad_order < 0 selects the reference default 2p+3. */
-int mb2_generate_patch_tables(mb2_ctx* ctx, int p, const int32_t* ncp, const double* const* knots,
-                              const int32_t* el_ijk, const double* x_ref, const double* weights,
-                              int quad_order);
+/* Reference node coordinates (the mesh Nodes GridFunction, byVDIM: x_ref[dim*node + c]) and NURBS weights
+ * per node (NULL = B-spline, all 1); what IsoparametricTransformation::PointMat and
+ * NURBSFiniteElement::Weights() hold per element (third_party/mfem/fem/eltrans.cpp:406-420). */
+int mb2_set_nodes(mb2_ctx* ctx, const double* x_ref, const double* weights);
+
+/* Device-side regeneration of the same tables for the elements [elem_begin, elem_begin+elem_count) of one
+ * tensor-product NURBS patch from its knot vectors, in MFEM's arithmetic order
+ * (third_party/mfem/mesh/nurbs.cpp:297-376, fem/fe/fe_nurbs.cpp:125-158,269-311, precomputed.cpp:289-321),
+ * bit-identical to PrecomputeElementQuadData. knots[d] has ncp[d]+p+1 entries; el_ijk is elem_count x dim,
+ * the knot-span index of every element (NURBSExtension::el_to_IJK). quad_order < 0 selects the reference
+ * default 2p+3. want_N != 0 also keeps the shape values N (QuadData::N). Call once per patch. */
+int mb2_generate_patch_tables(mb2_ctx* ctx, int64_t elem_begin, int64_t elem_count, int p, const int32_t* ncp,
+                              const double* const* knots, const int32_t* el_ijk, int quad_order, int want_N);
+/* Shape values N: NE x nq x nd (tests; contact). */
+int mb2_download_shape_values(mb2_ctx* ctx, double* N);
 
 /* Copies the device tables back (tests). Any pointer may be NULL. */
 int mb2_download_quad_tables(mb2_ctx* ctx, double* dN_dX, double* w_detJ);

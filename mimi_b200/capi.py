@@ -18,7 +18,7 @@ MB2_MAT_NEOHOOKEAN, MB2_MAT_STVK = 0, 1
 # every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "mb2_create", "mb2_destroy", "mb2_last_error", "mb2_version", "mb2_set_connectivity",
-    "mb2_upload_quad_tables", "mb2_generate_patch_tables", "mb2_download_quad_tables", "mb2_build_pattern",
+    "mb2_upload_quad_tables", "mb2_set_nodes", "mb2_generate_patch_tables", "mb2_download_shape_values", "mb2_download_quad_tables", "mb2_build_pattern",
     "mb2_get_pattern_i32", "mb2_get_pattern_i64", "mb2_get_A_ids_i32", "mb2_set_material",
     "mb2_add_domain_residual", "mb2_add_domain_residual_and_grad", "mb2_set_u", "mb2_set_r", "mb2_set_A",
     "mb2_get_r", "mb2_get_A", "mb2_assemble_residual_device", "mb2_assemble_residual_and_grad_device",
@@ -84,6 +84,26 @@ class Context:
         a, b, c = (np.ascontiguousarray(x, np.float64) for x in (dN_dX, w, detJ))
         assert a.size == self.NE * self.nq * self.tdof and b.size == self.NE * self.nq == c.size
         self._ck(self.lib.mb2_upload_quad_tables(self.h, _dp(a), _dp(b), _dp(c)))
+
+    def set_nodes(self, x_ref, weights=None):
+        x = np.ascontiguousarray(x_ref, np.float64)
+        w = None if weights is None else np.ascontiguousarray(weights, np.float64)
+        assert x.size == self.NV
+        self._ck(self.lib.mb2_set_nodes(self.h, _dp(x), _dp(w)))
+
+    def generate_patch_tables(self, p, ncp, knots, el_ijk, e0=0, quad_order=-1, want_N=False):
+        ncp = np.ascontiguousarray(ncp, np.int32)
+        ijk = np.ascontiguousarray(el_ijk, np.int32)
+        kv = [np.ascontiguousarray(k, np.float64) for k in knots]
+        assert all(len(k) == n + p + 1 for k, n in zip(kv, ncp))
+        arr = (C.c_void_p * len(kv))(*[k.ctypes.data for k in kv])
+        self._ck(self.lib.mb2_generate_patch_tables(self.h, C.c_int64(e0), C.c_int64(ijk.shape[0]), C.c_int(p), _dp(ncp),
+                                                    arr, _dp(ijk), C.c_int(quad_order), C.c_int(int(want_N))))
+
+    def download_shape_values(self):
+        N = np.empty((self.NE, self.nq, self.nd))
+        self._ck(self.lib.mb2_download_shape_values(self.h, _dp(N)))
+        return N
 
     def download_quad_tables(self):
         dN = np.empty((self.NE, self.nq, self.dim, self.nd))

@@ -22,7 +22,7 @@ static void dfree(T*& p) {
 }
 
 static void free_problem(mb2_ctx* c) {
-  dfree(c->d_vdofs); dfree(c->d_enodes); dfree(c->d_dNdX); dfree(c->d_wdetJ);
+  dfree(c->d_vdofs); dfree(c->d_enodes); dfree(c->d_dNdX); dfree(c->d_wdetJ); dfree(c->d_N); dfree(c->d_xref); dfree(c->d_nodew);
   dfree(c->d_n2e_ptr); dfree(c->d_n2e_elem); dfree(c->d_n2e_loc); dfree(c->d_nnbr); dfree(c->d_nodeptr);
   dfree(c->d_nbr); dfree(c->d_rank); dfree(c->d_I); dfree(c->d_J);
   dfree(c->d_u); dfree(c->d_r); dfree(c->d_A); dfree(c->d_Re); dfree(c->d_KeT);
@@ -323,11 +323,29 @@ int mb2_measure_fp64_peak(mb2_ctx* c, int fma, double* tflops) {
   return mb2::launch_fp64_peak(c, fma, tflops);
 }
 
-int mb2_generate_patch_tables(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
-                              const double* x_ref, const double* weights, int quad_order) {
+int mb2_set_nodes(mb2_ctx* c, const double* x_ref, const double* weights) {
   CHECK_CTX(c);
+  REQUIRE(c->NE > 0, "call mb2_set_connectivity first");
+  REQUIRE(x_ref, "null x_ref");
   MB2_CUDA(cudaSetDevice(c->device));
-  return mb2::generate_patch_tables(c, p, ncp, knots, el_ijk, x_ref, weights, quad_order);
+  return mb2::set_nodes(c, x_ref, weights);
+}
+
+int mb2_generate_patch_tables(mb2_ctx* c, int64_t elem_begin, int64_t elem_count, int p, const int32_t* ncp,
+                              const double* const* knots, const int32_t* el_ijk, int quad_order, int want_N) {
+  CHECK_CTX(c);
+  REQUIRE(c->NE > 0, "call mb2_set_connectivity first");
+  REQUIRE(ncp && knots && el_ijk, "null argument");
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::generate_patch_tables(c, elem_begin, elem_count, p, ncp, knots, el_ijk, quad_order, want_N != 0);
+}
+
+int mb2_download_shape_values(mb2_ctx* c, double* N) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_N && N, "no shape values on device (mb2_generate_patch_tables with want_N)");
+  MB2_CUDA(cudaMemcpyAsync(N, c->d_N, sizeof(double) * c->NE * c->nq * c->nd, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
 }
 
 }  // extern "C"

@@ -29,6 +29,9 @@ struct mb2_ctx {
   // tables
   double* d_dNdX = nullptr;  // NE x nq x (nd x dim col-major)
   double* d_wdetJ = nullptr; // NE x nq   (integration_weight * det_dX_dxi)
+  double* d_N = nullptr;     // NE x nq x nd shape values (optional; contact / tests)
+  double* d_xref = nullptr;  // NV  reference node coordinates, byVDIM
+  double* d_nodew = nullptr; // Nn  NURBS weights (nullptr = all 1)
 
   // node -> element adjacency (ascending element id) and pattern
   int64_t* d_n2e_ptr = nullptr;  // Nn+1
@@ -66,8 +69,9 @@ int launch_residual(mb2_ctx* c);
 int launch_residual_and_grad(mb2_ctx* c, double gf);
 int launch_fp64_peak(mb2_ctx* c, int fma, double* tflops);
 // mb2_tables.cu
-int generate_patch_tables(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
-                          const double* x_ref, const double* weights, int quad_order);
+int set_nodes(mb2_ctx* c, const double* x_ref, const double* weights);
+int generate_patch_tables(mb2_ctx* c, int64_t e0, int64_t ne, int p, const int32_t* ncp, const double* const* knots,
+                          const int32_t* el_ijk, int quad_order, bool want_N);
 }  // namespace mb2
 
 #define MB2_CUDA(call)                                                                      \

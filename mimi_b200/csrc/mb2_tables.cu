@@ -1,10 +1,319 @@
-// Device-side regeneration of the per-quadrature-point tables (placeholder until the MFEM-order
-// NURBS evaluation lands; see mb2_generate_patch_tables in include/mimi_b200.h).
+// Device-side regeneration of the per-quadrature-point tables of one tensor-product NURBS patch.
+//
+// Replaces PrecomputedData::PrecomputeElementQuadData (src/mimi/utils/precomputed.cpp:264-330), whose
+// heap-allocated per-qp objects (QuadData, precomputed.hpp:58-69) take ~1.5 KB per quadrature point and
+// cannot be built on a host for the 1e6-element configurations. Every value is produced in MFEM's
+// operation order (this translation unit is compiled -fmad=false), so the tables are bit-identical to
+// the reference's:
+//   1D Gauss-Legendre rule        third_party/mfem/fem/intrules.cpp:424-494 (host: needs libm cos)
+//   tensor rule ordering/weights  third_party/mfem/fem/intrules.cpp:56-84   (x fastest; (wx*wy)*wz)
+//   1D B-spline values            KnotVector::CalcShape,  third_party/mfem/mesh/nurbs.cpp:297-320
+//   1D B-spline derivatives       KnotVector::CalcDShape, third_party/mfem/mesh/nurbs.cpp:322-376
+//   rational 2D/3D gradients      NURBS{2,3}DFiniteElement::CalcDShape, third_party/mfem/fem/fe/fe_nurbs.cpp:130-175,269-311
+//   geometry Jacobian             IsoparametricTransformation::EvalJacobian, third_party/mfem/fem/eltrans.cpp:406-420
+//   det / inverse / dN_dX         DenseMatrix::Det (densemat.cpp:510-525), kernels::CalcInverse
+//                                 (kernels.hpp:244-251), kernels::Mult (kernels.hpp:341-357)
+#include <cmath>
+#include <vector>
+
 #include "mb2_ctx.h"
+#include "mb2_math.cuh"
+
 namespace mb2 {
-int generate_patch_tables(mb2_ctx* c, int, const int32_t*, const double* const*, const int32_t*, const double*,
-                          const double*, int) {
-  c->err = "mb2_generate_patch_tables: not implemented yet";
-  return MB2_ERR_UNSUPPORTED;
+
+constexpr int MAXP = 4;    // degree limit of the instantiated kernels
+constexpr int MAXQ1 = 8;   // 1D quadrature points limit
+
+// QuadratureFunctions1D::GaussLegendre on [0,1] (intrules.cpp:424-494), host arithmetic.
+static void gauss_legendre_01(int np, std::vector<double>& x, std::vector<double>& w) {
+  x.assign(np, 0.0);
+  w.assign(np, 0.0);
+  switch (np) {
+    case 1: x[0] = 0.5; w[0] = 1.0; return;
+    case 2:
+      x[0] = 0.21132486540518711775; w[0] = 0.5;
+      x[1] = 0.78867513459481288225; w[1] = 0.5;
+      return;
+    case 3:
+      x[0] = 0.11270166537925831148; w[0] = 5. / 18.;
+      x[1] = 0.5; w[1] = 4. / 9.;
+      x[2] = 0.88729833462074168852; w[2] = 5. / 18.;
+      return;
+  }
+  const int n = np, m = (n + 1) / 2;
+  for (int i = 1; i <= m; i++) {
+    double z = std::cos(M_PI * (i - 0.25) / (n + 0.5));
+    double pp, p1, dz, xi = 0.;
+    bool done = false;
+    while (1) {
+      double p2 = 1;
+      p1 = z;
+      for (int j = 2; j <= n; j++) {
+        const double p3 = p2;
+        p2 = p1;
+        p1 = ((2 * j - 1) * z * p2 - (j - 1) * p3) / j;
+      }
+      pp = n * (z * p1 - p2) / (z * z - 1);
+      if (done) break;
+      dz = p1 / pp;
+      if (std::fabs(dz) < 1e-16) {
+        done = true;
+        xi = ((1 - z) + dz) / 2;
+      }
+      z -= dz;
+    }
+    x[i - 1] = xi;
+    x[n - i] = 1 - xi;
+    w[i - 1] = w[n - i] = 1. / (4 * xi * (1 - xi) * pp * pp);
+  }
 }
+
+// 1D tables: for direction d, knot span s (ip = s + p), 1D point q: shape[0..p], dshape[0..p].
+// layout: B1[((s * nq1 + q) * (p+1)) + r]
+__global__ void k_basis_1d(int p, int nspan, int nq1, const double* __restrict__ knot, const double* __restrict__ gx,
+                           double* __restrict__ B1, double* __restrict__ D1) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nspan * nq1) return;
+  const int s = t / nq1, q = t % nq1;
+  const int ip = s + p;
+  const double xi = gx[q];
+  // KnotVector::getKnotLocation (nurbs.hpp:99-100)
+  const double u = (xi * knot[ip + 1] + (1. - xi) * knot[ip]);
+  double left[MAXP + 1], right[MAXP + 1];
+  {
+    // CalcShape, Algorithm A2.2
+    double shape[MAXP + 1];
+    shape[0] = 1.;
+    for (int j = 1; j <= p; ++j) {
+      left[j] = u - knot[ip + 1 - j];
+      right[j] = knot[ip + j] - u;
+      double saved = 0.;
+      for (int r = 0; r < j; ++r) {
+        const double tmp = shape[r] / (right[r + 1] + left[j - r]);
+        shape[r] = saved + right[r + 1] * tmp;
+        saved = left[j - r] * tmp;
+      }
+      shape[j] = saved;
+    }
+    for (int r = 0; r <= p; r++) B1[(size_t)t * (p + 1) + r] = shape[r];
+  }
+  {
+    // CalcDShape, Algorithm A2.3
+    double ndu[MAXP + 1][MAXP + 1];
+    ndu[0][0] = 1.0;
+    for (int j = 1; j <= p; j++) {
+      left[j] = u - knot[ip - j + 1];
+      right[j] = knot[ip + j] - u;
+      double saved = 0.0;
+      for (int r = 0; r < j; r++) {
+        ndu[j][r] = right[r + 1] + left[j - r];
+        const double temp = ndu[r][j - 1] / ndu[j][r];
+        ndu[r][j] = saved + right[r + 1] * temp;
+        saved = left[j - r] * temp;
+      }
+      ndu[j][j] = saved;
+    }
+    const double scale = p * (knot[ip + 1] - knot[ip]);
+    for (int r = 0; r <= p; ++r) {
+      double d = 0.0;
+      const int rk = r - 1, pk = p - 1;
+      if (r >= 1) d = ndu[rk][pk] / ndu[p][rk];
+      if (r <= pk) d -= ndu[r][pk] / ndu[p][r];
+      D1[(size_t)t * (p + 1) + r] = d * scale;  // grad *= p*(knot(ip+1) - knot(ip))
+    }
+  }
+}
+
+struct TabArgs {
+  int64_t e0, ne;
+  int nq1;
+  const int32_t* __restrict__ vdofs;   // all elements, NE x tdof
+  const int32_t* __restrict__ el_ijk;  // ne x DIM, relative to e0
+  const double* __restrict__ B1[3];
+  const double* __restrict__ D1[3];
+  const double* __restrict__ gw;       // 1D weights
+  const double* __restrict__ x_ref;    // NV byVDIM
+  const double* __restrict__ wts;      // Nn or nullptr (all 1.0)
+  double* __restrict__ dNdX;
+  double* __restrict__ wdetJ;
+  double* __restrict__ N;              // optional: NE x nq x nd shape values
+  int* __restrict__ flag;
+};
+
+// One thread per (element, quadrature point).
+template <int DIM, int P>
+__global__ void __launch_bounds__(128) k_tables(const TabArgs g) {
+  constexpr int P1 = P + 1;
+  constexpr int ND = (DIM == 3) ? P1 * P1 * P1 : P1 * P1;
+  constexpr int TD = DIM * ND;
+  const int nq1 = g.nq1;
+  const int nq = (DIM == 3) ? nq1 * nq1 * nq1 : nq1 * nq1;
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= g.ne * nq) return;
+  const int64_t el = t / nq;
+  const int q = (int)(t % nq);
+  const int64_t e = g.e0 + el;
+  int qd[3], sp[3];
+  qd[0] = q % nq1;
+  qd[1] = (q / nq1) % nq1;
+  qd[2] = (DIM == 3) ? q / (nq1 * nq1) : 0;
+  for (int d = 0; d < DIM; d++) sp[d] = g.el_ijk[el * DIM + d];
+  const double *sx = g.B1[0] + ((size_t)sp[0] * nq1 + qd[0]) * P1, *dsx = g.D1[0] + ((size_t)sp[0] * nq1 + qd[0]) * P1;
+  const double *sy = g.B1[1] + ((size_t)sp[1] * nq1 + qd[1]) * P1, *dsy = g.D1[1] + ((size_t)sp[1] * nq1 + qd[1]) * P1;
+  const double *sz = nullptr, *dsz = nullptr;
+  if (DIM == 3) {
+    sz = g.B1[2] + ((size_t)sp[2] * nq1 + qd[2]) * P1;
+    dsz = g.D1[2] + ((size_t)sp[2] * nq1 + qd[2]) * P1;
+  }
+  const int32_t* vd = g.vdofs + e * TD;
+
+  double uu[ND], ds[TD];  // ds(o, d) = ds[o + d*ND]
+  double sum = 0.0, dsum[3] = {0.0, 0.0, 0.0};
+  if (DIM == 3) {
+    int o = 0;
+    for (int k = 0; k < P1; k++) {
+      const double szk = sz[k], dszk = dsz[k];
+      for (int j = 0; j < P1; j++) {
+        const double sy_sz = sy[j] * szk;
+        const double dsy_sz = dsy[j] * szk;
+        const double sy_dsz = sy[j] * dszk;
+        for (int i = 0; i < P1; i++, o++) {
+          const double w = g.wts ? g.wts[vd[o] / DIM] : 1.0;
+          sum += (uu[o] = sx[i] * sy_sz * w);
+          dsum[0] += (ds[o] = dsx[i] * sy_sz * w);
+          dsum[1] += (ds[o + ND] = sx[i] * dsy_sz * w);
+          dsum[2] += (ds[o + 2 * ND] = sx[i] * sy_dsz * w);
+        }
+      }
+    }
+  } else {
+    // NURBS2DFiniteElement::CalcDShape (fe_nurbs.cpp:130-175)
+    int o = 0;
+    for (int j = 0; j < P1; j++) {
+      const double syj = sy[j], dsyj = dsy[j];
+      for (int i = 0; i < P1; i++, o++) {
+        const double w = g.wts ? g.wts[vd[o] / DIM] : 1.0;
+        sum += (uu[o] = sx[i] * syj * w);
+        dsum[0] += (ds[o] = dsx[i] * syj * w);
+        dsum[1] += (ds[o + ND] = sx[i] * dsyj * w);
+      }
+    }
+  }
+  if (g.N) {
+    // CalcShape: shape /= sum  -> m = 1.0/sum; shape[i] *= m  (vector.cpp:183-191)
+    const double m = 1.0 / sum;
+    double* No = g.N + (e * nq + q) * (int64_t)ND;
+    for (int o = 0; o < ND; o++) No[o] = uu[o] * m;
+  }
+  sum = 1.0 / sum;
+  for (int d = 0; d < DIM; d++) dsum[d] *= sum * sum;
+  for (int o = 0; o < ND; o++)
+    for (int d = 0; d < DIM; d++) ds[o + d * ND] = ds[o + d * ND] * sum - uu[o] * dsum[d];
+
+  // dFdx = PointMat * dshape (kernels::Mult: zero, then j, k, i)
+  double Jm[DIM * DIM];
+  for (int i = 0; i < DIM * DIM; i++) Jm[i] = 0.0;
+  for (int j = 0; j < DIM; j++)
+    for (int k = 0; k < ND; k++) {
+      const double c = ds[k + j * ND];
+      for (int i = 0; i < DIM; i++) Jm[i + DIM * j] += g.x_ref[vd[i * ND + k]] * c;
+    }
+  const double detJ = det_small<DIM>(Jm);
+  if (!(detJ > 0.0)) atomicExch(g.flag, 2);
+  double Ji[DIM * DIM];
+  inverse_small<DIM>(Jm, Ji);
+  // dN_dX = dN_dxi * dxi_dX (kernels::Mult)
+  double* out = g.dNdX + (e * nq + q) * (int64_t)TD;
+  for (int j = 0; j < DIM; j++)
+    for (int i = 0; i < ND; i++) {
+      double a = 0.0;
+      for (int k = 0; k < DIM; k++) a += ds[i + k * ND] * Ji[k + DIM * j];
+      out[i + j * ND] = a;
+    }
+  // integration weight: (wx*wy)*wz (intrules.cpp:80), times det_dX_dxi at use (nonlinear_solid.hpp:79)
+  double w = g.gw[qd[0]] * g.gw[qd[1]];
+  if (DIM == 3) w = w * g.gw[qd[2]];
+  g.wdetJ[e * nq + q] = w * detJ;
+}
+
+int set_nodes(mb2_ctx* c, const double* x_ref, const double* weights) {
+  if (!c->d_xref) MB2_CUDA(cudaMalloc(&c->d_xref, sizeof(double) * c->NV));
+  MB2_CUDA(cudaMemcpyAsync(c->d_xref, x_ref, sizeof(double) * c->NV, cudaMemcpyHostToDevice, c->stream));
+  if (weights) {
+    if (!c->d_nodew) MB2_CUDA(cudaMalloc(&c->d_nodew, sizeof(double) * c->Nn));
+    MB2_CUDA(cudaMemcpyAsync(c->d_nodew, weights, sizeof(double) * c->Nn, cudaMemcpyHostToDevice, c->stream));
+  } else if (c->d_nodew) {
+    cudaFree(c->d_nodew);
+    c->d_nodew = nullptr;
+  }
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+
+int generate_patch_tables(mb2_ctx* c, int64_t e0, int64_t ne, int p, const int32_t* ncp, const double* const* knots,
+                          const int32_t* el_ijk, int quad_order, bool want_N) {
+  const int dim = c->dim;
+  if (p < 1 || p > MAXP) { c->err = "degree must be 1..4"; return MB2_ERR_UNSUPPORTED; }
+  int nd = 1;
+  for (int d = 0; d < dim; d++) nd *= p + 1;
+  if (nd != c->nd) { c->err = "(p+1)^dim does not match nd of the connectivity"; return MB2_ERR_ARG; }
+  // IntegrationRules::Get(geom, order): segment real order = order | 1, n = order/2 + 1 (intrules.cpp:1004-1060)
+  const int order = quad_order < 0 ? 2 * p + 3 : quad_order;
+  const int nq1 = (order | 1) / 2 + 1;
+  int nq = 1;
+  for (int d = 0; d < dim; d++) nq *= nq1;
+  if (nq != c->nq || nq1 > MAXQ1) { c->err = "quadrature order does not match nq of the connectivity"; return MB2_ERR_ARG; }
+  if (!c->d_xref) { c->err = "call mb2_set_nodes first"; return MB2_ERR_ARG; }
+  if (e0 < 0 || ne <= 0 || e0 + ne > c->NE) { c->err = "element range out of bounds"; return MB2_ERR_ARG; }
+
+  std::vector<double> gx, gw;
+  gauss_legendre_01(nq1, gx, gw);
+  double *d_gx = nullptr, *d_gw = nullptr, *d_knot[3] = {nullptr, nullptr, nullptr};
+  double *d_B1[3] = {nullptr, nullptr, nullptr}, *d_D1[3] = {nullptr, nullptr, nullptr};
+  int32_t* d_ijk = nullptr;
+  MB2_CUDA(cudaMalloc(&d_gx, sizeof(double) * nq1));
+  MB2_CUDA(cudaMalloc(&d_gw, sizeof(double) * nq1));
+  MB2_CUDA(cudaMemcpyAsync(d_gx, gx.data(), sizeof(double) * nq1, cudaMemcpyHostToDevice, c->stream));
+  MB2_CUDA(cudaMemcpyAsync(d_gw, gw.data(), sizeof(double) * nq1, cudaMemcpyHostToDevice, c->stream));
+  for (int d = 0; d < dim; d++) {
+    const int nk = ncp[d] + p + 1;
+    const int nspan = ncp[d] - p;  // knot spans i = 0 .. ncp-p-1 (ip = i + p), zero-length ones included
+    MB2_CUDA(cudaMalloc(&d_knot[d], sizeof(double) * nk));
+    MB2_CUDA(cudaMemcpyAsync(d_knot[d], knots[d], sizeof(double) * nk, cudaMemcpyHostToDevice, c->stream));
+    MB2_CUDA(cudaMalloc(&d_B1[d], sizeof(double) * nspan * nq1 * (p + 1)));
+    MB2_CUDA(cudaMalloc(&d_D1[d], sizeof(double) * nspan * nq1 * (p + 1)));
+    k_basis_1d<<<(nspan * nq1 + 127) / 128, 128, 0, c->stream>>>(p, nspan, nq1, d_knot[d], d_gx, d_B1[d], d_D1[d]);
+    MB2_CUDA(cudaGetLastError());
+  }
+  MB2_CUDA(cudaMalloc(&d_ijk, sizeof(int32_t) * ne * dim));
+  MB2_CUDA(cudaMemcpyAsync(d_ijk, el_ijk, sizeof(int32_t) * ne * dim, cudaMemcpyHostToDevice, c->stream));
+  const int64_t nqp = c->NE * c->nq;
+  if (!c->d_dNdX) MB2_CUDA(cudaMalloc(&c->d_dNdX, sizeof(double) * nqp * c->tdof));
+  if (!c->d_wdetJ) MB2_CUDA(cudaMalloc(&c->d_wdetJ, sizeof(double) * nqp));
+  if (want_N && !c->d_N) MB2_CUDA(cudaMalloc(&c->d_N, sizeof(double) * nqp * c->nd));
+  MB2_CUDA(cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
+
+  TabArgs a;
+  a.e0 = e0; a.ne = ne; a.nq1 = nq1;
+  a.vdofs = c->d_vdofs; a.el_ijk = d_ijk;
+  for (int d = 0; d < 3; d++) { a.B1[d] = d_B1[d]; a.D1[d] = d_D1[d]; }
+  a.gw = d_gw; a.x_ref = c->d_xref; a.wts = c->d_nodew;
+  a.dNdX = c->d_dNdX; a.wdetJ = c->d_wdetJ; a.N = want_N ? c->d_N : nullptr; a.flag = c->d_flag;
+  const int64_t nthr = ne * nq;
+  const unsigned grid = (unsigned)((nthr + 127) / 128);
+  bool ok = true;
+#define MB2_TAB(D, PP) if (dim == D && p == PP) k_tables<D, PP><<<grid, 128, 0, c->stream>>>(a); else
+  MB2_TAB(3, 1) MB2_TAB(3, 2) MB2_TAB(3, 3) MB2_TAB(2, 1) MB2_TAB(2, 2) MB2_TAB(2, 3) MB2_TAB(2, 4) { ok = false; }
+#undef MB2_TAB
+  if (!ok) { c->err = "no table kernel for this (dim, p)"; return MB2_ERR_UNSUPPORTED; }
+  MB2_CUDA(cudaGetLastError());
+  int flag = 0;
+  MB2_CUDA(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  cudaFree(d_gx); cudaFree(d_gw); cudaFree(d_ijk);
+  for (int d = 0; d < dim; d++) { cudaFree(d_knot[d]); cudaFree(d_B1[d]); cudaFree(d_D1[d]); }
+  if (flag) { c->err = "non-positive geometry Jacobian determinant while generating tables"; return MB2_ERR_NUMERIC; }
+  return MB2_OK;
+}
+
 }  // namespace mb2

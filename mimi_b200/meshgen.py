@@ -126,3 +126,99 @@ def write_box_patch(path: str, p: int, spans, lengths=None) -> None:
             for y in grev[1]:
                 for x in grev[0]:
                     f.write("%r %r 1\n" % (float(x), float(y)))
+
+
+# ---------------------------------------------------------------------------------------------------
+# Synthetic connectivity of a single 3D patch in MFEM's own numbering, so that large meshes (which the
+# reference cannot precompute on a host) get the same DOF indexing the reference would produce.
+#
+# MFEM numbers the control points of a patch as: 8 patch vertices, then the interiors of the 12 patch
+# edges, then of the 6 patch faces, then the patch interior (NURBSExtension::GenerateOffsets,
+# third_party/mfem/mesh/nurbs.cpp:3255-3330), each entity traversed with the orientation the patch
+# topology gives it (NURBSPatchMap::operator()(i,j,k), third_party/mfem/mesh/nurbs.hpp:1201-1240). The
+# entity order/orientation below is the one of the hexahedron topology written by write_box_p1 /
+# write_box_patch; tests/test_meshgen.py checks it against dumps of the compiled reference.
+# Elements run i fastest, then j, then k, and list their (p+1)^3 nodes ii fastest
+# (Generate3DElementDofTable, nurbs.cpp:3759-3823).
+# ---------------------------------------------------------------------------------------------------
+def patch_node_grid(ncp) -> np.ndarray:
+    """Node id of control point (i, j, k) for a single hexahedral patch: int32 array [ncp0, ncp1, ncp2]."""
+    n0, n1, n2 = (int(x) for x in ncp)
+    I, J, K = n0 - 2, n1 - 2, n2 - 2
+    g = np.full((n0, n1, n2), -1, np.int64)
+    # vertices
+    for v, (i, j, k) in enumerate([(0, 0, 0), (-1, 0, 0), (-1, -1, 0), (0, -1, 0),
+                                   (0, 0, -1), (-1, 0, -1), (-1, -1, -1), (0, -1, -1)]):
+        g[i, j, k] = v
+    c = 8
+    ax, ay, az = np.arange(I), np.arange(J), np.arange(K)
+    # edges: 4 along x (the 2nd and 4th reversed), 4 along y, 4 along z
+    for (j, k, rev) in [(0, 0, 0), (-1, 0, 1), (0, -1, 0), (-1, -1, 1)]:
+        g[1:-1, j, k] = c + (ax[::-1] if rev else ax)
+        c += I
+    for (i, k) in [(0, 0), (-1, 0), (0, -1), (-1, -1)]:
+        g[i, 1:-1, k] = c + ay
+        c += J
+    for (i, j) in [(0, 0), (-1, 0), (-1, -1), (0, -1)]:
+        g[i, j, 1:-1] = c + az
+        c += K
+    # faces: z=0, y=0, x=1, y=1, x=0, z=1
+    g[1:-1, 1:-1, 0] = c + ax[:, None] + I * (J - 1 - ay)[None, :]
+    c += I * J
+    g[1:-1, 0, 1:-1] = c + ax[:, None] + I * az[None, :]
+    c += I * K
+    g[-1, 1:-1, 1:-1] = c + ay[:, None] + J * az[None, :]
+    c += J * K
+    g[1:-1, -1, 1:-1] = c + (I - 1 - ax)[:, None] + I * az[None, :]
+    c += I * K
+    g[0, 1:-1, 1:-1] = c + (J - 1 - ay)[:, None] + J * az[None, :]
+    c += J * K
+    g[1:-1, 1:-1, -1] = c + ax[:, None] + I * ay[None, :]
+    c += I * J
+    # interior
+    g[1:-1, 1:-1, 1:-1] = c + ax[:, None, None] + I * (ay[None, :, None] + J * az[None, None, :])
+    assert (g >= 0).all() and c + I * J * K == n0 * n1 * n2
+    return g.astype(np.int32)
+
+
+def patch_connectivity(p: int, spans, lengths=None):
+    """Synthetic single-patch box: returns dict(v_dofs [NE, 3*(p+1)^3] int32 component-major byVDIM,
+    el_ijk [NE,3] int32 knot-span indices, knots (3 arrays), ncp, x_ref [NV] byVDIM (Greville control
+    points = affine geometry), weights [Nn] (all 1), NV)."""
+    lengths = lengths or (1.0, 1.0, 1.0)
+    kvs = [open_uniform_knots(p, n) for n in spans]
+    ncp = [len(kv) - p - 1 for kv in kvs]
+    g = patch_node_grid(ncp)
+    n0, n1, n2 = spans
+    ei, ej, ek = np.meshgrid(np.arange(n0), np.arange(n1), np.arange(n2), indexing="ij")
+    # element order: i fastest
+    order = np.argsort((ek * n1 + ej).ravel() * n0 + ei.ravel(), kind="stable")
+    el_ijk = np.stack([ei.ravel()[order], ej.ravel()[order], ek.ravel()[order]], 1).astype(np.int32)
+    nd = (p + 1) ** 3
+    nodes = np.empty((len(el_ijk), nd), np.int32)
+    a = 0
+    for kk in range(p + 1):
+        for jj in range(p + 1):
+            for ii in range(p + 1):
+                nodes[:, a] = g[el_ijk[:, 0] + ii, el_ijk[:, 1] + jj, el_ijk[:, 2] + kk]
+                a += 1
+    v_dofs = np.concatenate([3 * nodes + c for c in range(3)], 1).astype(np.int32)
+    Nn = g.size
+    x = np.empty((Nn, 3))
+    grev = [greville(p, kv) * L for kv, L in zip(kvs, lengths)]
+    x[g.ravel(), 0] = np.repeat(grev[0], ncp[1] * ncp[2])
+    x[g.ravel(), 1] = np.tile(np.repeat(grev[1], ncp[2]), ncp[0])
+    x[g.ravel(), 2] = np.tile(grev[2], ncp[0] * ncp[1])
+    return dict(v_dofs=v_dofs, el_ijk=el_ijk, knots=kvs, ncp=np.array(ncp, np.int32), x_ref=x.ravel(),
+                weights=np.ones(Nn), NV=3 * Nn, Nn=Nn, NE=len(el_ijk), nd=nd, p=p)
+
+
+def synth_u(NV: int, seed: int = 12345) -> np.ndarray:
+    """u_i = 1e-3 (U_i - 0.5), U_i = splitmix64(seed + i) >> 11 scaled to [0,1): SURVEY.md section 8(d);
+    the same rule oracle/ref_harness.cpp applies inside the compiled reference."""
+    x = (np.arange(NV, dtype=np.uint64) + np.uint64(seed)) + np.uint64(0x9E3779B97F4A7C15)
+    x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    x = x ^ (x >> np.uint64(31))
+    U = (x >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+    return 1.0e-3 * (U - 0.5)

@@ -138,7 +138,7 @@ def run_ref_dump(mesh, elevate, refine, material, outdir, gf=1.0, nthreads=1, u_
     return load_dump(outdir)
 
 
-def run_ref_time(mesh, elevate, refine, material, nthreads, reps):
-    cmd = [REF_BIN, "time", mesh, str(elevate), str(refine), material, str(nthreads), str(reps)]
+def run_ref_time(mesh, elevate, refine, material, nthreads, reps, warmup=0):
+    cmd = [REF_BIN, "time", mesh, str(elevate), str(refine), material, str(nthreads), str(reps), str(warmup)]
     p = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, check=True, text=True)
     return json.loads(p.stderr.strip().splitlines()[-1])

@@ -4,7 +4,7 @@
 // and dumps / times what it computes. Nothing in the product links or executes this file.
 //
 //   mimi_ref dump <mesh> <elevate> <refine> <material> <nthreads> <gf> <u.bin|-> <outdir> [lite]
-//   mimi_ref time <mesh> <elevate> <refine> <material> <nthreads> <reps>
+//   mimi_ref time <mesh> <elevate> <refine> <material> <nthreads> <reps> [warmup reps, untimed]
 // material: neohookean | stvk  (E=2100, nu=0.3, rho=1: tests/test_nonlinear_solid.py:59-62)
 #include <chrono>
 #include <cstdint>
@@ -185,6 +185,7 @@ int main(int argc, char** argv) {
   }
   if (mode == "time") {
     const int reps = std::atoi(argv[7]);
+    const int warm = argc > 8 ? std::atoi(argv[8]) : 0;
     Setup s = build(mesh_file, elevate, refine, material, nthreads, false);
     auto& pre = *s.pre;
     const int NV = pre.n_v_dofs_, NE = pre.n_elements_;
@@ -193,6 +194,10 @@ int main(int argc, char** argv) {
     fill_u(u, "-");
     mfem::SparseMatrix A(*pre.sparsity_pattern_);
     double best_rg = 1e300, best_r = 1e300, sum_rg = 0;
+    for (int i = 0; i < warm; ++i) {
+      r = 0.0; A = 0.0;
+      s.integ->AddDomainResidualAndGrad(u, 1.0, r, A);
+    }
     for (int i = 0; i < reps; ++i) {
       r = 0.0; A = 0.0;
       auto t0 = std::chrono::steady_clock::now();
