@@ -199,6 +199,7 @@ def gpu_arm(args):
     n, p = args.n, 2
     stream = torch.cuda.Stream()            # the library launches on this stream, so torch events see its work
     ctx = capi.Context(local, stream=stream.cuda_stream)
+    ctx.set_option("elem_variant", args.variant)
     M = build_problem(ctx, n, p, rank)
     NE, nq, NV, nnz = M["NE"], M["nq"], M["NV"], M["nnz"]
     ctx.set_u(M["u"])
@@ -331,6 +332,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = max(args.warmup, 3) if not os.environ.get("MB2_BENCH_ALLOW_SHORT") else args.warmup

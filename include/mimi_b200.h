@@ -128,6 +128,9 @@ int mb2_last_launch_count(mb2_ctx* ctx);
 /* Synchronise ctx's stream. */
 int mb2_sync(mb2_ctx* ctx);
 
+/* Tuning / A-B switches (never change results): "elem_variant" 0 = default kernels, 1 = one-thread-per-dof FD kernel. */
+int mb2_set_option(mb2_ctx* ctx, const char* name, int value);
+
 /* FP64 pipe micro-benchmark used for the roofline denominator: runs `iters` dependent-chain-free
  * DMUL+DADD pairs (fma = 0) or DFMA (fma = 1) per thread on a full grid; returns TFLOP/s. */
 int mb2_measure_fp64_peak(mb2_ctx* ctx, int fma, double* tflops);

@@ -323,6 +323,14 @@ int mb2_measure_fp64_peak(mb2_ctx* c, int fma, double* tflops) {
   return mb2::launch_fp64_peak(c, fma, tflops);
 }
 
+int mb2_set_option(mb2_ctx* c, const char* name, int value) {
+  CHECK_CTX(c);
+  REQUIRE(name, "null option name");
+  if (!std::strcmp(name, "elem_variant")) { c->elem_variant = value; return MB2_OK; }
+  c->err = std::string("unknown option ") + name;
+  return MB2_ERR_ARG;
+}
+
 int mb2_set_nodes(mb2_ctx* c, const double* x_ref, const double* weights) {
   CHECK_CTX(c);
   REQUIRE(c->NE > 0, "call mb2_set_connectivity first");

@@ -153,12 +153,187 @@ __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel
               for (int i = 0; i < ND; i++) R[i + j * ND] += dN[i + k * ND] * bjk;
             }
         }
-        double* out = g.KeT + e * (int64_t)(TD * TD) + t;
+        // KeT layout: [e][row node i][perturbed dof m][row component j]  <->  K_e(i + j*ND, m)
+        double* out = g.KeT + e * (int64_t)(TD * TD) + t * DIM;
 #pragma unroll
-        for (int j = 0; j < TD; j++) out[(int64_t)j * TD] = (R[j] - sRb[j]) * hinv;
+        for (int j = 0; j < TD; j++) out[(int64_t)(j % ND) * (TD * DIM) + j / ND] = (R[j] - sRb[j]) * hinv;
       }
       __syncthreads();
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// FD-tangent element kernel, two-phase form (the production kernel for 3D).
+//
+// The 82 residual evaluations of one element (base + one per perturbed dof m) are split into
+//   phase 1  "stress":      task (m, q)  -> b_m(q)[j,k] = (w detJ)_q * P_m(q)[j,k]          (9 doubles to smem)
+//   phase 2  "accumulate":  task (m, j)  -> R_m(i, j) += dN(q; i, k) * b_m(q)[j, k], q then k ascending
+// Both phases keep ~95 % of the lanes busy (NM*QC and NM*DIM threads of a 256-thread CTA), and a
+// thread only carries ND accumulators instead of DIM*ND, so two CTAs (16 warps) fit per SM.
+// Every floating-point value is produced by the reference's own operation sequence (Appendix A of
+// SURVEY.md): the split changes which thread executes an operation, never the operation order seen
+// by any accumulator.
+// ---------------------------------------------------------------------------------------------
+template <int DIM, int ND, int NQ>
+struct Elem2Cfg {
+  static constexpr int TD = DIM * ND;
+  static constexpr int DD = DIM * DIM;
+  static constexpr int NM = TD + 1;                 // perturbations + the base evaluation (m == TD)
+  static constexpr int NT = 256;
+  static constexpr int QC = NT / NM;                // quadrature points per chunk
+  static constexpr int NCH = (NQ + QC - 1) / QC;
+  static constexpr int NDP = (ND + 1) / 2 * 2;      // padded row of dN (16-byte aligned rows)
+  static constexpr int NB = NM * DIM;               // phase-2 threads
+  static constexpr int OFF_DN = 0;                  // [NQ][DIM][NDP]
+  static constexpr int OFF_FB = OFF_DN + NQ * DIM * NDP;   // [NQ][DD] base F
+  static constexpr int OFF_SB = OFF_FB + NQ * DD;          // [2][QC][DIM][NB]
+  static constexpr int OFF_WD = OFF_SB + 2 * QC * DIM * NB;
+  static constexpr int OFF_UE = OFF_WD + NQ;
+  static constexpr int OFF_RB = OFF_UE + TD;
+  static constexpr int SMEM_DOUBLES = OFF_RB + TD;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
+  static_assert(QC >= 1 && NB <= NT, "CTA too small for this element type");
+};
+
+template <int DIM, int ND, int NQ, int MAT>
+__global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
+  using Cfg = Elem2Cfg<DIM, ND, NQ>;
+  constexpr int TD = Cfg::TD, DD = Cfg::DD, NM = Cfg::NM, NT = Cfg::NT, QC = Cfg::QC, NCH = Cfg::NCH, NDP = Cfg::NDP,
+                NB = Cfg::NB;
+  extern __shared__ __align__(16) double smem[];
+  double* sdN = smem + Cfg::OFF_DN;
+  double* sFb = smem + Cfg::OFF_FB;
+  double* sb = smem + Cfg::OFF_SB;
+  double* swd = smem + Cfg::OFF_WD;
+  double* sue = smem + Cfg::OFF_UE;
+  double* sRb = smem + Cfg::OFF_RB;
+  const int t = threadIdx.x;
+  // phase-1 role
+  const int qs1 = t / NM, m1 = t % NM;
+  const bool act1 = t < NM * QC;
+  const int c1 = (m1 < TD) ? m1 / ND : 0, a1 = (m1 < TD) ? m1 % ND : -1;
+  // phase-2 role
+  const int m2 = t / DIM, j2 = t % DIM;
+  const bool act2 = t < NB;
+
+  for (int64_t e = blockIdx.x; e < g.NE; e += gridDim.x) {
+    // ---- stage: gathered dofs (Vector::GetSubVector), weights, dN_dX rows padded to NDP
+    if (t < TD) sue[t] = g.u[g.vdofs[e * TD + t]];
+    if (t < NQ) swd[t] = g.wdetJ[e * NQ + t];
+    {
+      const double* src = g.dNdX + e * (int64_t)(NQ * TD);
+      for (int idx = t; idx < NQ * TD; idx += NT) {
+        const int row = idx / ND, i = idx - row * ND;  // row = q*DIM + k
+        sdN[row * NDP + i] = src[idx];
+      }
+    }
+    __syncthreads();
+    // ---- base F for every q: MultAtB(element_x_mat_, dN_dX, F_) + AddDiagonal(1.0) (integrator_utils.cpp:33-40)
+    for (int task = t; task < NQ * DD; task += NT) {
+      const int q = task / DD, n = task - q * DD;
+      const int i = n % DIM, j = n / DIM;
+      const double* dN = sdN + (q * DIM + j) * NDP;
+      const double* ui = sue + i * ND;
+      double d = 0.0;
+#pragma unroll
+      for (int k = 0; k < ND; k++) d += ui[k] * dN[k];
+      if (i == j) d += 1.0;
+      sFb[task] = d;
+    }
+    // perturbation of this thread's dof (nonlinear_solid.cpp:62-68)
+    double up1 = 0.0;
+    if (act1 && m1 < TD) {
+      const double orig = sue[m1];
+      const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
+      up1 = orig + h;
+    }
+    double R[ND];
+#pragma unroll
+    for (int i = 0; i < ND; i++) R[i] = 0.0;
+    __syncthreads();
+
+#pragma unroll 1
+    for (int ch = 0; ch < NCH; ch++) {
+      double* sbc = sb + (ch & 1) * (QC * DIM * NB);
+      // ---- phase 1: stress of (m1, q)
+      const int q1 = ch * QC + qs1;
+      if (act1 && q1 < NQ) {
+        double F[DD], P[DD];
+#pragma unroll
+        for (int n = 0; n < DD; n++) F[n] = sFb[q1 * DD + n];
+        if (m1 < TD) {
+          // only row c1 of F depends on the perturbed dof; the other rows are bit-identical to the base F
+          const double* uc = sue + c1 * ND;
+          const double* dN = sdN + q1 * DIM * NDP;
+          double drow[DIM];
+#pragma unroll
+          for (int j = 0; j < DIM; j++) drow[j] = 0.0;
+#pragma unroll
+          for (int k = 0; k < ND; k++) {
+            const double uk = (k == a1) ? up1 : uc[k];
+#pragma unroll
+            for (int j = 0; j < DIM; j++) drow[j] += uk * dN[j * NDP + k];
+          }
+#pragma unroll
+          for (int j = 0; j < DIM; j++) {
+            const double fnew = (j == c1) ? drow[j] + 1.0 : drow[j];
+#pragma unroll
+            for (int i = 0; i < DIM; i++)
+              if (i == c1) F[i + DIM * j] = fnew;
+          }
+        }
+        material_pk1<DIM, MAT>(g.lambda, g.mu, F, P);
+        const double aq = swd[q1];
+        double* o = sbc + qs1 * (DIM * NB) + m1 * DIM;
+        // bjk = a * P(j,k)   (densemat.cpp:3008)
+#pragma unroll
+        for (int k = 0; k < DIM; k++)
+#pragma unroll
+          for (int j = 0; j < DIM; j++) o[k * NB + j] = aq * P[j + DIM * k];
+      }
+      __syncthreads();
+      // ---- phase 2: R_m(:, j) += dN(q; :, k) * b_m(q)[j, k]   (AddMult_a_ABt, densemat.cpp:3002-3015)
+      if (act2) {
+#pragma unroll
+        for (int qs = 0; qs < QC; qs++) {
+          const int q = ch * QC + qs;
+          if (q < NQ) {
+#pragma unroll
+            for (int k = 0; k < DIM; k++) {
+              const double bjk = sbc[(qs * DIM + k) * NB + t];
+              const double2* d2 = reinterpret_cast<const double2*>(sdN + (q * DIM + k) * NDP);
+#pragma unroll
+              for (int x = 0; x < ND / 2; x++) {
+                const double2 v = d2[x];
+                R[2 * x] += v.x * bjk;
+                R[2 * x + 1] += v.y * bjk;
+              }
+              if (ND % 2) R[ND - 1] += sdN[(q * DIM + k) * NDP + ND - 1] * bjk;
+            }
+          }
+        }
+      }
+    }
+    // ---- base residual -> smem + global; then forward differences (nonlinear_solid.cpp:69-74)
+    if (act2 && m2 == TD) {
+#pragma unroll
+      for (int i = 0; i < ND; i++) {
+        sRb[i + j2 * ND] = R[i];
+        g.Re[e * TD + i + j2 * ND] = R[i];
+      }
+    }
+    __syncthreads();
+    if (act2 && m2 < TD) {
+      const double orig = sue[m2];
+      const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
+      const double hinv = 1. / h;
+      // KeT[e][row node i][perturbed dof m][row component j]: t = m*DIM + j is the fastest index
+      double* out = g.KeT + e * (int64_t)(TD * TD) + t;
+#pragma unroll
+      for (int i = 0; i < ND; i++) out[(int64_t)i * (TD * DIM)] = (R[i] - sRb[i + j2 * ND]) * hinv;
+    }
+    __syncthreads();
   }
 }
 
@@ -184,6 +359,8 @@ __global__ void residual_gather_kernel(int dim, int nd, int64_t Nn, const int64_
   r[v] += acc;
 }
 
+// KeT holds, per element, [row node a][column dof m][row component ci]: the dim x tdof block of one node
+// is one contiguous run of dim*tdof doubles.
 // One CTA per node I (block row of dim rows). Thread (ci, cj, b) adds K_e(a + ci*nd, b + cj*nd) into
 // the block-row accumulator slot rank[e][a][b]; elements visited in ascending id with a barrier in
 // between. Finally A[row, col] += grad_factor * acc  (nonlinear_base.hpp:141-144).
@@ -201,14 +378,14 @@ __global__ void csr_gather_kernel(int nd, int64_t Nn, const int64_t* __restrict_
     const int nn = nnbr[I];
     for (int i = t; i < nn * DD; i += blockDim.x) acc[i] = 0.0;
     __syncthreads();
-    const int ci = t / tdof, col = t % tdof;  // col = b + cj*nd
+    const int col = t / DIM, ci = t % DIM;  // col = b + cj*nd; consecutive threads read consecutive doubles
     const int cj = col / nd, b = col % nd;
     for (int64_t p = n2e_ptr[I]; p < n2e_ptr[I + 1]; p++) {
       const int64_t e = n2e_elem[p];
       const int a = n2e_loc[p];
       if (t < DIM * tdof) {
         const int s = rank[(e * nd + a) * nd + b];
-        acc[(s * DIM + ci) * DIM + cj] += KeT[e * (int64_t)(tdof * tdof) + (int64_t)(a + ci * nd) * tdof + col];
+        acc[(s * DIM + ci) * DIM + cj] += KeT[((e * nd + a) * (int64_t)tdof + col) * DIM + ci];
       }
       __syncthreads();
     }
@@ -242,6 +419,21 @@ static int launch_element(mb2_ctx* c, const ElemArgs& a) {
   return MB2_OK;
 }
 
+template <int DIM, int ND, int NQ, int MAT>
+static int launch_element_fd(mb2_ctx* c, const ElemArgs& a) {
+  using Cfg = Elem2Cfg<DIM, ND, NQ>;
+  auto kern = element_fd_kernel<DIM, ND, NQ, MAT>;
+  MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+  int per_sm = 0;
+  MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::NT, Cfg::SMEM_BYTES));
+  if (per_sm < 1) per_sm = 1;
+  int64_t grid = (int64_t)c->sm_count * per_sm;  // persistent: a whole number of resident CTAs per SM
+  if (grid > a.NE) grid = a.NE;
+  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, c->stream>>>(a);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
 template <int DIM, int ND, int NQ, bool GRAD, int MINB>
 static int launch_element_mat(mb2_ctx* c, const ElemArgs& a) {
   switch (c->mat_kind) {
@@ -255,6 +447,12 @@ static int launch_element_mat(mb2_ctx* c, const ElemArgs& a) {
 template <bool GRAD>
 static int dispatch_element(mb2_ctx* c, const ElemArgs& a) {
   const int dim = c->dim, nd = c->nd, nq = c->nq;
+  if (GRAD && dim == 3 && nd == 27 && nq == 64 && c->elem_variant != 1) {
+    switch (c->mat_kind) {
+      case MAT_NEOHOOKEAN: return launch_element_fd<3, 27, 64, MAT_NEOHOOKEAN>(c, a);
+      case MAT_STVK: return launch_element_fd<3, 27, 64, MAT_STVK>(c, a);
+    }
+  }
   if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a);
   if (dim == 3 && nd == 8 && nq == 27) return launch_element_mat<3, 8, 27, GRAD, 4>(c, a);
   if (dim == 2 && nd == 16 && nq == 25) return launch_element_mat<2, 16, 25, GRAD, 4>(c, a);

@@ -19,6 +19,7 @@ struct mb2_ctx {
   int64_t NE = 0, NV = 0, Nn = 0, nnz = 0;
 
   // material
+  int elem_variant = 0;  // 0 = default kernels, 1 = force the one-thread-per-dof FD kernel (A/B tests)
   int mat_kind = -1;
   double lambda = 0, mu = 0;
 
@@ -52,7 +53,7 @@ struct mb2_ctx {
 
   // per-element results
   double* d_Re = nullptr;  // NE x tdof
-  double* d_KeT = nullptr; // NE x tdof x tdof, [residual row j][perturbed dof i], i fastest
+  double* d_KeT = nullptr; // NE x [row node][perturbed dof][row component]  = K_e(node + comp*nd, dof)
   int* d_flag = nullptr;   // device failure flag
 
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
