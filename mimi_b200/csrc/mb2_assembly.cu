@@ -154,9 +154,10 @@ __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel
             }
         }
         // KeT layout: [e][row node i][perturbed dof m][row component j]  <->  K_e(i + j*ND, m)
-        double* out = g.KeT + e * (int64_t)(TD * TD) + t * DIM;
+        constexpr int KP = (TD * DIM + 3) / 4 * 4;  // pitch of one node-row block (see Elem2Cfg::KP)
+        double* out = g.KeT + e * (int64_t)(ND * KP) + t * DIM;
 #pragma unroll
-        for (int j = 0; j < TD; j++) out[(int64_t)(j % ND) * (TD * DIM) + j / ND] = (R[j] - sRb[j]) * hinv;
+        for (int j = 0; j < TD; j++) out[(int64_t)(j % ND) * KP + j / ND] = (R[j] - sRb[j]) * hinv;
       }
       __syncthreads();
     }
@@ -183,24 +184,32 @@ struct Elem2Cfg {
   static constexpr int NT = 256;
   static constexpr int QC = NT / NM;                // quadrature points per chunk
   static constexpr int NCH = (NQ + QC - 1) / QC;
-  static constexpr int NDP = (ND + 1) / 2 * 2;      // padded row of dN (16-byte aligned rows)
-  static constexpr int NB = NM * DIM;               // phase-2 threads
-  static constexpr int OFF_DN = 0;                  // [NQ][DIM][NDP]
+  static constexpr int NB = NM * DIM;               // phase-2 columns (m, j)
+  // phase-2 register tile: a thread owns TI rows i x TC columns (m,j); a warp is LI x LC lanes, so a
+  // dN value is re-used TC times and a b value TI times out of registers (shared memory delivers one
+  // 8-byte word per wavefront for a broadcast, so the un-tiled form is bound by shared memory).
+  static constexpr int LI = 4, LC = 8, TC = 4;
+  static constexpr int TI = (ND + LI - 1) / LI;
+  static constexpr int NDP = (LI * TI + 1) / 2 * 2;        // padded row of dN / ue (16-byte aligned rows)
+  static constexpr int NBP = (NB + TC - 1) / TC * TC;      // padded column count of the b buffer
+  static constexpr int KP = (TD * DIM + 3) / 4 * 4;        // pitch of one node-row block of K_e (32-byte aligned)
+  static constexpr int OFF_DN = 0;                         // [NQ][DIM][NDP]
   static constexpr int OFF_FB = OFF_DN + NQ * DIM * NDP;   // [NQ][DD] base F
-  static constexpr int OFF_SB = OFF_FB + NQ * DD;          // [2][QC][DIM][NB]
-  static constexpr int OFF_WD = OFF_SB + 2 * QC * DIM * NB;
-  static constexpr int OFF_UE = OFF_WD + NQ;
-  static constexpr int OFF_RB = OFF_UE + TD;
+  static constexpr int OFF_SB = OFF_FB + NQ * DD;          // [2][QC][DIM][NBP]
+  static constexpr int OFF_WD = OFF_SB + 2 * QC * DIM * NBP;
+  static constexpr int OFF_UE = OFF_WD + NQ;               // [DIM][NDP]
+  static constexpr int OFF_RB = OFF_UE + DIM * NDP;
   static constexpr int SMEM_DOUBLES = OFF_RB + TD;
   static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
-  static_assert(QC >= 1 && NB <= NT, "CTA too small for this element type");
+  static_assert(QC >= 1 && NBP <= (NT / 32) * LC * TC && LI * LC == 32, "CTA too small for this element type");
+  static_assert(NBP % 4 == 0 && OFF_SB % 2 == 0 && (QC * DIM * NBP) % 2 == 0, "b buffer alignment");
 };
 
 template <int DIM, int ND, int NQ, int MAT>
 __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
   using Cfg = Elem2Cfg<DIM, ND, NQ>;
   constexpr int TD = Cfg::TD, DD = Cfg::DD, NM = Cfg::NM, NT = Cfg::NT, QC = Cfg::QC, NCH = Cfg::NCH, NDP = Cfg::NDP,
-                NB = Cfg::NB;
+                NB = Cfg::NB, NBP = Cfg::NBP, TI = Cfg::TI, TC = Cfg::TC, LI = Cfg::LI, LC = Cfg::LC, KP = Cfg::KP;
   extern __shared__ __align__(16) double smem[];
   double* sdN = smem + Cfg::OFF_DN;
   double* sFb = smem + Cfg::OFF_FB;
@@ -209,17 +218,26 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
   double* sue = smem + Cfg::OFF_UE;
   double* sRb = smem + Cfg::OFF_RB;
   const int t = threadIdx.x;
-  // phase-1 role
+  // phase-1 role: one stress evaluation (m1, q = chunk*QC + qs1)
   const int qs1 = t / NM, m1 = t % NM;
   const bool act1 = t < NM * QC;
   const int c1 = (m1 < TD) ? m1 / ND : 0, a1 = (m1 < TD) ? m1 % ND : -1;
-  // phase-2 role
-  const int m2 = t / DIM, j2 = t % DIM;
-  const bool act2 = t < NB;
+  // phase-2 role: rows i0 .. i0+TI-1, columns col0 .. col0+TC-1 (column = m*DIM + j)
+  const int lane = t & 31, warp = t >> 5;
+  const int i0 = (lane % LI) * TI;
+  const int col0 = (warp * LC + lane / LI) * TC;
+  const bool act2 = col0 < NB;
+
+  // zero the pad lanes once: they are multiplied into accumulators that are never stored
+  for (int idx = t; idx < NQ * DIM; idx += NT)
+    for (int i = ND; i < NDP; i++) sdN[idx * NDP + i] = 0.0;
+  for (int idx = t; idx < 2 * QC * DIM * NBP; idx += NT) sb[idx] = 0.0;
+  if (t < DIM)
+    for (int i = ND; i < NDP; i++) sue[t * NDP + i] = 0.0;
 
   for (int64_t e = blockIdx.x; e < g.NE; e += gridDim.x) {
     // ---- stage: gathered dofs (Vector::GetSubVector), weights, dN_dX rows padded to NDP
-    if (t < TD) sue[t] = g.u[g.vdofs[e * TD + t]];
+    if (t < TD) sue[(t / ND) * NDP + t % ND] = g.u[g.vdofs[e * TD + t]];
     if (t < NQ) swd[t] = g.wdetJ[e * NQ + t];
     {
       const double* src = g.dNdX + e * (int64_t)(NQ * TD);
@@ -234,7 +252,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
       const int q = task / DD, n = task - q * DD;
       const int i = n % DIM, j = n / DIM;
       const double* dN = sdN + (q * DIM + j) * NDP;
-      const double* ui = sue + i * ND;
+      const double* ui = sue + i * NDP;
       double d = 0.0;
 #pragma unroll
       for (int k = 0; k < ND; k++) d += ui[k] * dN[k];
@@ -244,19 +262,21 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
     // perturbation of this thread's dof (nonlinear_solid.cpp:62-68)
     double up1 = 0.0;
     if (act1 && m1 < TD) {
-      const double orig = sue[m1];
+      const double orig = sue[c1 * NDP + a1];
       const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
       up1 = orig + h;
     }
-    double R[ND];
+    double R[TI][TC];
 #pragma unroll
-    for (int i = 0; i < ND; i++) R[i] = 0.0;
+    for (int x = 0; x < TI; x++)
+#pragma unroll
+      for (int y = 0; y < TC; y++) R[x][y] = 0.0;
     __syncthreads();
 
 #pragma unroll 1
     for (int ch = 0; ch < NCH; ch++) {
-      double* sbc = sb + (ch & 1) * (QC * DIM * NB);
-      // ---- phase 1: stress of (m1, q)
+      double* sbc = sb + (ch & 1) * (QC * DIM * NBP);
+      // ---- phase 1: stress of (m1, q1)
       const int q1 = ch * QC + qs1;
       if (act1 && q1 < NQ) {
         double F[DD], P[DD];
@@ -264,16 +284,22 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
         for (int n = 0; n < DD; n++) F[n] = sFb[q1 * DD + n];
         if (m1 < TD) {
           // only row c1 of F depends on the perturbed dof; the other rows are bit-identical to the base F
-          const double* uc = sue + c1 * ND;
-          const double* dN = sdN + q1 * DIM * NDP;
+          const double2* uc2 = reinterpret_cast<const double2*>(sue + c1 * NDP);
+          const double2* dN2 = reinterpret_cast<const double2*>(sdN + q1 * DIM * NDP);
           double drow[DIM];
 #pragma unroll
           for (int j = 0; j < DIM; j++) drow[j] = 0.0;
 #pragma unroll
-          for (int k = 0; k < ND; k++) {
-            const double uk = (k == a1) ? up1 : uc[k];
+          for (int x = 0; x < (ND + 1) / 2; x++) {
+            const double2 uv = uc2[x];
+            const double u0 = (2 * x == a1) ? up1 : uv.x;
+            const double u1 = (2 * x + 1 == a1) ? up1 : uv.y;
 #pragma unroll
-            for (int j = 0; j < DIM; j++) drow[j] += uk * dN[j * NDP + k];
+            for (int j = 0; j < DIM; j++) {
+              const double2 dv = dN2[j * (NDP / 2) + x];
+              drow[j] += u0 * dv.x;
+              if (2 * x + 1 < ND) drow[j] += u1 * dv.y;
+            }
           }
 #pragma unroll
           for (int j = 0; j < DIM; j++) {
@@ -285,15 +311,15 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
         }
         material_pk1<DIM, MAT>(g.lambda, g.mu, F, P);
         const double aq = swd[q1];
-        double* o = sbc + qs1 * (DIM * NB) + m1 * DIM;
+        double* o = sbc + qs1 * (DIM * NBP) + m1 * DIM;
         // bjk = a * P(j,k)   (densemat.cpp:3008)
 #pragma unroll
         for (int k = 0; k < DIM; k++)
 #pragma unroll
-          for (int j = 0; j < DIM; j++) o[k * NB + j] = aq * P[j + DIM * k];
+          for (int j = 0; j < DIM; j++) o[k * NBP + j] = aq * P[j + DIM * k];
       }
       __syncthreads();
-      // ---- phase 2: R_m(:, j) += dN(q; :, k) * b_m(q)[j, k]   (AddMult_a_ABt, densemat.cpp:3002-3015)
+      // ---- phase 2: R(i, col) += dN(q; i, k) * b(q; col, k), q then k ascending (AddMult_a_ABt, densemat.cpp:3002-3015)
       if (act2) {
 #pragma unroll
         for (int qs = 0; qs < QC; qs++) {
@@ -301,37 +327,71 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
           if (q < NQ) {
 #pragma unroll
             for (int k = 0; k < DIM; k++) {
-              const double bjk = sbc[(qs * DIM + k) * NB + t];
-              const double2* d2 = reinterpret_cast<const double2*>(sdN + (q * DIM + k) * NDP);
+              double bv[TC], dv[TI];
+              const double2* b2 = reinterpret_cast<const double2*>(sbc + (qs * DIM + k) * NBP + col0);
 #pragma unroll
-              for (int x = 0; x < ND / 2; x++) {
-                const double2 v = d2[x];
-                R[2 * x] += v.x * bjk;
-                R[2 * x + 1] += v.y * bjk;
+              for (int y = 0; y < TC / 2; y++) {
+                const double2 v = b2[y];
+                bv[2 * y] = v.x;
+                bv[2 * y + 1] = v.y;
               }
-              if (ND % 2) R[ND - 1] += sdN[(q * DIM + k) * NDP + ND - 1] * bjk;
+              const double* dN = sdN + (q * DIM + k) * NDP + i0;
+#pragma unroll
+              for (int x = 0; x < TI; x++) dv[x] = dN[x];
+#pragma unroll
+              for (int x = 0; x < TI; x++)
+#pragma unroll
+                for (int y = 0; y < TC; y++) R[x][y] += dv[x] * bv[y];
             }
           }
         }
       }
     }
     // ---- base residual -> smem + global; then forward differences (nonlinear_solid.cpp:69-74)
-    if (act2 && m2 == TD) {
+    if (act2) {
 #pragma unroll
-      for (int i = 0; i < ND; i++) {
-        sRb[i + j2 * ND] = R[i];
-        g.Re[e * TD + i + j2 * ND] = R[i];
+      for (int y = 0; y < TC; y++) {
+        const int col = col0 + y;
+        if (col >= TD * DIM && col < NB) {
+          const int j = col - TD * DIM;
+#pragma unroll
+          for (int x = 0; x < TI; x++)
+            if (i0 + x < ND) {
+              sRb[i0 + x + j * ND] = R[x][y];
+              g.Re[e * TD + i0 + x + j * ND] = R[x][y];
+            }
+        }
       }
     }
     __syncthreads();
-    if (act2 && m2 < TD) {
-      const double orig = sue[m2];
-      const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
-      const double hinv = 1. / h;
-      // KeT[e][row node i][perturbed dof m][row component j]: t = m*DIM + j is the fastest index
-      double* out = g.KeT + e * (int64_t)(TD * TD) + t;
+    if (act2) {
+      // K_e block layout: [row node i][KP]: column = perturbed dof m * DIM + row component j
+      double hinv[TC];
+      int jj[TC];
 #pragma unroll
-      for (int i = 0; i < ND; i++) out[(int64_t)i * (TD * DIM)] = (R[i] - sRb[i + j2 * ND]) * hinv;
+      for (int y = 0; y < TC; y++) {
+        const int col = col0 + y;
+        const int m = (col < TD * DIM) ? col / DIM : 0;
+        jj[y] = col % DIM;
+        const double orig = sue[(m / ND) * NDP + m % ND];
+        const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
+        hinv[y] = 1. / h;
+      }
+      double* out = g.KeT + e * (int64_t)(ND * KP) + col0;
+#pragma unroll
+      for (int x = 0; x < TI; x++) {
+        const int i = i0 + x;
+        if (i < ND) {
+          double v[TC];
+#pragma unroll
+          for (int y = 0; y < TC; y++) v[y] = (R[x][y] - sRb[i + jj[y] * ND]) * hinv[y];
+          if (col0 + TC <= KP) {
+            double2* o2 = reinterpret_cast<double2*>(out + (int64_t)i * KP);
+#pragma unroll
+            for (int y = 0; y < TC / 2; y++) o2[y] = make_double2(v[2 * y], v[2 * y + 1]);
+          }
+        }
+      }
     }
     __syncthreads();
   }
@@ -360,7 +420,7 @@ __global__ void residual_gather_kernel(int dim, int nd, int64_t Nn, const int64_
 }
 
 // KeT holds, per element, [row node a][column dof m][row component ci]: the dim x tdof block of one node
-// is one contiguous run of dim*tdof doubles.
+// is one contiguous run of dim*tdof doubles (pitch kp = dim*tdof rounded up to 4).
 // One CTA per node I (block row of dim rows). Thread (ci, cj, b) adds K_e(a + ci*nd, b + cj*nd) into
 // the block-row accumulator slot rank[e][a][b]; elements visited in ascending id with a barrier in
 // between. Finally A[row, col] += grad_factor * acc  (nonlinear_base.hpp:141-144).
@@ -373,6 +433,7 @@ __global__ void csr_gather_kernel(int nd, int64_t Nn, const int64_t* __restrict_
   constexpr int DD = DIM * DIM;
   extern __shared__ double acc[];  // nnbr(I) x DIM(ci) x DIM(cj)
   const int tdof = DIM * nd;
+  const int kp = (tdof * DIM + 3) / 4 * 4;
   const int t = threadIdx.x;
   for (int64_t I = blockIdx.x; I < Nn; I += gridDim.x) {
     const int nn = nnbr[I];
@@ -385,7 +446,7 @@ __global__ void csr_gather_kernel(int nd, int64_t Nn, const int64_t* __restrict_
       const int a = n2e_loc[p];
       if (t < DIM * tdof) {
         const int s = rank[(e * nd + a) * nd + b];
-        acc[(s * DIM + ci) * DIM + cj] += KeT[((e * nd + a) * (int64_t)tdof + col) * DIM + ci];
+        acc[(s * DIM + ci) * DIM + cj] += KeT[(e * nd + a) * (int64_t)kp + t];
       }
       __syncthreads();
     }
@@ -502,7 +563,8 @@ int launch_residual(mb2_ctx* c) {
 int launch_residual_and_grad(mb2_ctx* c, double gf) {
   c->last_launches = 0;
   if (!c->d_KeT) {
-    const size_t bytes = sizeof(double) * (size_t)c->NE * c->tdof * c->tdof;
+    const size_t kp = (size_t)(c->tdof * c->dim + 3) / 4 * 4;
+    const size_t bytes = sizeof(double) * (size_t)c->NE * c->nd * kp;
     MB2_CUDA(cudaMalloc(&c->d_KeT, bytes));
   }
   MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
