@@ -17,6 +17,7 @@
 #ifndef MIMI_B200_H
 #define MIMI_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -120,15 +121,24 @@ int mb2_assemble_residual_and_grad_device(mb2_ctx* ctx, double grad_factor);
 /* Raw device pointers of the resident arrays (u: NV, r: NV, A: nnz doubles). */
 int mb2_device_pointers(mb2_ctx* ctx, void** u, void** r, void** A);
 
+/* Pins a caller-owned host array (e.g. the mfem::SparseMatrix value array) so that the host-buffer entries
+ * can stream it chunk by chunk with the copy engines; without it the copies fall back to staged pageable copies. */
+int mb2_host_register(mb2_ctx* ctx, void* ptr, size_t bytes);
+int mb2_host_unregister(mb2_ctx* ctx, void* ptr);
+/* Chunk pipeline of the residual+tangent assembly: elements per chunk and number of chunks. */
+int mb2_plan_info(mb2_ctx* ctx, int64_t* chunk_elems, int* nchunks);
+
 /* Milliseconds of the kernels of the last assemble call, from CUDA events on ctx's stream:
- * out[0] = element kernel (FD tangent or residual), out[1] = CSR/residual gather-scatter, out[2] = total. */
+ * out[0] = element kernels (summed over chunks), out[1] = CSR/residual gather-scatter (summed), out[2] = start to
+ * end of the call; the gather of chunk c overlaps the element kernel of chunk c+1, so [0]+[1] may exceed [2]. */
 int mb2_last_timing_ms(mb2_ctx* ctx, float* out3);
 /* Kernel launches issued by the last assemble call. */
 int mb2_last_launch_count(mb2_ctx* ctx);
 /* Synchronise ctx's stream. */
 int mb2_sync(mb2_ctx* ctx);
 
-/* Tuning / A-B switches (never change results): "elem_variant" 0 = default kernels, 1 = one-thread-per-dof FD kernel. */
+/* Tuning / A-B switches (never change results): "elem_variant" 0 = default kernels, 1 = one-thread-per-dof FD
+ * kernel; "chunk_elems" = elements per pipeline chunk (0 = derive from "chunk_mb", the K_e buffer budget in MiB). */
 int mb2_set_option(mb2_ctx* ctx, const char* name, int value);
 
 /* FP64 pipe micro-benchmark used for the roofline denominator: runs `iters` dependent-chain-free

@@ -22,7 +22,7 @@ SYMBOLS = [
     "mb2_get_pattern_i32", "mb2_get_pattern_i64", "mb2_get_A_ids_i32", "mb2_set_material",
     "mb2_add_domain_residual", "mb2_add_domain_residual_and_grad", "mb2_set_u", "mb2_set_r", "mb2_set_A",
     "mb2_get_r", "mb2_get_A", "mb2_assemble_residual_device", "mb2_assemble_residual_and_grad_device",
-    "mb2_device_pointers", "mb2_last_timing_ms", "mb2_last_launch_count", "mb2_sync", "mb2_measure_fp64_peak", "mb2_set_option",
+    "mb2_device_pointers", "mb2_last_timing_ms", "mb2_last_launch_count", "mb2_sync", "mb2_measure_fp64_peak", "mb2_set_option", "mb2_host_register", "mb2_host_unregister", "mb2_plan_info",
 ]
 
 
@@ -176,6 +176,17 @@ class Context:
 
     def set_option(self, name, value):
         self._ck(self.lib.mb2_set_option(self.h, name.encode(), C.c_int(value)))
+
+    def plan_info(self):
+        ec, n = C.c_int64(), C.c_int()
+        self._ck(self.lib.mb2_plan_info(self.h, C.byref(ec), C.byref(n)))
+        return ec.value, n.value
+
+    def host_register(self, arr):
+        self._ck(self.lib.mb2_host_register(self.h, _dp(arr), C.c_size_t(arr.nbytes)))
+
+    def host_unregister(self, arr):
+        self._ck(self.lib.mb2_host_unregister(self.h, _dp(arr)))
 
     def sync(self):
         self._ck(self.lib.mb2_sync(self.h))

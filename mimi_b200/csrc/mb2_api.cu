@@ -25,7 +25,8 @@ static void free_problem(mb2_ctx* c) {
   dfree(c->d_vdofs); dfree(c->d_enodes); dfree(c->d_dNdX); dfree(c->d_wdetJ); dfree(c->d_N); dfree(c->d_xref); dfree(c->d_nodew);
   dfree(c->d_n2e_ptr); dfree(c->d_n2e_elem); dfree(c->d_n2e_loc); dfree(c->d_nnbr); dfree(c->d_nodeptr);
   dfree(c->d_nbr); dfree(c->d_rank); dfree(c->d_I); dfree(c->d_J);
-  dfree(c->d_u); dfree(c->d_r); dfree(c->d_A); dfree(c->d_Re); dfree(c->d_KeT);
+  dfree(c->d_u); dfree(c->d_r); dfree(c->d_A); dfree(c->d_Re);
+  mb2::free_plan(c);
   c->have_pattern = false;
   c->nnz = 0;
 }
@@ -277,7 +278,7 @@ int mb2_assemble_residual_and_grad_device(mb2_ctx* c, double gf) {
   int rc = ready(c, true);
   if (rc) return rc;
   MB2_CUDA(cudaSetDevice(c->device));
-  return mb2::launch_residual_and_grad(c, gf);
+  return mb2::launch_residual_and_grad(c, gf, nullptr, nullptr);
 }
 
 int mb2_add_domain_residual(mb2_ctx* c, const double* u, double* r) {
@@ -292,23 +293,38 @@ int mb2_add_domain_residual(mb2_ctx* c, const double* u, double* r) {
 int mb2_add_domain_residual_and_grad(mb2_ctx* c, const double* u, double gf, double* r, double* A) {
   CHECK_CTX(c);
   REQUIRE(u && r && A, "null vector");
-  int rc;
+  int rc = ready(c, true);
+  if (rc) return rc;
+  MB2_CUDA(cudaSetDevice(c->device));
   if ((rc = mb2_set_u(c, u))) return rc;
   if ((rc = mb2_set_r(c, r))) return rc;
-  if ((rc = mb2_set_A(c, A))) return rc;
-  if ((rc = mb2_assemble_residual_and_grad_device(c, gf))) return rc;
-  if ((rc = mb2_get_r(c, r))) return rc;
-  return mb2_get_A(c, A);
+  // A travels chunk by chunk inside the pipeline: rows are uploaded just before the chunk that completes them
+  // is gathered and downloaded right after (copy engines, overlapped with the element kernels).
+  if ((rc = mb2::launch_residual_and_grad(c, gf, A, A))) return rc;
+  return mb2_get_r(c, r);
+}
+
+int mb2_host_register(mb2_ctx* c, void* ptr, size_t bytes) {
+  CHECK_CTX(c);
+  REQUIRE(ptr && bytes, "null");
+  MB2_CUDA(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+  return MB2_OK;
+}
+int mb2_host_unregister(mb2_ctx* c, void* ptr) {
+  CHECK_CTX(c);
+  MB2_CUDA(cudaHostUnregister(ptr));
+  return MB2_OK;
 }
 
 int mb2_last_timing_ms(mb2_ctx* c, float* out3) {
   CHECK_CTX(c);
   REQUIRE(out3, "null");
-  MB2_CUDA(cudaEventSynchronize(c->ev[2]));
-  MB2_CUDA(cudaEventElapsedTime(&out3[0], c->ev[0], c->ev[1]));
-  MB2_CUDA(cudaEventElapsedTime(&out3[1], c->ev[1], c->ev[2]));
-  MB2_CUDA(cudaEventElapsedTime(&out3[2], c->ev[0], c->ev[2]));
-  return MB2_OK;
+  return mb2::collect_timing(c, out3);
+}
+int mb2_plan_info(mb2_ctx* c, int64_t* chunk_elems, int* nchunks) {
+  CHECK_CTX(c);
+  REQUIRE(c->have_pattern, "call mb2_build_pattern first");
+  return mb2::plan_info(c, chunk_elems, nchunks);
 }
 int mb2_last_launch_count(mb2_ctx* c) { return c ? c->last_launches : 0; }
 int mb2_sync(mb2_ctx* c) {
@@ -327,6 +343,8 @@ int mb2_set_option(mb2_ctx* c, const char* name, int value) {
   CHECK_CTX(c);
   REQUIRE(name, "null option name");
   if (!std::strcmp(name, "elem_variant")) { c->elem_variant = value; return MB2_OK; }
+  if (!std::strcmp(name, "chunk_elems")) { c->chunk_elems = value; mb2::free_plan(c); return MB2_OK; }
+  if (!std::strcmp(name, "chunk_mb")) { c->chunk_mb = value > 0 ? value : 2048; mb2::free_plan(c); return MB2_OK; }
   c->err = std::string("unknown option ") + name;
   return MB2_ERR_ARG;
 }

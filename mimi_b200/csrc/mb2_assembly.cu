@@ -8,6 +8,7 @@
 // Compiled -fmad=false: every value is produced by the reference's operation sequence, so results
 // are bit-identical to the reference at nthreads=1.
 #include <cstdio>
+#include <vector>
 
 #include "mb2_ctx.h"
 #include "mb2_math.cuh"
@@ -15,7 +16,7 @@
 namespace mb2 {
 
 struct ElemArgs {
-  int64_t NE;
+  int64_t e0, e1;  // element range of this launch; K_e is stored relative to e0
   const int32_t* __restrict__ vdofs;
   const double* __restrict__ dNdX;
   const double* __restrict__ wdetJ;
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel
   double* sRb = smem + Cfg::OFF_RB;
   const int t = threadIdx.x;
 
-  for (int64_t e = blockIdx.x; e < g.NE; e += gridDim.x) {
+  for (int64_t e = g.e0 + blockIdx.x; e < g.e1; e += gridDim.x) {
     // ---- stage the element: gathered dofs (Vector::GetSubVector), weights, dN_dX tables
     if (t < TD) sue[t] = g.u[g.vdofs[e * TD + t]];
     if (t < NQ) swd[t] = g.wdetJ[e * NQ + t];
@@ -155,7 +156,7 @@ __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel
         }
         // KeT layout: [e][row node i][perturbed dof m][row component j]  <->  K_e(i + j*ND, m)
         constexpr int KP = (TD * DIM + 3) / 4 * 4;  // pitch of one node-row block (see Elem2Cfg::KP)
-        double* out = g.KeT + e * (int64_t)(ND * KP) + t * DIM;
+        double* out = g.KeT + (e - g.e0) * (int64_t)(ND * KP) + t * DIM;
 #pragma unroll
         for (int j = 0; j < TD; j++) out[(int64_t)(j % ND) * KP + j / ND] = (R[j] - sRb[j]) * hinv;
       }
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
   if (t < DIM)
     for (int i = ND; i < NDP; i++) sue[t * NDP + i] = 0.0;
 
-  for (int64_t e = blockIdx.x; e < g.NE; e += gridDim.x) {
+  for (int64_t e = g.e0 + blockIdx.x; e < g.e1; e += gridDim.x) {
     // ---- stage: gathered dofs (Vector::GetSubVector), weights, dN_dX rows padded to NDP
     if (t < TD) sue[(t / ND) * NDP + t % ND] = g.u[g.vdofs[e * TD + t]];
     if (t < NQ) swd[t] = g.wdetJ[e * NQ + t];
@@ -377,7 +378,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
         const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
         hinv[y] = 1. / h;
       }
-      double* out = g.KeT + e * (int64_t)(ND * KP) + col0;
+      double* out = g.KeT + (e - g.e0) * (int64_t)(ND * KP) + col0;
 #pragma unroll
       for (int x = 0; x < TI; x++) {
         const int i = i0 + x;
@@ -419,43 +420,59 @@ __global__ void residual_gather_kernel(int dim, int nd, int64_t Nn, const int64_
   r[v] += acc;
 }
 
-// KeT holds, per element, [row node a][column dof m][row component ci]: the dim x tdof block of one node
-// is one contiguous run of dim*tdof doubles (pitch kp = dim*tdof rounded up to 4).
-// One CTA per node I (block row of dim rows). Thread (ci, cj, b) adds K_e(a + ci*nd, b + cj*nd) into
-// the block-row accumulator slot rank[e][a][b]; elements visited in ascending id with a barrier in
-// between. Finally A[row, col] += grad_factor * acc  (nonlinear_base.hpp:141-144).
+// KeT holds, per element of the current chunk, [row node a][column dof m][row component ci]: the dim x tdof
+// block of one node is one contiguous run of dim*tdof doubles (pitch kp = dim*tdof rounded up to 4).
+// One CTA per node I of the chunk's node list (block row of dim rows). Thread (ci, cj, b) adds
+// K_e(a + ci*nd, b + cj*nd) into the block-row accumulator slot rank[e][a][b]; the chunk's elements are visited
+// in ascending id with a barrier in between. Elements are processed in chunks [e0, e1) of ascending ids, so a
+// node whose elements straddle chunks carries its partial sum in A_tl (the reference's thread-local matrix,
+// nonlinear_solid.cpp:126-143) and the sum is still ((0 + K_e1) + K_e2) + ... in ascending element order.
+// When the node's last element lies in this chunk: A[row, col] += grad_factor * acc  (nonlinear_base.hpp:141-144).
 template <int DIM>
-__global__ void csr_gather_kernel(int nd, int64_t Nn, const int64_t* __restrict__ n2e_ptr,
-                                  const int32_t* __restrict__ n2e_elem, const uint8_t* __restrict__ n2e_loc,
-                                  const uint16_t* __restrict__ rank, const int32_t* __restrict__ nnbr,
-                                  const int64_t* __restrict__ nodeptr, const double* __restrict__ KeT,
-                                  double grad_factor, double* __restrict__ A) {
+__global__ void csr_gather_kernel(int nd, const int32_t* __restrict__ nodes, int64_t n_nodes, int64_t e0, int64_t e1,
+                                  const int64_t* __restrict__ n2e_ptr, const int32_t* __restrict__ n2e_elem,
+                                  const uint8_t* __restrict__ n2e_loc, const uint16_t* __restrict__ rank,
+                                  const int32_t* __restrict__ nnbr, const int64_t* __restrict__ nodeptr,
+                                  const double* __restrict__ KeT, double grad_factor, double* __restrict__ A,
+                                  double* __restrict__ A_tl) {
   constexpr int DD = DIM * DIM;
   extern __shared__ double acc[];  // nnbr(I) x DIM(ci) x DIM(cj)
   const int tdof = DIM * nd;
   const int kp = (tdof * DIM + 3) / 4 * 4;
   const int t = threadIdx.x;
-  for (int64_t I = blockIdx.x; I < Nn; I += gridDim.x) {
+  const int col = t / DIM, ci = t % DIM;  // col = b + cj*nd; consecutive threads read consecutive doubles
+  const int cj = col / nd, b = col % nd;
+  for (int64_t li = blockIdx.x; li < n_nodes; li += gridDim.x) {
+    const int64_t I = nodes ? nodes[li] : li;
     const int nn = nnbr[I];
-    for (int i = t; i < nn * DD; i += blockDim.x) acc[i] = 0.0;
-    __syncthreads();
-    const int col = t / DIM, ci = t % DIM;  // col = b + cj*nd; consecutive threads read consecutive doubles
-    const int cj = col / nd, b = col % nd;
-    for (int64_t p = n2e_ptr[I]; p < n2e_ptr[I + 1]; p++) {
-      const int64_t e = n2e_elem[p];
-      const int a = n2e_loc[p];
-      if (t < DIM * tdof) {
-        const int s = rank[(e * nd + a) * nd + b];
-        acc[(s * DIM + ci) * DIM + cj] += KeT[(e * nd + a) * (int64_t)kp + t];
-      }
-      __syncthreads();
-    }
-    // row dim*I + ci starts at DD*nodeptr[I] + ci*DIM*nn; entry (s, cj) at + DIM*s + cj
+    const int64_t pb = n2e_ptr[I], pe = n2e_ptr[I + 1];
+    const bool has_prev = n2e_elem[pb] < e0;       // partial sum from earlier chunks
+    const bool is_final = n2e_elem[pe - 1] < e1;   // no element of a later chunk touches this node
+    // row dim*I + rci starts at DD*nodeptr[I] + rci*DIM*nn; entry (s, rcj) at + DIM*s + rcj
     const int64_t base = (int64_t)DD * nodeptr[I];
     for (int i = t; i < nn * DD; i += blockDim.x) {
       const int rci = i / (nn * DIM), rem = i % (nn * DIM);
       const int s = rem / DIM, rcj = rem % DIM;
-      A[base + i] += grad_factor * acc[(s * DIM + rci) * DIM + rcj];
+      acc[(s * DIM + rci) * DIM + rcj] = has_prev ? A_tl[base + i] : 0.0;
+    }
+    __syncthreads();
+    for (int64_t p = pb; p < pe; p++) {
+      const int64_t e = n2e_elem[p];
+      if (e < e0) continue;
+      if (e >= e1) break;
+      const int a = n2e_loc[p];
+      if (t < DIM * tdof) {
+        const int s = rank[(e * nd + a) * nd + b];
+        acc[(s * DIM + ci) * DIM + cj] += KeT[((e - e0) * nd + a) * (int64_t)kp + t];
+      }
+      __syncthreads();
+    }
+    for (int i = t; i < nn * DD; i += blockDim.x) {
+      const int rci = i / (nn * DIM), rem = i % (nn * DIM);
+      const int s = rem / DIM, rcj = rem % DIM;
+      const double v = acc[(s * DIM + rci) * DIM + rcj];
+      if (is_final) A[base + i] += grad_factor * v;
+      else A_tl[base + i] = v;
     }
     __syncthreads();
   }
@@ -465,7 +482,7 @@ __global__ void csr_gather_kernel(int nd, int64_t Nn, const int64_t* __restrict_
 // launchers
 // ---------------------------------------------------------------------------------------------
 template <int DIM, int ND, int NQ, int MAT, bool GRAD, int MINB>
-static int launch_element(mb2_ctx* c, const ElemArgs& a) {
+static int launch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   using Cfg = ElemCfg<DIM, ND, NQ>;
   auto kern = element_kernel<DIM, ND, NQ, MAT, GRAD, MINB>;
   MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
@@ -474,75 +491,77 @@ static int launch_element(mb2_ctx* c, const ElemArgs& a) {
   if (per_sm < 1) per_sm = 1;
   // persistent grid: a whole number of resident CTAs per SM
   int64_t grid = (int64_t)c->sm_count * per_sm;
-  if (grid > a.NE) grid = a.NE;
-  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, c->stream>>>(a);
+  if (grid > a.e1 - a.e0) grid = a.e1 - a.e0;
+  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, st>>>(a);
   MB2_CUDA(cudaGetLastError());
   return MB2_OK;
 }
 
 template <int DIM, int ND, int NQ, int MAT>
-static int launch_element_fd(mb2_ctx* c, const ElemArgs& a) {
+static int launch_element_fd(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   using Cfg = Elem2Cfg<DIM, ND, NQ>;
   auto kern = element_fd_kernel<DIM, ND, NQ, MAT>;
   MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
   int per_sm = 0;
   MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::NT, Cfg::SMEM_BYTES));
   if (per_sm < 1) per_sm = 1;
-  int64_t grid = (int64_t)c->sm_count * per_sm;  // persistent: a whole number of resident CTAs per SM
-  if (grid > a.NE) grid = a.NE;
-  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, c->stream>>>(a);
+  // one CTA per element: as elements retire, the block scheduler hands their SM slots to the CTAs of the
+  // higher-priority gather stream and to the next chunk's elements (no wave tail between chunks)
+  (void)per_sm;
+  const int64_t grid = a.e1 - a.e0;
+  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, st>>>(a);
   MB2_CUDA(cudaGetLastError());
   return MB2_OK;
 }
 
 template <int DIM, int ND, int NQ, bool GRAD, int MINB>
-static int launch_element_mat(mb2_ctx* c, const ElemArgs& a) {
+static int launch_element_mat(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   switch (c->mat_kind) {
-    case MAT_NEOHOOKEAN: return launch_element<DIM, ND, NQ, MAT_NEOHOOKEAN, GRAD, MINB>(c, a);
-    case MAT_STVK: return launch_element<DIM, ND, NQ, MAT_STVK, GRAD, MINB>(c, a);
+    case MAT_NEOHOOKEAN: return launch_element<DIM, ND, NQ, MAT_NEOHOOKEAN, GRAD, MINB>(c, a, st);
+    case MAT_STVK: return launch_element<DIM, ND, NQ, MAT_STVK, GRAD, MINB>(c, a, st);
   }
   c->err = "material not set or unsupported";
   return MB2_ERR_UNSUPPORTED;
 }
 
 template <bool GRAD>
-static int dispatch_element(mb2_ctx* c, const ElemArgs& a) {
+static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   const int dim = c->dim, nd = c->nd, nq = c->nq;
   if (GRAD && dim == 3 && nd == 27 && nq == 64 && c->elem_variant != 1) {
     switch (c->mat_kind) {
-      case MAT_NEOHOOKEAN: return launch_element_fd<3, 27, 64, MAT_NEOHOOKEAN>(c, a);
-      case MAT_STVK: return launch_element_fd<3, 27, 64, MAT_STVK>(c, a);
+      case MAT_NEOHOOKEAN: return launch_element_fd<3, 27, 64, MAT_NEOHOOKEAN>(c, a, st);
+      case MAT_STVK: return launch_element_fd<3, 27, 64, MAT_STVK>(c, a, st);
     }
   }
-  if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a);
-  if (dim == 3 && nd == 8 && nq == 27) return launch_element_mat<3, 8, 27, GRAD, 4>(c, a);
-  if (dim == 2 && nd == 16 && nq == 25) return launch_element_mat<2, 16, 25, GRAD, 4>(c, a);
-  if (dim == 2 && nd == 9 && nq == 16) return launch_element_mat<2, 9, 16, GRAD, 4>(c, a);
-  if (dim == 2 && nd == 4 && nq == 9) return launch_element_mat<2, 4, 9, GRAD, 4>(c, a);
+  if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a, st);
+  if (dim == 3 && nd == 8 && nq == 27) return launch_element_mat<3, 8, 27, GRAD, 4>(c, a, st);
+  if (dim == 2 && nd == 16 && nq == 25) return launch_element_mat<2, 16, 25, GRAD, 4>(c, a, st);
+  if (dim == 2 && nd == 9 && nq == 16) return launch_element_mat<2, 9, 16, GRAD, 4>(c, a, st);
+  if (dim == 2 && nd == 4 && nq == 9) return launch_element_mat<2, 4, 9, GRAD, 4>(c, a, st);
   c->err = "no kernel instantiated for (dim, nd, nq) = (" + std::to_string(dim) + ", " + std::to_string(nd) + ", " +
            std::to_string(nq) + ")";
   return MB2_ERR_UNSUPPORTED;
 }
 
-static ElemArgs make_args(mb2_ctx* c) {
+static ElemArgs make_args(mb2_ctx* c, int64_t e0, int64_t e1, double* KeT) {
   ElemArgs a;
-  a.NE = c->NE;
+  a.e0 = e0;
+  a.e1 = e1;
   a.vdofs = c->d_vdofs;
   a.dNdX = c->d_dNdX;
   a.wdetJ = c->d_wdetJ;
   a.u = c->d_u;
   a.Re = c->d_Re;
-  a.KeT = c->d_KeT;
+  a.KeT = KeT;
   a.lambda = c->lambda;
   a.mu = c->mu;
   return a;
 }
 
-static int launch_residual_gather(mb2_ctx* c) {
+static int launch_residual_gather(mb2_ctx* c, cudaStream_t st) {
   const int64_t n = c->Nn * c->dim;
-  residual_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->dim, c->nd, c->Nn, c->d_n2e_ptr,
-                                                                              c->d_n2e_elem, c->d_n2e_loc, c->d_Re,
-                                                                              c->d_r);
+  residual_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(c->dim, c->nd, c->Nn, c->d_n2e_ptr, c->d_n2e_elem,
+                                                                      c->d_n2e_loc, c->d_Re, c->d_r);
   MB2_CUDA(cudaGetLastError());
   return MB2_OK;
 }
@@ -550,52 +569,249 @@ static int launch_residual_gather(mb2_ctx* c) {
 int launch_residual(mb2_ctx* c) {
   c->last_launches = 0;
   MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
-  int rc = dispatch_element<false>(c, make_args(c));
+  int rc = dispatch_element<false>(c, make_args(c, 0, c->NE, nullptr), c->stream);
   if (rc) return rc;
   MB2_CUDA(cudaEventRecord(c->ev[1], c->stream));
-  rc = launch_residual_gather(c);
+  rc = launch_residual_gather(c, c->stream);
   if (rc) return rc;
   MB2_CUDA(cudaEventRecord(c->ev[2], c->stream));
   c->last_launches = 2;
+  c->last_ms_valid = false;
   return MB2_OK;
 }
 
-int launch_residual_and_grad(mb2_ctx* c, double gf) {
-  c->last_launches = 0;
-  if (!c->d_KeT) {
-    const size_t kp = (size_t)(c->tdof * c->dim + 3) / 4 * 4;
-    const size_t bytes = sizeof(double) * (size_t)c->NE * c->nd * kp;
-    MB2_CUDA(cudaMalloc(&c->d_KeT, bytes));
+// ---------------------------------------------------------------------------------------------
+// Chunked assembly pipeline. Elements are processed in chunks of ascending ids: the FD kernel of chunk
+// c+1 runs while chunk c is gathered into the CSR values (second stream, higher priority) and -- in the
+// host-buffer entry -- while the CSR rows completed by chunk c travel to the host and the rows needed by
+// chunk c+1 travel to the device (copy engines). Only two chunks of K_e are ever resident.
+// ---------------------------------------------------------------------------------------------
+struct Run {
+  int64_t off, n;  // range of CSR values
+};
+struct Plan {
+  int64_t EC = 0;  // elements per chunk
+  int nch = 0;
+  std::vector<int64_t> node_ptr;        // nch+1: offsets into d_nodes
+  int32_t* d_nodes = nullptr;           // nodes touched by each chunk (ascending ids per chunk)
+  std::vector<std::vector<Run>> runs;   // per chunk: CSR value ranges of the nodes FINALISED by that chunk
+  double* d_KeT[2] = {nullptr, nullptr};
+  double* d_Atl = nullptr;              // partial sums of nodes that straddle chunks (same layout as A)
+  cudaStream_t s_el = nullptr, s_ga = nullptr, s_h2d = nullptr, s_d2h = nullptr;
+  std::vector<cudaEvent_t> el0, el1, ga0, ga1, h2d;
+  cudaEvent_t start = nullptr, done_ga = nullptr, done_d2h = nullptr;
+  int max_nnbr = 0;
+};
+
+void free_plan(mb2_ctx* c) {
+  Plan* P = static_cast<Plan*>(c->plan);
+  if (!P) return;
+  cudaFree(P->d_nodes);
+  cudaFree(P->d_KeT[0]);
+  cudaFree(P->d_KeT[1]);
+  cudaFree(P->d_Atl);
+  for (auto* v : {&P->el0, &P->el1, &P->ga0, &P->ga1, &P->h2d})
+    for (auto e : *v) cudaEventDestroy(e);
+  for (auto e : {P->start, P->done_ga, P->done_d2h})
+    if (e) cudaEventDestroy(e);
+  for (auto s : {P->s_el, P->s_ga, P->s_h2d, P->s_d2h})
+    if (s) cudaStreamDestroy(s);
+  delete P;
+  c->plan = nullptr;
+}
+
+__global__ void k_first_last(int64_t Nn, const int64_t* __restrict__ ptr, const int32_t* __restrict__ n2e_elem,
+                             int32_t* __restrict__ first, int32_t* __restrict__ last) {
+  const int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (I >= Nn) return;
+  const int64_t b = ptr[I], e = ptr[I + 1];
+  first[I] = (e > b) ? n2e_elem[b] : -1;
+  last[I] = (e > b) ? n2e_elem[e - 1] : -1;
+}
+
+static int build_plan(mb2_ctx* c) {
+  free_plan(c);
+  Plan* P = new Plan();
+  c->plan = P;
+  const int64_t NE = c->NE, Nn = c->Nn;
+  const size_t kp = (size_t)(c->tdof * c->dim + 3) / 4 * 4;
+  const size_t bytes_el = sizeof(double) * c->nd * kp;
+  // chunk size: a whole number of persistent-grid waves, K_e buffer of at most ~chunk_mb MiB (x2 buffers)
+  const int64_t wave = (int64_t)c->sm_count * 2;
+  int64_t EC = c->chunk_elems > 0 ? c->chunk_elems : (int64_t)((size_t)c->chunk_mb * (1u << 20) / bytes_el);
+  if (c->chunk_elems <= 0) {
+    EC = EC / wave * wave;
+    if (EC < wave) EC = wave;
   }
-  MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
-  int rc = dispatch_element<true>(c, make_args(c));
-  if (rc) return rc;
-  MB2_CUDA(cudaEventRecord(c->ev[1], c->stream));
-  rc = launch_residual_gather(c);
-  if (rc) return rc;
+  if (EC > NE) EC = NE;
+  P->EC = EC;
+  P->nch = (int)((NE + EC - 1) / EC);
+  const int nch = P->nch;
+
+  // first / last element of every node, neighbour counts and block-row offsets -> host
+  std::vector<int32_t> first((size_t)Nn), last((size_t)Nn), nnbr((size_t)Nn);
+  std::vector<int64_t> nodeptr((size_t)Nn + 1);
   {
-    const int threads = (c->dim * c->tdof + 31) / 32 * 32;
-    const int dd = c->dim * c->dim;
-    const int maxnbr = 1;  // placeholder, replaced below
-    (void)maxnbr;
-    int mx = 1;
-    for (int d = 0; d < c->dim; d++) mx *= 2 * 3 + 1;  // (2p+1)^dim for p <= 3
-    const size_t smem = sizeof(double) * (size_t)mx * dd;
-    int64_t grid = c->Nn < (int64_t)c->sm_count * 64 ? c->Nn : (int64_t)c->sm_count * 64;
-    if (c->dim == 3) {
-      MB2_CUDA(cudaFuncSetAttribute(csr_gather_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      csr_gather_kernel<3><<<(unsigned)grid, threads, smem, c->stream>>>(c->nd, c->Nn, c->d_n2e_ptr, c->d_n2e_elem,
-                                                                         c->d_n2e_loc, c->d_rank, c->d_nnbr,
-                                                                         c->d_nodeptr, c->d_KeT, gf, c->d_A);
-    } else {
-      csr_gather_kernel<2><<<(unsigned)grid, threads, smem, c->stream>>>(c->nd, c->Nn, c->d_n2e_ptr, c->d_n2e_elem,
-                                                                         c->d_n2e_loc, c->d_rank, c->d_nnbr,
-                                                                         c->d_nodeptr, c->d_KeT, gf, c->d_A);
-    }
+    int32_t *d_f = nullptr, *d_l = nullptr;
+    MB2_CUDA(cudaMalloc(&d_f, sizeof(int32_t) * Nn));
+    MB2_CUDA(cudaMalloc(&d_l, sizeof(int32_t) * Nn));
+    k_first_last<<<(unsigned)((Nn + 255) / 256), 256, 0, c->stream>>>(Nn, c->d_n2e_ptr, c->d_n2e_elem, d_f, d_l);
     MB2_CUDA(cudaGetLastError());
+    MB2_CUDA(cudaMemcpyAsync(first.data(), d_f, sizeof(int32_t) * Nn, cudaMemcpyDeviceToHost, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(last.data(), d_l, sizeof(int32_t) * Nn, cudaMemcpyDeviceToHost, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(nnbr.data(), c->d_nnbr, sizeof(int32_t) * Nn, cudaMemcpyDeviceToHost, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(nodeptr.data(), c->d_nodeptr, sizeof(int64_t) * (Nn + 1), cudaMemcpyDeviceToHost, c->stream));
+    MB2_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(d_f);
+    cudaFree(d_l);
+  }
+  const int64_t dd = (int64_t)c->dim * c->dim;
+  // per-chunk node lists (a node appears in every chunk between its first and last element's chunk)
+  P->node_ptr.assign(nch + 1, 0);
+  P->max_nnbr = 1;
+  for (int64_t I = 0; I < Nn; I++) {
+    if (first[I] < 0) continue;
+    if (nnbr[I] > P->max_nnbr) P->max_nnbr = nnbr[I];
+    for (int64_t ch = first[I] / EC; ch <= last[I] / EC; ch++) P->node_ptr[ch + 1]++;
+  }
+  for (int ch = 0; ch < nch; ch++) P->node_ptr[ch + 1] += P->node_ptr[ch];
+  std::vector<int32_t> nodes((size_t)P->node_ptr[nch]);
+  {
+    std::vector<int64_t> fill(P->node_ptr.begin(), P->node_ptr.end() - 1);
+    for (int64_t I = 0; I < Nn; I++) {
+      if (first[I] < 0) continue;
+      for (int64_t ch = first[I] / EC; ch <= last[I] / EC; ch++) nodes[(size_t)fill[ch]++] = (int32_t)I;
+    }
+  }
+  // value ranges finalised per chunk: merge nodes with consecutive ids (their block rows are contiguous)
+  P->runs.assign(nch, {});
+  for (int64_t I = 0; I < Nn; I++) {
+    if (first[I] < 0) continue;
+    auto& R = P->runs[(size_t)(last[I] / EC)];
+    const int64_t off = dd * nodeptr[I], n = dd * nnbr[I];
+    if (!R.empty() && R.back().off + R.back().n == off) R.back().n += n;
+    else R.push_back({off, n});
+  }
+  MB2_CUDA(cudaMalloc(&P->d_nodes, sizeof(int32_t) * (nodes.size() ? nodes.size() : 1)));
+  MB2_CUDA(cudaMemcpy(P->d_nodes, nodes.data(), sizeof(int32_t) * nodes.size(), cudaMemcpyHostToDevice));
+  const int nbuf = nch > 1 ? 2 : 1;
+  for (int b = 0; b < nbuf; b++) MB2_CUDA(cudaMalloc(&P->d_KeT[b], bytes_el * (size_t)EC));
+  if (nch > 1) MB2_CUDA(cudaMalloc(&P->d_Atl, sizeof(double) * (size_t)c->nnz));
+  int lo = 0, hi = 0;
+  MB2_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));  // hi = numerically smallest = highest priority
+  MB2_CUDA(cudaStreamCreateWithPriority(&P->s_el, cudaStreamNonBlocking, lo));
+  MB2_CUDA(cudaStreamCreateWithPriority(&P->s_ga, cudaStreamNonBlocking, hi));
+  MB2_CUDA(cudaStreamCreateWithFlags(&P->s_h2d, cudaStreamNonBlocking));
+  MB2_CUDA(cudaStreamCreateWithFlags(&P->s_d2h, cudaStreamNonBlocking));
+  for (auto* v : {&P->el0, &P->el1, &P->ga0, &P->ga1, &P->h2d}) {
+    v->resize(nch);
+    for (auto& e : *v) MB2_CUDA(cudaEventCreate(&e));
+  }
+  MB2_CUDA(cudaEventCreate(&P->start));
+  MB2_CUDA(cudaEventCreate(&P->done_ga));
+  MB2_CUDA(cudaEventCreate(&P->done_d2h));
+  return MB2_OK;
+}
+
+template <int DIM>
+static int launch_gather(mb2_ctx* c, Plan* P, int ch, int64_t e0, int64_t e1, double gf, cudaStream_t st) {
+  const int threads = (c->dim * c->tdof + 31) / 32 * 32;
+  const size_t smem = sizeof(double) * (size_t)P->max_nnbr * DIM * DIM;
+  const int64_t n_nodes = P->node_ptr[ch + 1] - P->node_ptr[ch];
+  if (n_nodes == 0) return MB2_OK;
+  auto kern = csr_gather_kernel<DIM>;
+  if (smem > 48 * 1024) MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t cap = (int64_t)c->sm_count * 256;
+  const unsigned grid = (unsigned)(n_nodes < cap ? n_nodes : cap);
+  kern<<<grid, threads, smem, st>>>(c->nd, P->d_nodes + P->node_ptr[ch], n_nodes, e0, e1, c->d_n2e_ptr, c->d_n2e_elem,
+                                    c->d_n2e_loc, c->d_rank, c->d_nnbr, c->d_nodeptr, P->d_KeT[ch & 1], gf, c->d_A,
+                                    P->d_Atl);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
+// r_dev += R(u_dev); A_dev += gf * K(u_dev). With A_in / A_out (pinned or registered host arrays of nnz
+// doubles): the rows a chunk completes are first loaded from A_in and afterwards stored to A_out, both
+// overlapped with the element kernels of the neighbouring chunks.
+int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* A_out) {
+  c->last_launches = 0;
+  if (!c->plan) {
+    int rc = build_plan(c);
+    if (rc) return rc;
+  }
+  Plan* P = static_cast<Plan*>(c->plan);
+  const int nch = P->nch;
+  MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
+  MB2_CUDA(cudaEventRecord(P->start, c->stream));
+  for (auto s : {P->s_el, P->s_ga, P->s_h2d, P->s_d2h}) MB2_CUDA(cudaStreamWaitEvent(s, P->start, 0));
+  for (int ch = 0; ch < nch; ch++) {
+    const int64_t e0 = (int64_t)ch * P->EC, e1 = (e0 + P->EC < c->NE) ? e0 + P->EC : c->NE;
+    if (A_in) {
+      for (const Run& r : P->runs[ch])
+        MB2_CUDA(cudaMemcpyAsync(c->d_A + r.off, A_in + r.off, sizeof(double) * r.n, cudaMemcpyHostToDevice, P->s_h2d));
+      MB2_CUDA(cudaEventRecord(P->h2d[ch], P->s_h2d));
+    }
+    if (ch >= 2) MB2_CUDA(cudaStreamWaitEvent(P->s_el, P->ga1[ch - 2], 0));  // K_e buffer re-use
+    MB2_CUDA(cudaEventRecord(P->el0[ch], P->s_el));
+    int rc = dispatch_element<true>(c, make_args(c, e0, e1, P->d_KeT[ch & 1]), P->s_el);
+    if (rc) return rc;
+    MB2_CUDA(cudaEventRecord(P->el1[ch], P->s_el));
+    MB2_CUDA(cudaStreamWaitEvent(P->s_ga, P->el1[ch], 0));
+    if (A_in) MB2_CUDA(cudaStreamWaitEvent(P->s_ga, P->h2d[ch], 0));
+    MB2_CUDA(cudaEventRecord(P->ga0[ch], P->s_ga));
+    rc = (c->dim == 3) ? launch_gather<3>(c, P, ch, e0, e1, gf, P->s_ga) : launch_gather<2>(c, P, ch, e0, e1, gf, P->s_ga);
+    if (rc) return rc;
+    MB2_CUDA(cudaEventRecord(P->ga1[ch], P->s_ga));
+    if (A_out) {
+      MB2_CUDA(cudaStreamWaitEvent(P->s_d2h, P->ga1[ch], 0));
+      for (const Run& r : P->runs[ch])
+        MB2_CUDA(cudaMemcpyAsync(A_out + r.off, c->d_A + r.off, sizeof(double) * r.n, cudaMemcpyDeviceToHost, P->s_d2h));
+    }
+  }
+  int rc = launch_residual_gather(c, P->s_ga);  // every element kernel has completed on s_ga's timeline
+  if (rc) return rc;
+  MB2_CUDA(cudaEventRecord(P->done_ga, P->s_ga));
+  MB2_CUDA(cudaStreamWaitEvent(c->stream, P->done_ga, 0));
+  if (A_out) {
+    MB2_CUDA(cudaEventRecord(P->done_d2h, P->s_d2h));
+    MB2_CUDA(cudaStreamWaitEvent(c->stream, P->done_d2h, 0));
   }
   MB2_CUDA(cudaEventRecord(c->ev[2], c->stream));
-  c->last_launches = 3;
+  c->last_launches = 2 * nch + 1;
+  c->last_ms_valid = true;
+  return MB2_OK;
+}
+
+// out[0] = sum of element kernel durations, out[1] = sum of gather durations, out[2] = start-to-end of the call
+// (with the pipeline, [0] + [1] may exceed [2]).
+int collect_timing(mb2_ctx* c, float* out3) {
+  MB2_CUDA(cudaEventSynchronize(c->ev[2]));
+  MB2_CUDA(cudaEventElapsedTime(&out3[2], c->ev[0], c->ev[2]));
+  if (!c->last_ms_valid) {
+    MB2_CUDA(cudaEventElapsedTime(&out3[0], c->ev[0], c->ev[1]));
+    MB2_CUDA(cudaEventElapsedTime(&out3[1], c->ev[1], c->ev[2]));
+    return MB2_OK;
+  }
+  Plan* P = static_cast<Plan*>(c->plan);
+  out3[0] = out3[1] = 0.f;
+  for (int ch = 0; ch < P->nch; ch++) {
+    float a = 0.f, b = 0.f;
+    MB2_CUDA(cudaEventElapsedTime(&a, P->el0[ch], P->el1[ch]));
+    MB2_CUDA(cudaEventElapsedTime(&b, P->ga0[ch], P->ga1[ch]));
+    out3[0] += a;
+    out3[1] += b;
+  }
+  return MB2_OK;
+}
+
+int plan_info(mb2_ctx* c, int64_t* chunk_elems, int* nchunks) {
+  if (!c->plan) {
+    int rc = build_plan(c);
+    if (rc) return rc;
+  }
+  Plan* P = static_cast<Plan*>(c->plan);
+  if (chunk_elems) *chunk_elems = P->EC;
+  if (nchunks) *nchunks = P->nch;
   return MB2_OK;
 }
 

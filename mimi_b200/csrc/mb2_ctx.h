@@ -19,6 +19,10 @@ struct mb2_ctx {
   int64_t NE = 0, NV = 0, Nn = 0, nnz = 0;
 
   // material
+  int chunk_mb = 2048;      // K_e buffer budget per chunk (MiB), two buffers
+  int64_t chunk_elems = 0;  // explicit chunk size (0 = from chunk_mb)
+  void* plan = nullptr;     // chunk pipeline state (mb2_assembly.cu)
+  bool last_ms_valid = false;
   int elem_variant = 0;  // 0 = default kernels, 1 = force the one-thread-per-dof FD kernel (A/B tests)
   int mat_kind = -1;
   double lambda = 0, mu = 0;
@@ -67,7 +71,10 @@ int build_pattern(mb2_ctx* c);
 int expand_A_ids(mb2_ctx* c, int32_t* d_out);
 // mb2_assembly.cu
 int launch_residual(mb2_ctx* c);
-int launch_residual_and_grad(mb2_ctx* c, double gf);
+int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* A_out);
+void free_plan(mb2_ctx* c);
+int collect_timing(mb2_ctx* c, float* out3);
+int plan_info(mb2_ctx* c, int64_t* chunk_elems, int* nchunks);
 int launch_fp64_peak(mb2_ctx* c, int fma, double* tflops);
 // mb2_tables.cu
 int set_nodes(mb2_ctx* c, const double* x_ref, const double* weights);
