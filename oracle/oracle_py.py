@@ -142,3 +142,22 @@ def run_ref_time(mesh, elevate, refine, material, nthreads, reps, warmup=0):
     cmd = [REF_BIN, "time", mesh, str(elevate), str(refine), material, str(nthreads), str(reps), str(warmup)]
     p = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, check=True, text=True)
     return json.loads(p.stderr.strip().splitlines()[-1])
+
+
+def element_matrices(dim, nd, nq, m, v_dofs, dN_dX, w, detJ, u, elems):
+    """Per-element residual R_e [n, tdof] and FD tangent K_e [n, tdof(col i), tdof(row j)] (K_e(j, i) column-major,
+    as ElementResidualAndGrad fills it) for the listed elements."""
+    tdof = dim * nd
+    n = len(elems)
+    R = np.zeros((n, tdof))
+    K = np.zeros((n, tdof, tdof))
+    Rf = np.zeros(tdof)
+    L = lib()
+    for x, e in enumerate(elems):
+        ue = np.ascontiguousarray(u[v_dofs[e]])
+        L.orc_element_residual_and_grad(C.c_int(dim), C.c_int(nd), C.c_int(nq), C.byref(m), _p(ue, C.c_double),
+                                        _p(np.ascontiguousarray(dN_dX[e]), C.c_double),
+                                        _p(np.ascontiguousarray(w[e]), C.c_double),
+                                        _p(np.ascontiguousarray(detJ[e]), C.c_double), _p(R[x], C.c_double),
+                                        _p(Rf, C.c_double), _p(K[x], C.c_double))
+    return R, K

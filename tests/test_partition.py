@@ -1,0 +1,99 @@
+"""CPU, world_size 2 over gloo: the multi-GPU host logic (mimi_b200/partition.py). Each rank computes the element
+matrices of its own range with the C oracle, sends the raw matrices of its send-set to the lower rank, and sums
+own + ghost contributions in ascending element id into the rows of the nodes it owns. The union of the owned rows
+must equal the reference's single-thread assembly bit for bit."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from mimi_b200 import partition as P
+from oracle import oracle_py as O
+from tests.cases import load_golden
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, name, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    D = load_golden(name)
+    dim, nd, nq, tdof = D["dim"], D["nd"], D["nq"], D["tdof"]
+    ranges = P.element_ranges(D["NE"], world)
+    R = P.rank_problem(D["v_dofs"], dim, D["NV"], ranges, rank)
+    m = O.mat(0)
+    own = np.arange(R["e0"], R["e1"])
+    Re, Ke = O.element_matrices(dim, nd, nq, m, D["v_dofs"], D["dN_dX"], D["w"], D["detJ"], D["u"], own)
+    n_local = len(R["local_elems"])
+    Re_l = np.zeros((n_local, tdof)); Ke_l = np.zeros((n_local, tdof, tdof))
+    Re_l[:len(own)] = Re; Ke_l[:len(own)] = Ke
+    ops, keep = [], []
+    for peer, idx in R["send"].items():
+        for buf in (torch.from_numpy(np.ascontiguousarray(Ke[idx])), torch.from_numpy(np.ascontiguousarray(Re[idx]))):
+            keep.append(buf); ops.append(dist.P2POp(dist.isend, buf, peer))
+    recv_bufs = []
+    for peer, idx in R["recv"].items():
+        kb, rb = torch.zeros(len(idx), tdof, tdof, dtype=torch.float64), torch.zeros(len(idx), tdof, dtype=torch.float64)
+        recv_bufs.append((idx, kb, rb)); ops += [dist.P2POp(dist.irecv, kb, peer), dist.P2POp(dist.irecv, rb, peer)]
+    if ops:
+        for w_ in dist.batch_isend_irecv(ops):
+            w_.wait()
+    for idx, kb, rb in recv_bufs:
+        Ke_l[idx] = kb.numpy(); Re_l[idx] = rb.numpy()
+    # ordered gather into owned rows (reference: thread-local sum from 0.0, then A += gf * A_tl)
+    owned_v = np.repeat(R["owned"], dim)
+    Atl = np.zeros(D["nnz"]); rtl = np.zeros(D["NV"])
+    for x, e in enumerate(R["local_elems"]):
+        vd = D["v_dofs"][e]
+        rows_owned = owned_v[vd]
+        np.add.at(rtl, vd[rows_owned], Re_l[x][rows_owned])
+        aid = D["A_ids"][e].reshape(tdof, tdof)            # [col i][row j]
+        sel = np.broadcast_to(rows_owned[None, :], (tdof, tdof))
+        np.add.at(Atl, aid[sel], Ke_l[x][sel])
+    A = D["mass"] + D["gf"] * Atl
+    I = D["I"].astype(np.int64)
+    row_of = np.repeat(np.arange(D["NV"]), np.diff(I))
+    ok_A = np.array_equal(A[owned_v[row_of]], D["A_neohookean"][owned_v[row_of]])
+    ok_r = np.array_equal(rtl[owned_v], D["r2_neohookean"][owned_v])
+    cover = torch.from_numpy(owned_v.astype(np.int64))
+    dist.all_reduce(cover)
+    out[rank] = (ok_A, ok_r, bool((cover.numpy() == 1).all()), len(R["send"]), len(R["recv"]))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name", ["cube_p2_n3_patch", "cube_p2_n2"])
+def test_two_rank_partition_reproduces_reference(name):
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), name, out), nprocs=world, join=True)
+    for r in range(world):
+        ok_A, ok_r, cover, ns, nr = out[r]
+        assert ok_A and ok_r and cover, (r, out[r])
+    assert out[0][4] == 1 and out[1][3] == 1       # rank 0 receives ghosts from rank 1, rank 1 sends to rank 0
+
+
+def test_ranges_and_ownership():
+    from mimi_b200 import meshgen
+    M = meshgen.patch_connectivity(2, (3, 3, 8))
+    rg = P.element_ranges(M["NE"], 4)
+    assert rg[0] == 0 and rg[-1] == M["NE"] and (np.diff(rg) > 0).all()
+    owned = np.zeros(M["Nn"], int)
+    for r in range(4):
+        R = P.rank_problem(M["v_dofs"], 3, M["NV"], rg, r)
+        owned += R["owned"]
+        # every ghost has a larger id than every own element and ghosts are ascending
+        assert (np.diff(R["local_elems"]) > 0).all()
+        for peer, idx in R["send"].items():
+            assert peer < r
+    assert (owned == 1).all()
