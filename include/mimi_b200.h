@@ -137,6 +137,33 @@ int mb2_last_launch_count(mb2_ctx* ctx);
 /* Synchronise ctx's stream. */
 int mb2_sync(mb2_ctx* ctx);
 
+/* ---- multi-GPU: element partition with raw element-matrix exchange ------------------
+ * One context per GPU / rank. The rank's connectivity (mb2_set_connectivity) lists its own elements first
+ * (global ascending order) and then its GHOST elements: elements computed by higher ranks that touch a node this
+ * rank owns. Node ids stay global. mb2_set_partition (before mb2_build_pattern): elements [0, n_compute) are
+ * computed here; owned_nodes[Nn] != 0 marks the nodes whose CSR rows / residual entries this rank assembles
+ * (owner = rank of the node's lowest element, mimi_b200/partition.py). Replaces the reference's thread-private
+ * accumulators + ordered reduction (src/mimi/integrators/nonlinear_base.hpp:90-151) across devices; results stay
+ * bit-identical to its single-thread order because raw K_e / R_e travel, not partial sums. */
+int mb2_set_partition(mb2_ctx* ctx, int64_t n_compute, const uint8_t* owned_nodes);
+/* Elements (local indices, ascending, < n_compute) whose K_e / R_e go to rank `peer`. */
+int mb2_mg_set_send(mb2_ctx* ctx, int peer, const int64_t* local_elems, int64_t n);
+/* Contiguous block of ghost elements [first_local_elem, +n) that rank `peer` fills. */
+int mb2_mg_set_recv(mb2_ctx* ctx, int peer, int64_t first_local_elem, int64_t n);
+/* NCCL transport (libnccl is loaded with dlopen): rank 0 creates the 128-byte id, every rank joins. After this the
+ * ordinary entries (mb2_assemble_*_device, mb2_add_domain_*) perform the exchange inside the call. */
+int mb2_mg_unique_id(void* out128);
+int mb2_mg_init_nccl(mb2_ctx* ctx, int rank, int world, const void* unique_id128);
+/* Manual transport: the host moves the packed buffers (tests emulating ranks on one GPU; foreign transports).
+ * Sequence per assembly: mb2_mg_begin -> mb2_mg_export_send on the sender / mb2_mg_import_recv on the owner ->
+ * mb2_mg_finish. Ke: [n][mb2_mg_ke_doubles] (NULL in residual-only mode), Re: [n][tdof]. */
+int mb2_mg_set_manual(mb2_ctx* ctx, int on);
+int mb2_mg_begin(mb2_ctx* ctx, double grad_factor, int grad);
+int mb2_mg_export_send(mb2_ctx* ctx, int peer, double* Ke_host, double* Re_host);
+int mb2_mg_import_recv(mb2_ctx* ctx, int peer, const double* Ke_host, const double* Re_host);
+int mb2_mg_finish(mb2_ctx* ctx, double grad_factor, int grad);
+int64_t mb2_mg_ke_doubles(mb2_ctx* ctx);
+
 /* Tuning / A-B switches (never change results): "elem_variant" 0 = default kernels, 1 = one-thread-per-dof FD
  * kernel; "chunk_elems" = elements per pipeline chunk (0 = derive from "chunk_mb", the K_e buffer budget in MiB). */
 int mb2_set_option(mb2_ctx* ctx, const char* name, int value);

@@ -22,7 +22,9 @@ SYMBOLS = [
     "mb2_get_pattern_i32", "mb2_get_pattern_i64", "mb2_get_A_ids_i32", "mb2_set_material",
     "mb2_add_domain_residual", "mb2_add_domain_residual_and_grad", "mb2_set_u", "mb2_set_r", "mb2_set_A",
     "mb2_get_r", "mb2_get_A", "mb2_assemble_residual_device", "mb2_assemble_residual_and_grad_device",
-    "mb2_device_pointers", "mb2_last_timing_ms", "mb2_last_launch_count", "mb2_sync", "mb2_measure_fp64_peak", "mb2_set_option", "mb2_host_register", "mb2_host_unregister", "mb2_plan_info",
+    "mb2_device_pointers", "mb2_last_timing_ms", "mb2_last_launch_count", "mb2_sync", "mb2_measure_fp64_peak", "mb2_set_option", "mb2_host_register", "mb2_host_unregister", "mb2_plan_info", "mb2_set_partition", "mb2_mg_set_send", "mb2_mg_set_recv", "mb2_mg_unique_id",
+    "mb2_mg_init_nccl", "mb2_mg_set_manual", "mb2_mg_begin", "mb2_mg_export_send", "mb2_mg_import_recv", "mb2_mg_finish",
+    "mb2_mg_ke_doubles",
 ]
 
 
@@ -32,6 +34,14 @@ class Mb2Error(RuntimeError):
 
 
 _lib = None
+
+
+def mg_unique_id():
+    buf = C.create_string_buffer(128)
+    rc = load().mb2_mg_unique_id(buf)
+    if rc:
+        raise Mb2Error("mb2_mg_unique_id failed (libnccl not loadable?)")
+    return buf.raw
 
 
 def load():
@@ -187,6 +197,47 @@ class Context:
 
     def host_unregister(self, arr):
         self._ck(self.lib.mb2_host_unregister(self.h, _dp(arr)))
+
+    # ---- multi-GPU partition
+    def set_partition(self, n_compute, owned_nodes):
+        m = np.ascontiguousarray(owned_nodes, np.uint8)
+        assert m.size == self.NV // self.dim
+        self._ck(self.lib.mb2_set_partition(self.h, C.c_int64(n_compute), _dp(m)))
+        self.n_compute = n_compute
+
+    def mg_setup(self, R, manual=False):
+        """R: a dict from mimi_b200.partition.rank_problem."""
+        self.set_partition(R["n_compute"], R["owned"])
+        for peer, idx in R["send"].items():
+            idx = np.ascontiguousarray(idx, np.int64)
+            self._ck(self.lib.mb2_mg_set_send(self.h, int(peer), _dp(idx), C.c_int64(len(idx))))
+        for peer, idx in R["recv"].items():
+            assert (np.diff(idx) == 1).all()
+            self._ck(self.lib.mb2_mg_set_recv(self.h, int(peer), C.c_int64(int(idx[0])), C.c_int64(len(idx))))
+        if manual:
+            self._ck(self.lib.mb2_mg_set_manual(self.h, 1))
+        self.mg = R
+
+    def mg_init_nccl(self, rank, world, uid):
+        self._ck(self.lib.mb2_mg_init_nccl(self.h, rank, world, uid))
+
+    def mg_begin(self, gf, grad=True):
+        self._ck(self.lib.mb2_mg_begin(self.h, C.c_double(gf), int(grad)))
+
+    def mg_finish(self, gf, grad=True):
+        self._ck(self.lib.mb2_mg_finish(self.h, C.c_double(gf), int(grad)))
+
+    def mg_export(self, peer, grad=True):
+        n = len(self.mg["send"][peer])
+        self.lib.mb2_mg_ke_doubles.restype = C.c_int64
+        ked = self.lib.mb2_mg_ke_doubles(self.h)
+        K = np.empty((n, ked)) if grad else None
+        R = np.empty((n, self.tdof))
+        self._ck(self.lib.mb2_mg_export_send(self.h, int(peer), _dp(K), _dp(R)))
+        return K, R
+
+    def mg_import(self, peer, K, R):
+        self._ck(self.lib.mb2_mg_import_recv(self.h, int(peer), _dp(K), _dp(R)))
 
     def sync(self):
         self._ck(self.lib.mb2_sync(self.h))

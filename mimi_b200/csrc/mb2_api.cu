@@ -27,6 +27,8 @@ static void free_problem(mb2_ctx* c) {
   dfree(c->d_nbr); dfree(c->d_rank); dfree(c->d_I); dfree(c->d_J);
   dfree(c->d_u); dfree(c->d_r); dfree(c->d_A); dfree(c->d_Re);
   mb2::free_plan(c);
+  mb2::free_mg(c);
+  dfree(c->d_owned);
   c->have_pattern = false;
   c->nnz = 0;
 }
@@ -93,7 +95,7 @@ int mb2_set_connectivity(mb2_ctx* c, int dim, int nd, int nq, int64_t NE, int64_
   REQUIRE(NV % dim == 0, "NV must be dim * number of nodes");
   MB2_CUDA(cudaSetDevice(c->device));
   free_problem(c);
-  c->dim = dim; c->nd = nd; c->nq = nq; c->tdof = dim * nd; c->NE = NE; c->NV = NV; c->Nn = NV / dim;
+  c->dim = dim; c->nd = nd; c->nq = nq; c->tdof = dim * nd; c->NE = NE; c->NV = NV; c->Nn = NV / dim; c->n_compute = NE;
   MB2_CUDA(cudaMalloc(&c->d_vdofs, sizeof(int32_t) * NE * c->tdof));
   MB2_CUDA(cudaMemcpyAsync(c->d_vdofs, v_dofs, sizeof(int32_t) * NE * c->tdof, cudaMemcpyHostToDevice, c->stream));
   MB2_CUDA(cudaMalloc(&c->d_u, sizeof(double) * NV));

@@ -408,10 +408,12 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
 // r[dim*I + c] += ((0 + R_e1) + R_e2) + ...   (thread_local_residual_ then nonlinear_base.hpp:96-105)
 __global__ void residual_gather_kernel(int dim, int nd, int64_t Nn, const int64_t* __restrict__ n2e_ptr,
                                        const int32_t* __restrict__ n2e_elem, const uint8_t* __restrict__ n2e_loc,
-                                       const double* __restrict__ Re, double* __restrict__ r) {
+                                       const double* __restrict__ Re, double* __restrict__ r,
+                                       const uint8_t* __restrict__ owned) {
   const int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (v >= Nn * dim) return;
   const int64_t I = v / dim;
+  if (owned && !owned[I]) return;  // residual entries of nodes owned by another rank are assembled there
   const int c = (int)(v % dim);
   const int tdof = dim * nd;
   double acc = 0.0;
@@ -561,22 +563,8 @@ static ElemArgs make_args(mb2_ctx* c, int64_t e0, int64_t e1, double* KeT) {
 static int launch_residual_gather(mb2_ctx* c, cudaStream_t st) {
   const int64_t n = c->Nn * c->dim;
   residual_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(c->dim, c->nd, c->Nn, c->d_n2e_ptr, c->d_n2e_elem,
-                                                                      c->d_n2e_loc, c->d_Re, c->d_r);
+                                                                      c->d_n2e_loc, c->d_Re, c->d_r, c->d_owned);
   MB2_CUDA(cudaGetLastError());
-  return MB2_OK;
-}
-
-int launch_residual(mb2_ctx* c) {
-  c->last_launches = 0;
-  MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
-  int rc = dispatch_element<false>(c, make_args(c, 0, c->NE, nullptr), c->stream);
-  if (rc) return rc;
-  MB2_CUDA(cudaEventRecord(c->ev[1], c->stream));
-  rc = launch_residual_gather(c, c->stream);
-  if (rc) return rc;
-  MB2_CUDA(cudaEventRecord(c->ev[2], c->stream));
-  c->last_launches = 2;
-  c->last_ms_valid = false;
   return MB2_OK;
 }
 
@@ -591,7 +579,13 @@ struct Run {
 };
 struct Plan {
   int64_t EC = 0;  // elements per chunk
-  int nch = 0;
+  int nch = 0;     // chunks of computed elements, plus one ghost chunk when the rank has ghosts
+  int nch_own = 0;
+  int64_t n_own = 0, NE = 0;
+  double* d_ghost = nullptr;  // [NE - n_own][nd][KP]: element matrices received from other ranks
+  int chunk_of(int64_t e) const { return e < n_own ? (int)(e / EC) : nch_own; }
+  int64_t begin_of(int ch) const { return ch < nch_own ? (int64_t)ch * EC : n_own; }
+  int64_t end_of(int ch) const { return ch < nch_own ? ((ch + 1) * EC < n_own ? (ch + 1) * EC : n_own) : NE; }
   std::vector<int64_t> node_ptr;        // nch+1: offsets into d_nodes
   int32_t* d_nodes = nullptr;           // nodes touched by each chunk (ascending ids per chunk)
   std::vector<std::vector<Run>> runs;   // per chunk: CSR value ranges of the nodes FINALISED by that chunk
@@ -610,6 +604,7 @@ void free_plan(mb2_ctx* c) {
   cudaFree(P->d_KeT[0]);
   cudaFree(P->d_KeT[1]);
   cudaFree(P->d_Atl);
+  cudaFree(P->d_ghost);
   for (auto* v : {&P->el0, &P->el1, &P->ga0, &P->ga1, &P->h2d})
     for (auto e : *v) cudaEventDestroy(e);
   for (auto e : {P->start, P->done_ga, P->done_d2h})
@@ -643,9 +638,13 @@ static int build_plan(mb2_ctx* c) {
     EC = EC / wave * wave;
     if (EC < wave) EC = wave;
   }
-  if (EC > NE) EC = NE;
+  const int64_t n_own = c->n_compute;
+  if (EC > n_own) EC = n_own;
   P->EC = EC;
-  P->nch = (int)((NE + EC - 1) / EC);
+  P->n_own = n_own;
+  P->NE = NE;
+  P->nch_own = (int)((n_own + EC - 1) / EC);
+  P->nch = P->nch_own + (NE > n_own ? 1 : 0);
   const int nch = P->nch;
 
   // first / last element of every node, neighbour counts and block-row offsets -> host
@@ -670,32 +669,33 @@ static int build_plan(mb2_ctx* c) {
   P->node_ptr.assign(nch + 1, 0);
   P->max_nnbr = 1;
   for (int64_t I = 0; I < Nn; I++) {
-    if (first[I] < 0) continue;
+    if (first[I] < 0 || nnbr[I] == 0) continue;  // untouched, or owned by another rank
     if (nnbr[I] > P->max_nnbr) P->max_nnbr = nnbr[I];
-    for (int64_t ch = first[I] / EC; ch <= last[I] / EC; ch++) P->node_ptr[ch + 1]++;
+    for (int ch = P->chunk_of(first[I]); ch <= P->chunk_of(last[I]); ch++) P->node_ptr[ch + 1]++;
   }
   for (int ch = 0; ch < nch; ch++) P->node_ptr[ch + 1] += P->node_ptr[ch];
   std::vector<int32_t> nodes((size_t)P->node_ptr[nch]);
   {
     std::vector<int64_t> fill(P->node_ptr.begin(), P->node_ptr.end() - 1);
     for (int64_t I = 0; I < Nn; I++) {
-      if (first[I] < 0) continue;
-      for (int64_t ch = first[I] / EC; ch <= last[I] / EC; ch++) nodes[(size_t)fill[ch]++] = (int32_t)I;
+      if (first[I] < 0 || nnbr[I] == 0) continue;
+      for (int ch = P->chunk_of(first[I]); ch <= P->chunk_of(last[I]); ch++) nodes[(size_t)fill[ch]++] = (int32_t)I;
     }
   }
   // value ranges finalised per chunk: merge nodes with consecutive ids (their block rows are contiguous)
   P->runs.assign(nch, {});
   for (int64_t I = 0; I < Nn; I++) {
-    if (first[I] < 0) continue;
-    auto& R = P->runs[(size_t)(last[I] / EC)];
+    if (first[I] < 0 || nnbr[I] == 0) continue;
+    auto& R = P->runs[(size_t)P->chunk_of(last[I])];
     const int64_t off = dd * nodeptr[I], n = dd * nnbr[I];
     if (!R.empty() && R.back().off + R.back().n == off) R.back().n += n;
     else R.push_back({off, n});
   }
   MB2_CUDA(cudaMalloc(&P->d_nodes, sizeof(int32_t) * (nodes.size() ? nodes.size() : 1)));
   MB2_CUDA(cudaMemcpy(P->d_nodes, nodes.data(), sizeof(int32_t) * nodes.size(), cudaMemcpyHostToDevice));
-  const int nbuf = nch > 1 ? 2 : 1;
+  const int nbuf = P->nch_own > 1 ? 2 : 1;
   for (int b = 0; b < nbuf; b++) MB2_CUDA(cudaMalloc(&P->d_KeT[b], bytes_el * (size_t)EC));
+  if (NE > n_own) MB2_CUDA(cudaMalloc(&P->d_ghost, bytes_el * (size_t)(NE - n_own)));
   if (nch > 1) MB2_CUDA(cudaMalloc(&P->d_Atl, sizeof(double) * (size_t)c->nnz));
   int lo = 0, hi = 0;
   MB2_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));  // hi = numerically smallest = highest priority
@@ -724,33 +724,57 @@ static int launch_gather(mb2_ctx* c, Plan* P, int ch, int64_t e0, int64_t e1, do
   const int64_t cap = (int64_t)c->sm_count * 256;
   const unsigned grid = (unsigned)(n_nodes < cap ? n_nodes : cap);
   kern<<<grid, threads, smem, st>>>(c->nd, P->d_nodes + P->node_ptr[ch], n_nodes, e0, e1, c->d_n2e_ptr, c->d_n2e_elem,
-                                    c->d_n2e_loc, c->d_rank, c->d_nnbr, c->d_nodeptr, P->d_KeT[ch & 1], gf, c->d_A,
+                                    c->d_n2e_loc, c->d_rank, c->d_nnbr, c->d_nodeptr, ch < P->nch_own ? P->d_KeT[ch & 1] : P->d_ghost, gf, c->d_A,
                                     P->d_Atl);
   MB2_CUDA(cudaGetLastError());
   return MB2_OK;
 }
 
-// r_dev += R(u_dev); A_dev += gf * K(u_dev). With A_in / A_out (pinned or registered host arrays of nnz
-// doubles): the rows a chunk completes are first loaded from A_in and afterwards stored to A_out, both
-// overlapped with the element kernels of the neighbouring chunks.
-int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* A_out) {
+// Stage 1 of an assembly: everything that only needs this rank's own elements.
+//  grad: r_dev += R(u_dev); A_dev += gf * K(u_dev). With A_in / A_out (pinned or registered host arrays of nnz
+//  doubles) the rows a chunk completes are first loaded from A_in and afterwards stored to A_out, both overlapped
+//  with the element kernels of the neighbouring chunks. Element matrices other ranks need are packed for sending.
+//  !grad: element residuals only.
+int assemble_begin(mb2_ctx* c, double gf, bool grad, const double* A_in, double* A_out) {
   c->last_launches = 0;
   if (!c->plan) {
     int rc = build_plan(c);
     if (rc) return rc;
   }
   Plan* P = static_cast<Plan*>(c->plan);
-  const int nch = P->nch;
+  MgState* mg = c->mg;
   MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
   MB2_CUDA(cudaEventRecord(P->start, c->stream));
   for (auto s : {P->s_el, P->s_ga, P->s_h2d, P->s_d2h}) MB2_CUDA(cudaStreamWaitEvent(s, P->start, 0));
-  for (int ch = 0; ch < nch; ch++) {
-    const int64_t e0 = (int64_t)ch * P->EC, e1 = (e0 + P->EC < c->NE) ? e0 + P->EC : c->NE;
+  if (!grad) {
+    MB2_CUDA(cudaEventRecord(P->el0[0], P->s_el));
+    int rc = dispatch_element<false>(c, make_args(c, 0, P->n_own, nullptr), P->s_el);
+    if (rc) return rc;
+    MB2_CUDA(cudaEventRecord(P->el1[0], P->s_el));
+    MB2_CUDA(cudaStreamWaitEvent(P->s_ga, P->el1[0], 0));
+    MB2_CUDA(cudaEventRecord(P->ga0[0], P->s_ga));
+    if (mg) {
+      rc = mg_pack_chunk(c, 0, P->n_own, nullptr, false, P->s_ga);
+      if (rc) return rc;
+      MB2_CUDA(cudaEventRecord(mg->ev_pack, P->s_ga));
+    }
+    c->last_launches = 1;
+    return MB2_OK;
+  }
+  int64_t last_send = -1;
+  if (mg)
+    for (auto& pr : mg->peers)
+      if (!pr.send_elems.empty() && pr.send_elems.back() > last_send) last_send = pr.send_elems.back();
+  if (mg && last_send < 0) MB2_CUDA(cudaEventRecord(mg->ev_pack, P->s_ga));
+  for (int ch = 0; ch < P->nch; ch++) {
+    const bool ghost = ch >= P->nch_own;
+    const int64_t e0 = P->begin_of(ch), e1 = P->end_of(ch);
     if (A_in) {
       for (const Run& r : P->runs[ch])
         MB2_CUDA(cudaMemcpyAsync(c->d_A + r.off, A_in + r.off, sizeof(double) * r.n, cudaMemcpyHostToDevice, P->s_h2d));
       MB2_CUDA(cudaEventRecord(P->h2d[ch], P->s_h2d));
     }
+    if (ghost) break;  // gathered in assemble_finish, once the element matrices have arrived
     if (ch >= 2) MB2_CUDA(cudaStreamWaitEvent(P->s_el, P->ga1[ch - 2], 0));  // K_e buffer re-use
     MB2_CUDA(cudaEventRecord(P->el0[ch], P->s_el));
     int rc = dispatch_element<true>(c, make_args(c, e0, e1, P->d_KeT[ch & 1]), P->s_el);
@@ -759,6 +783,11 @@ int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* 
     MB2_CUDA(cudaStreamWaitEvent(P->s_ga, P->el1[ch], 0));
     if (A_in) MB2_CUDA(cudaStreamWaitEvent(P->s_ga, P->h2d[ch], 0));
     MB2_CUDA(cudaEventRecord(P->ga0[ch], P->s_ga));
+    if (mg && last_send >= e0) {
+      rc = mg_pack_chunk(c, e0, e1, P->d_KeT[ch & 1], true, P->s_ga);
+      if (rc) return rc;
+      if (last_send < e1) MB2_CUDA(cudaEventRecord(mg->ev_pack, P->s_ga));  // every outgoing matrix is packed
+    }
     rc = (c->dim == 3) ? launch_gather<3>(c, P, ch, e0, e1, gf, P->s_ga) : launch_gather<2>(c, P, ch, e0, e1, gf, P->s_ga);
     if (rc) return rc;
     MB2_CUDA(cudaEventRecord(P->ga1[ch], P->s_ga));
@@ -767,9 +796,37 @@ int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* 
       for (const Run& r : P->runs[ch])
         MB2_CUDA(cudaMemcpyAsync(A_out + r.off, c->d_A + r.off, sizeof(double) * r.n, cudaMemcpyDeviceToHost, P->s_d2h));
     }
+    c->last_launches += 2;
+  }
+  return MB2_OK;
+}
+
+// Stage 2: ghost contributions (already in the ghost buffer / the tail of d_Re, stream-ordered through
+// mg->ev_comm or copied synchronously in manual mode), residual gather, join.
+int assemble_finish(mb2_ctx* c, double gf, bool grad, double* A_out) {
+  Plan* P = static_cast<Plan*>(c->plan);
+  MgState* mg = c->mg;
+  if (mg && !mg->manual && P->NE > P->n_own) MB2_CUDA(cudaStreamWaitEvent(P->s_ga, mg->ev_comm, 0));
+  if (grad && P->nch > P->nch_own) {
+    const int ch = P->nch_own;
+    const int64_t e0 = P->begin_of(ch), e1 = P->end_of(ch);
+    MB2_CUDA(cudaStreamWaitEvent(P->s_ga, P->h2d[ch], 0));  // recorded in assemble_begin when A_in was given
+    MB2_CUDA(cudaEventRecord(P->ga0[ch], P->s_ga));
+    int rc = (c->dim == 3) ? launch_gather<3>(c, P, ch, e0, e1, gf, P->s_ga) : launch_gather<2>(c, P, ch, e0, e1, gf, P->s_ga);
+    if (rc) return rc;
+    MB2_CUDA(cudaEventRecord(P->ga1[ch], P->s_ga));
+    MB2_CUDA(cudaEventRecord(P->el0[ch], P->s_ga));  // no element kernel for ghosts: zero-length interval
+    MB2_CUDA(cudaEventRecord(P->el1[ch], P->s_ga));
+    if (A_out) {
+      MB2_CUDA(cudaStreamWaitEvent(P->s_d2h, P->ga1[ch], 0));
+      for (const Run& r : P->runs[ch])
+        MB2_CUDA(cudaMemcpyAsync(A_out + r.off, c->d_A + r.off, sizeof(double) * r.n, cudaMemcpyDeviceToHost, P->s_d2h));
+    }
+    c->last_launches += 1;
   }
   int rc = launch_residual_gather(c, P->s_ga);  // every element kernel has completed on s_ga's timeline
   if (rc) return rc;
+  if (!grad) MB2_CUDA(cudaEventRecord(P->ga1[0], P->s_ga));
   MB2_CUDA(cudaEventRecord(P->done_ga, P->s_ga));
   MB2_CUDA(cudaStreamWaitEvent(c->stream, P->done_ga, 0));
   if (A_out) {
@@ -777,24 +834,39 @@ int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* 
     MB2_CUDA(cudaStreamWaitEvent(c->stream, P->done_d2h, 0));
   }
   MB2_CUDA(cudaEventRecord(c->ev[2], c->stream));
-  c->last_launches = 2 * nch + 1;
-  c->last_ms_valid = true;
+  c->last_launches += 1;
+  c->last_grad = grad;
   return MB2_OK;
 }
+
+static int assemble(mb2_ctx* c, double gf, bool grad, const double* A_in, double* A_out) {
+  int rc = assemble_begin(c, gf, grad, A_in, A_out);
+  if (rc) return rc;
+  if (c->mg) {
+    if (c->mg->manual) {
+      c->err = "partition in manual-exchange mode: use mb2_mg_begin / export / import / mb2_mg_finish";
+      return MB2_ERR_ARG;
+    }
+    Plan* P = static_cast<Plan*>(c->plan);
+    if ((rc = mg_exchange(c, grad, P->s_ga, P->s_ga))) return rc;
+  }
+  return assemble_finish(c, gf, grad, A_out);
+}
+int launch_residual(mb2_ctx* c) { return assemble(c, 0.0, false, nullptr, nullptr); }
+int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* A_out) {
+  return assemble(c, gf, true, A_in, A_out);
+}
+double* ghost_ke_buffer(mb2_ctx* c) { return c->plan ? static_cast<Plan*>(c->plan)->d_ghost : nullptr; }
 
 // out[0] = sum of element kernel durations, out[1] = sum of gather durations, out[2] = start-to-end of the call
 // (with the pipeline, [0] + [1] may exceed [2]).
 int collect_timing(mb2_ctx* c, float* out3) {
   MB2_CUDA(cudaEventSynchronize(c->ev[2]));
   MB2_CUDA(cudaEventElapsedTime(&out3[2], c->ev[0], c->ev[2]));
-  if (!c->last_ms_valid) {
-    MB2_CUDA(cudaEventElapsedTime(&out3[0], c->ev[0], c->ev[1]));
-    MB2_CUDA(cudaEventElapsedTime(&out3[1], c->ev[1], c->ev[2]));
-    return MB2_OK;
-  }
   Plan* P = static_cast<Plan*>(c->plan);
   out3[0] = out3[1] = 0.f;
-  for (int ch = 0; ch < P->nch; ch++) {
+  const int n = c->last_grad ? P->nch : 1;
+  for (int ch = 0; ch < n; ch++) {
     float a = 0.f, b = 0.f;
     MB2_CUDA(cudaEventElapsedTime(&a, P->el0[ch], P->el1[ch]));
     MB2_CUDA(cudaEventElapsedTime(&b, P->ga0[ch], P->ga1[ch]));

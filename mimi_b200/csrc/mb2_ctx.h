@@ -4,8 +4,29 @@
 
 #include <cstdint>
 #include <string>
+#include <vector>
 
 #include "../../include/mimi_b200.h"
+
+// Multi-GPU exchange state: which element matrices leave to / arrive from which peer (mb2_multigpu.cu).
+struct MgPeer {
+  int peer = -1;
+  // send: local element indices (ascending, < n_compute) whose K_e / R_e go to `peer`
+  std::vector<int64_t> send_elems;
+  int64_t* d_send_elems = nullptr;
+  double* d_send = nullptr;       // [n_send][nd*KP] K_e blocks, then [n_send][tdof] residuals
+  // recv: contiguous block of ghost elements [recv_first, recv_first + n_recv) filled by `peer`
+  int64_t recv_first = 0, n_recv = 0;
+};
+struct MgState {
+  std::vector<MgPeer> peers;
+  int rank = 0, world = 1;
+  void* nccl_lib = nullptr;   // dlopen handle
+  void* comm = nullptr;       // ncclComm_t
+  cudaStream_t s_comm = nullptr;
+  cudaEvent_t ev_pack = nullptr, ev_comm = nullptr;
+  bool manual = false;        // exchange driven by the host through mb2_mg_export/import (tests, foreign transports)
+};
 
 struct mb2_ctx {
   int device = 0;
@@ -22,10 +43,16 @@ struct mb2_ctx {
   int chunk_mb = 2048;      // K_e buffer budget per chunk (MiB), two buffers
   int64_t chunk_elems = 0;  // explicit chunk size (0 = from chunk_mb)
   void* plan = nullptr;     // chunk pipeline state (mb2_assembly.cu)
-  bool last_ms_valid = false;
+  bool last_grad = false;
   int elem_variant = 0;  // 0 = default kernels, 1 = force the one-thread-per-dof FD kernel (A/B tests)
   int mat_kind = -1;
   double lambda = 0, mu = 0;
+
+  // partition (multi-GPU): elements [0, n_compute) are computed here, [n_compute, NE) are ghosts whose
+  // element matrices arrive from other ranks; only rows of owned nodes are assembled
+  int64_t n_compute = 0;
+  uint8_t* d_owned = nullptr;  // Nn, nullptr = every node
+  MgState* mg = nullptr;       // exchange state (mb2_multigpu.cu)
 
   // connectivity
   int32_t* d_vdofs = nullptr;   // NE x tdof (reference layout)
@@ -75,6 +102,13 @@ int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* 
 void free_plan(mb2_ctx* c);
 int collect_timing(mb2_ctx* c, float* out3);
 int plan_info(mb2_ctx* c, int64_t* chunk_elems, int* nchunks);
+int assemble_begin(mb2_ctx* c, double gf, bool grad, const double* A_in, double* A_out);
+int assemble_finish(mb2_ctx* c, double gf, bool grad, double* A_out);
+double* ghost_ke_buffer(mb2_ctx* c);  // [NE - n_compute][nd][KP]
+// mb2_multigpu.cu
+void free_mg(mb2_ctx* c);
+int mg_pack_chunk(mb2_ctx* c, int64_t e0, int64_t e1, const double* d_KeT_chunk, bool grad, cudaStream_t st);
+int mg_exchange(mb2_ctx* c, bool grad, cudaStream_t after, cudaStream_t before);
 int launch_fp64_peak(mb2_ctx* c, int fma, double* tflops);
 // mb2_tables.cu
 int set_nodes(mb2_ctx* c, const double* x_ref, const double* weights);

@@ -115,10 +115,15 @@ __global__ void k_sort_n2e(int64_t Nn, int nd, const int64_t* __restrict__ ptr, 
 __global__ void k_neighbours(int64_t Nn, int nd, int cap /* pow2 */, const int64_t* __restrict__ ptr,
                              const int32_t* __restrict__ n2e_elem, const int32_t* __restrict__ enodes,
                              int32_t* __restrict__ nnbr, const int64_t* __restrict__ nodeptr,
-                             int32_t* __restrict__ out) {
+                             int32_t* __restrict__ out, const uint8_t* __restrict__ owned) {
   extern __shared__ int32_t s[];  // cap candidates + 1 counter
   __shared__ int s_cnt;
   for (int64_t I = blockIdx.x; I < Nn; I += gridDim.x) {
+    // rows of nodes owned by another rank are not assembled here: empty block row
+    if (owned && !owned[I]) {
+      if (out == nullptr && threadIdx.x == 0) nnbr[I] = 0;
+      continue;
+    }
     const int64_t b = ptr[I];
     const int ne = (int)(ptr[I + 1] - b);
     const int n = ne * nd;
@@ -275,7 +280,7 @@ int build_pattern(mb2_ctx* c) {
   MB2_CUDA(cudaMalloc(&c->d_nnbr, sizeof(int32_t) * (Nn + 1)));
   MB2_CUDA(cudaMemsetAsync(c->d_nnbr, 0, sizeof(int32_t) * (Nn + 1), st));
   k_neighbours<<<grid, 256, smem, st>>>(Nn, nd, cap, c->d_n2e_ptr, c->d_n2e_elem, c->d_enodes, c->d_nnbr, nullptr,
-                                        nullptr);
+                                        nullptr, c->d_owned);
   MB2_CUDA(cudaGetLastError());
   MB2_CUDA(cudaMalloc(&c->d_nodeptr, sizeof(int64_t) * (Nn + 1)));
   rc = exclusive_scan(c, Nn, c->d_nnbr, c->d_nodeptr);
@@ -285,7 +290,7 @@ int build_pattern(mb2_ctx* c) {
   c->nnz = nblocks * dim * dim;
   MB2_CUDA(cudaMalloc(&c->d_nbr, sizeof(int32_t) * nblocks));
   k_neighbours<<<grid, 256, smem, st>>>(Nn, nd, cap, c->d_n2e_ptr, c->d_n2e_elem, c->d_enodes, c->d_nnbr,
-                                        c->d_nodeptr, c->d_nbr);
+                                        c->d_nodeptr, c->d_nbr, c->d_owned);
   MB2_CUDA(cudaGetLastError());
 
   MB2_CUDA(cudaMalloc(&c->d_I, sizeof(int64_t) * (c->NV + 1)));
