@@ -17,10 +17,10 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    uid = [capi.mg_unique_id() if rank == 0 else None]
-    dist.broadcast_object_list(uid, src=0)
     ok_all = True
     for name in ("cube_p2_n3_patch", "cube_p2_n2"):
+        uid = [capi.mg_unique_id() if rank == 0 else None]   # one id per communicator
+        dist.broadcast_object_list(uid, src=0)
         D = load_golden(name)
         dim = D["dim"]
         R = P.rank_problem(D["v_dofs"], dim, D["NV"], P.element_ranges(D["NE"], world), rank)

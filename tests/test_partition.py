@@ -97,3 +97,21 @@ def test_ranges_and_ownership():
         for peer, idx in R["send"].items():
             assert peer < r
     assert (owned == 1).all()
+
+
+@pytest.mark.parametrize("p,spans,world", [(2, (3, 2, 8), 2), (2, (2, 3, 12), 4), (1, (2, 2, 6), 3), (3, (2, 2, 6), 2)])
+def test_slab_problem_equals_generic(p, spans, world):
+    from mimi_b200 import meshgen
+    M = meshgen.patch_connectivity(p, spans)
+    rg = P.element_ranges(M["NE"], world)
+    for r in range(world):
+        G = P.rank_problem(M["v_dofs"], 3, M["NV"], rg, r)
+        S = P.slab_rank_problem(p, spans, world, r)
+        assert S["n_compute"] == G["n_compute"] and np.array_equal(S["local_elems"], G["local_elems"])
+        assert np.array_equal(S["v_dofs"], G["v_dofs"]) and np.array_equal(S["owned"], G["owned"])
+        assert set(S["send"]) == set(G["send"]) and set(S["recv"]) == set(G["recv"])
+        for k in S["send"]:
+            assert np.array_equal(S["send"][k], G["send"][k])
+        for k in S["recv"]:
+            assert np.array_equal(S["recv"][k], G["recv"][k])
+        assert np.array_equal(S["x_ref"], M["x_ref"]) and np.array_equal(S["el_ijk"], M["el_ijk"][G["local_elems"]])
