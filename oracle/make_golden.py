@@ -43,6 +43,11 @@ def main():
                 out["r_" + mat] = D["r"]
                 out["r2_" + mat] = D["r2"]
                 out["A_" + mat] = D["A"]
+            # material with history variables: virgin-state assembly, accumulated state after DomainPostTimeAdvance(u),
+            # and the assembly at 1.5 u on that state
+            D = O.run_ref_dump(mesh, elevate, refine, "j2linear", os.path.join(tmp, "j2linear"), gf=gf)
+            out["r_j2linear"], out["r2_j2linear"], out["A_j2linear"] = D["r"], D["r2"], D["A"]
+            out["state_j2linear"], out["rb_j2linear"], out["Ab_j2linear"] = D["state"], D["r_b"], D["A_b"]
             np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
             print(name, {k: int(v) for k, v in zip(("dim", "nd", "nq", "NE", "NV", "nnz"), out["meta"])})
 

@@ -18,7 +18,31 @@ NEOHOOKEAN, STVK = 0, 1
 
 
 class Material(C.Structure):
-    _fields_ = [("kind", C.c_int), ("lam", C.c_double), ("mu", C.c_double)]
+    _fields_ = [("kind", C.c_int), ("lam", C.c_double), ("mu", C.c_double), ("K", C.c_double), ("G", C.c_double),
+                ("iso", C.c_double), ("kin", C.c_double), ("sigma_y", C.c_double), ("sqrt_6", C.c_double),
+                ("sqrt_3_2", C.c_double), ("sqrt_2_3", C.c_double), ("state", C.c_void_p), ("ns", C.c_int)]
+
+
+J2LINEAR = 2
+J2LINEAR_NS = 19
+# J2Linear test parameters used by oracle/ref_harness.cpp (material "j2linear")
+J2LINEAR_PARAMS = dict(iso=80.0, kin=40.0, sigma_y=2.0)
+
+
+def mat_j2linear(state, young=2100.0, poisson=0.3, iso=80.0, kin=40.0, sigma_y=2.0):
+    """state: float64 array [NE, nq, 19] (modified in place by post_time_advance)."""
+    lam, mu = lame(young, poisson)
+    K = young / (3.0 * (1.0 - (2.0 * poisson)))     # MaterialBase::SetYoungPoisson, materials.cpp:7-14
+    m = Material(J2LINEAR, lam, mu, K, mu, iso, kin, sigma_y, np.sqrt(6.0), np.sqrt(3.0 / 2.0), np.sqrt(2.0 / 3.0),
+                 state.ctypes.data, J2LINEAR_NS)
+    m._keep = state
+    return m
+
+
+def post_time_advance(dim, nd, nq, m, v_dofs, dN_dX, u):
+    rc = lib().orc_post_time_advance(C.c_int(dim), C.c_int(nd), C.c_int(nq), C.c_int64(v_dofs.shape[0]), C.byref(m),
+                                     _p(v_dofs, C.c_int32), _p(dN_dX, C.c_double), _p(u, C.c_double))
+    assert rc == 0
 
 
 def lame(young=2100.0, poisson=0.3):
@@ -53,7 +77,7 @@ def _p(a, t):
 
 def mat(kind, young=2100.0, poisson=0.3):
     lam, mu = lame(young, poisson)
-    return Material(kind, lam, mu)
+    return Material(kind, lam, mu, 0, 0, 0, 0, 0, 0, 0, 0, None, 0)
 
 
 def assemble_residual(dim, nd, nq, m, v_dofs, dN_dX, w, detJ, u):
@@ -124,7 +148,8 @@ def load_dump(d):
     out["dN_dX"] = rd("dN_dX.f64", np.float64, (NE, nq, dim, nd))
     out["dN_dxi"] = rd("dN_dxi.f64", np.float64, (NE, nq, dim, nd))
     out["N"] = rd("N.f64", np.float64, (NE, nq, nd))
-    for k in ("x_ref", "u", "r", "r2", "mass", "A"):
+    out["state"] = rd("state.f64", np.float64, (NE, nq, 19))
+    for k in ("x_ref", "u", "r", "r2", "mass", "A", "r_b", "A_b"):
         out[k] = rd(k + ".f64", np.float64)
     return out
 

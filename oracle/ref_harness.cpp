@@ -5,7 +5,10 @@
 //
 //   mimi_ref dump <mesh> <elevate> <refine> <material> <nthreads> <gf> <u.bin|-> <outdir> [lite]
 //   mimi_ref time <mesh> <elevate> <refine> <material> <nthreads> <reps> [warmup reps, untimed]
-// material: neohookean | stvk  (E=2100, nu=0.3, rho=1: tests/test_nonlinear_solid.py:59-62)
+// material: neohookean | stvk | j2linear  (E=2100, nu=0.3, rho=1: tests/test_nonlinear_solid.py:59-62;
+//           j2linear adds isotropic_hardening=80, kinematic_hardening=40, sigma_y=<MIMI_REF_SIGMA_Y or 2.0>)
+// For materials with history the dump continues: DomainPostTimeAdvance(u) -> state.f64 [NE][nq][19]
+// (plastic_strain 9, beta 9, accumulated), then u_b = 1.5 u -> r_b.f64, A_b.f64 on the accumulated state.
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
@@ -69,6 +72,14 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
                                                      mfem::Ordering::byVDIM);
   if (material == "neohookean") s.mat = std::make_shared<mimi::materials::CompressibleOgdenNeoHookean>();
   else if (material == "stvk") s.mat = std::make_shared<mimi::materials::StVenantKirchhoff>();
+  else if (material == "j2linear") {
+    auto m = std::make_shared<mimi::materials::J2Linear>();
+    m->isotropic_hardening_ = 80.0;
+    m->kinematic_hardening_ = 40.0;
+    const char* sy = std::getenv("MIMI_REF_SIGMA_Y");
+    m->sigma_y_ = sy ? std::atof(sy) : 2.0;
+    s.mat = m;
+  }
   else { std::fprintf(stderr, "unknown material %s\n", material.c_str()); std::exit(2); }
   s.mat->density_ = 1.0;
   s.mat->viscosity_ = -1.0;
@@ -176,6 +187,27 @@ int main(int argc, char** argv) {
     s.integ->AddDomainResidualAndGrad(u, gf, r2, A);
     dump(out, "r2.f64", r2.GetData(), (size_t)NV);
     dump(out, "A.f64", A.GetData(), (size_t)nnz);
+    if (material == "j2linear") {
+      s.integ->DomainPostTimeAdvance(u);
+      using St = mimi::materials::J2Linear::State;
+      std::vector<double> st((size_t)NE * nq * 19, 0.0);
+      for (int e = 0; e < NE; ++e)
+        for (int q = 0; q < nq; ++q) {
+          const auto& ms = *eqd[e].GetQuadData()[q].material_state;
+          double* o = &st[((size_t)e * nq + q) * 19];
+          std::memcpy(o, ms.matrices[St::k_plastic_strain].GetData(), sizeof(double) * dim * dim);
+          std::memcpy(o + 9, ms.matrices[St::k_beta].GetData(), sizeof(double) * dim * dim);
+          o[18] = ms.scalars[St::k_accumulated_plastic_strain];
+        }
+      dump(out, "state.f64", st.data(), st.size());
+      mfem::Vector ub(u), rb(NV);
+      ub *= 1.5;
+      rb = 0.0;
+      mfem::SparseMatrix Ab(s.mass->SpMat());
+      s.integ->AddDomainResidualAndGrad(ub, gf, rb, Ab);
+      dump(out, "r_b.f64", rb.GetData(), (size_t)NV);
+      dump(out, "A_b.f64", Ab.GetData(), (size_t)nnz);
+    }
     std::ofstream m(out + "/meta.json");
     m << "{\"NV\": " << NV << ", \"NE\": " << NE << ", \"nnz\": " << nnz << ", \"nd\": " << nd << ", \"nq\": " << nq
       << ", \"dim\": " << dim << ", \"tdof\": " << tdof << ", \"gf\": " << gf << ", \"nthreads\": " << nthreads

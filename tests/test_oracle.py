@@ -40,3 +40,24 @@ def test_oracle_vs_live_reference_4096_free():
     r2, A = O.assemble_residual_and_grad(3, 27, 64, m, D["v_dofs"], aid, D["dN_dX"], D["w"], D["detJ"], D["u"], 0.7,
                                          D["mass"])
     assert np.array_equal(r2, D["r2"]) and np.array_equal(A, D["A"])
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_j2linear_with_history_bit_exact(name):
+    """J2Linear (materials.hpp:138-249): virgin-state residual/tangent, the history variables committed by
+    DomainPostTimeAdvance (nonlinear_solid.cpp:179-199), and the assembly at 1.5 u on that history."""
+    D = load_golden(name)
+    S = np.zeros((D["NE"], D["nq"], O.J2LINEAR_NS))
+    m = O.mat_j2linear(S)
+    args = (D["dim"], D["nd"], D["nq"], m, D["v_dofs"])
+    r = O.assemble_residual(*args, D["dN_dX"], D["w"], D["detJ"], D["u"])
+    assert np.array_equal(r, D["r_j2linear"])
+    r2, A = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], D["u"], D["gf"], D["mass"])
+    assert np.array_equal(r2, D["r2_j2linear"]) and np.array_equal(A, D["A_j2linear"])
+    assert not S.any()                                   # evaluation never touches the history
+    O.post_time_advance(D["dim"], D["nd"], D["nq"], m, D["v_dofs"], D["dN_dX"], D["u"])
+    assert np.array_equal(S, D["state_j2linear"])
+    y = (S[:, :, 18] > 0).mean()
+    assert 0.05 < y < 0.999, y                           # both branches of the yield check are exercised
+    rb, Ab = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], 1.5 * D["u"], D["gf"], D["mass"])
+    assert np.array_equal(rb, D["rb_j2linear"]) and np.array_equal(Ab, D["Ab_j2linear"])
