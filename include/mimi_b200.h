@@ -37,7 +37,9 @@ enum {
 /* material ids: src/mimi/materials/materials.hpp (Name()) */
 enum {
   MB2_MAT_NEOHOOKEAN = 0, /* CompressibleOgdenNeoHookean, materials.cpp:96-118; params {lambda, mu} */
-  MB2_MAT_STVK = 1        /* StVenantKirchhoff,           materials.cpp:73-94;  params {lambda, mu} */
+  MB2_MAT_STVK = 1,       /* StVenantKirchhoff,           materials.cpp:73-94;  params {lambda, mu} */
+  MB2_MAT_J2LINEAR = 2    /* J2Linear, materials.hpp:142-249; params {lambda, mu, K, G, isotropic_hardening,
+                             kinematic_hardening, sigma_y}; 19 history doubles per quadrature point */
 };
 
 /* tangent modes */
@@ -100,6 +102,18 @@ int mb2_get_A_ids_i32(mb2_ctx* ctx, int32_t* A_ids);
 
 /* MaterialBase parameters (materials.hpp:24-40). */
 int mb2_set_material(mb2_ctx* ctx, int kind, const double* params, int nparams);
+
+/* History variables (QuadData::material_state, precomputed.hpp:58-69; MaterialBase::CreateState). They live on the
+ * device as [NE][nq][mb2_state_size] doubles -- J2Linear: plastic_strain[9] (column-major dim x dim in the first
+ * dim*dim slots), beta[9], accumulated_plastic_strain -- allocated and initialised by mb2_set_material (call it after
+ * mb2_set_connectivity). mb2_set_state(NULL) re-initialises; get/set are for checkpointing and tests. */
+int mb2_state_size(mb2_ctx* ctx);
+int mb2_get_state(mb2_ctx* ctx, double* state);
+int mb2_set_state(mb2_ctx* ctx, const double* state);
+/* Commits the history variables at the converged u. Replaces NonlinearSolid::DomainPostTimeAdvance
+ * (nonlinear_solid.cpp:179-199) + MaterialBase::Accumulate. No-op for stateless materials. */
+int mb2_post_time_advance(mb2_ctx* ctx, const double* u);
+int mb2_post_time_advance_device(mb2_ctx* ctx); /* on the resident u */
 
 /* ---- the hot path, host-buffer form (what the integrator virtuals forward to) ------------------- */
 /* r += R(u).  Replaces NonlinearSolid::AddDomainResidual (nonlinear_solid.cpp:151-160). */

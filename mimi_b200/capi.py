@@ -13,7 +13,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmimi_b200.so")
 
-MB2_MAT_NEOHOOKEAN, MB2_MAT_STVK = 0, 1
+MB2_MAT_NEOHOOKEAN, MB2_MAT_STVK, MB2_MAT_J2LINEAR = 0, 1, 2
 
 # every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
@@ -24,7 +24,8 @@ SYMBOLS = [
     "mb2_get_r", "mb2_get_A", "mb2_assemble_residual_device", "mb2_assemble_residual_and_grad_device",
     "mb2_device_pointers", "mb2_last_timing_ms", "mb2_last_launch_count", "mb2_sync", "mb2_measure_fp64_peak", "mb2_set_option", "mb2_host_register", "mb2_host_unregister", "mb2_plan_info", "mb2_set_partition", "mb2_mg_set_send", "mb2_mg_set_recv", "mb2_mg_unique_id",
     "mb2_mg_init_nccl", "mb2_mg_set_manual", "mb2_mg_begin", "mb2_mg_export_send", "mb2_mg_import_recv", "mb2_mg_finish",
-    "mb2_mg_ke_doubles",
+    "mb2_mg_ke_doubles", "mb2_state_size", "mb2_get_state", "mb2_set_state", "mb2_post_time_advance",
+    "mb2_post_time_advance_device",
 ]
 
 
@@ -142,6 +143,22 @@ class Context:
     def set_material(self, kind, params):
         p = np.ascontiguousarray(params, np.float64)
         self._ck(self.lib.mb2_set_material(self.h, kind, _dp(p), p.size))
+
+    # ---- history variables (materials with state)
+    def state_size(self):
+        return self.lib.mb2_state_size(self.h)
+
+    def get_state(self):
+        st = np.empty((self.NE, self.nq, self.state_size()))
+        self._ck(self.lib.mb2_get_state(self.h, _dp(st)))
+        return st
+
+    def set_state(self, state=None):
+        st = None if state is None else np.ascontiguousarray(state, np.float64)
+        self._ck(self.lib.mb2_set_state(self.h, _dp(st)))
+
+    def post_time_advance(self, u):
+        self._ck(self.lib.mb2_post_time_advance(self.h, _dp(u)))
 
     # ---- host-buffer hot path
     def add_domain_residual(self, u, r):

@@ -1,5 +1,6 @@
 // C ABI of libmimi_b200 (include/mimi_b200.h): context lifetime, uploads, hand-backs and the
 // host-buffer forms of the integrator entry points.
+#include <cmath>
 #include <cstring>
 #include <new>
 
@@ -25,7 +26,7 @@ static void free_problem(mb2_ctx* c) {
   dfree(c->d_vdofs); dfree(c->d_enodes); dfree(c->d_dNdX); dfree(c->d_wdetJ); dfree(c->d_N); dfree(c->d_xref); dfree(c->d_nodew);
   dfree(c->d_n2e_ptr); dfree(c->d_n2e_elem); dfree(c->d_n2e_loc); dfree(c->d_nnbr); dfree(c->d_nodeptr);
   dfree(c->d_nbr); dfree(c->d_rank); dfree(c->d_I); dfree(c->d_J);
-  dfree(c->d_u); dfree(c->d_r); dfree(c->d_A); dfree(c->d_Re);
+  dfree(c->d_u); dfree(c->d_r); dfree(c->d_A); dfree(c->d_Re); dfree(c->d_state);
   mb2::free_plan(c);
   mb2::free_mg(c);
   dfree(c->d_owned);
@@ -144,14 +145,73 @@ int mb2_download_quad_tables(mb2_ctx* c, double* dN_dX, double* w_detJ) {
   return MB2_OK;
 }
 
+// History variables as MaterialBase::CreateState initialises them (materials.cpp:120-133): all zero for J2Linear.
+static int alloc_state(mb2_ctx* c) {
+  dfree(c->d_state);
+  c->ns = mb2::mat_state_size(c->mat_kind);
+  if (c->ns == 0 || c->NE == 0) return MB2_OK;
+  const size_t bytes = sizeof(double) * (size_t)c->NE * c->nq * c->ns;
+  MB2_CUDA(cudaMalloc(&c->d_state, bytes));
+  MB2_CUDA(cudaMemsetAsync(c->d_state, 0, bytes, c->stream));
+  return MB2_OK;
+}
+
 int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
   CHECK_CTX(c);
-  REQUIRE(kind == MB2_MAT_NEOHOOKEAN || kind == MB2_MAT_STVK, "unknown material kind");
+  REQUIRE(kind == MB2_MAT_NEOHOOKEAN || kind == MB2_MAT_STVK || kind == MB2_MAT_J2LINEAR, "unknown material kind");
   REQUIRE(params && nparams >= 2, "material needs {lambda, mu}");
+  mb2::MatP m;
+  m.lambda = params[0];
+  m.mu = params[1];
+  if (kind == MB2_MAT_J2LINEAR) {
+    REQUIRE(nparams >= 7, "J2Linear needs {lambda, mu, K, G, isotropic_hardening, kinematic_hardening, sigma_y}");
+    REQUIRE(c->NE > 0, "call mb2_set_connectivity before setting a material with history variables");
+    m.K = params[2]; m.G = params[3]; m.iso = params[4]; m.kin = params[5]; m.sigma_y = params[6];
+    // materials.hpp:163-166: const members initialised with std::sqrt
+    m.sqrt_6 = std::sqrt(6.0);
+    m.sqrt_3_2 = std::sqrt(3.0 / 2.0);
+    m.sqrt_2_3 = std::sqrt(2.0 / 3.0);
+  }
+  const bool realloc_state = (kind != c->mat_kind) || (mb2::mat_state_size(kind) && !c->d_state);
   c->mat_kind = kind;
-  c->lambda = params[0];
-  c->mu = params[1];
+  c->mp = m;
+  if (realloc_state) {
+    MB2_CUDA(cudaSetDevice(c->device));
+    return alloc_state(c);
+  }
   return MB2_OK;
+}
+
+int mb2_state_size(mb2_ctx* c) { return c ? c->ns : 0; }
+int mb2_get_state(mb2_ctx* c, double* state) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_state && state, "material has no history variables");
+  MB2_CUDA(cudaMemcpyAsync(state, c->d_state, sizeof(double) * (size_t)c->NE * c->nq * c->ns, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+int mb2_set_state(mb2_ctx* c, const double* state) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_state, "material has no history variables");
+  if (state) MB2_CUDA(cudaMemcpyAsync(c->d_state, state, sizeof(double) * (size_t)c->NE * c->nq * c->ns, cudaMemcpyHostToDevice, c->stream));
+  else return alloc_state(c);
+  return MB2_OK;
+}
+
+int mb2_post_time_advance_device(mb2_ctx* c) {
+  CHECK_CTX(c);
+  REQUIRE(c->d_dNdX, "quadrature tables missing");
+  REQUIRE(c->mat_kind >= 0, "material not set");
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::launch_post_time_advance(c);
+}
+int mb2_post_time_advance(mb2_ctx* c, const double* u) {
+  CHECK_CTX(c);
+  REQUIRE(u, "null vector");
+  int rc;
+  if ((rc = mb2_set_u(c, u))) return rc;
+  if ((rc = mb2_post_time_advance_device(c))) return rc;
+  return mb2_sync(c);
 }
 
 int mb2_build_pattern(mb2_ctx* c, int64_t* nnz) {

@@ -23,7 +23,8 @@ struct ElemArgs {
   const double* __restrict__ u;
   double* __restrict__ Re;
   double* __restrict__ KeT;
-  double lambda, mu;
+  MatP mp;
+  const double* __restrict__ state;  // [NE][nq][NS] history variables (nullptr for stateless materials)
 };
 
 template <int DIM, int ND, int NQ>
@@ -47,7 +48,7 @@ struct ElemCfg {
 template <int DIM, int ND, int NQ, int MAT, bool GRAD, int MINB>
 __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel(const ElemArgs g) {
   using Cfg = ElemCfg<DIM, ND, NQ>;
-  constexpr int TD = Cfg::TD, DD = Cfg::DD, NT = Cfg::NT;
+  constexpr int TD = Cfg::TD, DD = Cfg::DD, NT = Cfg::NT, NS = mat_state_size(MAT);
   extern __shared__ __align__(16) double smem[];
   double* sdN = smem + Cfg::OFF_DN;
   double* sFb = smem + Cfg::OFF_FB;
@@ -87,7 +88,7 @@ __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel
         }
 #pragma unroll
       for (int i = 0; i < DIM; i++) F[i + DIM * i] += 1.0;
-      material_pk1<DIM, MAT>(g.lambda, g.mu, F, P);
+      material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + t) * NS : nullptr, P);
       const double aq = swd[t];
 #pragma unroll
       for (int n = 0; n < DD; n++) {
@@ -142,7 +143,7 @@ __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel
               const double fnew = (i == j) ? drow[j] + 1.0 : drow[j];
               F[i + DIM * j] = (i == c) ? fnew : sFb[q * DD + i + DIM * j];
             }
-          material_pk1<DIM, MAT>(g.lambda, g.mu, F, P);
+          material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + q) * NS : nullptr, P);
           const double aq = swd[q];
           // mfem::AddMult_a_ABt(a, dN_dX, P, R)  (densemat.cpp:3002-3015)
 #pragma unroll
@@ -210,7 +211,8 @@ template <int DIM, int ND, int NQ, int MAT>
 __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
   using Cfg = Elem2Cfg<DIM, ND, NQ>;
   constexpr int TD = Cfg::TD, DD = Cfg::DD, NM = Cfg::NM, NT = Cfg::NT, QC = Cfg::QC, NCH = Cfg::NCH, NDP = Cfg::NDP,
-                NB = Cfg::NB, NBP = Cfg::NBP, TI = Cfg::TI, TC = Cfg::TC, LI = Cfg::LI, LC = Cfg::LC, KP = Cfg::KP;
+                NB = Cfg::NB, NBP = Cfg::NBP, TI = Cfg::TI, TC = Cfg::TC, LI = Cfg::LI, LC = Cfg::LC, KP = Cfg::KP,
+                NS = mat_state_size(MAT);
   extern __shared__ __align__(16) double smem[];
   double* sdN = smem + Cfg::OFF_DN;
   double* sFb = smem + Cfg::OFF_FB;
@@ -310,7 +312,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
               if (i == c1) F[i + DIM * j] = fnew;
           }
         }
-        material_pk1<DIM, MAT>(g.lambda, g.mu, F, P);
+        material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + q1) * NS : nullptr, P);
         const double aq = swd[q1];
         double* o = sbc + qs1 * (DIM * NBP) + m1 * DIM;
         // bjk = a * P(j,k)   (densemat.cpp:3008)
@@ -396,6 +398,63 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
     }
     __syncthreads();
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// History commit: NonlinearSolid::DomainPostTimeAdvance (nonlinear_solid.cpp:179-199) = ElementResidual<true>:
+// per quadrature point ComputeF, then MaterialBase::Accumulate. One thread per (element, qp); the F dot products
+// keep MultAtB's k order. HBM-bound: reads dN_dX once (tdof doubles per qp) and read-modify-writes NS doubles.
+// ---------------------------------------------------------------------------------------------
+template <int DIM, int MAT>
+__global__ void __launch_bounds__(128) post_time_advance_kernel(int nd, int nq, int64_t n_elem,
+                                                                const int32_t* __restrict__ vdofs,
+                                                                const double* __restrict__ dNdX,
+                                                                const double* __restrict__ u, const MatP mp,
+                                                                double* __restrict__ state) {
+  constexpr int DD = DIM * DIM, NS = mat_state_size(MAT);
+  const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (idx >= n_elem * nq) return;
+  const int64_t e = idx / nq;
+  const int tdof = DIM * nd;
+  const int32_t* vd = vdofs + e * tdof;
+  const double* dN = dNdX + idx * tdof;
+  double F[DD];
+#pragma unroll
+  for (int j = 0; j < DIM; j++)
+#pragma unroll
+    for (int i = 0; i < DIM; i++) {
+      double d = 0.0;
+      for (int k = 0; k < nd; k++) d += u[vd[k + i * nd]] * dN[k + j * nd];
+      F[i + DIM * j] = d;
+    }
+#pragma unroll
+  for (int i = 0; i < DIM; i++) F[i + DIM * i] += 1.0;
+  if (MAT == MAT_J2LINEAR) {
+    double st[NS > 0 ? NS : 1];
+    double* g = state + idx * NS;
+#pragma unroll
+    for (int i = 0; i < NS; i++) st[i] = g[i];
+    j2linear_plastic_stress<DIM, true>(mp, F, st, nullptr);
+#pragma unroll
+    for (int i = 0; i < NS; i++) g[i] = st[i];
+  }
+}
+
+int launch_post_time_advance(mb2_ctx* c) {
+  if (!c->d_state) return MB2_OK;  // stateless material: MaterialBase::Accumulate is never reached (nullptr state)
+  const int64_t n = c->n_compute * c->nq;
+  const unsigned grid = (unsigned)((n + 127) / 128);
+  if (c->mat_kind == MAT_J2LINEAR) {
+    if (c->dim == 3)
+      post_time_advance_kernel<3, MAT_J2LINEAR><<<grid, 128, 0, c->stream>>>(c->nd, c->nq, c->n_compute, c->d_vdofs, c->d_dNdX,
+                                                                             c->d_u, c->mp, c->d_state);
+    else
+      post_time_advance_kernel<2, MAT_J2LINEAR><<<grid, 128, 0, c->stream>>>(c->nd, c->nq, c->n_compute, c->d_vdofs, c->d_dNdX,
+                                                                             c->d_u, c->mp, c->d_state);
+  }
+  MB2_CUDA(cudaGetLastError());
+  c->last_launches = 1;
+  return MB2_OK;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -521,6 +580,7 @@ static int launch_element_mat(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   switch (c->mat_kind) {
     case MAT_NEOHOOKEAN: return launch_element<DIM, ND, NQ, MAT_NEOHOOKEAN, GRAD, MINB>(c, a, st);
     case MAT_STVK: return launch_element<DIM, ND, NQ, MAT_STVK, GRAD, MINB>(c, a, st);
+    case MAT_J2LINEAR: return launch_element<DIM, ND, NQ, MAT_J2LINEAR, GRAD, MINB>(c, a, st);
   }
   c->err = "material not set or unsupported";
   return MB2_ERR_UNSUPPORTED;
@@ -533,6 +593,7 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
     switch (c->mat_kind) {
       case MAT_NEOHOOKEAN: return launch_element_fd<3, 27, 64, MAT_NEOHOOKEAN>(c, a, st);
       case MAT_STVK: return launch_element_fd<3, 27, 64, MAT_STVK>(c, a, st);
+      case MAT_J2LINEAR: return launch_element_fd<3, 27, 64, MAT_J2LINEAR>(c, a, st);
     }
   }
   if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a, st);
@@ -555,8 +616,8 @@ static ElemArgs make_args(mb2_ctx* c, int64_t e0, int64_t e1, double* KeT) {
   a.u = c->d_u;
   a.Re = c->d_Re;
   a.KeT = KeT;
-  a.lambda = c->lambda;
-  a.mu = c->mu;
+  a.mp = c->mp;
+  a.state = c->d_state;
   return a;
 }
 

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "../../include/mimi_b200.h"
+#include "mb2_math.cuh"
 
 // Multi-GPU exchange state: which element matrices leave to / arrive from which peer (mb2_multigpu.cu).
 struct MgPeer {
@@ -46,7 +47,9 @@ struct mb2_ctx {
   bool last_grad = false;
   int elem_variant = 0;  // 0 = default kernels, 1 = force the one-thread-per-dof FD kernel (A/B tests)
   int mat_kind = -1;
-  double lambda = 0, mu = 0;
+  mb2::MatP mp;
+  int ns = 0;                // history doubles per quadrature point (0 = stateless material)
+  double* d_state = nullptr; // [NE][nq][ns]
 
   // partition (multi-GPU): elements [0, n_compute) are computed here, [n_compute, NE) are ghosts whose
   // element matrices arrive from other ranks; only rows of owned nodes are assembled
@@ -98,6 +101,7 @@ int build_pattern(mb2_ctx* c);
 int expand_A_ids(mb2_ctx* c, int32_t* d_out);
 // mb2_assembly.cu
 int launch_residual(mb2_ctx* c);
+int launch_post_time_advance(mb2_ctx* c);
 int launch_residual_and_grad(mb2_ctx* c, double gf, const double* A_in, double* A_out);
 void free_plan(mb2_ctx* c);
 int collect_timing(mb2_ctx* c, float* out3);

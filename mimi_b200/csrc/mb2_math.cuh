@@ -6,13 +6,17 @@
 
 namespace mb2 {
 
-enum : int { MAT_NEOHOOKEAN = 0, MAT_STVK = 1 };
+enum : int { MAT_NEOHOOKEAN = 0, MAT_STVK = 1, MAT_J2LINEAR = 2 };
 
-struct MaterialParams {
-  int kind;
-  double lambda;
-  double mu;
+// MaterialBase parameters (materials.hpp:24-40) plus the J2Linear members (materials.hpp:147-166); the sqrt
+// constants are computed on the host by std::sqrt exactly like the reference's member initialisers.
+struct MatP {
+  double lambda = 0, mu = 0;
+  double K = 0, G = 0, iso = 0, kin = 0, sigma_y = 0, sqrt_6 = 0, sqrt_3_2 = 0, sqrt_2_3 = 0;
 };
+
+// per-quadrature-point history doubles: J2Linear = plastic_strain[9], beta[9], accumulated_plastic_strain
+__host__ __device__ constexpr int mat_state_size(int mat) { return mat == MAT_J2LINEAR ? 19 : 0; }
 
 // mfem::kernels::MultABt on DIM x DIM operands (third_party/mfem/linalg/kernels.hpp:363-384):
 // C zeroed, then k outer, j, i inner: C(i,j) += A(i,k) * B(j,k).
@@ -99,13 +103,88 @@ __device__ __forceinline__ void inverse_small(const double* A, double* B) {
 #undef MB2_b
 }
 
-// First Piola-Kirchhoff stress P(F). MAT is a compile-time material id.
+// J2Linear::PlasticStress<ACC> (src/mimi/materials/materials.hpp:187-238) on st = {plastic_strain[9], beta[9],
+// accumulated_plastic_strain}. ACC == false: sigma out, state read-only (EvaluateCauchy); ACC == true: the history
+// is committed (Accumulate, materials.hpp:245-248). Helpers in the reference's order: ElasticStrain
+// (material_utils.hpp:60-85: copy F, Symmetrize, -I, -plastic strain), Dev (:22-56), Norm (:117-127).
+template <int DIM, bool ACC>
+__device__ __forceinline__ void j2linear_plastic_stress(const MatP& m, const double* F, double* st, double* sigma) {
+  constexpr int DD = DIM * DIM;
+  double eps[DD], s[DD], eta[DD];
+  double* plastic_strain = st;
+  double* beta = st + 9;
+#pragma unroll
+  for (int i = 0; i < DD; i++) eps[i] = F[i];
+#pragma unroll
+  for (int i = 0; i < DIM; i++)
+#pragma unroll
+    for (int j = 0; j < i; j++) {
+      const double a = 0.5 * (eps[i * DIM + j] + eps[j * DIM + i]);
+      eps[j * DIM + i] = eps[i * DIM + j] = a;
+    }
+#pragma unroll
+  for (int i = 0; i < DIM; i++) eps[(DIM + 1) * i] -= 1.;
+#pragma unroll
+  for (int i = 0; i < DD; i++) eps[i] -= plastic_strain[i];
+  double tr = 0.0;
+#pragma unroll
+  for (int i = 0; i < DIM; i++) tr += eps[i + i * DIM];
+  const double p = m.K * tr;
+  const double factor = 2.0 * m.G;
+  if (DIM == 2) {
+    const double trd = (eps[0] + eps[3]) / 2.0;
+    s[0] = (eps[0] - trd) * factor;
+    s[1] = eps[1] * factor;
+    s[2] = eps[2] * factor;
+    s[3] = (eps[3] - trd) * factor;
+  } else {
+    const double trd = (eps[0] + eps[4] + eps[8]) / 3.0;
+#pragma unroll
+    for (int i = 0; i < DD; i++) s[i] = ((i % (DIM + 1) == 0) ? (eps[i] - trd) : eps[i]) * factor;
+  }
+#pragma unroll
+  for (int i = 0; i < DD; i++) eta[i] = s[i] + -1. * beta[i];  // mfem::Add(s, beta, -1., eta)
+  double a = 0.0;
+#pragma unroll
+  for (int i = 0; i < DD; i++) a += eta[i] * eta[i];
+  const double eta_norm = sqrt(a);
+  const double q = m.sqrt_3_2 * eta_norm;
+  const double phi = q - (m.sigma_y + m.iso * st[18]);
+  if (phi > 0.) {
+    const double inc = phi / (3. * m.G + m.kin + m.iso);
+    const double inv = 1. / eta_norm;
+#pragma unroll
+    for (int i = 0; i < DD; i++) eta[i] *= inv;
+    if (!ACC) {
+      const double c = -m.sqrt_6 * m.G * inc;
+#pragma unroll
+      for (int i = 0; i < DD; i++) s[i] += c * eta[i];
+    } else {
+      st[18] += inc;
+      const double c1 = m.sqrt_3_2 * inc;
+#pragma unroll
+      for (int i = 0; i < DD; i++) plastic_strain[i] += c1 * eta[i];
+      const double c2 = m.sqrt_2_3 * m.kin * inc;
+#pragma unroll
+      for (int i = 0; i < DD; i++) beta[i] += c2 * eta[i];
+    }
+  }
+  if (!ACC) {
+#pragma unroll
+    for (int i = 0; i < DD; i++) sigma[i] = s[i] + p * ((i % (DIM + 1) == 0) ? 1.0 : 0.0);
+  }
+}
+
+// First Piola-Kirchhoff stress P(F). MAT is a compile-time material id; st = this quadrature point's history
+// (read-only here; nullptr for stateless materials).
 //  NeoHookean: CompressibleOgdenNeoHookean::EvaluateCauchy (src/mimi/materials/materials.cpp:96-118)
 //              followed by MaterialBase::EvaluatePK1 (materials.cpp:60-71).
 //  StVK:       StVenantKirchhoff::EvaluatePK1 (materials.cpp:73-94).
+//  J2Linear:   J2Linear::EvaluateCauchy (materials.hpp:240-243) + MaterialBase::EvaluatePK1.
 template <int DIM, int MAT>
-__device__ __forceinline__ void material_pk1(const double lambda, const double mu, const double* F, double* P) {
+__device__ __forceinline__ void material_pk1(const MatP& m, const double* F, const double* st, double* P) {
   constexpr int DD = DIM * DIM;
+  const double lambda = m.lambda, mu = m.mu;
   if (MAT == MAT_STVK) {
     double C[DD], E[DD], S[DD];
     mult_AtB<DIM>(F, F, C);
@@ -129,13 +208,24 @@ __device__ __forceinline__ void material_pk1(const double lambda, const double m
   }
   double B[DD], sig[DD], Finv[DD];
   const double det_F = det_small<DIM>(F);
-  const double mu_over_det_F = mu / det_F;
-  mult_ABt<DIM>(F, F, B);
-  const double beta = -mu_over_det_F + lambda * (det_F - 1.);
+  if (MAT == MAT_J2LINEAR) {
+    double stl[19];
 #pragma unroll
-  for (int i = 0; i < DD; i++) {
-    const double Ii = (i % (DIM + 1) == 0) ? 1.0 : 0.0;
-    sig[i] = mu_over_det_F * B[i] + beta * Ii;
+    for (int i = 0; i < DD; i++) {
+      stl[i] = st[i];
+      stl[9 + i] = st[9 + i];
+    }
+    stl[18] = st[18];
+    j2linear_plastic_stress<DIM, false>(m, F, stl, sig);
+  } else {
+    const double mu_over_det_F = mu / det_F;
+    mult_ABt<DIM>(F, F, B);
+    const double beta = -mu_over_det_F + lambda * (det_F - 1.);
+#pragma unroll
+    for (int i = 0; i < DD; i++) {
+      const double Ii = (i % (DIM + 1) == 0) ? 1.0 : 0.0;
+      sig[i] = mu_over_det_F * B[i] + beta * Ii;
+    }
   }
   inverse_small<DIM>(F, Finv);
   mult_ABt<DIM>(sig, Finv, P);

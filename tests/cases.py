@@ -10,7 +10,7 @@ from oracle import oracle_py as O
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "quad_p2_n4", "cube_p2_n3_patch"]
-MATS = {"neohookean": 0, "stvk": 1}
+MATS = {"neohookean": 0, "stvk": 1, "j2linear": 2}
 
 
 def load_golden(name):
@@ -42,5 +42,10 @@ def setup_ctx(ctx, D, material):
     ctx.upload_quad_tables(D["dN_dX"], D["w"], D["detJ"])
     ctx.build_pattern()
     lam, mu = O.lame()
-    ctx.set_material(MATS[material], [lam, mu])
+    if material == "j2linear":
+        K = 2100.0 / (3.0 * (1.0 - (2.0 * 0.3)))  # MaterialBase::SetYoungPoisson, materials.cpp:7-14
+        P = O.J2LINEAR_PARAMS
+        ctx.set_material(MATS[material], [lam, mu, K, mu, P["iso"], P["kin"], P["sigma_y"]])
+    else:
+        ctx.set_material(MATS[material], [lam, mu])
     return ctx
