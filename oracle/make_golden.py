@@ -24,6 +24,34 @@ CASES = {
 }
 
 
+# contact fixtures: name: (mesh writer, elevate, refine, gf, boundary attribute, penalty, rigid body spec)
+CONTACT_CASES = {
+    "contact_cube_p2_n2_plane": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 1, 1, 0.7, 2, 1e5,
+                                 ("plane", [0, 0, 1.0, 0, 1, 0, 1, 0, 0, -10, 10])),
+    "contact_cube_p2_n4_sphere": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 1, 2, 0.7, 2, 1e5,
+                                  ("sphere", [0.5, 0.5, 1.9996, 1.0])),
+    "contact_quad_p3_n4_sphere": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 2, 2, 0.3, 2, 1e5,
+                                  ("sphere", [1.0, 1.9995, 1.0])),
+    "contact_quad_p2_n4_plane_clamped": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 1, 2, 0.3, 2, 1e5,
+                                         ("plane", [0.3, 1.0002, 1, 0, 0.0, 1.0])),
+}
+
+
+def contact_main():
+    for name, (writer, elevate, refine, gf, attr, penalty, spec) in CONTACT_CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            mesh = os.path.join(tmp, "m.mesh")
+            writer(mesh)
+            D = O.run_ref_contact(mesh, elevate, refine, os.path.join(tmp, "c"), attr, penalty, spec, gf=gf)
+            out = {k: v for k, v in D.items() if isinstance(v, np.ndarray)}
+            out["meta"] = np.array([D["dim"], D["NF"], D["ndf"], D["nqf"], D["NV"], D["nnz"], D["n_marked_nodes"]], np.int64)
+            out["gf"], out["penalty"] = np.float64(gf), np.float64(penalty)
+            out["body_kind"] = np.array(spec[0])
+            out["body_params"] = np.array(spec[1], np.float64)
+            np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+            print(name, out["meta"])
+
+
 def main():
     assert O.have_ref(), "build oracle/_ref first: make -f oracle/Makefile.ref -j8"
     os.makedirs(OUT, exist_ok=True)
@@ -53,4 +81,6 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "contact" not in sys.argv[1:]:
+        main()
+    contact_main()

@@ -53,9 +53,9 @@ def lame(young=2100.0, poisson=0.3):
 
 
 def build_oracle(force=False):
-    src = os.path.join(HERE, "mimi_oracle.c")
-    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(src):
-        subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", LIB, src, "-lm"])
+    srcs = [os.path.join(HERE, "mimi_oracle.c"), os.path.join(HERE, "mimi_oracle_contact.c")]
+    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(x) for x in srcs):
+        subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", LIB] + srcs + ["-lm"])
     return LIB
 
 
@@ -68,6 +68,7 @@ def lib():
         build_oracle()
         _lib = C.CDLL(LIB)
         _lib.orc_build_pattern.restype = C.c_int64
+        _lib.orc_contact_gap_norm.restype = C.c_double
     return _lib
 
 
@@ -186,3 +187,128 @@ def element_matrices(dim, nd, nq, m, v_dofs, dN_dX, w, detJ, u, elems):
                                         _p(np.ascontiguousarray(detJ[e]), C.c_double), _p(R[x], C.c_double),
                                         _p(Rf, C.c_double), _p(K[x], C.c_double))
     return R, K
+
+
+# ---------------------------------------------------------------- mortar contact (oracle/mimi_oracle_contact.c)
+RIGID_PLANE, RIGID_SPHERE = 0, 1
+
+
+class Rigid(C.Structure):
+    _fields_ = [("kind", C.c_int), ("dim", C.c_int), ("p", C.c_double * 16)]
+
+
+def rigid_plane(dim, o, t0, t1=None, lo=-1e300, hi=1e300):
+    p = np.zeros(16)
+    p[0:dim] = o
+    p[3:3 + dim] = t0
+    if t1 is not None:
+        p[6:6 + dim] = t1
+    p[9], p[10] = lo, hi
+    return Rigid(RIGID_PLANE, dim, (C.c_double * 16)(*p))
+
+
+def rigid_sphere(dim, c, R):
+    p = np.zeros(16)
+    p[0:dim] = c
+    p[3] = R
+    return Rigid(RIGID_SPHERE, dim, (C.c_double * 16)(*p))
+
+
+def rigid_from_spec(dim, spec):
+    """spec = ("plane", [o..., t0..., (t1...), lo, hi]) or ("sphere", [c..., R]) -- the harness' command line."""
+    kind, v = spec
+    v = list(v)
+    if kind == "plane":
+        o, t0 = v[0:dim], v[dim:2 * dim]
+        t1 = v[2 * dim:3 * dim] if dim == 3 else None
+        lo, hi = v[dim * dim], v[dim * dim + 1]
+        return rigid_plane(dim, o, t0, t1, lo, hi)
+    return rigid_sphere(dim, v[0:dim], v[dim])
+
+
+def rigid_params(dim, spec):
+    """Flat parameter list of the C ABI (mb2_contact_set_rigid_body): the Rigid.p layout."""
+    return np.array(list(rigid_from_spec(dim, spec).p))
+
+
+def contact_prepare(dim, v_dofs):
+    NF, tdf = v_dofs.shape
+    ndf = tdf // dim
+    local = np.zeros((NF, ndf), np.int32)
+    marked = np.zeros(NF * tdf, np.int32)
+    nm = C.c_int64()
+    n = lib().orc_contact_prepare(C.c_int(dim), C.c_int64(NF), C.c_int(ndf), _p(v_dofs, C.c_int32), _p(local, C.c_int32),
+                                  _p(marked, C.c_int32), C.byref(nm))
+    return local, n, marked[:nm.value].copy()
+
+
+def contact_pressure(dim, v_dofs, local, n_marked, N, dN_dxi, w, x_ref, u, body, penalty):
+    NF, tdf = v_dofs.shape
+    ndf, nqf = tdf // dim, w.shape[1]
+    gap, area, pr = np.zeros(n_marked), np.zeros(n_marked), np.zeros(n_marked)
+    tot = C.c_double(0.0)
+    rc = lib().orc_contact_pressure(C.c_int(dim), C.c_int64(NF), C.c_int(ndf), C.c_int(nqf), C.c_int(n_marked),
+                                    _p(v_dofs, C.c_int32), _p(local, C.c_int32), _p(N, C.c_double), _p(dN_dxi, C.c_double),
+                                    _p(w, C.c_double), _p(x_ref, C.c_double), _p(u, C.c_double), C.byref(body),
+                                    C.c_double(penalty), _p(gap, C.c_double), _p(area, C.c_double), _p(pr, C.c_double),
+                                    C.byref(tot))
+    assert rc == 0
+    return gap, area, pr, tot.value
+
+
+def contact_assemble(dim, v_dofs, local, A_ids, N, dN_dxi, w, x_ref, u, pressure, grad, gf, r, A):
+    """Adds into r (and A when grad) in place; returns (force[3], pressure_integral)."""
+    NF, tdf = v_dofs.shape
+    ndf, nqf = tdf // dim, w.shape[1]
+    force = np.zeros(3)
+    pint = C.c_double(0.0)
+    rc = lib().orc_contact_assemble(C.c_int(dim), C.c_int64(NF), C.c_int(ndf), C.c_int(nqf), _p(v_dofs, C.c_int32),
+                                    _p(local, C.c_int32), _p(A_ids, C.c_int32) if A_ids is not None else None,
+                                    _p(N, C.c_double), _p(dN_dxi, C.c_double), _p(w, C.c_double), _p(x_ref, C.c_double),
+                                    _p(u, C.c_double), _p(pressure, C.c_double), C.c_int(int(grad)), C.c_double(gf),
+                                    _p(r, C.c_double), _p(A, C.c_double) if A is not None else None,
+                                    _p(force, C.c_double), C.byref(pint))
+    assert rc == 0
+    return force, pint.value
+
+
+def contact_gap_norm(dim, v_dofs, N, w, x_ref, u, body):
+    NF, tdf = v_dofs.shape
+    return lib().orc_contact_gap_norm(C.c_int(dim), C.c_int64(NF), C.c_int(tdf // dim), C.c_int(w.shape[1]),
+                                      _p(v_dofs, C.c_int32), _p(N, C.c_double), _p(x_ref, C.c_double), _p(u, C.c_double),
+                                      C.byref(body))
+
+
+def load_contact_dump(d):
+    meta = json.load(open(os.path.join(d, "meta.json")))
+    NF, ndf, nqf, dim = meta["NF"], meta["ndf"], meta["nqf"], meta["dim"]
+    tdf = ndf * dim
+    out = dict(meta)
+
+    def rd(name, dt, shape=None):
+        a = np.fromfile(os.path.join(d, name), dtype=dt)
+        return a.reshape(shape) if shape else a
+
+    out["marked"] = rd("c_marked.i32", np.int32)
+    out["c_v_dofs"] = rd("c_v_dofs.i32", np.int32, (NF, tdf))
+    out["c_A_ids"] = rd("c_A_ids.i32", np.int32, (NF, tdf * tdf))
+    out["c_w"] = rd("c_w.f64", np.float64, (NF, nqf))
+    out["c_N"] = rd("c_N.f64", np.float64, (NF, nqf, ndf))
+    out["c_dN_dxi"] = rd("c_dN_dxi.f64", np.float64, (NF, nqf, dim - 1, ndf))
+    out["c_x_ref"] = rd("c_x_ref.f64", np.float64, (NF, dim, ndf))
+    out["c_marked_v_dofs"] = rd("c_marked_v_dofs.i32", np.int32)
+    out["I"] = rd("I.i32", np.int32)
+    out["J"] = rd("J.i32", np.int32)
+    for k in ("x_ref", "u", "mass", "c_r0", "c_r", "c_gap", "c_area", "c_pressure", "c_r2", "c_A", "c_scalars"):
+        out[k] = rd(k + ".f64", np.float64)
+    return out
+
+
+def run_ref_contact(mesh, elevate, refine, outdir, bdr_attr, penalty, body, gf=1.0, material="neohookean", u_file="-",
+                    nthreads=1):
+    """body = ("plane", [...]) / ("sphere", [...])."""
+    os.makedirs(outdir, exist_ok=True)
+    cmd = [REF_BIN, "contact", mesh, str(elevate), str(refine), material, str(nthreads), repr(gf), u_file, outdir,
+           str(bdr_attr), repr(float(penalty)), body[0]] + [repr(float(x)) for x in body[1]]
+    subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+    return load_contact_dump(outdir)

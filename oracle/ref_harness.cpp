@@ -5,6 +5,11 @@
 //
 //   mimi_ref dump <mesh> <elevate> <refine> <material> <nthreads> <gf> <u.bin|-> <outdir> [lite]
 //   mimi_ref time <mesh> <elevate> <refine> <material> <nthreads> <reps> [warmup reps, untimed]
+//   mimi_ref contact <mesh> <elevate> <refine> <material> <nthreads> <gf> <u.bin|-> <outdir> <bdr_attr> <penalty>
+//            <body> <p0> <p1> ...      rigid body = analytic NearestDistanceBase subclass (below):
+//            plane  o[dim] t0[dim] (t1[dim] in 3D) lo hi   closest point on the (clamped) affine patch o + s t0 + t t1
+//            sphere c[dim] R                                  closest point on the circle / sphere
+//   Dumps the marked faces' tables and what MortarContact (mortar_contact.cpp) computes on them.
 // material: neohookean | stvk | j2linear  (E=2100, nu=0.3, rho=1: tests/test_nonlinear_solid.py:59-62;
 //           j2linear adds isotropic_hardening=80, kinematic_hardening=40, sigma_y=<MIMI_REF_SIGMA_Y or 2.0>)
 // For materials with history the dump continues: DomainPostTimeAdvance(u) -> state.f64 [NE][nq][19]
@@ -20,6 +25,8 @@
 
 #include <mfem.hpp>
 
+#include "mimi/coefficients/nearest_distance.hpp"
+#include "mimi/integrators/mortar_contact.hpp"
 #include "mimi/integrators/nonlinear_solid.hpp"
 #include "mimi/materials/materials.hpp"
 #include "mimi/utils/precomputed.hpp"
@@ -105,6 +112,93 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
   s.t_precompute = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   return s;
 }
+
+// ---- analytic rigid bodies (closed-form closest point) filling NearestDistanceBase::Results exactly as
+// MortarContact reads it (nearest_distance.hpp:139-193): physical_minus_query_, distance_, first_derivatives_
+// [para_dim x dim, row-major]. The operation order below is the contract the C oracle (oracle/mimi_oracle.c,
+// orc_rigid_nearest) and the CUDA path (mb2_contact.cu, rigid_nearest) restate.
+struct RigidPlane : mimi::coefficients::NearestDistanceBase {
+  int dim = 0;
+  double o[3] = {0, 0, 0}, t[2][3] = {{0, 0, 0}, {0, 0, 0}}, lo = -1e300, hi = 1e300;
+  void NearestDistance(const Query& query, Results& r) const override {
+    const double* q = query.query.data();
+    double diff[3];
+    for (int d = 0; d < dim; ++d) diff[d] = q[d] - o[d];
+    double s[2] = {0, 0};
+    for (int k = 0; k < dim - 1; ++k) {
+      double num = 0.0, den = 0.0;
+      for (int d = 0; d < dim; ++d) num += diff[d] * t[k][d];
+      for (int d = 0; d < dim; ++d) den += t[k][d] * t[k][d];
+      double v = num / den;
+      if (v < lo) v = lo;
+      if (v > hi) v = hi;
+      s[k] = v;
+      r.parametric_[k] = v;
+    }
+    double sum = 0.0;
+    for (int d = 0; d < dim; ++d) {
+      double x = o[d] + s[0] * t[0][d];
+      if (dim == 3) x = x + s[1] * t[1][d];
+      r.physical_[d] = x;
+      const double pmq = x - q[d];
+      r.physical_minus_query_[d] = pmq;
+      sum += pmq * pmq;
+    }
+    r.distance_ = std::sqrt(sum);
+    for (int k = 0; k < dim - 1; ++k)
+      for (int d = 0; d < dim; ++d) r.first_derivatives_[k * dim + d] = t[k][d];
+  }
+  int Size() const override { return 1; }
+};
+
+struct RigidSphere : mimi::coefficients::NearestDistanceBase {
+  int dim = 0;
+  double c[3] = {0, 0, 0}, R = 1.0;
+  void NearestDistance(const Query& query, Results& r) const override {
+    const double* q = query.query.data();
+    double diff[3] = {0, 0, 0}, e[3] = {0, 0, 0};
+    double n2 = 0.0;
+    for (int d = 0; d < dim; ++d) {
+      diff[d] = q[d] - c[d];
+      n2 += diff[d] * diff[d];
+    }
+    const double dn = std::sqrt(n2);
+    double sum = 0.0;
+    for (int d = 0; d < dim; ++d) {
+      e[d] = diff[d] / dn;
+      const double x = c[d] + R * e[d];
+      r.physical_[d] = x;
+      const double pmq = x - q[d];
+      r.physical_minus_query_[d] = pmq;
+      sum += pmq * pmq;
+    }
+    r.distance_ = std::sqrt(sum);
+    double* fd = r.first_derivatives_.data();
+    if (dim == 2) {  // ComputeNormal: n = (d1, -d0)/|d|  ->  tangent (-e1, e0) gives n = e (outward)
+      fd[0] = -e[1];
+      fd[1] = e[0];
+    } else {  // t0 = a x e (a = z unless e is near z, then x), t1 = e x t0  ->  t0 x t1 = |t0|^2 e
+      if (std::abs(e[2]) < 0.9) {
+        fd[0] = -e[1]; fd[1] = e[0]; fd[2] = 0.0;
+      } else {
+        fd[0] = 0.0; fd[1] = -e[2]; fd[2] = e[1];
+      }
+      fd[3] = e[1] * fd[2] - e[2] * fd[1];
+      fd[4] = e[2] * fd[0] - e[0] * fd[2];
+      fd[5] = e[0] * fd[1] - e[1] * fd[0];
+    }
+  }
+  int Size() const override { return 1; }
+};
+
+// exposes MortarContact's protected nodal vectors for the dump
+struct ContactProbe : mimi::integrators::MortarContact {
+  using mimi::integrators::MortarContact::MortarContact;
+  const mfem::Vector& Gap() const { return average_gap_; }
+  const mfem::Vector& Pressure() const { return average_pressure_; }
+  const mfem::Vector& Area() const { return area_; }
+  const mimi::utils::Vector<int>& MarkedVDofs() const { return marked_boundary_v_dofs_; }
+};
 
 void fill_u(mfem::Vector& u, const char* u_file) {
   if (std::strcmp(u_file, "-") == 0) {
@@ -213,6 +307,118 @@ int main(int argc, char** argv) {
       << ", \"dim\": " << dim << ", \"tdof\": " << tdof << ", \"gf\": " << gf << ", \"nthreads\": " << nthreads
       << ", \"material\": \"" << material << "\", \"lambda\": \"" << std::hexfloat << s.mat->lambda_ << "\", \"mu\": \""
       << s.mat->mu_ << std::defaultfloat << "\", \"lite\": " << (lite ? 1 : 0) << "}\n";
+    return 0;
+  }
+  if (mode == "contact") {
+    if (argc < 13) { std::fprintf(stderr, "contact: too few arguments\n"); return 2; }
+    const double gf = std::atof(argv[7]);
+    const char* u_file = argv[8];
+    const std::string out = argv[9];
+    const int bdr_attr = std::atoi(argv[10]);
+    const double penalty = std::atof(argv[11]);
+    const std::string body = argv[12];
+    Setup s = build(mesh_file, elevate, refine, material, nthreads, true);
+    auto& pre = *s.pre;
+    const int dim = pre.dim_, NV = pre.n_v_dofs_;
+    std::vector<double> bp;
+    for (int i = 13; i < argc; ++i) bp.push_back(std::atof(argv[i]));
+    std::shared_ptr<mimi::coefficients::NearestDistanceBase> nd;
+    if (body == "plane") {
+      auto b = std::make_shared<RigidPlane>();
+      b->dim = dim;
+      size_t k = 0;
+      for (int d = 0; d < dim; ++d) b->o[d] = bp.at(k++);
+      for (int j = 0; j < dim - 1; ++j)
+        for (int d = 0; d < dim; ++d) b->t[j][d] = bp.at(k++);
+      b->lo = bp.at(k++);
+      b->hi = bp.at(k++);
+      nd = b;
+    } else if (body == "sphere") {
+      auto b = std::make_shared<RigidSphere>();
+      b->dim = dim;
+      size_t k = 0;
+      for (int d = 0; d < dim; ++d) b->c[d] = bp.at(k++);
+      b->R = bp.at(k++);
+      nd = b;
+    } else { std::fprintf(stderr, "unknown rigid body %s\n", body.c_str()); return 2; }
+    nd->coefficient_ = penalty;
+    nd->dim_ = dim;
+    nd->para_dim_ = dim - 1;
+
+    // wiring of py_nonlinear_solid.cpp:292-325
+    mfem::Array<int> marker(s.mesh->bdr_attributes.Max());
+    marker = 0;
+    marker[bdr_attr - 1] = 1;
+    auto integ = std::make_shared<ContactProbe>(nd, "contact" + std::to_string(bdr_attr), s.pre);
+    integ->runtime_communication_ = std::make_shared<mimi::utils::RuntimeCommunication>();
+    integ->SetBoundaryMarker(&marker);
+    auto& marked = integ->MarkedBoundaryElements();
+    pre.CreateBoundaryElementQuadData(integ->Name(), marked.data(), (int)marked.size());
+    pre.PrecomputeElementQuadData(integ->Name(), -1, false);
+    integ->Prepare();
+
+    auto& beqd = pre.GetElementQuadData(integ->Name());
+    const int NF = (int)beqd.size();
+    const int ndf = beqd[0].GetElementData().n_dof, tdf = beqd[0].GetElementData().n_tdof, nqf = beqd[0].n_quad;
+    std::vector<int> vd((size_t)NF * tdf), aid((size_t)NF * tdf * tdf);
+    std::vector<double> w((size_t)NF * nqf), N((size_t)NF * nqf * ndf), dxi((size_t)NF * nqf * ndf * (dim - 1)),
+        xr((size_t)NF * ndf * dim);
+    for (int f = 0; f < NF; ++f) {
+      const auto& ed = beqd[f].GetElementData();
+      std::memcpy(&vd[(size_t)f * tdf], ed.v_dofs.GetData(), sizeof(int) * tdf);
+      std::memcpy(&aid[(size_t)f * tdf * tdf], ed.A_ids.data(), sizeof(int) * tdf * tdf);
+      std::memcpy(&xr[(size_t)f * ndf * dim], beqd[f].GetMatrix(0).GetData(), sizeof(double) * ndf * dim);  // kXRef = 0
+      for (int q = 0; q < nqf; ++q) {
+        const auto& qd = beqd[f].GetQuadData()[q];
+        const size_t fq = (size_t)f * nqf + q;
+        w[fq] = qd.integration_weight;
+        std::memcpy(&N[fq * ndf], qd.N.GetData(), sizeof(double) * ndf);
+        std::memcpy(&dxi[fq * ndf * (dim - 1)], qd.dN_dxi.GetData(), sizeof(double) * ndf * (dim - 1));
+      }
+    }
+    dump(out, "c_marked.i32", marked.data(), marked.size());
+    dump(out, "c_v_dofs.i32", vd.data(), vd.size());
+    dump(out, "c_A_ids.i32", aid.data(), aid.size());
+    dump(out, "c_w.f64", w.data(), w.size());
+    dump(out, "c_N.f64", N.data(), N.size());
+    dump(out, "c_dN_dxi.f64", dxi.data(), dxi.size());
+    dump(out, "c_x_ref.f64", xr.data(), xr.size());
+    dump(out, "c_marked_v_dofs.i32", integ->MarkedVDofs().data(), integ->MarkedVDofs().size());
+    mfem::SparseMatrix& sp = *pre.sparsity_pattern_;
+    const int nnz = sp.NumNonZeroElems();
+    dump(out, "I.i32", sp.GetI(), (size_t)NV + 1);
+    dump(out, "J.i32", sp.GetJ(), (size_t)nnz);
+    mfem::GridFunction& nodes = *s.mesh->GetNodes();
+    dump(out, "x_ref.f64", nodes.GetData(), (size_t)nodes.Size());
+
+    mfem::Vector u(NV), r(NV), r2(NV);
+    fill_u(u, u_file);
+    dump(out, "u.f64", u.GetData(), (size_t)NV);
+    // AddBoundaryResidual on top of a non-zero residual (the domain residual): the faces add into it in order
+    r = 0.0;
+    s.integ->AddDomainResidual(u, r);
+    dump(out, "c_r0.f64", r.GetData(), (size_t)NV);
+    integ->AddBoundaryResidual(u, r);
+    dump(out, "c_r.f64", r.GetData(), (size_t)NV);
+    dump(out, "c_gap.f64", integ->Gap().GetData(), (size_t)integ->Gap().Size());
+    dump(out, "c_area.f64", integ->Area().GetData(), (size_t)integ->Area().Size());
+    dump(out, "c_pressure.f64", integ->Pressure().GetData(), (size_t)integ->Pressure().Size());
+    double scal[8] = {integ->last_area_, integ->last_pressure_, integ->last_force_[0], integ->last_force_[1],
+                      dim > 2 ? integ->last_force_[2] : 0.0, 0, 0, 0};
+    mfem::SparseMatrix A(s.mass->SpMat());
+    dump(out, "mass.f64", A.GetData(), (size_t)nnz);
+    r2 = 0.0;
+    integ->AddBoundaryResidualAndGrad(u, gf, r2, A);
+    dump(out, "c_r2.f64", r2.GetData(), (size_t)NV);
+    dump(out, "c_A.f64", A.GetData(), (size_t)nnz);
+    scal[5] = integ->GapNorm(u, 1);
+    scal[6] = integ->last_area_;
+    scal[7] = integ->last_pressure_;
+    dump(out, "c_scalars.f64", scal, 8);
+    std::ofstream m(out + "/meta.json");
+    m << "{\"NV\": " << NV << ", \"NE\": " << pre.n_elements_ << ", \"nnz\": " << nnz << ", \"dim\": " << dim
+      << ", \"NF\": " << NF << ", \"ndf\": " << ndf << ", \"nqf\": " << nqf << ", \"gf\": " << gf
+      << ", \"penalty\": " << penalty << ", \"n_marked_nodes\": " << integ->Area().Size() << "}\n";
     return 0;
   }
   if (mode == "time") {

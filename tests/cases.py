@@ -21,6 +21,19 @@ def load_golden(name):
     return D
 
 
+CONTACT_CASES = ["contact_cube_p2_n2_plane", "contact_cube_p2_n4_sphere", "contact_quad_p3_n4_sphere",
+                 "contact_quad_p2_n4_plane_clamped"]
+
+
+def load_contact_golden(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    D = {k: z[k] for k in z.files}
+    dim, NF, ndf, nqf, NV, nnz, nm = (int(x) for x in D["meta"])
+    D.update(dim=dim, NF=NF, ndf=ndf, nqf=nqf, NV=NV, nnz=nnz, n_marked_nodes=nm, gf=float(D["gf"]),
+             penalty=float(D["penalty"]), body=(str(D["body_kind"]), [float(x) for x in D["body_params"]]))
+    return D
+
+
 def ref_case(kind, p, n, material, gf=1.0):
     """Live reference run (nthreads=1). kind: 'refine' (p1 cube + DegreeElevate(p-1) + log2(n) refinements)
     or 'patch' (direct p, n spans)."""

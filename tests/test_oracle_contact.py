@@ -1,0 +1,50 @@
+"""CPU: the plain-C contact oracle (oracle/mimi_oracle_contact.c) against golden vectors dumped from the unmodified
+reference's MortarContact (src/mimi/integrators/mortar_contact.cpp) driven by analytic rigid bodies
+(oracle/ref_harness.cpp, mode "contact"). Bit-exact."""
+import numpy as np
+import pytest
+
+from oracle import oracle_py as O
+from tests.cases import CONTACT_CASES, load_contact_golden
+
+
+@pytest.mark.parametrize("name", CONTACT_CASES)
+def test_contact_oracle_bit_exact(name):
+    D = load_contact_golden(name)
+    dim = D["dim"]
+    body = O.rigid_from_spec(dim, D["body"])
+    # A11 Prepare: sorted unique marked vdofs and the reduced nodal numbering
+    local, nm, marked = O.contact_prepare(dim, D["c_v_dofs"])
+    assert nm == D["n_marked_nodes"] and np.array_equal(marked, D["c_marked_v_dofs"])
+    # A12 ComputePressure
+    gap, area, pr, tot = O.contact_pressure(dim, D["c_v_dofs"], local, nm, D["c_N"], D["c_dN_dxi"], D["c_w"],
+                                            D["c_x_ref"], D["u"], body, D["penalty"])
+    assert np.array_equal(gap, D["c_gap"]) and np.array_equal(area, D["c_area"])
+    assert np.array_equal(pr, D["c_pressure"]) and tot == D["c_scalars"][0]
+    assert 0 < (pr != 0).sum()
+    # A13 AddBoundaryResidual on top of the domain residual, then AddBoundaryResidualAndGrad on the mass values
+    r = D["c_r0"].copy()
+    force, pint = O.contact_assemble(dim, D["c_v_dofs"], local, None, D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"],
+                                     D["u"], pr, False, 0.0, r, None)
+    assert np.array_equal(r, D["c_r"])
+    assert np.array_equal(force, D["c_scalars"][2:5]) and pint == D["c_scalars"][1]
+    r2 = np.zeros_like(r)
+    A = D["mass"].copy()
+    O.contact_assemble(dim, D["c_v_dofs"], local, D["c_A_ids"], D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"], D["u"],
+                       pr, True, D["gf"], r2, A)
+    assert np.array_equal(r2, D["c_r2"]) and np.array_equal(A, D["c_A"])
+    # A14 GapNorm
+    assert O.contact_gap_norm(dim, D["c_v_dofs"], D["c_N"], D["c_w"], D["c_x_ref"], D["u"], body) == D["c_scalars"][5]
+
+
+def test_clamped_plane_exercises_the_angle_filter():
+    """Closest points on the patch edge are not perpendicular: ElementGapAndArea zeroes those gaps
+    (mortar_contact.cpp:174-181)."""
+    D = load_contact_golden("contact_quad_p2_n4_plane_clamped")
+    unclamped = ("plane", list(D["body"][1][:4]) + [-1e300, 1e300])
+    local, nm, _ = O.contact_prepare(2, D["c_v_dofs"])
+    a = O.contact_pressure(2, D["c_v_dofs"], local, nm, D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"], D["u"],
+                           O.rigid_from_spec(2, D["body"]), D["penalty"])
+    b = O.contact_pressure(2, D["c_v_dofs"], local, nm, D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"], D["u"],
+                           O.rigid_from_spec(2, unclamped), D["penalty"])
+    assert np.abs(a[0]).sum() < 0.1 * np.abs(b[0]).sum()      # most penetrating gaps are filtered out
