@@ -151,6 +151,50 @@ int mb2_last_launch_count(mb2_ctx* ctx);
 /* Synchronise ctx's stream. */
 int mb2_sync(mb2_ctx* ctx);
 
+/* ---- rigid-body mortar contact: mimi::integrators::MortarContact (src/mimi/integrators/mortar_contact.{hpp,cpp}) ----
+ * One contact boundary per context. Call order: mb2_set_connectivity, mb2_set_nodes (the faces' x_ref comes from the
+ * node coordinates, MortarContact::Prepare mortar_contact.cpp:96-107), mb2_build_pattern, mb2_contact_set_faces,
+ * mb2_contact_set_rigid_body. */
+enum {
+  /* closest point on the affine patch o + s t0 (+ t t1), s, t clamped to [lo, hi] (a degree-1 spline);
+   * params = o[3], t0[3], t1[3], lo, hi  (unused components 0; 2D uses o[0..1], t0[0..1]) */
+  MB2_RIGID_PLANE = 0,
+  /* closest point on the circle (2D) / sphere (3D): params = c[3], R; the outward normal is the contact normal */
+  MB2_RIGID_SPHERE = 1
+};
+/* The marked boundary faces and their quadrature tables as PrecomputedData holds them for the integrator's name
+ * (CreateBoundaryElementQuadData + PrecomputeElementQuadData(name, order, false), precomputed.cpp:243-330):
+ * v_dofs NF x (dim*nd_f) component-major byVDIM ids; N NF x nq_f x nd_f (QuadData::N); dN_dxi NF x nq_f x
+ * (nd_f x (dim-1)) column-major (QuadData::dN_dxi); w NF x nq_f (integration_weight). Performs MortarContact::Prepare
+ * (mortar_contact.cpp:19-133): sorted unique marked vdofs and the reduced nodal numbering. */
+int mb2_contact_set_faces(mb2_ctx* ctx, int64_t NF, int nd_f, int nq_f, const int32_t* v_dofs, const double* N,
+                          const double* dN_dxi, const double* w);
+/* The rigid body (replaces the NearestDistanceBase scene handed to the MortarContact constructor,
+ * mortar_contact.hpp:73-79) and NearestDistanceBase::coefficient_ (the penalty). May be called again every time step
+ * (moving body). */
+int mb2_contact_set_rigid_body(mb2_ctx* ctx, int kind, const double* params, int nparams, double penalty);
+int mb2_contact_n_marked_nodes(mb2_ctx* ctx, int64_t* n);
+/* MortarContact::marked_boundary_v_dofs_ (sorted, unique): dim * n_marked_nodes entries. */
+int mb2_contact_get_marked_v_dofs(mb2_ctx* ctx, int32_t* out);
+/* Boundary ElementData::A_ids (precomputed.cpp:202-217), NF x (dim*nd_f)^2, for parity tests. */
+int mb2_contact_get_A_ids_i32(mb2_ctx* ctx, int32_t* A_ids);
+/* r += R_contact(u). Replaces MortarContact::AddBoundaryResidual (mortar_contact.cpp:297-352). */
+int mb2_add_boundary_residual(mb2_ctx* ctx, const double* u, double* r);
+/* r += R_contact(u); A_values += K_contact * grad_factor (FD tangent with frozen pressure). Replaces
+ * MortarContact::AddBoundaryResidualAndGrad (mortar_contact.cpp:354-421). Only the CSR rows of the marked nodes are
+ * copied to the device and back. */
+int mb2_add_boundary_residual_and_grad(mb2_ctx* ctx, const double* u, double grad_factor, double* r, double* A_values);
+/* Device-resident forms: act on the resident u, r, A (after mb2_assemble_*_device for domain + contact in one go). */
+int mb2_contact_residual_device(mb2_ctx* ctx);
+int mb2_contact_residual_and_grad_device(mb2_ctx* ctx, double grad_factor);
+/* average_gap_, area_, average_pressure_ of the last assembly (n_marked_nodes each; any pointer may be NULL). */
+int mb2_contact_get_nodal(mb2_ctx* ctx, double* gap, double* area, double* pressure);
+/* out5 = {last_area_, last_pressure_, last_force_[0..2]} of the last assembly (what BoundaryPostTimeAdvance records,
+ * mortar_contact.cpp:469-488). Summed per face, then across faces in ascending id: 1e-12 relative to the reference. */
+int mb2_contact_last_scalars(mb2_ctx* ctx, double* out5);
+/* sqrt(sum of g_n^2 over penetrating quadrature points). Replaces MortarContact::GapNorm (mortar_contact.cpp:423-467). */
+int mb2_contact_gap_norm(mb2_ctx* ctx, const double* u, double* out);
+
 /* ---- multi-GPU: element partition with raw element-matrix exchange ------------------
  * One context per GPU / rank. The rank's connectivity (mb2_set_connectivity) lists its own elements first
  * (global ascending order) and then its GHOST elements: elements computed by higher ranks that touch a node this

@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmimi_b200.so")
 
 MB2_MAT_NEOHOOKEAN, MB2_MAT_STVK, MB2_MAT_J2LINEAR = 0, 1, 2
+MB2_RIGID_PLANE, MB2_RIGID_SPHERE = 0, 1
 
 # every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
@@ -25,7 +26,10 @@ SYMBOLS = [
     "mb2_device_pointers", "mb2_last_timing_ms", "mb2_last_launch_count", "mb2_sync", "mb2_measure_fp64_peak", "mb2_set_option", "mb2_host_register", "mb2_host_unregister", "mb2_plan_info", "mb2_set_partition", "mb2_mg_set_send", "mb2_mg_set_recv", "mb2_mg_unique_id",
     "mb2_mg_init_nccl", "mb2_mg_set_manual", "mb2_mg_begin", "mb2_mg_export_send", "mb2_mg_import_recv", "mb2_mg_finish",
     "mb2_mg_ke_doubles", "mb2_state_size", "mb2_get_state", "mb2_set_state", "mb2_post_time_advance",
-    "mb2_post_time_advance_device",
+    "mb2_post_time_advance_device", "mb2_contact_set_faces", "mb2_contact_set_rigid_body", "mb2_contact_n_marked_nodes",
+    "mb2_contact_get_marked_v_dofs", "mb2_contact_get_A_ids_i32", "mb2_add_boundary_residual",
+    "mb2_add_boundary_residual_and_grad", "mb2_contact_residual_device", "mb2_contact_residual_and_grad_device",
+    "mb2_contact_get_nodal", "mb2_contact_last_scalars", "mb2_contact_gap_norm",
 ]
 
 
@@ -159,6 +163,60 @@ class Context:
 
     def post_time_advance(self, u):
         self._ck(self.lib.mb2_post_time_advance(self.h, _dp(u)))
+
+    # ---- rigid-body mortar contact
+    def contact_set_faces(self, v_dofs, N, dN_dxi, w):
+        v = np.ascontiguousarray(v_dofs, np.int32)
+        N, dN, w = (np.ascontiguousarray(x, np.float64) for x in (N, dN_dxi, w))
+        self.NF, self.nqf = w.shape
+        self.ndf = v.shape[1] // self.dim
+        assert N.size == self.NF * self.nqf * self.ndf and dN.size == N.size * (self.dim - 1)
+        self._ck(self.lib.mb2_contact_set_faces(self.h, C.c_int64(self.NF), self.ndf, self.nqf, _dp(v), _dp(N), _dp(dN), _dp(w)))
+        n = C.c_int64()
+        self._ck(self.lib.mb2_contact_n_marked_nodes(self.h, C.byref(n)))
+        self.n_marked = n.value
+
+    def contact_set_rigid_body(self, kind, params, penalty):
+        p = np.ascontiguousarray(params, np.float64)
+        self._ck(self.lib.mb2_contact_set_rigid_body(self.h, kind, _dp(p), p.size, C.c_double(penalty)))
+
+    def contact_marked_v_dofs(self):
+        out = np.empty(self.n_marked * self.dim, np.int32)
+        self._ck(self.lib.mb2_contact_get_marked_v_dofs(self.h, _dp(out)))
+        return out
+
+    def contact_A_ids(self):
+        tdf = self.ndf * self.dim
+        out = np.empty((self.NF, tdf * tdf), np.int32)
+        self._ck(self.lib.mb2_contact_get_A_ids_i32(self.h, _dp(out)))
+        return out
+
+    def add_boundary_residual(self, u, r):
+        self._ck(self.lib.mb2_add_boundary_residual(self.h, _dp(u), _dp(r)))
+
+    def add_boundary_residual_and_grad(self, u, gf, r, A):
+        self._ck(self.lib.mb2_add_boundary_residual_and_grad(self.h, _dp(u), C.c_double(gf), _dp(r), _dp(A)))
+
+    def contact_residual_device(self):
+        self._ck(self.lib.mb2_contact_residual_device(self.h))
+
+    def contact_residual_and_grad_device(self, gf):
+        self._ck(self.lib.mb2_contact_residual_and_grad_device(self.h, C.c_double(gf)))
+
+    def contact_nodal(self):
+        g, a, p = (np.empty(self.n_marked) for _ in range(3))
+        self._ck(self.lib.mb2_contact_get_nodal(self.h, _dp(g), _dp(a), _dp(p)))
+        return g, a, p
+
+    def contact_last_scalars(self):
+        out = np.empty(5)
+        self._ck(self.lib.mb2_contact_last_scalars(self.h, _dp(out)))
+        return out
+
+    def contact_gap_norm(self, u):
+        out = C.c_double()
+        self._ck(self.lib.mb2_contact_gap_norm(self.h, _dp(u), C.byref(out)))
+        return out.value
 
     # ---- host-buffer hot path
     def add_domain_residual(self, u, r):

@@ -29,6 +29,7 @@ static void free_problem(mb2_ctx* c) {
   dfree(c->d_u); dfree(c->d_r); dfree(c->d_A); dfree(c->d_Re); dfree(c->d_state);
   mb2::free_plan(c);
   mb2::free_mg(c);
+  mb2::free_contact(c);
   dfree(c->d_owned);
   c->have_pattern = false;
   c->nnz = 0;

@@ -1,0 +1,833 @@
+// Rigid-body mortar contact boundary quadrature on the device.
+//
+// Reference path replaced: mimi::integrators::MortarContact (src/mimi/integrators/mortar_contact.{hpp,cpp}):
+//   Prepare (cpp:19-133)                         -> contact_set_faces   (host C++: sort/unique, adjacency; setup)
+//   ComputePressure + ElementGapAndArea (148-261) -> face_gap_area_kernel, nodal_pressure_kernel
+//   ElementResidual / ElementResidualAndGrad (hpp:99-134, cpp:263-295) -> face_residual_kernel<DIM, GRAD>
+//   AddBoundaryResidual[AndGrad] (297-421)        -> contact_residual_gather_kernel, contact_csr_gather_kernel
+//   GapNorm (423-467)                             -> gap_norm_kernel
+// Every per-face and per-node value follows the reference's operation order at nthreads = 1 (compiled -fmad=false):
+// residual and Jacobian contributions are bit-identical. The whole-boundary scalars (area, force, pressure integral,
+// gap norm) are summed per face in the reference's order and then across faces in ascending face id by one thread:
+// deterministic, but not the reference's single running sum (tolerance 1e-12 relative, stated in the tests).
+#include <algorithm>
+#include <cmath>
+#include <vector>
+
+#include "mb2_ctx.h"
+
+namespace mb2 {
+
+struct RigidBody {
+  int kind = -1;
+  double p[16] = {0};
+};
+
+struct ContactState {
+  int64_t NF = 0;
+  int ndf = 0, nqf = 0, tdf = 0;
+  int64_t n_marked = 0;            // marked nodes
+  std::vector<int32_t> marked_nodes;  // sorted unique node ids
+  int32_t* d_fvdofs = nullptr;     // NF x tdf
+  int32_t* d_flocal = nullptr;     // NF x ndf  reduced nodal index (MortarContact::local_marked_dofs_)
+  double* d_fN = nullptr;          // NF x nqf x ndf
+  double* d_fdN = nullptr;         // NF x nqf x (ndf x (dim-1)) column-major
+  double* d_fw = nullptr;          // NF x nqf
+  uint16_t* d_frank = nullptr;     // NF x ndf x ndf: rank of node b in node a's neighbour list (CSR position)
+  int32_t* d_mnode = nullptr;      // n_marked node ids
+  int64_t* d_mn_ptr = nullptr;     // n_marked+1: marked node -> (face, local index), ascending face id
+  int32_t* d_mn_face = nullptr;
+  uint8_t* d_mn_loc = nullptr;
+  double* d_la = nullptr;          // NF x ndf local_area_
+  double* d_lg = nullptr;          // NF x ndf local_gap_
+  double* d_fsum = nullptr;        // NF x 8 per-face scalars: area, pressure integral, force[3], gap^2
+  double* d_gap = nullptr;         // n_marked average_gap_
+  double* d_area = nullptr;        // n_marked area_
+  double* d_press = nullptr;       // n_marked average_pressure_
+  uint8_t* d_active = nullptr;     // NF: !IsPressureZero
+  double* d_fR = nullptr;          // NF x tdf
+  double* d_fK = nullptr;          // NF x tdf x tdf (column-major, column = perturbed dof)
+  double* d_scal = nullptr;        // 8: area, pressure integral, force[3], gap norm
+  RigidBody body;
+  double penalty = 1e4;            // NearestDistanceBase::coefficient_
+  std::vector<std::pair<int64_t, int64_t>> runs;  // CSR value ranges of the marked nodes' block rows (merged)
+  double h_scal[8] = {0};
+};
+
+// ---- rigid bodies: closed-form closest point, the operation order of oracle/ref_harness.cpp (RigidPlane,
+// RigidSphere). Fills what MortarContact reads from NearestDistanceBase::Results (nearest_distance.hpp:139-193).
+template <int DIM>
+__device__ __forceinline__ void rigid_nearest(const RigidBody& b, const double* q, double* pmq, double& distance,
+                                              double* fd) {
+  if (b.kind == MB2_RIGID_PLANE) {
+    const double* o = b.p;
+    const double lo = b.p[9], hi = b.p[10];
+    double diff[DIM], s[2] = {0, 0};
+#pragma unroll
+    for (int d = 0; d < DIM; d++) diff[d] = q[d] - o[d];
+#pragma unroll
+    for (int k = 0; k < DIM - 1; k++) {
+      const double* t = b.p + 3 + 3 * k;
+      double num = 0.0, den = 0.0;
+#pragma unroll
+      for (int d = 0; d < DIM; d++) num += diff[d] * t[d];
+#pragma unroll
+      for (int d = 0; d < DIM; d++) den += t[d] * t[d];
+      double v = num / den;
+      if (v < lo) v = lo;
+      if (v > hi) v = hi;
+      s[k] = v;
+    }
+    double sum = 0.0;
+#pragma unroll
+    for (int d = 0; d < DIM; d++) {
+      double x = o[d] + s[0] * b.p[3 + d];
+      if (DIM == 3) x = x + s[1] * b.p[6 + d];
+      pmq[d] = x - q[d];
+      sum += pmq[d] * pmq[d];
+    }
+    distance = sqrt(sum);
+#pragma unroll
+    for (int k = 0; k < DIM - 1; k++)
+#pragma unroll
+      for (int d = 0; d < DIM; d++) fd[k * DIM + d] = b.p[3 + 3 * k + d];
+    return;
+  }
+  const double* c = b.p;
+  const double R = b.p[3];
+  double diff[DIM], e[DIM];
+  double n2 = 0.0;
+#pragma unroll
+  for (int d = 0; d < DIM; d++) {
+    diff[d] = q[d] - c[d];
+    n2 += diff[d] * diff[d];
+  }
+  const double dn = sqrt(n2);
+  double sum = 0.0;
+#pragma unroll
+  for (int d = 0; d < DIM; d++) {
+    e[d] = diff[d] / dn;
+    const double x = c[d] + R * e[d];
+    pmq[d] = x - q[d];
+    sum += pmq[d] * pmq[d];
+  }
+  distance = sqrt(sum);
+  if (DIM == 2) {
+    fd[0] = -e[1];
+    fd[1] = e[0];
+  } else {
+    if (fabs(e[2]) < 0.9) {
+      fd[0] = -e[1]; fd[1] = e[0]; fd[2] = 0.0;
+    } else {
+      fd[0] = 0.0; fd[1] = -e[2]; fd[2] = e[1];
+    }
+    fd[3] = e[1] * fd[2] - e[2] * fd[1];
+    fd[4] = e[2] * fd[0] - e[0] * fd[2];
+    fd[5] = e[0] * fd[1] - e[1] * fd[0];
+  }
+}
+
+// Results::ComputeNormal<true> (nearest_distance.hpp:139-181) == ComputeUnitNormal (integrator_utils.hpp:218-251)
+template <int DIM>
+__device__ __forceinline__ void unit_normal(const double* d, double* n) {
+  if (DIM == 2) {
+    const double inv = 1. / sqrt(d[0] * d[0] + d[1] * d[1]);
+    n[0] = d[1] * inv;
+    n[1] = -d[0] * inv;
+  } else {
+    const double n0 = d[1] * d[5] - d[2] * d[4];
+    const double n1 = d[2] * d[3] - d[0] * d[5];
+    const double n2 = d[0] * d[4] - d[1] * d[3];
+    const double inv = 1. / sqrt(n0 * n0 + n1 * n1 + n2 * n2);
+    n[0] = n0 * inv;
+    n[1] = n1 * inv;
+    n[2] = n2 * inv;
+  }
+}
+
+// mfem::DenseMatrix::Weight, DIM x (DIM-1) (third_party/mfem/linalg/densemat.cpp:559-584)
+template <int DIM>
+__device__ __forceinline__ double jac_weight(const double* d) {
+  if (DIM == 2) return sqrt(d[0] * d[0] + d[1] * d[1]);
+  const double E = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+  const double G = d[3] * d[3] + d[4] * d[4] + d[5] * d[5];
+  const double F = d[0] * d[3] + d[1] * d[4] + d[2] * d[5];
+  return sqrt(E * G - F * F);
+}
+
+// MortarContactWorkData::ComputeJ = MultAtB(element_x_mat_, dN_dxi, J) (integrator_utils.cpp:99-104): k sequential.
+// x: ndf x DIM (shared), dN: ndf x (DIM-1). pm >= 0 replaces x[pm] by xp (finite-difference perturbation).
+template <int DIM>
+__device__ __forceinline__ void face_J(int ndf, const double* x, const double* dN, int pm, double xp, double* J) {
+#pragma unroll
+  for (int j = 0; j < DIM - 1; j++)
+#pragma unroll
+    for (int i = 0; i < DIM; i++) {
+      double d = 0.0;
+      for (int k = 0; k < ndf; k++) {
+        const int idx = k + i * ndf;
+        d += ((idx == pm) ? xp : x[idx]) * dN[k + j * ndf];
+      }
+      J[i + j * DIM] = d;
+    }
+}
+
+// ---- pass 1: MortarContact::ElementGapAndArea (mortar_contact.cpp:148-195). One CTA per face. Threads q < nqf
+// evaluate one quadrature point each (query, closest point, gap filter, |J|); threads i < ndf then sum
+// local_area_[i] / local_gap_[i] over q in ascending order. GAPNORM: only g^2 [g < 0] (GapNorm, cpp:423-467).
+template <int DIM, bool GAPNORM>
+__global__ void face_gap_area_kernel(int64_t NF, int ndf, int nqf, const int32_t* __restrict__ fvdofs,
+                                     const double* __restrict__ fN, const double* __restrict__ fdN,
+                                     const double* __restrict__ fw, const double* __restrict__ xref,
+                                     const double* __restrict__ u, const RigidBody body, double* __restrict__ la,
+                                     double* __restrict__ lg, double* __restrict__ fsum) {
+  extern __shared__ double sm[];
+  const int tdf = DIM * ndf;
+  double* sx = sm;             // tdf: current position x = u + x_ref (CurrentElementSolutionCopy)
+  double* sfac = sx + tdf;     // nqf
+  double* sfacg = sfac + nqf;  // nqf
+  const int t = threadIdx.x;
+  for (int64_t f = blockIdx.x; f < NF; f += gridDim.x) {
+    for (int k = t; k < tdf; k += blockDim.x) {
+      const int32_t v = fvdofs[f * tdf + k];
+      sx[k] = u[v] + xref[v];
+    }
+    __syncthreads();
+    if (t < nqf) {
+      const double* Nq = fN + (f * nqf + t) * ndf;
+      double query[DIM], pmq[DIM], fd[2 * DIM], nrm[DIM], J[2 * DIM], dist;
+      // ComputeNearestDistanceQuery = DenseMatrix::MultTranspose (densemat.cpp:166-179)
+#pragma unroll
+      for (int c = 0; c < DIM; c++) {
+        double y = 0.0;
+        for (int r = 0; r < ndf; r++) y += Nq[r] * sx[r + c * ndf];
+        query[c] = y;
+      }
+      rigid_nearest<DIM>(body, query, pmq, dist, fd);
+      unit_normal<DIM>(fd, nrm);
+      double dot = 0.0;
+#pragma unroll
+      for (int c = 0; c < DIM; c++) dot += pmq[c] * nrm[c];
+      const double true_g = -dot;  // Results::NormalGap
+      if (GAPNORM) {
+        sfac[t] = (true_g < 0.0) ? true_g * true_g : 0.0;
+      } else {
+        double g = (0. < true_g) ? 0. : true_g;  // std::min(true_g, 0.)
+        face_J<DIM>(ndf, sx, fdN + (f * nqf + t) * ndf * (DIM - 1), -1, 0.0, J);
+        const double fac = fw[f * nqf + t] * jac_weight<DIM>(J);
+        const double ratio = fabs(true_g) / dist;
+        const double cl = (ratio < 1.) ? ratio : 1.;  // std::min(1., ratio)
+        if (acos(cl) > 1.e-5) g = 0.0;
+        sfac[t] = fac;
+        sfacg[t] = fac * g;
+      }
+    }
+    __syncthreads();
+    if (!GAPNORM && t < ndf) {
+      double a = 0.0, g = 0.0;
+      for (int q = 0; q < nqf; q++) {
+        const double N = fN[(f * nqf + q) * ndf + t];
+        a += sfac[q] * N;
+        g += sfacg[q] * N;
+      }
+      la[f * ndf + t] = a;
+      lg[f * ndf + t] = g;
+    }
+    if (t == 0) {
+      double s = 0.0;
+      if (GAPNORM) {
+        for (int q = 0; q < nqf; q++)
+          if (sfac[q] != 0.0) s += sfac[q];  // the reference only adds penetrating points
+        fsum[f * 8 + 5] = s;
+      } else {
+        for (int q = 0; q < nqf; q++) s += sfac[q];
+        fsum[f * 8 + 0] = s;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- MortarContact::ComputePressure, second half (cpp:226-258): nodal area / gap = sum of the faces' local vectors
+// in ascending face id (thread_local_*_ at nthreads = 1), p = gap / area * penalty.
+__global__ void nodal_pressure_kernel(int64_t n_marked, int ndf, const int64_t* __restrict__ ptr,
+                                      const int32_t* __restrict__ face, const uint8_t* __restrict__ loc,
+                                      const double* __restrict__ la, const double* __restrict__ lg, double penalty,
+                                      double* __restrict__ gap, double* __restrict__ area, double* __restrict__ press) {
+  const int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (n >= n_marked) return;
+  double a = 0.0, g = 0.0;
+  for (int64_t p = ptr[n]; p < ptr[n + 1]; p++) {
+    a += la[(int64_t)face[p] * ndf + loc[p]];
+    g += lg[(int64_t)face[p] * ndf + loc[p]];
+  }
+  a = 0.0 + a;  // InitializeGapAreaPressure, then += thread-local
+  g = 0.0 + g;
+  area[n] = a;
+  gap[n] = g;
+  press[n] = g / a * penalty;
+}
+
+// Whole-boundary scalars: per-face partial sums added in ascending face id by one thread (deterministic).
+// mode 0: area (slot 0); mode 1: pressure integral + force (slots 1..4, active faces only); mode 2: gap norm (slot 5).
+__global__ void face_scalar_sum_kernel(int64_t NF, int mode, const double* __restrict__ fsum,
+                                       const uint8_t* __restrict__ active, double* __restrict__ scal) {
+  if (blockIdx.x || threadIdx.x) return;
+  if (mode == 0) {
+    double s = 0.0;
+    for (int64_t f = 0; f < NF; f++) s += fsum[f * 8];
+    scal[0] = 0.0 + s;
+  } else if (mode == 1) {
+    double s[4] = {0, 0, 0, 0};
+    for (int64_t f = 0; f < NF; f++)
+      if (active[f])
+        for (int k = 0; k < 4; k++) s[k] += fsum[f * 8 + 1 + k];
+    for (int k = 0; k < 4; k++) scal[1 + k] = s[k];
+  } else {
+    double s = 0.0;
+    for (int64_t f = 0; f < NF; f++) s += fsum[f * 8 + 5];
+    scal[5] = sqrt(s);
+  }
+}
+
+// ---- pass 2: MortarContact::ElementResidual<true> and ElementResidualAndGrad (mortar_contact.hpp:99-134,
+// cpp:263-295). One CTA per face; faces whose nodal pressures are all zero are skipped (IsPressureZero, cpp:321-325).
+//   stage A  task (m, q), m = tdf is the unperturbed evaluation: J(x + h e_m), |J|, unit normal, fac = w |J| p(q)
+//            -> aw[m][q][c] = normal[c] * (-fac)                       (pressure frozen, the step is on x = u + x_ref)
+//   stage B  task (m, j = i + c*ndf): R_m[j] = sum_q aw[m][q][c] * N_q[i], q ascending (Ptr_AddMult_a_VWt)
+//   stage C  K[j + m*tdf] = (R_m[j] - R[j]) * (1/h_m)
+template <int DIM, bool GRAD>
+__global__ void face_residual_kernel(int64_t NF, int ndf, int nqf, const int32_t* __restrict__ fvdofs,
+                                     const int32_t* __restrict__ flocal, const double* __restrict__ fN,
+                                     const double* __restrict__ fdN, const double* __restrict__ fw,
+                                     const double* __restrict__ xref, const double* __restrict__ u,
+                                     const double* __restrict__ press, uint8_t* __restrict__ active,
+                                     double* __restrict__ fR, double* __restrict__ fK, double* __restrict__ fsum) {
+  extern __shared__ double sm[];
+  const int tdf = DIM * ndf;
+  const int NM = GRAD ? tdf + 1 : 1;
+  double* sx = sm;               // tdf
+  double* spe = sx + tdf;        // ndf  element_pressure_
+  double* spq = spe + ndf;       // nqf  p(q) = N_q . pe
+  double* sfac = spq + nqf;      // nqf  fac(q) of the unperturbed evaluation
+  double* sR = sfac + nqf;       // tdf  base residual
+  double* saw = sR + tdf;        // NM x nqf x DIM
+  __shared__ int s_zero;
+  const int t = threadIdx.x;
+  for (int64_t f = blockIdx.x; f < NF; f += gridDim.x) {
+    if (t == 0) s_zero = 1;
+    __syncthreads();
+    for (int k = t; k < tdf; k += blockDim.x) {
+      const int32_t v = fvdofs[f * tdf + k];
+      sx[k] = u[v] + xref[v];
+    }
+    for (int i = t; i < ndf; i += blockDim.x) {
+      const double p = press[flocal[f * ndf + i]];
+      spe[i] = p;
+      if (p != 0.0) s_zero = 0;
+    }
+    __syncthreads();
+    const bool zero = s_zero != 0;
+    if (t == 0) active[f] = zero ? 0 : 1;
+    if (zero) {
+      __syncthreads();
+      continue;
+    }
+    for (int q = t; q < nqf; q += blockDim.x) {
+      const double* Nq = fN + (f * nqf + q) * ndf;
+      double p = 0.0;
+      for (int i = 0; i < ndf; i++) p += Nq[i] * spe[i];  // MortarContactWorkData::Pressure
+      spq[q] = p;
+    }
+    __syncthreads();
+    // stage A
+    for (int task = t; task < NM * nqf; task += blockDim.x) {
+      const int m = GRAD ? task / nqf : 0, q = task - m * nqf;
+      const bool base = !GRAD || m == tdf;
+      int pm = -1;
+      double xp = 0.0;
+      if (!base) {
+        const double orig = sx[m];
+        const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
+        pm = m;
+        xp = orig + h;
+      }
+      double J[2 * DIM], nrm[DIM];
+      face_J<DIM>(ndf, sx, fdN + (f * nqf + q) * ndf * (DIM - 1), pm, xp, J);
+      const double det_J = jac_weight<DIM>(J);
+      unit_normal<DIM>(J, nrm);
+      const double fac = fw[f * nqf + q] * det_J * spq[q];
+#pragma unroll
+      for (int c = 0; c < DIM; c++) saw[(m * nqf + q) * DIM + c] = nrm[c] * (-fac);
+      if (base) sfac[q] = fac;  // record == true: pressure_integral += fac, force.Add(fac, normal) -- summed below
+    }
+    __syncthreads();
+    // per-face scalars, q ascending from 0.0 (tl_force, local_pressure of one face)
+    if (t < DIM + 1) {
+      const int mb = GRAD ? tdf : 0;
+      double s = 0.0;
+      if (t == 0) {
+        for (int q = 0; q < nqf; q++) s += sfac[q];
+      } else {
+        // fac * normal[c] = -(normal[c] * (-fac)): exact negation
+        for (int q = 0; q < nqf; q++) s += -saw[(mb * nqf + q) * DIM + (t - 1)];
+      }
+      fsum[f * 8 + 1 + t] = s;
+    }
+    // stage B (base) -> sR
+    {
+      const int mb = GRAD ? tdf : 0;
+      for (int j = t; j < tdf; j += blockDim.x) {
+        const int i = j % ndf, c = j / ndf;
+        double r = 0.0;
+        for (int q = 0; q < nqf; q++) r += saw[(mb * nqf + q) * DIM + c] * fN[(f * nqf + q) * ndf + i];
+        sR[j] = r;
+        fR[f * tdf + j] = r;
+      }
+    }
+    __syncthreads();
+    if (GRAD) {
+      for (int task = t; task < tdf * tdf; task += blockDim.x) {
+        const int m = task / tdf, j = task - m * tdf;
+        const int i = j % ndf, c = j / ndf;
+        double r = 0.0;
+        for (int q = 0; q < nqf; q++) r += saw[(m * nqf + q) * DIM + c] * fN[(f * nqf + q) * ndf + i];
+        const double orig = sx[m];
+        const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
+        fK[f * (int64_t)tdf * tdf + task] = (r - sR[j]) * (1. / h);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- scatter, written as ordered gathers (faces ascending, straight onto the incoming values:
+// residual.AddElementVector / A[A_ids[k]] += K[k] * grad_factor, mortar_contact.cpp:336-340, 392-401).
+__global__ void contact_residual_gather_kernel(int dim, int64_t n_marked, int ndf, const int32_t* __restrict__ mnode,
+                                               const int64_t* __restrict__ ptr, const int32_t* __restrict__ face,
+                                               const uint8_t* __restrict__ loc, const uint8_t* __restrict__ active,
+                                               const double* __restrict__ fR, double* __restrict__ r) {
+  const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (idx >= n_marked * dim) return;
+  const int64_t n = idx / dim;
+  const int c = (int)(idx % dim);
+  const int64_t v = (int64_t)dim * mnode[n] + c;
+  double acc = r[v];
+  const int tdf = dim * ndf;
+  for (int64_t p = ptr[n]; p < ptr[n + 1]; p++)
+    if (active[face[p]]) acc += fR[(int64_t)face[p] * tdf + loc[p] + c * ndf];
+  r[v] = acc;
+}
+
+// One CTA per marked node a (block row of dim CSR rows). Thread = (column dof j = b + cj*ndf, row component ci).
+template <int DIM>
+__global__ void contact_csr_gather_kernel(int64_t n_marked, int ndf, const int32_t* __restrict__ mnode,
+                                          const int64_t* __restrict__ ptr, const int32_t* __restrict__ face,
+                                          const uint8_t* __restrict__ loc, const uint8_t* __restrict__ active,
+                                          const uint16_t* __restrict__ frank, const int64_t* __restrict__ I,
+                                          const double* __restrict__ fK, double grad_factor, double* __restrict__ A) {
+  const int tdf = DIM * ndf;
+  const int t = threadIdx.x;
+  const int j = t / DIM, ci = t % DIM;
+  const int b = j % ndf, cj = j / ndf;
+  for (int64_t n = blockIdx.x; n < n_marked; n += gridDim.x) {
+    const int64_t row = (int64_t)DIM * mnode[n] + ci;
+    for (int64_t p = ptr[n]; p < ptr[n + 1]; p++) {
+      const int64_t f = face[p];
+      if (active[f] && t < tdf * DIM) {
+        const int a = loc[p];
+        const int64_t pos = I[row] + DIM * (int64_t)frank[(f * ndf + a) * ndf + b] + cj;
+        A[pos] += fK[f * (int64_t)tdf * tdf + (int64_t)j * tdf + a + ci * ndf] * grad_factor;
+      }
+      __syncthreads();  // the next face may touch the same entries
+    }
+  }
+}
+
+// rank of face node b in the neighbour list of face node a (the block pattern built by mb2_build_pattern)
+__global__ void face_rank_kernel(int dim, int64_t NF, int ndf, const int32_t* __restrict__ fvdofs,
+                                 const int32_t* __restrict__ nnbr, const int64_t* __restrict__ nodeptr,
+                                 const int32_t* __restrict__ nbr, uint16_t* __restrict__ frank, int* __restrict__ flag) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= NF * ndf * ndf) return;
+  const int b = (int)(t % ndf), a = (int)((t / ndf) % ndf);
+  const int64_t f = t / ((int64_t)ndf * ndf);
+  const int tdf = dim * ndf;
+  const int32_t A = fvdofs[f * tdf + a] / dim, B = fvdofs[f * tdf + b] / dim;
+  const int32_t* list = nbr + nodeptr[A];
+  int lo = 0, hi = nnbr[A] - 1, pos = -1;
+  while (lo <= hi) {
+    const int mid = (lo + hi) >> 1;
+    if (list[mid] == B) { pos = mid; break; }
+    if (list[mid] < B) lo = mid + 1; else hi = mid - 1;
+  }
+  if (pos < 0) { *flag = 1; pos = 0; }
+  frank[t] = (uint16_t)pos;
+}
+
+__global__ void face_A_ids_kernel(int dim, int64_t NF, int ndf, const int32_t* __restrict__ fvdofs,
+                                  const uint16_t* __restrict__ frank, const int64_t* __restrict__ I,
+                                  int32_t* __restrict__ out) {
+  const int tdf = dim * ndf;
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= NF * tdf * tdf) return;
+  const int i = (int)(t % tdf), j = (int)((t / tdf) % tdf);
+  const int64_t f = t / ((int64_t)tdf * tdf);
+  const int a = i % ndf, ci = i / ndf, b = j % ndf, cj = j / ndf;
+  out[t] = (int32_t)(I[fvdofs[f * tdf + a] / dim * (int64_t)dim + ci] + dim * frank[(f * ndf + a) * ndf + b] + cj);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+static ContactState* CS(mb2_ctx* c) { return static_cast<ContactState*>(c->contact); }
+
+void free_contact(mb2_ctx* c) {
+  ContactState* S = CS(c);
+  if (!S) return;
+  for (void* p : {(void*)S->d_fvdofs, (void*)S->d_flocal, (void*)S->d_fN, (void*)S->d_fdN, (void*)S->d_fw, (void*)S->d_frank,
+                  (void*)S->d_mnode, (void*)S->d_mn_ptr, (void*)S->d_mn_face, (void*)S->d_mn_loc, (void*)S->d_la,
+                  (void*)S->d_lg, (void*)S->d_fsum, (void*)S->d_gap, (void*)S->d_area, (void*)S->d_press,
+                  (void*)S->d_active, (void*)S->d_fR, (void*)S->d_fK, (void*)S->d_scal})
+    if (p) cudaFree(p);
+  delete S;
+  c->contact = nullptr;
+}
+
+template <typename T>
+static int upload(mb2_ctx* c, T*& d, const T* h, size_t n) {
+  MB2_CUDA(cudaMalloc(&d, sizeof(T) * (n ? n : 1)));
+  if (h) MB2_CUDA(cudaMemcpyAsync(d, h, sizeof(T) * n, cudaMemcpyHostToDevice, c->stream));
+  return MB2_OK;
+}
+
+// MortarContact::Prepare (mortar_contact.cpp:19-133): sorted unique marked vdofs -> reduced nodal numbering
+// (local_marked_dofs_), plus what the ordered gathers need: marked node -> (face, local index) in ascending face id,
+// the CSR rank of every face node pair, and the value ranges of the marked block rows.
+int contact_set_faces(mb2_ctx* c, int64_t NF, int ndf, int nqf, const int32_t* v_dofs, const double* N,
+                      const double* dN_dxi, const double* w) {
+  free_contact(c);
+  ContactState* S = new ContactState();
+  c->contact = S;
+  const int dim = c->dim, tdf = dim * ndf;
+  S->NF = NF; S->ndf = ndf; S->nqf = nqf; S->tdf = tdf;
+  // component-major byVDIM check + marked node list
+  std::vector<int32_t> nodes((size_t)NF * ndf);
+  for (int64_t f = 0; f < NF; f++)
+    for (int k = 0; k < tdf; k++) {
+      const int32_t v = v_dofs[f * tdf + k];
+      if (v < 0 || v >= c->NV || v % dim != k / ndf || (k >= ndf && v / dim != v_dofs[f * tdf + k % ndf] / dim)) {
+        c->err = "contact face v_dofs are not component-major byVDIM ids of this space";
+        return MB2_ERR_ARG;
+      }
+      if (k < ndf) nodes[(size_t)f * ndf + k] = v / dim;
+    }
+  S->marked_nodes = nodes;
+  std::sort(S->marked_nodes.begin(), S->marked_nodes.end());
+  S->marked_nodes.erase(std::unique(S->marked_nodes.begin(), S->marked_nodes.end()), S->marked_nodes.end());
+  S->n_marked = (int64_t)S->marked_nodes.size();
+  std::vector<int32_t> local((size_t)NF * ndf);
+  std::vector<int64_t> ptr((size_t)S->n_marked + 1, 0);
+  for (size_t i = 0; i < nodes.size(); i++) {
+    local[i] = (int32_t)(std::lower_bound(S->marked_nodes.begin(), S->marked_nodes.end(), nodes[i]) - S->marked_nodes.begin());
+    ptr[(size_t)local[i] + 1]++;
+  }
+  for (int64_t n = 0; n < S->n_marked; n++) ptr[n + 1] += ptr[n];
+  std::vector<int32_t> mface((size_t)ptr[S->n_marked]);
+  std::vector<uint8_t> mloc((size_t)ptr[S->n_marked]);
+  {
+    std::vector<int64_t> fill(ptr.begin(), ptr.end() - 1);
+    for (int64_t f = 0; f < NF; f++)  // ascending face id per node
+      for (int i = 0; i < ndf; i++) {
+        const int64_t at = fill[(size_t)local[(size_t)f * ndf + i]]++;
+        mface[(size_t)at] = (int32_t)f;
+        mloc[(size_t)at] = (uint8_t)i;
+      }
+  }
+  int rc;
+  if ((rc = upload(c, S->d_fvdofs, v_dofs, (size_t)NF * tdf))) return rc;
+  if ((rc = upload(c, S->d_flocal, local.data(), local.size()))) return rc;
+  if ((rc = upload(c, S->d_fN, N, (size_t)NF * nqf * ndf))) return rc;
+  if ((rc = upload(c, S->d_fdN, dN_dxi, (size_t)NF * nqf * ndf * (dim - 1)))) return rc;
+  if ((rc = upload(c, S->d_fw, w, (size_t)NF * nqf))) return rc;
+  if ((rc = upload(c, S->d_mnode, S->marked_nodes.data(), S->marked_nodes.size()))) return rc;
+  if ((rc = upload(c, S->d_mn_ptr, ptr.data(), ptr.size()))) return rc;
+  if ((rc = upload(c, S->d_mn_face, mface.data(), mface.size()))) return rc;
+  if ((rc = upload(c, S->d_mn_loc, mloc.data(), mloc.size()))) return rc;
+  if ((rc = upload<double>(c, S->d_la, nullptr, (size_t)NF * ndf))) return rc;
+  if ((rc = upload<double>(c, S->d_lg, nullptr, (size_t)NF * ndf))) return rc;
+  if ((rc = upload<double>(c, S->d_fsum, nullptr, (size_t)NF * 8))) return rc;
+  if ((rc = upload<double>(c, S->d_gap, nullptr, (size_t)S->n_marked))) return rc;
+  if ((rc = upload<double>(c, S->d_area, nullptr, (size_t)S->n_marked))) return rc;
+  if ((rc = upload<double>(c, S->d_press, nullptr, (size_t)S->n_marked))) return rc;
+  if ((rc = upload<uint8_t>(c, S->d_active, nullptr, (size_t)NF))) return rc;
+  if ((rc = upload<double>(c, S->d_fR, nullptr, (size_t)NF * tdf))) return rc;
+  if ((rc = upload<double>(c, S->d_fK, nullptr, (size_t)NF * tdf * tdf))) return rc;
+  if ((rc = upload<double>(c, S->d_scal, nullptr, 8))) return rc;
+  if ((rc = upload<uint16_t>(c, S->d_frank, nullptr, (size_t)NF * ndf * ndf))) return rc;
+  MB2_CUDA(cudaMemsetAsync(S->d_fsum, 0, sizeof(double) * NF * 8, c->stream));
+  MB2_CUDA(cudaMemsetAsync(S->d_scal, 0, sizeof(double) * 8, c->stream));
+  MB2_CUDA(cudaMemsetAsync(S->d_active, 0, NF, c->stream));
+  // CSR ranks and the marked block rows' value ranges
+  MB2_CUDA(cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
+  const int64_t nr = NF * ndf * ndf;
+  face_rank_kernel<<<(unsigned)((nr + 255) / 256), 256, 0, c->stream>>>(dim, NF, ndf, S->d_fvdofs, c->d_nnbr, c->d_nodeptr,
+                                                                       c->d_nbr, S->d_frank, c->d_flag);
+  MB2_CUDA(cudaGetLastError());
+  int flag = 0;
+  MB2_CUDA(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  std::vector<int64_t> I((size_t)c->NV + 1);
+  MB2_CUDA(cudaMemcpyAsync(I.data(), c->d_I, sizeof(int64_t) * (c->NV + 1), cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  if (flag) {
+    c->err = "a contact face couples two nodes that share no domain element (pattern mismatch)";
+    return MB2_ERR_ARG;
+  }
+  for (int32_t n : S->marked_nodes) {
+    const int64_t off = I[(size_t)dim * n], end = I[(size_t)dim * n + dim];
+    if (!S->runs.empty() && S->runs.back().first + S->runs.back().second == off) S->runs.back().second += end - off;
+    else S->runs.push_back({off, end - off});
+  }
+  return MB2_OK;
+}
+
+template <int DIM>
+static int run_pressure(mb2_ctx* c, ContactState* S) {
+  const int threads = (std::max(S->nqf, S->ndf) + 31) / 32 * 32;
+  const size_t smem = sizeof(double) * (S->tdf + 2 * S->nqf);
+  const unsigned grid = (unsigned)std::min<int64_t>(S->NF, (int64_t)c->sm_count * 16);
+  face_gap_area_kernel<DIM, false><<<grid, threads, smem, c->stream>>>(S->NF, S->ndf, S->nqf, S->d_fvdofs, S->d_fN, S->d_fdN,
+                                                                       S->d_fw, c->d_xref, c->d_u, S->body, S->d_la,
+                                                                       S->d_lg, S->d_fsum);
+  MB2_CUDA(cudaGetLastError());
+  nodal_pressure_kernel<<<(unsigned)((S->n_marked + 127) / 128), 128, 0, c->stream>>>(
+      S->n_marked, S->ndf, S->d_mn_ptr, S->d_mn_face, S->d_mn_loc, S->d_la, S->d_lg, S->penalty, S->d_gap, S->d_area,
+      S->d_press);
+  MB2_CUDA(cudaGetLastError());
+  face_scalar_sum_kernel<<<1, 32, 0, c->stream>>>(S->NF, 0, S->d_fsum, S->d_active, S->d_scal);
+  MB2_CUDA(cudaGetLastError());
+  c->last_launches += 3;
+  return MB2_OK;
+}
+
+template <int DIM, bool GRAD>
+static int run_faces(mb2_ctx* c, ContactState* S, double gf) {
+  const int NM = GRAD ? S->tdf + 1 : 1;
+  const size_t smem = sizeof(double) * (2 * S->tdf + S->ndf + 2 * S->nqf + (size_t)NM * S->nqf * DIM);
+  auto kern = face_residual_kernel<DIM, GRAD>;
+  if (smem > 48 * 1024) MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const unsigned grid = (unsigned)std::min<int64_t>(S->NF, (int64_t)c->sm_count * 8);
+  kern<<<grid, 256, smem, c->stream>>>(S->NF, S->ndf, S->nqf, S->d_fvdofs, S->d_flocal, S->d_fN, S->d_fdN, S->d_fw,
+                                       c->d_xref, c->d_u, S->d_press, S->d_active, S->d_fR, S->d_fK, S->d_fsum);
+  MB2_CUDA(cudaGetLastError());
+  const int64_t nv = S->n_marked * DIM;
+  contact_residual_gather_kernel<<<(unsigned)((nv + 127) / 128), 128, 0, c->stream>>>(
+      DIM, S->n_marked, S->ndf, S->d_mnode, S->d_mn_ptr, S->d_mn_face, S->d_mn_loc, S->d_active, S->d_fR, c->d_r);
+  MB2_CUDA(cudaGetLastError());
+  if (GRAD) {
+    const int threads = (S->tdf * DIM + 31) / 32 * 32;
+    const unsigned g2 = (unsigned)std::min<int64_t>(S->n_marked, (int64_t)c->sm_count * 16);
+    contact_csr_gather_kernel<DIM><<<g2, threads, 0, c->stream>>>(S->n_marked, S->ndf, S->d_mnode, S->d_mn_ptr, S->d_mn_face,
+                                                                 S->d_mn_loc, S->d_active, S->d_frank, c->d_I, S->d_fK, gf,
+                                                                 c->d_A);
+    MB2_CUDA(cudaGetLastError());
+    c->last_launches += 1;
+  }
+  face_scalar_sum_kernel<<<1, 32, 0, c->stream>>>(S->NF, 1, S->d_fsum, S->d_active, S->d_scal);
+  MB2_CUDA(cudaGetLastError());
+  c->last_launches += 3;
+  return MB2_OK;
+}
+
+static int contact_ready(mb2_ctx* c) {
+  ContactState* S = CS(c);
+  if (!S) { c->err = "call mb2_contact_set_faces first"; return MB2_ERR_ARG; }
+  if (S->body.kind < 0) { c->err = "call mb2_contact_set_rigid_body first"; return MB2_ERR_ARG; }
+  if (!c->d_xref) { c->err = "call mb2_set_nodes first (reference coordinates of the face dofs)"; return MB2_ERR_ARG; }
+  return MB2_OK;
+}
+
+// AddBoundaryResidual / AddBoundaryResidualAndGrad on the resident u, r (and A): ComputePressure, then the faces.
+int contact_assemble(mb2_ctx* c, bool grad, double gf) {
+  int rc = contact_ready(c);
+  if (rc) return rc;
+  ContactState* S = CS(c);
+  c->last_launches = 0;
+  MB2_CUDA(cudaEventRecord(c->ev[0], c->stream));
+  if (c->dim == 3) {
+    if ((rc = run_pressure<3>(c, S))) return rc;
+    rc = grad ? run_faces<3, true>(c, S, gf) : run_faces<3, false>(c, S, gf);
+  } else {
+    if ((rc = run_pressure<2>(c, S))) return rc;
+    rc = grad ? run_faces<2, true>(c, S, gf) : run_faces<2, false>(c, S, gf);
+  }
+  if (rc) return rc;
+  MB2_CUDA(cudaEventRecord(c->ev[1], c->stream));
+  return MB2_OK;
+}
+
+int contact_gap_norm(mb2_ctx* c, double* out) {
+  int rc = contact_ready(c);
+  if (rc) return rc;
+  ContactState* S = CS(c);
+  const int threads = (std::max(S->nqf, S->ndf) + 31) / 32 * 32;
+  const size_t smem = sizeof(double) * (S->tdf + 2 * S->nqf);
+  const unsigned grid = (unsigned)std::min<int64_t>(S->NF, (int64_t)c->sm_count * 16);
+  if (c->dim == 3)
+    face_gap_area_kernel<3, true><<<grid, threads, smem, c->stream>>>(S->NF, S->ndf, S->nqf, S->d_fvdofs, S->d_fN, S->d_fdN,
+                                                                      S->d_fw, c->d_xref, c->d_u, S->body, S->d_la, S->d_lg,
+                                                                      S->d_fsum);
+  else
+    face_gap_area_kernel<2, true><<<grid, threads, smem, c->stream>>>(S->NF, S->ndf, S->nqf, S->d_fvdofs, S->d_fN, S->d_fdN,
+                                                                      S->d_fw, c->d_xref, c->d_u, S->body, S->d_la, S->d_lg,
+                                                                      S->d_fsum);
+  MB2_CUDA(cudaGetLastError());
+  face_scalar_sum_kernel<<<1, 32, 0, c->stream>>>(S->NF, 2, S->d_fsum, S->d_active, S->d_scal);
+  MB2_CUDA(cudaGetLastError());
+  MB2_CUDA(cudaMemcpyAsync(out, S->d_scal + 5, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  c->last_launches = 2;
+  return MB2_OK;
+}
+
+}  // namespace mb2
+
+// ---------------------------------------------------------------------------------------------
+// C ABI (include/mimi_b200.h, "contact" section)
+// ---------------------------------------------------------------------------------------------
+using mb2::ContactState;
+#define CCHECK(c) \
+  if (!(c)) return MB2_ERR_ARG
+#define CREQ(cond, msg) \
+  if (!(cond)) {        \
+    c->err = (msg);     \
+    return MB2_ERR_ARG; \
+  }
+
+extern "C" {
+
+int mb2_contact_set_faces(mb2_ctx* c, int64_t NF, int nd_f, int nq_f, const int32_t* v_dofs, const double* N,
+                          const double* dN_dxi, const double* w) {
+  CCHECK(c);
+  CREQ(c->have_pattern, "call mb2_build_pattern first");
+  CREQ(NF > 0 && nd_f > 0 && nd_f < 256 && nq_f > 0 && v_dofs && N && dN_dxi && w, "bad contact face arguments");
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::contact_set_faces(c, NF, nd_f, nq_f, v_dofs, N, dN_dxi, w);
+}
+
+int mb2_contact_set_rigid_body(mb2_ctx* c, int kind, const double* params, int nparams, double penalty) {
+  CCHECK(c);
+  ContactState* S = static_cast<ContactState*>(c->contact);
+  CREQ(S, "call mb2_contact_set_faces first");
+  CREQ(kind == MB2_RIGID_PLANE || kind == MB2_RIGID_SPHERE, "unknown rigid body kind");
+  CREQ(params && nparams >= (kind == MB2_RIGID_PLANE ? 11 : 4) && nparams <= 16, "rigid body parameter count");
+  S->body.kind = kind;
+  for (int i = 0; i < 16; i++) S->body.p[i] = i < nparams ? params[i] : 0.0;
+  S->penalty = penalty;
+  return MB2_OK;
+}
+
+int mb2_contact_n_marked_nodes(mb2_ctx* c, int64_t* n) {
+  CCHECK(c);
+  ContactState* S = static_cast<ContactState*>(c->contact);
+  CREQ(S && n, "call mb2_contact_set_faces first");
+  *n = S->n_marked;
+  return MB2_OK;
+}
+
+int mb2_contact_get_marked_v_dofs(mb2_ctx* c, int32_t* out) {
+  CCHECK(c);
+  ContactState* S = static_cast<ContactState*>(c->contact);
+  CREQ(S && out, "call mb2_contact_set_faces first");
+  for (size_t i = 0; i < S->marked_nodes.size(); i++)
+    for (int d = 0; d < c->dim; d++) out[i * c->dim + d] = c->dim * S->marked_nodes[i] + d;
+  return MB2_OK;
+}
+
+int mb2_contact_get_A_ids_i32(mb2_ctx* c, int32_t* A_ids) {
+  CCHECK(c);
+  ContactState* S = static_cast<ContactState*>(c->contact);
+  CREQ(S && A_ids, "call mb2_contact_set_faces first");
+  CREQ(c->nnz <= 2147483647LL, "nnz does not fit int");
+  const int64_t n = S->NF * S->tdf * S->tdf;
+  int32_t* d_tmp = nullptr;
+  MB2_CUDA(cudaMalloc(&d_tmp, sizeof(int32_t) * n));
+  mb2::face_A_ids_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->dim, S->NF, S->ndf, S->d_fvdofs, S->d_frank,
+                                                                            c->d_I, d_tmp);
+  MB2_CUDA(cudaGetLastError());
+  MB2_CUDA(cudaMemcpyAsync(A_ids, d_tmp, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  cudaFree(d_tmp);
+  return MB2_OK;
+}
+
+int mb2_contact_residual_device(mb2_ctx* c) {
+  CCHECK(c);
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::contact_assemble(c, false, 0.0);
+}
+int mb2_contact_residual_and_grad_device(mb2_ctx* c, double gf) {
+  CCHECK(c);
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::contact_assemble(c, true, gf);
+}
+
+int mb2_add_boundary_residual(mb2_ctx* c, const double* u, double* r) {
+  CCHECK(c);
+  CREQ(u && r, "null vector");
+  int rc;
+  if ((rc = mb2_set_u(c, u))) return rc;
+  if ((rc = mb2_set_r(c, r))) return rc;
+  if ((rc = mb2_contact_residual_device(c))) return rc;
+  return mb2_get_r(c, r);
+}
+
+// Only the CSR rows of the marked boundary nodes travel: they are the only values the faces touch.
+int mb2_add_boundary_residual_and_grad(mb2_ctx* c, const double* u, double gf, double* r, double* A) {
+  CCHECK(c);
+  CREQ(u && r && A, "null vector");
+  ContactState* S = static_cast<ContactState*>(c->contact);
+  CREQ(S, "call mb2_contact_set_faces first");
+  MB2_CUDA(cudaSetDevice(c->device));
+  int rc;
+  if ((rc = mb2_set_u(c, u))) return rc;
+  if ((rc = mb2_set_r(c, r))) return rc;
+  for (auto& run : S->runs)
+    MB2_CUDA(cudaMemcpyAsync(c->d_A + run.first, A + run.first, sizeof(double) * run.second, cudaMemcpyHostToDevice, c->stream));
+  if ((rc = mb2_contact_residual_and_grad_device(c, gf))) return rc;
+  for (auto& run : S->runs)
+    MB2_CUDA(cudaMemcpyAsync(A + run.first, c->d_A + run.first, sizeof(double) * run.second, cudaMemcpyDeviceToHost, c->stream));
+  return mb2_get_r(c, r);
+}
+
+int mb2_contact_get_nodal(mb2_ctx* c, double* gap, double* area, double* pressure) {
+  CCHECK(c);
+  ContactState* S = static_cast<ContactState*>(c->contact);
+  CREQ(S, "call mb2_contact_set_faces first");
+  const size_t b = sizeof(double) * (size_t)S->n_marked;
+  if (gap) MB2_CUDA(cudaMemcpyAsync(gap, S->d_gap, b, cudaMemcpyDeviceToHost, c->stream));
+  if (area) MB2_CUDA(cudaMemcpyAsync(area, S->d_area, b, cudaMemcpyDeviceToHost, c->stream));
+  if (pressure) MB2_CUDA(cudaMemcpyAsync(pressure, S->d_press, b, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+
+int mb2_contact_last_scalars(mb2_ctx* c, double* out5) {
+  CCHECK(c);
+  ContactState* S = static_cast<ContactState*>(c->contact);
+  CREQ(S && out5, "call mb2_contact_set_faces first");
+  MB2_CUDA(cudaMemcpyAsync(out5, S->d_scal, sizeof(double) * 5, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+
+int mb2_contact_gap_norm(mb2_ctx* c, const double* u, double* out) {
+  CCHECK(c);
+  CREQ(u && out, "null argument");
+  MB2_CUDA(cudaSetDevice(c->device));
+  int rc;
+  if ((rc = mb2_set_u(c, u))) return rc;
+  return mb2::contact_gap_norm(c, out);
+}
+
+}  // extern "C"

@@ -44,7 +44,8 @@ def contact_main():
             writer(mesh)
             D = O.run_ref_contact(mesh, elevate, refine, os.path.join(tmp, "c"), attr, penalty, spec, gf=gf)
             out = {k: v for k, v in D.items() if isinstance(v, np.ndarray)}
-            out["meta"] = np.array([D["dim"], D["NF"], D["ndf"], D["nqf"], D["NV"], D["nnz"], D["n_marked_nodes"]], np.int64)
+            out["meta"] = np.array([D["dim"], D["NF"], D["ndf"], D["nqf"], D["NV"], D["nnz"], D["n_marked_nodes"], D["nd"], D["nq"]],
+                                   np.int64)
             out["gf"], out["penalty"] = np.float64(gf), np.float64(penalty)
             out["body_kind"] = np.array(spec[0])
             out["body_params"] = np.array(spec[1], np.float64)

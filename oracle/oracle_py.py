@@ -289,6 +289,7 @@ def load_contact_dump(d):
         a = np.fromfile(os.path.join(d, name), dtype=dt)
         return a.reshape(shape) if shape else a
 
+    out["v_dofs"] = rd("v_dofs.i32", np.int32, (meta["NE"], dim * meta["nd"]))
     out["marked"] = rd("c_marked.i32", np.int32)
     out["c_v_dofs"] = rd("c_v_dofs.i32", np.int32, (NF, tdf))
     out["c_A_ids"] = rd("c_A_ids.i32", np.int32, (NF, tdf * tdf))

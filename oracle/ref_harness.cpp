@@ -376,6 +376,14 @@ int main(int argc, char** argv) {
         std::memcpy(&dxi[fq * ndf * (dim - 1)], qd.dN_dxi.GetData(), sizeof(double) * ndf * (dim - 1));
       }
     }
+    {  // domain connectivity (the device builds the CSR pattern from it)
+      auto& eqd = pre.GetElementQuadData("domain");
+      const int tdof = eqd[0].GetElementData().n_tdof;
+      std::vector<int> dvd((size_t)pre.n_elements_ * tdof);
+      for (int e = 0; e < pre.n_elements_; ++e)
+        std::memcpy(&dvd[(size_t)e * tdof], eqd[e].GetElementData().v_dofs.GetData(), sizeof(int) * tdof);
+      dump(out, "v_dofs.i32", dvd.data(), dvd.size());
+    }
     dump(out, "c_marked.i32", marked.data(), marked.size());
     dump(out, "c_v_dofs.i32", vd.data(), vd.size());
     dump(out, "c_A_ids.i32", aid.data(), aid.size());
@@ -418,7 +426,9 @@ int main(int argc, char** argv) {
     std::ofstream m(out + "/meta.json");
     m << "{\"NV\": " << NV << ", \"NE\": " << pre.n_elements_ << ", \"nnz\": " << nnz << ", \"dim\": " << dim
       << ", \"NF\": " << NF << ", \"ndf\": " << ndf << ", \"nqf\": " << nqf << ", \"gf\": " << gf
-      << ", \"penalty\": " << penalty << ", \"n_marked_nodes\": " << integ->Area().Size() << "}\n";
+      << ", \"penalty\": " << penalty << ", \"n_marked_nodes\": " << integ->Area().Size()
+      << ", \"nd\": " << pre.GetElementQuadData("domain")[0].GetElementData().n_dof
+      << ", \"nq\": " << pre.GetElementQuadData("domain")[0].n_quad << "}\n";
     return 0;
   }
   if (mode == "time") {

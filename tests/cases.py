@@ -28,8 +28,8 @@ CONTACT_CASES = ["contact_cube_p2_n2_plane", "contact_cube_p2_n4_sphere", "conta
 def load_contact_golden(name):
     z = np.load(os.path.join(GOLDEN, name + ".npz"))
     D = {k: z[k] for k in z.files}
-    dim, NF, ndf, nqf, NV, nnz, nm = (int(x) for x in D["meta"])
-    D.update(dim=dim, NF=NF, ndf=ndf, nqf=nqf, NV=NV, nnz=nnz, n_marked_nodes=nm, gf=float(D["gf"]),
+    dim, NF, ndf, nqf, NV, nnz, nm, nd, nq = (int(x) for x in D["meta"])
+    D.update(dim=dim, NF=NF, ndf=ndf, nqf=nqf, NV=NV, nnz=nnz, n_marked_nodes=nm, nd=nd, nq=nq, gf=float(D["gf"]),
              penalty=float(D["penalty"]), body=(str(D["body_kind"]), [float(x) for x in D["body_params"]]))
     return D
 

@@ -1,0 +1,123 @@
+"""GPU: rigid-body mortar contact through the C ABI against golden vectors dumped
+from the unmodified reference's MortarContact (src/mimi/integrators/mortar_contact.cpp) and against the C oracle.
+Bar: index maps bit-exact; nodal gap / area / pressure, residual and Jacobian bit-exact in FP64 (north_star: 1e-12
+relative); whole-boundary scalars (area, force, pressure integral, gap norm) within 1e-12 relative -- they are summed
+per face and then across faces, not as the reference's single running sum."""
+import numpy as np
+import pytest
+
+from mimi_b200 import capi
+from oracle import oracle_py as O
+from tests.cases import CONTACT_CASES, load_contact_golden
+
+pytestmark = pytest.mark.gpu
+
+KIND = {"plane": capi.MB2_RIGID_PLANE, "sphere": capi.MB2_RIGID_SPHERE}
+
+
+def setup_contact(ctx, D, body=None, penalty=None):
+    body = body or D["body"]
+    ctx.set_connectivity(D["dim"], D["nd"], D["nq"], D["NV"], D["v_dofs"])
+    ctx.set_nodes(D["x_ref"])
+    ctx.build_pattern()
+    ctx.contact_set_faces(D["c_v_dofs"], D["c_N"], D["c_dN_dxi"], D["c_w"])
+    ctx.contact_set_rigid_body(KIND[body[0]], O.rigid_params(D["dim"], body), penalty or D["penalty"])
+    return ctx
+
+
+def close(a, b, tol=1e-12):
+    return np.abs(np.asarray(a) - np.asarray(b)).max() <= tol * max(np.abs(np.asarray(b)).max(), 1e-300)
+
+
+@pytest.mark.parametrize("name", CONTACT_CASES)
+def test_contact_golden(ctx_factory, name):
+    D = load_contact_golden(name)
+    ctx = setup_contact(ctx_factory(), D)
+    # A11 Prepare: index maps
+    I, J = ctx.get_pattern()
+    assert np.array_equal(I, D["I"]) and np.array_equal(J, D["J"])
+    assert ctx.n_marked == D["n_marked_nodes"]
+    assert np.array_equal(ctx.contact_marked_v_dofs(), D["c_marked_v_dofs"])
+    assert np.array_equal(ctx.contact_A_ids(), D["c_A_ids"])
+    # A12 + A13 residual, added on top of the domain residual
+    r = D["c_r0"].copy()
+    ctx.add_boundary_residual(D["u"], r)
+    gap, area, pr = ctx.contact_nodal()
+    assert np.array_equal(gap, D["c_gap"]) and np.array_equal(area, D["c_area"]) and np.array_equal(pr, D["c_pressure"])
+    assert np.array_equal(r, D["c_r"])
+    s = ctx.contact_last_scalars()
+    assert close(s[0], D["c_scalars"][0]) and close(s[1], D["c_scalars"][1]) and close(s[2:5], D["c_scalars"][2:5])
+    # A13 residual + FD tangent, added onto the mass values
+    r2 = np.zeros(D["NV"])
+    A = D["mass"].copy()
+    ctx.add_boundary_residual_and_grad(D["u"], D["gf"], r2, A)
+    assert np.array_equal(r2, D["c_r2"])
+    assert np.abs(A - D["c_A"]).max() <= 1e-12 * np.abs(D["c_A"]).max()   # north_star tolerance
+    assert np.array_equal(A, D["c_A"])                                     # and in fact bit-exact
+    assert np.abs(A - D["mass"]).max() > 0
+    # A14 GapNorm
+    assert close(ctx.contact_gap_norm(D["u"]), D["c_scalars"][5])
+
+
+def test_contact_moving_body_vs_oracle(ctx_factory):
+    """The rigid body moves between steps (examples/nl_contact.py moves the spline every step): no contact at all
+    (every face skipped), then deeper penetration with another penalty; checked against the C oracle."""
+    D = load_contact_golden("contact_cube_p2_n4_sphere")
+    ctx = setup_contact(ctx_factory(), D)
+    dim = 3
+    local, nm, _ = O.contact_prepare(dim, D["c_v_dofs"])
+    for zc, penalty in ((2.5, 1e5), (1.998, 3e6)):
+        body = ("sphere", [0.5, 0.5, zc, 1.0])
+        ctx.contact_set_rigid_body(KIND["sphere"], O.rigid_params(dim, body), penalty)
+        gap, area, pr, tot = O.contact_pressure(dim, D["c_v_dofs"], local, nm, D["c_N"], D["c_dN_dxi"], D["c_w"],
+                                                D["c_x_ref"], D["u"], O.rigid_from_spec(dim, body), penalty)
+        r_o = D["c_r0"].copy()
+        A_o = D["mass"].copy()
+        O.contact_assemble(dim, D["c_v_dofs"], local, D["c_A_ids"], D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"],
+                           D["u"], pr, True, 0.25, r_o, A_o)
+        r = D["c_r0"].copy()
+        A = D["mass"].copy()
+        ctx.add_boundary_residual_and_grad(D["u"], 0.25, r, A)
+        assert np.array_equal(ctx.contact_nodal()[2], pr)
+        assert np.array_equal(r, r_o) and np.array_equal(A, A_o)
+        if zc > 2.4:
+            assert not pr.any() and np.array_equal(A, D["mass"])     # no contact: nothing is touched
+        else:
+            assert (pr != 0).sum() > 8
+
+
+def test_contact_after_domain_on_device(ctx_factory):
+    """Domain + contact assembled back to back on the resident r / A (the order forms::Nonlinear::AddMultGrad uses,
+    src/mimi/forms/nonlinear.hpp:53-116), vs oracle domain + oracle contact."""
+    D = load_contact_golden("contact_cube_p2_n2_plane")
+    ctx = setup_contact(ctx_factory(), D)
+    from tests.cases import load_golden
+    G = load_golden("cube_p2_n2")
+    assert np.array_equal(G["v_dofs"], D["v_dofs"])
+    ctx.upload_quad_tables(G["dN_dX"], G["w"], G["detJ"])
+    lam, mu = O.lame()
+    ctx.set_material(0, [lam, mu])
+    ctx.set_u(D["u"]); ctx.set_r(None); ctx.set_A(D["mass"])
+    ctx.assemble_residual_and_grad_device(0.7)
+    ctx.contact_residual_and_grad_device(0.7)
+    r, A = ctx.get_r(), ctx.get_A()
+    r_o, A_o = O.assemble_residual_and_grad(3, 27, 64, O.mat(0), G["v_dofs"], G["A_ids"], G["dN_dX"], G["w"], G["detJ"],
+                                            D["u"], 0.7, D["mass"])
+    local, nm, _ = O.contact_prepare(3, D["c_v_dofs"])
+    pr = D["c_pressure"]
+    O.contact_assemble(3, D["c_v_dofs"], local, D["c_A_ids"], D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"], D["u"], pr,
+                       True, 0.7, r_o, A_o)
+    assert np.array_equal(r, r_o) and np.array_equal(A, A_o)
+
+
+def test_contact_call_order_errors(ctx_factory):
+    D = load_contact_golden("contact_quad_p2_n4_plane_clamped")
+    ctx = ctx_factory()
+    ctx.set_connectivity(D["dim"], D["nd"], D["nq"], D["NV"], D["v_dofs"])
+    with pytest.raises(capi.Mb2Error):
+        ctx.contact_set_faces(D["c_v_dofs"], D["c_N"], D["c_dN_dxi"], D["c_w"])   # pattern first
+    ctx.build_pattern()
+    ctx.contact_set_faces(D["c_v_dofs"], D["c_N"], D["c_dN_dxi"], D["c_w"])
+    r = np.zeros(D["NV"])
+    with pytest.raises(capi.Mb2Error):
+        ctx.add_boundary_residual(D["u"], r)                                         # no rigid body yet
