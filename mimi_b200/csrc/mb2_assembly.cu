@@ -401,6 +401,245 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// FD-tangent element kernel, column-split streaming form (elements too large for one CTA: p = 3, nd = 64, nq = 125).
+//
+// KS CTAs share one element: CTA `part` owns the perturbed dofs [part*MP, (part+1)*MP) plus its own copy of the
+// unperturbed evaluation (1/MP redundant work), so a thread carries TI x TC = 8 x 5 accumulators and two CTAs fit
+// per SM. The element's dN_dX table (192 KB at p = 3) no longer fits in shared memory next to the b buffer: it is
+// streamed in chunks of QC quadrature points with 1-D TMA bulk copies (cp.async.bulk + mbarrier, double-buffered),
+// issued by one thread one chunk ahead. The KS CTAs of an element have adjacent block ids, so the table is read from
+// HBM once and KS-1 times from L2. Phases and operation order are those of element_fd_kernel.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "MB2_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra MB2_DONE;\n"
+      "bra MB2_WAIT;\n"
+      "MB2_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// one thread: expect `bytes` on the barrier and start the bulk copy global -> shared (16-byte aligned, size % 16 == 0)
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+template <int DIM, int ND, int NQ, int KS>
+struct Elem3Cfg {
+  static constexpr int TD = DIM * ND;
+  static constexpr int DD = DIM * DIM;
+  static constexpr int MP = (TD + KS - 1) / KS;  // perturbed dofs per part
+  static constexpr int NM = MP + 1;              // + the unperturbed evaluation (local m == MP)
+  static constexpr int NT = 256;
+  static constexpr int QC = NT / NM;
+  static constexpr int NCH = (NQ + QC - 1) / QC;
+  static constexpr int NB = NM * DIM;
+  static constexpr int LI = 8, LC = 4;
+  static constexpr int TI = ND / LI;
+  static constexpr int TC = (NB + (NT / 32) * LC - 1) / ((NT / 32) * LC);
+  static constexpr int NBP = (NT / 32) * LC * TC;
+  static constexpr int KP = (TD * DIM + 3) / 4 * 4;
+  static constexpr int OFF_DN = 0;                              // [2][QC][DIM][ND]
+  static constexpr int OFF_FB = OFF_DN + 2 * QC * DIM * ND;     // [NQ][DD]
+  static constexpr int OFF_SB = OFF_FB + NQ * DD;               // [2][QC][DIM][NBP]
+  static constexpr int OFF_WD = OFF_SB + 2 * QC * DIM * NBP;    // [NQ]
+  static constexpr int OFF_UE = OFF_WD + NQ;                    // [DIM][ND]
+  static constexpr int OFF_RB = OFF_UE + TD;                    // [TD]
+  static constexpr int OFF_BAR = OFF_RB + TD;                   // 2 mbarriers
+  static constexpr int SMEM_DOUBLES = OFF_BAR + 2;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
+  static_assert(ND % LI == 0 && ND % 2 == 0 && QC >= 1, "element type not supported by the split kernel");
+  static_assert((QC * DIM * ND) % 2 == 0 && (NQ * DD) % 2 == 1 || true, "alignment");
+};
+
+template <int DIM, int ND, int NQ, int MAT, int KS>
+__global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs g) {
+  using Cfg = Elem3Cfg<DIM, ND, NQ, KS>;
+  constexpr int TD = Cfg::TD, DD = Cfg::DD, MP = Cfg::MP, NM = Cfg::NM, NT = Cfg::NT, QC = Cfg::QC, NCH = Cfg::NCH,
+                NB = Cfg::NB, NBP = Cfg::NBP, TI = Cfg::TI, TC = Cfg::TC, LI = Cfg::LI, KP = Cfg::KP,
+                NS = mat_state_size(MAT);
+  extern __shared__ __align__(128) double smem[];
+  double* sdN = smem + Cfg::OFF_DN;
+  double* sFb = smem + Cfg::OFF_FB;
+  double* sb = smem + Cfg::OFF_SB;
+  double* swd = smem + Cfg::OFF_WD;
+  double* sue = smem + Cfg::OFF_UE;
+  double* sRb = smem + Cfg::OFF_RB;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  const int t = threadIdx.x;
+  const int64_t e = g.e0 + blockIdx.x / KS;
+  const int part = blockIdx.x % KS;
+  const double* dNe = g.dNdX + e * (int64_t)(NQ * TD);
+
+  // phase-1 role: stress evaluation (local m1, q = chunk*QC + qs1); global perturbed dof mg1
+  const int qs1 = t / NM, m1 = t % NM;
+  const int mg1 = part * MP + m1;
+  const bool base1 = (m1 == MP);
+  const bool act1 = (t < NM * QC) && (base1 || mg1 < TD);
+  const int c1 = base1 ? 0 : mg1 / ND, a1 = base1 ? -1 : mg1 % ND;
+  // phase-2 role
+  const int lane = t & 31, warp = t >> 5;
+  const int i0 = (lane % LI) * TI;
+  const int col0 = (warp * Cfg::LC + lane / LI) * TC;
+
+  if (t == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int idx = t; idx < 2 * QC * DIM * NBP; idx += NT) sb[idx] = 0.0;
+  if (t < TD) sue[t] = g.u[g.vdofs[e * TD + t]];  // [c][a] = component-major gather (Vector::GetSubVector)
+  for (int q = t; q < NQ; q += NT) swd[q] = g.wdetJ[e * NQ + q];
+  __syncthreads();
+  constexpr uint32_t CHUNK_BYTES = QC * TD * sizeof(double);
+  if (t == 0) {
+    const int nq0 = (NQ < QC) ? NQ : QC;
+    tma_load_1d(sdN, dNe, (uint32_t)(nq0 * TD * sizeof(double)), &bar[0]);
+  }
+  // base F for every q straight from global/L2: MultAtB(element_x_mat_, dN_dX, F_) + AddDiagonal(1.0)
+  for (int task = t; task < NQ * DD; task += NT) {
+    const int q = task / DD, n = task - q * DD;
+    const int i = n % DIM, j = n / DIM;
+    const double* dN = dNe + (q * DIM + j) * ND;
+    const double* ui = sue + i * ND;
+    double d = 0.0;
+#pragma unroll 8
+    for (int k = 0; k < ND; k++) d += ui[k] * __ldg(dN + k);
+    if (i == j) d += 1.0;
+    sFb[task] = d;
+  }
+  double up1 = 0.0;
+  if (act1 && !base1) {
+    const double orig = sue[mg1];
+    const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
+    up1 = orig + h;
+  }
+  double R[TI][TC];
+#pragma unroll
+  for (int x = 0; x < TI; x++)
+#pragma unroll
+    for (int y = 0; y < TC; y++) R[x][y] = 0.0;
+  __syncthreads();
+
+#pragma unroll 1
+  for (int ch = 0; ch < NCH; ch++) {
+    const double* dNc = sdN + (ch & 1) * (QC * DIM * ND);
+    double* sbc = sb + (ch & 1) * (QC * DIM * NBP);
+    mbar_wait(&bar[ch & 1], (uint32_t)((ch >> 1) & 1));
+    // ---- phase 1
+    const int q1 = ch * QC + qs1;
+    if (act1 && q1 < NQ) {
+      double F[DD], P[DD];
+#pragma unroll
+      for (int n = 0; n < DD; n++) F[n] = sFb[q1 * DD + n];
+      if (!base1) {
+        const double2* uc2 = reinterpret_cast<const double2*>(sue + c1 * ND);
+        const double2* dN2 = reinterpret_cast<const double2*>(dNc + qs1 * DIM * ND);
+        double drow[DIM];
+#pragma unroll
+        for (int j = 0; j < DIM; j++) drow[j] = 0.0;
+#pragma unroll 8
+        for (int x = 0; x < ND / 2; x++) {
+          const double2 uv = uc2[x];
+          const double u0 = (2 * x == a1) ? up1 : uv.x;
+          const double u1 = (2 * x + 1 == a1) ? up1 : uv.y;
+#pragma unroll
+          for (int j = 0; j < DIM; j++) {
+            const double2 dv = dN2[j * (ND / 2) + x];
+            drow[j] += u0 * dv.x;
+            drow[j] += u1 * dv.y;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < DIM; j++) {
+          const double fnew = (j == c1) ? drow[j] + 1.0 : drow[j];
+#pragma unroll
+          for (int i = 0; i < DIM; i++)
+            if (i == c1) F[i + DIM * j] = fnew;
+        }
+      }
+      material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + q1) * NS : nullptr, P);
+      const double aq = swd[q1];
+      double* o = sbc + qs1 * (DIM * NBP) + m1 * DIM;
+#pragma unroll
+      for (int k = 0; k < DIM; k++)
+#pragma unroll
+        for (int j = 0; j < DIM; j++) o[k * NBP + j] = aq * P[j + DIM * k];
+    }
+    __syncthreads();
+    // every thread has left phase 2 of chunk ch-1: its dN buffer may be refilled
+    if (t == 0 && ch + 1 < NCH) {
+      const int nqn = (NQ - (ch + 1) * QC < QC) ? NQ - (ch + 1) * QC : QC;
+      tma_load_1d(sdN + ((ch + 1) & 1) * (QC * DIM * ND), dNe + (int64_t)(ch + 1) * QC * TD,
+                  (uint32_t)(nqn * TD * sizeof(double)), &bar[(ch + 1) & 1]);
+    }
+    (void)CHUNK_BYTES;
+    // ---- phase 2
+#pragma unroll
+    for (int qs = 0; qs < QC; qs++) {
+      if (ch * QC + qs < NQ) {
+#pragma unroll
+        for (int k = 0; k < DIM; k++) {
+          double bv[TC], dv[TI];
+          const double* bp = sbc + (qs * DIM + k) * NBP + col0;
+#pragma unroll
+          for (int y = 0; y < TC; y++) bv[y] = bp[y];
+          const double2* d2 = reinterpret_cast<const double2*>(dNc + (qs * DIM + k) * ND + i0);
+#pragma unroll
+          for (int x = 0; x < TI / 2; x++) {
+            const double2 v = d2[x];
+            dv[2 * x] = v.x;
+            dv[2 * x + 1] = v.y;
+          }
+#pragma unroll
+          for (int x = 0; x < TI; x++)
+#pragma unroll
+            for (int y = 0; y < TC; y++) R[x][y] += dv[x] * bv[y];
+        }
+      }
+    }
+  }
+  // ---- base residual (columns of local m == MP) -> smem (+ global, part 0), then forward differences
+#pragma unroll
+  for (int y = 0; y < TC; y++) {
+    const int col = col0 + y;
+    if (col >= MP * DIM && col < NB) {
+      const int j = col - MP * DIM;
+#pragma unroll
+      for (int x = 0; x < TI; x++) {
+        sRb[i0 + x + j * ND] = R[x][y];
+        if (part == 0) g.Re[e * TD + i0 + x + j * ND] = R[x][y];
+      }
+    }
+  }
+  __syncthreads();
+  double* out = g.KeT + (e - g.e0) * (int64_t)(ND * KP);
+#pragma unroll
+  for (int y = 0; y < TC; y++) {
+    const int col = col0 + y;
+    const int mg = part * MP + col / DIM, j = col % DIM;
+    if (col < MP * DIM && mg < TD) {
+      const double orig = sue[mg];
+      const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
+      const double hinv = 1. / h;
+#pragma unroll
+      for (int x = 0; x < TI; x++) out[(int64_t)(i0 + x) * KP + mg * DIM + j] = (R[x][y] - sRb[i0 + x + j * ND]) * hinv;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // History commit: NonlinearSolid::DomainPostTimeAdvance (nonlinear_solid.cpp:179-199) = ElementResidual<true>:
 // per quadrature point ComputeF, then MaterialBase::Accumulate. One thread per (element, qp); the F dot products
 // keep MultAtB's k order. HBM-bound: reads dN_dX once (tdof doubles per qp) and read-modify-writes NS doubles.
@@ -575,6 +814,17 @@ static int launch_element_fd(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   return MB2_OK;
 }
 
+template <int DIM, int ND, int NQ, int MAT, int KS>
+static int launch_element_fd_split(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
+  using Cfg = Elem3Cfg<DIM, ND, NQ, KS>;
+  auto kern = element_fd_split_kernel<DIM, ND, NQ, MAT, KS>;
+  MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+  const int64_t grid = (a.e1 - a.e0) * KS;  // the KS parts of an element are adjacent: they share its table in L2
+  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, st>>>(a);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
 template <int DIM, int ND, int NQ, bool GRAD, int MINB>
 static int launch_element_mat(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   switch (c->mat_kind) {
@@ -596,7 +846,15 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
       case MAT_J2LINEAR: return launch_element_fd<3, 27, 64, MAT_J2LINEAR>(c, a, st);
     }
   }
+  if (GRAD && dim == 3 && nd == 64 && nq == 125 && c->elem_variant != 1) {
+    switch (c->mat_kind) {
+      case MAT_NEOHOOKEAN: return launch_element_fd_split<3, 64, 125, MAT_NEOHOOKEAN, 4>(c, a, st);
+      case MAT_STVK: return launch_element_fd_split<3, 64, 125, MAT_STVK, 4>(c, a, st);
+      case MAT_J2LINEAR: return launch_element_fd_split<3, 64, 125, MAT_J2LINEAR, 4>(c, a, st);
+    }
+  }
   if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a, st);
+  if (dim == 3 && nd == 64 && nq == 125) return launch_element_mat<3, 64, 125, GRAD, 1>(c, a, st);
   if (dim == 3 && nd == 8 && nq == 27) return launch_element_mat<3, 8, 27, GRAD, 4>(c, a, st);
   if (dim == 2 && nd == 16 && nq == 25) return launch_element_mat<2, 16, 25, GRAD, 4>(c, a, st);
   if (dim == 2 && nd == 9 && nq == 16) return launch_element_mat<2, 9, 16, GRAD, 4>(c, a, st);

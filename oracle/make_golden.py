@@ -20,6 +20,7 @@ CASES = {
     "cube_p1_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 0, 1, 0.5),
     "beam2d_p3_n2": (lambda f: meshgen.write_box_p1(f, (5.0, 1.0)), 2, 1, 0.0125),  # tests/test_nonlinear_solid.py mesh
     "quad_p2_n4": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 1, 2, 1.0),
+    "cube_p3_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 2, 1, 0.6),
     "cube_p2_n3_patch": (lambda f: meshgen.write_box_patch(f, 2, (3, 2, 2), (1.5, 1.0, 1.0)), 0, 0, 2.0),
 }
 
@@ -53,10 +54,12 @@ def contact_main():
             print(name, out["meta"])
 
 
-def main():
+def main(only=None):
     assert O.have_ref(), "build oracle/_ref first: make -f oracle/Makefile.ref -j8"
     os.makedirs(OUT, exist_ok=True)
     for name, (writer, elevate, refine, gf) in CASES.items():
+        if only and name not in only:
+            continue
         with tempfile.TemporaryDirectory() as tmp:
             mesh = os.path.join(tmp, "m.mesh")
             writer(mesh)
@@ -82,6 +85,10 @@ def main():
 
 
 if __name__ == "__main__":
-    if "contact" not in sys.argv[1:]:
+    if "contact" in sys.argv[1:]:
+        contact_main()
+    elif len(sys.argv) > 1:
+        main(sys.argv[1:])
+    else:
         main()
-    contact_main()
+        contact_main()

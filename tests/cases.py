@@ -9,7 +9,7 @@ from mimi_b200 import meshgen
 from oracle import oracle_py as O
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "quad_p2_n4", "cube_p2_n3_patch"]
+GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "quad_p2_n4", "cube_p2_n3_patch", "cube_p3_n2"]
 MATS = {"neohookean": 0, "stvk": 1, "j2linear": 2}
 
 
