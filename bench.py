@@ -36,11 +36,14 @@ UNIT = "qp/s"
 
 
 # flops per quadrature point, counted mul/add/div = 1 each
-def flops_per_qp(p, dim=3):
+STRESS_FLOPS = {"neohookean": 204, "stvk": 166}
+
+
+def flops_per_qp(p, dim=3, material="neohookean"):
     nd = (p + 1) ** dim
     tdof = dim * nd
     F = 2 * dim * dim * nd + dim           # MultAtB + AddDiagonal
-    stress = 204                           # NeoHookean: det 14, mu/J 1, FF^T 54, coeff 3, axpby 27, inverse 42, sigma F^-T 54, J* 9
+    stress = STRESS_FLOPS[material]        # NeoHookean: det 14, mu/J 1, FF^T 54, coeff 3, axpby 27, inverse 42, sigma F^-T 54, J* 9; StVK 166
     acc = dim * dim * (1 + 2 * nd) + 1     # AddMult_a_ABt + (w * detJ)
     algorithmic = (tdof + 1) * (F + stress + acc)
     # executed by the CUDA kernel: a perturbed dof only changes one row of F (the others are bit-identical
@@ -155,7 +158,7 @@ def reference_arm(args):
 # ----------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------
-def build_problem(ctx, n, p, rank=0, world=1, uid=None):
+def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean"):
     """Synthetic C3-style block in MFEM's numbering; tables regenerated on the device. world > 1: the global mesh
     is n x n x (n*world) spans (weak scaling), cut into z-slabs of n layers; rank g computes slab g, owns the nodes
     whose lowest element it computes, and receives the raw element matrices of the next slab's first p layers."""
@@ -179,7 +182,7 @@ def build_problem(ctx, n, p, rank=0, world=1, uid=None):
     young, poisson = 2100.0, 0.3
     lam = young * poisson / ((1 + poisson) * (1 - 2 * poisson))
     mu = young / (2.0 * (1.0 + poisson))
-    ctx.set_material(capi.MB2_MAT_NEOHOOKEAN, [lam, mu])
+    ctx.set_material({"neohookean": capi.MB2_MAT_NEOHOOKEAN, "stvk": capi.MB2_MAT_STVK}[material], [lam, mu])
     u = meshgen.synth_u(M["NV"])
     # face x = 0 clamped: exactly 0 (h = 1e-10 branch of the FD rule)
     x = M["x_ref"].reshape(-1, 3)
@@ -207,7 +210,7 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    n, p = args.n, 2
+    n, p = args.n, args.p
     stream = torch.cuda.Stream()            # the library launches on this stream, so torch events see its work
     ctx = capi.Context(local, stream=stream.cuda_stream)
     ctx.set_option("elem_variant", args.variant)
@@ -215,7 +218,7 @@ def gpu_arm(args):
     if world > 1:
         uid = [capi.mg_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
-    M = build_problem(ctx, n, p, rank, world, uid[0])
+    M = build_problem(ctx, n, p, rank, world, uid[0], args.material)
     NE, nq, NV, nnz = M["n_compute"], M["nq"], M["NV"], M["nnz"]     # NE = elements this rank computes
     ctx.set_u(M["u"])
     ctx.set_r(None)
@@ -280,7 +283,7 @@ def gpu_arm(args):
                "call": "mb2_add_domain_residual_and_grad(u, 1.0, r, A) with pinned host buffers"}
 
     if rank == 0:
-        alg, exe, fd = flops_per_qp(p)
+        alg, exe, fd = flops_per_qp(p, 3, args.material)
         el_ms = float(np.mean(t_el))
         qp_rate_kernel = float(NE) * nq / (el_ms * 1e-3)
         exe_qp = exe + fd / nq
@@ -293,7 +296,7 @@ def gpu_arm(args):
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         tdof = 3 * M["nd"]
         bytes_el = NE * (8.0 * nq * (tdof + 1) + 4 * tdof + 8 * tdof + 8 * tdof * tdof + 8 * tdof)
-        roofline = {"bound": "fp64", "kernel": "element_kernel<3,27,64,NeoHookean,GRAD>", "achieved": achieved, "peak": peak_nofma,
+        roofline = {"bound": "fp64", "kernel": ("element_fd_kernel<3,27,64,%s>" if p == 2 else "element_fd_split_kernel<3,64,125,%s,4>") % args.material, "achieved": achieved, "peak": peak_nofma,
                     "unit": "TFLOP/s", "frac": achieved / peak_nofma, "traffic": None,
                     "peak_source": "mb2_measure_fp64_peak(fma=0) on this GPU in this run: DMUL+DADD pairs = the only "
                                    "mix a bit-exact non-FMA kernel may issue (DFMA peak %.2f; MEASURED_PEAKS.json has no FP64 entry)" % peak_fma,
@@ -306,18 +309,19 @@ def gpu_arm(args):
         if not args.no_cpu:
             try:
                 cores = host_cores()
-                S = run_reference_sample(args.ref_n, 2, cores, warmup=1)
+                S = run_reference_sample(args.ref_n, 2, cores, warmup=1, p=p, material=args.material)
                 cpu = {"value": S["value_mean"], "unit": UNIT, "cores": cores, "kind": "reference",
-                       "sample": "unmodified reference (oracle/_ref/mimi_ref, OpenMP %d threads) on p=2 NeoHookean cube %d^3 = %d el, "
+                       "sample": "unmodified reference (oracle/_ref/mimi_ref, OpenMP %d threads) on p=%d %s cube %d^3 = %d el, "
                                  "mean of 2 steps after 1 warm-up; residual-only best %.3e qp/s" % (
-                                     cores, args.ref_n, S["NE"], S["qp"] / S["t_res_best"])}
+                                     cores, p, args.material, args.ref_n, S["NE"], S["qp"] / S["t_res_best"])}
             except Exception as ex:  # the checker binary is absent: report that, never substitute
                 cpu = {"value": None, "unit": UNIT, "cores": host_cores(), "kind": "reference", "sample": "unavailable: %s" % ex}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
-                "config": {"workload": "C3: 3D unit-cube B-spline patch p=2, %d^3 = %d elements x %d qp per GPU, compressible NeoHookean, "
-                                       "one residual+tangent assembly into CSR (nnz=%d per GPU), MFEM dof numbering" % (n, NE, nq, nnz),
+                "config": {"workload": "%s: 3D unit-cube B-spline patch p=%d, %d^3 = %d elements x %d qp per GPU, %s, "
+                                       "one residual+tangent assembly into CSR (nnz=%d per GPU), MFEM dof numbering" % (
+                                           "C3" if (p == 2 and args.material == "neohookean") else "C4-style block", p, n, NE, nq, args.material, nnz),
                            "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "nnz_per_gpu": nnz, "tangent": "FD parity (bit-exact vs reference)",
                            "l2": "inputs larger than L2 (tables %.1f GB, K_e %.1f GB per step)" % (8e-9 * NE * nq * (tdof + 1), 8e-9 * NE * tdof * tdof),
                            "parallelism": "1 GPU" if world == 1 else "z-slabs of %d^3 elements per GPU of one %dx%dx%d patch; raw K_e/R_e of the p interface layers sent to the owner rank by NCCL send/recv inside the step (bit-identical to the 1-thread reference order)" % (n, n, n, n * world),
@@ -347,6 +351,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--p", type=int, default=2, help="degree (2 = C3 headline; 3 = the C4 element type)")
+    ap.add_argument("--material", default="neohookean", choices=["neohookean", "stvk"])
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
