@@ -38,8 +38,19 @@ enum {
 enum {
   MB2_MAT_NEOHOOKEAN = 0, /* CompressibleOgdenNeoHookean, materials.cpp:96-118; params {lambda, mu} */
   MB2_MAT_STVK = 1,       /* StVenantKirchhoff,           materials.cpp:73-94;  params {lambda, mu} */
-  MB2_MAT_J2LINEAR = 2    /* J2Linear, materials.hpp:142-249; params {lambda, mu, K, G, isotropic_hardening,
+  MB2_MAT_J2LINEAR = 2,   /* J2Linear, materials.hpp:142-249; params {lambda, mu, K, G, isotropic_hardening,
                              kinematic_hardening, sigma_y}; 19 history doubles per quadrature point */
+  MB2_MAT_J2 = 3          /* J2 with nonlinear isotropic hardening, materials.hpp:259-404; params {lambda, mu, K, G,
+                             hardening kind (MB2_HARD_*), hp[10], dt, heat_fraction, density, specific_heat,
+                             initial_temperature, melting_temperature}; 11 history doubles per quadrature point:
+                             plastic_strain[9], accumulated_plastic_strain, temperature */
+};
+/* hardening laws, src/mimi/materials/material_hardening.hpp. hp[10] per law (unused entries 0):
+ *   POWERLAW {sigma_y, n, eps0}; VOCE {sigma_y, sigma_sat, strain_constant};
+ *   JC {A, B, n}; JC_RATE {A, B, n, C, eps0_dot}; JC_THERMO_RATE / JC_CONST_T {A, B, n, C, eps0_dot, T_ref, -, m} */
+enum {
+  MB2_HARD_POWERLAW = 0, MB2_HARD_VOCE = 1, MB2_HARD_JC = 2, MB2_HARD_JC_RATE = 3, MB2_HARD_JC_THERMO_RATE = 4,
+  MB2_HARD_JC_CONST_T = 5
 };
 
 /* tangent modes */
@@ -108,6 +119,12 @@ int mb2_set_material(mb2_ctx* ctx, int kind, const double* params, int nparams);
  * dim*dim slots), beta[9], accumulated_plastic_strain -- allocated and initialised by mb2_set_material (call it after
  * mb2_set_connectivity). mb2_set_state(NULL) re-initialises; get/set are for checkpointing and tests. */
 int mb2_state_size(mb2_ctx* ctx);
+/* NonlinearBase::dt_ (pushed into MaterialBase::dt_ by every assembly, nonlinear_solid.cpp:154,167): the time step the
+ * rate-dependent hardening laws divide by. */
+int mb2_set_time_step(mb2_ctx* ctx, double dt);
+/* Device failure flag of the return-mapping scalar solve (the reference throws, src/mimi/solvers/newton.hpp:81-93,
+ * 119-132): MB2_ERR_NUMERIC + message if raised since the last check. The host-buffer entries check it themselves. */
+int mb2_check_numeric(mb2_ctx* ctx);
 int mb2_get_state(mb2_ctx* ctx, double* state);
 int mb2_set_state(mb2_ctx* ctx, const double* state);
 /* Commits the history variables at the converged u. Replaces NonlinearSolid::DomainPostTimeAdvance

@@ -13,7 +13,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmimi_b200.so")
 
-MB2_MAT_NEOHOOKEAN, MB2_MAT_STVK, MB2_MAT_J2LINEAR = 0, 1, 2
+MB2_MAT_NEOHOOKEAN, MB2_MAT_STVK, MB2_MAT_J2LINEAR, MB2_MAT_J2 = 0, 1, 2, 3
 MB2_RIGID_PLANE, MB2_RIGID_SPHERE = 0, 1
 
 # every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
@@ -26,7 +26,7 @@ SYMBOLS = [
     "mb2_device_pointers", "mb2_last_timing_ms", "mb2_last_launch_count", "mb2_sync", "mb2_measure_fp64_peak", "mb2_set_option", "mb2_host_register", "mb2_host_unregister", "mb2_plan_info", "mb2_set_partition", "mb2_mg_set_send", "mb2_mg_set_recv", "mb2_mg_unique_id",
     "mb2_mg_init_nccl", "mb2_mg_set_manual", "mb2_mg_begin", "mb2_mg_export_send", "mb2_mg_import_recv", "mb2_mg_finish",
     "mb2_mg_ke_doubles", "mb2_state_size", "mb2_get_state", "mb2_set_state", "mb2_post_time_advance",
-    "mb2_post_time_advance_device", "mb2_contact_set_faces", "mb2_contact_set_rigid_body", "mb2_contact_n_marked_nodes",
+    "mb2_post_time_advance_device", "mb2_set_time_step", "mb2_check_numeric", "mb2_contact_set_faces", "mb2_contact_set_rigid_body", "mb2_contact_n_marked_nodes",
     "mb2_contact_get_marked_v_dofs", "mb2_contact_get_A_ids_i32", "mb2_add_boundary_residual",
     "mb2_add_boundary_residual_and_grad", "mb2_contact_residual_device", "mb2_contact_residual_and_grad_device",
     "mb2_contact_get_nodal", "mb2_contact_last_scalars", "mb2_contact_gap_norm",
@@ -160,6 +160,12 @@ class Context:
     def set_state(self, state=None):
         st = None if state is None else np.ascontiguousarray(state, np.float64)
         self._ck(self.lib.mb2_set_state(self.h, _dp(st)))
+
+    def set_time_step(self, dt):
+        self._ck(self.lib.mb2_set_time_step(self.h, C.c_double(dt)))
+
+    def check_numeric(self):
+        self._ck(self.lib.mb2_check_numeric(self.h))
 
     def post_time_advance(self, u):
         self._ck(self.lib.mb2_post_time_advance(self.h, _dp(u)))

@@ -146,6 +146,11 @@ int mb2_download_quad_tables(mb2_ctx* c, double* dN_dX, double* w_detJ) {
   return MB2_OK;
 }
 
+__global__ void k_fill_strided(int64_t n, int stride, int off, double v, double* __restrict__ a) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) a[i * stride + off] = v;
+}
+
 // History variables as MaterialBase::CreateState initialises them (materials.cpp:120-133): all zero for J2Linear.
 static int alloc_state(mb2_ctx* c) {
   dfree(c->d_state);
@@ -154,12 +159,17 @@ static int alloc_state(mb2_ctx* c) {
   const size_t bytes = sizeof(double) * (size_t)c->NE * c->nq * c->ns;
   MB2_CUDA(cudaMalloc(&c->d_state, bytes));
   MB2_CUDA(cudaMemsetAsync(c->d_state, 0, bytes, c->stream));
+  if (c->mat_kind == MB2_MAT_J2) {  // J2::CreateState (materials.cpp:151-166): temperature = initial_temperature_
+    const int64_t n = c->NE * c->nq;
+    k_fill_strided<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(n, c->ns, 10, c->mp.T0, c->d_state);
+    MB2_CUDA(cudaGetLastError());
+  }
   return MB2_OK;
 }
 
 int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
   CHECK_CTX(c);
-  REQUIRE(kind == MB2_MAT_NEOHOOKEAN || kind == MB2_MAT_STVK || kind == MB2_MAT_J2LINEAR, "unknown material kind");
+  REQUIRE(kind >= MB2_MAT_NEOHOOKEAN && kind <= MB2_MAT_J2, "unknown material kind");
   REQUIRE(params && nparams >= 2, "material needs {lambda, mu}");
   mb2::MatP m;
   m.lambda = params[0];
@@ -173,12 +183,55 @@ int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
     m.sqrt_3_2 = std::sqrt(3.0 / 2.0);
     m.sqrt_2_3 = std::sqrt(2.0 / 3.0);
   }
+  if (kind == MB2_MAT_J2) {
+    REQUIRE(nparams >= 21, "J2 needs {lambda, mu, K, G, hardening kind, hp[10], dt, heat_fraction, density, specific_heat, "
+                           "initial_temperature, melting_temperature}");
+    REQUIRE(c->NE > 0, "call mb2_set_connectivity before setting a material with history variables");
+    m.K = params[2]; m.G = params[3];
+    m.hard_kind = (int)params[4];
+    REQUIRE(m.hard_kind >= 0 && m.hard_kind <= 5, "unknown hardening law");
+    for (int i = 0; i < 10; i++) m.hp[i] = params[5 + i];
+    m.dt = params[15]; m.heat_fraction = params[16]; m.density = params[17]; m.specific_heat = params[18];
+    m.T0 = params[19];
+    const double Tmelt = params[20];
+    m.sqrt_3_2 = std::sqrt(3.0 / 2.0);  // materials.hpp:290
+    if (m.hard_kind >= mb2::HARD_JC_THERMO_RATE) {
+      // J2::Setup -> InitializeTemperature / Validate (materials.cpp:135-149, material_hardening.hpp:236-257,303-321)
+      m.hp[6] = Tmelt;
+      REQUIRE(!(m.hp[5] > m.hp[6]), "reference temperature can't be bigger than melting temperature");
+      if (m.hard_kind == mb2::HARD_JC_CONST_T) {
+        m.hp[8] = 1.0 - std::pow((m.T0 - m.hp[5]) / (m.hp[6] - m.hp[5]), m.hp[7]);
+        REQUIRE(m.hp[8] > 0.0, "Invalid temperature contribution");
+      }
+    }
+    m.flag = c->d_flag;
+  }
   const bool realloc_state = (kind != c->mat_kind) || (mb2::mat_state_size(kind) && !c->d_state);
   c->mat_kind = kind;
   c->mp = m;
   if (realloc_state) {
     MB2_CUDA(cudaSetDevice(c->device));
     return alloc_state(c);
+  }
+  return MB2_OK;
+}
+
+int mb2_set_time_step(mb2_ctx* c, double dt) {
+  CHECK_CTX(c);
+  c->mp.dt = dt;
+  return MB2_OK;
+}
+
+// Device failure flag raised by the return-mapping scalar solve (newton.hpp:81-93,119-132 throw in the reference).
+int mb2_check_numeric(mb2_ctx* c) {
+  CHECK_CTX(c);
+  int flag = 0;
+  MB2_CUDA(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  if (flag) {
+    MB2_CUDA(cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
+    c->err = flag == 1 ? "ScalarSolve: root not bracketed by input bounds" : "ScalarSolve: failed to converge in allotted iterations";
+    return MB2_ERR_NUMERIC;
   }
   return MB2_OK;
 }
@@ -351,7 +404,8 @@ int mb2_add_domain_residual(mb2_ctx* c, const double* u, double* r) {
   if ((rc = mb2_set_u(c, u))) return rc;
   if ((rc = mb2_set_r(c, r))) return rc;
   if ((rc = mb2_assemble_residual_device(c))) return rc;
-  return mb2_get_r(c, r);
+  if ((rc = mb2_get_r(c, r))) return rc;
+  return c->ns ? mb2_check_numeric(c) : MB2_OK;
 }
 int mb2_add_domain_residual_and_grad(mb2_ctx* c, const double* u, double gf, double* r, double* A) {
   CHECK_CTX(c);
@@ -364,7 +418,8 @@ int mb2_add_domain_residual_and_grad(mb2_ctx* c, const double* u, double gf, dou
   // A travels chunk by chunk inside the pipeline: rows are uploaded just before the chunk that completes them
   // is gathered and downloaded right after (copy engines, overlapped with the element kernels).
   if ((rc = mb2::launch_residual_and_grad(c, gf, A, A))) return rc;
-  return mb2_get_r(c, r);
+  if ((rc = mb2_get_r(c, r))) return rc;
+  return c->ns ? mb2_check_numeric(c) : MB2_OK;
 }
 
 int mb2_host_register(mb2_ctx* c, void* ptr, size_t bytes) {

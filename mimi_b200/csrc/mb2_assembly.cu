@@ -668,12 +668,13 @@ __global__ void __launch_bounds__(128) post_time_advance_kernel(int nd, int nq, 
     }
 #pragma unroll
   for (int i = 0; i < DIM; i++) F[i + DIM * i] += 1.0;
-  if (MAT == MAT_J2LINEAR) {
+  {
     double st[NS > 0 ? NS : 1];
     double* g = state + idx * NS;
 #pragma unroll
     for (int i = 0; i < NS; i++) st[i] = g[i];
-    j2linear_plastic_stress<DIM, true>(mp, F, st, nullptr);
+    if (MAT == MAT_J2LINEAR) j2linear_plastic_stress<DIM, true>(mp, F, st, nullptr);
+    else j2_plastic_stress<DIM, true>(mp, F, st, nullptr);
 #pragma unroll
     for (int i = 0; i < NS; i++) g[i] = st[i];
   }
@@ -683,14 +684,17 @@ int launch_post_time_advance(mb2_ctx* c) {
   if (!c->d_state) return MB2_OK;  // stateless material: MaterialBase::Accumulate is never reached (nullptr state)
   const int64_t n = c->n_compute * c->nq;
   const unsigned grid = (unsigned)((n + 127) / 128);
+#define MB2_PTA(D, M)                                                                                               \
+  post_time_advance_kernel<D, M><<<grid, 128, 0, c->stream>>>(c->nd, c->nq, c->n_compute, c->d_vdofs, c->d_dNdX, c->d_u, \
+                                                              c->mp, c->d_state)
   if (c->mat_kind == MAT_J2LINEAR) {
-    if (c->dim == 3)
-      post_time_advance_kernel<3, MAT_J2LINEAR><<<grid, 128, 0, c->stream>>>(c->nd, c->nq, c->n_compute, c->d_vdofs, c->d_dNdX,
-                                                                             c->d_u, c->mp, c->d_state);
-    else
-      post_time_advance_kernel<2, MAT_J2LINEAR><<<grid, 128, 0, c->stream>>>(c->nd, c->nq, c->n_compute, c->d_vdofs, c->d_dNdX,
-                                                                             c->d_u, c->mp, c->d_state);
+    if (c->dim == 3) MB2_PTA(3, MAT_J2LINEAR);
+    else MB2_PTA(2, MAT_J2LINEAR);
+  } else if (c->mat_kind == MAT_J2) {
+    if (c->dim == 3) MB2_PTA(3, MAT_J2);
+    else MB2_PTA(2, MAT_J2);
   }
+#undef MB2_PTA
   MB2_CUDA(cudaGetLastError());
   c->last_launches = 1;
   return MB2_OK;
@@ -831,6 +835,7 @@ static int launch_element_mat(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
     case MAT_NEOHOOKEAN: return launch_element<DIM, ND, NQ, MAT_NEOHOOKEAN, GRAD, MINB>(c, a, st);
     case MAT_STVK: return launch_element<DIM, ND, NQ, MAT_STVK, GRAD, MINB>(c, a, st);
     case MAT_J2LINEAR: return launch_element<DIM, ND, NQ, MAT_J2LINEAR, GRAD, MINB>(c, a, st);
+    case MAT_J2: return launch_element<DIM, ND, NQ, MAT_J2, GRAD, MINB>(c, a, st);
   }
   c->err = "material not set or unsupported";
   return MB2_ERR_UNSUPPORTED;
@@ -844,6 +849,7 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
       case MAT_NEOHOOKEAN: return launch_element_fd<3, 27, 64, MAT_NEOHOOKEAN>(c, a, st);
       case MAT_STVK: return launch_element_fd<3, 27, 64, MAT_STVK>(c, a, st);
       case MAT_J2LINEAR: return launch_element_fd<3, 27, 64, MAT_J2LINEAR>(c, a, st);
+      case MAT_J2: return launch_element_fd<3, 27, 64, MAT_J2>(c, a, st);
     }
   }
   if (GRAD && dim == 3 && nd == 64 && nq == 125 && c->elem_variant != 1) {
@@ -851,6 +857,7 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
       case MAT_NEOHOOKEAN: return launch_element_fd_split<3, 64, 125, MAT_NEOHOOKEAN, 4>(c, a, st);
       case MAT_STVK: return launch_element_fd_split<3, 64, 125, MAT_STVK, 4>(c, a, st);
       case MAT_J2LINEAR: return launch_element_fd_split<3, 64, 125, MAT_J2LINEAR, 4>(c, a, st);
+      case MAT_J2: return launch_element_fd_split<3, 64, 125, MAT_J2, 4>(c, a, st);
     }
   }
   if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a, st);

@@ -6,17 +6,27 @@
 
 namespace mb2 {
 
-enum : int { MAT_NEOHOOKEAN = 0, MAT_STVK = 1, MAT_J2LINEAR = 2 };
+enum : int { MAT_NEOHOOKEAN = 0, MAT_STVK = 1, MAT_J2LINEAR = 2, MAT_J2 = 3 };
+// hardening laws (src/mimi/materials/material_hardening.hpp); hp[] layout:
+//  POWERLAW {sigma_y, n, eps0}   VOCE {sigma_y, sigma_sat, strain_constant}
+//  JC* {A, B, n, C, eps0_dot, T_ref, T_melt, m, temperature_contribution_ (constant-temperature law)}
+enum : int { HARD_POWERLAW = 0, HARD_VOCE = 1, HARD_JC = 2, HARD_JC_RATE = 3, HARD_JC_THERMO_RATE = 4, HARD_JC_CONST_T = 5 };
 
 // MaterialBase parameters (materials.hpp:24-40) plus the J2Linear members (materials.hpp:147-166); the sqrt
 // constants are computed on the host by std::sqrt exactly like the reference's member initialisers.
 struct MatP {
   double lambda = 0, mu = 0;
   double K = 0, G = 0, iso = 0, kin = 0, sigma_y = 0, sqrt_6 = 0, sqrt_3_2 = 0, sqrt_2_3 = 0;
+  // J2 family (materials.hpp:259-404): hardening law, thermo members, dt_ pushed by the integrator, density_
+  int hard_kind = 0;
+  double hp[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  double dt = 0, heat_fraction = 0, density = 0, specific_heat = 0, T0 = 0;
+  int* flag = nullptr;  // device failure flag: 1 = root not bracketed, 2 = scalar solve did not converge
 };
 
 // per-quadrature-point history doubles: J2Linear = plastic_strain[9], beta[9], accumulated_plastic_strain
-__host__ __device__ constexpr int mat_state_size(int mat) { return mat == MAT_J2LINEAR ? 19 : 0; }
+//                                   J2 = plastic_strain[9], accumulated_plastic_strain, temperature
+__host__ __device__ constexpr int mat_state_size(int mat) { return mat == MAT_J2LINEAR ? 19 : (mat == MAT_J2 ? 11 : 0); }
 
 // mfem::kernels::MultABt on DIM x DIM operands (third_party/mfem/linalg/kernels.hpp:363-384):
 // C zeroed, then k outer, j, i inner: C(i,j) += A(i,k) * B(j,k).
@@ -175,6 +185,198 @@ __device__ __forceinline__ void j2linear_plastic_stress(const MatP& m, const dou
   }
 }
 
+// ---- J2 with nonlinear isotropic hardening (src/mimi/materials/materials.hpp:259-404) ----
+// ADScalar<double,1> operator sequences of the hardening laws (src/mimi/utils/ad.inl). pow / exp / log are CUDA's
+// libdevice functions (<= 1 ulp) where the reference calls glibc (< 1 ulp): values agree to the last bit or two, which
+// the tests state as a tolerance for this material family (every other operation keeps the reference's order).
+struct AD1 {
+  double v, d;
+};
+__device__ __forceinline__ AD1 ad_pow(AD1 b, double power) {  // ad.inl:261-279
+  const double tmp = pow(b.v, power - 1.0);
+  b.v *= tmp;
+  b.d *= power * tmp;
+  return b;
+}
+__device__ __forceinline__ AD1 hardening_evaluate(const MatP& m, AD1 eps) {
+  AD1 r;
+  if (m.hard_kind == HARD_POWERLAW) {  // sigma_y * pow(1.0 + eps / eps0, 1.0 / n)
+    const double inv = 1 / m.hp[2];
+    AD1 t = {eps.v * inv, eps.d * inv};
+    t.v += 1.0;
+    t = ad_pow(t, 1.0 / m.hp[1]);
+    r.v = t.v * m.hp[0];
+    r.d = t.d * m.hp[0];
+    return r;
+  }
+  if (m.hard_kind == HARD_VOCE) {  // sigma_sat - (sigma_sat - sigma_y) * exp(-eps / strain_constant)
+    const double inv = 1 / m.hp[2];
+    AD1 t = {-eps.v * inv, -eps.d * inv};
+    const double tmp = exp(t.v);
+    t.v = 1. * tmp;
+    t.d = t.d * tmp;
+    const double c = m.hp[1] - m.hp[0];
+    t.v *= c;
+    t.d *= c;
+    r.v = -t.v + m.hp[1];
+    r.d = -t.d;
+    return r;
+  }
+  if (fabs(eps.v) < 1.e-13) {  // JohnsonCookHardening::Evaluate, material_hardening.hpp:143-150
+    r.v = m.hp[0];
+    r.d = 0.0;
+    return r;
+  }
+  AD1 t = ad_pow(eps, m.hp[2]);
+  t.v *= m.hp[1];
+  t.d *= m.hp[1];
+  r.v = t.v + m.hp[0];
+  r.d = t.d;
+  return r;
+}
+__device__ __forceinline__ double hardening_rate(const MatP& m, double rate) {  // material_hardening.hpp:186-197
+  if (m.hard_kind < HARD_JC_RATE) return 1.;
+  double v = 1.0;
+  if (rate > m.hp[4]) v += m.hp[3] * log(rate / m.hp[4]);
+  return v;
+}
+__device__ __forceinline__ double hardening_thermo(const MatP& m, double T) {  // material_hardening.hpp:262-279
+  if (m.hard_kind < HARD_JC_THERMO_RATE) return 1.;
+  if (m.hard_kind == HARD_JC_CONST_T) return m.hp[8];
+  double v = 1.0;
+  if (T < m.hp[5]) {
+  } else if (T > m.hp[6]) {
+    v = 0.0;
+  } else {
+    v -= pow((T - m.hp[5]) / (m.hp[6] - m.hp[5]), m.hp[7]);
+  }
+  return v;
+}
+// return-mapping residual (materials.hpp:345-351) for a double and for an ADScalar argument (delta / dt is a true
+// division in the first and a multiplication by 1/dt in the second, ad.inl:184-193)
+__device__ __forceinline__ double j2_residual_d(const MatP& m, double q, double eqps_old, double thermo, double de) {
+  const AD1 e = {eqps_old + de, 0.0};
+  const AD1 H = hardening_evaluate(m, e);
+  const double cc = hardening_rate(m, de / m.dt) * thermo;
+  return -(H.v * cc) + (q - 3.0 * m.G * de);
+}
+__device__ __forceinline__ AD1 j2_residual_ad(const MatP& m, double q, double eqps_old, double thermo, double x) {
+  const double t1 = 3.0 * m.G;
+  AD1 a = {-(x * t1) + q, -(1.0 * t1)};
+  const AD1 e = {x + eqps_old, 1.0};
+  AD1 H = hardening_evaluate(m, e);
+  const double inv_dt = 1 / m.dt;
+  const double cc = hardening_rate(m, x * inv_dt) * thermo;
+  H.v *= cc;
+  H.d *= cc;
+  a.v -= H.v;
+  a.d -= H.d;
+  return a;
+}
+// mimi::solvers::ScalarSolve (src/mimi/solvers/newton.hpp:53-169), x0 = 0; failures raise the device flag
+__device__ __forceinline__ double j2_scalar_solve(const MatP& m, double q, double eqps_old, double thermo, double lower,
+                                                  double upper, double xtol, double rtol, int max_iter) {
+  const double fl = j2_residual_d(m, q, eqps_old, thermo, lower), fh = j2_residual_d(m, q, eqps_old, thermo, upper);
+  if (fabs(fl) < xtol) return lower;
+  if (fabs(fh) < xtol) return upper;
+  if (fl * fh > 0.) {
+    if (m.flag) *m.flag = 1;
+    return 0.0;
+  }
+  double xl = lower, xh = upper;
+  if (fl > 0) {
+    xl = upper;
+    xh = lower;
+  }
+  double x = 0.0;
+  if (x < lower || x > upper) x = 0.5 * (lower + upper);
+  double delta_x_old = fabs(upper - lower), delta_x = delta_x_old;
+  AD1 R = j2_residual_ad(m, q, eqps_old, thermo, x);
+  double fval = R.v, df = R.d;
+  int it = 0;
+  bool converged = false;
+  while (!converged) {
+    if (it == max_iter) {
+      if (m.flag) *m.flag = 2;
+      break;
+    }
+    if ((x - xh) * df - fval > 0 || (x - xl) * df - fval < 0 || fabs(2. * fval) > fabs(delta_x_old * df)) {
+      delta_x_old = delta_x;
+      delta_x = 0.5 * (xh - xl);
+      x = xl + delta_x;
+    } else {
+      delta_x_old = delta_x;
+      delta_x = fval / df;
+      x -= delta_x;
+    }
+    R = j2_residual_ad(m, q, eqps_old, thermo, x);
+    fval = R.v;
+    df = R.d;
+    converged = (fabs(delta_x) < xtol) || (fabs(fval) < rtol);
+    if (fval < 0) xl = x; else xh = x;
+    ++it;
+  }
+  return x;
+}
+// J2::PlasticStress<ACC> (materials.hpp:311-391) on st = {plastic_strain[9], accumulated_plastic_strain, temperature}
+template <int DIM, bool ACC>
+__device__ __noinline__ void j2_plastic_stress(const MatP& m, const double* F, double* st, double* sigma) {
+  constexpr int DD = DIM * DIM;
+  double eps[DD], s[DD];
+#pragma unroll
+  for (int i = 0; i < DD; i++) eps[i] = F[i];
+#pragma unroll
+  for (int i = 0; i < DIM; i++)
+#pragma unroll
+    for (int j = 0; j < i; j++) {
+      const double a = 0.5 * (eps[i * DIM + j] + eps[j * DIM + i]);
+      eps[j * DIM + i] = eps[i * DIM + j] = a;
+    }
+#pragma unroll
+  for (int i = 0; i < DIM; i++) eps[(DIM + 1) * i] -= 1.;
+#pragma unroll
+  for (int i = 0; i < DD; i++) eps[i] -= st[i];
+  double tr = 0.0;
+#pragma unroll
+  for (int i = 0; i < DIM; i++) tr += eps[i + i * DIM];
+  const double p = m.K * tr;
+  const double factor = 2.0 * m.G;
+  {
+    double trd;
+    if (DIM == 2) trd = (eps[0] + eps[3]) / 2.0;
+    else trd = (eps[0] + eps[4] + eps[8]) / 3.0;
+#pragma unroll
+    for (int i = 0; i < DD; i++) s[i] = ((i % (DIM + 1) == 0) ? (eps[i] - trd) : eps[i]) * factor;
+  }
+  double a = 0.0;
+#pragma unroll
+  for (int i = 0; i < DD; i++) a += s[i] * s[i];
+  const double q = m.sqrt_3_2 * sqrt(a);
+  const double eqps_old = st[9];
+  const double thermo = hardening_thermo(m, st[10]);
+  const double tolerance = m.hp[0] * 1.e-10;  // SigmaY() * k_tol
+  if (j2_residual_d(m, q, eqps_old, thermo, 0.0) > tolerance) {
+    const AD1 e0 = {eqps_old, 0.0};
+    const double upper = (q - hardening_evaluate(m, e0).v * thermo) / (3.0 * m.G);
+    const double de = j2_scalar_solve(m, q, eqps_old, thermo, 0.0, upper, 1.e-10, tolerance, 100);
+    const double al = 1.5 / q;
+    if (!ACC) {
+      const double cc = -2.0 * m.G * de;
+#pragma unroll
+      for (int i = 0; i < DD; i++) s[i] += cc * (al * s[i]);
+    } else {
+      st[9] += de;
+#pragma unroll
+      for (int i = 0; i < DD; i++) st[i] += de * (al * s[i]);
+      if (m.hard_kind == HARD_JC_THERMO_RATE) st[10] += m.heat_fraction * q * de / (m.density * m.specific_heat);
+    }
+  }
+  if (!ACC) {
+#pragma unroll
+    for (int i = 0; i < DD; i++) sigma[i] = s[i] + p * ((i % (DIM + 1) == 0) ? 1.0 : 0.0);
+  }
+}
+
 // First Piola-Kirchhoff stress P(F). MAT is a compile-time material id; st = this quadrature point's history
 // (read-only here; nullptr for stateless materials).
 //  NeoHookean: CompressibleOgdenNeoHookean::EvaluateCauchy (src/mimi/materials/materials.cpp:96-118)
@@ -217,6 +419,13 @@ __device__ __forceinline__ void material_pk1(const MatP& m, const double* F, con
     }
     stl[18] = st[18];
     j2linear_plastic_stress<DIM, false>(m, F, stl, sig);
+  } else if (MAT == MAT_J2) {
+    double stl[11];
+#pragma unroll
+    for (int i = 0; i < DD; i++) stl[i] = st[i];
+    stl[9] = st[9];
+    stl[10] = st[10];
+    j2_plastic_stress<DIM, false>(m, F, stl, sig);
   } else {
     const double mu_over_det_F = mu / det_F;
     mult_ABt<DIM>(F, F, B);

@@ -54,6 +54,25 @@ def contact_main():
             print(name, out["meta"])
 
 
+# J2 + hardening laws: results only (tables / connectivity are those of the named base fixture)
+J2_CASES = {"j2_cube_p2_n2": "cube_p2_n2", "j2_quad_p2_n4": "quad_p2_n4"}
+
+
+def j2_main():
+    for name, base in J2_CASES.items():
+        writer, elevate, refine, gf = CASES[base]
+        with tempfile.TemporaryDirectory() as tmp:
+            mesh = os.path.join(tmp, "m.mesh")
+            writer(mesh)
+            out = {"base": np.array(base), "gf": np.float64(gf)}
+            for law in O.HARD:
+                D = O.run_ref_dump(mesh, elevate, refine, "j2_" + law, os.path.join(tmp, law), gf=gf)
+                for k_out, k_in in (("r", "r"), ("r2", "r2"), ("A", "A"), ("state", "state"), ("rb", "r_b"), ("Ab", "A_b")):
+                    out[k_out + "_" + law] = D[k_in]
+            np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+            print(name, sorted(out)[:4])
+
+
 def main(only=None):
     assert O.have_ref(), "build oracle/_ref first: make -f oracle/Makefile.ref -j8"
     os.makedirs(OUT, exist_ok=True)
@@ -87,8 +106,11 @@ def main(only=None):
 if __name__ == "__main__":
     if "contact" in sys.argv[1:]:
         contact_main()
+    elif "j2" in sys.argv[1:]:
+        j2_main()
     elif len(sys.argv) > 1:
         main(sys.argv[1:])
     else:
         main()
         contact_main()
+        j2_main()

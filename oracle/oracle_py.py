@@ -20,7 +20,9 @@ NEOHOOKEAN, STVK = 0, 1
 class Material(C.Structure):
     _fields_ = [("kind", C.c_int), ("lam", C.c_double), ("mu", C.c_double), ("K", C.c_double), ("G", C.c_double),
                 ("iso", C.c_double), ("kin", C.c_double), ("sigma_y", C.c_double), ("sqrt_6", C.c_double),
-                ("sqrt_3_2", C.c_double), ("sqrt_2_3", C.c_double), ("state", C.c_void_p), ("ns", C.c_int)]
+                ("sqrt_3_2", C.c_double), ("sqrt_2_3", C.c_double), ("state", C.c_void_p), ("ns", C.c_int),
+                ("hard_kind", C.c_int), ("hp", C.c_double * 10), ("dt", C.c_double), ("heat_fraction", C.c_double),
+                ("density", C.c_double), ("specific_heat", C.c_double), ("error", C.POINTER(C.c_int))]
 
 
 J2LINEAR = 2
@@ -34,8 +36,51 @@ def mat_j2linear(state, young=2100.0, poisson=0.3, iso=80.0, kin=40.0, sigma_y=2
     lam, mu = lame(young, poisson)
     K = young / (3.0 * (1.0 - (2.0 * poisson)))     # MaterialBase::SetYoungPoisson, materials.cpp:7-14
     m = Material(J2LINEAR, lam, mu, K, mu, iso, kin, sigma_y, np.sqrt(6.0), np.sqrt(3.0 / 2.0), np.sqrt(2.0 / 3.0),
-                 state.ctypes.data, J2LINEAR_NS)
+                 state.ctypes.data, J2LINEAR_NS, 0, (C.c_double * 10)(), 0, 0, 0, 0, None)
     m._keep = state
+    return m
+
+
+J2 = 3
+J2_NS = 11
+HARD = {"powerlaw": 0, "voce": 1, "jc": 2, "jcrate": 3, "jcthermo": 4, "jcconst": 5}
+# the parameter sets oracle/ref_harness.cpp uses for material "j2_<law>"; hp layout of oracle/mimi_oracle.c
+J2_THERMO = dict(melting=1500.0, T0=20.0, specific_heat=450.0, heat_fraction=0.9, dt=0.5, density=1.0)
+
+
+def hardening_params(law):
+    hp = np.zeros(10)
+    if law == "powerlaw":
+        hp[:3] = [2.0, 3.0, 0.01]
+    elif law == "voce":
+        hp[:3] = [2.0, 3.0, 0.05]
+    else:
+        hp[:3] = [2.0, 4.0, 0.2835]
+        if law != "jc":
+            hp[3:5] = [0.015, 1.0e-5]
+        if law in ("jcthermo", "jcconst"):
+            hp[5:8] = [20.0 if law == "jcthermo" else 10.0, J2_THERMO["melting"], 1.3558]
+        if law == "jcconst":
+            # JohnsonCookConstantTemperatureHardening::SetTemperature (material_hardening.hpp:310-321)
+            hp[8] = 1.0 - np.power((J2_THERMO["T0"] - hp[5]) / (hp[6] - hp[5]), hp[7])
+    return hp
+
+
+def j2_initial_state(NE, nq):
+    """J2::CreateState (materials.cpp:151-166): zero plastic strain, zero eqps, initial temperature."""
+    S = np.zeros((NE, nq, J2_NS))
+    S[:, :, 10] = J2_THERMO["T0"]
+    return S
+
+
+def mat_j2(state, law, young=2100.0, poisson=0.3):
+    lam, mu = lame(young, poisson)
+    K = young / (3.0 * (1.0 - (2.0 * poisson)))
+    err = C.c_int(0)
+    m = Material(J2, lam, mu, K, mu, 0, 0, 0, 0, np.sqrt(3.0 / 2.0), 0, state.ctypes.data, J2_NS, HARD[law],
+                 (C.c_double * 10)(*hardening_params(law)), J2_THERMO["dt"], J2_THERMO["heat_fraction"],
+                 J2_THERMO["density"], J2_THERMO["specific_heat"], C.pointer(err))
+    m._keep = (state, err)
     return m
 
 
@@ -78,7 +123,7 @@ def _p(a, t):
 
 def mat(kind, young=2100.0, poisson=0.3):
     lam, mu = lame(young, poisson)
-    return Material(kind, lam, mu, 0, 0, 0, 0, 0, 0, 0, 0, None, 0)
+    return Material(kind, lam, mu, 0, 0, 0, 0, 0, 0, 0, 0, None, 0, 0, (C.c_double * 10)(), 0, 0, 0, 0, None)
 
 
 def assemble_residual(dim, nd, nq, m, v_dofs, dN_dX, w, detJ, u):
@@ -149,7 +194,9 @@ def load_dump(d):
     out["dN_dX"] = rd("dN_dX.f64", np.float64, (NE, nq, dim, nd))
     out["dN_dxi"] = rd("dN_dxi.f64", np.float64, (NE, nq, dim, nd))
     out["N"] = rd("N.f64", np.float64, (NE, nq, nd))
-    out["state"] = rd("state.f64", np.float64, (NE, nq, 19))
+    out["state"] = rd("state.f64", np.float64)
+    if out["state"] is not None:
+        out["state"] = out["state"].reshape(NE, nq, -1)
     for k in ("x_ref", "u", "r", "r2", "mass", "A", "r_b", "A_b"):
         out[k] = rd(k + ".f64", np.float64)
     return out

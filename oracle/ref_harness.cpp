@@ -87,6 +87,28 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
     m->sigma_y_ = sy ? std::atof(sy) : 2.0;
     s.mat = m;
   }
+  else if (material.rfind("j2_", 0) == 0) {
+    // J2 with nonlinear isotropic hardening (materials.hpp:259-404); thermo values of tests/test_nonlinear_solid.py:16-33,
+    // yield stresses scaled down so that the synthetic 1e-3 displacement field yields at part of the points
+    namespace mm = mimi::materials;
+    auto m = std::make_shared<mm::J2>();
+    m->melting_temperature_ = 1500; m->initial_temperature_ = 20; m->specific_heat_ = 450; m->heat_fraction_ = 0.9;
+    const std::string h = material.substr(3);
+    auto jc_fill = [](auto& jc) { jc.A_ = 2.0; jc.B_ = 4.0; jc.n_ = 0.2835; };
+    auto jcr_fill = [&](auto& jc) { jc_fill(jc); jc.C_ = 0.015; jc.effective_plastic_strain_rate_ = 1.0e-5; };
+    if (h == "powerlaw") { auto hd = std::make_shared<mm::PowerLawHardening>(); hd->sigma_y_ = 2.0; hd->n_ = 3.0; hd->eps0_ = 0.01; m->hardening_ = hd; }
+    else if (h == "voce") { auto hd = std::make_shared<mm::VoceHardening>(); hd->sigma_y_ = 2.0; hd->sigma_sat_ = 3.0; hd->strain_constant_ = 0.05; m->hardening_ = hd; }
+    else if (h == "jc") { auto hd = std::make_shared<mm::JohnsonCookHardening>(); jc_fill(*hd); m->hardening_ = hd; }
+    else if (h == "jcrate") { auto hd = std::make_shared<mm::JohnsonCookRateDependentHardening>(); jcr_fill(*hd); m->hardening_ = hd; }
+    else if (h == "jcthermo") {
+      auto hd = std::make_shared<mm::JohnsonCookTemperatureAndRateDependentHardening>();
+      jcr_fill(*hd); hd->reference_temperature_ = 20; hd->m_ = 1.3558; m->hardening_ = hd;
+    } else if (h == "jcconst") {
+      auto hd = std::make_shared<mm::JohnsonCookConstantTemperatureHardening>();
+      jcr_fill(*hd); hd->reference_temperature_ = 10; hd->m_ = 1.3558; m->hardening_ = hd;
+    } else { std::fprintf(stderr, "unknown hardening %s\n", h.c_str()); std::exit(2); }
+    s.mat = m;
+  }
   else { std::fprintf(stderr, "unknown material %s\n", material.c_str()); std::exit(2); }
   s.mat->density_ = 1.0;
   s.mat->viscosity_ = -1.0;
@@ -109,6 +131,9 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
   s.integ = std::make_shared<mimi::integrators::NonlinearSolid>(s.mat->Name() + "-NonlinearSolid", s.mat, s.pre);
   s.pre->PrecomputeElementQuadData("domain", -1, true);
   s.integ->Prepare();
+  s.integ->dt_ = 0.5;  // pushed into the material by AddDomainResidual[AndGrad] (nonlinear_solid.cpp:154,167)
+  s.integ->first_effective_dt_ = 0.5;
+  s.integ->second_effective_dt_ = 0.5;
   s.t_precompute = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   return s;
 }
@@ -281,17 +306,21 @@ int main(int argc, char** argv) {
     s.integ->AddDomainResidualAndGrad(u, gf, r2, A);
     dump(out, "r2.f64", r2.GetData(), (size_t)NV);
     dump(out, "A.f64", A.GetData(), (size_t)nnz);
-    if (material == "j2linear") {
+    if (material == "j2linear" || material.rfind("j2_", 0) == 0) {
       s.integ->DomainPostTimeAdvance(u);
-      using St = mimi::materials::J2Linear::State;
-      std::vector<double> st((size_t)NE * nq * 19, 0.0);
+      // history layout: every state matrix in a 9-double slot (column-major dim x dim in front), then the scalars;
+      // J2Linear has k_state_scalars = 2 but only uses the first (19 doubles), J2 = 9 + 2
+      const bool lin = material == "j2linear";
+      const int ns = lin ? 19 : 11;
+      std::vector<double> st((size_t)NE * nq * ns, 0.0);
       for (int e = 0; e < NE; ++e)
         for (int q = 0; q < nq; ++q) {
           const auto& ms = *eqd[e].GetQuadData()[q].material_state;
-          double* o = &st[((size_t)e * nq + q) * 19];
-          std::memcpy(o, ms.matrices[St::k_plastic_strain].GetData(), sizeof(double) * dim * dim);
-          std::memcpy(o + 9, ms.matrices[St::k_beta].GetData(), sizeof(double) * dim * dim);
-          o[18] = ms.scalars[St::k_accumulated_plastic_strain];
+          double* o = &st[((size_t)e * nq + q) * ns];
+          for (size_t k = 0; k < ms.matrices.size(); ++k)
+            std::memcpy(o + 9 * k, ms.matrices[k].GetData(), sizeof(double) * dim * dim);
+          o[9 * ms.matrices.size()] = ms.scalars[0];
+          if (!lin) o[9 * ms.matrices.size() + 1] = ms.scalars[1];
         }
       dump(out, "state.f64", st.data(), st.size());
       mfem::Vector ub(u), rb(NV);

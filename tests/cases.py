@@ -34,6 +34,30 @@ def load_contact_golden(name):
     return D
 
 
+J2_CASES = ["j2_cube_p2_n2", "j2_quad_p2_n4"]
+J2_LAWS = ["powerlaw", "voce", "jc", "jcrate", "jcthermo", "jcconst"]
+
+
+def load_j2_golden(name):
+    """Results of J2 + every hardening law on the tables of the base fixture."""
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    D = load_golden(str(z["base"]))
+    D.update({k: z[k] for k in z.files if k != "base"})
+    D["gf"] = float(z["gf"])
+    return D
+
+
+def j2_params(law):
+    """Parameter list of mb2_set_material(MB2_MAT_J2, ...) for the harness' material 'j2_<law>'."""
+    lam, mu = O.lame()
+    K = 2100.0 / (3.0 * (1.0 - (2.0 * 0.3)))
+    T = O.J2_THERMO
+    hp = O.hardening_params(law).copy()
+    hp[6] = hp[8] = 0.0   # the library derives T_melt / temperature_contribution_ itself (J2::Setup)
+    return [lam, mu, K, mu, O.HARD[law]] + list(hp) + [T["dt"], T["heat_fraction"], T["density"], T["specific_heat"],
+                                                      T["T0"], T["melting"]]
+
+
 def ref_case(kind, p, n, material, gf=1.0):
     """Live reference run (nthreads=1). kind: 'refine' (p1 cube + DegreeElevate(p-1) + log2(n) refinements)
     or 'patch' (direct p, n spans)."""

@@ -61,3 +61,26 @@ def test_j2linear_with_history_bit_exact(name):
     assert 0.05 < y < 0.999, y                           # both branches of the yield check are exercised
     rb, Ab = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], 1.5 * D["u"], D["gf"], D["mass"])
     assert np.array_equal(rb, D["rb_j2linear"]) and np.array_equal(Ab, D["Ab_j2linear"])
+
+
+from tests.cases import J2_CASES, J2_LAWS, load_j2_golden  # noqa: E402
+
+
+@pytest.mark.parametrize("law", J2_LAWS)
+@pytest.mark.parametrize("name", J2_CASES)
+def test_j2_hardening_laws_bit_exact(name, law):
+    """J2 (materials.hpp:259-404) + the hardening laws of material_hardening.hpp + ScalarSolve (newton.hpp:53-169):
+    the oracle runs on the same libm as the reference, so it is bit-exact."""
+    D = load_j2_golden(name)
+    S = O.j2_initial_state(D["NE"], D["nq"])
+    m = O.mat_j2(S, law)
+    args = (D["dim"], D["nd"], D["nq"], m, D["v_dofs"])
+    assert np.array_equal(O.assemble_residual(*args, D["dN_dX"], D["w"], D["detJ"], D["u"]), D["r_" + law])
+    r2, A = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], D["u"], D["gf"], D["mass"])
+    assert np.array_equal(r2, D["r2_" + law]) and np.array_equal(A, D["A_" + law])
+    O.post_time_advance(D["dim"], D["nd"], D["nq"], m, D["v_dofs"], D["dN_dX"], D["u"])
+    assert np.array_equal(S, D["state_" + law])
+    assert 0.05 < (S[:, :, 9] > 0).mean() < 0.999
+    rb, Ab = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], 1.5 * D["u"], D["gf"], D["mass"])
+    assert np.array_equal(rb, D["rb_" + law]) and np.array_equal(Ab, D["Ab_" + law])
+    assert m._keep[1].value == 0
