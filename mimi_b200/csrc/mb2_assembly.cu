@@ -459,7 +459,7 @@ struct Elem3Cfg {
   static constexpr int OFF_BAR = OFF_RB + TD;                   // 2 mbarriers
   static constexpr int SMEM_DOUBLES = OFF_BAR + 2;
   static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
-  static_assert(ND % LI == 0 && ND % 2 == 0 && QC >= 1, "element type not supported by the split kernel");
+  static_assert(ND % (2 * LI) == 0 && QC >= 1, "element type not supported by the split kernel");
   static_assert((QC * DIM * ND) % 2 == 0 && (NQ * DD) % 2 == 1 || true, "alignment");
 };
 
@@ -490,8 +490,11 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
   const int c1 = base1 ? 0 : mg1 / ND, a1 = base1 ? -1 : mg1 % ND;
   // phase-2 role
   const int lane = t & 31, warp = t >> 5;
-  const int i0 = (lane % LI) * TI;
+  // rows of this thread: row(x) = 2*LI*(x/2) + 2*(lane%LI) + x%2 -- the LI row lanes of a warp read one contiguous
+  // 128-byte run of a dN row per LDS.128 (conflict-free; a blocked row split costs a 4-way bank conflict)
+  const int i0 = (lane % LI) * 2;
   const int col0 = (warp * Cfg::LC + lane / LI) * TC;
+#define MB2_ROW(x) (2 * LI * ((x) / 2) + i0 + ((x) % 2))
 
   if (t == 0) {
     mbar_init(&bar[0], 1);
@@ -598,7 +601,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
           const double2* d2 = reinterpret_cast<const double2*>(dNc + (qs * DIM + k) * ND + i0);
 #pragma unroll
           for (int x = 0; x < TI / 2; x++) {
-            const double2 v = d2[x];
+            const double2 v = d2[x * LI];
             dv[2 * x] = v.x;
             dv[2 * x + 1] = v.y;
           }
@@ -618,8 +621,8 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
       const int j = col - MP * DIM;
 #pragma unroll
       for (int x = 0; x < TI; x++) {
-        sRb[i0 + x + j * ND] = R[x][y];
-        if (part == 0) g.Re[e * TD + i0 + x + j * ND] = R[x][y];
+        sRb[MB2_ROW(x) + j * ND] = R[x][y];
+        if (part == 0) g.Re[e * TD + MB2_ROW(x) + j * ND] = R[x][y];
       }
     }
   }
@@ -634,9 +637,11 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
       const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
       const double hinv = 1. / h;
 #pragma unroll
-      for (int x = 0; x < TI; x++) out[(int64_t)(i0 + x) * KP + mg * DIM + j] = (R[x][y] - sRb[i0 + x + j * ND]) * hinv;
+      for (int x = 0; x < TI; x++)
+        out[(int64_t)MB2_ROW(x) * KP + mg * DIM + j] = (R[x][y] - sRb[MB2_ROW(x) + j * ND]) * hinv;
     }
   }
+#undef MB2_ROW
 }
 
 // ---------------------------------------------------------------------------------------------
