@@ -40,10 +40,12 @@ enum {
   MB2_MAT_STVK = 1,       /* StVenantKirchhoff,           materials.cpp:73-94;  params {lambda, mu} */
   MB2_MAT_J2LINEAR = 2,   /* J2Linear, materials.hpp:142-249; params {lambda, mu, K, G, isotropic_hardening,
                              kinematic_hardening, sigma_y}; 19 history doubles per quadrature point */
-  MB2_MAT_J2 = 3          /* J2 with nonlinear isotropic hardening, materials.hpp:259-404; params {lambda, mu, K, G,
+  MB2_MAT_J2 = 3,         /* J2 with nonlinear isotropic hardening, materials.hpp:259-404; params {lambda, mu, K, G,
                              hardening kind (MB2_HARD_*), hp[10], dt, heat_fraction, density, specific_heat,
                              initial_temperature, melting_temperature}; 11 history doubles per quadrature point:
                              plastic_strain[9], accumulated_plastic_strain, temperature */
+  MB2_MAT_J2SIMO = 4      /* J2Simo (finite strain), materials.hpp:406-579; params as MB2_MAT_J2; 20 history doubles:
+                             be_old[9], F_old[9], accumulated_plastic_strain, temperature */
 };
 /* hardening laws, src/mimi/materials/material_hardening.hpp. hp[10] per law (unused entries 0):
  *   POWERLAW {sigma_y, n, eps0}; VOCE {sigma_y, sigma_sat, strain_constant};

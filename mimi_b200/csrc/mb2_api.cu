@@ -159,9 +159,17 @@ static int alloc_state(mb2_ctx* c) {
   const size_t bytes = sizeof(double) * (size_t)c->NE * c->nq * c->ns;
   MB2_CUDA(cudaMalloc(&c->d_state, bytes));
   MB2_CUDA(cudaMemsetAsync(c->d_state, 0, bytes, c->stream));
+  const int64_t n = c->NE * c->nq;
+  const unsigned gb = (unsigned)((n + 255) / 256);
   if (c->mat_kind == MB2_MAT_J2) {  // J2::CreateState (materials.cpp:151-166): temperature = initial_temperature_
-    const int64_t n = c->NE * c->nq;
-    k_fill_strided<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(n, c->ns, 10, c->mp.T0, c->d_state);
+    k_fill_strided<<<gb, 256, 0, c->stream>>>(n, c->ns, 10, c->mp.T0, c->d_state);
+    MB2_CUDA(cudaGetLastError());
+  } else if (c->mat_kind == MB2_MAT_J2SIMO) {  // J2Simo::CreateState (materials.cpp:184-203): be_old = F_old = I
+    for (int k = 0; k < c->dim; k++) {
+      k_fill_strided<<<gb, 256, 0, c->stream>>>(n, c->ns, k * (c->dim + 1), 1.0, c->d_state);
+      k_fill_strided<<<gb, 256, 0, c->stream>>>(n, c->ns, 9 + k * (c->dim + 1), 1.0, c->d_state);
+    }
+    k_fill_strided<<<gb, 256, 0, c->stream>>>(n, c->ns, 19, c->mp.T0, c->d_state);
     MB2_CUDA(cudaGetLastError());
   }
   return MB2_OK;
@@ -169,7 +177,7 @@ static int alloc_state(mb2_ctx* c) {
 
 int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
   CHECK_CTX(c);
-  REQUIRE(kind >= MB2_MAT_NEOHOOKEAN && kind <= MB2_MAT_J2, "unknown material kind");
+  REQUIRE(kind >= MB2_MAT_NEOHOOKEAN && kind <= MB2_MAT_J2SIMO, "unknown material kind");
   REQUIRE(params && nparams >= 2, "material needs {lambda, mu}");
   mb2::MatP m;
   m.lambda = params[0];
@@ -183,7 +191,7 @@ int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
     m.sqrt_3_2 = std::sqrt(3.0 / 2.0);
     m.sqrt_2_3 = std::sqrt(2.0 / 3.0);
   }
-  if (kind == MB2_MAT_J2) {
+  if (kind == MB2_MAT_J2 || kind == MB2_MAT_J2SIMO) {
     REQUIRE(nparams >= 21, "J2 needs {lambda, mu, K, G, hardening kind, hp[10], dt, heat_fraction, density, specific_heat, "
                            "initial_temperature, melting_temperature}");
     REQUIRE(c->NE > 0, "call mb2_set_connectivity before setting a material with history variables");

@@ -6,7 +6,7 @@
 
 namespace mb2 {
 
-enum : int { MAT_NEOHOOKEAN = 0, MAT_STVK = 1, MAT_J2LINEAR = 2, MAT_J2 = 3 };
+enum : int { MAT_NEOHOOKEAN = 0, MAT_STVK = 1, MAT_J2LINEAR = 2, MAT_J2 = 3, MAT_J2SIMO = 4 };
 // hardening laws (src/mimi/materials/material_hardening.hpp); hp[] layout:
 //  POWERLAW {sigma_y, n, eps0}   VOCE {sigma_y, sigma_sat, strain_constant}
 //  JC* {A, B, n, C, eps0_dot, T_ref, T_melt, m, temperature_contribution_ (constant-temperature law)}
@@ -26,7 +26,10 @@ struct MatP {
 
 // per-quadrature-point history doubles: J2Linear = plastic_strain[9], beta[9], accumulated_plastic_strain
 //                                   J2 = plastic_strain[9], accumulated_plastic_strain, temperature
-__host__ __device__ constexpr int mat_state_size(int mat) { return mat == MAT_J2LINEAR ? 19 : (mat == MAT_J2 ? 11 : 0); }
+//                                   J2Simo = be_old[9], F_old[9], accumulated_plastic_strain, temperature
+__host__ __device__ constexpr int mat_state_size(int mat) {
+  return mat == MAT_J2LINEAR ? 19 : (mat == MAT_J2 ? 11 : (mat == MAT_J2SIMO ? 20 : 0));
+}
 
 // mfem::kernels::MultABt on DIM x DIM operands (third_party/mfem/linalg/kernels.hpp:363-384):
 // C zeroed, then k outer, j, i inner: C(i,j) += A(i,k) * B(j,k).
@@ -254,15 +257,29 @@ __device__ __forceinline__ double hardening_thermo(const MatP& m, double T) {  /
 }
 // return-mapping residual (materials.hpp:345-351) for a double and for an ADScalar argument (delta / dt is a true
 // division in the first and a multiplication by 1/dt in the second, ad.inl:184-193)
-__device__ __forceinline__ double j2_residual_d(const MatP& m, double q, double eqps_old, double thermo, double de) {
+// RC = {q (or s_effective), eqps_old, thermo, simo, be_trace}: J2Simo's residual is q - G * delta * be_trace - ...
+// (materials.hpp:517-523) instead of q - 3 G delta - ...
+struct RC {
+  double q, eqps_old, thermo;
+  bool simo;
+  double bt;
+};
+__device__ __forceinline__ double j2_residual_d(const MatP& m, const RC& c, double de) {
+  const double q = c.q, eqps_old = c.eqps_old, thermo = c.thermo;
   const AD1 e = {eqps_old + de, 0.0};
   const AD1 H = hardening_evaluate(m, e);
   const double cc = hardening_rate(m, de / m.dt) * thermo;
+  if (c.simo) return -(H.v * cc) + (q - m.G * de * c.bt);
   return -(H.v * cc) + (q - 3.0 * m.G * de);
 }
-__device__ __forceinline__ AD1 j2_residual_ad(const MatP& m, double q, double eqps_old, double thermo, double x) {
+__device__ __forceinline__ AD1 j2_residual_ad(const MatP& m, const RC& c, double x) {
+  const double q = c.q, eqps_old = c.eqps_old, thermo = c.thermo;
   const double t1 = 3.0 * m.G;
   AD1 a = {-(x * t1) + q, -(1.0 * t1)};
+  if (c.simo) {
+    a.v = -((x * m.G) * c.bt) + q;
+    a.d = -((1.0 * m.G) * c.bt);
+  }
   const AD1 e = {x + eqps_old, 1.0};
   AD1 H = hardening_evaluate(m, e);
   const double inv_dt = 1 / m.dt;
@@ -274,9 +291,9 @@ __device__ __forceinline__ AD1 j2_residual_ad(const MatP& m, double q, double eq
   return a;
 }
 // mimi::solvers::ScalarSolve (src/mimi/solvers/newton.hpp:53-169), x0 = 0; failures raise the device flag
-__device__ __forceinline__ double j2_scalar_solve(const MatP& m, double q, double eqps_old, double thermo, double lower,
-                                                  double upper, double xtol, double rtol, int max_iter) {
-  const double fl = j2_residual_d(m, q, eqps_old, thermo, lower), fh = j2_residual_d(m, q, eqps_old, thermo, upper);
+static __device__ __noinline__ double j2_scalar_solve(const MatP& m, const RC& c, double lower, double upper, double xtol,
+                                               double rtol, int max_iter) {
+  const double fl = j2_residual_d(m, c, lower), fh = j2_residual_d(m, c, upper);
   if (fabs(fl) < xtol) return lower;
   if (fabs(fh) < xtol) return upper;
   if (fl * fh > 0.) {
@@ -291,7 +308,7 @@ __device__ __forceinline__ double j2_scalar_solve(const MatP& m, double q, doubl
   double x = 0.0;
   if (x < lower || x > upper) x = 0.5 * (lower + upper);
   double delta_x_old = fabs(upper - lower), delta_x = delta_x_old;
-  AD1 R = j2_residual_ad(m, q, eqps_old, thermo, x);
+  AD1 R = j2_residual_ad(m, c, x);
   double fval = R.v, df = R.d;
   int it = 0;
   bool converged = false;
@@ -309,7 +326,7 @@ __device__ __forceinline__ double j2_scalar_solve(const MatP& m, double q, doubl
       delta_x = fval / df;
       x -= delta_x;
     }
-    R = j2_residual_ad(m, q, eqps_old, thermo, x);
+    R = j2_residual_ad(m, c, x);
     fval = R.v;
     df = R.d;
     converged = (fabs(delta_x) < xtol) || (fabs(fval) < rtol);
@@ -354,11 +371,12 @@ __device__ __noinline__ void j2_plastic_stress(const MatP& m, const double* F, d
   const double q = m.sqrt_3_2 * sqrt(a);
   const double eqps_old = st[9];
   const double thermo = hardening_thermo(m, st[10]);
+  const RC rc = {q, eqps_old, thermo, false, 0.0};
   const double tolerance = m.hp[0] * 1.e-10;  // SigmaY() * k_tol
-  if (j2_residual_d(m, q, eqps_old, thermo, 0.0) > tolerance) {
+  if (j2_residual_d(m, rc, 0.0) > tolerance) {
     const AD1 e0 = {eqps_old, 0.0};
     const double upper = (q - hardening_evaluate(m, e0).v * thermo) / (3.0 * m.G);
-    const double de = j2_scalar_solve(m, q, eqps_old, thermo, 0.0, upper, 1.e-10, tolerance, 100);
+    const double de = j2_scalar_solve(m, rc, 0.0, upper, 1.e-10, tolerance, 100);
     const double al = 1.5 / q;
     if (!ACC) {
       const double cc = -2.0 * m.G * de;
@@ -374,6 +392,85 @@ __device__ __noinline__ void j2_plastic_stress(const MatP& m, const double* F, d
   if (!ACC) {
 #pragma unroll
     for (int i = 0; i < DD; i++) sigma[i] = s[i] + p * ((i % (DIM + 1) == 0) ? 1.0 : 0.0);
+  }
+}
+
+// Dev (material_utils.hpp:22-56)
+template <int DIM>
+__device__ __forceinline__ void dev_mat(const double* A, double factor, double* D) {
+  constexpr int DD = DIM * DIM;
+  double trd;
+  if (DIM == 2) trd = (A[0] + A[3]) / 2.0;
+  else trd = (A[0] + A[4] + A[8]) / 3.0;
+#pragma unroll
+  for (int i = 0; i < DD; i++) D[i] = ((i % (DIM + 1) == 0) ? (A[i] - trd) : A[i]) * factor;
+}
+
+// J2Simo::PlasticStress<ACC> (materials.hpp:455-562) on st = {be_old[9], F_old[9], eqps, temperature}; Finv / det_F
+// are NonlinearSolidWorkData::FInv / DetF. ACC == false: P out (EvaluatePK1, materials.hpp:564-570). cbrt: libdevice.
+template <int DIM, bool ACC>
+__device__ __noinline__ void j2simo_plastic_stress(const MatP& m, const double* F, const double* Finv, double det_F,
+                                                   double* st, double* P) {
+  constexpr int DD = DIM * DIM;
+  double w0[DD], w1[DD], w2[DD];
+  double* be_old = st;
+  double* F_old = st + 9;
+  mult_AB<DIM>(F_old, Finv, w0);
+  inverse_small<DIM>(w0, w1);
+  const double cb = cbrt(det_small<DIM>(w1));
+#pragma unroll
+  for (int i = 0; i < DD; i++) w1[i] *= cb;
+  mult_AB<DIM>(w1, be_old, w2);
+  mult_ABt<DIM>(w2, w1, w0);
+  double* be = w0;
+  double* s = w1;
+  double* Np = w2;
+  dev_mat<DIM>(be, m.G, s);
+  double a = 0.0;
+#pragma unroll
+  for (int i = 0; i < DD; i++) a += s[i] * s[i];
+  const double s_norm = sqrt(a);
+  if (fabs(s_norm) < 2.220446049250313e-16) {
+    const double v = sqrt(1. / 2.);
+#pragma unroll
+    for (int i = 0; i < DD; i++) Np[i] = (i % (DIM + 1) == 0) ? v : 0.0;
+  } else {
+    const double al = sqrt(3. / 2.) / s_norm;
+#pragma unroll
+    for (int i = 0; i < DD; i++) Np[i] = al * s[i];
+  }
+  double s_eff = 0.0;
+#pragma unroll
+  for (int i = 0; i < DD; i++) s_eff += Np[i] * s[i];
+  double be_trace = 0.0;
+#pragma unroll
+  for (int i = 0; i < DIM; i++) be_trace += be[i + i * DIM];
+  const RC rc = {s_eff, st[18], hardening_thermo(m, st[19]), true, be_trace};
+  const double tolerance = m.hp[0] * 1.e-10;
+  if (j2_residual_d(m, rc, 0.0) > tolerance) {
+    const AD1 e0 = {rc.eqps_old, 0.0};
+    const double upper = (s_eff - hardening_evaluate(m, e0).v * rc.thermo) / (m.G * be_trace);
+    const double de = j2_scalar_solve(m, rc, 0.0, upper, 1.e-10, tolerance, 100);
+    const double cc = -2. / 3. * de * be_trace;
+#pragma unroll
+    for (int i = 0; i < DD; i++) be[i] += cc * Np[i];
+    dev_mat<DIM>(be, m.G, s);
+    if (ACC) {
+      st[18] += de;
+      if (m.hard_kind == HARD_JC_THERMO_RATE) st[19] += m.heat_fraction * s_eff * de / (m.density * m.specific_heat);
+    }
+  }
+  if (!ACC) {
+    const double al = m.K * (det_F * det_F - 1.) * .5;
+    double* tau = w2;
+#pragma unroll
+    for (int i = 0; i < DD; i++) tau[i] = s[i] + al * ((i % (DIM + 1) == 0) ? 1.0 : 0.0);
+    mult_ABt<DIM>(tau, Finv, P);
+  } else {
+#pragma unroll
+    for (int i = 0; i < DD; i++) F_old[i] = F[i];
+#pragma unroll
+    for (int i = 0; i < DD; i++) be_old[i] = be[i];
   }
 }
 
@@ -410,6 +507,19 @@ __device__ __forceinline__ void material_pk1(const MatP& m, const double* F, con
   }
   double B[DD], sig[DD], Finv[DD];
   const double det_F = det_small<DIM>(F);
+  if (MAT == MAT_J2SIMO) {
+    double stl[20];
+#pragma unroll
+    for (int i = 0; i < DD; i++) {
+      stl[i] = st[i];
+      stl[9 + i] = st[9 + i];
+    }
+    stl[18] = st[18];
+    stl[19] = st[19];
+    inverse_small<DIM>(F, Finv);
+    j2simo_plastic_stress<DIM, false>(m, F, Finv, det_F, stl, P);
+    return;
+  }
   if (MAT == MAT_J2LINEAR) {
     double stl[19];
 #pragma unroll

@@ -58,6 +58,9 @@ def contact_main():
 J2_CASES = {"j2_cube_p2_n2": "cube_p2_n2", "j2_quad_p2_n4": "quad_p2_n4"}
 
 
+SIMO_LAWS = ("voce", "jcthermo")
+
+
 def j2_main():
     for name, base in J2_CASES.items():
         writer, elevate, refine, gf = CASES[base]
@@ -69,6 +72,10 @@ def j2_main():
                 D = O.run_ref_dump(mesh, elevate, refine, "j2_" + law, os.path.join(tmp, law), gf=gf)
                 for k_out, k_in in (("r", "r"), ("r2", "r2"), ("A", "A"), ("state", "state"), ("rb", "r_b"), ("Ab", "A_b")):
                     out[k_out + "_" + law] = D[k_in]
+            for law in SIMO_LAWS:  # J2Simo (finite strain) on two representative laws
+                D = O.run_ref_dump(mesh, elevate, refine, "j2simo_" + law, os.path.join(tmp, "simo" + law), gf=gf)
+                for k_out, k_in in (("r", "r"), ("r2", "r2"), ("A", "A"), ("state", "state"), ("rb", "r_b"), ("Ab", "A_b")):
+                    out[k_out + "_simo_" + law] = D[k_in]
             np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
             print(name, sorted(out)[:4])
 

@@ -73,11 +73,26 @@ def j2_initial_state(NE, nq):
     return S
 
 
-def mat_j2(state, law, young=2100.0, poisson=0.3):
+J2SIMO = 4
+J2SIMO_NS = 20
+
+
+def j2simo_initial_state(NE, nq, dim):
+    """J2Simo::CreateState (materials.cpp:184-203): be_old = F_old = I, zero eqps, initial temperature."""
+    S = np.zeros((NE, nq, J2SIMO_NS))
+    for k in range(dim):
+        S[:, :, k * (dim + 1)] = 1.0
+        S[:, :, 9 + k * (dim + 1)] = 1.0
+    S[:, :, 19] = J2_THERMO["T0"]
+    return S
+
+
+def mat_j2(state, law, young=2100.0, poisson=0.3, simo=False):
     lam, mu = lame(young, poisson)
     K = young / (3.0 * (1.0 - (2.0 * poisson)))
     err = C.c_int(0)
-    m = Material(J2, lam, mu, K, mu, 0, 0, 0, 0, np.sqrt(3.0 / 2.0), 0, state.ctypes.data, J2_NS, HARD[law],
+    m = Material(J2SIMO if simo else J2, lam, mu, K, mu, 0, 0, 0, 0, np.sqrt(3.0 / 2.0), 0, state.ctypes.data,
+                 J2SIMO_NS if simo else J2_NS, HARD[law],
                  (C.c_double * 10)(*hardening_params(law)), J2_THERMO["dt"], J2_THERMO["heat_fraction"],
                  J2_THERMO["density"], J2_THERMO["specific_heat"], C.pointer(err))
     m._keep = (state, err)

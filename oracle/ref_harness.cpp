@@ -87,13 +87,26 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
     m->sigma_y_ = sy ? std::atof(sy) : 2.0;
     s.mat = m;
   }
-  else if (material.rfind("j2_", 0) == 0) {
+  else if (material.rfind("j2_", 0) == 0 || material.rfind("j2simo_", 0) == 0) {
     // J2 with nonlinear isotropic hardening (materials.hpp:259-404); thermo values of tests/test_nonlinear_solid.py:16-33,
     // yield stresses scaled down so that the synthetic 1e-3 displacement field yields at part of the points
     namespace mm = mimi::materials;
-    auto m = std::make_shared<mm::J2>();
-    m->melting_temperature_ = 1500; m->initial_temperature_ = 20; m->specific_heat_ = 450; m->heat_fraction_ = 0.9;
-    const std::string h = material.substr(3);
+    const bool simo = material.rfind("j2simo_", 0) == 0;
+    std::shared_ptr<mm::HardeningBase>* hard_slot = nullptr;
+    if (simo) {
+      auto m = std::make_shared<mm::J2Simo>();
+      m->melting_temperature_ = 1500; m->initial_temperature_ = 20; m->specific_heat_ = 450; m->heat_fraction_ = 0.9;
+      hard_slot = &m->hardening_;
+      s.mat = m;
+    } else {
+      auto m = std::make_shared<mm::J2>();
+      m->melting_temperature_ = 1500; m->initial_temperature_ = 20; m->specific_heat_ = 450; m->heat_fraction_ = 0.9;
+      hard_slot = &m->hardening_;
+      s.mat = m;
+    }
+    struct { std::shared_ptr<mm::HardeningBase>& hardening_; } mref{*hard_slot};
+    auto* m = &mref;
+    const std::string h = material.substr(simo ? 7 : 3);
     auto jc_fill = [](auto& jc) { jc.A_ = 2.0; jc.B_ = 4.0; jc.n_ = 0.2835; };
     auto jcr_fill = [&](auto& jc) { jc_fill(jc); jc.C_ = 0.015; jc.effective_plastic_strain_rate_ = 1.0e-5; };
     if (h == "powerlaw") { auto hd = std::make_shared<mm::PowerLawHardening>(); hd->sigma_y_ = 2.0; hd->n_ = 3.0; hd->eps0_ = 0.01; m->hardening_ = hd; }
@@ -107,7 +120,6 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
       auto hd = std::make_shared<mm::JohnsonCookConstantTemperatureHardening>();
       jcr_fill(*hd); hd->reference_temperature_ = 10; hd->m_ = 1.3558; m->hardening_ = hd;
     } else { std::fprintf(stderr, "unknown hardening %s\n", h.c_str()); std::exit(2); }
-    s.mat = m;
   }
   else { std::fprintf(stderr, "unknown material %s\n", material.c_str()); std::exit(2); }
   s.mat->density_ = 1.0;
@@ -306,12 +318,12 @@ int main(int argc, char** argv) {
     s.integ->AddDomainResidualAndGrad(u, gf, r2, A);
     dump(out, "r2.f64", r2.GetData(), (size_t)NV);
     dump(out, "A.f64", A.GetData(), (size_t)nnz);
-    if (material == "j2linear" || material.rfind("j2_", 0) == 0) {
+    if (material == "j2linear" || material.rfind("j2", 0) == 0) {
       s.integ->DomainPostTimeAdvance(u);
       // history layout: every state matrix in a 9-double slot (column-major dim x dim in front), then the scalars;
       // J2Linear has k_state_scalars = 2 but only uses the first (19 doubles), J2 = 9 + 2
       const bool lin = material == "j2linear";
-      const int ns = lin ? 19 : 11;
+      const int ns = lin ? 19 : 9 * (int)eqd[0].GetQuadData()[0].material_state->matrices.size() + 2;
       std::vector<double> st((size_t)NE * nq * ns, 0.0);
       for (int e = 0; e < NE; ++e)
         for (int q = 0; q < nq; ++q) {

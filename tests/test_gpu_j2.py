@@ -136,3 +136,42 @@ def test_j2_scalar_solve_failure_is_reported(ctx_factory):
         ctx.add_domain_residual(D["u"], r)
     ctx.set_material(3, j2_params("jcrate"))      # recovers
     ctx.add_domain_residual(D["u"], r)
+
+
+from tests.cases import SIMO_LAWS  # noqa: E402
+
+
+@pytest.mark.parametrize("law", SIMO_LAWS)
+@pytest.mark.parametrize("name", J2_CASES)
+def test_j2simo_golden(ctx_factory, name, law):
+    """J2Simo (materials.hpp:406-579): libdevice cbrt / pow / exp / log. Residual and history 1e-12 as for J2; FD tangent
+    2e-3 of the largest entry: the formulation takes dev(b_e) of b_e = I + O(strain), so a last-bit difference in
+    cbrt(det f) (1e-16 of b_e) is a 1e-13 relative difference of the deviatoric stress at strains of 1e-3, which the
+    forward difference divides by h = 1e-8 |u| ~ 1e-11. The reference's own K carries rounding noise of that size
+    (observed deviations are printed: 2e-5 .. 4e-4)."""
+    D = load_j2_golden(name)
+    k = "_simo_" + law
+    ctx = ctx_factory()
+    ctx.set_connectivity(D["dim"], D["nd"], D["nq"], D["NV"], D["v_dofs"])
+    ctx.upload_quad_tables(D["dN_dX"], D["w"], D["detJ"])
+    ctx.build_pattern()
+    ctx.set_material(4, j2_params(law))
+    assert ctx.state_size() == O.J2SIMO_NS
+    assert np.array_equal(ctx.get_state(), O.j2simo_initial_state(D["NE"], D["nq"], D["dim"]))
+    r = np.zeros(D["NV"])
+    ctx.add_domain_residual(D["u"], r)
+    assert _rel(r, D["r" + k]) <= 1e-12
+    r2 = np.zeros(D["NV"])
+    A = D["mass"].copy()
+    ctx.add_domain_residual_and_grad(D["u"], D["gf"], r2, A)
+    assert np.array_equal(r2, r) and _rel(A, D["A" + k]) <= 2e-3
+    ctx.post_time_advance(D["u"])
+    S = ctx.get_state()
+    assert _rel(S, D["state" + k]) <= 1e-12
+    rb = np.zeros(D["NV"])
+    Ab = D["mass"].copy()
+    ctx.add_domain_residual_and_grad(np.ascontiguousarray(1.5 * D["u"]), D["gf"], rb, Ab)
+    assert _rel(rb, D["rb" + k]) <= 1e-12 and _rel(Ab, D["Ab" + k]) <= 2e-3
+    print("\n[j2simo %s %s] rel dev: r %.1e  A %.1e  state %.1e  rb %.1e  Ab %.1e" % (
+        name, law, _rel(r, D["r" + k]), _rel(A, D["A" + k]), _rel(S, D["state" + k]), _rel(rb, D["rb" + k]),
+        _rel(Ab, D["Ab" + k])))

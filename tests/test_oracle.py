@@ -84,3 +84,24 @@ def test_j2_hardening_laws_bit_exact(name, law):
     rb, Ab = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], 1.5 * D["u"], D["gf"], D["mass"])
     assert np.array_equal(rb, D["rb_" + law]) and np.array_equal(Ab, D["Ab_" + law])
     assert m._keep[1].value == 0
+
+
+from tests.cases import SIMO_LAWS  # noqa: E402
+
+
+@pytest.mark.parametrize("law", SIMO_LAWS)
+@pytest.mark.parametrize("name", J2_CASES)
+def test_j2simo_bit_exact(name, law):
+    """J2Simo (finite strain, materials.hpp:406-579): be_old / F_old history, cbrt, s_effective residual."""
+    D = load_j2_golden(name)
+    S = O.j2simo_initial_state(D["NE"], D["nq"], D["dim"])
+    m = O.mat_j2(S, law, simo=True)
+    args = (D["dim"], D["nd"], D["nq"], m, D["v_dofs"])
+    k = "_simo_" + law
+    assert np.array_equal(O.assemble_residual(*args, D["dN_dX"], D["w"], D["detJ"], D["u"]), D["r" + k])
+    r2, A = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], D["u"], D["gf"], D["mass"])
+    assert np.array_equal(r2, D["r2" + k]) and np.array_equal(A, D["A" + k])
+    O.post_time_advance(D["dim"], D["nd"], D["nq"], m, D["v_dofs"], D["dN_dX"], D["u"])
+    assert np.array_equal(S, D["state" + k])
+    rb, Ab = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], 1.5 * D["u"], D["gf"], D["mass"])
+    assert np.array_equal(rb, D["rb" + k]) and np.array_equal(Ab, D["Ab" + k])
