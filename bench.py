@@ -151,7 +151,7 @@ def reference_arm(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.time() - t0}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -328,7 +328,7 @@ def gpu_arm(args):
                            "setup_s": M["setup_s"]},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "wall_s_timed_region": wall}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
@@ -338,6 +338,15 @@ def gpu_arm(args):
 def C_void(t):
     import ctypes
     return ctypes.c_void_p(t.data_ptr())
+
+
+_JSON_OUT = None
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
@@ -355,6 +364,12 @@ def main():
     ap.add_argument("--material", default="neohookean", choices=["neohookean", "stvk"])
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     args = ap.parse_args()
+    # The contract is ONE JSON line on stdout: libraries that write to fd 1 (NCCL prints its version banner there)
+    # are sent to stderr; the JSON line goes to the original stdout.
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = max(args.warmup, 3) if not os.environ.get("MB2_BENCH_ALLOW_SHORT") else args.warmup
     if args.impl == "reference":

@@ -179,7 +179,13 @@ enum {
    * params = o[3], t0[3], t1[3], lo, hi  (unused components 0; 2D uses o[0..1], t0[0..1]) */
   MB2_RIGID_PLANE = 0,
   /* closest point on the circle (2D) / sphere (3D): params = c[3], R; the outward normal is the contact normal */
-  MB2_RIGID_SPHERE = 1
+  MB2_RIGID_SPHERE = 1,
+  /* Bezier curve (2D) / tensor-product surface (3D), degree 1..5, what NearestDistanceToSplines::AddSpline holds
+   * (coefficients/nearest_distance.hpp:225-244): params = deg_u, deg_v (0 for curves), n_seed, control points
+   * [deg_v+1][deg_u+1][dim] (u fastest). Closest point: nearest of (n_seed+1)^(dim-1) samples, then bound-clipped
+   * Newton. The reference delegates this search to splinepy: converged results agree to rounding, not bitwise
+   * (parity unpinned). The spline's orientation defines the contact normal as in the reference. */
+  MB2_RIGID_BEZIER = 2
 };
 /* The marked boundary faces and their quadrature tables as PrecomputedData holds them for the integrator's name
  * (CreateBoundaryElementQuadData + PrecomputeElementQuadData(name, order, false), precomputed.cpp:243-330):

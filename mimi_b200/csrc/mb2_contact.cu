@@ -21,7 +21,11 @@ namespace mb2 {
 struct RigidBody {
   int kind = -1;
   double p[16] = {0};
+  // MB2_RIGID_BEZIER: degrees, sampling resolution of the initial guess, control net [deg_v+1][deg_u+1][dim] (device)
+  int deg_u = 0, deg_v = 0, n_seed = 0;
+  const double* cp = nullptr;
 };
+constexpr int BEZ_MAXDEG = 5;
 
 struct ContactState {
   int64_t NF = 0;
@@ -48,17 +52,151 @@ struct ContactState {
   double* d_fR = nullptr;          // NF x tdf
   double* d_fK = nullptr;          // NF x tdf x tdf (column-major, column = perturbed dof)
   double* d_scal = nullptr;        // 8: area, pressure integral, force[3], gap norm
+  double* d_cp = nullptr;          // Bezier control net
   RigidBody body;
   double penalty = 1e4;            // NearestDistanceBase::coefficient_
   std::vector<std::pair<int64_t, int64_t>> runs;  // CSR value ranges of the marked nodes' block rows (merged)
   double h_scal[8] = {0};
 };
 
+// ---- Bezier rigid bodies (curve in 2D, tensor-product surface in 3D): PARITY UNPINNED against the reference, whose
+// NearestDistanceToSplines hands the search to splinepy (k-d tree of sampled points, Newton with bound clipping, SLSQP
+// fallback). Restated scheme: sampled initial guess + bound-clipped Newton on |S(xi) - q|^2 / 2 with the exact Hessian
+// (Gauss-Newton when it is not positive definite), in the operation order of oracle/mimi_oracle_contact.c
+// (orc_bezier_nearest), which the tests compare bit for bit.
+__device__ __forceinline__ void bernstein(int p, double t, double* B, double* dB, double* ddB) {
+  double lvl[BEZ_MAXDEG + 1][BEZ_MAXDEG + 1];
+  const double s = 1.0 - t;
+  lvl[0][0] = 1.0;
+  for (int k = 1; k <= p; k++)
+    for (int i = 0; i <= k; i++) {
+      const double a = (i < k) ? s * lvl[k - 1][i] : 0.0;
+      const double b = (i > 0) ? t * lvl[k - 1][i - 1] : 0.0;
+      lvl[k][i] = a + b;
+    }
+  for (int i = 0; i <= p; i++) {
+    B[i] = lvl[p][i];
+    double d1 = 0.0, d2 = 0.0;
+    if (p >= 1) {
+      const double lo = (i > 0) ? lvl[p - 1][i - 1] : 0.0;
+      const double hi = (i < p) ? lvl[p - 1][i] : 0.0;
+      d1 = (double)p * (lo - hi);
+    }
+    if (p >= 2) {
+      const double a = (i > 1) ? lvl[p - 2][i - 2] : 0.0;
+      const double b = (i > 0 && i < p) ? lvl[p - 2][i - 1] : 0.0;
+      const double c = (i < p - 1) ? lvl[p - 2][i] : 0.0;
+      d2 = (double)(p * (p - 1)) * (a - 2.0 * b + c);
+    }
+    dB[i] = d1;
+    ddB[i] = d2;
+  }
+}
+
+// S, S_u, S_v, S_uu, S_uv, S_vv at (u, v)
+template <int DIM>
+__device__ __noinline__ void bezier_eval(const RigidBody& b, double u, double v, double (*out)[3]) {
+  double Bu[BEZ_MAXDEG + 1], dBu[BEZ_MAXDEG + 1], ddBu[BEZ_MAXDEG + 1];
+  double Bv[BEZ_MAXDEG + 1], dBv[BEZ_MAXDEG + 1], ddBv[BEZ_MAXDEG + 1];
+  bernstein(b.deg_u, u, Bu, dBu, ddBu);
+  bernstein(b.deg_v, v, Bv, dBv, ddBv);
+  for (int k = 0; k < 6; k++)
+    for (int d = 0; d < 3; d++) out[k][d] = 0.0;
+  for (int j = 0; j <= b.deg_v; j++)
+    for (int i = 0; i <= b.deg_u; i++) {
+      const double* P = b.cp + ((size_t)j * (b.deg_u + 1) + i) * DIM;
+      const double w[6] = {Bu[i] * Bv[j], dBu[i] * Bv[j], Bu[i] * dBv[j], ddBu[i] * Bv[j], dBu[i] * dBv[j], Bu[i] * ddBv[j]};
+      for (int k = 0; k < 6; k++)
+#pragma unroll
+        for (int d = 0; d < DIM; d++) out[k][d] += w[k] * P[d];
+    }
+}
+
+template <int DIM>
+__device__ __noinline__ void rigid_nearest_bezier(const RigidBody& b, const double* q, double* pmq, double& distance,
+                                                  double* fd) {
+  constexpr int PD = DIM - 1;
+  const int ns = b.n_seed;
+  double E[6][3];
+  double best = 1e300, u = 0.0, v = 0.0;
+  for (int jv = 0; jv <= (PD == 2 ? ns : 0); jv++)
+    for (int iu = 0; iu <= ns; iu++) {
+      const double su = (double)iu / (double)ns, sv = (PD == 2) ? (double)jv / (double)ns : 0.0;
+      bezier_eval<DIM>(b, su, sv, E);
+      double d2 = 0.0;
+#pragma unroll
+      for (int d = 0; d < DIM; d++) d2 += (E[0][d] - q[d]) * (E[0][d] - q[d]);
+      if (d2 < best) {
+        best = d2;
+        u = su;
+        v = sv;
+      }
+    }
+  for (int it = 0; it < 40; it++) {
+    bezier_eval<DIM>(b, u, v, E);
+    double r[3] = {0, 0, 0};
+#pragma unroll
+    for (int d = 0; d < DIM; d++) r[d] = E[0][d] - q[d];
+    double g0 = 0.0, g1 = 0.0, a00 = 0.0, a01 = 0.0, a11 = 0.0, h00 = 0.0, h01 = 0.0, h11 = 0.0;
+#pragma unroll
+    for (int d = 0; d < DIM; d++) {
+      g0 += r[d] * E[1][d];
+      g1 += r[d] * E[2][d];
+      a00 += E[1][d] * E[1][d];
+      a01 += E[1][d] * E[2][d];
+      a11 += E[2][d] * E[2][d];
+      h00 += r[d] * E[3][d];
+      h01 += r[d] * E[4][d];
+      h11 += r[d] * E[5][d];
+    }
+    double du, dv = 0.0;
+    if (PD == 1) {
+      double H = a00 + h00;
+      if (!(H > 0.0)) H = a00;
+      du = -g0 / H;
+    } else {
+      double H00 = a00 + h00, H01 = a01 + h01, H11 = a11 + h11;
+      double det = H00 * H11 - H01 * H01;
+      if (!(H00 > 0.0 && det > 0.0)) {
+        H00 = a00; H01 = a01; H11 = a11;
+        det = H00 * H11 - H01 * H01;
+      }
+      du = (-g0 * H11 + g1 * H01) / det;
+      dv = (-g1 * H00 + g0 * H01) / det;
+    }
+    double un = u + du, vn = v + dv;
+    if (un < 0.0) un = 0.0;
+    if (un > 1.0) un = 1.0;
+    if (vn < 0.0) vn = 0.0;
+    if (vn > 1.0) vn = 1.0;
+    const double mu = fabs(un - u), mv = fabs(vn - v);
+    u = un;
+    v = vn;
+    if (mu <= 1e-16 && mv <= 1e-16) break;
+  }
+  bezier_eval<DIM>(b, u, v, E);
+  double sum = 0.0;
+#pragma unroll
+  for (int d = 0; d < DIM; d++) {
+    pmq[d] = E[0][d] - q[d];
+    sum += pmq[d] * pmq[d];
+  }
+  distance = sqrt(sum);
+#pragma unroll
+  for (int k = 0; k < PD; k++)
+#pragma unroll
+    for (int d = 0; d < DIM; d++) fd[k * DIM + d] = E[1 + k][d];
+}
+
 // ---- rigid bodies: closed-form closest point, the operation order of oracle/ref_harness.cpp (RigidPlane,
 // RigidSphere). Fills what MortarContact reads from NearestDistanceBase::Results (nearest_distance.hpp:139-193).
 template <int DIM>
 __device__ __forceinline__ void rigid_nearest(const RigidBody& b, const double* q, double* pmq, double& distance,
                                               double* fd) {
+  if (b.kind == MB2_RIGID_BEZIER) {
+    rigid_nearest_bezier<DIM>(b, q, pmq, distance, fd);
+    return;
+  }
   if (b.kind == MB2_RIGID_PLANE) {
     const double* o = b.p;
     const double lo = b.p[9], hi = b.p[10];
@@ -488,7 +626,7 @@ void free_contact(mb2_ctx* c) {
   for (void* p : {(void*)S->d_fvdofs, (void*)S->d_flocal, (void*)S->d_fN, (void*)S->d_fdN, (void*)S->d_fw, (void*)S->d_frank,
                   (void*)S->d_mnode, (void*)S->d_mn_ptr, (void*)S->d_mn_face, (void*)S->d_mn_loc, (void*)S->d_la,
                   (void*)S->d_lg, (void*)S->d_fsum, (void*)S->d_gap, (void*)S->d_area, (void*)S->d_press,
-                  (void*)S->d_active, (void*)S->d_fR, (void*)S->d_fK, (void*)S->d_scal})
+                  (void*)S->d_active, (void*)S->d_fR, (void*)S->d_fK, (void*)S->d_scal, (void*)S->d_cp})
     if (p) cudaFree(p);
   delete S;
   c->contact = nullptr;
@@ -719,8 +857,29 @@ int mb2_contact_set_rigid_body(mb2_ctx* c, int kind, const double* params, int n
   CCHECK(c);
   ContactState* S = static_cast<ContactState*>(c->contact);
   CREQ(S, "call mb2_contact_set_faces first");
-  CREQ(kind == MB2_RIGID_PLANE || kind == MB2_RIGID_SPHERE, "unknown rigid body kind");
+  CREQ(kind == MB2_RIGID_PLANE || kind == MB2_RIGID_SPHERE || kind == MB2_RIGID_BEZIER, "unknown rigid body kind");
+  if (kind == MB2_RIGID_BEZIER) {
+    CREQ(params && nparams >= 3, "Bezier body needs {deg_u, deg_v, n_seed, control points}");
+    const int du = (int)params[0], dv = (int)params[1], ns = (int)params[2];
+    CREQ(du >= 1 && du <= mb2::BEZ_MAXDEG && dv >= 0 && dv <= mb2::BEZ_MAXDEG && ns >= 1, "Bezier degree must be 1..5");
+    CREQ((c->dim == 2) == (dv == 0), "a 2D body is a curve (deg_v = 0), a 3D body a surface");
+    const int ncp = (du + 1) * (dv + 1) * c->dim;
+    CREQ(nparams == 3 + ncp, "Bezier control point count does not match the degrees");
+    MB2_CUDA(cudaSetDevice(c->device));
+    MB2_CUDA(cudaStreamSynchronize(c->stream));  // a previous assembly may still read the old control net
+    if (S->d_cp) cudaFree(S->d_cp);
+    S->d_cp = nullptr;
+    MB2_CUDA(cudaMalloc(&S->d_cp, sizeof(double) * ncp));
+    MB2_CUDA(cudaMemcpy(S->d_cp, params + 3, sizeof(double) * ncp, cudaMemcpyHostToDevice));
+    S->body = mb2::RigidBody();
+    S->body.kind = kind;
+    S->body.deg_u = du; S->body.deg_v = dv; S->body.n_seed = ns;
+    S->body.cp = S->d_cp;
+    S->penalty = penalty;
+    return MB2_OK;
+  }
   CREQ(params && nparams >= (kind == MB2_RIGID_PLANE ? 11 : 4) && nparams <= 16, "rigid body parameter count");
+  S->body = mb2::RigidBody();
   S->body.kind = kind;
   for (int i = 0; i < 16; i++) S->body.p[i] = i < nparams ? params[i] : 0.0;
   S->penalty = penalty;

@@ -27,13 +27,22 @@ typedef struct {
   int kind;
   int dim;
   double p[16];
+  /* kind == ORC_RIGID_BEZIER (below): degrees, sampling resolution of the initial guess, control net */
+  int deg_u, deg_v, n_seed;
+  const double* cp;
 } orc_rigid;
+
+static void rigid_bezier_nearest(const orc_rigid* b, const double* q, double* pmq, double* distance, double* fd);
 
 /* NearestDistanceBase::NearestDistance as implemented by RigidPlane / RigidSphere in oracle/ref_harness.cpp,
  * filling what MortarContact reads from Results (src/mimi/coefficients/nearest_distance.hpp:139-193):
  * pmq = physical - query, distance, fd = first_derivatives [para_dim x dim]. */
 void orc_rigid_nearest(const orc_rigid* b, const double* q, double* pmq, double* distance, double* fd) {
   const int dim = b->dim;
+  if (b->kind == 2) { /* ORC_RIGID_BEZIER */
+    rigid_bezier_nearest(b, q, pmq, distance, fd);
+    return;
+  }
   if (b->kind == ORC_RIGID_PLANE) {
     const double* o = b->p;
     const double* t[2] = {b->p + 3, b->p + 6};
@@ -335,4 +344,157 @@ double orc_contact_gap_norm(int dim, int64_t NF, int ndf, int nqf, const int32_t
   }
   free(x);
   return sqrt(sum);
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Bezier rigid bodies (curve in 2D, tensor-product surface in 3D) -- PARITY UNPINNED.
+ * The reference's NearestDistanceToSplines hands the closest-point search to splinepy (third_party/splinepy @ f1662da:
+ * k-d tree of sampled points for the initial guess, Newton with bound clipping, SLSQP fallback; tolerance 1e-24, i.e.
+ * iterate to the end), which is not linked into oracle/_ref. What is restated here is the published scheme -- sampled
+ * initial guess + bound-clipped Newton on J = |S(xi) - q|^2 / 2 with the exact Hessian, Gauss-Newton when that is
+ * not positive definite -- in a fixed operation order that mb2_contact.cu (rigid_nearest_bezier) repeats bit for bit.
+ * A converged search returns the same closest point as splinepy to rounding (checked in tests by first-order
+ * optimality and against dense sampling), not the same bits.
+ * cp layout: [deg_v + 1][deg_u + 1][dim], u fastest; curves have deg_v = 0.
+ * --------------------------------------------------------------------------------------------------------------- */
+#define ORC_RIGID_BEZIER 2
+#define ORC_BEZ_MAXDEG 5
+
+typedef struct {
+  int dim, deg_u, deg_v, n_seed;
+  const double* cp;
+} orc_bezier;
+
+/* Bernstein basis of degree p at t with first and second derivatives (recurrence on the lower-degree bases) */
+static void bernstein(int p, double t, double* B, double* dB, double* ddB) {
+  double lvl[ORC_BEZ_MAXDEG + 1][ORC_BEZ_MAXDEG + 1];
+  const double s = 1.0 - t;
+  lvl[0][0] = 1.0;
+  for (int k = 1; k <= p; k++)
+    for (int i = 0; i <= k; i++) {
+      const double a = (i < k) ? s * lvl[k - 1][i] : 0.0;
+      const double b = (i > 0) ? t * lvl[k - 1][i - 1] : 0.0;
+      lvl[k][i] = a + b;
+    }
+  for (int i = 0; i <= p; i++) {
+    B[i] = lvl[p][i];
+    double d1 = 0.0, d2 = 0.0;
+    if (p >= 1) {
+      const double lo = (i > 0) ? lvl[p - 1][i - 1] : 0.0;
+      const double hi = (i < p) ? lvl[p - 1][i] : 0.0;
+      d1 = (double)p * (lo - hi);
+    }
+    if (p >= 2) {
+      const double a = (i > 1) ? lvl[p - 2][i - 2] : 0.0;
+      const double b = (i > 0 && i < p) ? lvl[p - 2][i - 1] : 0.0;
+      const double c = (i < p - 1) ? lvl[p - 2][i] : 0.0;
+      d2 = (double)(p * (p - 1)) * (a - 2.0 * b + c);
+    }
+    dB[i] = d1;
+    ddB[i] = d2;
+  }
+}
+
+/* S, S_u, S_v, S_uu, S_uv, S_vv at (u, v): out[6][3] */
+static void bezier_eval(const orc_bezier* b, double u, double v, double out[6][3]) {
+  double Bu[ORC_BEZ_MAXDEG + 1], dBu[ORC_BEZ_MAXDEG + 1], ddBu[ORC_BEZ_MAXDEG + 1];
+  double Bv[ORC_BEZ_MAXDEG + 1], dBv[ORC_BEZ_MAXDEG + 1], ddBv[ORC_BEZ_MAXDEG + 1];
+  bernstein(b->deg_u, u, Bu, dBu, ddBu);
+  bernstein(b->deg_v, v, Bv, dBv, ddBv);
+  for (int k = 0; k < 6; k++)
+    for (int d = 0; d < 3; d++) out[k][d] = 0.0;
+  for (int j = 0; j <= b->deg_v; j++)
+    for (int i = 0; i <= b->deg_u; i++) {
+      const double* P = b->cp + ((size_t)j * (b->deg_u + 1) + i) * b->dim;
+      const double w[6] = {Bu[i] * Bv[j], dBu[i] * Bv[j], Bu[i] * dBv[j], ddBu[i] * Bv[j], dBu[i] * dBv[j], Bu[i] * ddBv[j]};
+      for (int k = 0; k < 6; k++)
+        for (int d = 0; d < b->dim; d++) out[k][d] += w[k] * P[d];
+    }
+}
+
+void orc_bezier_nearest(const orc_bezier* b, const double* q, double* xi, double* pmq, double* distance, double* fd) {
+  const int dim = b->dim, pd = dim - 1, ns = b->n_seed;
+  double E[6][3];
+  /* initial guess: nearest point of a uniform (ns+1)^pd sampling */
+  double best = 1e300, u = 0.0, v = 0.0;
+  for (int jv = 0; jv <= (pd == 2 ? ns : 0); jv++)
+    for (int iu = 0; iu <= ns; iu++) {
+      const double su = (double)iu / (double)ns, sv = (pd == 2) ? (double)jv / (double)ns : 0.0;
+      bezier_eval(b, su, sv, E);
+      double d2 = 0.0;
+      for (int d = 0; d < dim; d++) d2 += (E[0][d] - q[d]) * (E[0][d] - q[d]);
+      if (d2 < best) {
+        best = d2;
+        u = su;
+        v = sv;
+      }
+    }
+  for (int it = 0; it < 40; it++) {
+    bezier_eval(b, u, v, E);
+    double r[3] = {0, 0, 0};
+    for (int d = 0; d < dim; d++) r[d] = E[0][d] - q[d];
+    double g0 = 0.0, g1 = 0.0, a00 = 0.0, a01 = 0.0, a11 = 0.0, h00 = 0.0, h01 = 0.0, h11 = 0.0;
+    for (int d = 0; d < dim; d++) {
+      g0 += r[d] * E[1][d];
+      g1 += r[d] * E[2][d];
+      a00 += E[1][d] * E[1][d];
+      a01 += E[1][d] * E[2][d];
+      a11 += E[2][d] * E[2][d];
+      h00 += r[d] * E[3][d];
+      h01 += r[d] * E[4][d];
+      h11 += r[d] * E[5][d];
+    }
+    double du, dv = 0.0;
+    if (pd == 1) {
+      double H = a00 + h00;
+      if (!(H > 0.0)) H = a00; /* Gauss-Newton when the exact Hessian is not positive */
+      du = -g0 / H;
+    } else {
+      double H00 = a00 + h00, H01 = a01 + h01, H11 = a11 + h11;
+      double det = H00 * H11 - H01 * H01;
+      if (!(H00 > 0.0 && det > 0.0)) {
+        H00 = a00; H01 = a01; H11 = a11;
+        det = H00 * H11 - H01 * H01;
+      }
+      du = (-g0 * H11 + g1 * H01) / det;
+      dv = (-g1 * H00 + g0 * H01) / det;
+    }
+    double un = u + du, vn = v + dv;
+    if (un < 0.0) un = 0.0;
+    if (un > 1.0) un = 1.0;
+    if (vn < 0.0) vn = 0.0;
+    if (vn > 1.0) vn = 1.0;
+    const double mu = fabs(un - u), mv = fabs(vn - v);
+    u = un;
+    v = vn;
+    if (mu <= 1e-16 && mv <= 1e-16) break;
+  }
+  bezier_eval(b, u, v, E);
+  double sum = 0.0;
+  for (int d = 0; d < dim; d++) {
+    pmq[d] = E[0][d] - q[d];
+    sum += pmq[d] * pmq[d];
+  }
+  *distance = sqrt(sum);
+  for (int k = 0; k < pd; k++)
+    for (int d = 0; d < dim; d++) fd[k * dim + d] = E[1 + k][d];
+  if (xi) {
+    xi[0] = u;
+    if (pd == 2) xi[1] = v;
+  }
+}
+
+static void rigid_bezier_nearest(const orc_rigid* b, const double* q, double* pmq, double* distance, double* fd) {
+  const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp};
+  orc_bezier_nearest(&z, q, 0, pmq, distance, fd);
+}
+
+/* test helper: closest point only (xi out) */
+void orc_rigid_query(const orc_rigid* b, const double* q, double* xi, double* pmq, double* distance, double* fd) {
+  if (b->kind == ORC_RIGID_BEZIER) {
+    const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp};
+    orc_bezier_nearest(&z, q, xi, pmq, distance, fd);
+  } else {
+    orc_rigid_nearest(b, q, pmq, distance, fd);
+  }
 }

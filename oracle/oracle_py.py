@@ -256,7 +256,39 @@ RIGID_PLANE, RIGID_SPHERE = 0, 1
 
 
 class Rigid(C.Structure):
-    _fields_ = [("kind", C.c_int), ("dim", C.c_int), ("p", C.c_double * 16)]
+    _fields_ = [("kind", C.c_int), ("dim", C.c_int), ("p", C.c_double * 16), ("deg_u", C.c_int), ("deg_v", C.c_int),
+                ("n_seed", C.c_int), ("cp", C.c_void_p)]
+
+
+RIGID_BEZIER = 2
+
+
+def rigid_bezier(dim, cps, n_seed=None):
+    """cps: curve [deg_u+1, 2] or surface [deg_v+1, deg_u+1, 3] (u fastest). PARITY UNPINNED (see the C file)."""
+    cps = np.ascontiguousarray(cps, np.float64)
+    if dim == 2:
+        deg_u, deg_v = cps.shape[0] - 1, 0
+    else:
+        deg_v, deg_u = cps.shape[0] - 1, cps.shape[1] - 1
+    n_seed = n_seed or (64 if dim == 2 else 16)
+    r = Rigid(RIGID_BEZIER, dim, (C.c_double * 16)(), deg_u, deg_v, n_seed, cps.ctypes.data)
+    r._keep = cps
+    return r
+
+
+def bezier_params(dim, cps, n_seed=None):
+    """Flat parameter list of mb2_contact_set_rigid_body(MB2_RIGID_BEZIER): {deg_u, deg_v, n_seed, control points}."""
+    b = rigid_bezier(dim, cps, n_seed)
+    return np.concatenate([[b.deg_u, b.deg_v, b.n_seed], b._keep.ravel()])
+
+
+def rigid_query(body, q):
+    q = np.ascontiguousarray(q, np.float64)
+    xi, pmq, fd = np.zeros(2), np.zeros(3), np.zeros(6)
+    dist = C.c_double()
+    lib().orc_rigid_query(C.byref(body), _p(q, C.c_double), _p(xi, C.c_double), _p(pmq, C.c_double), C.byref(dist),
+                          _p(fd, C.c_double))
+    return xi, pmq[:body.dim], dist.value, fd[:(body.dim - 1) * body.dim].reshape(body.dim - 1, body.dim)
 
 
 def rigid_plane(dim, o, t0, t1=None, lo=-1e300, hi=1e300):
@@ -266,14 +298,14 @@ def rigid_plane(dim, o, t0, t1=None, lo=-1e300, hi=1e300):
     if t1 is not None:
         p[6:6 + dim] = t1
     p[9], p[10] = lo, hi
-    return Rigid(RIGID_PLANE, dim, (C.c_double * 16)(*p))
+    return Rigid(RIGID_PLANE, dim, (C.c_double * 16)(*p), 0, 0, 0, None)
 
 
 def rigid_sphere(dim, c, R):
     p = np.zeros(16)
     p[0:dim] = c
     p[3] = R
-    return Rigid(RIGID_SPHERE, dim, (C.c_double * 16)(*p))
+    return Rigid(RIGID_SPHERE, dim, (C.c_double * 16)(*p), 0, 0, 0, None)
 
 
 def rigid_from_spec(dim, spec):

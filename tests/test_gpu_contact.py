@@ -121,3 +121,42 @@ def test_contact_call_order_errors(ctx_factory):
     r = np.zeros(D["NV"])
     with pytest.raises(capi.Mb2Error):
         ctx.add_boundary_residual(D["u"], r)                                         # no rigid body yet
+
+
+# ---- Bezier rigid bodies: the device repeats the C oracle's closest-point search bit for bit; against the reference
+# (splinepy's search) this body kind is parity-unpinned -- see oracle/mimi_oracle_contact.c and DESIGN.md section 5.
+def _bezier_cases():
+    # the curve of examples/nl_contact.py (its normal (d1, -d0) points down onto the body's top edge), moved into light
+    # penetration of the 2 x 1 quad fixture: the curve's lowest point is 0.85 above its control polygon's y origin
+    curve = (np.array([[-2.5, 1.3], [0.3, 0.7], [0.7, 0.7], [1.5, 1.3]]) + [0.6, 0.1495])
+    g = np.linspace(0.0, 1.0, 3)
+    dome = np.zeros((3, 3, 3))
+    for j in range(3):
+        for i in range(3):
+            # u runs along y and v along x so that S_u x S_v points down (-z), towards the cube below
+            dome[j, i] = [1.4 * g[j] - 0.2, 1.4 * g[i] - 0.2, 0.6996 + 1.2 * ((g[i] - 0.5) ** 2 + (g[j] - 0.5) ** 2)]
+    return {"contact_quad_p3_n4_sphere": curve, "contact_cube_p2_n4_sphere": dome}
+
+
+@pytest.mark.parametrize("name", ["contact_quad_p3_n4_sphere", "contact_cube_p2_n4_sphere"])
+def test_contact_bezier_body_vs_oracle(ctx_factory, name):
+    D = load_contact_golden(name)
+    dim = D["dim"]
+    cps = _bezier_cases()[name]
+    ctx = setup_contact(ctx_factory(), D)
+    ctx.contact_set_rigid_body(capi.MB2_RIGID_BEZIER, O.bezier_params(dim, cps), D["penalty"])
+    body = O.rigid_bezier(dim, cps)
+    local, nm, _ = O.contact_prepare(dim, D["c_v_dofs"])
+    gap, area, pr, tot = O.contact_pressure(dim, D["c_v_dofs"], local, nm, D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"],
+                                            D["u"], body, D["penalty"])
+    assert 2 <= (pr != 0).sum()                        # the body really touches
+    r_o, A_o = D["c_r0"].copy(), D["mass"].copy()
+    O.contact_assemble(dim, D["c_v_dofs"], local, D["c_A_ids"], D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"], D["u"], pr,
+                       True, D["gf"], r_o, A_o)
+    r, A = D["c_r0"].copy(), D["mass"].copy()
+    ctx.add_boundary_residual_and_grad(D["u"], D["gf"], r, A)
+    g2, a2, p2 = ctx.contact_nodal()
+    assert np.array_equal(g2, gap) and np.array_equal(a2, area) and np.array_equal(p2, pr)
+    assert np.array_equal(r, r_o) and np.array_equal(A, A_o)
+    assert close(ctx.contact_gap_norm(D["u"]),
+                 O.contact_gap_norm(dim, D["c_v_dofs"], D["c_N"], D["c_w"], D["c_x_ref"], D["u"], body))

@@ -48,3 +48,33 @@ def test_clamped_plane_exercises_the_angle_filter():
     b = O.contact_pressure(2, D["c_v_dofs"], local, nm, D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"], D["u"],
                            O.rigid_from_spec(2, unclamped), D["penalty"])
     assert np.abs(a[0]).sum() < 0.1 * np.abs(b[0]).sum()      # most penetrating gaps are filtered out
+
+
+def test_bezier_closest_point_properties():
+    """Bezier rigid bodies are parity-unpinned against splinepy's search; the restated search is checked by what a
+    closest point must satisfy: no sampled point is closer, and the residual is orthogonal to the tangents unless the
+    point sits on the parametric boundary."""
+    rng = np.random.default_rng(0)
+    cps = np.array([[-2.5, 1.3], [0.3, 0.7], [0.7, 0.7], [1.5, 1.3]]) + [0.05, 1.0]     # examples/nl_contact.py
+    b = O.rigid_bezier(2, cps)
+    ts = np.linspace(0, 1, 20001)
+    B = np.stack([(1 - ts) ** 3, 3 * ts * (1 - ts) ** 2, 3 * ts ** 2 * (1 - ts), ts ** 3], 1) @ cps
+    for _ in range(100):
+        q = rng.uniform([-2, 0.5], [1.5, 2.5])
+        xi, pmq, d, fd = O.rigid_query(b, q)
+        assert d <= np.sqrt(((B - q) ** 2).sum(1).min()) + 1e-12
+        assert abs(pmq @ fd[0]) <= 1e-10 * np.linalg.norm(fd[0]) * d or xi[0] in (0.0, 1.0)
+    g = np.linspace(0.0, 1.0, 3)
+    cp = np.zeros((3, 3, 3))
+    for j in range(3):
+        for i in range(3):
+            cp[j, i] = [1.4 * g[i] - 0.2, 1.4 * g[j] - 0.2, 1.0 + 1.2 * ((g[i] - 0.5) ** 2 + (g[j] - 0.5) ** 2)]
+    b = O.rigid_bezier(3, cp)
+    s = np.linspace(0, 1, 201)
+    Bs = np.stack([(1 - s) ** 2, 2 * s * (1 - s), s ** 2], -1)
+    S = np.einsum("ai,bj,jid->bad", Bs, Bs, cp).reshape(-1, 3)
+    for _ in range(50):
+        q = rng.uniform([0, 0, 0.8], [1, 1, 1.3])
+        xi, pmq, d, fd = O.rigid_query(b, q)
+        assert d <= np.sqrt(((S - q) ** 2).sum(1).min()) + 1e-12
+        assert max(abs(pmq @ fd[0]), abs(pmq @ fd[1])) <= 1e-10 or 0.0 in xi or 1.0 in xi
