@@ -335,6 +335,155 @@ def gpu_arm(args):
     return 0
 
 
+# ----------------------------------------------------------------------------------------------------
+# --workload c5: J2 elastoplasticity (history variables per qp) + rigid contact on the top face, one GPU.
+# A "step" = what one Newton iteration of an implicit time step assembles: domain residual + FD tangent, then the
+# contact residual + FD tangent on the same resident r / CSR values; DomainPostTimeAdvance is timed separately
+# (once per converged step in the reference). Secondary workload: the headline bench line stays C3.
+# ----------------------------------------------------------------------------------------------------
+def c5_arm(args):
+    import torch
+    from mimi_b200 import capi, meshgen
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: libmimi_b200 has no CPU fallback")
+    torch.cuda.set_device(0)
+    n, p = args.n, 2
+    spans = (n, n, n)
+    stream = torch.cuda.Stream()
+    ctx = capi.Context(0, stream=stream.cuda_stream)
+    t0 = time.time()
+    M = meshgen.patch_connectivity(p, spans)
+    nq1 = p + 2
+    ctx.set_connectivity(3, M["nd"], nq1 ** 3, M["NV"], M["v_dofs"])
+    ctx.set_nodes(M["x_ref"], None)
+    ctx.generate_patch_tables(p, M["ncp"], M["knots"], M["el_ijk"])
+    nnz = ctx.build_pattern()
+    young, poisson = 2100.0, 0.3
+    lam = young * poisson / ((1 + poisson) * (1 - 2 * poisson))
+    mu = young / (2.0 * (1.0 + poisson))
+    K = young / (3.0 * (1.0 - (2.0 * poisson)))
+    # J2 + JohnsonCookTemperatureAndRateDependentHardening (tests/test_nonlinear_solid.py:16-33), yield stress scaled so
+    # that the synthetic 1e-3 displacement field yields at about half of the quadrature points
+    hp = [2.0, 4.0, 0.2835, 0.015, 1.0e-5, 20.0, 0.0, 1.3558, 0.0, 0.0]
+    ctx.set_material(capi.MB2_MAT_J2, [lam, mu, K, mu, 4] + hp + [0.05, 0.9, 1.0, 450.0, 20.0, 1500.0])
+    F = meshgen.top_face_tables(M, spans)
+    ctx.contact_set_faces(F["v_dofs"], F["N"], F["dN_dxi"], F["w"])
+    body = np.zeros(16)
+    body[:4] = [0.5, 0.5, 1.9998, 1.0]              # rigid sphere pressed 2e-4 into the face z = 1
+    ctx.contact_set_rigid_body(capi.MB2_RIGID_SPHERE, body, 1.0e4 * young)
+    u = meshgen.synth_u(M["NV"])
+    x = M["x_ref"].reshape(-1, 3)
+    u.reshape(-1, 3)[x[:, 2] == 0.0, :] = 0.0       # clamped bottom
+    setup_s = time.time() - t0
+    NE, nq = M["NE"], nq1 ** 3
+    ctx.set_u(u); ctx.set_r(None); ctx.set_A(None)
+    # commit a first history so that the timed assemblies run on a non-virgin state
+    ctx._ck(ctx.lib.mb2_post_time_advance_device(ctx.h))
+    ctx.set_u(np.ascontiguousarray(1.5 * u))
+    ctx.sync()
+
+    def step():
+        ctx.assemble_residual_and_grad_device(1.0)
+        el, sc, tot = ctx.last_timing_ms()
+        l0 = ctx.last_launch_count()
+        ctx.contact_residual_and_grad_device(1.0)
+        return el, sc, l0 + ctx.last_launch_count()
+
+    for _ in range(args.warmup):
+        step()
+    ctx.sync()
+    sampler = ClockSampler(0)
+    torch.cuda.synchronize()
+    sampler.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 2)]
+    t_el, launches, t_contact = [], 0, []
+    ev[0].record(stream)
+    for k in range(args.steps):
+        ctx.assemble_residual_and_grad_device(1.0)
+        el, sc, tot = ctx.last_timing_ms()
+        t_el.append(el)
+        launches += ctx.last_launch_count()
+        ev[1 + 2 * k].record(stream)
+        ctx.contact_residual_and_grad_device(1.0)
+        launches += ctx.last_launch_count()
+        ev[2 + 2 * k].record(stream)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    dev_ms = float(ev[0].elapsed_time(ev[2 * args.steps]))
+    contact_ms = float(np.mean([ev[1 + 2 * k].elapsed_time(ev[2 + 2 * k]) for k in range(args.steps)]))
+    ctx.check_numeric()
+    # history commit, timed on its own
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    ctx._ck(ctx.lib.mb2_post_time_advance_device(ctx.h))
+    e1.record(stream)
+    torch.cuda.synchronize()
+    pta_ms = float(e0.elapsed_time(e1))
+    gap, area, pr = ctx.contact_nodal()
+    S = None
+    face_qp = F["NF"] * F["nqf"]
+    ms_per_step = dev_ms / args.steps
+    total_qp = float(NE) * nq + face_qp
+    value = total_qp / (ms_per_step * 1e-3)
+    # end to end: host-buffer entries (domain + contact) with pinned buffers
+    e2e = None
+    if not args.no_e2e:
+        u_h = torch.from_numpy(np.ascontiguousarray(1.5 * u)).pin_memory()
+        r_h = torch.zeros(M["NV"], dtype=torch.float64).pin_memory()
+        A_h = torch.zeros(nnz, dtype=torch.float64).pin_memory()
+        up, rp, Ap = (C_void(t) for t in (u_h, r_h, A_h))
+        one = capi.C.c_double(1.0)
+
+        def host_step():
+            ctx._ck(ctx.lib.mb2_add_domain_residual_and_grad(ctx.h, up, one, rp, Ap))
+            ctx._ck(ctx.lib.mb2_add_boundary_residual_and_grad(ctx.h, up, one, rp, Ap))
+
+        host_step()
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        k2 = max(1, min(args.steps, args.e2e_steps))
+        for _ in range(k2):
+            host_step()
+        torch.cuda.synchronize()
+        e2e_s = (time.perf_counter() - t1) / k2
+        e2e = {"value": total_qp / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * (4 * M["NV"] + nnz),
+               "d2h_bytes_per_step": 8 * (2 * M["NV"] + nnz), "ms_per_step": e2e_s * 1e3, "steps": k2,
+               "call": "mb2_add_domain_residual_and_grad + mb2_add_boundary_residual_and_grad with pinned host buffers"}
+    peak_nofma = ctx.measure_fp64_peak(0)
+    el_ms = float(np.mean(t_el))
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": "C5-style (secondary workload, not the headline): 3D unit-cube B-spline patch p=2, %d^3 = %d "
+                                   "elements x %d qp, J2 + JohnsonCookTemperatureAndRateDependent hardening with %d history "
+                                   "doubles per qp, rigid sphere on the %d faces (x %d qp) of z = 1; one step = domain "
+                                   "residual+tangent + contact residual+tangent into the same CSR (nnz=%d)" % (
+                                       n, NE, nq, ctx.state_size(), F["NF"], F["nqf"], nnz),
+                       "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "face_qp": face_qp, "nnz_per_gpu": nnz,
+                       "active_contact_nodes": int((pr != 0).sum()), "marked_nodes": int(pr.size),
+                       "l2": "inputs larger than L2", "parallelism": "1 GPU", "setup_s": setup_s},
+            "roofline": {"bound": "fp64", "kernel": "element_fd_kernel<3,27,64,J2>", "achieved": None, "peak": peak_nofma,
+                         "unit": "TFLOP/s", "frac": None, "traffic": None,
+                         "note": "data-dependent flop count (return mapping: bracketed Newton per yielded qp); kernel time "
+                                 "reported instead", "kernel_ms": el_ms},
+            "extra": {"domain_element_kernel_ms": el_ms, "contact_ms": contact_ms, "post_time_advance_ms": pta_ms,
+                      "contact_share": contact_ms / ms_per_step},
+            "cpu_baseline": None, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
+    if not args.no_cpu:
+        try:
+            cores = host_cores()
+            S = run_reference_sample(args.ref_n, 2, cores, warmup=1, p=2, material="j2_jcthermo")
+            line["cpu_baseline"] = {"value": S["value_mean"], "unit": UNIT, "cores": cores, "kind": "reference",
+                                    "sample": "unmodified reference, domain integrator only (J2 + JC thermo-rate hardening), "
+                                              "p=2 cube %d^3 = %d el, virgin state, %d threads" % (args.ref_n, S["NE"], cores)}
+        except Exception as ex:
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": host_cores(), "kind": "reference",
+                                    "sample": "unavailable: %s" % ex}
+    emit(line)
+    ctx.close()
+    return 0
+
+
 def C_void(t):
     import ctypes
     return ctypes.c_void_p(t.data_ptr())
@@ -362,6 +511,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--p", type=int, default=2, help="degree (2 = C3 headline; 3 = the C4 element type)")
     ap.add_argument("--material", default="neohookean", choices=["neohookean", "stvk"])
+    ap.add_argument("--workload", default="c3", choices=["c3", "c5"], help="c5: J2 + contact secondary workload (1 GPU)")
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     args = ap.parse_args()
     # The contract is ONE JSON line on stdout: libraries that write to fd 1 (NCCL prints its version banner there)
@@ -374,6 +524,8 @@ def main():
         args.warmup = max(args.warmup, 3) if not os.environ.get("MB2_BENCH_ALLOW_SHORT") else args.warmup
     if args.impl == "reference":
         return reference_arm(args)
+    if args.workload == "c5":
+        return c5_arm(args)
     return gpu_arm(args)
 
 

@@ -406,25 +406,30 @@ __global__ void nodal_pressure_kernel(int64_t n_marked, int ndf, const int64_t* 
   press[n] = g / a * penalty;
 }
 
-// Whole-boundary scalars: per-face partial sums added in ascending face id by one thread (deterministic).
-// mode 0: area (slot 0); mode 1: pressure integral + force (slots 1..4, active faces only); mode 2: gap norm (slot 5).
-__global__ void face_scalar_sum_kernel(int64_t NF, int mode, const double* __restrict__ fsum,
-                                       const uint8_t* __restrict__ active, double* __restrict__ scal) {
-  if (blockIdx.x || threadIdx.x) return;
-  if (mode == 0) {
-    double s = 0.0;
-    for (int64_t f = 0; f < NF; f++) s += fsum[f * 8];
-    scal[0] = 0.0 + s;
-  } else if (mode == 1) {
-    double s[4] = {0, 0, 0, 0};
-    for (int64_t f = 0; f < NF; f++)
-      if (active[f])
-        for (int k = 0; k < 4; k++) s[k] += fsum[f * 8 + 1 + k];
-    for (int k = 0; k < 4; k++) scal[1 + k] = s[k];
-  } else {
-    double s = 0.0;
-    for (int64_t f = 0; f < NF; f++) s += fsum[f * 8 + 5];
-    scal[5] = sqrt(s);
+// Whole-boundary scalars: per-face partial sums reduced by ONE 256-thread CTA in a fixed order (thread t adds faces
+// t, t+256, ... in ascending id, then a shared-memory tree): deterministic, run-to-run identical, 1e-12 relative to the
+// reference's single running sum. mode 0: area (slot 0); mode 1: pressure integral + force (slots 1..4, active faces
+// only); mode 2: gap norm (slot 5).
+__global__ void __launch_bounds__(256) face_scalar_sum_kernel(int64_t NF, int mode, const double* __restrict__ fsum,
+                                                              const uint8_t* __restrict__ active,
+                                                              double* __restrict__ scal) {
+  __shared__ double sh[4][256];
+  const int t = threadIdx.x;
+  const int first = (mode == 0) ? 0 : (mode == 1 ? 1 : 5), cnt = (mode == 1) ? 4 : 1;
+  double s[4] = {0, 0, 0, 0};
+  for (int64_t f = t; f < NF; f += 256)
+    if (mode != 1 || active[f])
+      for (int k = 0; k < cnt; k++) s[k] += fsum[f * 8 + first + k];
+  for (int k = 0; k < cnt; k++) sh[k][t] = s[k];
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (t < w)
+      for (int k = 0; k < cnt; k++) sh[k][t] += sh[k][t + w];
+    __syncthreads();
+  }
+  if (t < cnt) {
+    const double v = sh[t][0];
+    scal[first + t] = (mode == 2) ? sqrt(v) : (mode == 0 ? 0.0 + v : v);
   }
 }
 
@@ -544,10 +549,12 @@ __global__ void face_residual_kernel(int64_t NF, int ndf, int nqf, const int32_t
 __global__ void contact_residual_gather_kernel(int dim, int64_t n_marked, int ndf, const int32_t* __restrict__ mnode,
                                                const int64_t* __restrict__ ptr, const int32_t* __restrict__ face,
                                                const uint8_t* __restrict__ loc, const uint8_t* __restrict__ active,
-                                               const double* __restrict__ fR, double* __restrict__ r) {
+                                               const double* __restrict__ fR, double* __restrict__ r,
+                                               const uint8_t* __restrict__ owned) {
   const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (idx >= n_marked * dim) return;
   const int64_t n = idx / dim;
+  if (owned && !owned[mnode[n]]) return;  // partitioned run: the owner rank assembles this node's entries
   const int c = (int)(idx % dim);
   const int64_t v = (int64_t)dim * mnode[n] + c;
   double acc = r[v];
@@ -563,12 +570,14 @@ __global__ void contact_csr_gather_kernel(int64_t n_marked, int ndf, const int32
                                           const int64_t* __restrict__ ptr, const int32_t* __restrict__ face,
                                           const uint8_t* __restrict__ loc, const uint8_t* __restrict__ active,
                                           const uint16_t* __restrict__ frank, const int64_t* __restrict__ I,
-                                          const double* __restrict__ fK, double grad_factor, double* __restrict__ A) {
+                                          const double* __restrict__ fK, double grad_factor, double* __restrict__ A,
+                                          const uint8_t* __restrict__ owned) {
   const int tdf = DIM * ndf;
   const int t = threadIdx.x;
   const int j = t / DIM, ci = t % DIM;
   const int b = j % ndf, cj = j / ndf;
   for (int64_t n = blockIdx.x; n < n_marked; n += gridDim.x) {
+    if (owned && !owned[mnode[n]]) continue;  // uniform per CTA
     const int64_t row = (int64_t)DIM * mnode[n] + ci;
     for (int64_t p = ptr[n]; p < ptr[n + 1]; p++) {
       const int64_t f = face[p];
@@ -585,13 +594,18 @@ __global__ void contact_csr_gather_kernel(int64_t n_marked, int ndf, const int32
 // rank of face node b in the neighbour list of face node a (the block pattern built by mb2_build_pattern)
 __global__ void face_rank_kernel(int dim, int64_t NF, int ndf, const int32_t* __restrict__ fvdofs,
                                  const int32_t* __restrict__ nnbr, const int64_t* __restrict__ nodeptr,
-                                 const int32_t* __restrict__ nbr, uint16_t* __restrict__ frank, int* __restrict__ flag) {
+                                 const int32_t* __restrict__ nbr, uint16_t* __restrict__ frank, int* __restrict__ flag,
+                                 const uint8_t* __restrict__ owned) {
   const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (t >= NF * ndf * ndf) return;
   const int b = (int)(t % ndf), a = (int)((t / ndf) % ndf);
   const int64_t f = t / ((int64_t)ndf * ndf);
   const int tdf = dim * ndf;
   const int32_t A = fvdofs[f * tdf + a] / dim, B = fvdofs[f * tdf + b] / dim;
+  if (owned && !owned[A]) {  // rows of another rank: never gathered here
+    frank[t] = 0;
+    return;
+  }
   const int32_t* list = nbr + nodeptr[A];
   int lo = 0, hi = nnbr[A] - 1, pos = -1;
   while (lo <= hi) {
@@ -710,7 +724,7 @@ int contact_set_faces(mb2_ctx* c, int64_t NF, int ndf, int nqf, const int32_t* v
   MB2_CUDA(cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
   const int64_t nr = NF * ndf * ndf;
   face_rank_kernel<<<(unsigned)((nr + 255) / 256), 256, 0, c->stream>>>(dim, NF, ndf, S->d_fvdofs, c->d_nnbr, c->d_nodeptr,
-                                                                       c->d_nbr, S->d_frank, c->d_flag);
+                                                                       c->d_nbr, S->d_frank, c->d_flag, c->d_owned);
   MB2_CUDA(cudaGetLastError());
   int flag = 0;
   MB2_CUDA(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -721,7 +735,13 @@ int contact_set_faces(mb2_ctx* c, int64_t NF, int ndf, int nqf, const int32_t* v
     c->err = "a contact face couples two nodes that share no domain element (pattern mismatch)";
     return MB2_ERR_ARG;
   }
+  std::vector<uint8_t> owned;
+  if (c->d_owned) {
+    owned.resize((size_t)c->Nn);
+    MB2_CUDA(cudaMemcpy(owned.data(), c->d_owned, (size_t)c->Nn, cudaMemcpyDeviceToHost));
+  }
   for (int32_t n : S->marked_nodes) {
+    if (!owned.empty() && !owned[(size_t)n]) continue;
     const int64_t off = I[(size_t)dim * n], end = I[(size_t)dim * n + dim];
     if (!S->runs.empty() && S->runs.back().first + S->runs.back().second == off) S->runs.back().second += end - off;
     else S->runs.push_back({off, end - off});
@@ -742,7 +762,7 @@ static int run_pressure(mb2_ctx* c, ContactState* S) {
       S->n_marked, S->ndf, S->d_mn_ptr, S->d_mn_face, S->d_mn_loc, S->d_la, S->d_lg, S->penalty, S->d_gap, S->d_area,
       S->d_press);
   MB2_CUDA(cudaGetLastError());
-  face_scalar_sum_kernel<<<1, 32, 0, c->stream>>>(S->NF, 0, S->d_fsum, S->d_active, S->d_scal);
+  face_scalar_sum_kernel<<<1, 256, 0, c->stream>>>(S->NF, 0, S->d_fsum, S->d_active, S->d_scal);
   MB2_CUDA(cudaGetLastError());
   c->last_launches += 3;
   return MB2_OK;
@@ -760,18 +780,18 @@ static int run_faces(mb2_ctx* c, ContactState* S, double gf) {
   MB2_CUDA(cudaGetLastError());
   const int64_t nv = S->n_marked * DIM;
   contact_residual_gather_kernel<<<(unsigned)((nv + 127) / 128), 128, 0, c->stream>>>(
-      DIM, S->n_marked, S->ndf, S->d_mnode, S->d_mn_ptr, S->d_mn_face, S->d_mn_loc, S->d_active, S->d_fR, c->d_r);
+      DIM, S->n_marked, S->ndf, S->d_mnode, S->d_mn_ptr, S->d_mn_face, S->d_mn_loc, S->d_active, S->d_fR, c->d_r, c->d_owned);
   MB2_CUDA(cudaGetLastError());
   if (GRAD) {
     const int threads = (S->tdf * DIM + 31) / 32 * 32;
     const unsigned g2 = (unsigned)std::min<int64_t>(S->n_marked, (int64_t)c->sm_count * 16);
     contact_csr_gather_kernel<DIM><<<g2, threads, 0, c->stream>>>(S->n_marked, S->ndf, S->d_mnode, S->d_mn_ptr, S->d_mn_face,
                                                                  S->d_mn_loc, S->d_active, S->d_frank, c->d_I, S->d_fK, gf,
-                                                                 c->d_A);
+                                                                 c->d_A, c->d_owned);
     MB2_CUDA(cudaGetLastError());
     c->last_launches += 1;
   }
-  face_scalar_sum_kernel<<<1, 32, 0, c->stream>>>(S->NF, 1, S->d_fsum, S->d_active, S->d_scal);
+  face_scalar_sum_kernel<<<1, 256, 0, c->stream>>>(S->NF, 1, S->d_fsum, S->d_active, S->d_scal);
   MB2_CUDA(cudaGetLastError());
   c->last_launches += 3;
   return MB2_OK;
@@ -820,7 +840,7 @@ int contact_gap_norm(mb2_ctx* c, double* out) {
                                                                       S->d_fw, c->d_xref, c->d_u, S->body, S->d_la, S->d_lg,
                                                                       S->d_fsum);
   MB2_CUDA(cudaGetLastError());
-  face_scalar_sum_kernel<<<1, 32, 0, c->stream>>>(S->NF, 2, S->d_fsum, S->d_active, S->d_scal);
+  face_scalar_sum_kernel<<<1, 256, 0, c->stream>>>(S->NF, 2, S->d_fsum, S->d_active, S->d_scal);
   MB2_CUDA(cudaGetLastError());
   MB2_CUDA(cudaMemcpyAsync(out, S->d_scal + 5, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   MB2_CUDA(cudaStreamSynchronize(c->stream));

@@ -222,3 +222,74 @@ def synth_u(NV: int, seed: int = 12345) -> np.ndarray:
     x = x ^ (x >> np.uint64(31))
     U = (x >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
     return 1.0e-3 * (U - 0.5)
+
+
+def bspline_basis_1d(p: int, knots: np.ndarray, span: int, xi: np.ndarray):
+    """Values and reference-coordinate derivatives of the p+1 B-spline basis functions that are non-zero on knot span
+    `span` (between knots[p+span] and knots[p+span+1]) at local coordinates xi in [0,1] (Cox-de Boor).
+    Returns N [len(xi), p+1], dN/dxi [len(xi), p+1]."""
+    i = p + span
+    t0, t1 = knots[i], knots[i + 1]
+    t = t0 + (t1 - t0) * xi
+
+    def basis(deg):
+        N = np.zeros((len(xi), deg + 1))
+        N[:, 0] = 1.0
+        left, right = np.zeros((deg + 1, len(xi))), np.zeros((deg + 1, len(xi)))
+        for j in range(1, deg + 1):
+            left[j] = t - knots[i + 1 - j]
+            right[j] = knots[i + j] - t
+            saved = np.zeros(len(xi))
+            for r in range(j):
+                tmp = N[:, r] / (right[r + 1] + left[j - r])
+                N[:, r] = saved + right[r + 1] * tmp
+                saved = left[j - r] * tmp
+            N[:, j] = saved
+        return N
+
+    N = basis(p)
+    Nm = basis(p - 1) if p > 0 else np.zeros((len(xi), 1))
+    dN = np.zeros_like(N)
+    for a in range(p + 1):          # function index i - p + a
+        idx = i - p + a
+        if a > 0:
+            dN[:, a] += p * Nm[:, a - 1] / (knots[idx + p] - knots[idx])
+        if a < p:
+            dN[:, a] -= p * Nm[:, a] / (knots[idx + p + 1] - knots[idx + 1])
+    return N, dN * (t1 - t0)
+
+
+def top_face_tables(M, spans, quad_points=None):
+    """Boundary-face data of the z = max face of a patch_connectivity() box, in the layout mb2_contact_set_faces takes:
+    v_dofs [NF, 3*(p+1)^2] (component-major byVDIM; face nodes ii fastest, then jj), N [NF, nq, (p+1)^2],
+    dN_dxi [NF, nq, 2, (p+1)^2], w [NF, nq]. Face parameters (xi0, xi1) = (x, y): the face normal x_xi0 x x_xi1 = +z
+    points out of the body, as MFEM orients this boundary element; node order, values and derivatives agree with the
+    reference's tables for this face to rounding (tests/test_meshgen.py). Synthetic workloads (bench.py); parity tests
+    use the reference's own face tables."""
+    p = M["p"]
+    n0, n1, n2 = spans
+    nq1 = quad_points or (p + 2)                      # order 2p+3 Gauss-Legendre
+    gx, gw = np.polynomial.legendre.leggauss(nq1)
+    gx, gw = 0.5 * (gx + 1.0), 0.5 * gw
+    el = M["el_ijk"]
+    top = np.nonzero(el[:, 2] == n2 - 1)[0]
+    nd1 = p + 1
+    vd = M["v_dofs"][top]
+    nd = nd1 ** 3
+    loc = np.array([ii + nd1 * (jj + nd1 * p) for jj in range(nd1) for ii in range(nd1)])
+    nodes = vd[:, loc] // 3
+    fv = np.concatenate([3 * nodes + c for c in range(3)], 1).astype(np.int32)
+    NF, ndf, nq = len(top), nd1 * nd1, nq1 * nq1
+    N = np.empty((NF, nq, ndf))
+    dN = np.empty((NF, nq, 2, ndf))
+    bx = [bspline_basis_1d(p, M["knots"][0], s, gx) for s in range(n0)]
+    by = [bspline_basis_1d(p, M["knots"][1], s, gx) for s in range(n1)]
+    for f, e in enumerate(top):
+        Nx, dNx = bx[el[e, 0]]
+        Ny, dNy = by[el[e, 1]]
+        # q = qx + nq1*qy ; a = ii + nd1*jj
+        N[f] = np.einsum("xi,yj->yxji", Nx, Ny).reshape(nq, ndf)
+        dN[f, :, 0] = np.einsum("xi,yj->yxji", dNx, Ny).reshape(nq, ndf)
+        dN[f, :, 1] = np.einsum("xi,yj->yxji", Nx, dNy).reshape(nq, ndf)
+    w = np.tile(np.outer(gw, gw).reshape(1, nq), (NF, 1))
+    return dict(v_dofs=fv, N=N, dN_dxi=dN, w=w, NF=NF, ndf=ndf, nqf=nq)

@@ -160,3 +160,41 @@ def test_contact_bezier_body_vs_oracle(ctx_factory, name):
     assert np.array_equal(r, r_o) and np.array_equal(A, A_o)
     assert close(ctx.contact_gap_norm(D["u"]),
                  O.contact_gap_norm(dim, D["c_v_dofs"], D["c_N"], D["c_w"], D["c_x_ref"], D["u"], body))
+
+
+@pytest.mark.parametrize("name,world", [("contact_cube_p2_n4_sphere", 2), ("contact_cube_p2_n4_sphere", 3),
+                                        ("contact_quad_p3_n4_sphere", 2)])
+def test_contact_on_emulated_ranks(ctx_factory, name, world):
+    """Partitioned run: every rank evaluates ALL marked faces (faces << elements, so pass 1 is
+    replicated instead of all-reduced: no collective, identical nodal pressures everywhere) and gathers the face
+    contributions only into the CSR rows / residual entries of the nodes it owns. The union of the owned rows must equal
+    the reference's assembly bit for bit."""
+    from mimi_b200 import partition as P
+    D = load_contact_golden(name)
+    dim = D["dim"]
+    ranges = P.element_ranges(D["v_dofs"].shape[0], world)
+    gI = D["I"].astype(np.int64)
+    r_glob, A_glob = np.full(D["NV"], np.nan), np.full(D["nnz"], np.nan)
+    touched = 0
+    for rk in range(world):
+        R = P.rank_problem(D["v_dofs"], dim, D["NV"], ranges, rk)
+        ctx = ctx_factory()
+        ctx.set_connectivity(dim, D["nd"], D["nq"], D["NV"], R["v_dofs"])
+        ctx.mg_setup(R, manual=True)
+        ctx.set_nodes(D["x_ref"])
+        ctx.build_pattern()
+        ctx.contact_set_faces(D["c_v_dofs"], D["c_N"], D["c_dN_dxi"], D["c_w"])
+        ctx.contact_set_rigid_body(KIND[D["body"][0]], O.rigid_params(dim, D["body"]), D["penalty"])
+        rows = np.repeat(R["owned"], dim)
+        idx = np.concatenate([np.arange(gI[v], gI[v + 1]) for v in np.nonzero(rows)[0]])
+        ctx.set_u(D["u"]); ctx.set_r(D["c_r0"]); ctx.set_A(np.ascontiguousarray(D["mass"][idx]))
+        ctx.contact_residual_and_grad_device(D["gf"])
+        assert np.array_equal(ctx.contact_nodal()[2], D["c_pressure"])       # replicated pass 1
+        r_loc, A_loc = ctx.get_r(), ctx.get_A()
+        r_glob[rows] = r_loc[rows]
+        A_glob[idx] = A_loc
+        touched += int((A_loc != D["mass"][idx]).any())
+    # AddBoundaryResidualAndGrad started from r = 0 in the fixture (c_r2); here from the domain residual c_r0
+    assert np.array_equal(r_glob, D["c_r0"] + (D["c_r"] - D["c_r0"])) or np.array_equal(r_glob, D["c_r"])
+    assert np.array_equal(A_glob, D["c_A"])
+    assert touched >= 1

@@ -34,3 +34,18 @@ def test_numbering_matches_live_reference(p, spans):
 def test_node_grid_is_a_permutation():
     g = meshgen.patch_node_grid((7, 5, 9))
     assert sorted(g.ravel().tolist()) == list(range(7 * 5 * 9))
+
+
+def test_top_face_tables_match_the_reference_tables():
+    """meshgen.top_face_tables (synthetic contact workloads of bench.py) against the boundary tables the unmodified
+    reference precomputed for the same 4^3 p=2 cube (tests/golden/contact_cube_p2_n4_sphere.npz): same faces in the same
+    order, same node order, values to rounding."""
+    import numpy as np
+    from mimi_b200 import meshgen
+    from tests.cases import load_contact_golden
+    D = load_contact_golden("contact_cube_p2_n4_sphere")
+    M = meshgen.patch_connectivity(2, (4, 4, 4))
+    T = meshgen.top_face_tables(M, (4, 4, 4))
+    assert np.array_equal(M["v_dofs"], D["v_dofs"]) and np.array_equal(T["v_dofs"], D["c_v_dofs"])
+    assert np.abs(T["N"] - D["c_N"]).max() < 1e-14 and np.abs(T["dN_dxi"] - D["c_dN_dxi"]).max() < 1e-14
+    assert np.abs(T["w"] - D["c_w"]).max() < 1e-15
