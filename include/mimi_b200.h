@@ -220,6 +220,21 @@ int mb2_contact_last_scalars(mb2_ctx* ctx, double* out5);
 /* sqrt(sum of g_n^2 over penetrating quadrature points). Replaces MortarContact::GapNorm (mortar_contact.cpp:423-467). */
 int mb2_contact_gap_norm(mb2_ctx* ctx, const double* u, double* out);
 
+/* ---- Newton-iteration sweeps on the resident CSR ------------------------------------
+ * What mimi::operators::NonlinearSolid::ResidualAndGrad (src/mimi/operators/nonlinear_solid.cpp:240-283) does around
+ * the integrators, with forms::Nonlinear::AddMultGrad's essential-dof handling (src/mimi/forms/nonlinear.hpp:111-115),
+ * so that an implicit step keeps y and J on the device:
+ *   u := x + fac0 a;  y := M a (+ S (v + fac1 a));  J := M;  domain integrators (y += R(u), J += fac0 K(u));
+ *   y[ess] := 0, J.EliminateRowCol(ess) (row/column zeroed, diagonal 1);  contact integrators if a rigid body is set,
+ *   then the same elimination again;  J += fac1 S;  y -= rhs;  y[ess] := 0.
+ * Results stay resident (mb2_get_r / mb2_get_A / mb2_device_pointers) and are bit-identical to the reference's. */
+int mb2_set_mass(mb2_ctx* ctx, const double* M_values);          /* nnz values on mb2_build_pattern's pattern */
+int mb2_set_viscosity(mb2_ctx* ctx, const double* S_values);     /* nnz values, NULL = none */
+int mb2_set_rhs(mb2_ctx* ctx, const double* rhs);                /* NV, NULL = none (linear forms: body force, traction) */
+int mb2_set_essential_dofs(mb2_ctx* ctx, const int32_t* tdofs, int64_t n);
+int mb2_newton_residual_and_grad_device(mb2_ctx* ctx, const double* x, const double* v, const double* a, double fac0,
+                                        double fac1);
+
 /* ---- multi-GPU: element partition with raw element-matrix exchange ------------------
  * One context per GPU / rank. The rank's connectivity (mb2_set_connectivity) lists its own elements first
  * (global ascending order) and then its GHOST elements: elements computed by higher ranks that touch a node this

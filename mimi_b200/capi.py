@@ -29,7 +29,8 @@ SYMBOLS = [
     "mb2_post_time_advance_device", "mb2_set_time_step", "mb2_check_numeric", "mb2_contact_set_faces", "mb2_contact_set_rigid_body", "mb2_contact_n_marked_nodes",
     "mb2_contact_get_marked_v_dofs", "mb2_contact_get_A_ids_i32", "mb2_add_boundary_residual",
     "mb2_add_boundary_residual_and_grad", "mb2_contact_residual_device", "mb2_contact_residual_and_grad_device",
-    "mb2_contact_get_nodal", "mb2_contact_last_scalars", "mb2_contact_gap_norm",
+    "mb2_contact_get_nodal", "mb2_contact_last_scalars", "mb2_contact_gap_norm", "mb2_set_mass", "mb2_set_viscosity",
+    "mb2_set_rhs", "mb2_set_essential_dofs", "mb2_newton_residual_and_grad_device",
 ]
 
 
@@ -223,6 +224,24 @@ class Context:
         out = C.c_double()
         self._ck(self.lib.mb2_contact_gap_norm(self.h, _dp(u), C.byref(out)))
         return out.value
+
+    # ---- Newton-iteration sweeps on the resident CSR
+    def set_mass(self, M):
+        self._ck(self.lib.mb2_set_mass(self.h, _dp(np.ascontiguousarray(M, np.float64))))
+
+    def set_viscosity(self, S=None):
+        self._ck(self.lib.mb2_set_viscosity(self.h, _dp(None if S is None else np.ascontiguousarray(S, np.float64))))
+
+    def set_rhs(self, rhs=None):
+        self._ck(self.lib.mb2_set_rhs(self.h, _dp(None if rhs is None else np.ascontiguousarray(rhs, np.float64))))
+
+    def set_essential_dofs(self, tdofs):
+        t = np.ascontiguousarray(tdofs, np.int32)
+        self._ck(self.lib.mb2_set_essential_dofs(self.h, _dp(t), C.c_int64(t.size)))
+
+    def newton_residual_and_grad_device(self, x, v, a, fac0, fac1):
+        self._ck(self.lib.mb2_newton_residual_and_grad_device(self.h, _dp(x), _dp(v), _dp(a), C.c_double(fac0),
+                                                              C.c_double(fac1)))
 
     # ---- host-buffer hot path
     def add_domain_residual(self, u, r):

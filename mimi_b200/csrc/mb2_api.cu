@@ -30,6 +30,7 @@ static void free_problem(mb2_ctx* c) {
   mb2::free_plan(c);
   mb2::free_mg(c);
   mb2::free_contact(c);
+  mb2::free_newton(c);
   dfree(c->d_owned);
   c->have_pattern = false;
   c->nnz = 0;

@@ -824,6 +824,8 @@ int contact_assemble(mb2_ctx* c, bool grad, double gf) {
   return MB2_OK;
 }
 
+bool contact_active(mb2_ctx* c) { return CS(c) && CS(c)->body.kind >= 0 && c->d_xref; }
+
 int contact_gap_norm(mb2_ctx* c, double* out) {
   int rc = contact_ready(c);
   if (rc) return rc;

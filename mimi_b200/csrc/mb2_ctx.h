@@ -57,6 +57,7 @@ struct mb2_ctx {
   uint8_t* d_owned = nullptr;  // Nn, nullptr = every node
   MgState* mg = nullptr;       // exchange state (mb2_multigpu.cu)
   void* contact = nullptr;     // mortar contact state (mb2_contact.cu)
+  void* newton = nullptr;      // Newton-iteration sweeps: mass / viscosity / rhs / essential dofs (mb2_newton.cu)
 
   // connectivity
   int32_t* d_vdofs = nullptr;   // NE x tdof (reference layout)
@@ -112,6 +113,8 @@ int assemble_finish(mb2_ctx* c, double gf, bool grad, double* A_out);
 double* ghost_ke_buffer(mb2_ctx* c);  // [NE - n_compute][nd][KP]
 // mb2_contact.cu
 void free_contact(mb2_ctx* c);
+// mb2_newton.cu
+void free_newton(mb2_ctx* c);
 // mb2_multigpu.cu
 void free_mg(mb2_ctx* c);
 int mg_pack_chunk(mb2_ctx* c, int64_t e0, int64_t e1, const double* d_KeT_chunk, bool grad, cudaStream_t st);

@@ -80,6 +80,19 @@ def j2_main():
             print(name, sorted(out)[:4])
 
 
+def sweeps_main():
+    """Newton-iteration sweeps (harness mode 'sweeps') on the meshes of two base fixtures."""
+    for name, base, fac0, fac1 in (("sweeps_cube_p2_n2", "cube_p2_n2", 0.25, 0.5), ("sweeps_quad_p2_n4", "quad_p2_n4", 0.0625, 0.25)):
+        writer, elevate, refine, gf = CASES[base]
+        with tempfile.TemporaryDirectory() as tmp:
+            mesh = os.path.join(tmp, "m.mesh")
+            writer(mesh)
+            W = O.run_ref_sweeps(mesh, elevate, refine, "neohookean", os.path.join(tmp, "s"), fac0, fac1)
+            W["base"] = np.array(base)
+            np.savez_compressed(os.path.join(OUT, name + ".npz"), **W)
+            print(name, W["y"].size, W["Jac"].size, W["ess"].size)
+
+
 def main(only=None):
     assert O.have_ref(), "build oracle/_ref first: make -f oracle/Makefile.ref -j8"
     os.makedirs(OUT, exist_ok=True)
@@ -115,9 +128,12 @@ if __name__ == "__main__":
         contact_main()
     elif "j2" in sys.argv[1:]:
         j2_main()
+    elif "sweeps" in sys.argv[1:]:
+        sweeps_main()
     elif len(sys.argv) > 1:
         main(sys.argv[1:])
     else:
         main()
         contact_main()
         j2_main()
+        sweeps_main()

@@ -407,3 +407,56 @@ def run_ref_contact(mesh, elevate, refine, outdir, bdr_attr, penalty, body, gf=1
            str(bdr_attr), repr(float(penalty)), body[0]] + [repr(float(x)) for x in body[1]]
     subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
     return load_contact_dump(outdir)
+
+
+# ---------------------------------------------------------------- Newton-iteration sweeps
+def spmv(I, J, A, x, y=None):
+    out = np.zeros(len(I) - 1) if y is None else y
+    lib().orc_spmv(C.c_int64(len(I) - 1), _p(I, C.c_int32), _p(J, C.c_int32), _p(A, C.c_double), _p(x, C.c_double),
+                   _p(out, C.c_double), C.c_int(0 if y is None else 1))
+    return out
+
+
+def eliminate(ess, I, J, A, y):
+    ess = np.ascontiguousarray(ess, np.int32)
+    rc = lib().orc_eliminate(C.c_int64(ess.size), _p(ess, C.c_int32), _p(I, C.c_int32), _p(J, C.c_int32), _p(A, C.c_double),
+                             _p(y, C.c_double))
+    assert rc == 0
+
+
+def newton_residual_and_grad(dim, nd, nq, m, D, W, contact=None):
+    """NonlinearSolid::ResidualAndGrad (operators/nonlinear_solid.cpp:240-283) restated on the oracle's pieces.
+    D: domain fixture (tables, A_ids, ...), W: dict(I, J, mass, visc|None, x, v, a, rhs|None, ess, fac0, fac1)."""
+    fac0, fac1 = W["fac0"], W["fac1"]
+    tx = W["x"] + fac0 * W["a"]
+    y = spmv(W["I"], W["J"], W["mass"], W["a"])
+    if W.get("visc") is not None:
+        tv = W["v"] + fac1 * W["a"]
+        spmv(W["I"], W["J"], W["visc"], np.ascontiguousarray(tv), y)
+    r, Jm = assemble_residual_and_grad(dim, nd, nq, m, D["v_dofs"], D["A_ids"], D["dN_dX"], D["w"], D["detJ"],
+                                       np.ascontiguousarray(tx), fac0, W["mass"])
+    y = y + r            # the integrators add their (zero-started, ordered) thread-local sum onto y
+    eliminate(W["ess"], W["I"], W["J"], Jm, y)
+    if contact is not None:
+        contact(np.ascontiguousarray(tx), fac0, y, Jm)
+        eliminate(W["ess"], W["I"], W["J"], Jm, y)
+    if W.get("visc") is not None:
+        Jm += fac1 * W["visc"]
+    if W.get("rhs") is not None:
+        y += -1.0 * W["rhs"]
+    y[W["ess"]] = 0.0
+    return y, Jm, tx
+
+
+def run_ref_sweeps(mesh, elevate, refine, material, outdir, fac0, fac1, nthreads=1):
+    os.makedirs(outdir, exist_ok=True)
+    cmd = [REF_BIN, "sweeps", mesh, str(elevate), str(refine), material, str(nthreads), repr(fac0), repr(fac1), outdir]
+    subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+    meta = json.load(open(os.path.join(outdir, "meta.json")))
+    out = dict(fac0=fac0, fac1=fac1)
+    for k in ("I", "J", "ess"):
+        out[k] = np.fromfile(os.path.join(outdir, k + ".i32"), np.int32)
+    for k in ("mass", "visc", "x", "v", "a", "rhs", "y", "Jac", "tx"):
+        out[k] = np.fromfile(os.path.join(outdir, k + ".f64"), np.float64)
+    assert out["y"].size == meta["NV"]
+    return out

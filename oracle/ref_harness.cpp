@@ -472,6 +472,59 @@ int main(int argc, char** argv) {
       << ", \"nq\": " << pre.GetElementQuadData("domain")[0].n_quad << "}\n";
     return 0;
   }
+  if (mode == "sweeps") {
+    // The O(nnz) sweeps around the integrators in one Newton iteration (operators/nonlinear_solid.cpp:240-283,
+    // forms/nonlinear.hpp:53-116): y = M a; J = M; J += fac0 K(x + fac0 a) (+ r); r[ess] = 0; EliminateRowCol(ess);
+    // J += fac1 S; y -= rhs.   mimi_ref sweeps <mesh> <elevate> <refine> <material> <nthreads> <fac0> <fac1> <outdir>
+    const double fac0 = std::atof(argv[7]), fac1 = std::atof(argv[8]);
+    const std::string out = argv[9];
+    Setup s = build(mesh_file, elevate, refine, material, nthreads, true);
+    auto& pre = *s.pre;
+    const int NV = pre.n_v_dofs_, dim = pre.dim_;
+    mfem::SparseMatrix& M = s.mass->SpMat();
+    const int nnz = M.NumNonZeroElems();
+    dump(out, "I.i32", M.GetI(), (size_t)NV + 1);
+    dump(out, "J.i32", M.GetJ(), (size_t)nnz);
+    dump(out, "mass.f64", M.GetData(), (size_t)nnz);
+    // a second matrix on the same pattern standing in for the viscosity form: S = 0.37 M (+ index-dependent wobble)
+    mfem::SparseMatrix S(M);
+    for (int i = 0; i < nnz; ++i) S.GetData()[i] = M.GetData()[i] * (0.37 + 1.0e-3 * (i % 7));
+    dump(out, "visc.f64", S.GetData(), (size_t)nnz);
+    mfem::Vector x(NV), v(NV), a(NV), rhs(NV), tx(NV), tv(NV), y(NV);
+    for (int i = 0; i < NV; ++i) {
+      x[i] = synth_u(12345, (uint64_t)i);
+      v[i] = 10.0 * synth_u(777, (uint64_t)i);
+      a[i] = 100.0 * synth_u(4242, (uint64_t)i);
+      rhs[i] = synth_u(99, (uint64_t)i);
+    }
+    dump(out, "x.f64", x.GetData(), (size_t)NV); dump(out, "v.f64", v.GetData(), (size_t)NV);
+    dump(out, "a.f64", a.GetData(), (size_t)NV); dump(out, "rhs.f64", rhs.GetData(), (size_t)NV);
+    // essential dofs: every vdof of the nodes on x = 0 (clamped face)
+    mfem::GridFunction& nodes = *s.mesh->GetNodes();
+    std::vector<int> ess;
+    for (int n = 0; n < NV / dim; ++n)
+      if (nodes[dim * n] == 0.0)
+        for (int c = 0; c < dim; ++c) ess.push_back(dim * n + c);
+    dump(out, "ess.i32", ess.data(), ess.size());
+    // NonlinearSolid::ResidualAndGrad (operators/nonlinear_solid.cpp:240-283)
+    add(x, fac0, a, tx);
+    M.Mult(a, y);
+    add(v, fac1, a, tv);
+    S.AddMult(tv, y);
+    mfem::SparseMatrix Jm(M);
+    s.integ->AddDomainResidualAndGrad(tx, fac0, y, Jm);
+    for (const int t : ess) { y[t] = 0.0; Jm.EliminateRowCol(t); }   // forms/nonlinear.hpp:111-115
+    Jm.Add(fac1, S);
+    y.Add(-1.0, rhs);
+    for (const int t : ess) y[t] = 0.0;
+    dump(out, "y.f64", y.GetData(), (size_t)NV);
+    dump(out, "Jac.f64", Jm.GetData(), (size_t)nnz);
+    dump(out, "tx.f64", tx.GetData(), (size_t)NV);
+    std::ofstream m(out + "/meta.json");
+    m << "{\"NV\": " << NV << ", \"nnz\": " << nnz << ", \"n_ess\": " << ess.size() << ", \"fac0\": " << fac0
+      << ", \"fac1\": " << fac1 << "}\n";
+    return 0;
+  }
   if (mode == "time") {
     const int reps = std::atoi(argv[7]);
     const int warm = argc > 8 ? std::atoi(argv[8]) : 0;

@@ -59,6 +59,16 @@ def j2_params(law):
                                                       T["T0"], T["melting"]]
 
 
+SWEEP_CASES = ["sweeps_cube_p2_n2", "sweeps_quad_p2_n4"]
+
+
+def load_sweeps_golden(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    W = {k: z[k] for k in z.files if k != "base"}
+    W["fac0"], W["fac1"] = float(W["fac0"]), float(W["fac1"])
+    return load_golden(str(z["base"])), W
+
+
 def ref_case(kind, p, n, material, gf=1.0):
     """Live reference run (nthreads=1). kind: 'refine' (p1 cube + DegreeElevate(p-1) + log2(n) refinements)
     or 'patch' (direct p, n spans)."""

@@ -1,0 +1,60 @@
+"""GPU: the Newton-iteration sweeps on the resident CSR through the C ABI
+against dumps of the unmodified reference running the sequence of operators/nonlinear_solid.cpp:240-283 (harness mode
+'sweeps'), and -- with contact in the loop -- against the oracle. Bit-exact y and J."""
+import numpy as np
+import pytest
+
+from mimi_b200 import capi
+from oracle import oracle_py as O
+from tests.cases import SWEEP_CASES, load_contact_golden, load_golden, load_sweeps_golden, setup_ctx
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", SWEEP_CASES)
+def test_newton_sweeps_golden(ctx_factory, name):
+    D, W = load_sweeps_golden(name)
+    ctx = setup_ctx(ctx_factory(), D, "neohookean")
+    ctx.set_mass(W["mass"]); ctx.set_viscosity(W["visc"]); ctx.set_rhs(W["rhs"]); ctx.set_essential_dofs(W["ess"])
+    for _ in range(2):      # the second call starts from the first one's y / J: nothing may leak
+        ctx.newton_residual_and_grad_device(W["x"], W["v"], W["a"], W["fac0"], W["fac1"])
+        assert np.array_equal(ctx.get_r(), W["y"]) and np.array_equal(ctx.get_A(), W["Jac"])
+    # without viscosity / rhs the eliminated rows are unit rows and the eliminated columns are zero
+    ctx.set_viscosity(None); ctx.set_rhs(None)
+    ctx.newton_residual_and_grad_device(W["x"], None, W["a"], W["fac0"], 0.0)
+    y, Jm = ctx.get_r(), ctx.get_A()
+    Wn = dict(W, visc=None, rhs=None)
+    y_o, J_o, _ = O.newton_residual_and_grad(D["dim"], D["nd"], D["nq"], O.mat(0), D, Wn)
+    assert np.array_equal(y, y_o) and np.array_equal(Jm, J_o)
+    I, J = W["I"], W["J"]
+    for rc in W["ess"]:
+        assert np.array_equal(Jm[I[rc]:I[rc + 1]], (J[I[rc]:I[rc + 1]] == rc).astype(float)) and y[rc] == 0.0
+    assert not Jm[np.isin(J, W["ess"]) & ~np.isin(np.repeat(np.arange(len(I) - 1), np.diff(I)), W["ess"])].any()
+
+
+def test_newton_sweeps_with_contact_vs_oracle(ctx_factory):
+    """Domain + contact + both eliminations on the resident arrays (the order of ResidualAndGrad)."""
+    Cg = load_contact_golden("contact_cube_p2_n2_plane")
+    D = load_golden("cube_p2_n2")
+    _, W = load_sweeps_golden("sweeps_cube_p2_n2")
+    W = dict(W, visc=None)
+    ctx = setup_ctx(ctx_factory(), D, "neohookean")
+    ctx.set_nodes(Cg["x_ref"])
+    ctx.contact_set_faces(Cg["c_v_dofs"], Cg["c_N"], Cg["c_dN_dxi"], Cg["c_w"])
+    ctx.contact_set_rigid_body(capi.MB2_RIGID_PLANE, O.rigid_params(3, Cg["body"]), Cg["penalty"])
+    ctx.set_mass(W["mass"]); ctx.set_rhs(W["rhs"]); ctx.set_essential_dofs(W["ess"])
+    ctx.newton_residual_and_grad_device(W["x"], None, W["a"], W["fac0"], W["fac1"])
+    local, nm, _ = O.contact_prepare(3, Cg["c_v_dofs"])
+    body = O.rigid_from_spec(3, Cg["body"])
+    seen = {}
+
+    def contact(tx, gf, y, Jm):
+        gap, area, pr, tot = O.contact_pressure(3, Cg["c_v_dofs"], local, nm, Cg["c_N"], Cg["c_dN_dxi"], Cg["c_w"],
+                                                Cg["c_x_ref"], tx, body, Cg["penalty"])
+        seen["active"] = int((pr != 0).sum())
+        O.contact_assemble(3, Cg["c_v_dofs"], local, Cg["c_A_ids"], Cg["c_N"], Cg["c_dN_dxi"], Cg["c_w"], Cg["c_x_ref"], tx,
+                           pr, True, gf, y, Jm)
+
+    y_o, J_o, _ = O.newton_residual_and_grad(3, 27, 64, O.mat(0), D, W, contact=contact)
+    assert seen["active"] > 0
+    assert np.array_equal(ctx.get_r(), y_o) and np.array_equal(ctx.get_A(), J_o)
