@@ -59,6 +59,7 @@ J2_CASES = {"j2_cube_p2_n2": "cube_p2_n2", "j2_quad_p2_n4": "quad_p2_n4"}
 
 
 SIMO_LAWS = ("voce", "jcthermo")
+LOG_LAWS = ("voce", "jcthermo")
 
 
 def j2_main():
@@ -76,8 +77,51 @@ def j2_main():
                 D = O.run_ref_dump(mesh, elevate, refine, "j2simo_" + law, os.path.join(tmp, "simo" + law), gf=gf)
                 for k_out, k_in in (("r", "r"), ("r2", "r2"), ("A", "A"), ("state", "state"), ("rb", "r_b"), ("Ab", "A_b")):
                     out[k_out + "_simo_" + law] = D[k_in]
+            for law in LOG_LAWS:  # J2Log (finite strain, logarithmic) on the same two laws
+                D = O.run_ref_dump(mesh, elevate, refine, "j2log_" + law, os.path.join(tmp, "log" + law), gf=gf)
+                for k_out, k_in in (("r", "r"), ("r2", "r2"), ("A", "A"), ("state", "state"), ("rb", "r_b"), ("Ab", "A_b")):
+                    out[k_out + "_log_" + law] = D[k_in]
             np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
             print(name, sorted(out)[:4])
+
+
+def eig_matrices(dim):
+    """Symmetric test matrices for CalcEigenvalues: generic, near-identity (like C_e = F_e^T F_e), tiny deviatoric
+    (like the plastic increment), and the degenerate inputs that take the solver's special branches."""
+    rng = np.random.default_rng(20 + dim)
+    mats = []
+    for _ in range(150):
+        B = rng.standard_normal((dim, dim))
+        mats.append(B + B.T)
+    for s in (1e-2, 1e-5, 1e-9):
+        for _ in range(40):
+            B = s * rng.standard_normal((dim, dim))
+            mats.append(np.eye(dim) + B + B.T)
+    for _ in range(40):
+        B = 1e-4 * rng.standard_normal((dim, dim))
+        B = B + B.T
+        mats.append(B - np.trace(B) / dim * np.eye(dim))
+    for _ in range(30):      # repeated eigenvalue, rotated
+        Q, _r = np.linalg.qr(rng.standard_normal((dim, dim)))
+        mats.append(Q @ np.diag([1.0, 1.0, 3.0][:dim]) @ Q.T)
+    for _ in range(30):      # coordinate-plane coupling only
+        A = np.diag(rng.standard_normal(dim))
+        A[0, dim - 1] = A[dim - 1, 0] = rng.standard_normal()
+        mats.append(A)
+    mats += [np.eye(dim) * 2.5, np.zeros((dim, dim)), np.diag([1.0, 1.0, 3.0][:dim]), np.diag([3.0, 1.0, 2.0][:dim]),
+             1e300 * np.eye(dim), 1e-300 * (np.ones((dim, dim)) + np.eye(dim)), np.ones((dim, dim))]
+    return np.array(mats)
+
+
+def eig_main():
+    out = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        for dim in (2, 3):
+            mats = eig_matrices(dim)
+            lam, vec = O.run_ref_eig(mats, os.path.join(tmp, str(dim)))
+            out["A%d" % dim], out["lambda%d" % dim], out["vec%d" % dim] = mats, lam, vec
+    np.savez_compressed(os.path.join(OUT, "eig_sym.npz"), **out)
+    print("eig_sym", out["A2"].shape, out["A3"].shape)
 
 
 def sweeps_main():
@@ -130,6 +174,8 @@ if __name__ == "__main__":
         j2_main()
     elif "sweeps" in sys.argv[1:]:
         sweeps_main()
+    elif "eig" in sys.argv[1:]:
+        eig_main()
     elif len(sys.argv) > 1:
         main(sys.argv[1:])
     else:
@@ -137,3 +183,4 @@ if __name__ == "__main__":
         contact_main()
         j2_main()
         sweeps_main()
+        eig_main()

@@ -87,12 +87,35 @@ def j2simo_initial_state(NE, nq, dim):
     return S
 
 
-def mat_j2(state, law, young=2100.0, poisson=0.3, simo=False):
+J2LOG = 5
+J2LOG_NS = 11
+
+
+def j2log_initial_state(NE, nq, dim):
+    """J2Log::CreateState (materials.cpp:221-240): Fp_inv = I, zero eqps, initial temperature."""
+    S = np.zeros((NE, nq, J2LOG_NS))
+    for k in range(dim):
+        S[:, :, k * (dim + 1)] = 1.0
+    S[:, :, 10] = J2_THERMO["T0"]
+    return S
+
+
+def eig_sym(A):
+    """mfem::DenseMatrix::CalcEigenvalues on a column-major dim x dim symmetric matrix -> (lambda, vectors[k] = k-th)."""
+    A = np.ascontiguousarray(A, dtype=np.float64)
+    dim = A.shape[0]
+    lam = np.zeros(dim)
+    vec = np.zeros(dim * dim)
+    lib().orc_eig_sym(C.c_int(dim), _p(np.ascontiguousarray(A.T).ravel(), C.c_double), _p(lam, C.c_double), _p(vec, C.c_double))
+    return lam, vec.reshape(dim, dim)
+
+
+def mat_j2(state, law, young=2100.0, poisson=0.3, simo=False, log=False):
     lam, mu = lame(young, poisson)
     K = young / (3.0 * (1.0 - (2.0 * poisson)))
     err = C.c_int(0)
-    m = Material(J2SIMO if simo else J2, lam, mu, K, mu, 0, 0, 0, 0, np.sqrt(3.0 / 2.0), 0, state.ctypes.data,
-                 J2SIMO_NS if simo else J2_NS, HARD[law],
+    m = Material(J2LOG if log else (J2SIMO if simo else J2), lam, mu, K, mu, 0, 0, 0, 0, np.sqrt(3.0 / 2.0), 0,
+                 state.ctypes.data, J2LOG_NS if log else (J2SIMO_NS if simo else J2_NS), HARD[law],
                  (C.c_double * 10)(*hardening_params(law)), J2_THERMO["dt"], J2_THERMO["heat_fraction"],
                  J2_THERMO["density"], J2_THERMO["specific_heat"], C.pointer(err))
     m._keep = (state, err)
@@ -113,7 +136,7 @@ def lame(young=2100.0, poisson=0.3):
 
 
 def build_oracle(force=False):
-    srcs = [os.path.join(HERE, "mimi_oracle.c"), os.path.join(HERE, "mimi_oracle_contact.c")]
+    srcs = [os.path.join(HERE, x) for x in ("mimi_oracle.c", "mimi_oracle_contact.c", "mimi_oracle_eig.c")]
     if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(x) for x in srcs):
         subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", LIB] + srcs + ["-lm"])
     return LIB
@@ -460,3 +483,15 @@ def run_ref_sweeps(mesh, elevate, refine, material, outdir, fac0, fac1, nthreads
         out[k] = np.fromfile(os.path.join(outdir, k + ".f64"), np.float64)
     assert out["y"].size == meta["NV"]
     return out
+
+
+def run_ref_eig(mats, outdir):
+    """mfem::DenseMatrix::CalcEigenvalues of the unmodified reference (harness mode 'eig') on mats [n][dim][dim]."""
+    os.makedirs(outdir, exist_ok=True)
+    n, dim, _ = mats.shape
+    f = os.path.join(outdir, "in.f64")
+    np.ascontiguousarray(np.transpose(mats, (0, 2, 1))).tofile(f)   # column-major
+    subprocess.check_call([REF_BIN, "eig", f, str(dim), str(n), "-", "0", outdir, "-"], stdout=subprocess.DEVNULL)
+    lam = np.fromfile(os.path.join(outdir, "lambda.f64")).reshape(n, dim)
+    vec = np.fromfile(os.path.join(outdir, "vec.f64")).reshape(n, dim, dim)
+    return lam, vec

@@ -87,13 +87,19 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
     m->sigma_y_ = sy ? std::atof(sy) : 2.0;
     s.mat = m;
   }
-  else if (material.rfind("j2_", 0) == 0 || material.rfind("j2simo_", 0) == 0) {
+  else if (material.rfind("j2_", 0) == 0 || material.rfind("j2simo_", 0) == 0 || material.rfind("j2log_", 0) == 0) {
     // J2 with nonlinear isotropic hardening (materials.hpp:259-404); thermo values of tests/test_nonlinear_solid.py:16-33,
     // yield stresses scaled down so that the synthetic 1e-3 displacement field yields at part of the points
     namespace mm = mimi::materials;
     const bool simo = material.rfind("j2simo_", 0) == 0;
+    const bool logm = material.rfind("j2log_", 0) == 0;
     std::shared_ptr<mm::HardeningBase>* hard_slot = nullptr;
-    if (simo) {
+    if (logm) {
+      auto m = std::make_shared<mm::J2Log>();
+      m->melting_temperature_ = 1500; m->initial_temperature_ = 20; m->specific_heat_ = 450; m->heat_fraction_ = 0.9;
+      hard_slot = &m->hardening_;
+      s.mat = m;
+    } else if (simo) {
       auto m = std::make_shared<mm::J2Simo>();
       m->melting_temperature_ = 1500; m->initial_temperature_ = 20; m->specific_heat_ = 450; m->heat_fraction_ = 0.9;
       hard_slot = &m->hardening_;
@@ -106,7 +112,7 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
     }
     struct { std::shared_ptr<mm::HardeningBase>& hardening_; } mref{*hard_slot};
     auto* m = &mref;
-    const std::string h = material.substr(simo ? 7 : 3);
+    const std::string h = material.substr(simo ? 7 : (logm ? 6 : 3));
     auto jc_fill = [](auto& jc) { jc.A_ = 2.0; jc.B_ = 4.0; jc.n_ = 0.2835; };
     auto jcr_fill = [&](auto& jc) { jc_fill(jc); jc.C_ = 0.015; jc.effective_plastic_strain_rate_ = 1.0e-5; };
     if (h == "powerlaw") { auto hd = std::make_shared<mm::PowerLawHardening>(); hd->sigma_y_ = 2.0; hd->n_ = 3.0; hd->eps0_ = 0.01; m->hardening_ = hd; }
@@ -257,6 +263,25 @@ int main(int argc, char** argv) {
   const std::string material = argv[5];
   const int nthreads = std::atoi(argv[6]);
   std::cout.setstate(std::ios_base::failbit);  // silence the reference's PrintInfo chatter
+
+  if (mode == "eig") {
+    // eig <matrices.f64> <dim> <count> - - <out dir> -: mfem::DenseMatrix::CalcEigenvalues on column-major dim x dim
+    // symmetric matrices (the log / exp maps of J2Log go through it) -> lambda.f64 [count][dim], vec.f64 [count][dim*dim]
+    const int dim = elevate, count = refine;
+    const std::string out = argv[7];
+    std::vector<double> in((size_t)count * dim * dim), lam((size_t)count * dim), vec((size_t)count * dim * dim);
+    FILE* f = std::fopen(mesh_file, "rb");
+    if (!f || std::fread(in.data(), sizeof(double), in.size(), f) != in.size()) { std::fprintf(stderr, "eig: bad input\n"); return 2; }
+    std::fclose(f);
+    for (int i = 0; i < count; ++i) {
+      mfem::DenseMatrix A(dim, dim);
+      std::memcpy(A.GetData(), &in[(size_t)i * dim * dim], sizeof(double) * dim * dim);
+      A.CalcEigenvalues(&lam[(size_t)i * dim], &vec[(size_t)i * dim * dim]);
+    }
+    dump(out, "lambda.f64", lam.data(), lam.size());
+    dump(out, "vec.f64", vec.data(), vec.size());
+    return 0;
+  }
 
   if (mode == "dump") {
     const double gf = std::atof(argv[7]);

@@ -37,6 +37,7 @@ def load_contact_golden(name):
 J2_CASES = ["j2_cube_p2_n2", "j2_quad_p2_n4"]
 J2_LAWS = ["powerlaw", "voce", "jc", "jcrate", "jcthermo", "jcconst"]
 SIMO_LAWS = ["voce", "jcthermo"]
+LOG_LAWS = ["voce", "jcthermo"]
 
 
 def load_j2_golden(name):

@@ -1,4 +1,5 @@
 """CPU: the plain-C oracle against the golden vectors dumped from the unmodified reference (bit-exact)."""
+import os
 import numpy as np
 import pytest
 
@@ -86,7 +87,7 @@ def test_j2_hardening_laws_bit_exact(name, law):
     assert m._keep[1].value == 0
 
 
-from tests.cases import SIMO_LAWS  # noqa: E402
+from tests.cases import SIMO_LAWS, LOG_LAWS  # noqa: E402
 
 
 @pytest.mark.parametrize("law", SIMO_LAWS)
@@ -105,3 +106,58 @@ def test_j2simo_bit_exact(name, law):
     assert np.array_equal(S, D["state" + k])
     rb, Ab = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], 1.5 * D["u"], D["gf"], D["mass"])
     assert np.array_equal(rb, D["rb" + k]) and np.array_equal(Ab, D["Ab" + k])
+
+
+@pytest.mark.parametrize("law", LOG_LAWS)
+@pytest.mark.parametrize("name", J2_CASES)
+def test_j2log_bit_exact(name, law):
+    """J2Log (finite strain, logarithmic, materials.hpp:580-756): Fp_inv history; the log / exp maps go through the
+    restated mfem CalcEigenvalues (oracle/mimi_oracle_eig.c), which these fixtures pin to the bit."""
+    D = load_j2_golden(name)
+    S = O.j2log_initial_state(D["NE"], D["nq"], D["dim"])
+    m = O.mat_j2(S, law, log=True)
+    args = (D["dim"], D["nd"], D["nq"], m, D["v_dofs"])
+    k = "_log_" + law
+    assert np.array_equal(O.assemble_residual(*args, D["dN_dX"], D["w"], D["detJ"], D["u"]), D["r" + k])
+    r2, A = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], D["u"], D["gf"], D["mass"])
+    assert np.array_equal(r2, D["r2" + k]) and np.array_equal(A, D["A" + k])
+    O.post_time_advance(D["dim"], D["nd"], D["nq"], m, D["v_dofs"], D["dN_dX"], D["u"])
+    assert np.array_equal(S, D["state" + k])
+    assert np.any(S[:, :, 9] > 0) and not np.all(S[:, :, 9] > 0)   # both the elastic and the plastic branch ran
+    rb, Ab = O.assemble_residual_and_grad(*args, D["A_ids"], D["dN_dX"], D["w"], D["detJ"], 1.5 * D["u"], D["gf"], D["mass"])
+    assert np.array_equal(rb, D["rb" + k]) and np.array_equal(Ab, D["Ab" + k])
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_eig_sym_properties(dim):
+    """The restated symmetric eigen-solver: ascending eigenvalues, orthonormal vectors, A V = V Lambda, vs numpy eigh;
+    degenerate inputs (multiple of I, zero, a repeated eigenvalue) take the reference's special branches."""
+    rng = np.random.default_rng(5)
+    mats = []
+    for _ in range(200):
+        B = rng.standard_normal((dim, dim))
+        mats.append(B + B.T)
+    for _ in range(50):      # near the identity, as C_e = F_e^T F_e is
+        B = 1e-3 * rng.standard_normal((dim, dim))
+        mats.append(np.eye(dim) + B + B.T)
+    mats += [np.eye(dim) * 2.5, np.zeros((dim, dim)), np.diag([1.0, 1.0, 3.0][:dim]), 1e300 * np.eye(dim), np.diag([3.0, 1.0, 2.0][:dim])]
+    for A in mats:
+        lam, V = O.eig_sym(A)
+        assert np.all(np.diff(lam) >= 0)
+        scale = max(np.abs(A).max(), 1e-300)
+        assert np.allclose(lam / scale, np.linalg.eigvalsh(A / scale), rtol=0, atol=1e-14)
+        assert np.allclose(V @ V.T, np.eye(dim), atol=1e-14)
+        assert np.allclose((A / scale) @ V.T, V.T * (lam / scale), atol=2e-14)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_eig_sym_bit_exact_vs_reference(dim):
+    """oracle/mimi_oracle_eig.c against mfem::DenseMatrix::CalcEigenvalues of the unmodified reference (fixture
+    eig_sym.npz from harness mode 'eig'): generic, near-identity, tiny deviatoric, repeated-eigenvalue and degenerate
+    matrices -- every pivoting branch -- to the bit."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "eig_sym.npz"))
+    A, lam_ref, vec_ref = z["A%d" % dim], z["lambda%d" % dim], z["vec%d" % dim]
+    for i in range(A.shape[0]):
+        lam, V = O.eig_sym(A[i])
+        assert np.array_equal(lam, lam_ref[i]), i
+        assert np.array_equal(V, vec_ref[i]), i
