@@ -44,8 +44,10 @@ enum {
                              hardening kind (MB2_HARD_*), hp[10], dt, heat_fraction, density, specific_heat,
                              initial_temperature, melting_temperature}; 11 history doubles per quadrature point:
                              plastic_strain[9], accumulated_plastic_strain, temperature */
-  MB2_MAT_J2SIMO = 4      /* J2Simo (finite strain), materials.hpp:406-579; params as MB2_MAT_J2; 20 history doubles:
+  MB2_MAT_J2SIMO = 4,     /* J2Simo (finite strain), materials.hpp:406-579; params as MB2_MAT_J2; 20 history doubles:
                              be_old[9], F_old[9], accumulated_plastic_strain, temperature */
+  MB2_MAT_J2LOG = 5       /* J2Log (finite strain, logarithmic), materials.hpp:580-756; params as MB2_MAT_J2; 11 history
+                             doubles: Fp_inv[9], accumulated_plastic_strain, temperature */
 };
 /* hardening laws, src/mimi/materials/material_hardening.hpp. hp[10] per law (unused entries 0):
  *   POWERLAW {sigma_y, n, eps0}; VOCE {sigma_y, sigma_sat, strain_constant};

@@ -172,13 +172,18 @@ static int alloc_state(mb2_ctx* c) {
     }
     k_fill_strided<<<gb, 256, 0, c->stream>>>(n, c->ns, 19, c->mp.T0, c->d_state);
     MB2_CUDA(cudaGetLastError());
+  } else if (c->mat_kind == MB2_MAT_J2LOG) {  // J2Log::CreateState (materials.cpp:221-240): Fp_inv = I
+    for (int k = 0; k < c->dim; k++)
+      k_fill_strided<<<gb, 256, 0, c->stream>>>(n, c->ns, k * (c->dim + 1), 1.0, c->d_state);
+    k_fill_strided<<<gb, 256, 0, c->stream>>>(n, c->ns, 10, c->mp.T0, c->d_state);
+    MB2_CUDA(cudaGetLastError());
   }
   return MB2_OK;
 }
 
 int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
   CHECK_CTX(c);
-  REQUIRE(kind >= MB2_MAT_NEOHOOKEAN && kind <= MB2_MAT_J2SIMO, "unknown material kind");
+  REQUIRE(kind >= MB2_MAT_NEOHOOKEAN && kind <= MB2_MAT_J2LOG, "unknown material kind");
   REQUIRE(params && nparams >= 2, "material needs {lambda, mu}");
   mb2::MatP m;
   m.lambda = params[0];
@@ -192,7 +197,7 @@ int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
     m.sqrt_3_2 = std::sqrt(3.0 / 2.0);
     m.sqrt_2_3 = std::sqrt(2.0 / 3.0);
   }
-  if (kind == MB2_MAT_J2 || kind == MB2_MAT_J2SIMO) {
+  if (kind == MB2_MAT_J2 || kind == MB2_MAT_J2SIMO || kind == MB2_MAT_J2LOG) {
     REQUIRE(nparams >= 21, "J2 needs {lambda, mu, K, G, hardening kind, hp[10], dt, heat_fraction, density, specific_heat, "
                            "initial_temperature, melting_temperature}");
     REQUIRE(c->NE > 0, "call mb2_set_connectivity before setting a material with history variables");

@@ -680,6 +680,7 @@ __global__ void __launch_bounds__(128) post_time_advance_kernel(int nd, int nq, 
     for (int i = 0; i < NS; i++) st[i] = g[i];
     if (MAT == MAT_J2LINEAR) j2linear_plastic_stress<DIM, true>(mp, F, st, nullptr);
     else if (MAT == MAT_J2) j2_plastic_stress<DIM, true>(mp, F, st, nullptr);
+    else if (MAT == MAT_J2LOG) j2log_plastic_stress<DIM, true>(mp, F, nullptr, 0.0, st, nullptr);
     else {
       double Finv[DD];
       inverse_small<DIM>(F, Finv);
@@ -706,6 +707,9 @@ int launch_post_time_advance(mb2_ctx* c) {
   } else if (c->mat_kind == MAT_J2SIMO) {
     if (c->dim == 3) MB2_PTA(3, MAT_J2SIMO);
     else MB2_PTA(2, MAT_J2SIMO);
+  } else if (c->mat_kind == MAT_J2LOG) {
+    if (c->dim == 3) MB2_PTA(3, MAT_J2LOG);
+    else MB2_PTA(2, MAT_J2LOG);
   }
 #undef MB2_PTA
   MB2_CUDA(cudaGetLastError());
@@ -850,6 +854,7 @@ static int launch_element_mat(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
     case MAT_J2LINEAR: return launch_element<DIM, ND, NQ, MAT_J2LINEAR, GRAD, MINB>(c, a, st);
     case MAT_J2: return launch_element<DIM, ND, NQ, MAT_J2, GRAD, MINB>(c, a, st);
     case MAT_J2SIMO: return launch_element<DIM, ND, NQ, MAT_J2SIMO, GRAD, MINB>(c, a, st);
+    case MAT_J2LOG: return launch_element<DIM, ND, NQ, MAT_J2LOG, GRAD, MINB>(c, a, st);
   }
   c->err = "material not set or unsupported";
   return MB2_ERR_UNSUPPORTED;
@@ -865,6 +870,7 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
       case MAT_J2LINEAR: return launch_element_fd<3, 27, 64, MAT_J2LINEAR>(c, a, st);
       case MAT_J2: return launch_element_fd<3, 27, 64, MAT_J2>(c, a, st);
       case MAT_J2SIMO: return launch_element_fd<3, 27, 64, MAT_J2SIMO>(c, a, st);
+      case MAT_J2LOG: return launch_element_fd<3, 27, 64, MAT_J2LOG>(c, a, st);
     }
   }
   if (GRAD && dim == 3 && nd == 64 && nq == 125 && c->elem_variant != 1) {
@@ -874,6 +880,7 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
       case MAT_J2LINEAR: return launch_element_fd_split<3, 64, 125, MAT_J2LINEAR, 4>(c, a, st);
       case MAT_J2: return launch_element_fd_split<3, 64, 125, MAT_J2, 4>(c, a, st);
       case MAT_J2SIMO: return launch_element_fd_split<3, 64, 125, MAT_J2SIMO, 4>(c, a, st);
+      case MAT_J2LOG: return launch_element_fd_split<3, 64, 125, MAT_J2LOG, 4>(c, a, st);
     }
   }
   if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a, st);

@@ -4,9 +4,11 @@
 #pragma once
 #include <cstdint>
 
+#include "mb2_eig.cuh"
+
 namespace mb2 {
 
-enum : int { MAT_NEOHOOKEAN = 0, MAT_STVK = 1, MAT_J2LINEAR = 2, MAT_J2 = 3, MAT_J2SIMO = 4 };
+enum : int { MAT_NEOHOOKEAN = 0, MAT_STVK = 1, MAT_J2LINEAR = 2, MAT_J2 = 3, MAT_J2SIMO = 4, MAT_J2LOG = 5 };
 // hardening laws (src/mimi/materials/material_hardening.hpp); hp[] layout:
 //  POWERLAW {sigma_y, n, eps0}   VOCE {sigma_y, sigma_sat, strain_constant}
 //  JC* {A, B, n, C, eps0_dot, T_ref, T_melt, m, temperature_contribution_ (constant-temperature law)}
@@ -27,8 +29,9 @@ struct MatP {
 // per-quadrature-point history doubles: J2Linear = plastic_strain[9], beta[9], accumulated_plastic_strain
 //                                   J2 = plastic_strain[9], accumulated_plastic_strain, temperature
 //                                   J2Simo = be_old[9], F_old[9], accumulated_plastic_strain, temperature
+//                                   J2Log = Fp_inv[9], accumulated_plastic_strain, temperature
 __host__ __device__ constexpr int mat_state_size(int mat) {
-  return mat == MAT_J2LINEAR ? 19 : (mat == MAT_J2 ? 11 : (mat == MAT_J2SIMO ? 20 : 0));
+  return mat == MAT_J2LINEAR ? 19 : ((mat == MAT_J2 || mat == MAT_J2LOG) ? 11 : (mat == MAT_J2SIMO ? 20 : 0));
 }
 
 // mfem::kernels::MultABt on DIM x DIM operands (third_party/mfem/linalg/kernels.hpp:363-384):
@@ -474,6 +477,73 @@ __device__ __noinline__ void j2simo_plastic_stress(const MatP& m, const double* 
   }
 }
 
+// J2Log::PlasticStress<ACC> (materials.hpp:636-739) on st = {Fp_inv[9], eqps, temperature}. J2Log has no EvaluatePK1
+// of its own: what reaches the residual is MaterialBase::EvaluatePK1 (materials.cpp:60-71) on alternative_stress_ =
+// M = s + p / det F * I (materials.hpp:727), P = det F * M * F^-T; the F_e^-T M F_e^T F^-T product written to
+// tmp.stress_ (materials.hpp:728-734) is overwritten by that call and the exponential map only feeds it when
+// ACC == false, so neither is executed here. log / exp / hypot / acos / cos: libdevice.
+template <int DIM, bool ACC>
+__device__ __noinline__ void j2log_plastic_stress(const MatP& m, const double* F, const double* Finv, double det_F,
+                                                  double* st, double* P) {
+  constexpr int DD = DIM * DIM;
+  double w0[DD], w1[DD], V[DD], lam[DIM];
+  double* Fp_inv = st;
+  mult_AB<DIM>(F, Fp_inv, w0);   // F_e
+  mult_AtB<DIM>(w0, w0, w1);     // C_e (LogarithmicStrain, material_utils.hpp:92-114)
+  eig_sym<DIM>(w1, lam, V);
+#pragma unroll
+  for (int i = 0; i < DIM; i++) lam[i] = log(lam[i]);
+  mult_ADAt<DIM>(V, lam, w0);    // E_e
+#pragma unroll
+  for (int i = 0; i < DD; i++) w0[i] *= 0.5;
+  double tr = 0.0;
+#pragma unroll
+  for (int i = 0; i < DIM; i++) tr += w0[i + i * DIM];
+  const double p = m.K * tr;
+  double* s = w1;
+  dev_mat<DIM>(w0, 2.0 * m.G, s);
+  double a = 0.0;
+#pragma unroll
+  for (int i = 0; i < DD; i++) a += s[i] * s[i];
+  const double q = m.sqrt_3_2 * sqrt(a);
+  const RC rc = {q, st[9], hardening_thermo(m, st[10]), false, 0.0};
+  const double tolerance = m.hp[0] * 1.e-10;
+  if (j2_residual_d(m, rc, 0.0) > tolerance) {
+    const AD1 e0 = {rc.eqps_old, 0.0};
+    const double upper = (q - hardening_evaluate(m, e0).v * rc.thermo) / (3.0 * m.G);
+    const double de = j2_scalar_solve(m, rc, 0.0, upper, 1.e-10, tolerance, 100);
+    const double al = 1.5 / q;
+    double* Np = w0;
+#pragma unroll
+    for (int i = 0; i < DD; i++) Np[i] = al * s[i];
+    const double cc = -2.0 * m.G * de;
+#pragma unroll
+    for (int i = 0; i < DD; i++) s[i] += cc * Np[i];
+    if (ACC) {
+#pragma unroll
+      for (int i = 0; i < DD; i++) Np[i] = -de * Np[i];   // increment
+      eig_sym<DIM>(Np, lam, V);
+#pragma unroll
+      for (int i = 0; i < DIM; i++) lam[i] = exp(lam[i]);
+      double ex[DD], old[DD];
+      mult_ADAt<DIM>(V, lam, ex);
+      st[9] += de;
+#pragma unroll
+      for (int i = 0; i < DD; i++) old[i] = Fp_inv[i];
+      mult_AB<DIM>(old, ex, Fp_inv);
+    }
+  }
+  if (!ACC) {
+    const double al = p / det_F;
+    double* M = w0;
+#pragma unroll
+    for (int i = 0; i < DD; i++) M[i] = s[i] + al * ((i % (DIM + 1) == 0) ? 1.0 : 0.0);
+    mult_ABt<DIM>(M, Finv, P);
+#pragma unroll
+    for (int i = 0; i < DD; i++) P[i] *= det_F;
+  }
+}
+
 // First Piola-Kirchhoff stress P(F). MAT is a compile-time material id; st = this quadrature point's history
 // (read-only here; nullptr for stateless materials).
 //  NeoHookean: CompressibleOgdenNeoHookean::EvaluateCauchy (src/mimi/materials/materials.cpp:96-118)
@@ -507,6 +577,16 @@ __device__ __forceinline__ void material_pk1(const MatP& m, const double* F, con
   }
   double B[DD], sig[DD], Finv[DD];
   const double det_F = det_small<DIM>(F);
+  if (MAT == MAT_J2LOG) {
+    double stl[11];
+#pragma unroll
+    for (int i = 0; i < DD; i++) stl[i] = st[i];
+    stl[9] = st[9];
+    stl[10] = st[10];
+    inverse_small<DIM>(F, Finv);
+    j2log_plastic_stress<DIM, false>(m, F, Finv, det_F, stl, P);
+    return;
+  }
   if (MAT == MAT_J2SIMO) {
     double stl[20];
 #pragma unroll
