@@ -3,6 +3,7 @@
 Run from the repo root where /root/reference exists:  python oracle/make_golden.py
 """
 import os
+import shutil
 import sys
 import tempfile
 
@@ -19,6 +20,8 @@ CASES = {
     "cube_p2_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 1, 1, 1.0),
     "cube_p1_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 0, 1, 0.5),
     "beam2d_p3_n2": (lambda f: meshgen.write_box_p1(f, (5.0, 1.0)), 2, 1, 0.0125),  # tests/test_nonlinear_solid.py mesh
+    # the reference's own test mesh (tests/test_nonlinear_solid.py:6-13: balken.mesh, elevate 2, subdivide 1)
+    "balken_p3_n2": (lambda f: shutil.copy("/root/reference/tests/data/balken.mesh", f), 2, 1, 0.0625),
     "quad_p2_n4": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 1, 2, 1.0),
     "cube_p3_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 2, 1, 0.6),
     "cube_p2_n3_patch": (lambda f: meshgen.write_box_patch(f, 2, (3, 2, 2), (1.5, 1.0, 1.0)), 0, 0, 2.0),
@@ -124,6 +127,17 @@ def eig_main():
     print("eig_sym", out["A2"].shape, out["A3"].shape)
 
 
+def histories_main():
+    """The reference's own golden vectors for this path: tests/data/ref/<case>_h1_p2/x_<i>.txt, the
+    displacement after each of 10 generalized-alpha steps of the 2D p=3 beam (tests/test_nonlinear_solid.py:54-112).
+    Packed unchanged into one fixture; tests/test_reference_histories.py replays them."""
+    out = {}
+    for key, folder in (("neohook", "neohook_h1_p2"), ("j2", "j2_h1_p2"), ("j2_simo", "j2_simo_h1_p2"), ("j2_log", "j2_log_h1_p2")):
+        out[key] = np.array([np.genfromtxt("/root/reference/tests/data/ref/%s/x_%d.txt" % (folder, i)) for i in range(10)])
+    np.savez_compressed(os.path.join(OUT, "balken_histories.npz"), **out)
+    print("balken_histories", {k: v.shape for k, v in out.items()})
+
+
 def sweeps_main():
     """Newton-iteration sweeps (harness mode 'sweeps') on the meshes of two base fixtures."""
     for name, base, fac0, fac1 in (("sweeps_cube_p2_n2", "cube_p2_n2", 0.25, 0.5), ("sweeps_quad_p2_n4", "quad_p2_n4", 0.0625, 0.25)):
@@ -176,6 +190,8 @@ if __name__ == "__main__":
         sweeps_main()
     elif "eig" in sys.argv[1:]:
         eig_main()
+    elif "histories" in sys.argv[1:]:
+        histories_main()
     elif len(sys.argv) > 1:
         main(sys.argv[1:])
     else:
@@ -184,3 +200,4 @@ if __name__ == "__main__":
         j2_main()
         sweeps_main()
         eig_main()
+        histories_main()

@@ -110,13 +110,14 @@ def eig_sym(A):
     return lam, vec.reshape(dim, dim)
 
 
-def mat_j2(state, law, young=2100.0, poisson=0.3, simo=False, log=False):
+def mat_j2(state, law, young=2100.0, poisson=0.3, simo=False, log=False, hp=None):
+    """hp: hardening parameters (oracle hp[] layout) overriding the harness' set for `law`."""
     lam, mu = lame(young, poisson)
     K = young / (3.0 * (1.0 - (2.0 * poisson)))
     err = C.c_int(0)
     m = Material(J2LOG if log else (J2SIMO if simo else J2), lam, mu, K, mu, 0, 0, 0, 0, np.sqrt(3.0 / 2.0), 0,
                  state.ctypes.data, J2LOG_NS if log else (J2SIMO_NS if simo else J2_NS), HARD[law],
-                 (C.c_double * 10)(*hardening_params(law)), J2_THERMO["dt"], J2_THERMO["heat_fraction"],
+                 (C.c_double * 10)(*(hardening_params(law) if hp is None else hp)), J2_THERMO["dt"], J2_THERMO["heat_fraction"],
                  J2_THERMO["density"], J2_THERMO["specific_heat"], C.pointer(err))
     m._keep = (state, err)
     return m

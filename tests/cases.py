@@ -9,7 +9,7 @@ from mimi_b200 import meshgen
 from oracle import oracle_py as O
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "quad_p2_n4", "cube_p2_n3_patch", "cube_p3_n2"]
+GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "balken_p3_n2", "quad_p2_n4", "cube_p2_n3_patch", "cube_p3_n2"]
 MATS = {"neohookean": 0, "stvk": 1, "j2linear": 2}
 
 
@@ -49,12 +49,13 @@ def load_j2_golden(name):
     return D
 
 
-def j2_params(law):
-    """Parameter list of mb2_set_material(MB2_MAT_J2, ...) for the harness' material 'j2_<law>'."""
+def j2_params(law, hp=None):
+    """Parameter list of mb2_set_material(MB2_MAT_J2, ...) for the harness' material 'j2_<law>' (hp: override of the
+    hardening parameters, oracle layout)."""
     lam, mu = O.lame()
     K = 2100.0 / (3.0 * (1.0 - (2.0 * 0.3)))
     T = O.J2_THERMO
-    hp = O.hardening_params(law).copy()
+    hp = (O.hardening_params(law) if hp is None else np.asarray(hp, dtype=np.float64)).copy()
     hp[6] = hp[8] = 0.0   # the library derives T_melt / temperature_contribution_ itself (J2::Setup)
     return [lam, mu, K, mu, O.HARD[law]] + list(hp) + [T["dt"], T["heat_fraction"], T["density"], T["specific_heat"],
                                                       T["T0"], T["melting"]]
