@@ -225,9 +225,14 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
   const int qs1 = t / NM, m1 = t % NM;
   const bool act1 = t < NM * QC;
   const int c1 = (m1 < TD) ? m1 / ND : 0, a1 = (m1 < TD) ? m1 % ND : -1;
-  // phase-2 role: rows i0 .. i0+TI-1, columns col0 .. col0+TC-1 (column = m*DIM + j)
+  // phase-2 role: TI rows (interleaved, below), columns col0 .. col0+TC-1 (column = m*DIM + j)
   const int lane = t & 31, warp = t >> 5;
-  const int i0 = (lane % LI) * TI;
+  // rows of this lane: NP aligned pairs {2 LI p + 2 li, +1} (one 16-byte LDS.128 each -- an LDS.64 costs the same two
+  // shared-memory wavefronts as an LDS.128, ncu profiles/r01_elem_v4_summary.txt) and, TI being odd, one single row
+  const int li = lane % LI;
+  constexpr int NP = TI / 2;
+#define MB2_ROW2(x) (((x) < 2 * NP) ? (2 * LI * ((x) / 2) + 2 * li + (x) % 2) : (2 * LI * NP + li))
+  static_assert(LI * TI >= ND && LI * TI <= NDP, "phase-2 rows must cover the element's nodes inside the padded row");
   const int col0 = (warp * LC + lane / LI) * TC;
   const bool act2 = col0 < NB;
 
@@ -338,9 +343,14 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
                 bv[2 * y] = v.x;
                 bv[2 * y + 1] = v.y;
               }
-              const double* dN = sdN + (q * DIM + k) * NDP + i0;
+              const double* dN = sdN + (q * DIM + k) * NDP;
 #pragma unroll
-              for (int x = 0; x < TI; x++) dv[x] = dN[x];
+              for (int p = 0; p < NP; p++) {
+                const double2 v = *reinterpret_cast<const double2*>(dN + 2 * LI * p + 2 * li);
+                dv[2 * p] = v.x;
+                dv[2 * p + 1] = v.y;
+              }
+              if (TI % 2) dv[TI - 1] = dN[2 * LI * NP + li];
 #pragma unroll
               for (int x = 0; x < TI; x++)
 #pragma unroll
@@ -359,9 +369,9 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
           const int j = col - TD * DIM;
 #pragma unroll
           for (int x = 0; x < TI; x++)
-            if (i0 + x < ND) {
-              sRb[i0 + x + j * ND] = R[x][y];
-              g.Re[e * TD + i0 + x + j * ND] = R[x][y];
+            if (MB2_ROW2(x) < ND) {
+              sRb[MB2_ROW2(x) + j * ND] = R[x][y];
+              g.Re[e * TD + MB2_ROW2(x) + j * ND] = R[x][y];
             }
         }
       }
@@ -383,7 +393,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
       double* out = g.KeT + (e - g.e0) * (int64_t)(ND * KP) + col0;
 #pragma unroll
       for (int x = 0; x < TI; x++) {
-        const int i = i0 + x;
+        const int i = MB2_ROW2(x);
         if (i < ND) {
           double v[TC];
 #pragma unroll
@@ -398,6 +408,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
     }
     __syncthreads();
   }
+#undef MB2_ROW2
 }
 
 // ---------------------------------------------------------------------------------------------
