@@ -1,0 +1,157 @@
+// Reference-side binding of libmimi_b200: a mimi::integrators::NonlinearBase subclass with NonlinearSolid's
+// constructor signature (src/mimi/integrators/nonlinear_solid.hpp:45-50) that forwards the domain virtuals of
+// src/mimi/integrators/nonlinear_base.hpp:14-154 to the C ABI of include/mimi_b200.h. A maintainer drops this file
+// into src/mimi/integrators/ and constructs it in PyNonlinearSolid::Setup (src/mimi/py/py_nonlinear_solid.cpp:202-217)
+// instead of NonlinearSolid; forms::Nonlinear, the operators, Newton, the ODE solvers and the pybind11 module stay
+// as they are.
+//
+// It needs MFEM and the reference's headers, so it is NOT part of the product library. oracle/Makefile.ref compiles
+// it, together with the unmodified reference sources, into oracle/_ref/mimi_ref_b200 (test infrastructure):
+// tests/test_gpu_adapter.py runs that binary on the GPU box and compares what the reference's own call chain
+// produces through this adapter with the golden vectors of the reference's CPU integrator.
+#pragma once
+#include <algorithm>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "mimi/integrators/nonlinear_base.hpp"
+#include "mimi/materials/materials.hpp"
+#include "mimi/utils/precomputed.hpp"
+#include "mimi/utils/print.hpp"
+#include "mimi_b200.h"
+
+namespace mimi::integrators {
+
+class B200NonlinearSolid : public NonlinearBase {
+  mb2_ctx* ctx_{nullptr};
+  std::shared_ptr<mimi::materials::MaterialBase> material_;
+  mutable double* pinned_{nullptr};
+  bool pin_jacobian_{false};
+
+  void Check(int rc) const {  // same error convention as the rest of mimi (utils/print.hpp:49-56)
+    if (rc) mimi::utils::PrintAndThrowError("mimi_b200:", mb2_last_error(ctx_));
+  }
+
+public:
+  B200NonlinearSolid(const std::string& name,
+                     const std::shared_ptr<mimi::materials::MaterialBase>& material,
+                     const std::shared_ptr<mimi::utils::PrecomputedData>& precomputed)
+      : NonlinearBase(name, precomputed),
+        material_(material) {
+    if (mb2_create(&ctx_, /*device*/ 0, /*stream*/ nullptr))
+      mimi::utils::PrintAndThrowError("mimi_b200:", mb2_last_error(nullptr));
+  }
+  ~B200NonlinearSolid() override {
+    if (pinned_) mb2_host_unregister(ctx_, pinned_);
+    mb2_destroy(ctx_);
+  }
+  mb2_ctx* Context() const { return ctx_; }  // shared with the contact adapter
+  /// operators::NonlinearSolid keeps ONE jacobian_ for the whole run (operators/nonlinear_solid.cpp:114-121): page-lock its
+  /// value array once so that the rows stream through the copy engines. Off by default (callers with temporaries).
+  void SetPinJacobian(const bool on) { pin_jacobian_ = on; }
+
+  /// NonlinearSolid::Prepare (nonlinear_solid.cpp:21-46): material setup, then the element tables go to the device.
+  /// This variant uploads the tables PrecomputedData already holds (precomputed.cpp:264-330); for meshes whose tables
+  /// do not fit the host, mb2_set_nodes + mb2_generate_patch_tables rebuild them on the device bit-identically.
+  void Prepare() override {
+    auto& pre = *precomputed_;
+    material_->Setup(pre.dim_);
+    auto& eqd = pre.GetElementQuadData("domain");
+    const int dim = pre.dim_, NE = pre.n_elements_;
+    const int tdof = eqd[0].GetElementData().n_tdof, nd = eqd[0].GetElementData().n_dof, nq = eqd[0].n_quad;
+    std::vector<int> vdofs(size_t(NE) * tdof);
+    std::vector<double> w(size_t(NE) * nq), dj(size_t(NE) * nq), dX(size_t(NE) * nq * nd * dim);
+    for (int e = 0; e < NE; ++e) {
+      std::copy_n(eqd[e].GetElementData().v_dofs.GetData(), tdof, &vdofs[size_t(e) * tdof]);
+      for (int q = 0; q < nq; ++q) {
+        const auto& qd = eqd[e].GetQuadData()[q];  // precomputed.hpp:58-69
+        w[size_t(e) * nq + q] = qd.integration_weight;
+        dj[size_t(e) * nq + q] = qd.det_dX_dxi;
+        std::copy_n(qd.dN_dX.GetData(), nd * dim, &dX[(size_t(e) * nq + q) * nd * dim]);
+      }
+    }
+    Check(mb2_set_connectivity(ctx_, dim, nd, nq, NE, pre.n_v_dofs_, vdofs.data()));
+    Check(mb2_upload_quad_tables(ctx_, dX.data(), w.data(), dj.data()));
+    int64_t nnz = 0;
+    Check(mb2_build_pattern(ctx_, &nnz));  // bit-identical to precomputed_->sparsity_pattern_
+    if (pre.sparsity_pattern_ && nnz != pre.sparsity_pattern_->NumNonZeroElems())
+      mimi::utils::PrintAndThrowError("mimi_b200: pattern size differs from PrepareSparsity()");
+    SetMaterial();
+  }
+
+  /// Dispatch on MaterialBase::Name() (materials.hpp); user subclasses the library does not know throw.
+  void SetMaterial() {
+    namespace mm = mimi::materials;
+    auto& m = *material_;
+    const std::string n = m.Name();
+    if (n == "StVenantKirchhoff" || n.find("NeoHookean") != std::string::npos) {
+      const double par[2] = {m.lambda_, m.mu_};
+      Check(mb2_set_material(ctx_, n == "StVenantKirchhoff" ? MB2_MAT_STVK : MB2_MAT_NEOHOOKEAN, par, 2));
+    } else if (n == "J2Linear") {
+      auto& j = dynamic_cast<mm::J2Linear&>(m);
+      const double par[7] = {m.lambda_, m.mu_, m.K_, m.G_, j.isotropic_hardening_, j.kinematic_hardening_, j.sigma_y_};
+      Check(mb2_set_material(ctx_, MB2_MAT_J2LINEAR, par, 7));
+    } else if (n == "J2" || n == "J2Simo" || n == "J2Log") {  // three classes with the same members
+      auto fill = [&](auto& j, int kind) {
+        double par[21] = {m.lambda_, m.mu_, m.K_, m.G_};
+        auto& hb = *j.hardening_;
+        double* hp = par + 5;
+        if (auto* pl = dynamic_cast<mm::PowerLawHardening*>(&hb)) {
+          par[4] = MB2_HARD_POWERLAW; hp[0] = pl->sigma_y_; hp[1] = pl->n_; hp[2] = pl->eps0_;
+        } else if (auto* vo = dynamic_cast<mm::VoceHardening*>(&hb)) {
+          par[4] = MB2_HARD_VOCE; hp[0] = vo->sigma_y_; hp[1] = vo->sigma_sat_; hp[2] = vo->strain_constant_;
+        } else {  // the JohnsonCook family derives from JohnsonCookHardening
+          auto& l = dynamic_cast<mm::JohnsonCookHardening&>(hb);
+          hp[0] = l.A_; hp[1] = l.B_; hp[2] = l.n_; par[4] = MB2_HARD_JC;
+          if (auto* r = dynamic_cast<mm::JohnsonCookRateDependentHardening*>(&l)) {
+            hp[3] = r->C_; hp[4] = r->effective_plastic_strain_rate_; par[4] = MB2_HARD_JC_RATE;
+          }
+          if (auto* t = dynamic_cast<mm::JohnsonCookTemperatureAndRateDependentHardening*>(&l)) {
+            hp[5] = t->reference_temperature_; hp[7] = t->m_;
+            par[4] = dynamic_cast<mm::JohnsonCookConstantTemperatureHardening*>(&l) ? MB2_HARD_JC_CONST_T
+                                                                                    : MB2_HARD_JC_THERMO_RATE;
+          }
+        }
+        par[15] = dt_; par[16] = j.heat_fraction_; par[17] = m.density_; par[18] = j.specific_heat_;
+        par[19] = j.initial_temperature_; par[20] = j.melting_temperature_;
+        Check(mb2_set_material(ctx_, kind, par, 21));
+      };
+      if (n == "J2") fill(dynamic_cast<mm::J2&>(m), MB2_MAT_J2);
+      else if (n == "J2Simo") fill(dynamic_cast<mm::J2Simo&>(m), MB2_MAT_J2SIMO);
+      else fill(dynamic_cast<mm::J2Log&>(m), MB2_MAT_J2LOG);
+    } else {
+      mimi::utils::PrintAndThrowError("mimi_b200: unsupported material", n);
+    }
+  }
+
+  void AddDomainResidual(const mfem::Vector& u, mfem::Vector& r) const override {
+    Check(mb2_set_time_step(ctx_, dt_));  // nonlinear_solid.cpp:154: material_->dt_ = dt_
+    Check(mb2_add_domain_residual(ctx_, u.GetData(), r.GetData()));
+  }
+
+  void AddDomainResidualAndGrad(const mfem::Vector& u, const double grad_factor, mfem::Vector& r,
+                                mfem::SparseMatrix& A) const override {
+    if (pin_jacobian_ && A.GetData() != pinned_) {
+      if (pinned_) Check(mb2_host_unregister(ctx_, pinned_));
+      Check(mb2_host_register(ctx_, A.GetData(), sizeof(double) * A.NumNonZeroElems()));
+      pinned_ = A.GetData();
+    }
+    Check(mb2_set_time_step(ctx_, dt_));
+    Check(mb2_add_domain_residual_and_grad(ctx_, u.GetData(), grad_factor, r.GetData(), A.GetData()));
+  }
+
+  /// commits the device-resident history (no-op for stateless materials)
+  void DomainPostTimeAdvance(const mfem::Vector& u) override { Check(mb2_post_time_advance(ctx_, u.GetData())); }
+
+  /// history variables [NE][nq][mb2_state_size] (checkpoints, tests); empty for stateless materials
+  std::vector<double> State() const {
+    const int ns = mb2_state_size(ctx_);
+    auto& eqd = precomputed_->GetElementQuadData("domain");
+    std::vector<double> st(size_t(precomputed_->n_elements_) * eqd[0].n_quad * std::max(ns, 0));
+    if (!st.empty()) Check(mb2_get_state(ctx_, st.data()));
+    return st;
+  }
+};
+
+}  // namespace mimi::integrators

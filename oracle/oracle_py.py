@@ -241,9 +241,16 @@ def load_dump(d):
     return out
 
 
-def run_ref_dump(mesh, elevate, refine, material, outdir, gf=1.0, nthreads=1, u_file="-", lite=False):
+REF_B200_BIN = os.path.join(HERE, "_ref", "mimi_ref_b200")   # the harness with adapter/b200_nonlinear_solid.hpp
+
+
+def have_ref_b200():
+    return os.path.exists(REF_B200_BIN) and os.access(REF_B200_BIN, os.X_OK)
+
+
+def run_ref_dump(mesh, elevate, refine, material, outdir, gf=1.0, nthreads=1, u_file="-", lite=False, binary=None):
     os.makedirs(outdir, exist_ok=True)
-    cmd = [REF_BIN, "dump", mesh, str(elevate), str(refine), material, str(nthreads), repr(gf), u_file, outdir]
+    cmd = [binary or REF_BIN, "dump", mesh, str(elevate), str(refine), material, str(nthreads), repr(gf), u_file, outdir]
     if lite:
         cmd.append("lite")
     subprocess.check_call(cmd, stdout=subprocess.DEVNULL)

@@ -31,6 +31,16 @@
 #include "mimi/materials/materials.hpp"
 #include "mimi/utils/precomputed.hpp"
 
+// -DMIMI_REF_USE_B200 (target oracle/_ref/mimi_ref_b200): the reference's call chain with its domain integrator replaced
+// by the adapter a maintainer would add (adapter/b200_nonlinear_solid.hpp -> C ABI of libmimi_b200.so). Everything
+// else in this file -- mesh, FE space, PrecomputedData, materials, mass form, the dumps -- stays the reference's.
+#ifdef MIMI_REF_USE_B200
+#include "b200_nonlinear_solid.hpp"
+using DomainIntegrator = mimi::integrators::B200NonlinearSolid;
+#else
+using DomainIntegrator = mimi::integrators::NonlinearSolid;
+#endif
+
 // The only splinepy *library* symbol the reference's contact integrator pulls in
 // (coefficients/nearest_distance.hpp:259-281, NearestDistanceToSplines). The harness never builds a
 // NearestDistanceToSplines (rigid bodies are analytic NearestDistanceBase subclasses), so it must never run.
@@ -63,7 +73,7 @@ struct Setup {
   std::unique_ptr<mfem::FiniteElementSpace> fes;
   std::shared_ptr<mimi::utils::PrecomputedData> pre;
   std::shared_ptr<mimi::materials::MaterialBase> mat;
-  std::shared_ptr<mimi::integrators::NonlinearSolid> integ;
+  std::shared_ptr<DomainIntegrator> integ;
   std::unique_ptr<mfem::BilinearForm> mass;
   double t_precompute = 0.0;
 };
@@ -146,7 +156,7 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
     s.mass->Finalize(0);
     s.mass->SpMat().SortColumnIndices();  // operators/nonlinear_solid.cpp:86-122 expects sorted CSR
   }
-  s.integ = std::make_shared<mimi::integrators::NonlinearSolid>(s.mat->Name() + "-NonlinearSolid", s.mat, s.pre);
+  s.integ = std::make_shared<DomainIntegrator>(s.mat->Name() + "-NonlinearSolid", s.mat, s.pre);
   s.pre->PrecomputeElementQuadData("domain", -1, true);
   s.integ->Prepare();
   s.integ->dt_ = 0.5;  // pushed into the material by AddDomainResidual[AndGrad] (nonlinear_solid.cpp:154,167)
@@ -348,6 +358,10 @@ int main(int argc, char** argv) {
       // history layout: every state matrix in a 9-double slot (column-major dim x dim in front), then the scalars;
       // J2Linear has k_state_scalars = 2 but only uses the first (19 doubles), J2 = 9 + 2
       const bool lin = material == "j2linear";
+#ifdef MIMI_REF_USE_B200
+      (void)lin;
+      std::vector<double> st = s.integ->State();  // the history lives on the device, same [NE][nq][ns] layout
+#else
       const int ns = lin ? 19 : 9 * (int)eqd[0].GetQuadData()[0].material_state->matrices.size() + 2;
       std::vector<double> st((size_t)NE * nq * ns, 0.0);
       for (int e = 0; e < NE; ++e)
@@ -359,6 +373,7 @@ int main(int argc, char** argv) {
           o[9 * ms.matrices.size()] = ms.scalars[0];
           if (!lin) o[9 * ms.matrices.size() + 1] = ms.scalars[1];
         }
+#endif
       dump(out, "state.f64", st.data(), st.size());
       mfem::Vector ub(u), rb(NV);
       ub *= 1.5;

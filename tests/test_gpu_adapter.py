@@ -1,0 +1,68 @@
+"""Drop-in proof (GPU): the reference's OWN call chain -- mfem::Mesh / FiniteElementSpace, PrecomputedData, the material
+objects, the mass BilinearForm, AddDomainResidual / AddDomainResidualAndGrad / DomainPostTimeAdvance called through the
+NonlinearBase interface -- with the domain integrator replaced by adapter/b200_nonlinear_solid.hpp, the NonlinearBase
+subclass INTEGRATION.md describes, which forwards to the C ABI of libmimi_b200.so.
+
+oracle/_ref/mimi_ref_b200 is that program: oracle/ref_harness.cpp compiled with -DMIMI_REF_USE_B200 against the
+unmodified reference sources (oracle/Makefile.ref, built where /root/reference exists; the binary travels to the GPU
+box). Its dumps must equal the golden vectors the reference's CPU integrator produced for the same inputs."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+
+from mimi_b200 import meshgen
+from oracle import oracle_py as O
+from tests.cases import load_golden, load_j2_golden
+
+pytestmark = pytest.mark.gpu
+
+# (fixture, mesh writer, elevate, refine): the recipes of oracle/make_golden.py CASES
+RECIPES = {
+    "cube_p2_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 1, 1),
+    "beam2d_p3_n2": (lambda f: meshgen.write_box_p1(f, (5.0, 1.0)), 2, 1),
+    "quad_p2_n4": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 1, 2),
+    "cube_p3_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 2, 1),
+}
+
+
+def run_adapter(name, material, gf):
+    if not O.have_ref_b200():
+        pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
+    writer, elevate, refine = RECIPES[name]
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        writer(mesh)
+        return O.run_ref_dump(mesh, elevate, refine, material, os.path.join(tmp, "d"), gf=gf, binary=O.REF_B200_BIN)
+
+
+@pytest.mark.parametrize("material", ["neohookean", "stvk", "j2linear"])
+@pytest.mark.parametrize("name", list(RECIPES))
+def test_reference_chain_through_the_adapter_bit_exact(name, material):
+    G = load_golden(name)
+    D = run_adapter(name, material, G["gf"])
+    assert np.array_equal(D["u"], G["u"]) and np.array_equal(D["mass"], G["mass"])     # same inputs
+    assert np.array_equal(D["r"], G["r_" + material])
+    assert np.array_equal(D["r2"], G["r2_" + material])
+    assert np.array_equal(D["A"], G["A_" + material])          # mass + gf * K, added into the reference's SparseMatrix
+    if material == "j2linear":
+        assert np.array_equal(D["state"].reshape(G["state_j2linear"].shape), G["state_j2linear"])
+        assert np.array_equal(D["r_b"], G["rb_j2linear"]) and np.array_equal(D["A_b"], G["Ab_j2linear"])
+
+
+def _rel(a, b):
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+@pytest.mark.parametrize("material,key,ktol", [("j2_jcthermo", "_jcthermo", 1e-4), ("j2_voce", "_voce", 1e-4),
+                                               ("j2simo_voce", "_simo_voce", 2e-3), ("j2log_jcthermo", "_log_jcthermo", 1e-2)])
+def test_reference_chain_through_the_adapter_j2_family(material, key, ktol):
+    """The adapter's material dispatch (MaterialBase::Name + dynamic_cast on the hardening law) for the J2 family;
+    tolerances as in tests/test_gpu_j2.py."""
+    name = "j2_cube_p2_n2"
+    G = load_j2_golden(name)
+    D = run_adapter("cube_p2_n2", material, G["gf"])
+    assert _rel(D["r"], G["r" + key]) <= 1e-12 and _rel(D["A"], G["A" + key]) <= ktol
+    assert _rel(D["state"].reshape(G["state" + key].shape), G["state" + key]) <= 1e-12
+    assert _rel(D["r_b"], G["rb" + key]) <= 1e-12 and _rel(D["A_b"], G["Ab" + key]) <= ktol
