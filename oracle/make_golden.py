@@ -127,6 +127,10 @@ def eig_main():
     print("eig_sym", out["A2"].shape, out["A3"].shape)
 
 
+HISTORY_RUNS = {"neohook": ("neohookean", -5.0, 0.05), "j2": ("j2_balken", -3.0, 0.5),
+                "j2_simo": ("j2simo_balken", -3.0, 0.5), "j2_log": ("j2log_balken", -3.0, 0.5)}
+
+
 def histories_main():
     """The reference's own golden vectors for this path: tests/data/ref/<case>_h1_p2/x_<i>.txt, the
     displacement after each of 10 generalized-alpha steps of the 2D p=3 beam (tests/test_nonlinear_solid.py:54-112).
@@ -134,6 +138,13 @@ def histories_main():
     out = {}
     for key, folder in (("neohook", "neohook_h1_p2"), ("j2", "j2_h1_p2"), ("j2_simo", "j2_simo_h1_p2"), ("j2_log", "j2_log_h1_p2")):
         out[key] = np.array([np.genfromtxt("/root/reference/tests/data/ref/%s/x_%d.txt" % (folder, i)) for i in range(10)])
+    # and what the compiled reference itself does on that set-up here (harness mode 'steps', dense LU for UMFPACK):
+    # Newton iteration counts per step, the north_star's "identical Newton iteration counts" reference
+    with tempfile.TemporaryDirectory() as tmp:
+        for key, (mat, force, dt) in HISTORY_RUNS.items():
+            x, its = O.run_ref_steps("/root/reference/tests/data/balken.mesh", 2, 1, mat, force, dt, 10, os.path.join(tmp, key))
+            assert np.allclose(x, out[key]), key
+            out["ref_x_" + key], out["ref_its_" + key] = x, its
     np.savez_compressed(os.path.join(OUT, "balken_histories.npz"), **out)
     print("balken_histories", {k: v.shape for k, v in out.items()})
 

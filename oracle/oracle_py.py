@@ -503,3 +503,13 @@ def run_ref_eig(mats, outdir):
     lam = np.fromfile(os.path.join(outdir, "lambda.f64")).reshape(n, dim)
     vec = np.fromfile(os.path.join(outdir, "vec.f64")).reshape(n, dim, dim)
     return lam, vec
+
+
+def run_ref_steps(mesh, elevate, refine, material, force, dt, nsteps, outdir, binary=None, nthreads=1):
+    """Harness mode 'steps': the reference's own time loop (forms::Nonlinear + operators::NonlinearSolid + LineSearchNewton
+    + GeneralizedAlpha2) on the clamped-beam set-up of its tests -> (x history [nsteps][NV], Newton iterations)."""
+    os.makedirs(outdir, exist_ok=True)
+    subprocess.check_call([binary or REF_BIN, "steps", mesh, str(elevate), str(refine), material, str(nthreads), repr(force),
+                           repr(dt), str(nsteps), outdir], stdout=subprocess.DEVNULL)
+    its = np.fromfile(os.path.join(outdir, "newton_its.i32"), np.int32)
+    return np.fromfile(os.path.join(outdir, "x_hist.f64")).reshape(nsteps, -1), its

@@ -29,6 +29,10 @@
 #include "mimi/integrators/mortar_contact.hpp"
 #include "mimi/integrators/nonlinear_solid.hpp"
 #include "mimi/materials/materials.hpp"
+#include "mimi/forms/nonlinear.hpp"
+#include "mimi/operators/nonlinear_solid.hpp"
+#include "mimi/solvers/newton.hpp"
+#include "mimi/solvers/ode.hpp"
 #include "mimi/utils/precomputed.hpp"
 
 // -DMIMI_REF_USE_B200 (target oracle/_ref/mimi_ref_b200): the reference's call chain with its domain integrator replaced
@@ -135,6 +139,10 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
     } else if (h == "jcconst") {
       auto hd = std::make_shared<mm::JohnsonCookConstantTemperatureHardening>();
       jcr_fill(*hd); hd->reference_temperature_ = 10; hd->m_ = 1.3558; m->hardening_ = hd;
+    } else if (h == "balken") {  // balken_plasticity of the reference's tests/test_nonlinear_solid.py:16-33 (C_ stays value-initialised)
+      auto hd = std::make_shared<mm::JohnsonCookTemperatureAndRateDependentHardening>();
+      hd->A_ = 70; hd->B_ = 140; hd->n_ = 0.2835; hd->m_ = 1.3558; hd->effective_plastic_strain_rate_ = 0.004;
+      hd->reference_temperature_ = 20; m->hardening_ = hd;
     } else { std::fprintf(stderr, "unknown hardening %s\n", h.c_str()); std::exit(2); }
   }
   else { std::fprintf(stderr, "unknown material %s\n", material.c_str()); std::exit(2); }
@@ -512,6 +520,87 @@ int main(int argc, char** argv) {
       << ", \"nq\": " << pre.GetElementQuadData("domain")[0].n_quad << "}\n";
     return 0;
   }
+  if (mode == "steps") {
+    // steps <mesh> <elevate> <refine> <material> <nthreads> <body force on component 1> <dt> <n steps> <out dir>
+    // The reference's own time loop (tests/test_nonlinear_solid.py:54-112): PyNonlinearSolid::Setup
+    // (py_nonlinear_solid.cpp:155-386) restated on the reference's classes -- forms::Nonlinear, operators::NonlinearSolid,
+    // LineSearchNewton, GeneralizedAlpha2 -- with essential dofs on boundary id 2, rho_inf = 0.5 and Newton
+    // (1e-12, 1e-8, 10, false). UMFPACK is absent from this image: the 50-dof systems are solved by a dense LU.
+    const double force = std::atof(argv[7]);
+    double dt = std::atof(argv[8]);
+    const int nsteps = std::atoi(argv[9]);
+    const std::string out = argv[10];
+    Setup s = build(mesh_file, elevate, refine, material, nthreads, false);
+    auto& fes = *s.fes;
+    const int dim = s.pre->dim_, NV = s.pre->n_v_dofs_;
+    mfem::Array<int> zero_dofs;
+    for (int c = 0; c < dim; ++c) {
+      mfem::Array<int> marker(s.mesh->bdr_attributes.Max()), list;
+      marker = 0;
+      marker[2] = 1;  // bc.initial.dirichlet(2, c): PySolid::FindBoundaryDofIds, py_solid.cpp:184-234
+      fes.GetEssentialTrueDofs(marker, list, c);
+      zero_dofs.Append(list);
+    }
+    zero_dofs.Sort();
+    zero_dofs.Unique();
+    auto nl_oper = std::make_unique<mimi::operators::NonlinearSolid>(fes);
+    mfem::SparseMatrix tmp;
+    auto mass = std::make_shared<mfem::BilinearForm>(&fes);
+    nl_oper->AddBilinearForm("mass", mass);
+    mfem::ConstantCoefficient rho(s.mat->density_);
+    mass->AddDomainIntegrator(new mfem::VectorMassIntegrator(rho));
+    mass->Assemble(0);
+    mass->FormSystemMatrix(zero_dofs, tmp);
+    auto stiffness = std::make_shared<mimi::forms::Nonlinear>(&fes);
+    nl_oper->AddNonlinearForm("nonlinear_stiffness", stiffness);
+    stiffness->AddDomainIntegrator(s.integ);
+    stiffness->SetEssentialTrueDofs(zero_dofs);
+    auto rhs = std::make_shared<mfem::LinearForm>(&fes);
+    mfem::VectorArrayCoefficient bf(dim);
+    bf.Set(1, new mfem::ConstantCoefficient(force));
+    rhs->AddDomainIntegrator(new mfem::VectorDomainLFIntegrator(bf));
+    rhs->Assemble();
+    rhs->SetSubVector(zero_dofs, 0.0);
+    nl_oper->AddLinearForm("rhs", rhs);
+    struct DenseLU : mfem::Solver {
+      std::unique_ptr<mfem::DenseMatrix> d;
+      std::unique_ptr<mfem::DenseMatrixInverse> inv;
+      void SetOperator(const mfem::Operator& op) override {
+        d.reset(dynamic_cast<const mfem::SparseMatrix&>(op).ToDenseMatrix());
+        inv = std::make_unique<mfem::DenseMatrixInverse>(*d);
+        height = width = d->Height();
+      }
+      void Mult(const mfem::Vector& b, mfem::Vector& x) const override { inv->Mult(b, x); }
+    } lin;
+    auto newton = std::make_shared<mimi::solvers::LineSearchNewton>();
+    newton->nl_oper_ = nl_oper.get();
+    newton->iterative_mode = false;
+    newton->SetOperator(*nl_oper);
+    newton->SetSolver(lin);
+    newton->SetPrintLevel(-1);
+    newton->SetRelTol(1e-12);
+    newton->SetAbsTol(1e-8);
+    newton->SetMaxIter(10);
+    nl_oper->SetNewtonSolver(newton);
+    mimi::solvers::GeneralizedAlpha2 ode(*nl_oper, 0.5);
+    nl_oper->Setup();
+    ode.SetupDirichletDofs(nl_oper->dirichlet_dofs_);
+    mfem::Vector x(NV), v(NV);
+    x = 0.0;
+    v = 0.0;
+    double t = 0.0;
+    std::vector<double> hist;
+    std::vector<int> its;
+    for (int i = 0; i < nsteps; ++i) {
+      ode.StepTime2(x, v, t, dt);
+      hist.insert(hist.end(), x.GetData(), x.GetData() + NV);
+      its.push_back(newton->GetNumIterations());
+    }
+    dump(out, "x_hist.f64", hist.data(), hist.size());
+    dump(out, "newton_its.i32", its.data(), its.size());
+    return 0;
+  }
+
   if (mode == "sweeps") {
     // The O(nnz) sweeps around the integrators in one Newton iteration (operators/nonlinear_solid.cpp:240-283,
     // forms/nonlinear.hpp:53-116): y = M a; J = M; J += fac0 K(x + fac0 a) (+ r); r[ess] = 0; EliminateRowCol(ess);
