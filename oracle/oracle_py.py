@@ -431,10 +431,10 @@ def load_contact_dump(d):
 
 
 def run_ref_contact(mesh, elevate, refine, outdir, bdr_attr, penalty, body, gf=1.0, material="neohookean", u_file="-",
-                    nthreads=1):
+                    nthreads=1, binary=None):
     """body = ("plane", [...]) / ("sphere", [...])."""
     os.makedirs(outdir, exist_ok=True)
-    cmd = [REF_BIN, "contact", mesh, str(elevate), str(refine), material, str(nthreads), repr(gf), u_file, outdir,
+    cmd = [binary or REF_BIN, "contact", mesh, str(elevate), str(refine), material, str(nthreads), repr(gf), u_file, outdir,
            str(bdr_attr), repr(float(penalty)), body[0]] + [repr(float(x)) for x in body[1]]
     subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
     return load_contact_dump(outdir)

@@ -39,10 +39,13 @@
 // by the adapter a maintainer would add (adapter/b200_nonlinear_solid.hpp -> C ABI of libmimi_b200.so). Everything
 // else in this file -- mesh, FE space, PrecomputedData, materials, mass form, the dumps -- stays the reference's.
 #ifdef MIMI_REF_USE_B200
+#include "b200_mortar_contact.hpp"
 #include "b200_nonlinear_solid.hpp"
 using DomainIntegrator = mimi::integrators::B200NonlinearSolid;
+#define MIMI_REF_B200_BODY , mimi::integrators::B200RigidBody
 #else
 using DomainIntegrator = mimi::integrators::NonlinearSolid;
+#define MIMI_REF_B200_BODY
 #endif
 
 // The only splinepy *library* symbol the reference's contact integrator pulls in
@@ -178,7 +181,7 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
 // MortarContact reads it (nearest_distance.hpp:139-193): physical_minus_query_, distance_, first_derivatives_
 // [para_dim x dim, row-major]. The operation order below is the contract the C oracle (oracle/mimi_oracle.c,
 // orc_rigid_nearest) and the CUDA path (mb2_contact.cu, rigid_nearest) restate.
-struct RigidPlane : mimi::coefficients::NearestDistanceBase {
+struct RigidPlane : mimi::coefficients::NearestDistanceBase MIMI_REF_B200_BODY {
   int dim = 0;
   double o[3] = {0, 0, 0}, t[2][3] = {{0, 0, 0}, {0, 0, 0}}, lo = -1e300, hi = 1e300;
   void NearestDistance(const Query& query, Results& r) const override {
@@ -210,9 +213,15 @@ struct RigidPlane : mimi::coefficients::NearestDistanceBase {
       for (int d = 0; d < dim; ++d) r.first_derivatives_[k * dim + d] = t[k][d];
   }
   int Size() const override { return 1; }
+#ifdef MIMI_REF_USE_B200
+  int B200Kind() const override { return MB2_RIGID_PLANE; }
+  std::vector<double> B200Params() const override {
+    return {o[0], o[1], o[2], t[0][0], t[0][1], t[0][2], t[1][0], t[1][1], t[1][2], lo, hi};
+  }
+#endif
 };
 
-struct RigidSphere : mimi::coefficients::NearestDistanceBase {
+struct RigidSphere : mimi::coefficients::NearestDistanceBase MIMI_REF_B200_BODY {
   int dim = 0;
   double c[3] = {0, 0, 0}, R = 1.0;
   void NearestDistance(const Query& query, Results& r) const override {
@@ -250,6 +259,10 @@ struct RigidSphere : mimi::coefficients::NearestDistanceBase {
     }
   }
   int Size() const override { return 1; }
+#ifdef MIMI_REF_USE_B200
+  int B200Kind() const override { return MB2_RIGID_SPHERE; }
+  std::vector<double> B200Params() const override { return {c[0], c[1], c[2], R}; }
+#endif
 };
 
 // exposes MortarContact's protected nodal vectors for the dump
@@ -260,6 +273,12 @@ struct ContactProbe : mimi::integrators::MortarContact {
   const mfem::Vector& Area() const { return area_; }
   const mimi::utils::Vector<int>& MarkedVDofs() const { return marked_boundary_v_dofs_; }
 };
+
+#ifdef MIMI_REF_USE_B200
+using ContactIntegrator = mimi::integrators::B200MortarContact;
+#else
+using ContactIntegrator = ContactProbe;
+#endif
 
 void fill_u(mfem::Vector& u, const char* u_file) {
   if (std::strcmp(u_file, "-") == 0) {
@@ -438,7 +457,11 @@ int main(int argc, char** argv) {
     mfem::Array<int> marker(s.mesh->bdr_attributes.Max());
     marker = 0;
     marker[bdr_attr - 1] = 1;
-    auto integ = std::make_shared<ContactProbe>(nd, "contact" + std::to_string(bdr_attr), s.pre);
+#ifdef MIMI_REF_USE_B200
+    auto integ = std::make_shared<ContactIntegrator>(nd, "contact" + std::to_string(bdr_attr), s.pre, s.integ->Context());
+#else
+    auto integ = std::make_shared<ContactIntegrator>(nd, "contact" + std::to_string(bdr_attr), s.pre);
+#endif
     integ->runtime_communication_ = std::make_shared<mimi::utils::RuntimeCommunication>();
     integ->SetBoundaryMarker(&marker);
     auto& marked = integ->MarkedBoundaryElements();
@@ -456,7 +479,12 @@ int main(int argc, char** argv) {
       const auto& ed = beqd[f].GetElementData();
       std::memcpy(&vd[(size_t)f * tdf], ed.v_dofs.GetData(), sizeof(int) * tdf);
       std::memcpy(&aid[(size_t)f * tdf * tdf], ed.A_ids.data(), sizeof(int) * tdf * tdf);
+#ifdef MIMI_REF_USE_B200  // MortarContact::Prepare's per-face x_ref matrices do not exist: same values from their source
+      for (int a = 0; a < ndf; ++a)
+        for (int c = 0; c < dim; ++c) xr[(size_t)f * ndf * dim + a + (size_t)c * ndf] = ed.element_trans->GetPointMat()(c, a);
+#else
       std::memcpy(&xr[(size_t)f * ndf * dim], beqd[f].GetMatrix(0).GetData(), sizeof(double) * ndf * dim);  // kXRef = 0
+#endif
       for (int q = 0; q < nqf; ++q) {
         const auto& qd = beqd[f].GetQuadData()[q];
         const size_t fq = (size_t)f * nqf + q;

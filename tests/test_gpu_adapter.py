@@ -101,3 +101,29 @@ def test_reference_time_loop_through_the_adapter(case):
         # the tolerance may take one iteration more or less; the converged trajectory must not move
         assert max(abs(a - b) for a, b in zip(its, ref_its)) <= 1
         assert np.allclose(x, z["ref_x_" + case], rtol=1e-9, atol=1e-12)
+
+
+from oracle.make_golden import CONTACT_CASES as CONTACT_RECIPES  # noqa: E402  (mesh recipe, boundary, penalty, body)
+from tests.cases import load_contact_golden  # noqa: E402
+
+
+@pytest.mark.parametrize("name", list(CONTACT_RECIPES))
+def test_reference_contact_chain_through_the_adapter(name):
+    """adapter/b200_mortar_contact.hpp in the place of mimi::integrators::MortarContact, wired as
+    py_nonlinear_solid.cpp:292-325 does (boundary marker, CreateBoundaryElementQuadData, PrecomputeElementQuadData,
+    Prepare), sharing the domain adapter's context: AddDomainResidual then AddBoundaryResidual on the same r,
+    AddBoundaryResidualAndGrad into the reference's SparseMatrix (pre-loaded with mass), GapNorm, and the recordings
+    (nodal gap / area / pressure, marked vdofs, area / pressure / force). Golden = the reference's own MortarContact."""
+    if not O.have_ref_b200():
+        pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
+    writer, elevate, refine, gf, attr, penalty, spec = CONTACT_RECIPES[name]
+    G = load_contact_golden(name)
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        writer(mesh)
+        D = O.run_ref_contact(mesh, elevate, refine, os.path.join(tmp, "c"), attr, penalty, spec, gf=gf, binary=O.REF_B200_BIN)
+    assert np.array_equal(D["c_marked_v_dofs"], G["c_marked_v_dofs"])
+    for k in ("c_r0", "c_r", "c_gap", "c_area", "c_pressure", "c_r2", "c_A"):
+        assert np.array_equal(D[k], G[k]), k
+    assert np.any(G["c_pressure"] != 0)
+    assert np.allclose(D["c_scalars"], G["c_scalars"], rtol=1e-12, atol=0)      # whole-boundary sums: DESIGN.md section 2
