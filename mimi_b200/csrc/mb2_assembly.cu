@@ -522,16 +522,33 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
     tma_load_1d(sdN, dNe, (uint32_t)(nq0 * TD * sizeof(double)), &bar[0]);
   }
   // base F for every q straight from global/L2: MultAtB(element_x_mat_, dN_dX, F_) + AddDiagonal(1.0)
-  for (int task = t; task < NQ * DD; task += NT) {
-    const int q = task / DD, n = task - q * DD;
-    const int i = n % DIM, j = n / DIM;
-    const double* dN = dNe + (q * DIM + j) * ND;
-    const double* ui = sue + i * ND;
-    double d = 0.0;
-#pragma unroll 8
-    for (int k = 0; k < ND; k++) d += ui[k] * __ldg(dN + k);
-    if (i == j) d += 1.0;
-    sFb[task] = d;
+  // One task = one dN row (q, j) feeding the DIM entries F(:, j): the row is fetched once, 16 bytes per load and 8
+  // loads in flight (the scalar, dependent form spent 10 % of the kernel waiting on L2, profiles/r01_elem_p3_split_v2_summary.txt);
+  // every F entry still sums k = 0 .. ND-1 in order.
+  static_assert(ND % 16 == 0, "base-F prefetch batches 8 double2 loads");
+  for (int task = t; task < NQ * DIM; task += NT) {
+    const int q = task / DIM, j = task - q * DIM;
+    const double2* dN2g = reinterpret_cast<const double2*>(dNe + (q * DIM + j) * ND);
+    double d[DIM];
+#pragma unroll
+    for (int i = 0; i < DIM; i++) d[i] = 0.0;
+#pragma unroll 1
+    for (int k0 = 0; k0 < ND / 2; k0 += 8) {
+      double2 v[8];
+#pragma unroll
+      for (int x = 0; x < 8; x++) v[x] = __ldg(dN2g + k0 + x);
+#pragma unroll
+      for (int x = 0; x < 8; x++) {
+#pragma unroll
+        for (int i = 0; i < DIM; i++) {
+          const double2 uu = *reinterpret_cast<const double2*>(sue + i * ND + 2 * (k0 + x));
+          d[i] += uu.x * v[x].x;
+          d[i] += uu.y * v[x].y;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < DIM; i++) sFb[q * DD + i + DIM * j] = (i == j) ? d[i] + 1.0 : d[i];
   }
   double up1 = 0.0;
   if (act1 && !base1) {
