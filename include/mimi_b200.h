@@ -187,7 +187,13 @@ enum {
    * [deg_v+1][deg_u+1][dim] (u fastest). Closest point: nearest of (n_seed+1)^(dim-1) samples, then bound-clipped
    * Newton. The reference delegates this search to splinepy: converged results agree to rounding, not bitwise
    * (parity unpinned). The spline's orientation defines the contact normal as in the reference. */
-  MB2_RIGID_BEZIER = 2
+  MB2_RIGID_BEZIER = 2,
+  /* B-spline curve / surface with interior knots (open knot vectors; what toy_problem.py's extracted boundaries are):
+   * params = deg_u, deg_v, n_seed, ncp_u, ncp_v (1 for curves), knots_u[ncp_u + deg_u + 1], knots_v[ncp_v + deg_v + 1]
+   * (absent for curves), control points [ncp_v][ncp_u][dim]. The library splits it into Bezier patches by knot insertion
+   * on the host and queries every patch (the nearest wins). MB2_RIGID_BEZIER also accepts several patches of one degree
+   * back to back after n_seed. Parity unpinned like MB2_RIGID_BEZIER. */
+  MB2_RIGID_BSPLINE = 3
 };
 /* The marked boundary faces and their quadrature tables as PrecomputedData holds them for the integrator's name
  * (CreateBoundaryElementQuadData + PrecomputeElementQuadData(name, order, false), precomputed.cpp:243-330):

@@ -24,6 +24,7 @@ struct RigidBody {
   // MB2_RIGID_BEZIER: degrees, sampling resolution of the initial guess, control net [deg_v+1][deg_u+1][dim] (device)
   int deg_u = 0, deg_v = 0, n_seed = 0;
   const double* cp = nullptr;
+  int n_patches = 1;  // B-spline bodies: their Bezier patches one after the other in cp
 };
 constexpr int BEZ_MAXDEG = 5;
 
@@ -113,7 +114,7 @@ __device__ __noinline__ void bezier_eval(const RigidBody& b, double u, double v,
 }
 
 template <int DIM>
-__device__ __noinline__ void rigid_nearest_bezier(const RigidBody& b, const double* q, double* pmq, double& distance,
+__device__ __noinline__ void bezier_patch_nearest(const RigidBody& b, const double* q, double* pmq, double& distance,
                                                   double* fd) {
   constexpr int PD = DIM - 1;
   const int ns = b.n_seed;
@@ -186,6 +187,33 @@ __device__ __noinline__ void rigid_nearest_bezier(const RigidBody& b, const doub
   for (int k = 0; k < PD; k++)
 #pragma unroll
     for (int d = 0; d < DIM; d++) fd[k * DIM + d] = E[1 + k][d];
+}
+
+// Multi-patch bodies (B-splines with interior knots, split into Bezier patches on the host): the closest point of every
+// patch, the nearest wins, the first on ties (oracle: rigid_bezier_nearest in mimi_oracle_contact.c).
+template <int DIM>
+__device__ __noinline__ void rigid_nearest_bezier(const RigidBody& b, const double* q, double* pmq, double& distance,
+                                                  double* fd) {
+  if (b.n_patches <= 1) {
+    bezier_patch_nearest<DIM>(b, q, pmq, distance, fd);
+    return;
+  }
+  const size_t stride = (size_t)(b.deg_u + 1) * (b.deg_v + 1) * DIM;
+  double best = 1e300;
+  for (int p = 0; p < b.n_patches; p++) {
+    RigidBody bp = b;
+    bp.cp = b.cp + p * stride;
+    double pm[3], dist, f[6];
+    bezier_patch_nearest<DIM>(bp, q, pm, dist, f);
+    if (dist < best) {
+      best = dist;
+#pragma unroll
+      for (int d = 0; d < DIM; d++) pmq[d] = pm[d];
+#pragma unroll
+      for (int k = 0; k < (DIM - 1) * DIM; k++) fd[k] = f[k];
+    }
+  }
+  distance = best;
 }
 
 // ---- rigid bodies: closed-form closest point, the operation order of oracle/ref_harness.cpp (RigidPlane,
@@ -875,28 +903,124 @@ int mb2_contact_set_faces(mb2_ctx* c, int64_t NF, int nd_f, int nq_f, const int3
   return mb2::contact_set_faces(c, NF, nd_f, nq_f, v_dofs, N, dN_dxi, w);
 }
 
+namespace mb2 {
+// Bezier extraction of a B-spline curve by Boehm knot insertion (every interior knot raised to multiplicity p):
+// Q_i = alpha P_i + (1 - alpha) P_{i-1}, alpha = (u - t_i) / (t_{i+p} - t_i); the formula and order of
+// oracle_py.bspline_to_bezier. P: n points of `dim` doubles. Returns [n_spans][p+1][dim].
+static std::vector<double> bspline_curve_extract(int dim, int p, std::vector<double> U, std::vector<double> P) {
+  std::vector<double> interior(U.begin() + p + 1, U.end() - p - 1);
+  interior.erase(std::unique(interior.begin(), interior.end()), interior.end());
+  for (double u : interior) {
+    while ((int)std::count(U.begin(), U.end(), u) < p) {
+      int k = -1;
+      for (int i = 0; i + 1 < (int)U.size(); i++)
+        if (U[i] <= u && u < U[i + 1]) k = i;
+      if (k < 0) return {};
+      const int n = (int)(P.size() / dim);
+      std::vector<double> Q((size_t)(n + 1) * dim);
+      for (int i = 0; i <= n; i++) {
+        for (int d = 0; d < dim; d++) {
+          double v;
+          if (i <= k - p) v = P[(size_t)i * dim + d];
+          else if (i > k) v = P[(size_t)(i - 1) * dim + d];
+          else {
+            const double a = (u - U[i]) / (U[i + p] - U[i]);
+            v = a * P[(size_t)i * dim + d] + (1.0 - a) * P[(size_t)(i - 1) * dim + d];
+          }
+          Q[(size_t)i * dim + d] = v;
+        }
+      }
+      P.swap(Q);
+      U.insert(U.begin() + k + 1, u);
+    }
+  }
+  const int n = (int)(P.size() / dim);
+  if ((n - 1) % p != 0) return {};
+  const int spans = (n - 1) / p;
+  std::vector<double> out;
+  out.reserve((size_t)spans * (p + 1) * dim);
+  for (int s = 0; s < spans; s++)
+    for (int i = 0; i <= p; i++)
+      for (int d = 0; d < dim; d++) out.push_back(P[(size_t)(s * p + i) * dim + d]);
+  return out;
+}
+
+// Curve (dv == 0) or tensor-product surface: rows first (u), then columns (v); patch order v span slow, u span fast;
+// a patch is [dv+1][du+1][dim], u fastest (oracle_py.bspline_surface_to_bezier).
+static std::vector<double> bspline_extract(int dim, int du, int dv, int nu, int nv, const double* ku, const double* kv,
+                                           const double* P) {
+  const std::vector<double> Uu(ku, ku + nu + du + 1);
+  if (dv == 0) return bspline_curve_extract(dim, du, Uu, std::vector<double>(P, P + (size_t)nu * dim));
+  const std::vector<double> Uv(kv, kv + nv + dv + 1);
+  std::vector<std::vector<double>> rows(nv);
+  for (int j = 0; j < nv; j++) {
+    rows[j] = bspline_curve_extract(dim, du, Uu, std::vector<double>(P + (size_t)j * nu * dim, P + (size_t)(j + 1) * nu * dim));
+    if (rows[j].empty()) return {};
+  }
+  const int su = (int)(rows[0].size() / ((du + 1) * dim));
+  std::vector<std::vector<double>> cols((size_t)su * (du + 1));
+  int sv = 0;
+  for (int a = 0; a < su; a++)
+    for (int i = 0; i <= du; i++) {
+      std::vector<double> line((size_t)nv * dim);
+      for (int j = 0; j < nv; j++)
+        for (int d = 0; d < dim; d++) line[(size_t)j * dim + d] = rows[j][((size_t)a * (du + 1) + i) * dim + d];
+      cols[(size_t)a * (du + 1) + i] = bspline_curve_extract(dim, dv, Uv, line);
+      if (cols[(size_t)a * (du + 1) + i].empty()) return {};
+      sv = (int)(cols[(size_t)a * (du + 1) + i].size() / ((dv + 1) * dim));
+    }
+  std::vector<double> out;
+  for (int b = 0; b < sv; b++)
+    for (int a = 0; a < su; a++)
+      for (int jj = 0; jj <= dv; jj++)
+        for (int i = 0; i <= du; i++)
+          for (int d = 0; d < dim; d++) out.push_back(cols[(size_t)a * (du + 1) + i][((size_t)b * (dv + 1) + jj) * dim + d]);
+  return out;
+}
+}  // namespace mb2
+
 int mb2_contact_set_rigid_body(mb2_ctx* c, int kind, const double* params, int nparams, double penalty) {
   CCHECK(c);
   ContactState* S = static_cast<ContactState*>(c->contact);
   CREQ(S, "call mb2_contact_set_faces first");
-  CREQ(kind == MB2_RIGID_PLANE || kind == MB2_RIGID_SPHERE || kind == MB2_RIGID_BEZIER, "unknown rigid body kind");
-  if (kind == MB2_RIGID_BEZIER) {
-    CREQ(params && nparams >= 3, "Bezier body needs {deg_u, deg_v, n_seed, control points}");
+  CREQ(kind == MB2_RIGID_PLANE || kind == MB2_RIGID_SPHERE || kind == MB2_RIGID_BEZIER || kind == MB2_RIGID_BSPLINE,
+       "unknown rigid body kind");
+  if (kind == MB2_RIGID_BEZIER || kind == MB2_RIGID_BSPLINE) {
+    CREQ(params && nparams >= 3, "spline body needs {deg_u, deg_v, n_seed, ...}");
     const int du = (int)params[0], dv = (int)params[1], ns = (int)params[2];
-    CREQ(du >= 1 && du <= mb2::BEZ_MAXDEG && dv >= 0 && dv <= mb2::BEZ_MAXDEG && ns >= 1, "Bezier degree must be 1..5");
+    CREQ(du >= 1 && du <= mb2::BEZ_MAXDEG && dv >= 0 && dv <= mb2::BEZ_MAXDEG && ns >= 1, "spline degree must be 1..5");
     CREQ((c->dim == 2) == (dv == 0), "a 2D body is a curve (deg_v = 0), a 3D body a surface");
     const int ncp = (du + 1) * (dv + 1) * c->dim;
-    CREQ(nparams == 3 + ncp, "Bezier control point count does not match the degrees");
+    std::vector<double> patches;
+    if (kind == MB2_RIGID_BEZIER) {
+      CREQ(nparams > 3 && (nparams - 3) % ncp == 0, "Bezier control point count does not match the degrees");
+      patches.assign(params + 3, params + nparams);
+    } else {
+      CREQ(nparams >= 5, "B-spline body needs {deg_u, deg_v, n_seed, ncp_u, ncp_v, knots_u, knots_v, control points}");
+      const int nu = (int)params[3], nv = (int)params[4];
+      CREQ(nu >= du + 1 && nv >= dv + 1 && (dv > 0 || nv == 1), "B-spline control point counts");
+      const int nku = nu + du + 1, nkv = dv > 0 ? nv + dv + 1 : 0;
+      CREQ(nparams == 5 + nku + nkv + nu * nv * c->dim, "B-spline parameter count");
+      const double* ku = params + 5;
+      const double* kv = ku + nku;
+      const double* P = kv + nkv;
+      for (int i = 0; i + 1 < nku; i++) CREQ(ku[i] <= ku[i + 1], "knot vectors must be non-decreasing");
+      for (int i = 0; i + 1 < nkv; i++) CREQ(kv[i] <= kv[i + 1], "knot vectors must be non-decreasing");
+      patches = mb2::bspline_extract(c->dim, du, dv, nu, nv, ku, kv, P);
+      CREQ(!patches.empty(), "B-spline body: open knot vectors (end multiplicity degree + 1) expected");
+    }
+    const int np = (int)(patches.size() / ncp);
     MB2_CUDA(cudaSetDevice(c->device));
     MB2_CUDA(cudaStreamSynchronize(c->stream));  // a previous assembly may still read the old control net
     if (S->d_cp) cudaFree(S->d_cp);
     S->d_cp = nullptr;
-    MB2_CUDA(cudaMalloc(&S->d_cp, sizeof(double) * ncp));
-    MB2_CUDA(cudaMemcpy(S->d_cp, params + 3, sizeof(double) * ncp, cudaMemcpyHostToDevice));
+    MB2_CUDA(cudaMalloc(&S->d_cp, sizeof(double) * patches.size()));
+    MB2_CUDA(cudaMemcpy(S->d_cp, patches.data(), sizeof(double) * patches.size(), cudaMemcpyHostToDevice));
     S->body = mb2::RigidBody();
-    S->body.kind = kind;
+    S->body.kind = MB2_RIGID_BEZIER;
     S->body.deg_u = du; S->body.deg_v = dv; S->body.n_seed = ns;
     S->body.cp = S->d_cp;
+    S->body.n_patches = np;
     S->penalty = penalty;
     return MB2_OK;
   }

@@ -30,6 +30,8 @@ typedef struct {
   /* kind == ORC_RIGID_BEZIER (below): degrees, sampling resolution of the initial guess, control net */
   int deg_u, deg_v, n_seed;
   const double* cp;
+  /* a B-spline body = its Bezier patches one after the other in cp (0 or 1: a single patch) */
+  int n_patches;
 } orc_rigid;
 
 static void rigid_bezier_nearest(const orc_rigid* b, const double* q, double* pmq, double* distance, double* fd);
@@ -484,14 +486,28 @@ void orc_bezier_nearest(const orc_bezier* b, const double* q, double* xi, double
   }
 }
 
+/* Multi-patch bodies (B-splines with interior knots, split into Bezier patches by the caller): the closest point of
+ * every patch, the nearest wins, the first on ties -- mb2_contact.cu (rigid_nearest_bezier) does the same. */
 static void rigid_bezier_nearest(const orc_rigid* b, const double* q, double* pmq, double* distance, double* fd) {
-  const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp};
-  orc_bezier_nearest(&z, q, 0, pmq, distance, fd);
+  const int np = b->n_patches > 1 ? b->n_patches : 1;
+  const size_t stride = (size_t)(b->deg_u + 1) * (b->deg_v + 1) * b->dim;
+  double best = 1e300;
+  for (int p = 0; p < np; p++) {
+    const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp + p * stride};
+    double pm[3], dist, f[6];
+    orc_bezier_nearest(&z, q, 0, pm, &dist, f);
+    if (dist < best) {
+      best = dist;
+      for (int d = 0; d < b->dim; d++) pmq[d] = pm[d];
+      for (int k = 0; k < (b->dim - 1) * b->dim; k++) fd[k] = f[k];
+    }
+  }
+  *distance = best;
 }
 
 /* test helper: closest point only (xi out) */
 void orc_rigid_query(const orc_rigid* b, const double* q, double* xi, double* pmq, double* distance, double* fd) {
-  if (b->kind == ORC_RIGID_BEZIER) {
+  if (b->kind == ORC_RIGID_BEZIER && b->n_patches <= 1) {
     const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp};
     orc_bezier_nearest(&z, q, xi, pmq, distance, fd);
   } else {

@@ -288,7 +288,7 @@ RIGID_PLANE, RIGID_SPHERE = 0, 1
 
 class Rigid(C.Structure):
     _fields_ = [("kind", C.c_int), ("dim", C.c_int), ("p", C.c_double * 16), ("deg_u", C.c_int), ("deg_v", C.c_int),
-                ("n_seed", C.c_int), ("cp", C.c_void_p)]
+                ("n_seed", C.c_int), ("cp", C.c_void_p), ("n_patches", C.c_int)]
 
 
 RIGID_BEZIER = 2
@@ -302,9 +302,78 @@ def rigid_bezier(dim, cps, n_seed=None):
     else:
         deg_v, deg_u = cps.shape[0] - 1, cps.shape[1] - 1
     n_seed = n_seed or (64 if dim == 2 else 16)
-    r = Rigid(RIGID_BEZIER, dim, (C.c_double * 16)(), deg_u, deg_v, n_seed, cps.ctypes.data)
+    r = Rigid(RIGID_BEZIER, dim, (C.c_double * 16)(), deg_u, deg_v, n_seed, cps.ctypes.data, 1)
     r._keep = cps
     return r
+
+
+def bspline_to_bezier(p, knots, P):
+    """Bezier extraction of a B-spline curve by Boehm knot insertion (every interior knot raised to multiplicity p):
+    P [n, dim] -> patches [n_spans, p+1, dim]. The same formula and order as mb2_contact.cu (bspline_extract):
+    Q_i = alpha P_i + (1 - alpha) P_{i-1}, alpha = (u - t_i) / (t_{i+p} - t_i)."""
+    U = [float(x) for x in knots]
+    P = [np.array(x, np.float64) for x in P]
+    for u in sorted(set(U[p + 1:len(U) - p - 1])):
+        while U.count(u) < p:
+            k = max(i for i in range(len(U) - 1) if U[i] <= u < U[i + 1])
+            Q = []
+            for i in range(len(P) + 1):
+                if i <= k - p:
+                    Q.append(P[i])
+                elif i > k:
+                    Q.append(P[i - 1])
+                else:
+                    a = (u - U[i]) / (U[i + p] - U[i])
+                    Q.append(a * P[i] + (1.0 - a) * P[i - 1])
+            P = Q
+            U.insert(k + 1, u)
+    n_spans = (len(P) - 1) // p
+    return np.array([[P[s * p + i] for i in range(p + 1)] for s in range(n_spans)])
+
+
+def bspline_surface_to_bezier(pu, pv, ku, kv, P):
+    """Tensor-product extraction: P [ncp_v, ncp_u, dim] (u fastest) -> patches [n_spans_v * n_spans_u, pv+1, pu+1, dim],
+    rows first (u direction), then columns; patch order: v span slow, u span fast."""
+    P = np.asarray(P, np.float64)
+    rows = [bspline_to_bezier(pu, ku, P[j]) for j in range(P.shape[0])]           # [ncp_v][su][pu+1][dim]
+    su = rows[0].shape[0]
+    out = []
+    cols = {}
+    for a in range(su):
+        for i in range(pu + 1):
+            cols[(a, i)] = bspline_to_bezier(pv, kv, [rows[j][a][i] for j in range(P.shape[0])])   # [sv][pv+1][dim]
+    sv = cols[(0, 0)].shape[0]
+    for b in range(sv):
+        for a in range(su):
+            out.append([[cols[(a, i)][b][jj] for i in range(pu + 1)] for jj in range(pv + 1)])
+    return np.array(out)
+
+
+def rigid_bezier_patches(dim, patches, n_seed=None):
+    """patches: curves [np, deg_u+1, 2] / surfaces [np, deg_v+1, deg_u+1, 3]."""
+    patches = np.ascontiguousarray(patches, np.float64)
+    r = rigid_bezier(dim, patches[0], n_seed)
+    r.cp = patches.ctypes.data
+    r.n_patches = patches.shape[0]
+    r._keep = patches
+    return r
+
+
+def bezier_patches_params(dim, patches, n_seed=None):
+    """mb2_contact_set_rigid_body(MB2_RIGID_BEZIER) with several patches: {deg_u, deg_v, n_seed, patch 0, patch 1, ...}."""
+    b = rigid_bezier_patches(dim, patches, n_seed)
+    return np.concatenate([[b.deg_u, b.deg_v, b.n_seed], b._keep.ravel()])
+
+
+def bspline_params(dim, pu, pv, ku, kv, P, n_seed=None):
+    """mb2_contact_set_rigid_body(MB2_RIGID_BSPLINE): {deg_u, deg_v, n_seed, ncp_u, ncp_v, knots_u, knots_v, control
+    points [ncp_v][ncp_u][dim]} (curves: deg_v = 0, ncp_v = 1, no knots_v)."""
+    P = np.ascontiguousarray(P, np.float64)
+    n_seed = n_seed or (64 if dim == 2 else 16)
+    ncp_u = P.shape[-2]
+    ncp_v = P.shape[0] if dim == 3 else 1
+    return np.concatenate([[pu, pv, n_seed, ncp_u, ncp_v], np.asarray(ku, np.float64),
+                           np.asarray(kv, np.float64) if dim == 3 else [], P.ravel()])
 
 
 def bezier_params(dim, cps, n_seed=None):

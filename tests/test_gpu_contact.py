@@ -198,3 +198,84 @@ def test_contact_on_emulated_ranks(ctx_factory, name, world):
     assert np.array_equal(r_glob, D["c_r0"] + (D["c_r"] - D["c_r0"])) or np.array_equal(r_glob, D["c_r"])
     assert np.array_equal(A_glob, D["c_A"])
     assert touched >= 1
+
+
+# ---- B-spline rigid bodies (interior knots): split into Bezier patches, every patch queried, the nearest wins
+def _bspline_cases():
+    """The Bezier bodies above with knots inserted (same geometry, now 3 / 2x2 patches) -- elevating the knot vector does
+    not move the curve, so everything must agree with the single-patch body to rounding."""
+    from scipy.interpolate import BSpline  # noqa: F401  (only to make the intent explicit; the insertion is our own)
+    curve, dome = _bezier_cases()["contact_quad_p3_n4_sphere"], _bezier_cases()["contact_cube_p2_n4_sphere"]
+    return {"contact_quad_p3_n4_sphere": (3, 0, curve), "contact_cube_p2_n4_sphere": (2, 2, dome)}
+
+
+def _insert_knots(p, U, P, new):
+    """Boehm insertion, one knot at a time (the B-spline a user would hand over: same curve, interior knots)."""
+    U = list(U)
+    P = [np.array(x, float) for x in P]
+    for u in new:
+        k = max(i for i in range(len(U) - 1) if U[i] <= u < U[i + 1])
+        Q = []
+        for i in range(len(P) + 1):
+            if i <= k - p:
+                Q.append(P[i])
+            elif i > k:
+                Q.append(P[i - 1])
+            else:
+                a = (u - U[i]) / (U[i + p] - U[i])
+                Q.append(a * P[i] + (1.0 - a) * P[i - 1])
+        P = Q
+        U.insert(k + 1, u)
+    return np.array(U), np.array(P)
+
+
+@pytest.mark.parametrize("name", ["contact_quad_p3_n4_sphere", "contact_cube_p2_n4_sphere"])
+def test_contact_bspline_body(ctx_factory, name):
+    D = load_contact_golden(name)
+    dim = D["dim"]
+    pu, pv, cps = _bspline_cases()[name]
+    if dim == 2:
+        ku, P = _insert_knots(pu, [0.0] * (pu + 1) + [1.0] * (pu + 1), cps, [0.3, 0.55])
+        kv = []
+        patches = O.bspline_to_bezier(pu, ku, P)
+    else:
+        ku, rows = None, []
+        for j in range(cps.shape[0]):                                  # u direction, every row
+            ku, Pj = _insert_knots(pu, [0.0] * (pu + 1) + [1.0] * (pu + 1), cps[j], [0.4])
+            rows.append(Pj)
+        rows = np.array(rows)
+        cols = []
+        for i in range(rows.shape[1]):                                 # v direction, every column
+            kv, Pi = _insert_knots(pv, [0.0] * (pv + 1) + [1.0] * (pv + 1), rows[:, i], [0.6])
+            cols.append(Pi)
+        P = np.transpose(np.array(cols), (1, 0, 2))                    # [ncp_v][ncp_u][3]
+        patches = O.bspline_surface_to_bezier(pu, pv, ku, kv, P)
+    assert patches.shape[0] == (3 if dim == 2 else 4)
+
+    def run(kind, params):
+        ctx = setup_contact(ctx_factory(), D)
+        ctx.contact_set_rigid_body(kind, params, D["penalty"])
+        r, A = D["c_r0"].copy(), D["mass"].copy()
+        ctx.add_boundary_residual_and_grad(D["u"], D["gf"], r, A)
+        return r, A, ctx.contact_nodal(), ctx.contact_gap_norm(D["u"])
+
+    # (1) the library's own extraction == the patches handed over explicitly, bit for bit
+    r_s, A_s, nod_s, gn_s = run(capi.MB2_RIGID_BSPLINE, O.bspline_params(dim, pu, pv, ku, kv, P))
+    r_p, A_p, nod_p, gn_p = run(capi.MB2_RIGID_BEZIER, O.bezier_patches_params(dim, patches))
+    assert np.array_equal(r_s, r_p) and np.array_equal(A_s, A_p) and gn_s == gn_p
+    # (2) device == C oracle on the multi-patch body, bit for bit
+    body = O.rigid_bezier_patches(dim, patches)
+    local, nm, _ = O.contact_prepare(dim, D["c_v_dofs"])
+    gap, area, pr, tot = O.contact_pressure(dim, D["c_v_dofs"], local, nm, D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"],
+                                            D["u"], body, D["penalty"])
+    assert 2 <= (pr != 0).sum()
+    r_o, A_o = D["c_r0"].copy(), D["mass"].copy()
+    O.contact_assemble(dim, D["c_v_dofs"], local, D["c_A_ids"], D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"], D["u"], pr,
+                       True, D["gf"], r_o, A_o)
+    assert np.array_equal(nod_p[0], gap) and np.array_equal(nod_p[1], area) and np.array_equal(nod_p[2], pr)
+    assert np.array_equal(r_p, r_o) and np.array_equal(A_p, A_o)
+    # (3) same geometry as the single Bezier patch: gaps / pressures agree to rounding
+    r_1, A_1, nod_1, gn_1 = run(capi.MB2_RIGID_BEZIER, O.bezier_params(dim, cps))
+    assert np.allclose(nod_p[0], nod_1[0], rtol=0, atol=1e-12 * max(1.0, np.abs(nod_1[0]).max()))
+    assert np.allclose(nod_p[2], nod_1[2], rtol=1e-6, atol=1e-6 * np.abs(nod_1[2]).max())
+    assert close(gn_p, gn_1, 1e-8)

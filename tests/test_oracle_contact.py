@@ -78,3 +78,51 @@ def test_bezier_closest_point_properties():
         xi, pmq, d, fd = O.rigid_query(b, q)
         assert d <= np.sqrt(((S - q) ** 2).sum(1).min()) + 1e-12
         assert max(abs(pmq @ fd[0]), abs(pmq @ fd[1])) <= 1e-10 or 0.0 in xi or 1.0 in xi
+
+
+def test_bspline_extraction_and_multipatch_nearest():
+    """B-spline rigid bodies: Bezier extraction by knot insertion reproduces the B-spline (scipy evaluates the original),
+    and the multi-patch closest point is the minimum over the patches (checked against dense sampling). Parity unpinned
+    against splinepy like the single-patch body."""
+    from scipy.interpolate import BSpline
+    rng = np.random.default_rng(11)
+    p = 3
+    U = np.array([0, 0, 0, 0, 0.2, 0.5, 0.5, 0.8, 1, 1, 1, 1.0])
+    P = rng.standard_normal((len(U) - p - 1, 2))
+    patches = O.bspline_to_bezier(p, U, P)
+    assert patches.shape == (4, p + 1, 2)
+    spl = BSpline(U, P, p)
+    breaks = [0, 0.2, 0.5, 0.8, 1.0]
+    from math import comb
+    for s in range(4):
+        for t in np.linspace(0, 1, 7):
+            B = np.array([comb(p, i) * t ** i * (1 - t) ** (p - i) for i in range(p + 1)])
+            assert np.allclose(B @ patches[s], spl(breaks[s] + t * (breaks[s + 1] - breaks[s])), atol=1e-13)
+    body = O.rigid_bezier_patches(2, patches, n_seed=32)
+    tt = np.linspace(0, 1, 20001)
+    dense = spl(tt)
+    for _ in range(25):
+        q = rng.standard_normal(2) * 1.5
+        xi, pmq, dist, fd = O.rigid_query(body, q)
+        brute = np.sqrt(((dense - q) ** 2).sum(1)).min()
+        assert dist <= brute + 1e-12 and abs(dist - brute) <= 1e-6
+    # surface: 2 x 2 patches reproduce the tensor-product B-spline at the patch corners' interiors
+    ku = np.array([0, 0, 0, 0.4, 1, 1, 1.0])
+    kv = np.array([0, 0, 0, 0.6, 1, 1, 1.0])
+    S = rng.standard_normal((4, 4, 3))
+    pt = O.bspline_surface_to_bezier(2, 2, ku, kv, S)
+    assert pt.shape == (4, 3, 3, 3)
+
+    def surf(u, v):
+        Bu = BSpline(ku, np.eye(4), 2)(u)
+        Bv = BSpline(kv, np.eye(4), 2)(v)
+        return np.einsum("j,i,jid->d", Bv, Bu, S)
+
+    ub, vb = [0, 0.4, 1.0], [0, 0.6, 1.0]
+    for b in range(2):
+        for a in range(2):
+            for (s, t) in [(0.0, 0.0), (0.3, 0.7), (1.0, 1.0), (0.5, 0.1)]:
+                Bs = np.array([comb(2, i) * s ** i * (1 - s) ** (2 - i) for i in range(3)])
+                Bt = np.array([comb(2, i) * t ** i * (1 - t) ** (2 - i) for i in range(3)])
+                val = np.einsum("j,i,jid->d", Bt, Bs, pt[b * 2 + a])
+                assert np.allclose(val, surf(ub[a] + s * (ub[a + 1] - ub[a]), vb[b] + t * (vb[b + 1] - vb[b])), atol=1e-13)
