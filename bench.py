@@ -259,6 +259,29 @@ def gpu_arm(args):
     total_qp = float(NE) * nq * world
     value = total_qp / (ms_per_step * 1e-3)
 
+    # ---- residual-only pass (SURVEY 8(d) "also report residual-only qp/s"): streams the per-qp tables once, HBM-bound
+    res_only = None
+    if not args.no_res_only:
+        for _ in range(2):
+            ctx.assemble_residual_device()
+        ctx.sync()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(max(args.steps, 3)):
+            ctx.assemble_residual_device()
+        e1.record(stream)
+        barrier()
+        ro_ms = float(e0.elapsed_time(e1)) / max(args.steps, 3)
+        if world > 1:
+            tt = torch.tensor([ro_ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ro_ms = float(tt[0])
+        tdof_ = 3 * M["nd"]
+        ro_bytes = float(NE) * (8.0 * nq * (tdof_ + 1) + 4 * tdof_ + 8 * tdof_ + 8 * tdof_)   # tables + v_dofs + u gather + R_e
+        res_only = {"value": float(NE) * nq * world / (ro_ms * 1e-3), "unit": UNIT, "ms_per_step": ro_ms,
+                    "algorithmic_gb_per_gpu": ro_bytes / 1e9, "achieved_gbs_per_gpu": ro_bytes / 1e9 / (ro_ms * 1e-3)}
+
     # ---- end to end through the host-buffer C-ABI call (pinned host memory) ----
     e2e = None
     if not args.no_e2e:
@@ -328,6 +351,10 @@ def gpu_arm(args):
                            "setup_s": M["setup_s"]},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "wall_s_timed_region": wall}
+        if res_only:
+            res_only["hbm_peak_gbs"] = hbm_peak
+            res_only["frac_hbm"] = res_only["achieved_gbs_per_gpu"] / hbm_peak
+            line["residual_only"] = res_only
         emit(line)
     ctx.close()
     if world > 1:
@@ -508,6 +535,7 @@ def main():
     ap.add_argument("--ref-n", type=int, default=24, help="spans per direction of the CPU reference sample")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-res-only", action="store_true", help="skip the residual-only pass")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--p", type=int, default=2, help="degree (2 = C3 headline; 3 = the C4 element type)")
     ap.add_argument("--material", default="neohookean", choices=["neohookean", "stvk"])

@@ -828,6 +828,117 @@ __global__ void csr_gather_kernel(int nd, const int32_t* __restrict__ nodes, int
 }
 
 // ---------------------------------------------------------------------------------------------
+// Residual-only element kernel (AddDomainResidual: the line-search evaluations of the Newton loop).
+// 1 189 flop per quadrature point against 664 bytes of tables: HBM-bound. One CTA per element (grid-stride), the
+// element's dN_dX tile (NQ x TD doubles) arrives by ONE bulk copy (cp.async.bulk + mbarrier) so that no thread spends
+// issue slots on the copy and several resident CTAs per SM keep the copy engines busy while others compute:
+//   F tasks   (q, i, j): NQ*DD sequential dot products over the ND nodes, spread over all threads
+//   stress    one thread per quadrature point: P, b = (w detJ) P
+//   R tasks   one thread per residual entry (i, j): q then k ascending (AddMult_a_ABt order, densemat.cpp:3002-3015)
+// Operation order of every accumulator = the reference's, as in element_kernel.
+// ---------------------------------------------------------------------------------------------
+template <int DIM, int ND, int NQ>
+struct ElemResCfg {
+  static constexpr int TD = DIM * ND;
+  static constexpr int DD = DIM * DIM;
+  static constexpr int NT = 192;
+  static constexpr int OFF_DN = 0;                       // [NQ][DIM][ND] (the global layout), 16-byte aligned
+  static constexpr int OFF_FB = (OFF_DN + NQ * TD + 1) / 2 * 2;
+  static constexpr int OFF_BQ = OFF_FB + NQ * DD;
+  static constexpr int OFF_WD = OFF_BQ + NQ * DD;
+  static constexpr int OFF_UE = OFF_WD + NQ;
+  static constexpr int OFF_BAR = (OFF_UE + TD + 1) / 2 * 2;
+  static constexpr int SMEM_DOUBLES = OFF_BAR + 2;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
+  static_assert((NQ * TD * sizeof(double)) % 16 == 0, "bulk copy size must be a multiple of 16 bytes");
+  static_assert(NT >= TD && NT >= NQ, "CTA too small");
+};
+
+template <int DIM, int ND, int NQ, int MAT>
+__global__ void __launch_bounds__(192) element_res_kernel(const ElemArgs g) {
+  using Cfg = ElemResCfg<DIM, ND, NQ>;
+  constexpr int TD = Cfg::TD, DD = Cfg::DD, NT = Cfg::NT, NS = mat_state_size(MAT);
+  extern __shared__ __align__(128) double smem[];
+  double* sdN = smem + Cfg::OFF_DN;
+  double* sFb = smem + Cfg::OFF_FB;
+  double* sbq = smem + Cfg::OFF_BQ;
+  double* swd = smem + Cfg::OFF_WD;
+  double* sue = smem + Cfg::OFF_UE;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  const int t = threadIdx.x;
+  if (t == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t phase = 0;
+  for (int64_t e = g.e0 + blockIdx.x; e < g.e1; e += gridDim.x) {
+    if (t == 0) tma_load_1d(sdN, g.dNdX + e * (int64_t)(NQ * TD), (uint32_t)(NQ * TD * sizeof(double)), bar);
+    if (t < TD) sue[t] = g.u[g.vdofs[e * TD + t]];
+    if (t < NQ) swd[t] = g.wdetJ[e * NQ + t];
+    __syncthreads();
+    mbar_wait(bar, phase);
+    phase ^= 1u;
+    // ---- F: MultAtB(element_x_mat_, dN_dX, F_) + AddDiagonal(1.0) (integrator_utils.cpp:33-40)
+    // one task = one dN row (q, j) and the DIM entries F(:, j) it feeds: a dN value is read once for DIM products
+    for (int task = t; task < NQ * DIM; task += NT) {
+      const int q = task / DIM, j = task - q * DIM;
+      const double* dN = sdN + q * TD + j * ND;
+      double d[DIM];
+#pragma unroll
+      for (int i = 0; i < DIM; i++) d[i] = 0.0;
+#pragma unroll
+      for (int k = 0; k < ND; k++) {
+        const double v = dN[k];
+#pragma unroll
+        for (int i = 0; i < DIM; i++) d[i] += sue[i * ND + k] * v;
+      }
+#pragma unroll
+      for (int i = 0; i < DIM; i++) sFb[q * DD + i + DIM * j] = (i == j) ? d[i] + 1.0 : d[i];
+    }
+    __syncthreads();
+    // ---- stress: b = (w detJ) P, bjk = a * P(j,k) (densemat.cpp:3008)
+    if (t < NQ) {
+      double F[DD], P[DD];
+#pragma unroll
+      for (int n = 0; n < DD; n++) F[n] = sFb[t * DD + n];
+      material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + t) * NS : nullptr, P);
+      const double aq = swd[t];
+#pragma unroll
+      for (int n = 0; n < DD; n++) sbq[t * DD + n] = aq * P[n];
+    }
+    __syncthreads();
+    // ---- R(i, j) = sum_q sum_k dN(q; i, k) * b(q; j, k)
+    if (t < TD) {
+      const int i = t % ND, j = t / ND;
+      double r = 0.0;
+#pragma unroll 4
+      for (int q = 0; q < NQ; q++) {
+#pragma unroll
+        for (int k = 0; k < DIM; k++) r += sdN[q * TD + i + k * ND] * sbq[q * DD + j + DIM * k];
+      }
+      g.Re[e * TD + t] = r;
+    }
+    __syncthreads();  // smem is reused by the next element's copy
+  }
+}
+
+template <int DIM, int ND, int NQ, int MAT>
+static int launch_element_res(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
+  using Cfg = ElemResCfg<DIM, ND, NQ>;
+  auto kern = element_res_kernel<DIM, ND, NQ, MAT>;
+  MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+  int per_sm = 0;
+  MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::NT, Cfg::SMEM_BYTES));
+  if (per_sm < 1) per_sm = 1;
+  int64_t grid = (int64_t)c->sm_count * per_sm;  // persistent: a whole number of resident CTAs per SM
+  if (grid > a.e1 - a.e0) grid = a.e1 - a.e0;
+  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, st>>>(a);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // launchers
 // ---------------------------------------------------------------------------------------------
 template <int DIM, int ND, int NQ, int MAT, bool GRAD, int MINB>
@@ -909,6 +1020,16 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
       case MAT_J2: return launch_element_fd_split<3, 64, 125, MAT_J2, 4>(c, a, st);
       case MAT_J2SIMO: return launch_element_fd_split<3, 64, 125, MAT_J2SIMO, 4>(c, a, st);
       case MAT_J2LOG: return launch_element_fd_split<3, 64, 125, MAT_J2LOG, 4>(c, a, st);
+    }
+  }
+  if (!GRAD && dim == 3 && nd == 27 && nq == 64 && c->elem_variant != 1) {
+    switch (c->mat_kind) {
+      case MAT_NEOHOOKEAN: return launch_element_res<3, 27, 64, MAT_NEOHOOKEAN>(c, a, st);
+      case MAT_STVK: return launch_element_res<3, 27, 64, MAT_STVK>(c, a, st);
+      case MAT_J2LINEAR: return launch_element_res<3, 27, 64, MAT_J2LINEAR>(c, a, st);
+      case MAT_J2: return launch_element_res<3, 27, 64, MAT_J2>(c, a, st);
+      case MAT_J2SIMO: return launch_element_res<3, 27, 64, MAT_J2SIMO>(c, a, st);
+      case MAT_J2LOG: return launch_element_res<3, 27, 64, MAT_J2LOG>(c, a, st);
     }
   }
   if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a, st);
