@@ -158,6 +158,8 @@ def sweeps_main():
             writer(mesh)
             W = O.run_ref_sweeps(mesh, elevate, refine, "neohookean", os.path.join(tmp, "s"), fac0, fac1)
             W["base"] = np.array(base)
+            # the linear system of that Newton iteration, solved by the reference's iterative option (harness 'gmres')
+            W["gmres_x"], W["gmres_info"] = O.run_ref_gmres(W["I"], W["J"], W["Jac"], W["y"], os.path.join(tmp, "g"))
             np.savez_compressed(os.path.join(OUT, name + ".npz"), **W)
             print(name, W["y"].size, W["Jac"].size, W["ess"].size)
 

@@ -582,3 +582,26 @@ def run_ref_steps(mesh, elevate, refine, material, force, dt, nsteps, outdir, bi
                            repr(dt), str(nsteps), outdir], stdout=subprocess.DEVNULL)
     its = np.fromfile(os.path.join(outdir, "newton_its.i32"), np.int32)
     return np.fromfile(os.path.join(outdir, "x_hist.f64")).reshape(nsteps, -1), its
+
+
+def gmres_jacobi(I, J, A, b, rel_tol=1e-8, abs_tol=1e-12, max_iter=300, m=50):
+    """mfem::GMRESSolver + DSmoother as the reference configures them (py_nonlinear_solid.cpp:330-339) -> (x, iterations,
+    final norm, converged)."""
+    n = len(I) - 1
+    x = np.zeros(n)
+    it, fn = C.c_int(), C.c_double()
+    lib().orc_gmres_jacobi.restype = C.c_int
+    conv = lib().orc_gmres_jacobi(C.c_int64(n), _p(I, C.c_int32), _p(J, C.c_int32), _p(A, C.c_double), _p(b, C.c_double),
+                                  C.c_double(rel_tol), C.c_double(abs_tol), C.c_int(max_iter), C.c_int(m), _p(x, C.c_double),
+                                  C.byref(it), C.byref(fn))
+    return x, it.value, fn.value, bool(conv)
+
+
+def run_ref_gmres(I, J, A, b, workdir):
+    """Harness mode 'gmres': the compiled reference's GMRESSolver + DSmoother on the given CSR system."""
+    os.makedirs(workdir, exist_ok=True)
+    for name, arr, t in (("I.i32", I, np.int32), ("J.i32", J, np.int32), ("A.f64", A, np.float64), ("b.f64", b, np.float64)):
+        np.ascontiguousarray(arr, t).tofile(os.path.join(workdir, name))
+    subprocess.check_call([REF_BIN, "gmres", workdir, str(len(I) - 1), str(len(J)), "-", "0", workdir, "-"],
+                          stdout=subprocess.DEVNULL)
+    return np.fromfile(os.path.join(workdir, "x.f64")), np.fromfile(os.path.join(workdir, "info.f64"))

@@ -320,6 +320,40 @@ int main(int argc, char** argv) {
     return 0;
   }
 
+  if (mode == "gmres") {
+    // gmres <dir with I.i32, J.i32, A.f64, b.f64> <n> <nnz> - - <out dir> -: the reference's iterative linear solver
+    // (py_nonlinear_solid.cpp:330-339): GMRESSolver + DSmoother, rel 1e-8, abs 1e-12, 300 iterations -> x.f64, info.f64
+    const int n = elevate, nnz = refine;
+    const std::string in = mesh_file, out = argv[7];
+    std::vector<int> I(n + 1), J(nnz);
+    std::vector<double> A(nnz), b(n);
+    auto rd = [&](const char* name, void* p, size_t bytes) {
+      std::ifstream f(in + "/" + name, std::ios::binary);
+      f.read(reinterpret_cast<char*>(p), bytes);
+      if (!f) { std::fprintf(stderr, "gmres: short read of %s\n", name); std::exit(2); }
+    };
+    rd("I.i32", I.data(), sizeof(int) * (n + 1));
+    rd("J.i32", J.data(), sizeof(int) * nnz);
+    rd("A.f64", A.data(), sizeof(double) * nnz);
+    rd("b.f64", b.data(), sizeof(double) * n);
+    mfem::SparseMatrix M(I.data(), J.data(), A.data(), n, n, false, false, true);
+    mfem::GMRESSolver lin;
+    mfem::DSmoother prec;
+    lin.SetRelTol(1e-8);
+    lin.SetAbsTol(1e-12);
+    lin.SetMaxIter(300);
+    lin.SetPrintLevel(-1);
+    lin.SetPreconditioner(prec);
+    lin.SetOperator(M);
+    mfem::Vector bv(b.data(), n), x(n);
+    x = 0.0;
+    lin.Mult(bv, x);
+    double info[3] = {(double)lin.GetNumIterations(), lin.GetFinalNorm(), lin.GetConverged() ? 1.0 : 0.0};
+    dump(out, "x.f64", x.GetData(), (size_t)n);
+    dump(out, "info.f64", info, 3);
+    return 0;
+  }
+
   if (mode == "dump") {
     const double gf = std::atof(argv[7]);
     const char* u_file = argv[8];
