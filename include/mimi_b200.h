@@ -242,6 +242,17 @@ int mb2_set_rhs(mb2_ctx* ctx, const double* rhs);                /* NV, NULL = n
 int mb2_set_essential_dofs(mb2_ctx* ctx, const int32_t* tdofs, int64_t n);
 int mb2_newton_residual_and_grad_device(mb2_ctx* ctx, const double* x, const double* v, const double* a, double fac0,
                                         double fac1);
+/* the reference's iterative linear solver on the resident arrays, J c = y with J = the
+ * resident CSR values and y = the resident residual (what mb2_newton_residual_and_grad_device leaves behind):
+ * mfem::GMRESSolver (restart kdim; the reference uses 50, rel 1e-8, abs 1e-12, 300 iterations) left-preconditioned by
+ * mfem::DSmoother, iterative_mode == false (src/mimi/py/py_nonlinear_solid.cpp:330-339,
+ * third_party/mfem/linalg/solvers.cpp:931-1160). The solution stays on the device (mb2_newton_get_solution copies it out).
+ * Floating-point parity: SpMV and the preconditioner keep the reference's expressions; the dot products are
+ * deterministic tree reductions, so iterates agree with the reference to rounding (solution within the solver
+ * tolerance, iteration count within a few), not bitwise. */
+int mb2_newton_solve_gmres_device(mb2_ctx* ctx, double rel_tol, double abs_tol, int max_iter, int kdim, int* iterations,
+                                  double* final_norm, int* converged);
+int mb2_newton_get_solution(mb2_ctx* ctx, double* c_host);
 
 /* ---- multi-GPU: element partition with raw element-matrix exchange ------------------
  * One context per GPU / rank. The rank's connectivity (mb2_set_connectivity) lists its own elements first

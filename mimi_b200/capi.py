@@ -30,7 +30,7 @@ SYMBOLS = [
     "mb2_contact_get_marked_v_dofs", "mb2_contact_get_A_ids_i32", "mb2_add_boundary_residual",
     "mb2_add_boundary_residual_and_grad", "mb2_contact_residual_device", "mb2_contact_residual_and_grad_device",
     "mb2_contact_get_nodal", "mb2_contact_last_scalars", "mb2_contact_gap_norm", "mb2_set_mass", "mb2_set_viscosity",
-    "mb2_set_rhs", "mb2_set_essential_dofs", "mb2_newton_residual_and_grad_device",
+    "mb2_set_rhs", "mb2_set_essential_dofs", "mb2_newton_residual_and_grad_device", "mb2_newton_solve_gmres_device", "mb2_newton_get_solution",
 ]
 
 
@@ -244,6 +244,17 @@ class Context:
                                                               C.c_double(fac1)))
 
     # ---- host-buffer hot path
+    def newton_solve_gmres_device(self, rel_tol=1e-8, abs_tol=1e-12, max_iter=300, kdim=50):
+        it, conv, fn = C.c_int(), C.c_int(), C.c_double()
+        self._ck(self.lib.mb2_newton_solve_gmres_device(self.h, C.c_double(rel_tol), C.c_double(abs_tol), max_iter, kdim,
+                                                        C.byref(it), C.byref(fn), C.byref(conv)))
+        return it.value, fn.value, bool(conv.value)
+
+    def newton_get_solution(self):
+        x = np.empty(self.NV)
+        self._ck(self.lib.mb2_newton_get_solution(self.h, _dp(x)))
+        return x
+
     def add_domain_residual(self, u, r):
         self._ck(self.lib.mb2_add_domain_residual(self.h, _dp(u), _dp(r)))
 

@@ -14,6 +14,8 @@
 //   y -= rhs; y[ess] = 0                      Vector::Add(-1.0, rhs)
 // Every kernel keeps the reference's per-entry expression (row sums sequential in column order), so y and J are
 // bit-identical to the reference's (tests/test_gpu_newton.py against dumps of the compiled reference).
+#include <algorithm>
+#include <cmath>
 #include <vector>
 
 #include "mb2_ctx.h"
@@ -30,6 +32,13 @@ struct NewtonState {
   double* d_x = nullptr;     // NV
   int32_t* d_ess = nullptr;  // essential tdofs
   int64_t n_ess = 0;
+  // linear solve: GMRES(m) + Jacobi on the resident Jacobian
+  int64_t* d_diag = nullptr;  // position of the diagonal entry of every row
+  double* d_c = nullptr;      // solution of the last solve
+  double* d_w = nullptr;      // NV work
+  double* d_t = nullptr;      // NV work
+  double* d_part = nullptr;   // block partials of the dot products
+  std::vector<double*> d_vk;  // Krylov basis, m + 1 vectors
 };
 
 static NewtonState* NS(mb2_ctx* c) { return static_cast<NewtonState*>(c->newton); }
@@ -38,7 +47,9 @@ void free_newton(mb2_ctx* c) {
   NewtonState* S = NS(c);
   if (!S) return;
   for (void* p : {(void*)S->d_M, (void*)S->d_S, (void*)S->d_rhs, (void*)S->d_a, (void*)S->d_tv, (void*)S->d_v, (void*)S->d_x,
-                  (void*)S->d_ess})
+                  (void*)S->d_ess, (void*)S->d_diag, (void*)S->d_c, (void*)S->d_w, (void*)S->d_t, (void*)S->d_part})
+    if (p) cudaFree(p);
+  for (double* p : S->d_vk)
     if (p) cudaFree(p);
   delete S;
   c->newton = nullptr;
@@ -146,6 +157,206 @@ int newton_residual_and_grad(mb2_ctx* c, const double* x, const double* v, const
   return MB2_OK;
 }
 
+
+// ---- the reference's iterative linear solver on the resident CSR --------------------------------
+// mfem::GMRESSolver left-preconditioned by mfem::DSmoother (PyNonlinearSolid::Setup with use_iterative_solver,
+// src/mimi/py/py_nonlinear_solid.cpp:330-339; third_party/mfem/linalg/solvers.cpp:931-1160, sparsemat.cpp:2683-2720):
+// modified Gram-Schmidt, Givens rotations, restart m, iterative_mode == false. SpMV keeps the reference's row sums; the
+// dot products are fixed-shape two-level tree reductions (deterministic, but not the reference's sequential sum), so the
+// iterates agree with the reference to rounding, not bitwise: tolerance parity (tests/test_gpu_newton.py).
+__global__ void k_find_diag(int64_t n, const int64_t* __restrict__ I, const int32_t* __restrict__ J, int64_t* __restrict__ diag,
+                            int* flag) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int64_t lo = I[i], hi = I[i + 1] - 1, pos = -1;
+  while (lo <= hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (J[mid] == i) { pos = mid; break; }
+    if (J[mid] < i) lo = mid + 1; else hi = mid - 1;
+  }
+  diag[i] = pos;
+  if (pos < 0) *flag = 4;  // "Diagonal not found in SparseMatrix::DiagScale"
+}
+// x[i] = 1.0 * b[i] / A[diag(i)]   (SparseMatrix::DiagScale, sc = 1)
+__global__ void k_diag_scale(int64_t n, const int64_t* __restrict__ diag, const double* __restrict__ A,
+                             const double* __restrict__ b, double* __restrict__ x) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) x[i] = 1.0 * b[i] / A[diag[i]];
+}
+__global__ void k_scale_to(int64_t n, double a, const double* __restrict__ x, double* __restrict__ y) {  // y = a x
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) y[i] = a * x[i];
+}
+__global__ void k_sub(int64_t n, const double* __restrict__ a, const double* __restrict__ b, double* __restrict__ z) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) z[i] = a[i] - b[i];
+}
+constexpr int DOT_CHUNK = 4096;  // elements per block: thread t sums t, t + 256, ... in order, then a shared-memory tree
+__global__ void __launch_bounds__(256) k_dot_partial(int64_t n, const double* __restrict__ a, const double* __restrict__ b,
+                                                     double* __restrict__ part) {
+  __shared__ double sh[256];
+  const int64_t base = (int64_t)blockIdx.x * DOT_CHUNK;
+  double d = 0.0;
+  for (int k = threadIdx.x; k < DOT_CHUNK; k += 256) {
+    const int64_t i = base + k;
+    if (i < n) d += a[i] * b[i];
+  }
+  sh[threadIdx.x] = d;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) part[blockIdx.x] = sh[0];
+}
+__global__ void __launch_bounds__(256) k_dot_final(int64_t nparts, const double* __restrict__ part, double* __restrict__ out) {
+  __shared__ double sh[256];
+  double d = 0.0;
+  for (int64_t k = threadIdx.x; k < nparts; k += 256) d += part[k];
+  sh[threadIdx.x] = d;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = sh[0];
+}
+
+static int dev_dot(mb2_ctx* c, NewtonState* S, const double* a, const double* b, double* out) {
+  const int64_t n = c->NV, nparts = (n + DOT_CHUNK - 1) / DOT_CHUNK;
+  k_dot_partial<<<(unsigned)nparts, 256, 0, c->stream>>>(n, a, b, S->d_part);
+  k_dot_final<<<1, 256, 0, c->stream>>>(nparts, S->d_part, S->d_part + nparts);
+  MB2_CUDA(cudaMemcpyAsync(out, S->d_part + nparts, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
+}
+
+int newton_solve_gmres(mb2_ctx* c, double rel_tol, double abs_tol, int max_iter, int m, int* final_iter, double* final_norm,
+                       int* converged_out) {
+  NewtonState* S = NS(c);
+  const int64_t n = c->NV;
+  cudaStream_t st = c->stream;
+  const int64_t nparts = (n + DOT_CHUNK - 1) / DOT_CHUNK;
+  if (!S->d_diag) {
+    MB2_CUDA(cudaMalloc(&S->d_diag, sizeof(int64_t) * n));
+    k_find_diag<<<nb(n), 256, 0, st>>>(n, c->d_I, c->d_J, S->d_diag, c->d_flag);
+    for (double** p : {&S->d_c, &S->d_w, &S->d_t}) MB2_CUDA(cudaMalloc(p, sizeof(double) * n));
+    MB2_CUDA(cudaMalloc(&S->d_part, sizeof(double) * (nparts + 1)));
+  }
+  if ((int)S->d_vk.size() < m + 1) S->d_vk.resize(m + 1, nullptr);
+  const int ldh = m + 1;
+  std::vector<double> H((size_t)ldh * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0), y(m + 1, 0.0);
+  double* r = S->d_t;   // preconditioned residual
+  double* w = S->d_w;
+  double* x = S->d_c;
+  const double* b = c->d_r;
+  const double* A = c->d_A;
+  auto update = [&](int k) {  // Update(x, k, H, s, v): back substitution on the host, x += sum_j y_j v_j
+    for (int i = 0; i <= m; i++) y[i] = s[i];
+    for (int i = k; i >= 0; i--) {
+      y[i] /= H[i + (size_t)i * ldh];
+      for (int j = i - 1; j >= 0; j--) y[j] -= H[j + (size_t)i * ldh] * y[i];
+    }
+    for (int j = 0; j <= k; j++) k_axpy<<<nb(n), 256, 0, st>>>(n, y[j], S->d_vk[j], x);
+  };
+  int rc, i = 0, j = 0, converged = 0;
+  MB2_CUDA(cudaMemsetAsync(x, 0, sizeof(double) * n, st));
+  k_diag_scale<<<nb(n), 256, 0, st>>>(n, S->d_diag, A, b, r);
+  double dd = 0.0;
+  if ((rc = dev_dot(c, S, r, r, &dd))) return rc;
+  double beta = std::sqrt(dd);
+  if (!std::isfinite(beta)) { c->err = "GMRES: beta is not finite"; return MB2_ERR_NUMERIC; }
+  *final_norm = std::max(rel_tol * beta, abs_tol);
+  if (beta <= *final_norm) {
+    *final_norm = beta;
+    *final_iter = 0;
+    converged = 1;
+    goto finish;
+  }
+  for (j = 1; j <= max_iter;) {
+    if (!S->d_vk[0]) MB2_CUDA(cudaMalloc(&S->d_vk[0], sizeof(double) * n));
+    k_scale_to<<<nb(n), 256, 0, st>>>(n, 1.0 / beta, r, S->d_vk[0]);
+    std::fill(s.begin(), s.end(), 0.0);
+    s[0] = beta;
+    for (i = 0; i < m && j <= max_iter; i++, j++) {
+      k_spmv_rows<<<nb(n), 256, 0, st>>>(n, c->d_I, c->d_J, A, S->d_vk[i], r, 0);
+      k_diag_scale<<<nb(n), 256, 0, st>>>(n, S->d_diag, A, r, w);
+      for (int k = 0; k <= i; k++) {
+        double h = 0.0;
+        if ((rc = dev_dot(c, S, w, S->d_vk[k], &h))) return rc;
+        H[k + (size_t)i * ldh] = h;
+        k_axpy<<<nb(n), 256, 0, st>>>(n, -h, S->d_vk[k], w);
+      }
+      if ((rc = dev_dot(c, S, w, w, &dd))) return rc;
+      const double hn = std::sqrt(dd);
+      if (!std::isfinite(hn)) { c->err = "GMRES: Norm(w) is not finite"; return MB2_ERR_NUMERIC; }
+      H[i + 1 + (size_t)i * ldh] = hn;
+      if (!S->d_vk[i + 1]) MB2_CUDA(cudaMalloc(&S->d_vk[i + 1], sizeof(double) * n));
+      k_scale_to<<<nb(n), 256, 0, st>>>(n, 1.0 / hn, w, S->d_vk[i + 1]);
+      for (int k = 0; k < i; k++) {  // ApplyPlaneRotation
+        double& dx = H[k + (size_t)i * ldh];
+        double& dy = H[k + 1 + (size_t)i * ldh];
+        const double t = cs[k] * dx + sn[k] * dy;
+        dy = -sn[k] * dx + cs[k] * dy;
+        dx = t;
+      }
+      {  // GeneratePlaneRotation
+        const double dx = H[i + (size_t)i * ldh], dy = H[i + 1 + (size_t)i * ldh];
+        if (dy == 0.0) {
+          cs[i] = 1.0;
+          sn[i] = 0.0;
+        } else if (std::fabs(dy) > std::fabs(dx)) {
+          const double t = dx / dy;
+          sn[i] = 1.0 / std::sqrt(1.0 + t * t);
+          cs[i] = t * sn[i];
+        } else {
+          const double t = dy / dx;
+          cs[i] = 1.0 / std::sqrt(1.0 + t * t);
+          sn[i] = t * cs[i];
+        }
+      }
+      {
+        double& dx = H[i + (size_t)i * ldh];
+        double& dy = H[i + 1 + (size_t)i * ldh];
+        double t = cs[i] * dx + sn[i] * dy;
+        dy = -sn[i] * dx + cs[i] * dy;
+        dx = t;
+        t = cs[i] * s[i] + sn[i] * s[i + 1];
+        s[i + 1] = -sn[i] * s[i] + cs[i] * s[i + 1];
+        s[i] = t;
+      }
+      const double resid = std::fabs(s[i + 1]);
+      if (!std::isfinite(resid)) { c->err = "GMRES: resid is not finite"; return MB2_ERR_NUMERIC; }
+      if (resid <= *final_norm) {
+        update(i);
+        *final_norm = resid;
+        *final_iter = j;
+        converged = 1;
+        goto finish;
+      }
+    }
+    update(i - 1);
+    k_spmv_rows<<<nb(n), 256, 0, st>>>(n, c->d_I, c->d_J, A, x, r, 0);
+    k_sub<<<nb(n), 256, 0, st>>>(n, b, r, w);
+    k_diag_scale<<<nb(n), 256, 0, st>>>(n, S->d_diag, A, w, r);
+    if ((rc = dev_dot(c, S, r, r, &dd))) return rc;
+    beta = std::sqrt(dd);
+    if (beta <= *final_norm) {
+      *final_norm = beta;
+      *final_iter = j;
+      converged = 1;
+      goto finish;
+    }
+  }
+  *final_norm = beta;
+  *final_iter = max_iter;
+finish:
+  MB2_CUDA(cudaGetLastError());
+  MB2_CUDA(cudaStreamSynchronize(st));
+  *converged_out = converged;
+  return MB2_OK;
+}
+
 static int ensure(mb2_ctx* c) {
   if (!c->have_pattern) { c->err = "call mb2_build_pattern first"; return MB2_ERR_ARG; }
   if (!c->newton) {
@@ -229,6 +440,36 @@ int mb2_newton_residual_and_grad_device(mb2_ctx* c, const double* x, const doubl
   if (!c->d_dNdX || c->mat_kind < 0) { c->err = "tables / material missing"; return MB2_ERR_ARG; }
   MB2_CUDA(cudaSetDevice(c->device));
   return mb2::newton_residual_and_grad(c, x, v, a, fac0, fac1);
+}
+
+int mb2_newton_solve_gmres_device(mb2_ctx* c, double rel_tol, double abs_tol, int max_iter, int kdim, int* iterations,
+                                  double* final_norm, int* converged) {
+  if (!c) return MB2_ERR_ARG;
+  int rc = mb2::ensure(c);
+  if (rc) return rc;
+  if (!iterations || !final_norm || !converged) { c->err = "null output"; return MB2_ERR_ARG; }
+  if (max_iter < 1 || kdim < 1 || kdim > 1000) { c->err = "GMRES: max_iter >= 1 and 1 <= kdim <= 1000"; return MB2_ERR_ARG; }
+  MB2_CUDA(cudaSetDevice(c->device));
+  rc = mb2::newton_solve_gmres(c, rel_tol, abs_tol, max_iter, kdim, iterations, final_norm, converged);
+  if (rc) return rc;
+  int flag = 0;
+  MB2_CUDA(cudaMemcpy(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost));
+  if (flag == 4) {
+    int zero = 0;
+    MB2_CUDA(cudaMemcpy(c->d_flag, &zero, sizeof(int), cudaMemcpyHostToDevice));
+    c->err = "Diagonal not found in SparseMatrix::DiagScale";
+    return MB2_ERR_NUMERIC;
+  }
+  return MB2_OK;
+}
+
+int mb2_newton_get_solution(mb2_ctx* c, double* out) {
+  if (!c) return MB2_ERR_ARG;
+  NewtonState* S = static_cast<NewtonState*>(c->newton);
+  if (!S || !S->d_c || !out) { c->err = "no linear solve has run"; return MB2_ERR_ARG; }
+  MB2_CUDA(cudaMemcpyAsync(out, S->d_c, sizeof(double) * c->NV, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  return MB2_OK;
 }
 
 }  // extern "C"

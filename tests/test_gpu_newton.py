@@ -58,3 +58,32 @@ def test_newton_sweeps_with_contact_vs_oracle(ctx_factory):
     y_o, J_o, _ = O.newton_residual_and_grad(3, 27, 64, O.mat(0), D, W, contact=contact)
     assert seen["active"] > 0
     assert np.array_equal(ctx.get_r(), y_o) and np.array_equal(ctx.get_A(), J_o)
+
+
+@pytest.mark.parametrize("name", SWEEP_CASES)
+def test_newton_linear_solve_gmres(ctx_factory, name):
+    """after the sweeps, J c = y is solved on the resident arrays by the reference's iterative option
+    (GMRES(50) + Jacobi, rel 1e-8, abs 1e-12, 300 iterations). Golden: the compiled reference's GMRESSolver on the same
+    system (fixture keys gmres_x / gmres_info). Tolerance parity, stated: the device's dot products are tree reductions,
+    the reference's are sequential sums, so the Krylov iterates differ in the last bits; stated bound: solution within
+    1e-10 of the reference's (observed 1e-14), iteration count within 1 (observed equal), true residual within tolerance."""
+    D, W = load_sweeps_golden(name)
+    ctx = setup_ctx(ctx_factory(), D, "neohookean")
+    ctx.set_mass(W["mass"]); ctx.set_viscosity(W["visc"]); ctx.set_rhs(W["rhs"]); ctx.set_essential_dofs(W["ess"])
+    ctx.newton_residual_and_grad_device(W["x"], W["v"], W["a"], W["fac0"], W["fac1"])
+    it, fn, conv = ctx.newton_solve_gmres_device()
+    c = ctx.newton_get_solution()
+    ref_it, ref_fn = int(W["gmres_info"][0]), float(W["gmres_info"][1])
+    print("\n[gmres %s] device %d iterations (reference %d), final norm %.3e (%.3e), max |c - c_ref| / max |c_ref| = %.2e" % (
+        name, it, ref_it, fn, ref_fn, np.abs(c - W["gmres_x"]).max() / np.abs(W["gmres_x"]).max()))
+    assert conv and abs(it - ref_it) <= 1
+    assert np.abs(c - W["gmres_x"]).max() <= 1e-10 * np.abs(W["gmres_x"]).max()
+    r = O.spmv(W["I"], W["J"], W["Jac"], c) - W["y"]
+    assert np.linalg.norm(r) <= 1e-6 * np.linalg.norm(W["y"])
+    assert np.array_equal(ctx.get_r(), W["y"]) and np.array_equal(ctx.get_A(), W["Jac"])      # the solve leaves y and J alone
+    # a second solve reproduces the first bit for bit (deterministic reductions)
+    it2, fn2, _ = ctx.newton_solve_gmres_device()
+    assert it2 == it and fn2 == fn and np.array_equal(ctx.newton_get_solution(), c)
+    # restart path and non-convergence are reported like the reference does (converged = false, final_iter = max_iter)
+    it3, fn3, conv3 = ctx.newton_solve_gmres_device(max_iter=5)
+    assert not conv3 and it3 == 5
