@@ -242,6 +242,12 @@ int mb2_set_rhs(mb2_ctx* ctx, const double* rhs);                /* NV, NULL = n
 int mb2_set_essential_dofs(mb2_ctx* ctx, const int32_t* tdofs, int64_t n);
 int mb2_newton_residual_and_grad_device(mb2_ctx* ctx, const double* x, const double* v, const double* a, double fac0,
                                         double fac1);
+/* The residual-only evaluation of the line search (mimi::operators::NonlinearSolid::Mult(a, y),
+ * src/mimi/operators/nonlinear_solid.cpp:172-205; two per Newton iteration, src/mimi/solvers/newton.cpp:138-157) on
+ * the resident arrays, and its l2 norm (NULL = not wanted): y bit-identical to the reference's, the norm a
+ * deterministic tree reduction. */
+int mb2_newton_residual_device(mb2_ctx* ctx, const double* x, const double* v, const double* a, double fac0, double fac1,
+                               double* norm_out);
 /* the reference's iterative linear solver on the resident arrays, J c = y with J = the
  * resident CSR values and y = the resident residual (what mb2_newton_residual_and_grad_device leaves behind):
  * mfem::GMRESSolver (restart kdim; the reference uses 50, rel 1e-8, abs 1e-12, 300 iterations) left-preconditioned by

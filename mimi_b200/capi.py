@@ -30,7 +30,7 @@ SYMBOLS = [
     "mb2_contact_get_marked_v_dofs", "mb2_contact_get_A_ids_i32", "mb2_add_boundary_residual",
     "mb2_add_boundary_residual_and_grad", "mb2_contact_residual_device", "mb2_contact_residual_and_grad_device",
     "mb2_contact_get_nodal", "mb2_contact_last_scalars", "mb2_contact_gap_norm", "mb2_set_mass", "mb2_set_viscosity",
-    "mb2_set_rhs", "mb2_set_essential_dofs", "mb2_newton_residual_and_grad_device", "mb2_newton_solve_gmres_device", "mb2_newton_get_solution",
+    "mb2_set_rhs", "mb2_set_essential_dofs", "mb2_newton_residual_and_grad_device", "mb2_newton_residual_device", "mb2_newton_solve_gmres_device", "mb2_newton_get_solution",
 ]
 
 
@@ -244,6 +244,12 @@ class Context:
                                                               C.c_double(fac1)))
 
     # ---- host-buffer hot path
+    def newton_residual_device(self, x, v, a, fac0, fac1, want_norm=True):
+        nrm = C.c_double()
+        self._ck(self.lib.mb2_newton_residual_device(self.h, _dp(x), _dp(v), _dp(a), C.c_double(fac0), C.c_double(fac1),
+                                                     C.byref(nrm) if want_norm else None))
+        return nrm.value
+
     def newton_solve_gmres_device(self, rel_tol=1e-8, abs_tol=1e-12, max_iter=300, kdim=50):
         it, conv, fn = C.c_int(), C.c_int(), C.c_double()
         self._ck(self.lib.mb2_newton_solve_gmres_device(self.h, C.c_double(rel_tol), C.c_double(abs_tol), max_iter, kdim,

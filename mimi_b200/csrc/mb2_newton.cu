@@ -241,8 +241,8 @@ int newton_solve_gmres(mb2_ctx* c, double rel_tol, double abs_tol, int max_iter,
     MB2_CUDA(cudaMalloc(&S->d_diag, sizeof(int64_t) * n));
     k_find_diag<<<nb(n), 256, 0, st>>>(n, c->d_I, c->d_J, S->d_diag, c->d_flag);
     for (double** p : {&S->d_c, &S->d_w, &S->d_t}) MB2_CUDA(cudaMalloc(p, sizeof(double) * n));
-    MB2_CUDA(cudaMalloc(&S->d_part, sizeof(double) * (nparts + 1)));
   }
+  if (!S->d_part) MB2_CUDA(cudaMalloc(&S->d_part, sizeof(double) * (nparts + 1)));
   if ((int)S->d_vk.size() < m + 1) S->d_vk.resize(m + 1, nullptr);
   const int ldh = m + 1;
   std::vector<double> H((size_t)ldh * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0), y(m + 1, 0.0);
@@ -354,6 +354,50 @@ finish:
   MB2_CUDA(cudaGetLastError());
   MB2_CUDA(cudaStreamSynchronize(st));
   *converged_out = converged;
+  return MB2_OK;
+}
+
+// NonlinearSolid::Mult(a, y) (src/mimi/operators/nonlinear_solid.cpp:172-205): the residual-only evaluation the line
+// search of LineSearchNewton makes twice per iteration (solvers/newton.cpp:138-157), and its norm:
+//   temp_x = x + fac0 a;  y = M a;  stiffness->AddMult(temp_x, y) (+ y[ess] = 0, forms/nonlinear.hpp:53-82);
+//   y += S (v + fac1 a);  contact->AddMult(temp_x, y) (+ y[ess] = 0);  y -= rhs;  y[dirichlet] = 0;  ||y||_2
+// y bit-identical to the reference; the norm is a deterministic tree reduction (the reference: sequential sum).
+int newton_residual(mb2_ctx* c, const double* x, const double* v, const double* a, double fac0, double fac1,
+                    double* norm_out) {
+  NewtonState* S = NS(c);
+  const int64_t NV = c->NV;
+  cudaStream_t st = c->stream;
+  MB2_CUDA(cudaMemcpyAsync(S->d_x, x, sizeof(double) * NV, cudaMemcpyHostToDevice, st));
+  MB2_CUDA(cudaMemcpyAsync(S->d_a, a, sizeof(double) * NV, cudaMemcpyHostToDevice, st));
+  k_add_scaled<<<nb(NV), 256, 0, st>>>(NV, S->d_x, fac0, S->d_a, c->d_u);
+  k_spmv_rows<<<nb(NV), 256, 0, st>>>(NV, c->d_I, c->d_J, S->d_M, S->d_a, c->d_r, 0);
+  MB2_CUDA(cudaGetLastError());
+  int rc = launch_residual(c);
+  if (rc) return rc;
+  int launches = c->last_launches + 2;
+  if (S->n_ess) k_zero_list<<<nb(S->n_ess), 256, 0, st>>>(S->n_ess, S->d_ess, c->d_r);
+  if (S->d_S) {
+    if (!v) { c->err = "viscosity is set: v must be given"; return MB2_ERR_ARG; }
+    MB2_CUDA(cudaMemcpyAsync(S->d_v, v, sizeof(double) * NV, cudaMemcpyHostToDevice, st));
+    k_add_scaled<<<nb(NV), 256, 0, st>>>(NV, S->d_v, fac1, S->d_a, S->d_tv);
+    k_spmv_rows<<<nb(NV), 256, 0, st>>>(NV, c->d_I, c->d_J, S->d_S, S->d_tv, c->d_r, 1);
+    launches += 2;
+  }
+  if (contact_active(c)) {
+    if ((rc = contact_assemble(c, false, 0.0))) return rc;
+    launches += c->last_launches;
+    if (S->n_ess) k_zero_list<<<nb(S->n_ess), 256, 0, st>>>(S->n_ess, S->d_ess, c->d_r);
+  }
+  if (S->d_rhs) k_axpy<<<nb(NV), 256, 0, st>>>(NV, -1.0, S->d_rhs, c->d_r);
+  if (S->n_ess) k_zero_list<<<nb(S->n_ess), 256, 0, st>>>(S->n_ess, S->d_ess, c->d_r);
+  MB2_CUDA(cudaGetLastError());
+  c->last_launches = launches + 3;
+  if (norm_out) {
+    if (!S->d_part) MB2_CUDA(cudaMalloc(&S->d_part, sizeof(double) * ((NV + DOT_CHUNK - 1) / DOT_CHUNK + 1)));
+    double dd = 0.0;
+    if ((rc = dev_dot(c, S, c->d_r, c->d_r, &dd))) return rc;
+    *norm_out = std::sqrt(dd);
+  }
   return MB2_OK;
 }
 
@@ -470,6 +514,17 @@ int mb2_newton_get_solution(mb2_ctx* c, double* out) {
   MB2_CUDA(cudaMemcpyAsync(out, S->d_c, sizeof(double) * c->NV, cudaMemcpyDeviceToHost, c->stream));
   MB2_CUDA(cudaStreamSynchronize(c->stream));
   return MB2_OK;
+}
+
+int mb2_newton_residual_device(mb2_ctx* c, const double* x, const double* v, const double* a, double fac0, double fac1,
+                               double* norm_out) {
+  if (!c) return MB2_ERR_ARG;
+  NewtonState* S = static_cast<NewtonState*>(c->newton);
+  if (!S || !S->d_M) { c->err = "call mb2_set_mass first"; return MB2_ERR_ARG; }
+  if (!x || !a) { c->err = "null vector"; return MB2_ERR_ARG; }
+  if (!c->d_dNdX || c->mat_kind < 0) { c->err = "tables / material missing"; return MB2_ERR_ARG; }
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::newton_residual(c, x, v, a, fac0, fac1, norm_out);
 }
 
 }  // extern "C"

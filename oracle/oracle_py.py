@@ -548,6 +548,25 @@ def newton_residual_and_grad(dim, nd, nq, m, D, W, contact=None):
     return y, Jm, tx
 
 
+def newton_residual(dim, nd, nq, m, D, W, contact=None):
+    """NonlinearSolid::Mult(a, y) (operators/nonlinear_solid.cpp:172-205), the line search's residual-only evaluation,
+    restated on the oracle's pieces (same W as newton_residual_and_grad)."""
+    fac0, fac1 = W["fac0"], W["fac1"]
+    tx = np.ascontiguousarray(W["x"] + fac0 * W["a"])
+    y = spmv(W["I"], W["J"], W["mass"], W["a"])
+    y = y + assemble_residual(dim, nd, nq, m, D["v_dofs"], D["dN_dX"], D["w"], D["detJ"], tx)
+    y[W["ess"]] = 0.0
+    if W.get("visc") is not None:
+        spmv(W["I"], W["J"], W["visc"], np.ascontiguousarray(W["v"] + fac1 * W["a"]), y)
+    if contact is not None:
+        contact(tx, y)
+        y[W["ess"]] = 0.0
+    if W.get("rhs") is not None:
+        y += -1.0 * W["rhs"]
+    y[W["ess"]] = 0.0
+    return y
+
+
 def run_ref_sweeps(mesh, elevate, refine, material, outdir, fac0, fac1, nthreads=1):
     os.makedirs(outdir, exist_ok=True)
     cmd = [REF_BIN, "sweeps", mesh, str(elevate), str(refine), material, str(nthreads), repr(fac0), repr(fac1), outdir]

@@ -86,6 +86,9 @@ class Beam:
         y[self.ess] = 0.0
         return y, Jd
 
+    def _solve(self, Jd, r):      # the linear solver of the Newton step (UMFPACK in the reference's test)
+        return np.linalg.solve(Jd, r)
+
     # LineSearchNewton::Mult with iterative_mode == false (solvers/newton.cpp:10-218)
     def _newton(self, xa, fac0):
         a = np.zeros(self.NV)
@@ -104,7 +107,7 @@ class Beam:
             if not any(improved):
                 a = best_a
                 break
-            c = np.linalg.solve(Jd, r)
+            c = self._solve(Jd, r)
             q1 = norm
             r3 = self._residual(xa, fac0, a - c)
             q3 = np.sqrt(r3 @ r3)
@@ -156,3 +159,32 @@ class Beam:
         self.a = self.a * prev + aa / f5
         self.be.post_time_advance(np.ascontiguousarray(self.x))
         return self.x
+
+
+class DeviceNewtonBeam(Beam):
+    """The same time loop with every O(N) / O(nnz) operation of the Newton iteration on the GPU (SURVEY 8(f) ranks 1, 2
+    and the line-search part of 4): mb2_newton_residual_and_grad_device (operator composition + elimination),
+    mb2_newton_solve_gmres_device (the reference's GMRES + Jacobi option instead of UMFPACK) and
+    mb2_newton_residual_device (line-search residuals). Only the 50-entry iterate travels."""
+
+    def __init__(self, D, backend, ctx, *args, **kw):
+        super().__init__(D, backend, *args, **kw)
+        self.ctx = ctx
+        ctx.set_mass(self.mass)
+        ctx.set_rhs(self.rhs)
+        ctx.set_essential_dofs(self.ess)
+        self.gmres_iterations = []
+
+    def _residual(self, xa, fac0, a):
+        self.ctx.newton_residual_device(np.ascontiguousarray(xa), None, np.ascontiguousarray(a), fac0, 0.0, want_norm=False)
+        return self.ctx.get_r()
+
+    def _residual_and_grad(self, xa, fac0, a):
+        self.ctx.newton_residual_and_grad_device(np.ascontiguousarray(xa), None, np.ascontiguousarray(a), fac0, 0.0)
+        return self.ctx.get_r(), None
+
+    def _solve(self, Jd, r):      # J and y are resident: nothing is uploaded
+        it, fn, conv = self.ctx.newton_solve_gmres_device()
+        assert conv
+        self.gmres_iterations.append(it)
+        return self.ctx.newton_get_solution()

@@ -124,3 +124,24 @@ def test_device_replays_reference_histories(ctx_factory, case):
     ob, _ = replay(case, OracleBackend)
     assert beam.newton_iterations == ob.newton_iterations      # identical Newton iteration counts (north_star)
     assert np.allclose(beam.x, ob.x, rtol=1e-9, atol=1e-12)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", CASES)
+def test_device_newton_loop_replays_reference_histories(ctx_factory, case):
+    """The whole Newton iteration on the device (tests/beam_driver.py: DeviceNewtonBeam): operator composition and
+    elimination, GMRES(50) + Jacobi in place of UMFPACK, line-search residuals; ten generalized-alpha steps against the
+    reference's committed vectors with the reference's own assertion."""
+    from tests.beam_driver import DeviceNewtonBeam
+    D = load_golden("balken_p3_n2")
+    force, dt = SETUP[case]
+    ctx = ctx_factory()
+    beam = DeviceNewtonBeam(D, DeviceBackend(D, case, ctx), ctx, {1: force}, dt)
+    ref = histories()[case]
+    worst = 0.0
+    for i in range(10):
+        u = beam.step()
+        worst = max(worst, float(np.max(np.abs(u - ref[i]) / (1e-8 + 1e-5 * np.abs(ref[i])))))
+        assert np.allclose(u, ref[i]), (case, i)
+    print("\n[%s] device Newton loop: worst |u - ref| / (atol + rtol |ref|) = %.2e, Newton iterations %s, GMRES iterations "
+          "per solve %d..%d" % (case, worst, beam.newton_iterations, min(beam.gmres_iterations), max(beam.gmres_iterations)))
