@@ -98,6 +98,23 @@ int mb2_set_nodes(mb2_ctx* ctx, const double* x_ref, const double* weights);
  * default 2p+3. want_N != 0 also keeps the shape values N (QuadData::N). Call once per patch. */
 int mb2_generate_patch_tables(mb2_ctx* ctx, int64_t elem_begin, int64_t elem_count, int p, const int32_t* ncp,
                               const double* const* knots, const int32_t* el_ijk, int quad_order, int want_N);
+/* Mass matrix on the device: A += M on the resident CSR values, M = what
+ * mass->AddDomainIntegrator(new mfem::VectorMassIntegrator(rho)); mass->Assemble(0) leaves in the BilinearForm
+ * (src/mimi/py/py_nonlinear_solid.cpp:154-172; third_party/mfem/fem/bilininteg.cpp:1542-1620), bit for bit: rule
+ * IntRules.Get(geom, 2p + OrderW) (quad_order < 0; OrderW = p*dim - 1), per point (N_i N_j) * ((ip.weight * Trans.Weight())
+ * * density), points then elements added in ascending order. Needs mb2_set_nodes + mb2_build_pattern; the domain tables
+ * are not touched. el_ijk: knot-span index of every element this context computes (one tensor-product patch).
+ * In a partitioned run the ghost blocks travel like the K_e blocks. */
+int mb2_assemble_mass_device(mb2_ctx* ctx, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                             int quad_order, double density);
+/* Body-force linear form on the device: r += b on the resident vector, b = what
+ * rhs->AddDomainIntegrator(new mfem::VectorDomainLFIntegrator(body_force)); rhs->Assemble() produces for a constant
+ * force (src/mimi/py/py_nonlinear_solid.cpp:221-241; third_party/mfem/fem/lininteg.cpp:268-308), bit for bit: rule
+ * IntRules.Get(geom, 2p) (quad_order < 0), elvect(nd k + s) += ip.weight * (Tr.Weight() * f_k) * shape(s), elements added
+ * in ascending order. force: dim values. Essential entries are zeroed by the caller (rhs->SetSubVector(zero_dofs, 0.0))
+ * or by mb2_newton_rhs_from_r. */
+int mb2_assemble_body_force_device(mb2_ctx* ctx, int p, const int32_t* ncp, const double* const* knots,
+                                   const int32_t* el_ijk, int quad_order, const double* force);
 /* Shape values N: NE x nq x nd (tests; contact). */
 int mb2_download_shape_values(mb2_ctx* ctx, double* N);
 
@@ -237,6 +254,14 @@ int mb2_contact_gap_norm(mb2_ctx* ctx, const double* u, double* out);
  *   then the same elimination again;  J += fac1 S;  y -= rhs;  y[ess] := 0.
  * Results stay resident (mb2_get_r / mb2_get_A / mb2_device_pointers) and are bit-identical to the reference's. */
 int mb2_set_mass(mb2_ctx* ctx, const double* M_values);          /* nnz values on mb2_build_pattern's pattern */
+/* The resident CSR values (e.g. after mb2_set_A(NULL) + mb2_assemble_mass_device) become the mass of the Newton
+ * sweeps without leaving the device; form_system_matrix != 0 applies BilinearForm::FormSystemMatrix(zero_dofs, .)
+ * (py_nonlinear_solid.cpp:173) for the dofs of mb2_set_essential_dofs: rows / columns zeroed, diagonal one. */
+int mb2_newton_mass_from_A(mb2_ctx* ctx, int form_system_matrix);
+int mb2_newton_get_mass(mb2_ctx* ctx, double* M_host);
+/* The resident vector r (e.g. after mb2_set_r(NULL) + mb2_assemble_body_force_device) becomes the rhs of the Newton
+ * sweeps; zero_essential != 0 applies rhs->SetSubVector(zero_dofs, 0.0) (py_nonlinear_solid.cpp:281). */
+int mb2_newton_rhs_from_r(mb2_ctx* ctx, int zero_essential);
 int mb2_set_viscosity(mb2_ctx* ctx, const double* S_values);     /* nnz values, NULL = none */
 int mb2_set_rhs(mb2_ctx* ctx, const double* rhs);                /* NV, NULL = none (linear forms: body force, traction) */
 int mb2_set_essential_dofs(mb2_ctx* ctx, const int32_t* tdofs, int64_t n);

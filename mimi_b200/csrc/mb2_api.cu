@@ -489,6 +489,24 @@ int mb2_set_nodes(mb2_ctx* c, const double* x_ref, const double* weights) {
   return mb2::set_nodes(c, x_ref, weights);
 }
 
+int mb2_assemble_mass_device(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                             int quad_order, double density) {
+  CHECK_CTX(c);
+  REQUIRE(c->NE > 0, "call mb2_set_connectivity first");
+  REQUIRE(ncp && knots && el_ijk, "null argument");
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::assemble_mass(c, p, ncp, knots, el_ijk, quad_order, density);
+}
+
+int mb2_assemble_body_force_device(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                                   int quad_order, const double* force) {
+  CHECK_CTX(c);
+  REQUIRE(c->NE > 0, "call mb2_set_connectivity first");
+  REQUIRE(ncp && knots && el_ijk && force, "null argument");
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::assemble_body_force(c, p, ncp, knots, el_ijk, quad_order, force);
+}
+
 int mb2_generate_patch_tables(mb2_ctx* c, int64_t elem_begin, int64_t elem_count, int p, const int32_t* ncp,
                               const double* const* knots, const int32_t* el_ijk, int quad_order, int want_N) {
   CHECK_CTX(c);

@@ -58,6 +58,7 @@ struct mb2_ctx {
   MgState* mg = nullptr;       // exchange state (mb2_multigpu.cu)
   void* contact = nullptr;     // mortar contact state (mb2_contact.cu)
   void* newton = nullptr;      // Newton-iteration sweeps: mass / viscosity / rhs / essential dofs (mb2_newton.cu)
+  void* mass_tab = nullptr;    // non-null only inside mb2_assemble_mass_device: the element stage writes M_e (mb2_tables.cu)
 
   // connectivity
   int32_t* d_vdofs = nullptr;   // NE x tdof (reference layout)
@@ -124,6 +125,13 @@ int launch_fp64_peak(mb2_ctx* c, int fma, double* tflops);
 int set_nodes(mb2_ctx* c, const double* x_ref, const double* weights);
 int generate_patch_tables(mb2_ctx* c, int64_t e0, int64_t ne, int p, const int32_t* ncp, const double* const* knots,
                           const int32_t* el_ijk, int quad_order, bool want_N);
+int assemble_mass(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk, int quad_order,
+                  double rho);
+int launch_mass_element(mb2_ctx* c, int64_t e0, int64_t e1, double* KeT, double* Re, cudaStream_t st);
+int assemble_body_force(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                        int quad_order, const double* f);
+int launch_lform_element(mb2_ctx* c, int64_t e0, int64_t e1, double* Re, cudaStream_t st);
+int form_mode(const mb2_ctx* c);  // 0 mass, 1 body force (valid while mass_tab is set)
 }  // namespace mb2
 
 #define MB2_CUDA(call)                                                                      \

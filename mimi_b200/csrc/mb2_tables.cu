@@ -13,6 +13,7 @@
 //   geometry Jacobian             IsoparametricTransformation::EvalJacobian, third_party/mfem/fem/eltrans.cpp:406-420
 //   det / inverse / dN_dX         DenseMatrix::Det (densemat.cpp:510-525), kernels::CalcInverse
 //                                 (kernels.hpp:244-251), kernels::Mult (kernels.hpp:341-357)
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -315,5 +316,303 @@ int generate_patch_tables(mb2_ctx* c, int64_t e0, int64_t ne, int p, const int32
   if (flag) { c->err = "non-positive geometry Jacobian determinant while generating tables"; return MB2_ERR_NUMERIC; }
   return MB2_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------
+// Mass matrix on the device: mfem::VectorMassIntegrator::AssembleElementMatrix
+// (third_party/mfem/fem/bilininteg.cpp:1542-1620) as the reference adds it in PyNonlinearSolid::Setup
+// (src/mimi/py/py_nonlinear_solid.cpp:154-173), gathered by BilinearForm::Assemble in ascending element order.
+//   rule      IntRules.Get(geom, 2 p + Trans.OrderW()), OrderW = p dim - 1 for Qk (eltrans.cpp:453-465)
+//   per point norm = (ip.weight * Trans.Weight()) * rho;  partelmat = shape shape^t (MultVVt);  partelmat *= norm;
+//             elmat(k nd + i, k nd + j) += partelmat(i, j)   -> m_ij = ((0 + (N_i N_j) norm_0) + (N_i N_j) norm_1) + ...
+// The element blocks are written in the K_e layout of mb2_assembly.cu (zeros between different components, exactly
+// what AddSubMatrix adds with skip_zeros = 0), so the ordered CSR gather, its chunk pipeline and the multi-GPU ghost
+// exchange are reused unchanged with grad_factor = 1.
+// ---------------------------------------------------------------------------------------------
+struct MassTab {
+  int p = 0, nq1 = 0;
+  int mode = 0;  // 0: mass matrix (Jacobian pipeline), 1: body-force linear form (residual pipeline)
+  double rho = 1.0;
+  double f[3] = {0.0, 0.0, 0.0};
+  int32_t* d_ijk = nullptr;
+  double *d_gw = nullptr, *d_B1[3] = {nullptr, nullptr, nullptr}, *d_D1[3] = {nullptr, nullptr, nullptr};
+};
+
+struct MassArgs {
+  int64_t e0, e1;
+  int nq1;
+  double rho;
+  double f[3];
+  const int32_t* __restrict__ vdofs;
+  const int32_t* __restrict__ el_ijk;
+  const double* __restrict__ B1[3];
+  const double* __restrict__ D1[3];
+  const double* __restrict__ gw;
+  const double* __restrict__ x_ref;
+  const double* __restrict__ wts;
+  double* __restrict__ KeT;
+  double* __restrict__ Re;
+};
+
+constexpr int MASS_NT = 128;  // threads per element
+constexpr int MASS_QB = 32;   // quadrature points staged per batch
+
+// el.CalcShape(ip, shape), ip.weight and Trans.Weight() at quadrature point q of element e, in MFEM's operation order.
+template <int DIM, int P>
+__device__ void mass_point(const MassArgs& g, const int32_t* vd, int64_t e, int q, double* shape, double* ipw, double* detJ) {
+  constexpr int P1 = P + 1;
+  constexpr int ND = (DIM == 3) ? P1 * P1 * P1 : P1 * P1;
+  constexpr int TD = DIM * ND;
+  const int nq1 = g.nq1;
+  int qd[3], sp[3];
+  qd[0] = q % nq1;
+  qd[1] = (q / nq1) % nq1;
+  qd[2] = (DIM == 3) ? q / (nq1 * nq1) : 0;
+  for (int d = 0; d < DIM; d++) sp[d] = g.el_ijk[e * DIM + d];
+  const double *sx = g.B1[0] + ((size_t)sp[0] * nq1 + qd[0]) * P1, *dsx = g.D1[0] + ((size_t)sp[0] * nq1 + qd[0]) * P1;
+  const double *sy = g.B1[1] + ((size_t)sp[1] * nq1 + qd[1]) * P1, *dsy = g.D1[1] + ((size_t)sp[1] * nq1 + qd[1]) * P1;
+  double uu[ND], ds[TD];
+  double sum = 0.0, dsum[3] = {0.0, 0.0, 0.0};
+  if (DIM == 3) {
+    const double* sz = g.B1[2] + ((size_t)sp[2] * nq1 + qd[2]) * P1;
+    const double* dsz = g.D1[2] + ((size_t)sp[2] * nq1 + qd[2]) * P1;
+    int o = 0;
+    for (int k = 0; k < P1; k++)
+      for (int j = 0; j < P1; j++) {
+        const double sy_sz = sy[j] * sz[k], dsy_sz = dsy[j] * sz[k], sy_dsz = sy[j] * dsz[k];
+        for (int i = 0; i < P1; i++, o++) {
+          const double w = g.wts ? g.wts[vd[o] / DIM] : 1.0;
+          sum += (uu[o] = sx[i] * sy_sz * w);
+          dsum[0] += (ds[o] = dsx[i] * sy_sz * w);
+          dsum[1] += (ds[o + ND] = sx[i] * dsy_sz * w);
+          dsum[2] += (ds[o + 2 * ND] = sx[i] * sy_dsz * w);
+        }
+      }
+  } else {
+    int o = 0;
+    for (int j = 0; j < P1; j++)
+      for (int i = 0; i < P1; i++, o++) {
+        const double w = g.wts ? g.wts[vd[o] / DIM] : 1.0;
+        sum += (uu[o] = sx[i] * sy[j] * w);
+        dsum[0] += (ds[o] = dsx[i] * sy[j] * w);
+        dsum[1] += (ds[o + ND] = sx[i] * dsy[j] * w);
+      }
+  }
+  // el.CalcShape: shape /= sum (fe_nurbs.cpp:125-158,236-267; Vector::operator/=: m = 1/sum, shape[i] *= m)
+  const double m = 1.0 / sum;
+  for (int o = 0; o < ND; o++) shape[o] = uu[o] * m;
+  // Trans.Weight(): the Jacobian is built from CalcDShape (eltrans.cpp:406-420)
+  for (int d = 0; d < DIM; d++) dsum[d] *= m * m;
+  for (int o = 0; o < ND; o++)
+    for (int d = 0; d < DIM; d++) ds[o + d * ND] = ds[o + d * ND] * m - uu[o] * dsum[d];
+  double Jm[DIM * DIM];
+  for (int i = 0; i < DIM * DIM; i++) Jm[i] = 0.0;
+  for (int j = 0; j < DIM; j++)
+    for (int k = 0; k < ND; k++) {
+      const double cc = ds[k + j * ND];
+      for (int i = 0; i < DIM; i++) Jm[i + DIM * j] += g.x_ref[vd[i * ND + k]] * cc;
+    }
+  double w = g.gw[qd[0]] * g.gw[qd[1]];
+  if (DIM == 3) w = w * g.gw[qd[2]];
+  *ipw = w;
+  *detJ = det_small<DIM>(Jm);
+}
+
+template <int DIM, int P>
+__global__ void __launch_bounds__(MASS_NT) k_mass_element(const MassArgs g) {
+  constexpr int P1 = P + 1;
+  constexpr int ND = (DIM == 3) ? P1 * P1 * P1 : P1 * P1;
+  constexpr int TD = DIM * ND;
+  constexpr int KP = (TD * DIM + 3) / 4 * 4;
+  constexpr int NACC = (ND * ND + MASS_NT - 1) / MASS_NT;
+  __shared__ double sN[MASS_QB][ND];
+  __shared__ double sNorm[MASS_QB];
+  const int nq1 = g.nq1;
+  const int nq = (DIM == 3) ? nq1 * nq1 * nq1 : nq1 * nq1;
+  const int t = threadIdx.x;
+  for (int64_t e = g.e0 + blockIdx.x; e < g.e1; e += gridDim.x) {
+    const int32_t* vd = g.vdofs + e * TD;
+    double acc[NACC];
+#pragma unroll
+    for (int k = 0; k < NACC; k++) acc[k] = 0.0;
+    for (int q0 = 0; q0 < nq; q0 += MASS_QB) {
+      const int nb = min(MASS_QB, nq - q0);
+      if (t < nb) {
+        double w, dj;
+        mass_point<DIM, P>(g, vd, e, q0 + t, sN[t], &w, &dj);
+        sNorm[t] = (w * dj) * g.rho;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < NACC; k++) {
+        const int idx = t + k * MASS_NT;
+        if (idx < ND * ND) {
+          const int i = idx % ND, j = idx / ND;
+          double a = acc[k];
+          for (int s = 0; s < nb; s++) a += (sN[s][i] * sN[s][j]) * sNorm[s];
+          acc[k] = a;
+        }
+      }
+      __syncthreads();
+    }
+    double* out = g.KeT + (e - g.e0) * (int64_t)(ND * KP);
+#pragma unroll
+    for (int k = 0; k < NACC; k++) {
+      const int idx = t + k * MASS_NT;
+      if (idx < ND * ND) {
+        const int a = idx % ND, b = idx / ND;  // row node, column node
+        for (int cj = 0; cj < DIM; cj++)
+          for (int ci = 0; ci < DIM; ci++) out[(int64_t)a * KP + (b + cj * ND) * DIM + ci] = (ci == cj) ? acc[k] : 0.0;
+      }
+    }
+    for (int i = t; i < TD; i += MASS_NT) g.Re[e * TD + i] = 0.0;  // the pipeline also gathers R_e: r += 0
+  }
+}
+
+// Body-force linear form: mfem::VectorDomainLFIntegrator::AssembleRHSElementVect (third_party/mfem/fem/lininteg.cpp) with
+// a VectorConstantCoefficient, as PyNonlinearSolid::Setup adds it (src/mimi/py/py_nonlinear_solid.cpp:221-241):
+//   rule IntRules.Get(geom, 2 p);  per point val = Tr.Weight(), cf = val * f_k,  elvect(nd k + s) += ip.weight * cf * shape(s)
+// The element vectors land in R_e; the ordered residual gather adds them in ascending element order (LinearForm::Assemble).
+template <int DIM, int P>
+__global__ void __launch_bounds__(MASS_NT) k_lform_element(const MassArgs g) {
+  constexpr int P1 = P + 1;
+  constexpr int ND = (DIM == 3) ? P1 * P1 * P1 : P1 * P1;
+  constexpr int TD = DIM * ND;
+  __shared__ double sN[MASS_QB][ND];
+  __shared__ double sW[MASS_QB], sVal[MASS_QB];
+  const int nq1 = g.nq1;
+  const int nq = (DIM == 3) ? nq1 * nq1 * nq1 : nq1 * nq1;
+  const int t = threadIdx.x;
+  for (int64_t e = g.e0 + blockIdx.x; e < g.e1; e += gridDim.x) {
+    const int32_t* vd = g.vdofs + e * TD;
+    double acc0 = 0.0, acc1 = 0.0;  // TD <= 2 * MASS_NT
+    for (int q0 = 0; q0 < nq; q0 += MASS_QB) {
+      const int nb = min(MASS_QB, nq - q0);
+      if (t < nb) mass_point<DIM, P>(g, vd, e, q0 + t, sN[t], &sW[t], &sVal[t]);
+      __syncthreads();
+      for (int s = 0; s < nb; s++) {
+        if (t < TD) acc0 += sW[s] * (sVal[s] * g.f[t / ND]) * sN[s][t % ND];
+        if (t + MASS_NT < TD) acc1 += sW[s] * (sVal[s] * g.f[(t + MASS_NT) / ND]) * sN[s][(t + MASS_NT) % ND];
+      }
+      __syncthreads();
+    }
+    if (t < TD) g.Re[e * TD + t] = acc0;
+    if (t + MASS_NT < TD) g.Re[e * TD + t + MASS_NT] = acc1;
+  }
+}
+
+int launch_lform_element(mb2_ctx* c, int64_t e0, int64_t e1, double* Re, cudaStream_t st) {
+  const MassTab* T = static_cast<const MassTab*>(c->mass_tab);
+  MassArgs a;
+  a.e0 = e0; a.e1 = e1; a.nq1 = T->nq1; a.rho = 1.0;
+  for (int d = 0; d < 3; d++) a.f[d] = T->f[d];
+  a.vdofs = c->d_vdofs; a.el_ijk = T->d_ijk;
+  for (int d = 0; d < 3; d++) { a.B1[d] = T->d_B1[d]; a.D1[d] = T->d_D1[d]; }
+  a.gw = T->d_gw; a.x_ref = c->d_xref; a.wts = c->d_nodew;
+  a.KeT = nullptr; a.Re = Re;
+  const int64_t ne = e1 - e0;
+  if (ne <= 0) return MB2_OK;
+  const unsigned grid = (unsigned)std::min<int64_t>(ne, (int64_t)c->sm_count * 8);
+  const int dim = c->dim, p = T->p;
+  bool ok = true;
+#define MB2_LF(D, PP) if (dim == D && p == PP) k_lform_element<D, PP><<<grid, MASS_NT, 0, st>>>(a); else
+  MB2_LF(3, 1) MB2_LF(3, 2) MB2_LF(3, 3) MB2_LF(2, 1) MB2_LF(2, 2) MB2_LF(2, 3) MB2_LF(2, 4) { ok = false; }
+#undef MB2_LF
+  if (!ok) { c->err = "no linear-form kernel for this (dim, p)"; return MB2_ERR_UNSUPPORTED; }
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
+int launch_mass_element(mb2_ctx* c, int64_t e0, int64_t e1, double* KeT, double* Re, cudaStream_t st) {
+  const MassTab* T = static_cast<const MassTab*>(c->mass_tab);
+  MassArgs a;
+  a.e0 = e0; a.e1 = e1; a.nq1 = T->nq1; a.rho = T->rho;
+  for (int d = 0; d < 3; d++) a.f[d] = 0.0;
+  a.vdofs = c->d_vdofs; a.el_ijk = T->d_ijk;
+  for (int d = 0; d < 3; d++) { a.B1[d] = T->d_B1[d]; a.D1[d] = T->d_D1[d]; }
+  a.gw = T->d_gw; a.x_ref = c->d_xref; a.wts = c->d_nodew;
+  a.KeT = KeT; a.Re = Re;
+  const int64_t ne = e1 - e0;
+  if (ne <= 0) return MB2_OK;
+  const unsigned grid = (unsigned)std::min<int64_t>(ne, (int64_t)c->sm_count * 8);
+  const int dim = c->dim, p = T->p;
+  bool ok = true;
+#define MB2_MASS(D, PP) if (dim == D && p == PP) k_mass_element<D, PP><<<grid, MASS_NT, 0, st>>>(a); else
+  MB2_MASS(3, 1) MB2_MASS(3, 2) MB2_MASS(3, 3) MB2_MASS(2, 1) MB2_MASS(2, 2) MB2_MASS(2, 3) MB2_MASS(2, 4) { ok = false; }
+#undef MB2_MASS
+  if (!ok) { c->err = "no mass kernel for this (dim, p)"; return MB2_ERR_UNSUPPORTED; }
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
+static void free_mass_tab(MassTab& T) {
+  cudaFree(T.d_ijk);
+  cudaFree(T.d_gw);
+  for (int d = 0; d < 3; d++) { cudaFree(T.d_B1[d]); cudaFree(T.d_D1[d]); }
+}
+
+// mode 0: A += M on the resident CSR values; mode 1: r += b (body force). el_ijk: knot-span index of the n_compute
+// elements this context computes.
+static int assemble_form(mb2_ctx* c, int mode, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                         int quad_order, double rho, const double* f) {
+  const int dim = c->dim;
+  if (p < 1 || p > MAXP) { c->err = "degree must be 1..4"; return MB2_ERR_UNSUPPORTED; }
+  int nd = 1;
+  for (int d = 0; d < dim; d++) nd *= p + 1;
+  if (nd != c->nd) { c->err = "(p+1)^dim does not match nd of the connectivity"; return MB2_ERR_ARG; }
+  if (!c->d_xref) { c->err = "call mb2_set_nodes first"; return MB2_ERR_ARG; }
+  if (!c->have_pattern) { c->err = "call mb2_build_pattern first"; return MB2_ERR_ARG; }
+  const int order = quad_order >= 0 ? quad_order : (mode == 0 ? 2 * p + (p * dim - 1) : 2 * p);
+  MassTab T;
+  T.p = p;
+  T.mode = mode;
+  if (f)
+    for (int d = 0; d < dim; d++) T.f[d] = f[d];
+  T.nq1 = (order | 1) / 2 + 1;
+  T.rho = rho;
+  if (T.nq1 > MAXQ1) { c->err = "mass quadrature order above the instantiated limit"; return MB2_ERR_UNSUPPORTED; }
+  std::vector<double> gx, gw;
+  gauss_legendre_01(T.nq1, gx, gw);
+  double* d_gx = nullptr;
+  int rc = [&]() -> int {
+    MB2_CUDA(cudaMalloc(&d_gx, sizeof(double) * T.nq1));
+    MB2_CUDA(cudaMalloc(&T.d_gw, sizeof(double) * T.nq1));
+    MB2_CUDA(cudaMemcpyAsync(d_gx, gx.data(), sizeof(double) * T.nq1, cudaMemcpyHostToDevice, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(T.d_gw, gw.data(), sizeof(double) * T.nq1, cudaMemcpyHostToDevice, c->stream));
+    std::vector<double*> d_knot(dim, nullptr);
+    for (int d = 0; d < dim; d++) {
+      const int nk = ncp[d] + p + 1, nspan = ncp[d] - p;
+      MB2_CUDA(cudaMalloc(&d_knot[d], sizeof(double) * nk));
+      MB2_CUDA(cudaMemcpyAsync(d_knot[d], knots[d], sizeof(double) * nk, cudaMemcpyHostToDevice, c->stream));
+      MB2_CUDA(cudaMalloc(&T.d_B1[d], sizeof(double) * nspan * T.nq1 * (p + 1)));
+      MB2_CUDA(cudaMalloc(&T.d_D1[d], sizeof(double) * nspan * T.nq1 * (p + 1)));
+      k_basis_1d<<<(nspan * T.nq1 + 127) / 128, 128, 0, c->stream>>>(p, nspan, T.nq1, d_knot[d], d_gx, T.d_B1[d], T.d_D1[d]);
+      MB2_CUDA(cudaGetLastError());
+    }
+    MB2_CUDA(cudaMalloc(&T.d_ijk, sizeof(int32_t) * c->n_compute * dim));
+    MB2_CUDA(cudaMemcpyAsync(T.d_ijk, el_ijk, sizeof(int32_t) * c->n_compute * dim, cudaMemcpyHostToDevice, c->stream));
+    MB2_CUDA(cudaStreamSynchronize(c->stream));
+    for (int d = 0; d < dim; d++) cudaFree(d_knot[d]);
+    c->mass_tab = &T;
+    int r = mode == 0 ? launch_residual_and_grad(c, 1.0, nullptr, nullptr) : launch_residual(c);
+    if (r) return r;
+    MB2_CUDA(cudaStreamSynchronize(c->stream));
+    return MB2_OK;
+  }();
+  c->mass_tab = nullptr;
+  cudaFree(d_gx);
+  free_mass_tab(T);
+  return rc;
+}
+
+int assemble_mass(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk, int quad_order,
+                  double rho) {
+  return assemble_form(c, 0, p, ncp, knots, el_ijk, quad_order, rho, nullptr);
+}
+int assemble_body_force(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                        int quad_order, const double* f) {
+  return assemble_form(c, 1, p, ncp, knots, el_ijk, quad_order, 1.0, f);
+}
+int form_mode(const mb2_ctx* c) { return static_cast<const MassTab*>(c->mass_tab)->mode; }
 
 }  // namespace mb2

@@ -164,6 +164,25 @@ def sweeps_main():
             print(name, W["y"].size, W["Jac"].size, W["ess"].size)
 
 
+BODY_FORCE = (0.3, -1.7, 0.9)      # the constant force oracle/ref_harness.cpp puts into its body-force linear form
+
+
+def bodyforce_main():
+    """tests/golden/bodyforce.npz: mfem::VectorDomainLFIntegrator of a constant body force (harness mode 'dump',
+    bodyforce.f64) for every base fixture; the meshes / numbering are those of the fixtures of the same name."""
+    out = {"f": np.array(BODY_FORCE)}
+    for name, (writer, elevate, refine, gf) in CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            mesh = os.path.join(tmp, "m.mesh")
+            writer(mesh)
+            D = O.run_ref_dump(mesh, elevate, refine, "neohookean", os.path.join(tmp, "d"), gf=gf)
+            base = np.load(os.path.join(OUT, name + ".npz"))
+            assert np.array_equal(D["mass"], base["mass"]) and np.array_equal(D["x_ref"], base["x_ref"])
+            out[name] = D["bodyforce"]
+    np.savez_compressed(os.path.join(OUT, "bodyforce.npz"), **out)
+    print("bodyforce", {k: v.shape for k, v in out.items()})
+
+
 def main(only=None):
     assert O.have_ref(), "build oracle/_ref first: make -f oracle/Makefile.ref -j8"
     os.makedirs(OUT, exist_ok=True)
@@ -197,6 +216,8 @@ def main(only=None):
 if __name__ == "__main__":
     if "contact" in sys.argv[1:]:
         contact_main()
+    elif "bodyforce" in sys.argv[1:]:
+        bodyforce_main()
     elif "j2" in sys.argv[1:]:
         j2_main()
     elif "sweeps" in sys.argv[1:]:

@@ -410,6 +410,15 @@ int main(int argc, char** argv) {
     mfem::SparseMatrix A(s.mass->SpMat());
     if (A.NumNonZeroElems() != nnz) { std::fprintf(stderr, "mass pattern != sparsity pattern\n"); return 3; }
     dump(out, "mass.f64", A.GetData(), (size_t)nnz);
+    {  // body-force linear form as PyNonlinearSolid::Setup builds it (py_nonlinear_solid.cpp:221-241), f = (0.3, -1.7, 0.9)
+      mfem::LinearForm lf(s.fes.get());
+      mfem::VectorArrayCoefficient bf(dim);
+      const double fv[3] = {0.3, -1.7, 0.9};
+      for (int c = 0; c < dim; ++c) bf.Set(c, new mfem::ConstantCoefficient(fv[c]));
+      lf.AddDomainIntegrator(new mfem::VectorDomainLFIntegrator(bf));
+      lf.Assemble();
+      dump(out, "bodyforce.f64", lf.GetData(), (size_t)NV);
+    }
     r2 = 0.0;
     s.integ->AddDomainResidualAndGrad(u, gf, r2, A);
     dump(out, "r2.f64", r2.GetData(), (size_t)NV);

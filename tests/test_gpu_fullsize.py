@@ -11,6 +11,7 @@ nnz = 1 152 216 576) through properties that do not need a full-size oracle run:
   4. adds-into semantics: assembling twice into the same r / A gives exactly 2 r and 2 A (x + x is exact).
   5. u = 0: the NeoHookean stress at F = I is exactly zero, so r == 0 exactly, and K annihilates rigid translations
      (row sums over each component block ~ 0) on the sampled rows.
+  6. the mass matrix (mb2_assemble_mass_device): corner block == small patch bit for bit, entries sum to dim x volume.
 """
 import numpy as np
 import pytest
@@ -155,6 +156,38 @@ def test_c3_full_size_properties(ctx_factory):
         for k in range(3):
             worst = max(worst, abs(Ar[Jr % 3 == k].sum()) / scale)
     assert worst <= 1e-5, worst       # observed 1.1e-7: forward-difference rounding noise (h = 1e-10)
+    del A0
+
+    # ---- 6. mass matrix at full size (mb2_assemble_mass_device; bit-exact against the reference on the fixtures,
+    #         tests/test_gpu_mass.py): corner block == the 5^3 patch's bit for bit (locality), partition of unity
+    import time
+    ctx.set_A(None)
+    t0 = time.perf_counter()
+    ctx.assemble_mass_device(P, M["ncp"], M["knots"], M["el_ijk"])
+    ctx.sync()
+    t_mass = time.perf_counter() - t0
+    Mb = ctx.get_A()
+    cs.set_A(None)
+    cs.assemble_mass_device(P, S["ncp"], S["knots"], S["el_ijk"])
+    Ms = cs.get_A()
+    mchecked = 0
+    for a in range(3):
+        for b in range(3):
+            for c in range(3):
+                for k in range(3):
+                    rs, rb = int(3 * g_s[a, b, c] + k), int(3 * g_big[a, b, c] + k)
+                    Js, As = _rows(I_s, J_s, Ms, rs)
+                    Jb, Ab = _rows(I, J, Mb, rb)
+                    big = dict(zip(Jb.tolist(), Ab.tolist()))
+                    for j, v in zip(Js.tolist(), As.tolist()):
+                        assert big[col_of[j]] == v, ("mass", a, b, c, k, j)
+                        mchecked += 1
+    total = float(np.sum(Mb, dtype=np.longdouble))
+    assert abs(total - 3.0) < 1e-9, total            # 3 component blocks x volume 1
+    assert Mb.min() >= 0.0                            # B-splines are non-negative
+    del Mb
+    print("\n[full size] mass 100^3: %d corner entries bit-equal to the small patch, sum = 3 + %.1e, %.0f ms incl. tables"
+          % (mchecked, total - 3.0, 1e3 * t_mass))
     print("\n[full size] C3 100^3: corner block %d CSR entries bit-equal to the oracle; determinism, gf linearity, "
           "adds-into and u = 0 properties hold (translation row sums <= %.1e of the largest entry); launches per "
           "assembly = %d" % (checked, worst, ctx.last_launch_count()))
