@@ -107,6 +107,13 @@ int mb2_generate_patch_tables(mb2_ctx* ctx, int64_t elem_begin, int64_t elem_cou
  * In a partitioned run the ghost blocks travel like the K_e blocks. */
 int mb2_assemble_mass_device(mb2_ctx* ctx, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
                              int quad_order, double density);
+/* Viscosity (damping) matrix on the device: A += S, S = what visc->AddDomainIntegrator(new
+ * mfem::VectorDiffusionIntegrator(viscosity)); visc->Assemble(0) leaves in the BilinearForm
+ * (src/mimi/py/py_nonlinear_solid.cpp:174-191; third_party/mfem/fem/bilininteg.cpp:2854-2934), bit for bit: rule
+ * IntRules.Get(geom, 2p + dim - 1) (quad_order < 0), per point w = (ip.weight / Trans.Weight()) * viscosity,
+ * dshapedxt = dshape adj(J), pelmat = w * dshapedxt dshapedxt^t (Mult_a_AAt) on every diagonal component block. */
+int mb2_assemble_viscosity_device(mb2_ctx* ctx, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                                  int quad_order, double viscosity);
 /* Body-force linear form on the device: r += b on the resident vector, b = what
  * rhs->AddDomainIntegrator(new mfem::VectorDomainLFIntegrator(body_force)); rhs->Assemble() produces for a constant
  * force (src/mimi/py/py_nonlinear_solid.cpp:221-241; third_party/mfem/fem/lininteg.cpp:268-308), bit for bit: rule
@@ -259,6 +266,8 @@ int mb2_set_mass(mb2_ctx* ctx, const double* M_values);          /* nnz values o
  * (py_nonlinear_solid.cpp:173) for the dofs of mb2_set_essential_dofs: rows / columns zeroed, diagonal one. */
 int mb2_newton_mass_from_A(mb2_ctx* ctx, int form_system_matrix);
 int mb2_newton_get_mass(mb2_ctx* ctx, double* M_host);
+int mb2_newton_viscosity_from_A(mb2_ctx* ctx, int form_system_matrix);   /* same for the viscosity matrix */
+int mb2_newton_get_viscosity(mb2_ctx* ctx, double* S_host);
 /* The resident vector r (e.g. after mb2_set_r(NULL) + mb2_assemble_body_force_device) becomes the rhs of the Newton
  * sweeps; zero_essential != 0 applies rhs->SetSubVector(zero_dofs, 0.0) (py_nonlinear_solid.cpp:281). */
 int mb2_newton_rhs_from_r(mb2_ctx* ctx, int zero_essential);

@@ -19,7 +19,7 @@ MB2_RIGID_PLANE, MB2_RIGID_SPHERE, MB2_RIGID_BEZIER, MB2_RIGID_BSPLINE = 0, 1, 2
 # every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "mb2_create", "mb2_destroy", "mb2_last_error", "mb2_version", "mb2_set_connectivity",
-    "mb2_upload_quad_tables", "mb2_set_nodes", "mb2_generate_patch_tables", "mb2_assemble_mass_device", "mb2_assemble_body_force_device", "mb2_newton_rhs_from_r", "mb2_newton_mass_from_A", "mb2_newton_get_mass", "mb2_download_shape_values", "mb2_download_quad_tables", "mb2_build_pattern",
+    "mb2_upload_quad_tables", "mb2_set_nodes", "mb2_generate_patch_tables", "mb2_assemble_mass_device", "mb2_assemble_body_force_device", "mb2_assemble_viscosity_device", "mb2_newton_viscosity_from_A", "mb2_newton_get_viscosity", "mb2_newton_rhs_from_r", "mb2_newton_mass_from_A", "mb2_newton_get_mass", "mb2_download_shape_values", "mb2_download_quad_tables", "mb2_build_pattern",
     "mb2_get_pattern_i32", "mb2_get_pattern_i64", "mb2_get_A_ids_i32", "mb2_set_material",
     "mb2_add_domain_residual", "mb2_add_domain_residual_and_grad", "mb2_set_u", "mb2_set_r", "mb2_set_A",
     "mb2_get_r", "mb2_get_A", "mb2_assemble_residual_device", "mb2_assemble_residual_and_grad_device",
@@ -139,6 +139,24 @@ class Context:
 
     def newton_rhs_from_r(self, zero_essential=True):
         self._ck(self.lib.mb2_newton_rhs_from_r(self.h, C.c_int(int(zero_essential))))
+
+    def assemble_viscosity_device(self, p, ncp, knots, el_ijk, viscosity, quad_order=-1):
+        """A += S (VectorDiffusionIntegrator) on the resident CSR values."""
+        ncp = np.ascontiguousarray(ncp, np.int32)
+        ijk = np.ascontiguousarray(el_ijk, np.int32)
+        kv = [np.ascontiguousarray(k, np.float64) for k in knots]
+        assert all(len(k) == n + p + 1 for k, n in zip(kv, ncp))
+        arr = (C.c_void_p * len(kv))(*[k.ctypes.data for k in kv])
+        self._ck(self.lib.mb2_assemble_viscosity_device(self.h, C.c_int(p), _dp(ncp), arr, _dp(ijk), C.c_int(quad_order),
+                                                        C.c_double(viscosity)))
+
+    def newton_viscosity_from_A(self, form_system_matrix=True):
+        self._ck(self.lib.mb2_newton_viscosity_from_A(self.h, C.c_int(int(form_system_matrix))))
+
+    def newton_get_viscosity(self):
+        S = np.empty(self.nnz)
+        self._ck(self.lib.mb2_newton_get_viscosity(self.h, _dp(S)))
+        return S
 
     def newton_mass_from_A(self, form_system_matrix=True):
         self._ck(self.lib.mb2_newton_mass_from_A(self.h, C.c_int(int(form_system_matrix))))

@@ -1003,7 +1003,7 @@ template <bool GRAD>
 static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   const int dim = c->dim, nd = c->nd, nq = c->nq;
   if (c->mass_tab) {  // mb2_assemble_mass_device / mb2_assemble_body_force_device: same pipelines, M_e / b_e instead of K_e / R_e
-    if (GRAD != (form_mode(c) == 0)) { c->err = "bilinear forms use the Jacobian pipeline, linear forms the residual one"; return MB2_ERR_ARG; }
+    if (GRAD != (form_mode(c) != 1)) { c->err = "bilinear forms use the Jacobian pipeline, linear forms the residual one"; return MB2_ERR_ARG; }
     return GRAD ? launch_mass_element(c, a.e0, a.e1, a.KeT, a.Re, st) : launch_lform_element(c, a.e0, a.e1, a.Re, st);
   }
   if (GRAD && dim == 3 && nd == 27 && nq == 64 && c->elem_variant != 1) {

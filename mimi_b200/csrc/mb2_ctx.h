@@ -131,7 +131,9 @@ int launch_mass_element(mb2_ctx* c, int64_t e0, int64_t e1, double* KeT, double*
 int assemble_body_force(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
                         int quad_order, const double* f);
 int launch_lform_element(mb2_ctx* c, int64_t e0, int64_t e1, double* Re, cudaStream_t st);
-int form_mode(const mb2_ctx* c);  // 0 mass, 1 body force (valid while mass_tab is set)
+int assemble_viscosity(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                       int quad_order, double coef);
+int form_mode(const mb2_ctx* c);  // 0 mass, 1 body force, 2 viscosity (valid while mass_tab is set)
 }  // namespace mb2
 
 #define MB2_CUDA(call)                                                                      \

@@ -428,24 +428,44 @@ int mb2_set_mass(mb2_ctx* c, const double* M) {
   return MB2_OK;
 }
 
-int mb2_newton_mass_from_A(mb2_ctx* c, int form_system_matrix) {
-  if (!c) return MB2_ERR_ARG;
-  int rc = mb2::ensure(c);
-  if (rc) return rc;
+static int adopt_A(mb2_ctx* c, double** dst, int form_system_matrix) {
   NewtonState* S = static_cast<NewtonState*>(c->newton);
   if (!c->d_A) { c->err = "no resident CSR values"; return MB2_ERR_ARG; }
-  if (!S->d_M) MB2_CUDA(cudaMalloc(&S->d_M, sizeof(double) * c->nnz));
-  MB2_CUDA(cudaMemcpyAsync(S->d_M, c->d_A, sizeof(double) * c->nnz, cudaMemcpyDeviceToDevice, c->stream));
+  if (!*dst) MB2_CUDA(cudaMalloc(dst, sizeof(double) * c->nnz));
+  MB2_CUDA(cudaMemcpyAsync(*dst, c->d_A, sizeof(double) * c->nnz, cudaMemcpyDeviceToDevice, c->stream));
   if (form_system_matrix && S->n_ess) {
-    // BilinearForm::FormSystemMatrix(zero_dofs, .) (py_nonlinear_solid.cpp:173): EliminateRowCol(dof, DIAG_ONE) per dof
+    // BilinearForm::FormSystemMatrix(zero_dofs, .) (py_nonlinear_solid.cpp:173,190): EliminateRowCol(dof, DIAG_ONE) per dof
     MB2_CUDA(cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
-    mb2::k_eliminate<<<(unsigned)S->n_ess, 64, 0, c->stream>>>(S->n_ess, S->d_ess, c->d_I, c->d_J, S->d_M, S->d_tv, c->d_flag);
+    mb2::k_eliminate<<<(unsigned)S->n_ess, 64, 0, c->stream>>>(S->n_ess, S->d_ess, c->d_I, c->d_J, *dst, S->d_tv, c->d_flag);
     MB2_CUDA(cudaGetLastError());
     int flag = 0;
     MB2_CUDA(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     MB2_CUDA(cudaStreamSynchronize(c->stream));
-    if (flag) { c->err = "non-symmetric pattern while eliminating essential dofs from the mass"; return MB2_ERR_NUMERIC; }
+    if (flag) { c->err = "non-symmetric pattern while eliminating essential dofs"; return MB2_ERR_NUMERIC; }
   }
+  return MB2_OK;
+}
+
+int mb2_newton_mass_from_A(mb2_ctx* c, int form_system_matrix) {
+  if (!c) return MB2_ERR_ARG;
+  int rc = mb2::ensure(c);
+  if (rc) return rc;
+  return adopt_A(c, &static_cast<NewtonState*>(c->newton)->d_M, form_system_matrix);
+}
+
+int mb2_newton_viscosity_from_A(mb2_ctx* c, int form_system_matrix) {
+  if (!c) return MB2_ERR_ARG;
+  int rc = mb2::ensure(c);
+  if (rc) return rc;
+  return adopt_A(c, &static_cast<NewtonState*>(c->newton)->d_S, form_system_matrix);
+}
+
+int mb2_newton_get_viscosity(mb2_ctx* c, double* Sv) {
+  if (!c) return MB2_ERR_ARG;
+  NewtonState* S = static_cast<NewtonState*>(c->newton);
+  if (!S || !S->d_S || !Sv) { c->err = "no viscosity on the device"; return MB2_ERR_ARG; }
+  MB2_CUDA(cudaMemcpyAsync(Sv, S->d_S, sizeof(double) * c->nnz, cudaMemcpyDeviceToHost, c->stream));
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
   return MB2_OK;
 }
 

@@ -331,7 +331,7 @@ int generate_patch_tables(mb2_ctx* c, int64_t e0, int64_t ne, int p, const int32
 // ---------------------------------------------------------------------------------------------
 struct MassTab {
   int p = 0, nq1 = 0;
-  int mode = 0;  // 0: mass matrix (Jacobian pipeline), 1: body-force linear form (residual pipeline)
+  int mode = 0;  // 0: mass matrix, 2: viscosity matrix (Jacobian pipeline); 1: body-force linear form (residual pipeline)
   double rho = 1.0;
   double f[3] = {0.0, 0.0, 0.0};
   int32_t* d_ijk = nullptr;
@@ -358,7 +358,8 @@ constexpr int MASS_NT = 128;  // threads per element
 constexpr int MASS_QB = 32;   // quadrature points staged per batch
 
 // el.CalcShape(ip, shape), ip.weight and Trans.Weight() at quadrature point q of element e, in MFEM's operation order.
-template <int DIM, int P>
+// GRAD: `shape` receives dshapedxt = dshape * adj(J) (ND x DIM, column-major) instead of the shape values.
+template <int DIM, int P, bool GRAD = false>
 __device__ void mass_point(const MassArgs& g, const int32_t* vd, int64_t e, int q, double* shape, double* ipw, double* detJ) {
   constexpr int P1 = P + 1;
   constexpr int ND = (DIM == 3) ? P1 * P1 * P1 : P1 * P1;
@@ -400,7 +401,8 @@ __device__ void mass_point(const MassArgs& g, const int32_t* vd, int64_t e, int 
   }
   // el.CalcShape: shape /= sum (fe_nurbs.cpp:125-158,236-267; Vector::operator/=: m = 1/sum, shape[i] *= m)
   const double m = 1.0 / sum;
-  for (int o = 0; o < ND; o++) shape[o] = uu[o] * m;
+  if (!GRAD)
+    for (int o = 0; o < ND; o++) shape[o] = uu[o] * m;
   // Trans.Weight(): the Jacobian is built from CalcDShape (eltrans.cpp:406-420)
   for (int d = 0; d < DIM; d++) dsum[d] *= m * m;
   for (int o = 0; o < ND; o++)
@@ -416,17 +418,50 @@ __device__ void mass_point(const MassArgs& g, const int32_t* vd, int64_t e, int 
   if (DIM == 3) w = w * g.gw[qd[2]];
   *ipw = w;
   *detJ = det_small<DIM>(Jm);
+  if (GRAD) {
+    // Trans.AdjugateJacobian(): CalcAdjugate (densemat.cpp:2495-2563); a(i, j) = Jm[i + DIM * j]
+    double ad[DIM * DIM];
+#define A_(i, j) Jm[(i) + DIM * (j)]
+#define AD_(i, j) ad[(i) + DIM * (j)]
+    if (DIM == 2) {
+      AD_(0, 0) = A_(1, 1); AD_(0, 1) = -A_(0, 1); AD_(1, 0) = -A_(1, 0); AD_(1, 1) = A_(0, 0);
+    } else {
+      AD_(0, 0) = A_(1, 1) * A_(2, 2) - A_(1, 2) * A_(2, 1);
+      AD_(0, 1) = A_(0, 2) * A_(2, 1) - A_(0, 1) * A_(2, 2);
+      AD_(0, 2) = A_(0, 1) * A_(1, 2) - A_(0, 2) * A_(1, 1);
+      AD_(1, 0) = A_(1, 2) * A_(2, 0) - A_(1, 0) * A_(2, 2);
+      AD_(1, 1) = A_(0, 0) * A_(2, 2) - A_(0, 2) * A_(2, 0);
+      AD_(1, 2) = A_(0, 2) * A_(1, 0) - A_(0, 0) * A_(1, 2);
+      AD_(2, 0) = A_(1, 0) * A_(2, 1) - A_(1, 1) * A_(2, 0);
+      AD_(2, 1) = A_(0, 1) * A_(2, 0) - A_(0, 0) * A_(2, 1);
+      AD_(2, 2) = A_(0, 0) * A_(1, 1) - A_(0, 1) * A_(1, 0);
+    }
+    // Mult(dshape, adjJ, dshapedxt) (kernels::Mult: zero, then j, k, i)
+    for (int j = 0; j < DIM; j++)
+      for (int i = 0; i < ND; i++) {
+        double a = 0.0;
+        for (int k = 0; k < DIM; k++) a += ds[i + k * ND] * AD_(k, j);
+        shape[i + j * ND] = a;
+      }
+#undef A_
+#undef AD_
+  }
 }
 
-template <int DIM, int P>
+// VISC: mfem::VectorDiffusionIntegrator::AssembleElementMatrix (bilininteg.cpp:2854-2934) instead of the mass:
+//   rule DiffusionIntegrator::GetRule = IntRules.Get(geom, 2p + dim - 1);  w = (ip.weight / Trans.Weight()) * coef;
+//   dshapedxt = dshape adj(J);  pelmat(i, j) = w * sum_k dshapedxt(i, k) dshapedxt(j, k)  (Mult_a_AAt);  elmat += pelmat
+template <int DIM, int P, bool VISC>
 __global__ void __launch_bounds__(MASS_NT) k_mass_element(const MassArgs g) {
   constexpr int P1 = P + 1;
   constexpr int ND = (DIM == 3) ? P1 * P1 * P1 : P1 * P1;
   constexpr int TD = DIM * ND;
   constexpr int KP = (TD * DIM + 3) / 4 * 4;
   constexpr int NACC = (ND * ND + MASS_NT - 1) / MASS_NT;
-  __shared__ double sN[MASS_QB][ND];
-  __shared__ double sNorm[MASS_QB];
+  constexpr int QB = VISC ? MASS_QB / 2 : MASS_QB;  // dshapedxt rows are DIM times longer
+  constexpr int ROW = VISC ? ND * DIM : ND;
+  __shared__ double sN[QB][ROW];
+  __shared__ double sNorm[QB];
   const int nq1 = g.nq1;
   const int nq = (DIM == 3) ? nq1 * nq1 * nq1 : nq1 * nq1;
   const int t = threadIdx.x;
@@ -435,12 +470,12 @@ __global__ void __launch_bounds__(MASS_NT) k_mass_element(const MassArgs g) {
     double acc[NACC];
 #pragma unroll
     for (int k = 0; k < NACC; k++) acc[k] = 0.0;
-    for (int q0 = 0; q0 < nq; q0 += MASS_QB) {
-      const int nb = min(MASS_QB, nq - q0);
+    for (int q0 = 0; q0 < nq; q0 += QB) {
+      const int nb = min(QB, nq - q0);
       if (t < nb) {
         double w, dj;
-        mass_point<DIM, P>(g, vd, e, q0 + t, sN[t], &w, &dj);
-        sNorm[t] = (w * dj) * g.rho;
+        mass_point<DIM, P, VISC>(g, vd, e, q0 + t, sN[t], &w, &dj);
+        sNorm[t] = VISC ? (w / dj) * g.rho : (w * dj) * g.rho;
       }
       __syncthreads();
 #pragma unroll
@@ -449,7 +484,15 @@ __global__ void __launch_bounds__(MASS_NT) k_mass_element(const MassArgs g) {
         if (idx < ND * ND) {
           const int i = idx % ND, j = idx / ND;
           double a = acc[k];
-          for (int s = 0; s < nb; s++) a += (sN[s][i] * sN[s][j]) * sNorm[s];
+          if (VISC) {
+            for (int s = 0; s < nb; s++) {
+              double d = 0.0;
+              for (int k = 0; k < DIM; k++) d += sN[s][i + k * ND] * sN[s][j + k * ND];
+              a += sNorm[s] * d;
+            }
+          } else {
+            for (int s = 0; s < nb; s++) a += (sN[s][i] * sN[s][j]) * sNorm[s];
+          }
           acc[k] = a;
         }
       }
@@ -537,7 +580,11 @@ int launch_mass_element(mb2_ctx* c, int64_t e0, int64_t e1, double* KeT, double*
   const unsigned grid = (unsigned)std::min<int64_t>(ne, (int64_t)c->sm_count * 8);
   const int dim = c->dim, p = T->p;
   bool ok = true;
-#define MB2_MASS(D, PP) if (dim == D && p == PP) k_mass_element<D, PP><<<grid, MASS_NT, 0, st>>>(a); else
+#define MB2_MASS(D, PP)                                                      \
+  if (dim == D && p == PP) {                                                 \
+    if (T->mode == 2) k_mass_element<D, PP, true><<<grid, MASS_NT, 0, st>>>(a); \
+    else k_mass_element<D, PP, false><<<grid, MASS_NT, 0, st>>>(a);          \
+  } else
   MB2_MASS(3, 1) MB2_MASS(3, 2) MB2_MASS(3, 3) MB2_MASS(2, 1) MB2_MASS(2, 2) MB2_MASS(2, 3) MB2_MASS(2, 4) { ok = false; }
 #undef MB2_MASS
   if (!ok) { c->err = "no mass kernel for this (dim, p)"; return MB2_ERR_UNSUPPORTED; }
@@ -562,7 +609,7 @@ static int assemble_form(mb2_ctx* c, int mode, int p, const int32_t* ncp, const 
   if (nd != c->nd) { c->err = "(p+1)^dim does not match nd of the connectivity"; return MB2_ERR_ARG; }
   if (!c->d_xref) { c->err = "call mb2_set_nodes first"; return MB2_ERR_ARG; }
   if (!c->have_pattern) { c->err = "call mb2_build_pattern first"; return MB2_ERR_ARG; }
-  const int order = quad_order >= 0 ? quad_order : (mode == 0 ? 2 * p + (p * dim - 1) : 2 * p);
+  const int order = quad_order >= 0 ? quad_order : (mode == 0 ? 2 * p + (p * dim - 1) : mode == 2 ? 2 * p + dim - 1 : 2 * p);
   MassTab T;
   T.p = p;
   T.mode = mode;
@@ -594,7 +641,7 @@ static int assemble_form(mb2_ctx* c, int mode, int p, const int32_t* ncp, const 
     MB2_CUDA(cudaStreamSynchronize(c->stream));
     for (int d = 0; d < dim; d++) cudaFree(d_knot[d]);
     c->mass_tab = &T;
-    int r = mode == 0 ? launch_residual_and_grad(c, 1.0, nullptr, nullptr) : launch_residual(c);
+    int r = mode != 1 ? launch_residual_and_grad(c, 1.0, nullptr, nullptr) : launch_residual(c);
     if (r) return r;
     MB2_CUDA(cudaStreamSynchronize(c->stream));
     return MB2_OK;
@@ -608,6 +655,10 @@ static int assemble_form(mb2_ctx* c, int mode, int p, const int32_t* ncp, const 
 int assemble_mass(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk, int quad_order,
                   double rho) {
   return assemble_form(c, 0, p, ncp, knots, el_ijk, quad_order, rho, nullptr);
+}
+int assemble_viscosity(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
+                       int quad_order, double coef) {
+  return assemble_form(c, 2, p, ncp, knots, el_ijk, quad_order, coef, nullptr);
 }
 int assemble_body_force(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
                         int quad_order, const double* f) {

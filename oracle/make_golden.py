@@ -168,8 +168,8 @@ BODY_FORCE = (0.3, -1.7, 0.9)      # the constant force oracle/ref_harness.cpp p
 
 
 def bodyforce_main():
-    """tests/golden/bodyforce.npz: mfem::VectorDomainLFIntegrator of a constant body force (harness mode 'dump',
-    bodyforce.f64) for every base fixture; the meshes / numbering are those of the fixtures of the same name."""
+    """tests/golden/forms.npz: mfem::VectorDomainLFIntegrator of a constant body force (harness mode 'dump',
+    bodyforce.f64) and the mfem::VectorDiffusionIntegrator viscosity matrix (viscform.f64) for every base fixture; the meshes / numbering are those of the fixtures of the same name."""
     out = {"f": np.array(BODY_FORCE)}
     for name, (writer, elevate, refine, gf) in CASES.items():
         with tempfile.TemporaryDirectory() as tmp:
@@ -179,7 +179,9 @@ def bodyforce_main():
             base = np.load(os.path.join(OUT, name + ".npz"))
             assert np.array_equal(D["mass"], base["mass"]) and np.array_equal(D["x_ref"], base["x_ref"])
             out[name] = D["bodyforce"]
-    np.savez_compressed(os.path.join(OUT, "bodyforce.npz"), **out)
+            out["visc_" + name] = D["viscform"]         # VectorDiffusionIntegrator(0.37) on the fixture's pattern
+    out["viscosity"] = np.float64(0.37)
+    np.savez_compressed(os.path.join(OUT, "forms.npz"), **out)
     print("bodyforce", {k: v.shape for k, v in out.items()})
 
 

@@ -419,6 +419,16 @@ int main(int argc, char** argv) {
       lf.Assemble();
       dump(out, "bodyforce.f64", lf.GetData(), (size_t)NV);
     }
+    {  // viscosity form as PyNonlinearSolid::Setup builds it (py_nonlinear_solid.cpp:174-191), coefficient 0.37
+      mfem::BilinearForm visc(s.fes.get());
+      mfem::ConstantCoefficient v_coef(0.37);
+      visc.AddDomainIntegrator(new mfem::VectorDiffusionIntegrator(v_coef));
+      visc.Assemble(0);
+      visc.Finalize(0);
+      visc.SpMat().SortColumnIndices();
+      if (visc.SpMat().NumNonZeroElems() != nnz) { std::fprintf(stderr, "viscosity pattern != sparsity pattern\n"); return 3; }
+      dump(out, "viscform.f64", visc.SpMat().GetData(), (size_t)nnz);
+    }
     r2 = 0.0;
     s.integ->AddDomainResidualAndGrad(u, gf, r2, A);
     dump(out, "r2.f64", r2.GetData(), (size_t)NV);

@@ -1,5 +1,6 @@
-"""GPU: mass matrix and body-force vector assembled on the device. The body-force vector
-(mb2_assemble_body_force_device) is bit-identical to the reference's mfem::VectorDomainLFIntegrator (tests/golden/bodyforce.npz,
+"""GPU: mass matrix, viscosity matrix and body-force vector assembled on the device. The viscosity
+matrix (mb2_assemble_viscosity_device) is bit-identical to the reference's mfem::VectorDiffusionIntegrator. The body-force vector
+(mb2_assemble_body_force_device) is bit-identical to the reference's mfem::VectorDomainLFIntegrator (tests/golden/forms.npz,
 oracle/make_golden.py bodyforce). The mass matrix (mb2_assemble_mass_device) is BIT-identical to
 what the compiled reference dumps after  mass->AddDomainIntegrator(new mfem::VectorMassIntegrator(rho));
 mass->Assemble(0)  (src/mimi/py/py_nonlinear_solid.cpp:154-172; oracle/ref_harness.cpp dumps `mass` into every golden
@@ -147,7 +148,7 @@ BF = {k: v for k, v in FIX.items() if not k.startswith("contact_")}
 def bodyforce():
     import os
     from tests.cases import GOLDEN
-    z = np.load(os.path.join(GOLDEN, "bodyforce.npz"))
+    z = np.load(os.path.join(GOLDEN, "forms.npz"))
     return {k: z[k] for k in z.files}
 
 
@@ -171,6 +172,41 @@ def test_body_force_bit_exact_vs_reference(ctx_factory, name):
     for c in range(D["dim"]):
         assert abs(b[c::D["dim"]].sum() - G["f"][c] * vol) < 1e-12 * max(1.0, vol)
     print("\n[body force %s] %d entries bit-equal to the reference's VectorDomainLFIntegrator" % (name, b.size))
+
+
+@pytest.mark.parametrize("name", sorted(BF))
+def test_viscosity_bit_exact_vs_reference(ctx_factory, name):
+    """mb2_assemble_viscosity_device against the reference's mfem::VectorDiffusionIntegrator matrix (forms.npz, visc_*)."""
+    D = load_golden(name)
+    G = bodyforce()
+    p = BF[name]
+    ctx = ctx_factory()
+    setup(ctx, D)
+    ncp, knots, ijk = patch_of(D, p)
+    ctx.set_A(None)
+    ctx.assemble_viscosity_device(p, ncp, knots, ijk, float(G["viscosity"]))
+    S = ctx.get_A()
+    ref = G["visc_" + name]
+    assert np.abs(ref).max() > 0
+    assert np.array_equal(S, ref), "max |dS| = %.3e" % np.abs(S - ref).max()
+    # a diffusion matrix annihilates constants: every row sums to ~0 over each component block
+    rows = np.repeat(np.arange(D["NV"]), np.diff(D["I"]))
+    rs = np.zeros(D["NV"])
+    np.add.at(rs, rows, S)
+    assert np.abs(rs).max() < 1e-11 * np.abs(S).max()
+    # FormSystemMatrix elimination when it becomes the viscosity of the Newton sweeps
+    xr = D["x_ref"].reshape(-1, D["dim"])
+    nodes = np.nonzero(xr[:, 0] == 0.0)[0]
+    ess = np.sort(np.concatenate([D["dim"] * nodes + c for c in range(D["dim"])])).astype(np.int32)
+    ctx.set_essential_dofs(ess)
+    ctx.newton_viscosity_from_A(True)
+    is_ess = np.zeros(D["NV"], bool)
+    is_ess[ess] = True
+    want = ref.copy()
+    want[is_ess[rows] | is_ess[D["J"]]] = 0.0
+    want[(rows == D["J"]) & is_ess[rows]] = 1.0
+    assert np.array_equal(ctx.newton_get_viscosity(), want)
+    print("\n[viscosity %s] %d CSR values bit-equal to the reference's VectorDiffusionIntegrator" % (name, S.size))
 
 
 def test_body_force_becomes_newton_rhs_and_drives_the_beam(ctx_factory):
