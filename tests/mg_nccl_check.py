@@ -43,7 +43,24 @@ def main():
             ctx.assemble_residual_device()
             ok = ok and np.array_equal(ctx.get_r()[rows], D["r_neohookean"][rows])
             ok_all = ok_all and ok
-        print("rank %d/%d %s: %s (own %d elements, %d ghosts, %d owned rows)" % (rank, world, name, "OK" if ok else "MISMATCH",
+        # the setup forms ride the same pipelines and the same ghost exchange: mass / viscosity (K_e blocks), body force (R_e)
+        from tests.test_gpu_mass import bodyforce, patch_of
+        G = bodyforce()
+        ncp, knots, ijk = patch_of(D, 2)
+        mine = ijk[loc[:R["n_compute"]]]
+        ctx.set_nodes(D["x_ref"], None)
+        ctx.set_A(None)
+        ctx.assemble_mass_device(2, ncp, knots, mine)
+        ok = np.array_equal(ctx.get_A(), D["mass"][idx])
+        ctx.set_A(None)
+        ctx.assemble_viscosity_device(2, ncp, knots, mine, float(G["viscosity"]))
+        ok = ok and np.array_equal(ctx.get_A(), G["visc_" + name][idx])
+        ctx.set_r(None)
+        ctx.assemble_body_force_device(2, ncp, knots, mine, G["f"])
+        ok = ok and np.array_equal(ctx.get_r()[rows], G[name][rows])
+        ok_all = ok_all and ok
+        print("rank %d/%d %s forms (mass, viscosity, body force): %s" % (rank, world, name, "OK" if ok else "MISMATCH"), flush=True)
+        print("rank %d/%d %s: %s (own %d elements, %d ghosts, %d owned rows)" % (rank, world, name, "OK" if ok_all else "MISMATCH",
               R["n_compute"], len(loc) - R["n_compute"], int(rows.sum())), flush=True)
         ctx.close()
     t = torch.tensor([int(ok_all)], device="cuda")
