@@ -137,7 +137,7 @@ def lame(young=2100.0, poisson=0.3):
 
 
 def build_oracle(force=False):
-    srcs = [os.path.join(HERE, x) for x in ("mimi_oracle.c", "mimi_oracle_contact.c", "mimi_oracle_eig.c")]
+    srcs = [os.path.join(HERE, x) for x in ("mimi_oracle.c", "mimi_oracle_contact.c", "mimi_oracle_eig.c", "mimi_oracle_forms.c")]
     if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(x) for x in srcs):
         subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", LIB] + srcs + ["-lm"])
     return LIB
@@ -624,3 +624,66 @@ def run_ref_gmres(I, J, A, b, workdir):
     subprocess.check_call([REF_BIN, "gmres", workdir, str(len(I) - 1), str(len(J)), "-", "0", workdir, "-"],
                           stdout=subprocess.DEVNULL)
     return np.fromfile(os.path.join(workdir, "x.f64")), np.fromfile(os.path.join(workdir, "info.f64"))
+
+
+# ---------------------------------------------------------------- setup forms (oracle/mimi_oracle_forms.c)
+def _knot_ptrs(knots):
+    kv = [np.ascontiguousarray(k, np.float64) for k in knots]
+    return kv, (C.c_void_p * len(kv))(*[k.ctypes.data for k in kv])
+
+
+def form_element_matrices(kind, dim, p, v_dofs, el_ijk, knots, x_ref, coef=1.0, weights=None, quad_order=-1):
+    """Scalar element blocks [NE, nd, nd] of mfem::VectorMassIntegrator (kind 0) / VectorDiffusionIntegrator (kind 2)."""
+    vd = np.ascontiguousarray(v_dofs, np.int32)
+    ijk = np.ascontiguousarray(el_ijk, np.int32)
+    NE, nd = vd.shape[0], (p + 1) ** dim
+    kv, arr = _knot_ptrs(knots)
+    x = np.ascontiguousarray(x_ref, np.float64)
+    w = None if weights is None else np.ascontiguousarray(weights, np.float64)
+    out = np.empty((NE, nd, nd))
+    rc = lib().orc_form_element_matrices(C.c_int(kind), C.c_int(dim), C.c_int(p), C.c_int64(NE), _p(vd, C.c_int32),
+                                         _p(ijk, C.c_int32), arr, _p(x, C.c_double),
+                                         None if w is None else _p(w, C.c_double), C.c_int(quad_order), C.c_double(coef),
+                                         _p(out, C.c_double))
+    assert rc == 0
+    return out
+
+
+def form_element_vectors(dim, p, v_dofs, el_ijk, knots, x_ref, force, weights=None, quad_order=-1):
+    """Element vectors [NE, dim*nd] of mfem::VectorDomainLFIntegrator for a constant body force."""
+    vd = np.ascontiguousarray(v_dofs, np.int32)
+    ijk = np.ascontiguousarray(el_ijk, np.int32)
+    NE, nd = vd.shape[0], (p + 1) ** dim
+    kv, arr = _knot_ptrs(knots)
+    x = np.ascontiguousarray(x_ref, np.float64)
+    w = None if weights is None else np.ascontiguousarray(weights, np.float64)
+    f = np.ascontiguousarray(force, np.float64)
+    out = np.empty((NE, dim * nd))
+    rc = lib().orc_form_element_vectors(C.c_int(dim), C.c_int(p), C.c_int64(NE), _p(vd, C.c_int32), _p(ijk, C.c_int32), arr,
+                                        _p(x, C.c_double), None if w is None else _p(w, C.c_double), C.c_int(quad_order),
+                                        _p(f, C.c_double), _p(out, C.c_double))
+    assert rc == 0
+    return out
+
+
+def assemble_bilinear_form(dim, nd, v_dofs, I, J, Me):
+    """BilinearForm::Assemble(0): element blocks added into the CSR in ascending element order, the same scalar block on
+    every diagonal component block (AddSubMatrix also adds the zeros between components: no effect on the values)."""
+    A = np.zeros(len(J))
+    vd = np.asarray(v_dofs).reshape(len(Me), dim, nd)
+    for e in range(len(Me)):
+        for c in range(dim):
+            rows = vd[e, c]
+            for a in range(nd):
+                r = rows[a]
+                pos = I[r] + np.searchsorted(J[I[r]:I[r + 1]], rows)
+                A[pos] += Me[e, a]
+    return A
+
+
+def assemble_linear_form(NV, v_dofs, be):
+    """LinearForm::Assemble: element vectors added in ascending element order."""
+    b = np.zeros(NV)
+    for e in range(len(be)):
+        b[np.asarray(v_dofs[e])] += be[e]      # the vdofs of one element are distinct
+    return b

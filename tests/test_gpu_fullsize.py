@@ -159,7 +159,7 @@ def test_c3_full_size_properties(ctx_factory):
     del A0
 
     # ---- 6. mass matrix at full size (mb2_assemble_mass_device; bit-exact against the reference on the fixtures,
-    #         tests/test_gpu_mass.py): corner block == the 5^3 patch's bit for bit (locality), partition of unity
+    #         tests/test_gpu_mass.py): corner block == the ORACLE's mass of the 5^3 patch bit for bit (locality), partition of unity
     import time
     ctx.set_A(None)
     t0 = time.perf_counter()
@@ -167,9 +167,11 @@ def test_c3_full_size_properties(ctx_factory):
     ctx.sync()
     t_mass = time.perf_counter() - t0
     Mb = ctx.get_A()
+    Ms = O.assemble_bilinear_form(3, S["nd"], S["v_dofs"], I_s, J_s,
+                                  O.form_element_matrices(0, 3, P, S["v_dofs"], S["el_ijk"], S["knots"], S["x_ref"]))
     cs.set_A(None)
     cs.assemble_mass_device(P, S["ncp"], S["knots"], S["el_ijk"])
-    Ms = cs.get_A()
+    assert np.array_equal(cs.get_A(), Ms)          # device == oracle on the small patch
     mchecked = 0
     for a in range(3):
         for b in range(3):
@@ -186,7 +188,7 @@ def test_c3_full_size_properties(ctx_factory):
     assert abs(total - 3.0) < 1e-9, total            # 3 component blocks x volume 1
     assert Mb.min() >= 0.0                            # B-splines are non-negative
     del Mb
-    print("\n[full size] mass 100^3: %d corner entries bit-equal to the small patch, sum = 3 + %.1e, %.0f ms incl. tables"
+    print("\n[full size] mass 100^3: %d corner entries bit-equal to the oracle, sum = 3 + %.1e, %.0f ms incl. tables"
           % (mchecked, total - 3.0, 1e3 * t_mass))
     print("\n[full size] C3 100^3: corner block %d CSR entries bit-equal to the oracle; determinism, gf linearity, "
           "adds-into and u = 0 properties hold (translation row sums <= %.1e of the largest entry); launches per "

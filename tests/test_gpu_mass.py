@@ -236,3 +236,32 @@ def test_body_force_becomes_newton_rhs_and_drives_the_beam(ctx_factory):
     for i in range(10):
         assert np.allclose(beam.step(), ref[i]), i               # the reference's own assertion
     _ = O
+
+
+def test_forms_with_nurbs_weights_vs_oracle(ctx_factory):
+    """Rational basis (NURBS weights != 1; no reference fixture has them): device == CPU oracle bit for bit, the oracle
+    itself being pinned against the reference on the unit-weight fixtures (tests/test_oracle_forms.py)."""
+    from oracle import oracle_py as O
+    D = load_golden("cube_p2_n2")
+    G = bodyforce()
+    dim, nd, p = D["dim"], D["nd"], 2
+    w = np.random.default_rng(11).uniform(0.7, 1.3, D["NV"] // dim)
+    ctx = ctx_factory()
+    ctx.set_connectivity(dim, nd, D["nq"], D["NV"], D["v_dofs"])
+    ctx.set_nodes(D["x_ref"], w)
+    ctx.build_pattern()
+    ncp, knots, ijk = patch_of(D, p)
+    for kind, coef, run in ((0, 1.7, lambda: ctx.assemble_mass_device(p, ncp, knots, ijk, density=1.7)),
+                            (2, 0.37, lambda: ctx.assemble_viscosity_device(p, ncp, knots, ijk, 0.37))):
+        ctx.set_A(None)
+        run()
+        want = O.assemble_bilinear_form(dim, nd, D["v_dofs"], D["I"], D["J"],
+                                        O.form_element_matrices(kind, dim, p, D["v_dofs"], ijk, knots, D["x_ref"], coef=coef,
+                                                                weights=w))
+        assert np.array_equal(ctx.get_A(), want), kind
+        assert not np.array_equal(want, D["mass"])
+    ctx.set_r(None)
+    ctx.assemble_body_force_device(p, ncp, knots, ijk, G["f"])
+    want = O.assemble_linear_form(D["NV"], D["v_dofs"], O.form_element_vectors(dim, p, D["v_dofs"], ijk, knots, D["x_ref"],
+                                                                               G["f"], weights=w))
+    assert np.array_equal(ctx.get_r(), want)
