@@ -144,6 +144,71 @@ public:
   /// commits the device-resident history (no-op for stateless materials)
   void DomainPostTimeAdvance(const mfem::Vector& u) override { Check(mb2_post_time_advance(ctx_, u.GetData())); }
 
+  // ---- the forms PyNonlinearSolid::Setup assembles with MFEM (py_nonlinear_solid.cpp:154-191, 221-241), on the device ----
+  /// knot vectors / control-point counts / knot-span indices of the single tensor-product patch (mesh/nurbs.hpp:556-879)
+  struct Patch {
+    int p{0};
+    std::vector<int> ncp, ijk;
+    std::vector<std::vector<double>> kv;
+    std::vector<const double*> knots;
+  };
+  Patch DescribePatch(mfem::Mesh& mesh) const {
+    mfem::NURBSExtension* ext = mesh.NURBSext;
+    if (!ext || ext->GetNP() != 1) mimi::utils::PrintAndThrowError("mimi_b200: device forms need a single-patch NURBS mesh");
+    const int dim = mesh.Dimension();
+    mfem::Array<const mfem::KnotVector*> kvs;
+    ext->GetPatchKnotVectors(0, kvs);
+    Patch P;
+    P.p = kvs[0]->GetOrder();
+    P.kv.resize(dim);
+    for (int d = 0; d < dim; ++d) {
+      if (kvs[d]->GetOrder() != P.p) mimi::utils::PrintAndThrowError("mimi_b200: mixed degrees are not supported");
+      P.ncp.push_back(kvs[d]->GetNCP());
+      for (int i = 0; i < kvs[d]->Size(); ++i) P.kv[d].push_back((*kvs[d])[i]);
+    }
+    for (int d = 0; d < dim; ++d) P.knots.push_back(P.kv[d].data());
+    mfem::Array<int> ijk(dim);
+    for (int e = 0; e < mesh.GetNE(); ++e) {
+      ext->GetElementIJK(e, ijk);
+      for (int d = 0; d < dim; ++d) P.ijk.push_back(ijk[d]);
+    }
+    return P;
+  }
+  /// node coordinates (byVDIM) and NURBS weights -> mb2_set_nodes
+  void SetNodes(mfem::Mesh& mesh) const {
+    const mfem::GridFunction& nodes = *mesh.GetNodes();
+    const int dim = mesh.Dimension(), nn = nodes.Size() / dim;
+    std::vector<double> x(nodes.GetData(), nodes.GetData() + nodes.Size());
+    if (nodes.FESpace()->GetOrdering() == mfem::Ordering::byNODES)
+      for (int a = 0; a < nn; ++a)
+        for (int c = 0; c < dim; ++c) x[size_t(a) * dim + c] = nodes(c * nn + a);
+    Check(mb2_set_nodes(ctx_, x.data(), mesh.NURBSext->GetWeights().GetData()));
+  }
+  /// M <- VectorMassIntegrator(rho); M must carry the library's pattern (a copy of precomputed_->sparsity_pattern_)
+  void AssembleMass(mfem::Mesh& mesh, const double rho, mfem::SparseMatrix& M) const {
+    const Patch P = DescribePatch(mesh);
+    SetNodes(mesh);
+    Check(mb2_set_A(ctx_, nullptr));
+    Check(mb2_assemble_mass_device(ctx_, P.p, P.ncp.data(), P.knots.data(), P.ijk.data(), -1, rho));
+    Check(mb2_get_A(ctx_, M.GetData()));
+  }
+  /// S <- VectorDiffusionIntegrator(viscosity)
+  void AssembleViscosity(mfem::Mesh& mesh, const double viscosity, mfem::SparseMatrix& S) const {
+    const Patch P = DescribePatch(mesh);
+    SetNodes(mesh);
+    Check(mb2_set_A(ctx_, nullptr));
+    Check(mb2_assemble_viscosity_device(ctx_, P.p, P.ncp.data(), P.knots.data(), P.ijk.data(), -1, viscosity));
+    Check(mb2_get_A(ctx_, S.GetData()));
+  }
+  /// b <- VectorDomainLFIntegrator(constant force)
+  void AssembleBodyForce(mfem::Mesh& mesh, const mfem::Vector& force, mfem::Vector& b) const {
+    const Patch P = DescribePatch(mesh);
+    SetNodes(mesh);
+    Check(mb2_set_r(ctx_, nullptr));
+    Check(mb2_assemble_body_force_device(ctx_, P.p, P.ncp.data(), P.knots.data(), P.ijk.data(), -1, force.GetData()));
+    Check(mb2_get_r(ctx_, b.GetData()));
+  }
+
   /// history variables [NE][nq][mb2_state_size] (checkpoints, tests); empty for stateless materials
   std::vector<double> State() const {
     const int ns = mb2_state_size(ctx_);

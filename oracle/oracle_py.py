@@ -236,7 +236,7 @@ def load_dump(d):
     out["state"] = rd("state.f64", np.float64)
     if out["state"] is not None:
         out["state"] = out["state"].reshape(NE, nq, -1)
-    for k in ("x_ref", "u", "r", "r2", "mass", "bodyforce", "viscform", "A", "r_b", "A_b"):
+    for k in ("x_ref", "u", "r", "r2", "mass", "bodyforce", "viscform", "mass_b200", "viscform_b200", "bodyforce_b200", "A", "r_b", "A_b"):
         out[k] = rd(k + ".f64", np.float64)
     return out
 

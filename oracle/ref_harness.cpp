@@ -429,6 +429,20 @@ int main(int argc, char** argv) {
       if (visc.SpMat().NumNonZeroElems() != nnz) { std::fprintf(stderr, "viscosity pattern != sparsity pattern\n"); return 3; }
       dump(out, "viscform.f64", visc.SpMat().GetData(), (size_t)nnz);
     }
+#ifdef MIMI_REF_USE_B200  // the same three forms through the adapter (device assembly), dumped beside MFEM's
+    {
+      mfem::SparseMatrix Mb(sp), Sb(sp);
+      s.integ->AssembleMass(*s.mesh, s.mat->density_, Mb);
+      dump(out, "mass_b200.f64", Mb.GetData(), (size_t)nnz);
+      s.integ->AssembleViscosity(*s.mesh, 0.37, Sb);
+      dump(out, "viscform_b200.f64", Sb.GetData(), (size_t)nnz);
+      mfem::Vector fv(dim), bb(NV);
+      const double fc[3] = {0.3, -1.7, 0.9};
+      for (int c = 0; c < dim; ++c) fv[c] = fc[c];
+      s.integ->AssembleBodyForce(*s.mesh, fv, bb);
+      dump(out, "bodyforce_b200.f64", bb.GetData(), (size_t)NV);
+    }
+#endif
     r2 = 0.0;
     s.integ->AddDomainResidualAndGrad(u, gf, r2, A);
     dump(out, "r2.f64", r2.GetData(), (size_t)NV);

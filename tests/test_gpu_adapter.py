@@ -51,6 +51,19 @@ def test_reference_chain_through_the_adapter_bit_exact(name, material):
         assert np.array_equal(D["r_b"], G["rb_j2linear"]) and np.array_equal(D["A_b"], G["Ab_j2linear"])
 
 
+@pytest.mark.parametrize("name", list(RECIPES))
+def test_setup_forms_through_the_adapter_bit_exact(name):
+    """B200NonlinearSolid::AssembleMass / AssembleViscosity / AssembleBodyForce (patch description taken from the
+    reference's own NURBSExtension) against MFEM's VectorMassIntegrator / VectorDiffusionIntegrator /
+    VectorDomainLFIntegrator in the same process, on the same mesh."""
+    G = load_golden(name)
+    D = run_adapter(name, "neohookean", G["gf"])
+    assert np.array_equal(D["mass"], G["mass"])
+    assert np.array_equal(D["mass_b200"], D["mass"])
+    assert np.array_equal(D["viscform_b200"], D["viscform"]) and np.abs(D["viscform"]).max() > 0
+    assert np.array_equal(D["bodyforce_b200"], D["bodyforce"]) and np.abs(D["bodyforce"]).max() > 0
+
+
 def _rel(a, b):
     return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
 
