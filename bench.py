@@ -319,8 +319,22 @@ def gpu_arm(args):
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         tdof = 3 * M["nd"]
         bytes_el = NE * (8.0 * nq * (tdof + 1) + 4 * tdof + 8 * tdof + 8 * tdof * tdof + 8 * tdof)
+        # DRAM traffic of the dominant kernel from the one `ncu --set full` capture of it (profiles/r01_elem_v4_summary.txt:
+        # a 4096-element launch, dram__bytes_read.sum 173.53 MB + dram__bytes_write.sum 165.42 MB; algorithmic 172.0 MB of
+        # tables read -- no re-reads -- and 215.9 MB of K_e written, of which the tail is still in L2 when the kernel ends),
+        # scaled to the elements one launch of this run processes. Only the p=2 kernel has a capture at this revision.
+        traffic = traffic_note = None
+        try:
+            chunk_elems, n_chunks = ctx.plan_info()
+            if p == 2:
+                traffic = (173.530880e6 + 165.421056e6) / 4096.0 * min(chunk_elems, NE)
+                traffic_note = ("bytes per element-kernel launch (%d elements; %d launches per step), scaled from the 4096-element "
+                                "ncu --set full capture in profiles/r01_elem_v4_summary.txt; algorithmic %.3e" % (
+                                    min(chunk_elems, NE), n_chunks, bytes_el / NE * min(chunk_elems, NE)))
+        except Exception:
+            pass
         roofline = {"bound": "fp64", "kernel": ("element_fd_kernel<3,27,64,%s>" if p == 2 else "element_fd_split_kernel<3,64,125,%s,4>") % args.material, "achieved": achieved, "peak": peak_nofma,
-                    "unit": "TFLOP/s", "frac": achieved / peak_nofma, "traffic": None,
+                    "unit": "TFLOP/s", "frac": achieved / peak_nofma, "traffic": traffic, "traffic_note": traffic_note,
                     "peak_source": "mb2_measure_fp64_peak(fma=0) on this GPU in this run: DMUL+DADD pairs = the only "
                                    "mix a bit-exact non-FMA kernel may issue (DFMA peak %.2f; MEASURED_PEAKS.json has no FP64 entry)" % peak_fma,
                     "flop_per_qp_executed": exe_qp, "flop_per_qp_algorithmic": alg + fd / nq,

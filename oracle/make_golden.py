@@ -180,7 +180,16 @@ def bodyforce_main():
             assert np.array_equal(D["mass"], base["mass"]) and np.array_equal(D["x_ref"], base["x_ref"])
             out[name] = D["bodyforce"]
             out["visc_" + name] = D["viscform"]         # VectorDiffusionIntegrator(0.37) on the fixture's pattern
+            # body force + traction in one LinearForm, and the face tables of the loaded boundary at the rule 2p
+            NF, ndf, nqf = (int(x) for x in D["t_meta"])
+            out["rhs_" + name] = D["rhs_bf_traction"]
+            out["tmeta_" + name] = D["t_meta"]
+            out["tvd_" + name] = D["t_v_dofs"].reshape(NF, -1)
+            out["tN_" + name] = D["t_N"].reshape(NF, nqf, ndf)
+            out["tw_" + name] = D["t_w"].reshape(NF, nqf)
+            out["tdet_" + name] = D["t_detW"].reshape(NF, nqf)
     out["viscosity"] = np.float64(0.37)
+    out["traction"] = np.array([0.5, -0.25, 1.5])
     np.savez_compressed(os.path.join(OUT, "forms.npz"), **out)
     print("bodyforce", {k: v.shape for k, v in out.items()})
 

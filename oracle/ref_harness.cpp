@@ -429,6 +429,49 @@ int main(int argc, char** argv) {
       if (visc.SpMat().NumNonZeroElems() != nnz) { std::fprintf(stderr, "viscosity pattern != sparsity pattern\n"); return 3; }
       dump(out, "viscform.f64", visc.SpMat().GetData(), (size_t)nnz);
     }
+    {  // body force + traction in ONE linear form, as PyNonlinearSolid::Setup assembles rhs (py_nonlinear_solid.cpp:221-282):
+       // traction (0.5, -0.25, 1.5) on the boundary elements of the highest attribute; and the tables of those faces the
+       // way the reference precomputes boundary data, at VectorBoundaryLFIntegrator's rule (order 2p)
+      const int attr = s.mesh->bdr_attributes.Max();
+      const double tv[3] = {0.5, -0.25, 1.5}, fv[3] = {0.3, -1.7, 0.9};
+      mfem::LinearForm lf(s.fes.get());
+      mfem::VectorArrayCoefficient bf(dim), tc(dim);
+      for (int c = 0; c < dim; ++c) {
+        bf.Set(c, new mfem::ConstantCoefficient(fv[c]));
+        mfem::Vector pw(attr);
+        pw = 0.0;
+        pw(attr - 1) = tv[c];
+        tc.Set(c, new mfem::PWConstCoefficient(pw));
+      }
+      lf.AddDomainIntegrator(new mfem::VectorDomainLFIntegrator(bf));
+      lf.AddBoundaryIntegrator(new mfem::VectorBoundaryLFIntegrator(tc));
+      lf.Assemble();
+      dump(out, "rhs_bf_traction.f64", lf.GetData(), (size_t)NV);
+      std::vector<int> marked;
+      for (int b = 0; b < s.mesh->GetNBE(); ++b)
+        if (s.mesh->GetBdrAttribute(b) == attr) marked.push_back(b);
+      const int p_order = s.fes->GetFE(0)->GetOrder();
+      pre.CreateBoundaryElementQuadData("traction", marked.data(), (int)marked.size());
+      pre.PrecomputeElementQuadData("traction", 2 * p_order, false);
+      auto& tq = pre.GetElementQuadData("traction");
+      const int NF = (int)tq.size(), ndf = tq[0].GetElementData().n_dof, tdf = tq[0].GetElementData().n_tdof, nqf = tq[0].n_quad;
+      std::vector<int> tvd((size_t)NF * tdf), tmeta = {NF, ndf, nqf};
+      std::vector<double> tw((size_t)NF * nqf), tdet((size_t)NF * nqf), tN((size_t)NF * nqf * ndf);
+      for (int f = 0; f < NF; ++f) {
+        std::memcpy(&tvd[(size_t)f * tdf], tq[f].GetElementData().v_dofs.GetData(), sizeof(int) * tdf);
+        for (int q = 0; q < nqf; ++q) {
+          const auto& qd = tq[f].GetQuadData()[q];
+          tw[(size_t)f * nqf + q] = qd.integration_weight;
+          tdet[(size_t)f * nqf + q] = qd.det_dX_dxi;
+          std::memcpy(&tN[((size_t)f * nqf + q) * ndf], qd.N.GetData(), sizeof(double) * ndf);
+        }
+      }
+      dump(out, "t_meta.i32", tmeta.data(), tmeta.size());
+      dump(out, "t_v_dofs.i32", tvd.data(), tvd.size());
+      dump(out, "t_w.f64", tw.data(), tw.size());
+      dump(out, "t_detW.f64", tdet.data(), tdet.size());
+      dump(out, "t_N.f64", tN.data(), tN.size());
+    }
 #ifdef MIMI_REF_USE_B200  // the same three forms through the adapter (device assembly), dumped beside MFEM's
     {
       mfem::SparseMatrix Mb(sp), Sb(sp);
