@@ -122,6 +122,15 @@ int mb2_assemble_viscosity_device(mb2_ctx* ctx, int p, const int32_t* ncp, const
  * or by mb2_newton_rhs_from_r. */
 int mb2_assemble_body_force_device(mb2_ctx* ctx, int p, const int32_t* ncp, const double* const* knots,
                                    const int32_t* el_ijk, int quad_order, const double* force);
+/* Traction linear form on the device: r = ((r + f_1) + f_2) + ... over the loaded faces in ascending order, f = what
+ * mfem::VectorBoundaryLFIntegrator contributes per boundary element (src/mimi/py/py_nonlinear_solid.cpp:243-276;
+ * third_party/mfem/fem/lininteg.cpp:375-408): elvect(ndf k + s) += (t_k * (Tr.Weight() * ip.weight)) * shape(s), bit for
+ * bit. Face tables as the reference precomputes boundary data at the integrator's rule (order 2p,
+ * PrecomputedData::PrecomputeElementQuadData, precomputed.cpp:264-330): face_vdofs NF x dim*ndf (component-major),
+ * N NF x nqf x ndf, w = integration_weight and detW = det_dX_dxi NF x nqf. traction: dim values (one loaded boundary per
+ * call). LinearForm::Assemble adds domain integrators first: call mb2_assemble_body_force_device before this one. */
+int mb2_assemble_traction_device(mb2_ctx* ctx, int64_t NF, int ndf, int nqf, const int32_t* face_vdofs, const double* N,
+                                 const double* w, const double* detW, const double* traction);
 /* Shape values N: NE x nq x nd (tests; contact). */
 int mb2_download_shape_values(mb2_ctx* ctx, double* N);
 

@@ -19,7 +19,7 @@ MB2_RIGID_PLANE, MB2_RIGID_SPHERE, MB2_RIGID_BEZIER, MB2_RIGID_BSPLINE = 0, 1, 2
 # every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "mb2_create", "mb2_destroy", "mb2_last_error", "mb2_version", "mb2_set_connectivity",
-    "mb2_upload_quad_tables", "mb2_set_nodes", "mb2_generate_patch_tables", "mb2_assemble_mass_device", "mb2_assemble_body_force_device", "mb2_assemble_viscosity_device", "mb2_newton_viscosity_from_A", "mb2_newton_get_viscosity", "mb2_newton_rhs_from_r", "mb2_newton_mass_from_A", "mb2_newton_get_mass", "mb2_download_shape_values", "mb2_download_quad_tables", "mb2_build_pattern",
+    "mb2_upload_quad_tables", "mb2_set_nodes", "mb2_generate_patch_tables", "mb2_assemble_mass_device", "mb2_assemble_body_force_device", "mb2_assemble_viscosity_device", "mb2_assemble_traction_device", "mb2_newton_viscosity_from_A", "mb2_newton_get_viscosity", "mb2_newton_rhs_from_r", "mb2_newton_mass_from_A", "mb2_newton_get_mass", "mb2_download_shape_values", "mb2_download_quad_tables", "mb2_build_pattern",
     "mb2_get_pattern_i32", "mb2_get_pattern_i64", "mb2_get_A_ids_i32", "mb2_set_material",
     "mb2_add_domain_residual", "mb2_add_domain_residual_and_grad", "mb2_set_u", "mb2_set_r", "mb2_set_A",
     "mb2_get_r", "mb2_get_A", "mb2_assemble_residual_device", "mb2_assemble_residual_and_grad_device",
@@ -136,6 +136,18 @@ class Context:
         arr = (C.c_void_p * len(kv))(*[k.ctypes.data for k in kv])
         self._ck(self.lib.mb2_assemble_body_force_device(self.h, C.c_int(p), _dp(ncp), arr, _dp(ijk), C.c_int(quad_order),
                                                          _dp(f)))
+
+    def assemble_traction_device(self, face_vdofs, N, w, detW, traction):
+        """r = ((r + f_1) + f_2) + ... (VectorBoundaryLFIntegrator of a constant traction on the uploaded faces)."""
+        vd = np.ascontiguousarray(face_vdofs, np.int32)
+        N = np.ascontiguousarray(N, np.float64)
+        w = np.ascontiguousarray(w, np.float64)
+        dw = np.ascontiguousarray(detW, np.float64)
+        t = np.ascontiguousarray(traction, np.float64)
+        NF, nqf, ndf = N.shape
+        assert vd.shape == (NF, self.dim * ndf) and w.shape == (NF, nqf) and dw.shape == (NF, nqf) and t.size == self.dim
+        self._ck(self.lib.mb2_assemble_traction_device(self.h, C.c_int64(NF), C.c_int(ndf), C.c_int(nqf), _dp(vd), _dp(N),
+                                                       _dp(w), _dp(dw), _dp(t)))
 
     def newton_rhs_from_r(self, zero_essential=True):
         self._ck(self.lib.mb2_newton_rhs_from_r(self.h, C.c_int(int(zero_essential))))

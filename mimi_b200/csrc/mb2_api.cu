@@ -498,6 +498,15 @@ int mb2_assemble_mass_device(mb2_ctx* c, int p, const int32_t* ncp, const double
   return mb2::assemble_mass(c, p, ncp, knots, el_ijk, quad_order, density);
 }
 
+int mb2_assemble_traction_device(mb2_ctx* c, int64_t NF, int ndf, int nqf, const int32_t* face_vdofs, const double* N,
+                                 const double* w, const double* detW, const double* traction) {
+  CHECK_CTX(c);
+  REQUIRE(c->NE > 0, "call mb2_set_connectivity first");
+  REQUIRE(face_vdofs && N && w && detW && traction, "null argument");
+  MB2_CUDA(cudaSetDevice(c->device));
+  return mb2::assemble_traction(c, NF, ndf, nqf, face_vdofs, N, w, detW, traction);
+}
+
 int mb2_assemble_viscosity_device(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
                                   int quad_order, double viscosity) {
   CHECK_CTX(c);

@@ -133,6 +133,8 @@ int assemble_body_force(mb2_ctx* c, int p, const int32_t* ncp, const double* con
 int launch_lform_element(mb2_ctx* c, int64_t e0, int64_t e1, double* Re, cudaStream_t st);
 int assemble_viscosity(mb2_ctx* c, int p, const int32_t* ncp, const double* const* knots, const int32_t* el_ijk,
                        int quad_order, double coef);
+int assemble_traction(mb2_ctx* c, int64_t NF, int ndf, int nqf, const int32_t* face_vdofs, const double* N, const double* w,
+                      const double* detW, const double* traction);
 int form_mode(const mb2_ctx* c);  // 0 mass, 1 body force, 2 viscosity (valid while mass_tab is set)
 }  // namespace mb2
 

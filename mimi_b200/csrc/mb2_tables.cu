@@ -15,6 +15,7 @@
 //                                 (kernels.hpp:244-251), kernels::Mult (kernels.hpp:341-357)
 #include <algorithm>
 #include <cmath>
+#include <utility>
 #include <vector>
 
 #include "mb2_ctx.h"
@@ -665,5 +666,95 @@ int assemble_body_force(mb2_ctx* c, int p, const int32_t* ncp, const double* con
   return assemble_form(c, 1, p, ncp, knots, el_ijk, quad_order, 1.0, f);
 }
 int form_mode(const mb2_ctx* c) { return static_cast<const MassTab*>(c->mass_tab)->mode; }
+
+
+// ---------------------------------------------------------------------------------------------
+// Traction linear form: mfem::VectorBoundaryLFIntegrator::AssembleRHSElementVect (third_party/mfem/fem/lininteg.cpp:375-408)
+// as PyNonlinearSolid::Setup adds it to rhs (src/mimi/py/py_nonlinear_solid.cpp:243-276), on face tables the caller
+// uploads the way the reference precomputes boundary data (CreateBoundaryElementQuadData + PrecomputeElementQuadData at the
+// integrator's rule, order 2p: QuadData::N, integration_weight, det_dX_dxi = Tr.Weight()):
+//   per point  vec = t;  vec *= Tr.Weight() * ip.weight;  elvect(ndf k + s) += vec(k) * shape(s)
+// LinearForm::Assemble adds the boundary elements after the domain ones, face by face ONTO the vector, so the gather
+// continues from the resident r:  r[v] = ((r[v] + f_1) + f_2) + ...  in ascending face order.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_traction_faces(int64_t NF, int dim, int ndf, int nqf, const double* __restrict__ N,
+                                 const double* __restrict__ w, const double* __restrict__ detW, double t0, double t1,
+                                 double t2, double* __restrict__ fe) {
+  const int tdf = dim * ndf;
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= NF * tdf) return;
+  const int64_t f = i / tdf;
+  const int l = (int)(i % tdf), k = l / ndf, s = l % ndf;
+  const double tk = k == 0 ? t0 : (k == 1 ? t1 : t2);
+  double acc = 0.0;
+  for (int q = 0; q < nqf; q++) {
+    const double vec = tk * (detW[f * nqf + q] * w[f * nqf + q]);
+    acc += vec * N[(f * nqf + q) * ndf + s];
+  }
+  fe[i] = acc;
+}
+
+// one thread per loaded vdof: entries (face-major ascending) ptr[j] .. ptr[j+1]
+__global__ void k_traction_gather(int64_t n, const int32_t* __restrict__ vdof, const int64_t* __restrict__ ptr,
+                                  const int64_t* __restrict__ src, const double* __restrict__ fe, double* __restrict__ r) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  double x = r[vdof[j]];
+  for (int64_t e = ptr[j]; e < ptr[j + 1]; e++) x += fe[src[e]];
+  r[vdof[j]] = x;
+}
+
+int assemble_traction(mb2_ctx* c, int64_t NF, int ndf, int nqf, const int32_t* face_vdofs, const double* N, const double* w,
+                      const double* detW, const double* traction) {
+  const int dim = c->dim, tdf = dim * ndf;
+  if (!c->d_r) { c->err = "call mb2_build_pattern first"; return MB2_ERR_ARG; }
+  if (NF <= 0 || ndf <= 0 || nqf <= 0) { c->err = "bad face table sizes"; return MB2_ERR_ARG; }
+  // vdof -> (face, local) entries in ascending face order (a face's vdofs are distinct)
+  std::vector<std::pair<int32_t, int64_t>> ent((size_t)NF * tdf);
+  for (int64_t i = 0; i < NF * tdf; i++) {
+    const int32_t v = face_vdofs[i];
+    if (v < 0 || v >= c->NV) { c->err = "face vdof out of range"; return MB2_ERR_ARG; }
+    ent[(size_t)i] = {v, i};
+  }
+  std::stable_sort(ent.begin(), ent.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+  std::vector<int32_t> vd;
+  std::vector<int64_t> ptr, src(ent.size());
+  for (size_t i = 0; i < ent.size(); i++) {
+    if (i == 0 || ent[i].first != ent[i - 1].first) { vd.push_back(ent[i].first); ptr.push_back((int64_t)i); }
+    src[i] = ent[i].second;
+  }
+  ptr.push_back((int64_t)ent.size());
+  const int64_t nv = (int64_t)vd.size();
+  double *d_N = nullptr, *d_w = nullptr, *d_det = nullptr, *d_fe = nullptr;
+  int32_t* d_vd = nullptr;
+  int64_t *d_ptr = nullptr, *d_src = nullptr;
+  int rc = [&]() -> int {
+    const size_t nfq = (size_t)NF * nqf;
+    MB2_CUDA(cudaMalloc(&d_N, sizeof(double) * nfq * ndf));
+    MB2_CUDA(cudaMalloc(&d_w, sizeof(double) * nfq));
+    MB2_CUDA(cudaMalloc(&d_det, sizeof(double) * nfq));
+    MB2_CUDA(cudaMalloc(&d_fe, sizeof(double) * NF * tdf));
+    MB2_CUDA(cudaMalloc(&d_vd, sizeof(int32_t) * nv));
+    MB2_CUDA(cudaMalloc(&d_ptr, sizeof(int64_t) * (nv + 1)));
+    MB2_CUDA(cudaMalloc(&d_src, sizeof(int64_t) * src.size()));
+    MB2_CUDA(cudaMemcpyAsync(d_N, N, sizeof(double) * nfq * ndf, cudaMemcpyHostToDevice, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(d_w, w, sizeof(double) * nfq, cudaMemcpyHostToDevice, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(d_det, detW, sizeof(double) * nfq, cudaMemcpyHostToDevice, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(d_vd, vd.data(), sizeof(int32_t) * nv, cudaMemcpyHostToDevice, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(d_ptr, ptr.data(), sizeof(int64_t) * (nv + 1), cudaMemcpyHostToDevice, c->stream));
+    MB2_CUDA(cudaMemcpyAsync(d_src, src.data(), sizeof(int64_t) * src.size(), cudaMemcpyHostToDevice, c->stream));
+    const double t2 = dim == 3 ? traction[2] : 0.0;
+    k_traction_faces<<<(unsigned)((NF * tdf + 255) / 256), 256, 0, c->stream>>>(NF, dim, ndf, nqf, d_N, d_w, d_det, traction[0],
+                                                                                traction[1], t2, d_fe);
+    MB2_CUDA(cudaGetLastError());
+    k_traction_gather<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(nv, d_vd, d_ptr, d_src, d_fe, c->d_r);
+    MB2_CUDA(cudaGetLastError());
+    MB2_CUDA(cudaStreamSynchronize(c->stream));
+    return MB2_OK;
+  }();
+  for (void* p : {(void*)d_N, (void*)d_w, (void*)d_det, (void*)d_fe, (void*)d_vd, (void*)d_ptr, (void*)d_src})
+    if (p) cudaFree(p);
+  return rc;
+}
 
 }  // namespace mb2

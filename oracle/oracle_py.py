@@ -689,3 +689,18 @@ def assemble_linear_form(NV, v_dofs, be):
     for e in range(len(be)):
         b[np.asarray(v_dofs[e])] += be[e]      # the vdofs of one element are distinct
     return b
+
+
+def add_traction_form(b, dim, face_vdofs, N, w, detW, traction):
+    """mfem::VectorBoundaryLFIntegrator (lininteg.cpp:375-408) on precomputed face tables, added face by face onto b the
+    way LinearForm::Assemble does after the domain integrators: vec = t; vec *= Tr.Weight() * ip.weight;
+    elvect(ndf k + s) += vec(k) * shape(s)."""
+    NF, nqf, ndf = N.shape
+    for f in range(NF):
+        el = np.zeros(dim * ndf)
+        for q in range(nqf):
+            c = detW[f, q] * w[f, q]
+            for k in range(dim):
+                el[k * ndf:(k + 1) * ndf] += (traction[k] * c) * N[f, q]
+        b[face_vdofs[f]] += el
+    return b

@@ -175,6 +175,33 @@ def test_body_force_bit_exact_vs_reference(ctx_factory, name):
 
 
 @pytest.mark.parametrize("name", sorted(BF))
+def test_rhs_body_force_plus_traction_bit_exact_vs_reference(ctx_factory, name):
+    """The reference's whole rhs linear form (VectorDomainLFIntegrator + VectorBoundaryLFIntegrator in one
+    LinearForm::Assemble, py_nonlinear_solid.cpp:221-282) on the device: body force through the residual gather, then
+    mb2_assemble_traction_device on the loaded faces' tables (dumped from the reference's boundary precompute)."""
+    from oracle import oracle_py as O
+    D = load_golden(name)
+    G = bodyforce()
+    p, dim = BF[name], D["dim"]
+    ctx = ctx_factory()
+    setup(ctx, D)
+    ncp, knots, ijk = patch_of(D, p)
+    ctx.set_r(None)
+    ctx.assemble_body_force_device(p, ncp, knots, ijk, G["f"][:dim])
+    ctx.assemble_traction_device(G["tvd_" + name], G["tN_" + name], G["tw_" + name], G["tdet_" + name], G["traction"][:dim])
+    rhs = ctx.get_r()
+    assert np.array_equal(rhs, G["rhs_" + name]), "max |d rhs| = %.3e" % np.abs(rhs - G["rhs_" + name]).max()
+    assert not np.array_equal(rhs, G[name])
+    # traction alone on a zero vector == the oracle's
+    ctx.set_r(None)
+    ctx.assemble_traction_device(G["tvd_" + name], G["tN_" + name], G["tw_" + name], G["tdet_" + name], G["traction"][:dim])
+    want = O.add_traction_form(np.zeros(D["NV"]), dim, G["tvd_" + name], G["tN_" + name], G["tw_" + name], G["tdet_" + name],
+                               G["traction"][:dim])
+    assert np.array_equal(ctx.get_r(), want)
+    print("\n[rhs %s] body force + traction: %d entries bit-equal to the reference's LinearForm" % (name, rhs.size))
+
+
+@pytest.mark.parametrize("name", sorted(BF))
 def test_viscosity_bit_exact_vs_reference(ctx_factory, name):
     """mb2_assemble_viscosity_device against the reference's mfem::VectorDiffusionIntegrator matrix (forms.npz, visc_*)."""
     D = load_golden(name)

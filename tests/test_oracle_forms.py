@@ -48,6 +48,11 @@ def test_oracle_forms_bit_exact_vs_reference(name):
     be = O.form_element_vectors(dim, p, D["v_dofs"], ijk, knots, D["x_ref"], G["f"][:dim])
     b = O.assemble_linear_form(D["NV"], D["v_dofs"], be)
     assert np.array_equal(b, G[name]), np.abs(b - G[name]).max()
+    # body force, then the traction of the loaded boundary on top: the reference's rhs linear form
+    rhs = O.add_traction_form(b.copy(), dim, G["tvd_" + name], G["tN_" + name], G["tw_" + name], G["tdet_" + name],
+                              G["traction"][:dim])
+    assert not np.array_equal(rhs, b)
+    assert np.array_equal(rhs, G["rhs_" + name]), np.abs(rhs - G["rhs_" + name]).max()
 
 
 def test_oracle_forms_properties():
