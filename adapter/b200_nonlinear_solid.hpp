@@ -209,6 +209,29 @@ public:
     Check(mb2_get_r(ctx_, b.GetData()));
   }
 
+  /// b <- ((b + f_1) + f_2) + ...: VectorBoundaryLFIntegrator(constant traction) on the boundary elements whose quadrature
+  /// data the caller created under `bdr_name` at the integrator's rule:
+  ///   precomputed->CreateBoundaryElementQuadData(bdr_name, marked, n); precomputed->PrecomputeElementQuadData(bdr_name, 2 * p, false);
+  /// Call after AssembleBodyForce with the same b (LinearForm::Assemble adds the domain integrators first).
+  void AddTraction(const std::string& bdr_name, const mfem::Vector& traction, mfem::Vector& b) const {
+    auto& tq = precomputed_->GetElementQuadData(std::string(bdr_name));  // the accessor takes an rvalue (precomputed.hpp:183)
+    const int NF = (int)tq.size(), ndf = tq[0].GetElementData().n_dof, tdf = tq[0].GetElementData().n_tdof, nqf = tq[0].n_quad;
+    std::vector<int> vd(size_t(NF) * tdf);
+    std::vector<double> w(size_t(NF) * nqf), dw(size_t(NF) * nqf), N(size_t(NF) * nqf * ndf);
+    for (int f = 0; f < NF; ++f) {
+      std::copy_n(tq[f].GetElementData().v_dofs.GetData(), tdf, &vd[size_t(f) * tdf]);
+      for (int q = 0; q < nqf; ++q) {
+        const auto& qd = tq[f].GetQuadData()[q];
+        w[size_t(f) * nqf + q] = qd.integration_weight;
+        dw[size_t(f) * nqf + q] = qd.det_dX_dxi;
+        std::copy_n(qd.N.GetData(), ndf, &N[(size_t(f) * nqf + q) * ndf]);
+      }
+    }
+    Check(mb2_set_r(ctx_, b.GetData()));
+    Check(mb2_assemble_traction_device(ctx_, NF, ndf, nqf, vd.data(), N.data(), w.data(), dw.data(), traction.GetData()));
+    Check(mb2_get_r(ctx_, b.GetData()));
+  }
+
   /// history variables [NE][nq][mb2_state_size] (checkpoints, tests); empty for stateless materials
   std::vector<double> State() const {
     const int ns = mb2_state_size(ctx_);

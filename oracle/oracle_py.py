@@ -238,7 +238,7 @@ def load_dump(d):
         out["state"] = out["state"].reshape(NE, nq, -1)
     out["t_meta"] = rd("t_meta.i32", np.int32)
     out["t_v_dofs"] = rd("t_v_dofs.i32", np.int32)
-    for k in ("x_ref", "u", "r", "r2", "mass", "bodyforce", "viscform", "mass_b200", "viscform_b200", "bodyforce_b200", "rhs_bf_traction", "t_w", "t_detW", "t_N", "A", "r_b", "A_b"):
+    for k in ("x_ref", "u", "r", "r2", "mass", "bodyforce", "viscform", "mass_b200", "viscform_b200", "bodyforce_b200", "rhs_b200", "rhs_bf_traction", "t_w", "t_detW", "t_N", "A", "r_b", "A_b"):
         out[k] = rd(k + ".f64", np.float64)
     return out
 

@@ -484,6 +484,11 @@ int main(int argc, char** argv) {
       for (int c = 0; c < dim; ++c) fv[c] = fc[c];
       s.integ->AssembleBodyForce(*s.mesh, fv, bb);
       dump(out, "bodyforce_b200.f64", bb.GetData(), (size_t)NV);
+      mfem::Vector tvv(dim);
+      const double tcv[3] = {0.5, -0.25, 1.5};
+      for (int c = 0; c < dim; ++c) tvv[c] = tcv[c];
+      s.integ->AddTraction("traction", tvv, bb);  // the "traction" boundary data were created above at the rule 2p
+      dump(out, "rhs_b200.f64", bb.GetData(), (size_t)NV);
     }
 #endif
     r2 = 0.0;

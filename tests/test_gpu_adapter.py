@@ -53,7 +53,7 @@ def test_reference_chain_through_the_adapter_bit_exact(name, material):
 
 @pytest.mark.parametrize("name", list(RECIPES))
 def test_setup_forms_through_the_adapter_bit_exact(name):
-    """B200NonlinearSolid::AssembleMass / AssembleViscosity / AssembleBodyForce (patch description taken from the
+    """B200NonlinearSolid::AssembleMass / AssembleViscosity / AssembleBodyForce / AddTraction (patch description taken from the
     reference's own NURBSExtension) against MFEM's VectorMassIntegrator / VectorDiffusionIntegrator /
     VectorDomainLFIntegrator in the same process, on the same mesh."""
     G = load_golden(name)
@@ -62,6 +62,8 @@ def test_setup_forms_through_the_adapter_bit_exact(name):
     assert np.array_equal(D["mass_b200"], D["mass"])
     assert np.array_equal(D["viscform_b200"], D["viscform"]) and np.abs(D["viscform"]).max() > 0
     assert np.array_equal(D["bodyforce_b200"], D["bodyforce"]) and np.abs(D["bodyforce"]).max() > 0
+    assert np.array_equal(D["rhs_b200"], D["rhs_bf_traction"])       # body force + traction = the reference's rhs form
+    assert not np.array_equal(D["rhs_b200"], D["bodyforce"])
 
 
 def _rel(a, b):
