@@ -226,7 +226,15 @@ enum {
    * (absent for curves), control points [ncp_v][ncp_u][dim]. The library splits it into Bezier patches by knot insertion
    * on the host and queries every patch (the nearest wins). MB2_RIGID_BEZIER also accepts several patches of one degree
    * back to back after n_seed. Parity unpinned like MB2_RIGID_BEZIER. */
-  MB2_RIGID_BSPLINE = 3
+  MB2_RIGID_BSPLINE = 3,
+  /* Rational Bezier patches (splinepy RationalBezier bodies: circular arcs, spherical caps ...): the MB2_RIGID_BEZIER
+   * list with dim + 1 doubles per control point, {x[dim], weight} (weight > 0, x not pre-multiplied). */
+  MB2_RIGID_RATIONAL_BEZIER = 4,
+  /* NURBS curve / surface: the MB2_RIGID_BSPLINE list with {x[dim], weight} per control point. Knot insertion runs on
+   * the homogeneous points {w x, w}; every patch is evaluated as numerator / denominator with the quotient rule for
+   * the first and second derivatives (oracle: bezier_eval in mimi_oracle_contact.c). Parity unpinned like
+   * MB2_RIGID_BEZIER; a rational quarter circle / sphere octant reproduces MB2_RIGID_SPHERE to rounding (tests). */
+  MB2_RIGID_NURBS = 5
 };
 /* The marked boundary faces and their quadrature tables as PrecomputedData holds them for the integrator's name
  * (CreateBoundaryElementQuadData + PrecomputeElementQuadData(name, order, false), precomputed.cpp:243-330):

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libmimi_b200.so")
 
 MB2_MAT_NEOHOOKEAN, MB2_MAT_STVK, MB2_MAT_J2LINEAR, MB2_MAT_J2, MB2_MAT_J2SIMO, MB2_MAT_J2LOG = 0, 1, 2, 3, 4, 5
 MB2_RIGID_PLANE, MB2_RIGID_SPHERE, MB2_RIGID_BEZIER, MB2_RIGID_BSPLINE = 0, 1, 2, 3
+MB2_RIGID_RATIONAL_BEZIER, MB2_RIGID_NURBS = 4, 5
 
 # every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [

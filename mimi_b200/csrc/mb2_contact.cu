@@ -25,6 +25,7 @@ struct RigidBody {
   int deg_u = 0, deg_v = 0, n_seed = 0;
   const double* cp = nullptr;
   int n_patches = 1;  // B-spline bodies: their Bezier patches one after the other in cp
+  int rational = 0;   // control points are homogeneous {w x, w}: dim + 1 doubles each
 };
 constexpr int BEZ_MAXDEG = 5;
 
@@ -94,23 +95,40 @@ __device__ __forceinline__ void bernstein(int p, double t, double* B, double* dB
   }
 }
 
-// S, S_u, S_v, S_uu, S_uv, S_vv at (u, v)
+// S, S_u, S_v, S_uu, S_uv, S_vv at (u, v); rational patches: numerator and denominator sums, then the quotient rule in
+// the order of the oracle's bezier_eval
 template <int DIM>
 __device__ __noinline__ void bezier_eval(const RigidBody& b, double u, double v, double (*out)[3]) {
   double Bu[BEZ_MAXDEG + 1], dBu[BEZ_MAXDEG + 1], ddBu[BEZ_MAXDEG + 1];
   double Bv[BEZ_MAXDEG + 1], dBv[BEZ_MAXDEG + 1], ddBv[BEZ_MAXDEG + 1];
+  const int stride = DIM + (b.rational ? 1 : 0);
+  double W[6] = {0, 0, 0, 0, 0, 0};
   bernstein(b.deg_u, u, Bu, dBu, ddBu);
   bernstein(b.deg_v, v, Bv, dBv, ddBv);
   for (int k = 0; k < 6; k++)
     for (int d = 0; d < 3; d++) out[k][d] = 0.0;
   for (int j = 0; j <= b.deg_v; j++)
     for (int i = 0; i <= b.deg_u; i++) {
-      const double* P = b.cp + ((size_t)j * (b.deg_u + 1) + i) * DIM;
+      const double* P = b.cp + ((size_t)j * (b.deg_u + 1) + i) * stride;
       const double w[6] = {Bu[i] * Bv[j], dBu[i] * Bv[j], Bu[i] * dBv[j], ddBu[i] * Bv[j], dBu[i] * dBv[j], Bu[i] * ddBv[j]};
       for (int k = 0; k < 6; k++)
 #pragma unroll
         for (int d = 0; d < DIM; d++) out[k][d] += w[k] * P[d];
+      if (b.rational)
+        for (int k = 0; k < 6; k++) W[k] += w[k] * P[DIM];
     }
+  if (b.rational) {
+#pragma unroll
+    for (int d = 0; d < DIM; d++) {
+      const double S = out[0][d] / W[0];
+      const double Su = (out[1][d] - W[1] * S) / W[0];
+      const double Sv = (out[2][d] - W[2] * S) / W[0];
+      const double Suu = ((out[3][d] - (2.0 * W[1]) * Su) - W[3] * S) / W[0];
+      const double Suv = (((out[4][d] - W[1] * Sv) - W[2] * Su) - W[4] * S) / W[0];
+      const double Svv = ((out[5][d] - (2.0 * W[2]) * Sv) - W[5] * S) / W[0];
+      out[0][d] = S; out[1][d] = Su; out[2][d] = Sv; out[3][d] = Suu; out[4][d] = Suv; out[5][d] = Svv;
+    }
+  }
 }
 
 template <int DIM>
@@ -198,7 +216,7 @@ __device__ __noinline__ void rigid_nearest_bezier(const RigidBody& b, const doub
     bezier_patch_nearest<DIM>(b, q, pmq, distance, fd);
     return;
   }
-  const size_t stride = (size_t)(b.deg_u + 1) * (b.deg_v + 1) * DIM;
+  const size_t stride = (size_t)(b.deg_u + 1) * (b.deg_v + 1) * (DIM + (b.rational ? 1 : 0));
   double best = 1e300;
   for (int p = 0; p < b.n_patches; p++) {
     RigidBody bp = b;
@@ -983,30 +1001,53 @@ int mb2_contact_set_rigid_body(mb2_ctx* c, int kind, const double* params, int n
   CCHECK(c);
   ContactState* S = static_cast<ContactState*>(c->contact);
   CREQ(S, "call mb2_contact_set_faces first");
-  CREQ(kind == MB2_RIGID_PLANE || kind == MB2_RIGID_SPHERE || kind == MB2_RIGID_BEZIER || kind == MB2_RIGID_BSPLINE,
+  CREQ(kind == MB2_RIGID_PLANE || kind == MB2_RIGID_SPHERE || kind == MB2_RIGID_BEZIER || kind == MB2_RIGID_BSPLINE ||
+           kind == MB2_RIGID_RATIONAL_BEZIER || kind == MB2_RIGID_NURBS,
        "unknown rigid body kind");
-  if (kind == MB2_RIGID_BEZIER || kind == MB2_RIGID_BSPLINE) {
+  const int rational = (kind == MB2_RIGID_RATIONAL_BEZIER || kind == MB2_RIGID_NURBS) ? 1 : 0;
+  if (kind == MB2_RIGID_BEZIER || kind == MB2_RIGID_BSPLINE || rational) {
     CREQ(params && nparams >= 3, "spline body needs {deg_u, deg_v, n_seed, ...}");
     const int du = (int)params[0], dv = (int)params[1], ns = (int)params[2];
     CREQ(du >= 1 && du <= mb2::BEZ_MAXDEG && dv >= 0 && dv <= mb2::BEZ_MAXDEG && ns >= 1, "spline degree must be 1..5");
     CREQ((c->dim == 2) == (dv == 0), "a 2D body is a curve (deg_v = 0), a 3D body a surface");
-    const int ncp = (du + 1) * (dv + 1) * c->dim;
+    const int hd = c->dim + rational;  // doubles per control point
+    const int ncp = (du + 1) * (dv + 1) * hd;
     std::vector<double> patches;
-    if (kind == MB2_RIGID_BEZIER) {
+    // rational bodies: {x, w} per point -> homogeneous {w x, w}
+    auto to_homogeneous = [&](const double* P, size_t npts, std::vector<double>& out) -> bool {
+      out.resize(npts * hd);
+      for (size_t i = 0; i < npts; i++) {
+        const double w = P[i * hd + c->dim];
+        if (!(w > 0.0)) return false;
+        for (int d = 0; d < c->dim; d++) out[i * hd + d] = P[i * hd + d] * w;
+        out[i * hd + c->dim] = w;
+      }
+      return true;
+    };
+    if (kind == MB2_RIGID_BEZIER || kind == MB2_RIGID_RATIONAL_BEZIER) {
       CREQ(nparams > 3 && (nparams - 3) % ncp == 0, "Bezier control point count does not match the degrees");
-      patches.assign(params + 3, params + nparams);
+      if (rational) {
+        CREQ(to_homogeneous(params + 3, (size_t)(nparams - 3) / hd, patches), "weights must be positive");
+      } else {
+        patches.assign(params + 3, params + nparams);
+      }
     } else {
       CREQ(nparams >= 5, "B-spline body needs {deg_u, deg_v, n_seed, ncp_u, ncp_v, knots_u, knots_v, control points}");
       const int nu = (int)params[3], nv = (int)params[4];
       CREQ(nu >= du + 1 && nv >= dv + 1 && (dv > 0 || nv == 1), "B-spline control point counts");
       const int nku = nu + du + 1, nkv = dv > 0 ? nv + dv + 1 : 0;
-      CREQ(nparams == 5 + nku + nkv + nu * nv * c->dim, "B-spline parameter count");
+      CREQ(nparams == 5 + nku + nkv + nu * nv * hd, "B-spline parameter count");
       const double* ku = params + 5;
       const double* kv = ku + nku;
       const double* P = kv + nkv;
+      std::vector<double> Ph;
+      if (rational) {
+        CREQ(to_homogeneous(P, (size_t)nu * nv, Ph), "weights must be positive");
+        P = Ph.data();
+      }
       for (int i = 0; i + 1 < nku; i++) CREQ(ku[i] <= ku[i + 1], "knot vectors must be non-decreasing");
       for (int i = 0; i + 1 < nkv; i++) CREQ(kv[i] <= kv[i + 1], "knot vectors must be non-decreasing");
-      patches = mb2::bspline_extract(c->dim, du, dv, nu, nv, ku, kv, P);
+      patches = mb2::bspline_extract(hd, du, dv, nu, nv, ku, kv, P);
       CREQ(!patches.empty(), "B-spline body: open knot vectors (end multiplicity degree + 1) expected");
     }
     const int np = (int)(patches.size() / ncp);
@@ -1021,6 +1062,7 @@ int mb2_contact_set_rigid_body(mb2_ctx* c, int kind, const double* params, int n
     S->body.deg_u = du; S->body.deg_v = dv; S->body.n_seed = ns;
     S->body.cp = S->d_cp;
     S->body.n_patches = np;
+    S->body.rational = rational;
     S->penalty = penalty;
     return MB2_OK;
   }

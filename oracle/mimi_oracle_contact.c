@@ -32,6 +32,8 @@ typedef struct {
   const double* cp;
   /* a B-spline body = its Bezier patches one after the other in cp (0 or 1: a single patch) */
   int n_patches;
+  /* 1: rational patches (NURBS bodies), control points homogeneous {w x, w} = dim + 1 doubles each */
+  int rational;
 } orc_rigid;
 
 static void rigid_bezier_nearest(const orc_rigid* b, const double* q, double* pmq, double* distance, double* fd);
@@ -365,6 +367,7 @@ double orc_contact_gap_norm(int dim, int64_t NF, int ndf, int nqf, const int32_t
 typedef struct {
   int dim, deg_u, deg_v, n_seed;
   const double* cp;
+  int rational; /* control points are homogeneous {w x, w}: dim + 1 doubles each */
 } orc_bezier;
 
 /* Bernstein basis of degree p at t with first and second derivatives (recurrence on the lower-degree bases) */
@@ -397,20 +400,36 @@ static void bernstein(int p, double t, double* B, double* dB, double* ddB) {
   }
 }
 
-/* S, S_u, S_v, S_uu, S_uv, S_vv at (u, v): out[6][3] */
+/* S, S_u, S_v, S_uu, S_uv, S_vv at (u, v): out[6][3]. Rational patches (splinepy's RationalBezier / NURBS rigid
+ * bodies, src/mimi/coefficients/nearest_distance.hpp:139-193 takes either): numerator A = sum B w P and denominator
+ * W = sum B w with their derivatives first, then the quotient rule in the order written below. */
 static void bezier_eval(const orc_bezier* b, double u, double v, double out[6][3]) {
   double Bu[ORC_BEZ_MAXDEG + 1], dBu[ORC_BEZ_MAXDEG + 1], ddBu[ORC_BEZ_MAXDEG + 1];
   double Bv[ORC_BEZ_MAXDEG + 1], dBv[ORC_BEZ_MAXDEG + 1], ddBv[ORC_BEZ_MAXDEG + 1];
+  const int stride = b->dim + (b->rational ? 1 : 0);
+  double W[6] = {0, 0, 0, 0, 0, 0};
   bernstein(b->deg_u, u, Bu, dBu, ddBu);
   bernstein(b->deg_v, v, Bv, dBv, ddBv);
   for (int k = 0; k < 6; k++)
     for (int d = 0; d < 3; d++) out[k][d] = 0.0;
   for (int j = 0; j <= b->deg_v; j++)
     for (int i = 0; i <= b->deg_u; i++) {
-      const double* P = b->cp + ((size_t)j * (b->deg_u + 1) + i) * b->dim;
+      const double* P = b->cp + ((size_t)j * (b->deg_u + 1) + i) * stride;
       const double w[6] = {Bu[i] * Bv[j], dBu[i] * Bv[j], Bu[i] * dBv[j], ddBu[i] * Bv[j], dBu[i] * dBv[j], Bu[i] * ddBv[j]};
       for (int k = 0; k < 6; k++)
         for (int d = 0; d < b->dim; d++) out[k][d] += w[k] * P[d];
+      if (b->rational)
+        for (int k = 0; k < 6; k++) W[k] += w[k] * P[b->dim];
+    }
+  if (b->rational)
+    for (int d = 0; d < b->dim; d++) {
+      const double S = out[0][d] / W[0];
+      const double Su = (out[1][d] - W[1] * S) / W[0];
+      const double Sv = (out[2][d] - W[2] * S) / W[0];
+      const double Suu = ((out[3][d] - (2.0 * W[1]) * Su) - W[3] * S) / W[0];
+      const double Suv = (((out[4][d] - W[1] * Sv) - W[2] * Su) - W[4] * S) / W[0];
+      const double Svv = ((out[5][d] - (2.0 * W[2]) * Sv) - W[5] * S) / W[0];
+      out[0][d] = S; out[1][d] = Su; out[2][d] = Sv; out[3][d] = Suu; out[4][d] = Suv; out[5][d] = Svv;
     }
 }
 
@@ -490,10 +509,10 @@ void orc_bezier_nearest(const orc_bezier* b, const double* q, double* xi, double
  * every patch, the nearest wins, the first on ties -- mb2_contact.cu (rigid_nearest_bezier) does the same. */
 static void rigid_bezier_nearest(const orc_rigid* b, const double* q, double* pmq, double* distance, double* fd) {
   const int np = b->n_patches > 1 ? b->n_patches : 1;
-  const size_t stride = (size_t)(b->deg_u + 1) * (b->deg_v + 1) * b->dim;
+  const size_t stride = (size_t)(b->deg_u + 1) * (b->deg_v + 1) * (b->dim + (b->rational ? 1 : 0));
   double best = 1e300;
   for (int p = 0; p < np; p++) {
-    const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp + p * stride};
+    const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp + p * stride, b->rational};
     double pm[3], dist, f[6];
     orc_bezier_nearest(&z, q, 0, pm, &dist, f);
     if (dist < best) {
@@ -508,7 +527,7 @@ static void rigid_bezier_nearest(const orc_rigid* b, const double* q, double* pm
 /* test helper: closest point only (xi out) */
 void orc_rigid_query(const orc_rigid* b, const double* q, double* xi, double* pmq, double* distance, double* fd) {
   if (b->kind == ORC_RIGID_BEZIER && b->n_patches <= 1) {
-    const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp};
+    const orc_bezier z = {b->dim, b->deg_u, b->deg_v, b->n_seed, b->cp, b->rational};
     orc_bezier_nearest(&z, q, xi, pmq, distance, fd);
   } else {
     orc_rigid_nearest(b, q, pmq, distance, fd);

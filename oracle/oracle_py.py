@@ -290,7 +290,7 @@ RIGID_PLANE, RIGID_SPHERE = 0, 1
 
 class Rigid(C.Structure):
     _fields_ = [("kind", C.c_int), ("dim", C.c_int), ("p", C.c_double * 16), ("deg_u", C.c_int), ("deg_v", C.c_int),
-                ("n_seed", C.c_int), ("cp", C.c_void_p), ("n_patches", C.c_int)]
+                ("n_seed", C.c_int), ("cp", C.c_void_p), ("n_patches", C.c_int), ("rational", C.c_int)]
 
 
 RIGID_BEZIER = 2
@@ -376,6 +376,36 @@ def bspline_params(dim, pu, pv, ku, kv, P, n_seed=None):
     ncp_v = P.shape[0] if dim == 3 else 1
     return np.concatenate([[pu, pv, n_seed, ncp_u, ncp_v], np.asarray(ku, np.float64),
                            np.asarray(kv, np.float64) if dim == 3 else [], P.ravel()])
+
+
+def homogeneous(cps, weights):
+    """Control points [..., dim] + weights [...] -> {w x, w} [..., dim + 1], the layout rational patches are queried in."""
+    cps = np.asarray(cps, np.float64)
+    w = np.asarray(weights, np.float64)
+    return np.ascontiguousarray(np.concatenate([cps * w[..., None], w[..., None]], axis=-1))
+
+
+def rigid_rational_patches(dim, patches_h, n_seed=None):
+    """patches_h: homogeneous patches, curves [np, deg_u+1, 3] / surfaces [np, deg_v+1, deg_u+1, 4]."""
+    patches_h = np.ascontiguousarray(patches_h, np.float64)
+    r = rigid_bezier_patches(dim, patches_h, n_seed)
+    r.rational = 1
+    return r
+
+
+def rational_bezier_params(dim, patches, weights, n_seed=None):
+    """mb2_contact_set_rigid_body(MB2_RIGID_RATIONAL_BEZIER): {deg_u, deg_v, n_seed, patches of {x, w} per point}."""
+    patches = np.asarray(patches, np.float64)
+    w = np.asarray(weights, np.float64)
+    b = rigid_bezier_patches(dim, patches, n_seed)
+    return np.concatenate([[b.deg_u, b.deg_v, b.n_seed], np.concatenate([patches, w[..., None]], axis=-1).ravel()])
+
+
+def nurbs_params(dim, pu, pv, ku, kv, P, weights, n_seed=None):
+    """mb2_contact_set_rigid_body(MB2_RIGID_NURBS): the MB2_RIGID_BSPLINE list with {x, w} per control point."""
+    P = np.asarray(P, np.float64)
+    w = np.asarray(weights, np.float64)
+    return bspline_params(dim, pu, pv, ku, kv, np.concatenate([P, w[..., None]], axis=-1), n_seed)
 
 
 def bezier_params(dim, cps, n_seed=None):

@@ -126,3 +126,81 @@ def test_bspline_extraction_and_multipatch_nearest():
                 Bt = np.array([comb(2, i) * t ** i * (1 - t) ** (2 - i) for i in range(3)])
                 val = np.einsum("j,i,jid->d", Bt, Bs, pt[b * 2 + a])
                 assert np.allclose(val, surf(ub[a] + s * (ub[a + 1] - ub[a]), vb[b] + t * (vb[b + 1] - vb[b])), atol=1e-13)
+
+
+def _arc(c, R, a0, a1):
+    """Rational quadratic Bezier arc of the circle (c, R) from angle a0 to a1 (< 180 degrees apart): control points and
+    weights (1, cos(half angle), 1)."""
+    c = np.asarray(c, np.float64)
+    h = 0.5 * (a1 - a0)
+    m = 0.5 * (a0 + a1)
+    P = np.array([c + R * np.array([np.cos(a0), np.sin(a0)]),
+                  c + R / np.cos(h) * np.array([np.cos(m), np.sin(m)]),
+                  c + R * np.array([np.cos(a1), np.sin(a1)])])
+    return P, np.array([1.0, np.cos(h), 1.0])
+
+
+def test_rational_arc_reproduces_the_closed_form_circle():
+    """Rational patches (NURBS rigid bodies): numerator / denominator evaluation + quotient rule. A rational quadratic arc
+    IS a circle, so the search must return the closed-form circle's distance, closest point and tangent direction
+    (RigidSphere of the reference harness, pinned) wherever the foot point lies on the arc."""
+    rng = np.random.default_rng(3)
+    c, R = np.array([1.0, 1.9995]), 1.0
+    P, w = _arc(c, R, np.deg2rad(210.0), np.deg2rad(330.0))
+    arc = O.rigid_rational_patches(2, O.homogeneous(P, w)[None])
+    sph = O.rigid_from_spec(2, ("sphere", [c[0], c[1], R]))
+    n = 0
+    for _ in range(200):
+        q = c + rng.uniform(0.3, 1.6) * np.array([np.cos(t := np.deg2rad(rng.uniform(215.0, 325.0))), np.sin(t)])
+        xi, pmq, d, fd = O.rigid_query(arc, q)
+        _, pmq_s, d_s, fd_s = O.rigid_query(sph, q)
+        assert abs(d - d_s) <= 1e-13 and np.abs(pmq - pmq_s).max() <= 1e-13
+        tan = fd[0] / np.linalg.norm(fd[0])
+        assert abs(tan @ (q + pmq - c)) <= 1e-13                     # tangent is perpendicular to the radius
+        assert abs(np.array([tan[1], -tan[0]]) @ (q + pmq - c) / R - 1.0) <= 1e-12      # normal (d1, -d0) points outward
+        n += 1
+    assert n == 200
+
+
+def test_unit_weights_equal_the_polynomial_patch_and_nurbs_extraction_keeps_the_circle():
+    rng = np.random.default_rng(4)
+    cps = np.array([[-2.5, 1.3], [0.3, 0.7], [0.7, 0.7], [1.5, 1.3]]) + [0.05, 1.0]
+    poly = O.rigid_bezier(2, cps)
+    rat = O.rigid_rational_patches(2, O.homogeneous(cps, np.ones(4))[None], n_seed=64)
+    for _ in range(50):
+        q = rng.uniform([-2, 0.5], [1.5, 2.5])
+        a, b = O.rigid_query(poly, q), O.rigid_query(rat, q)
+        assert abs(a[2] - b[2]) <= 1e-13 and np.abs(a[1] - b[1]).max() <= 1e-13 and np.abs(a[3] - b[3]).max() <= 1e-11
+    # knot insertion on homogeneous points (what MB2_RIGID_NURBS does on the host): the arc with an extra knot at 0.3,
+    # split back into two rational Bezier patches, is still the circle
+    c, R = np.array([0.2, -0.1]), 0.7
+    P, w = _arc(c, R, np.deg2rad(20.0), np.deg2rad(140.0))
+    H = O.homogeneous(P, w)
+    a = 0.3
+    Hn = np.array([H[0], a * H[1] + (1 - a) * H[0], a * H[2] + (1 - a) * H[1], H[2]])     # Boehm, one insertion
+    patches = O.bspline_to_bezier(2, [0, 0, 0, 0.3, 1, 1, 1], Hn)
+    assert patches.shape == (2, 3, 3)
+    body = O.rigid_rational_patches(2, patches, n_seed=32)
+    for _ in range(100):
+        q = c + rng.uniform(0.2, 1.5) * np.array([np.cos(t := np.deg2rad(rng.uniform(25.0, 135.0))), np.sin(t)])
+        _, pmq, d, fd = O.rigid_query(body, q)
+        assert abs(d - abs(np.linalg.norm(q - c) - R)) <= 1e-13
+        assert abs(np.linalg.norm(q + pmq - c) - R) <= 1e-13
+
+
+def test_rational_cylinder_surface():
+    """3D: rational quadratic arc (u) extruded along y (v, degree 1) = a cylinder; distance = | rho - R |."""
+    rng = np.random.default_rng(5)
+    c, R = np.array([0.5, 2.0]), 1.0                        # axis along y through (x, z) = c
+    P2, w = _arc(c, R, np.deg2rad(210.0), np.deg2rad(330.0))
+    cp = np.zeros((2, 3, 3))
+    for j, y in enumerate([-0.5, 1.5]):
+        cp[j, :, 0], cp[j, :, 1], cp[j, :, 2] = P2[:, 0], y, P2[:, 1]
+    body = O.rigid_rational_patches(3, O.homogeneous(cp, np.stack([w, w]))[None])
+    for _ in range(100):
+        t = np.deg2rad(rng.uniform(215.0, 325.0))
+        rho = rng.uniform(0.3, 1.5)
+        q = np.array([c[0] + rho * np.cos(t), rng.uniform(-0.4, 1.4), c[1] + rho * np.sin(t)])
+        xi, pmq, d, fd = O.rigid_query(body, q)
+        assert abs(d - abs(rho - R)) <= 1e-13 and abs(pmq[1]) <= 1e-13
+        assert max(abs(pmq @ fd[0]), abs(pmq @ fd[1])) <= 1e-12
