@@ -121,7 +121,7 @@ def run_reference_sample(n, reps, nthreads, warmup=0, p=2, material="neohookean"
     qp = T["NE"] * T["nq"]
     return {"qp": qp, "NE": T["NE"], "t_mean": T["t_res_grad_mean"], "t_best": T["t_res_grad_best"],
             "t_res_best": T["t_res_best"], "value_mean": qp / T["t_res_grad_mean"], "value_best": qp / T["t_res_grad_best"],
-            "t_precompute": T["t_precompute"]}
+            "t_precompute": T["t_precompute"], "omp_team": int(T.get("omp_team", 0)), "omp_max_threads": int(T.get("omp_max_threads", 0))}
 
 
 def host_cores():
@@ -141,14 +141,16 @@ def reference_arm(args):
     t0 = time.time()
     S = run_reference_sample(n, reps, cores, warmup=args.warmup)
     value = S["qp"] / S["t_mean"]
+    team = S["omp_team"] or cores
     sample = ("unmodified reference AddDomainResidualAndGrad (MFEM 4.7.1 + mimi integrators, OpenMP, -O3), "
-              "p=2 unit cube %d^3 = %d elements (%d qp) per step, %d threads; mean of %d steps after %d warm-up" % (n, S["NE"], S["qp"], cores, reps, args.warmup))
+              "p=2 unit cube %d^3 = %d elements (%d qp) per step, OpenMP team of %d threads (%d requested = host cores); "
+              "mean of %d steps after %d warm-up" % (n, S["NE"], S["qp"], team, cores, reps, args.warmup))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": S["t_mean"] * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C3 sample: p=2 NeoHookean unit cube %d^3 (bounded sample of the 100^3 workload)" % n,
                        "elements": S["NE"], "qp": S["qp"]},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": team, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.time() - t0}
     emit(line)
@@ -158,7 +160,7 @@ def reference_arm(args):
 # ----------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------
-def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean"):
+def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean", slab=None):
     """Synthetic C3-style block in MFEM's numbering; tables regenerated on the device. world > 1: the global mesh
     is n x n x (n*world) spans (weak scaling), cut into z-slabs of n layers; rank g computes slab g, owns the nodes
     whose lowest element it computes, and receives the raw element matrices of the next slab's first p layers."""
@@ -170,7 +172,8 @@ def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean"):
         M["n_compute"] = M["NE"]
         owned_rows = None
     else:
-        M = partition.slab_rank_problem(p, (n, n, n * world), world, rank)
+        # weak scaling: n layers per rank of an n x n x (n world) patch; strong (slab given): slab layers of n x n x n
+        M = partition.slab_rank_problem(p, (n, n, (slab or n) * world), world, rank)
         owned_rows = np.repeat(M["owned"], 3)
     ctx.set_connectivity(3, M["nd"], nq1 ** 3, M["NV"], M["v_dofs"])
     if world > 1:
@@ -189,6 +192,110 @@ def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean"):
     u.reshape(-1, 3)[x[:, 0] == 0.0, :] = 0.0
     M.update(u=u, nnz=nnz, nq=nq1 ** 3, setup_s=time.time() - t0, owned_rows=owned_rows)
     return M
+
+
+def source_md5():
+    """md5 of the kernel sources: a committed ncu capture only speaks for the binary built from the same sources."""
+    import hashlib
+    h = hashlib.md5()
+    for f in ("mb2_assembly.cu", "mb2_math.cuh"):
+        with open(os.path.join(ROOT, "mimi_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
+def ncu_traffic(kernel_key, launch_elems):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/traffic.json,
+    written by scripts/ncu_traffic.py from the .ncu-rep): dram__bytes_read.sum + dram__bytes_write.sum of a capture of
+    THIS source revision, scaled to the elements one launch of this run processes. No capture of the current sources ->
+    null (never a stale constant)."""
+    try:
+        T = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    except (OSError, ValueError):
+        return None, "no profiles/traffic.json"
+    ent = T.get(kernel_key)
+    if not ent:
+        return None, "no ncu capture of %s in profiles/traffic.json" % kernel_key
+    if ent.get("source_md5") != source_md5():
+        return None, "profiles/traffic.json holds a capture of another source revision of %s (%s)" % (kernel_key, ent.get("capture"))
+    per_el = (ent["dram_read_bytes"] + ent["dram_write_bytes"]) / float(ent["launch_elements"])
+    return per_el * launch_elems, "%s: %d-element launch, read %.1f MB + write %.1f MB, scaled to %d elements per launch" % (
+        ent.get("capture"), ent["launch_elements"], ent["dram_read_bytes"] / 1e6, ent["dram_write_bytes"] / 1e6, launch_elems)
+
+
+def nccl_parity_check(rank, world, local, dist):
+    """Before any timing at N > 1: a small partitioned residual + tangent assembly over the LIVE NCCL exchange, every
+    rank's owned rows compared bit for bit with the unmodified reference's dump (tests/golden/cube_p2_n3_patch.npz:
+    27 p=2 elements, NeoHookean). Several assemblies are enqueued back to back without a host sync in between, so a
+    sender running ahead of its receiver would show. Fails the run on any mismatch."""
+    from mimi_b200 import capi, partition as P
+    z = np.load(os.path.join(ROOT, "tests", "golden", "cube_p2_n3_patch.npz"))
+    D = {k: z[k] for k in z.files}
+    dim, nd, nq, NE, NV, nnz = (int(x) for x in D["meta"])
+    uid = [capi.mg_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    R = P.rank_problem(D["v_dofs"], dim, NV, P.element_ranges(NE, world), rank)
+    ctx = capi.Context(local)
+    loc = R["local_elems"]
+    ctx.set_connectivity(dim, nd, nq, NV, R["v_dofs"])
+    ctx.upload_quad_tables(D["dN_dX"][loc], D["w"][loc], D["detJ"][loc])
+    ctx.mg_setup(R)
+    ctx.mg_init_nccl(rank, world, uid[0])
+    ctx.build_pattern()
+    ctx.set_material(capi.MB2_MAT_NEOHOOKEAN, list(D["lambda_mu"]))
+    rows = np.repeat(R["owned"], dim)
+    gI = D["I"].astype(np.int64)
+    own = np.nonzero(rows)[0]
+    idx = np.concatenate([np.arange(gI[v], gI[v + 1]) for v in own]) if own.size else np.zeros(0, np.int64)
+    ok = True
+    gf = float(D["gf"])
+    for rep in range(2):
+        ctx.set_u(D["u"]); ctx.set_r(None); ctx.set_A(np.ascontiguousarray(D["mass"][idx]))
+        ctx.assemble_residual_and_grad_device(gf)
+        ok = ok and np.array_equal(ctx.get_r()[rows], D["r2_neohookean"][rows]) and np.array_equal(ctx.get_A(), D["A_neohookean"][idx])
+    # three assemblies in flight without a host sync: A = mass + 3 gf K must equal the sequentially added reference values
+    ctx.set_r(None); ctx.set_A(np.ascontiguousarray(D["mass"][idx]))
+    for _ in range(3):
+        ctx.assemble_residual_and_grad_device(gf)
+    K = D["A_neohookean"][idx] - D["mass"][idx]
+    A3 = ctx.get_A()
+    ok = ok and bool(np.allclose(A3, D["mass"][idx] + 3.0 * K, rtol=1e-12, atol=1e-12 * float(np.abs(K).max() if K.size else 1.0)))
+    ctx.close()
+    import torch
+    t = torch.tensor([int(ok)], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return {"ranks": world, "ok": bool(int(t) == 1), "fixture": "tests/golden/cube_p2_n3_patch.npz (reference dump), owned rows of r and CSR values bit-equal on every rank over the live NCCL exchange"}
+
+
+def timed_steps(ctx, stream, steps, warmup, barrier, world, dist, sampler=None):
+    """W untimed + K timed device-resident assemblies bracketed by barrier + synchronize; CUDA events on the launching
+    stream; max over ranks."""
+    import torch
+    for _ in range(warmup):
+        ctx.assemble_residual_and_grad_device(1.0)
+    ctx.sync()
+    barrier()
+    if sampler:
+        sampler.start()
+    t_el, t_sc, launches = [], [], 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    for _ in range(steps):
+        ctx.assemble_residual_and_grad_device(1.0)
+        el, sc, tot = ctx.last_timing_ms()      # CUDA events on the library's stream (synchronises on the last)
+        t_el.append(el); t_sc.append(sc)
+        launches += ctx.last_launch_count()
+    ev1.record(stream)
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if sampler else None
+    dev_ms = float(ev0.elapsed_time(ev1))
+    if world > 1:
+        tt = torch.tensor([dev_ms, wall], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dev_ms, wall = float(tt[0]), float(tt[1])
+    return {"ms_per_step": dev_ms / steps, "wall": wall, "t_el": t_el, "t_sc": t_sc, "launches": launches, "clocks": clocks}
 
 
 def gpu_arm(args):
@@ -210,6 +317,19 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def maxr(x):
+        if world > 1:
+            tt = torch.tensor([x], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt[0])
+        return x
+
+    parity = None
+    if world > 1:
+        parity = nccl_parity_check(rank, world, local, dist)
+        if not parity["ok"]:
+            raise RuntimeError("partitioned assembly over NCCL differs from the reference's golden vectors: not timing a wrong result")
+
     n, p = args.n, args.p
     stream = torch.cuda.Stream()            # the library launches on this stream, so torch events see its work
     ctx = capi.Context(local, stream=stream.cuda_stream)
@@ -230,32 +350,9 @@ def gpu_arm(args):
     peak_nofma = ctx.measure_fp64_peak(0)
     peak_fma = ctx.measure_fp64_peak(1)
 
-    # ---- device-resident steps ----
-    for _ in range(args.warmup):
-        ctx.assemble_residual_and_grad_device(1.0)
-    ctx.sync()
-    sampler = ClockSampler(local)
-    barrier()
-    sampler.start()
-    t_el, t_sc, launches = [], [], 0
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t0 = time.perf_counter()
-    ev0.record(stream)
-    for _ in range(args.steps):
-        ctx.assemble_residual_and_grad_device(1.0)
-        el, sc, tot = ctx.last_timing_ms()      # CUDA events on the library's stream (synchronises on the last)
-        t_el.append(el); t_sc.append(sc)
-        launches += ctx.last_launch_count()
-    ev1.record(stream)
-    barrier()
-    wall = time.perf_counter() - t0
-    clocks = sampler.stop()
-    dev_ms = float(ev0.elapsed_time(ev1))         # device time of the K steps, CUDA events on the launching stream
-    if world > 1:
-        tt = torch.tensor([dev_ms, wall], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dev_ms, wall = float(tt[0]), float(tt[1])
-    ms_per_step = dev_ms / args.steps
+    # ---- device-resident steps (weak scaling: n^3 elements per GPU) ----
+    T = timed_steps(ctx, stream, args.steps, args.warmup, barrier, world, dist, ClockSampler(local))
+    ms_per_step, wall, t_el, t_sc, launches, clocks = T["ms_per_step"], T["wall"], T["t_el"], T["t_sc"], T["launches"], T["clocks"]
     total_qp = float(NE) * nq * world
     value = total_qp / (ms_per_step * 1e-3)
 
@@ -272,38 +369,92 @@ def gpu_arm(args):
             ctx.assemble_residual_device()
         e1.record(stream)
         barrier()
-        ro_ms = float(e0.elapsed_time(e1)) / max(args.steps, 3)
-        if world > 1:
-            tt = torch.tensor([ro_ms], device="cuda", dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            ro_ms = float(tt[0])
+        ro_ms = maxr(float(e0.elapsed_time(e1)) / max(args.steps, 3))
         tdof_ = 3 * M["nd"]
         ro_bytes = float(NE) * (8.0 * nq * (tdof_ + 1) + 4 * tdof_ + 8 * tdof_ + 8 * tdof_)   # tables + v_dofs + u gather + R_e
         res_only = {"value": float(NE) * nq * world / (ro_ms * 1e-3), "unit": UNIT, "ms_per_step": ro_ms,
                     "algorithmic_gb_per_gpu": ro_bytes / 1e9, "achieved_gbs_per_gpu": ro_bytes / 1e9 / (ro_ms * 1e-3)}
 
-    # ---- end to end through the host-buffer C-ABI call (pinned host memory) ----
-    e2e = None
+    # ---- end to end through the reference-facing C-ABI calls, pinned HOST buffers, copies inside the timed region ----
+    # e2e           : the Newton-iteration assembly with the CSR consumed on the device (the only consumer that exists at
+    #                 every N: a host mfem::SparseMatrix cannot index N x 1.15e9 entries with its int nnz) --
+    #                 mb2_newton_residual_and_grad_device(x, v, a, fac0, fac1): x, a H2D; y = M a + R(x + fac0 a) and
+    #                 J = M + fac0 K stay resident for mb2_newton_solve_gmres_device; y D2H (mb2_get_r).
+    # e2e_host_csr  : the host mfem::SparseMatrix consumer with the mass resident (mb2_set_mass once): u, r H2D; r and the
+    #                 whole CSR D2H (mb2_domain_residual_and_grad_on_mass).
+    # e2e_roundtrip : round 1's number: the CSR values travel both ways (mb2_add_domain_residual_and_grad adds into A).
+    e2e = e2e_host = e2e_rt = None
     if not args.no_e2e:
+        e2e_steps = max(1, args.e2e_steps if args.e2e_steps > 0 else args.steps)
+        one = capi.C.c_double(1.0)
         u_h = torch.from_numpy(M["u"]).pin_memory()
+        a_h = torch.zeros(NV, dtype=torch.float64).pin_memory()
         r_h = torch.zeros(NV, dtype=torch.float64).pin_memory()
         A_h = torch.zeros(nnz, dtype=torch.float64).pin_memory()
-        up, rp, Ap = (C_void(t) for t in (u_h, r_h, A_h))
-        e2e_steps = max(1, min(args.steps, args.e2e_steps))
-        ctx._ck(ctx.lib.mb2_add_domain_residual_and_grad(ctx.h, up, capi.C.c_double(1.0), rp, Ap))  # warm-up
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            ctx._ck(ctx.lib.mb2_add_domain_residual_and_grad(ctx.h, up, capi.C.c_double(1.0), rp, Ap))
-        barrier()
-        e2e_s = (time.perf_counter() - t0) / e2e_steps
-        if world > 1:
-            tt = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            e2e_s = float(tt[0])
-        e2e = {"value": total_qp / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * (2 * NV + nnz),
-               "d2h_bytes_per_step": 8 * (NV + nnz), "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
-               "call": "mb2_add_domain_residual_and_grad(u, 1.0, r, A) with pinned host buffers"}
+        up, ap_, rp, Ap = (C_void(t) for t in (u_h, a_h, r_h, A_h))
+        # mass, resident: assembled on the device (VectorMassIntegrator, rho = 1), never leaves it
+        ctx.set_A(None)
+        ctx.assemble_mass_device(p, M["ncp"], M["knots"], M["el_ijk"][:M["n_compute"]])
+        ctx.newton_mass_from_A(False)
+        ctx.sync()
+
+        def run(fn, k):
+            fn()                                  # warm-up
+            barrier()
+            t0_ = time.perf_counter()
+            for _ in range(k):
+                fn()
+            barrier()
+            return maxr((time.perf_counter() - t0_) / k)
+
+        def step_newton():
+            ctx._ck(ctx.lib.mb2_newton_residual_and_grad_device(ctx.h, up, None, ap_, one, capi.C.c_double(0.0)))
+            ctx._ck(ctx.lib.mb2_get_r(ctx.h, rp))
+
+        s = run(step_newton, e2e_steps)
+        e2e = {"value": total_qp / s, "unit": UNIT, "h2d_bytes_per_step": 8 * 2 * NV, "d2h_bytes_per_step": 8 * NV,
+               "ms_per_step": s * 1e3, "steps": e2e_steps, "consumer": "device (CSR stays resident for mb2_newton_solve_gmres_device)",
+               "call": "mb2_newton_residual_and_grad_device(x, NULL, a, 1.0, 0.0) + mb2_get_r(y): pinned host x, a in; y = M a + R(x + a) out; "
+                       "J = M + K(x + a) resident"}
+
+        def step_host():
+            ctx._ck(ctx.lib.mb2_domain_residual_and_grad_on_mass(ctx.h, up, one, rp, Ap))
+
+        k2 = max(1, min(e2e_steps, 5))
+        s = run(step_host, k2)
+        e2e_host = {"value": total_qp / s, "unit": UNIT, "h2d_bytes_per_step": 8 * 2 * NV, "d2h_bytes_per_step": 8 * (NV + nnz),
+                    "ms_per_step": s * 1e3, "steps": k2, "consumer": "host mfem::SparseMatrix (mass resident on the device)",
+                    "call": "mb2_domain_residual_and_grad_on_mass(u, 1.0, r, A_out) with pinned host buffers"}
+
+        def step_rt():
+            ctx._ck(ctx.lib.mb2_add_domain_residual_and_grad(ctx.h, up, one, rp, Ap))
+
+        s = run(step_rt, k2)
+        e2e_rt = {"value": total_qp / s, "unit": UNIT, "h2d_bytes_per_step": 8 * (2 * NV + nnz), "d2h_bytes_per_step": 8 * (NV + nnz),
+                  "ms_per_step": s * 1e3, "steps": k2, "call": "mb2_add_domain_residual_and_grad(u, 1.0, r, A) with pinned host buffers"}
+        del A_h, Ap
+
+    chunk_elems, n_chunks = ctx.plan_info()
+    ctx.close()
+
+    # ---- strong scaling: the SAME 1e6-element block (n^3) cut into N z-slabs ----
+    strong = None
+    if world > 1 and args.scaling in ("strong", "both") and n % world == 0:
+        ctx2 = capi.Context(local, stream=stream.cuda_stream)
+        ctx2.set_option("elem_variant", args.variant)
+        uid2 = [capi.mg_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid2, src=0)
+        M2 = build_problem(ctx2, n, p, rank, world, uid2[0], args.material, slab=n // world)
+        ctx2.set_u(M2["u"]); ctx2.set_r(None); ctx2.set_A(None); ctx2.sync()
+        T2 = timed_steps(ctx2, stream, args.steps, args.warmup, barrier, world, dist)
+        qp2 = float(n) ** 3 * M2["nq"]
+        strong = {"value": qp2 / (T2["ms_per_step"] * 1e-3), "unit": UNIT, "ms_per_step": T2["ms_per_step"],
+                  "elements_total": n ** 3, "elements_per_gpu": M2["n_compute"],
+                  "workload": "the one %d^3-element block cut into %d z-slabs of %d layers" % (n, world, n // world)}
+        ctx2.close()
+    elif world == 1:
+        strong = {"value": value, "unit": UNIT, "ms_per_step": ms_per_step, "elements_total": NE, "elements_per_gpu": NE,
+                  "workload": "N = 1: identical to the weak value"}
 
     if rank == 0:
         alg, exe, fd = flops_per_qp(p, 3, args.material)
@@ -319,24 +470,16 @@ def gpu_arm(args):
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         tdof = 3 * M["nd"]
         bytes_el = NE * (8.0 * nq * (tdof + 1) + 4 * tdof + 8 * tdof + 8 * tdof * tdof + 8 * tdof)
-        # DRAM traffic of the dominant kernel from the one `ncu --set full` capture of it (profiles/r01_elem_v4_summary.txt:
-        # a 4096-element launch, dram__bytes_read.sum 173.53 MB + dram__bytes_write.sum 165.42 MB; algorithmic 172.0 MB of
-        # tables read -- no re-reads -- and 215.9 MB of K_e written, of which the tail is still in L2 when the kernel ends),
-        # scaled to the elements one launch of this run processes. Only the p=2 kernel has a capture at this revision.
-        traffic = traffic_note = None
-        try:
-            chunk_elems, n_chunks = ctx.plan_info()
-            if p == 2:
-                traffic = (173.530880e6 + 165.421056e6) / 4096.0 * min(chunk_elems, NE)
-                traffic_note = ("bytes per element-kernel launch (%d elements; %d launches per step), scaled from the 4096-element "
-                                "ncu --set full capture in profiles/r01_elem_v4_summary.txt; algorithmic %.3e" % (
-                                    min(chunk_elems, NE), n_chunks, bytes_el / NE * min(chunk_elems, NE)))
-        except Exception:
-            pass
-        roofline = {"bound": "fp64", "kernel": ("element_fd_kernel<3,27,64,%s>" if p == 2 else "element_fd_split_kernel<3,64,125,%s,4>") % args.material, "achieved": achieved, "peak": peak_nofma,
-                    "unit": "TFLOP/s", "frac": achieved / peak_nofma, "traffic": traffic, "traffic_note": traffic_note,
+        kern = ("element_fd_kernel<3,27,64,%s>" if p == 2 else "element_fd_split_kernel<3,64,125,%s,4>") % args.material
+        traffic, traffic_note = ncu_traffic(kern, min(chunk_elems, NE))
+        roofline = {"bound": "fp64", "kernel": kern, "achieved": achieved, "peak": peak_nofma,
+                    "unit": "TFLOP/s", "frac": achieved / peak_nofma,
+                    "peak_fma": peak_fma, "frac_vs_fma_peak": achieved / peak_fma,
+                    "frac_algorithmic": qp_rate_kernel * (alg + fd / nq) / 1e12 / peak_nofma,
+                    "traffic": traffic, "traffic_note": traffic_note,
+                    "algorithmic_bytes_per_launch": bytes_el / NE * min(chunk_elems, NE), "launches_per_step": n_chunks,
                     "peak_source": "mb2_measure_fp64_peak(fma=0) on this GPU in this run: DMUL+DADD pairs = the only "
-                                   "mix a bit-exact non-FMA kernel may issue (DFMA peak %.2f; MEASURED_PEAKS.json has no FP64 entry)" % peak_fma,
+                                   "mix a bit-exact non-FMA kernel may issue; peak_fma = the same with DFMA (MEASURED_PEAKS.json has no FP64 entry)",
                     "flop_per_qp_executed": exe_qp, "flop_per_qp_algorithmic": alg + fd / nq,
                     "achieved_algorithmic": qp_rate_kernel * (alg + fd / nq) / 1e12,
                     "kernel_ms": el_ms, "scatter_ms": float(np.mean(t_sc)),
@@ -347,10 +490,12 @@ def gpu_arm(args):
             try:
                 cores = host_cores()
                 S = run_reference_sample(args.ref_n, 2, cores, warmup=1, p=p, material=args.material)
-                cpu = {"value": S["value_mean"], "unit": UNIT, "cores": cores, "kind": "reference",
-                       "sample": "unmodified reference (oracle/_ref/mimi_ref, OpenMP %d threads) on p=%d %s cube %d^3 = %d el, "
+                cpu = {"value": S["value_mean"], "unit": UNIT, "cores": S["omp_team"], "kind": "reference",
+                       "sample": "unmodified reference (oracle/_ref/mimi_ref, OpenMP team of %d threads, %d requested) on p=%d %s cube %d^3 = %d el, "
                                  "mean of 2 steps after 1 warm-up; residual-only best %.3e qp/s" % (
-                                     cores, p, args.material, args.ref_n, S["NE"], S["qp"] / S["t_res_best"])}
+                                     S["omp_team"], cores, p, args.material, args.ref_n, S["NE"], S["qp"] / S["t_res_best"])}
+                if S["omp_team"] < cores:
+                    cpu["flag"] = "OpenMP team smaller than the host core count"
             except Exception as ex:  # the checker binary is absent: report that, never substitute
                 cpu = {"value": None, "unit": UNIT, "cores": host_cores(), "kind": "reference", "sample": "unavailable: %s" % ex}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -363,14 +508,15 @@ def gpu_arm(args):
                            "l2": "inputs larger than L2 (tables %.1f GB, K_e %.1f GB per step)" % (8e-9 * NE * nq * (tdof + 1), 8e-9 * NE * tdof * tdof),
                            "parallelism": "1 GPU" if world == 1 else "z-slabs of %d^3 elements per GPU of one %dx%dx%d patch; raw K_e/R_e of the p interface layers sent to the owner rank by NCCL send/recv inside the step (bit-identical to the 1-thread reference order)" % (n, n, n, n * world),
                            "setup_s": M["setup_s"]},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-                "wall_s_timed_region": wall}
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_host_csr": e2e_host, "e2e_roundtrip": e2e_rt,
+                "strong_scaling": strong, "gpu_launches": launches, "clocks": clocks, "wall_s_timed_region": wall}
+        if parity:
+            line["parity_check"] = parity
         if res_only:
             res_only["hbm_peak_gbs"] = hbm_peak
             res_only["frac_hbm"] = res_only["achieved_gbs_per_gpu"] / hbm_peak
             line["residual_only"] = res_only
         emit(line)
-    ctx.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -546,8 +692,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n", type=int, default=100, help="knot spans per direction (per GPU)")
-    ap.add_argument("--ref-n", type=int, default=24, help="spans per direction of the CPU reference sample")
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--ref-n", type=int, default=32, help="spans per direction of the CPU reference sample")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="timed e2e steps (0 = --steps)")
+    ap.add_argument("--scaling", default="both", choices=["weak", "strong", "both"],
+                    help="N > 1: weak = n^3 elements per GPU (the headline value); strong = the one n^3 block cut into N slabs (key strong_scaling)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-res-only", action="store_true", help="skip the residual-only pass")
     ap.add_argument("--no-cpu", action="store_true")

@@ -159,8 +159,13 @@ int mb2_state_size(mb2_ctx* ctx);
 /* NonlinearBase::dt_ (pushed into MaterialBase::dt_ by every assembly, nonlinear_solid.cpp:154,167): the time step the
  * rate-dependent hardening laws divide by. */
 int mb2_set_time_step(mb2_ctx* ctx, double dt);
-/* Device failure flag of the return-mapping scalar solve (the reference throws, src/mimi/solvers/newton.hpp:81-93,
- * 119-132): MB2_ERR_NUMERIC + message if raised since the last check. The host-buffer entries check it themselves. */
+/* Device failure flag: MB2_ERR_NUMERIC + a message per cause if raised since the last check -- the return-mapping scalar
+ * solve (the reference throws, src/mimi/solvers/newton.hpp:81-93, 119-132: "root not bracketed" / "failed to converge"),
+ * EliminateRowCol on a non-symmetric pattern, DiagScale without a diagonal. The host-buffer entries check it themselves;
+ * of the device-resident entries mb2_newton_solve_gmres_device and mb2_newton_residual_device (when it returns the norm)
+ * do, because they synchronise anyway. The asynchronous ones (mb2_assemble_*_device,
+ * mb2_newton_residual_and_grad_device) do NOT: a caller that consumes their output without going through the solve
+ * must call mb2_check_numeric once per iteration. */
 int mb2_check_numeric(mb2_ctx* ctx);
 int mb2_get_state(mb2_ctx* ctx, double* state);
 int mb2_set_state(mb2_ctx* ctx, const double* state);
@@ -278,6 +283,12 @@ int mb2_contact_gap_norm(mb2_ctx* ctx, const double* u, double* out);
  *   then the same elimination again;  J += fac1 S;  y -= rhs;  y[ess] := 0.
  * Results stay resident (mb2_get_r / mb2_get_A / mb2_device_pointers) and are bit-identical to the reference's. */
 int mb2_set_mass(mb2_ctx* ctx, const double* M_values);          /* nnz values on mb2_build_pattern's pattern */
+/* The host-CSR consumer without the per-step CSR upload: the mass stays resident (mb2_set_mass / mb2_newton_mass_from_A)
+ * and the call does what operators::NonlinearSolid::ResidualAndGrad does around the domain integrator
+ * (src/mimi/operators/nonlinear_solid.cpp:257: J.data <- mass.data; then AddDomainResidualAndGrad): r += R(u),
+ * A_out = M + grad_factor K_fd(u), bit-identical to mb2_add_domain_residual_and_grad on an A preloaded with M.
+ * Host traffic per call: u, r in (2 NV doubles), r and A_out out (NV + nnz doubles). */
+int mb2_domain_residual_and_grad_on_mass(mb2_ctx* ctx, const double* u, double grad_factor, double* r, double* A_out);
 /* The resident CSR values (e.g. after mb2_set_A(NULL) + mb2_assemble_mass_device) become the mass of the Newton
  * sweeps without leaving the device; form_system_matrix != 0 applies BilinearForm::FormSystemMatrix(zero_dofs, .)
  * (py_nonlinear_solid.cpp:173) for the dofs of mb2_set_essential_dofs: rows / columns zeroed, diagonal one. */

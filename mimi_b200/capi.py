@@ -32,6 +32,7 @@ SYMBOLS = [
     "mb2_add_boundary_residual_and_grad", "mb2_contact_residual_device", "mb2_contact_residual_and_grad_device",
     "mb2_contact_get_nodal", "mb2_contact_last_scalars", "mb2_contact_gap_norm", "mb2_set_mass", "mb2_set_viscosity",
     "mb2_set_rhs", "mb2_set_essential_dofs", "mb2_newton_residual_and_grad_device", "mb2_newton_residual_device", "mb2_newton_solve_gmres_device", "mb2_newton_get_solution",
+    "mb2_domain_residual_and_grad_on_mass",
 ]
 
 
@@ -329,6 +330,10 @@ class Context:
 
     def add_domain_residual_and_grad(self, u, gf, r, A):
         self._ck(self.lib.mb2_add_domain_residual_and_grad(self.h, _dp(u), C.c_double(gf), _dp(r), _dp(A)))
+
+    def domain_residual_and_grad_on_mass(self, u, gf, r, A_out):
+        """r += R(u); A_out = M + gf K(u) with the mass resident on the device (mb2_set_mass): no CSR upload."""
+        self._ck(self.lib.mb2_domain_residual_and_grad_on_mass(self.h, _dp(u), C.c_double(gf), _dp(r), _dp(A_out)))
 
     # ---- device-resident hot path
     def set_u(self, u):

@@ -236,18 +236,32 @@ int mb2_set_time_step(mb2_ctx* c, double dt) {
   return MB2_OK;
 }
 
-// Device failure flag raised by the return-mapping scalar solve (newton.hpp:81-93,119-132 throw in the reference).
-int mb2_check_numeric(mb2_ctx* c) {
-  CHECK_CTX(c);
+// Device failure flag: every code has its own message, and the flag is cleared once reported.
+//   1, 2  return-mapping scalar solve (newton.hpp:81-93,119-132 throw in the reference)
+//   3     EliminateRowCol on a non-symmetric pattern (sparsemat.cpp "EliminateRowCol() #2")
+//   4     DSmoother / DiagScale without a diagonal entry
+extern "C++" {
+namespace mb2 {
+int consume_flag(mb2_ctx* c) {
   int flag = 0;
   MB2_CUDA(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   MB2_CUDA(cudaStreamSynchronize(c->stream));
-  if (flag) {
-    MB2_CUDA(cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
-    c->err = flag == 1 ? "ScalarSolve: root not bracketed by input bounds" : "ScalarSolve: failed to converge in allotted iterations";
-    return MB2_ERR_NUMERIC;
+  if (!flag) return MB2_OK;
+  MB2_CUDA(cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
+  switch (flag) {
+    case 1: c->err = "ScalarSolve: root not bracketed by input bounds"; break;
+    case 2: c->err = "ScalarSolve: failed to converge in allotted iterations"; break;
+    case 3: c->err = "EliminateRowCol: the sparsity pattern is not symmetric (column entry without its row twin)"; break;
+    case 4: c->err = "Diagonal not found in SparseMatrix::DiagScale"; break;
+    default: c->err = "device failure flag " + std::to_string(flag); break;
   }
-  return MB2_OK;
+  return MB2_ERR_NUMERIC;
+}
+}  // namespace mb2
+}  // extern "C++"
+int mb2_check_numeric(mb2_ctx* c) {
+  CHECK_CTX(c);
+  return mb2::consume_flag(c);
 }
 
 int mb2_state_size(mb2_ctx* c) { return c ? c->ns : 0; }

@@ -1308,7 +1308,9 @@ int assemble_begin(mb2_ctx* c, double gf, bool grad, const double* A_in, double*
 int assemble_finish(mb2_ctx* c, double gf, bool grad, double* A_out) {
   Plan* P = static_cast<Plan*>(c->plan);
   MgState* mg = c->mg;
-  if (mg && !mg->manual && P->NE > P->n_own) MB2_CUDA(cudaStreamWaitEvent(P->s_ga, mg->ev_comm, 0));
+  // Join the exchange on EVERY rank, also the ones that only send: the caller's stream must not complete (and the next
+  // assembly's k_pack must not overwrite p.d_send) while an ncclSend of this step is still reading the packed buffers.
+  if (mg && !mg->manual) MB2_CUDA(cudaStreamWaitEvent(P->s_ga, mg->ev_comm, 0));
   if (grad && P->nch > P->nch_own) {
     const int ch = P->nch_own;
     const int64_t e0 = P->begin_of(ch), e1 = P->end_of(ch);

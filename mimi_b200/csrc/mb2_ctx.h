@@ -102,6 +102,8 @@ namespace mb2 {
 // mb2_pattern.cu
 int build_pattern(mb2_ctx* c);
 int expand_A_ids(mb2_ctx* c, int32_t* d_out);
+// mb2_api.cu
+int consume_flag(mb2_ctx* c);  // reads + clears the device failure flag; MB2_ERR_NUMERIC with a per-code message
 // mb2_assembly.cu
 int launch_residual(mb2_ctx* c);
 int launch_post_time_advance(mb2_ctx* c);

@@ -397,6 +397,7 @@ int newton_residual(mb2_ctx* c, const double* x, const double* v, const double* 
     double dd = 0.0;
     if ((rc = dev_dot(c, S, c->d_r, c->d_r, &dd))) return rc;
     *norm_out = std::sqrt(dd);
+    if ((rc = consume_flag(c))) return rc;  // the norm already synchronised: a failed return mapping surfaces here
   }
   return MB2_OK;
 }
@@ -561,15 +562,29 @@ int mb2_newton_solve_gmres_device(mb2_ctx* c, double rel_tol, double abs_tol, in
   MB2_CUDA(cudaSetDevice(c->device));
   rc = mb2::newton_solve_gmres(c, rel_tol, abs_tol, max_iter, kdim, iterations, final_norm, converged);
   if (rc) return rc;
-  int flag = 0;
-  MB2_CUDA(cudaMemcpy(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost));
-  if (flag == 4) {
-    int zero = 0;
-    MB2_CUDA(cudaMemcpy(c->d_flag, &zero, sizeof(int), cudaMemcpyHostToDevice));
-    c->err = "Diagonal not found in SparseMatrix::DiagScale";
-    return MB2_ERR_NUMERIC;
-  }
-  return MB2_OK;
+  // any latched device failure (a failed return mapping in the assembly that produced J, a bad elimination, a missing
+  // diagonal) makes this solve meaningless: the reference would have thrown before reaching its linear solver
+  return mb2::consume_flag(c);
+}
+
+// Host-CSR consumer without the per-step upload of the CSR: what operators::NonlinearSolid::ResidualAndGrad does around
+// the domain integrator (operators/nonlinear_solid.cpp:257: J.data <- mass.data, then stiffness->AddMultGrad), with the mass
+// resident since mb2_set_mass / mb2_newton_mass_from_A. r += R(u) (r travels both ways, NV doubles); A_out = M + gf K(u)
+// leaves chunk by chunk behind the element kernels (D2H only).
+int mb2_domain_residual_and_grad_on_mass(mb2_ctx* c, const double* u, double gf, double* r, double* A_out) {
+  if (!c) return MB2_ERR_ARG;
+  NewtonState* S = static_cast<NewtonState*>(c->newton);
+  if (!S || !S->d_M) { c->err = "call mb2_set_mass (or mb2_newton_mass_from_A) first"; return MB2_ERR_ARG; }
+  if (!u || !r || !A_out) { c->err = "null vector"; return MB2_ERR_ARG; }
+  if (!c->d_dNdX || c->mat_kind < 0) { c->err = "tables / material missing"; return MB2_ERR_ARG; }
+  MB2_CUDA(cudaSetDevice(c->device));
+  int rc;
+  if ((rc = mb2_set_u(c, u))) return rc;
+  if ((rc = mb2_set_r(c, r))) return rc;
+  MB2_CUDA(cudaMemcpyAsync(c->d_A, S->d_M, sizeof(double) * c->nnz, cudaMemcpyDeviceToDevice, c->stream));
+  if ((rc = mb2::launch_residual_and_grad(c, gf, nullptr, A_out))) return rc;
+  if ((rc = mb2_get_r(c, r))) return rc;
+  return c->ns ? mb2_check_numeric(c) : MB2_OK;
 }
 
 int mb2_newton_get_solution(mb2_ctx* c, double* out) {

@@ -261,7 +261,10 @@ def run_ref_dump(mesh, elevate, refine, material, outdir, gf=1.0, nthreads=1, u_
 
 def run_ref_time(mesh, elevate, refine, material, nthreads, reps, warmup=0):
     cmd = [REF_BIN, "time", mesh, str(elevate), str(refine), material, str(nthreads), str(reps), str(warmup)]
-    p = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, check=True, text=True)
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to its children; the reference sizes its own OpenMP team
+    # (py_solid.cpp:303-318) and the harness does too, but the environment must not cap it either
+    env = {**os.environ, "OMP_NUM_THREADS": str(nthreads), "OMP_DYNAMIC": "false"}
+    p = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, check=True, text=True, env=env)
     return json.loads(p.stderr.strip().splitlines()[-1])
 
 

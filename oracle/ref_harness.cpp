@@ -24,6 +24,7 @@
 #include <vector>
 
 #include <mfem.hpp>
+#include <omp.h>
 
 #include "mimi/coefficients/nearest_distance.hpp"
 #include "mimi/integrators/mortar_contact.hpp"
@@ -88,6 +89,9 @@ struct Setup {
 Setup build(const char* mesh_file, int elevate, int refine, const std::string& material, int nthreads,
             bool with_mass) {
   Setup s;
+  // PySolid::SetupNTheads (py_solid.cpp:303-318): the reference sizes its OpenMP team itself. Without this a parent that
+  // exports OMP_NUM_THREADS=1 (torch.distributed.run does) would run NThreadExe's `#pragma omp parallel for` on one thread.
+  omp_set_num_threads(nthreads > 0 ? nthreads : 1);
   s.mesh = std::make_unique<mfem::Mesh>(mesh_file, 1, 1);  // py_solid.cpp:76
   if (elevate > 0) s.mesh->DegreeElevate(elevate, 50);     // py_solid.cpp:155
   for (int i = 0; i < refine; ++i) s.mesh->UniformRefinement();  // py_solid.cpp:177
@@ -808,6 +812,12 @@ int main(int argc, char** argv) {
     fill_u(u, "-");
     mfem::SparseMatrix A(*pre.sparsity_pattern_);
     double best_rg = 1e300, best_r = 1e300, sum_rg = 0;
+    int omp_team = 0;  // threads an OpenMP parallel region really gets here (what NThreadExe runs on)
+#pragma omp parallel
+    {
+#pragma omp single
+      omp_team = omp_get_num_threads();
+    }
     for (int i = 0; i < warm; ++i) {
       r = 0.0; A = 0.0;
       s.integ->AddDomainResidualAndGrad(u, 1.0, r, A);
@@ -826,8 +836,10 @@ int main(int argc, char** argv) {
     }
     std::fprintf(stderr,
                  "{\"NE\": %d, \"nq\": %d, \"NV\": %d, \"nnz\": %d, \"nthreads\": %d, \"reps\": %d, "
-                 "\"t_res_grad_best\": %.6f, \"t_res_grad_mean\": %.6f, \"t_res_best\": %.6f, \"t_precompute\": %.3f}\n",
-                 NE, nq, NV, A.NumNonZeroElems(), nthreads, reps, best_rg, sum_rg / reps, best_r, s.t_precompute);
+                 "\"t_res_grad_best\": %.6f, \"t_res_grad_mean\": %.6f, \"t_res_best\": %.6f, \"t_precompute\": %.3f, "
+                 "\"omp_max_threads\": %d, \"omp_team\": %d}\n",
+                 NE, nq, NV, A.NumNonZeroElems(), nthreads, reps, best_rg, sum_rg / reps, best_r, s.t_precompute,
+                 omp_get_max_threads(), omp_team);
     return 0;
   }
   std::fprintf(stderr, "unknown mode\n");
