@@ -194,13 +194,18 @@ def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean", s
     return M
 
 
-def source_md5():
-    """md5 of the kernel sources: a committed ncu capture only speaks for the binary built from the same sources."""
+def source_md5(kernel_key=""):
+    """md5 of the kernel's source text: a committed ncu capture only speaks for a binary built from the same kernel
+    source. p=2: the text of element_fd_kernel (Elem2Cfg .. the next section) + mb2_math.cuh; p=3: element_fd_split_kernel."""
     import hashlib
+    src = open(os.path.join(ROOT, "mimi_b200", "csrc", "mb2_assembly.cu")).read()
+    a, b = ("struct Elem3Cfg", "// History commit:") if "split" in kernel_key else ("struct Elem2Cfg", "// FD-tangent element kernel, column-split")
+    i = src.find(a)
+    j = src.find(b, i)
     h = hashlib.md5()
-    for f in ("mb2_assembly.cu", "mb2_math.cuh"):
-        with open(os.path.join(ROOT, "mimi_b200", "csrc", f), "rb") as fh:
-            h.update(fh.read())
+    h.update((src[i:j] if i >= 0 and j > i else src).encode())
+    with open(os.path.join(ROOT, "mimi_b200", "csrc", "mb2_math.cuh"), "rb") as fh:
+        h.update(fh.read())
     return h.hexdigest()
 
 
@@ -216,7 +221,7 @@ def ncu_traffic(kernel_key, launch_elems):
     ent = T.get(kernel_key)
     if not ent:
         return None, "no ncu capture of %s in profiles/traffic.json" % kernel_key
-    if ent.get("source_md5") != source_md5():
+    if ent.get("source_md5") != source_md5(kernel_key):
         return None, "profiles/traffic.json holds a capture of another source revision of %s (%s)" % (kernel_key, ent.get("capture"))
     per_el = (ent["dram_read_bytes"] + ent["dram_write_bytes"]) / float(ent["launch_elements"])
     return per_el * launch_elems, "%s: %d-element launch, read %.1f MB + write %.1f MB, scaled to %d elements per launch" % (

@@ -177,6 +177,11 @@ __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel
 // Every floating-point value is produced by the reference's own operation sequence (Appendix A of
 // SURVEY.md): the split changes which thread executes an operation, never the operation order seen
 // by any accumulator.
+// What bounds it (ncu, profiles/r02_elem_fd_variants_summary.txt): the FP64 pipe (77 % of the cycles) AND the
+// shared-memory path (62 %: a broadcast LDS.128 costs 1.9 wavefronts, the 4-address form of phase 2 costs 3.26).
+// Two round-2 rewrites that cut FP64 instructions by 9 % (re-using the unperturbed products u_k dN_k of the F row)
+// but needed more wavefronts, with and without warp-specialised producer / consumer warps, measured 7 - 9 % SLOWER
+// and were removed again.
 // ---------------------------------------------------------------------------------------------
 template <int DIM, int ND, int NQ>
 struct Elem2Cfg {
@@ -409,353 +414,6 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
     __syncthreads();
   }
 #undef MB2_ROW2
-}
-
-// ---------------------------------------------------------------------------------------------
-// FD-tangent element kernel, round-2 form: product re-use in phase 1 + optional warp specialisation.
-//
-// (1) Product re-use. The perturbed row of F is the sequential sum  d = ((0 + u_0 dN_0) + u_1 dN_1) + ...  (MultAtB,
-//     densemat.cpp:3051-3068) in which ONE factor u_a is replaced by u_a + h. Every other product u_k dN_k is the very
-//     double the unperturbed evaluation rounds to, so it is computed once per (q, c, j, k) -- by the phase-1 thread that
-//     owns k == a, one chunk ahead -- and kept in shared memory; a perturbed evaluation then only re-runs the additions
-//     (81 DADD + 3 DMUL instead of 81 DMUL + 81 DADD), in the same order, bit for bit.
-// (2) Tasks are ordered by the perturbed node a (task = a*DIM*QC + c*QC + qs), so the lanes of a warp span <= 5 values of
-//     a: the "is this the replaced term" select is only needed for those k; all other k run select-free behind a
-//     warp-uniform branch.
-// (3) NPW > 0: NPW producer warps run phase 1 (stress) and 8 consumer warps run phase 2 (accumulate) CONCURRENTLY on a
-//     double-buffered b tile, handing chunks over through named barriers (bar.sync / bar.arrive): the latency-bound
-//     material evaluations and the throughput-bound register-tiled accumulation share every SM sub-partition all the
-//     time instead of alternating. NPW == 0: all warps alternate as in element_fd_kernel.
-// ---------------------------------------------------------------------------------------------
-template <int DIM, int ND, int NQ, int NPW>
-struct Elem4Cfg {
-  static constexpr int TD = DIM * ND;
-  static constexpr int DD = DIM * DIM;
-  static constexpr int NM = TD + 1;                  // perturbations + the base evaluation
-  static constexpr int NCW = 8;                      // warps that run phase 2
-  static constexpr int NCT = 32 * NCW;
-  static constexpr int NT = 32 * (NCW + NPW);
-  static constexpr int MAXR = (65536 / (2 * NT)) / 8 * 8;
-  static constexpr int QC = NCT / NM;                // quadrature points per chunk
-  static constexpr int NCH = (NQ + QC - 1) / QC;
-  static constexpr int NB = NM * DIM;                // phase-2 columns (m, j)
-  static constexpr int LI = 4, LC = 8, TC = 4;
-  static constexpr int TI = (ND + LI - 1) / LI;
-  static constexpr int NDP = (LI * TI + 1) / 2 * 2;
-  static constexpr int NBP = (NB + TC - 1) / TC * TC;
-  static constexpr int KP = (TD * DIM + 3) / 4 * 4;
-  static constexpr int NPERT = TD * QC;              // perturbed phase-1 tasks per chunk
-  static constexpr int NTASK = NM * QC;              // + QC base tasks
-  static constexpr int NPT = NPW ? 32 * NPW : NCT;   // threads that run phase 1
-  static constexpr int NRND = (NTASK + NPT - 1) / NPT;
-  static constexpr int SPR = DIM * NDP + 2;          // one (qs, c) group of product rows [j][NDP] (+2: bank spread)
-  static constexpr int SPBUF = QC * DIM * SPR;
-  static constexpr int SBBUF = QC * DIM * NBP;
-  static constexpr int OFF_DN = 0;                          // [NQ][DIM][NDP]
-  static constexpr int OFF_FB = OFF_DN + NQ * DIM * NDP;    // [NQ][DD] base F
-  static constexpr int OFF_SB = (OFF_FB + NQ * DD + 1) / 2 * 2;  // [2][QC][DIM][NBP]
-  static constexpr int OFF_SP = OFF_SB + 2 * SBBUF;         // [2][QC*DIM][SPR] products u_k dN_k
-  static constexpr int OFF_WD = OFF_SP + 2 * SPBUF;         // [NQ]
-  static constexpr int OFF_UE = (OFF_WD + NQ + 1) / 2 * 2;  // [DIM][NDP]
-  static constexpr int OFF_UP = OFF_UE + DIM * NDP;         // [TD] perturbed values u_m + h_m
-  static constexpr int OFF_RB = OFF_UP + TD;                // [TD]
-  static constexpr int SMEM_DOUBLES = OFF_RB + TD;
-  static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
-  static_assert(QC >= 1 && NBP <= NCW * LC * TC && LI * LC == 32, "CTA too small for this element type");
-  static_assert(NBP % 4 == 0 && SBBUF % 2 == 0 && SPBUF % 2 == 0 && SPR % 2 == 0, "alignment");
-};
-
-__device__ __forceinline__ void named_bar_sync(int id, int count) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
-}
-__device__ __forceinline__ void named_bar_arrive(int id, int count) {
-  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
-}
-
-// products of chunk `chn` owned by task tau = (a, c, qs): p(qs, c, j, k = a) = u_c[a] * dN(q; a, j)
-template <class Cfg, int DIM, int NQ>
-__device__ __forceinline__ void fd4_products(int tau, int chn, const double* sdN, const double* sue, double* sP) {
-  if (tau >= Cfg::NPERT) return;
-  const int a = tau / (DIM * Cfg::QC), rem = tau - a * (DIM * Cfg::QC);
-  const int c = rem / Cfg::QC, qs = rem - c * Cfg::QC;
-  const int q = chn * Cfg::QC + qs;
-  if (q >= NQ) return;
-  const double un = sue[c * Cfg::NDP + a];
-  double* o = sP + (chn & 1) * Cfg::SPBUF + (qs * DIM + c) * Cfg::SPR + a;
-#pragma unroll
-  for (int j = 0; j < DIM; j++) o[j * Cfg::NDP] = un * sdN[(q * DIM + j) * Cfg::NDP + a];
-}
-
-// phase 1 of task tau in chunk ch: b(qs; m, :, :) = (w detJ) P(F_m(q)); also the products of chunk ch+1 it owns
-template <class Cfg, int DIM, int ND, int NQ, int MAT>
-__device__ __forceinline__ void fd4_phase1(int tau, int ch, int xlo, int xhi, const ElemArgs& g, int64_t e, const double* sdN,
-                                           const double* sFb, const double* sue, const double* sup, const double* swd,
-                                           double* sP, double* sb) {
-  constexpr int DD = DIM * DIM, TD = DIM * ND, QC = Cfg::QC, NDP = Cfg::NDP, NBP = Cfg::NBP, NS = mat_state_size(MAT);
-  if (tau >= Cfg::NTASK) return;
-  const bool pert = tau < Cfg::NPERT;
-  int a = 0, c = 0, qs;
-  if (pert) {
-    a = tau / (DIM * QC);
-    const int rem = tau - a * (DIM * QC);
-    c = rem / QC;
-    qs = rem - c * QC;
-  } else {
-    qs = tau - Cfg::NPERT;
-  }
-  const int q = ch * QC + qs;
-  if (q >= NQ) return;
-  double F[DD], P[DD];
-#pragma unroll
-  for (int n = 0; n < DD; n++) F[n] = sFb[q * DD + n];
-  if (pert) {
-    // only row c of F depends on the perturbed dof; the other rows are bit-identical to the base F
-    const double up = sup[c * ND + a];
-    const double* spc = sP + (ch & 1) * Cfg::SPBUF + (qs * DIM + c) * Cfg::SPR;
-    double pt[DIM], drow[DIM];
-#pragma unroll
-    for (int j = 0; j < DIM; j++) {
-      pt[j] = up * sdN[(q * DIM + j) * NDP + a];
-      drow[j] = 0.0;
-    }
-#pragma unroll
-    for (int x = 0; x < (ND + 1) / 2; x++) {
-      double2 pv[DIM];
-#pragma unroll
-      for (int j = 0; j < DIM; j++) pv[j] = *reinterpret_cast<const double2*>(spc + j * NDP + 2 * x);
-      if (x >= xlo && x <= xhi) {  // warp-uniform: some lane's replaced term lies in this pair
-#pragma unroll
-        for (int j = 0; j < DIM; j++) {
-          const double p0 = (2 * x == a) ? pt[j] : pv[j].x;
-          const double p1 = (2 * x + 1 == a) ? pt[j] : pv[j].y;
-          drow[j] += p0;
-          if (2 * x + 1 < ND) drow[j] += p1;
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < DIM; j++) {
-          drow[j] += pv[j].x;
-          if (2 * x + 1 < ND) drow[j] += pv[j].y;
-        }
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < DIM; j++) {
-      const double fnew = (j == c) ? drow[j] + 1.0 : drow[j];
-#pragma unroll
-      for (int i = 0; i < DIM; i++)
-        if (i == c) F[i + DIM * j] = fnew;
-    }
-    fd4_products<Cfg, DIM, NQ>(tau, ch + 1, sdN, sue, sP);
-  }
-  material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + q) * NS : nullptr, P);
-  const double aq = swd[q];
-  double* o = sb + (ch & 1) * Cfg::SBBUF + qs * (DIM * NBP) + (pert ? c * ND + a : TD) * DIM;
-  // bjk = a * P(j,k)   (densemat.cpp:3008)
-#pragma unroll
-  for (int k = 0; k < DIM; k++)
-#pragma unroll
-    for (int j = 0; j < DIM; j++) o[k * NBP + j] = aq * P[j + DIM * k];
-}
-
-// registers per thread for 2 CTAs per SM: 65536 / (2 NT), rounded down to the allocation unit of 8
-template <int DIM, int ND, int NQ, int MAT, int NPW>
-__global__ void __launch_bounds__(Elem4Cfg<DIM, ND, NQ, NPW>::NT) __maxnreg__((Elem4Cfg<DIM, ND, NQ, NPW>::MAXR))
-    element_fd4_kernel(const ElemArgs g) {
-  using Cfg = Elem4Cfg<DIM, ND, NQ, NPW>;
-  constexpr int TD = Cfg::TD, DD = Cfg::DD, NT = Cfg::NT, NCT = Cfg::NCT, QC = Cfg::QC, NCH = Cfg::NCH, NDP = Cfg::NDP,
-                NB = Cfg::NB, NBP = Cfg::NBP, TI = Cfg::TI, TC = Cfg::TC, LI = Cfg::LI, LC = Cfg::LC, KP = Cfg::KP,
-                NPT = Cfg::NPT, NRND = Cfg::NRND;
-  extern __shared__ __align__(16) double smem[];
-  double* sdN = smem + Cfg::OFF_DN;
-  double* sFb = smem + Cfg::OFF_FB;
-  double* sb = smem + Cfg::OFF_SB;
-  double* sP = smem + Cfg::OFF_SP;
-  double* swd = smem + Cfg::OFF_WD;
-  double* sue = smem + Cfg::OFF_UE;
-  double* sup = smem + Cfg::OFF_UP;
-  double* sRb = smem + Cfg::OFF_RB;
-  const int t = threadIdx.x;
-  const int lane = t & 31, warp = t >> 5;
-  const int64_t e = g.e0 + blockIdx.x;
-
-  // ---- stage: gathered dofs (Vector::GetSubVector), weights, dN_dX rows padded to NDP; pads zeroed
-  for (int idx = t; idx < NQ * DIM; idx += NT)
-    for (int i = ND; i < NDP; i++) sdN[idx * NDP + i] = 0.0;
-  for (int idx = t; idx < 2 * Cfg::SBBUF; idx += NT) sb[idx] = 0.0;
-  if (t < DIM)
-    for (int i = ND; i < NDP; i++) sue[t * NDP + i] = 0.0;
-  if (t < TD) {
-    const double orig = g.u[g.vdofs[e * TD + t]];
-    sue[(t / ND) * NDP + t % ND] = orig;
-    const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;  // nonlinear_solid.cpp:62-68
-    sup[t] = orig + h;
-  }
-  if (t < NQ) swd[t] = g.wdetJ[e * NQ + t];
-  {
-    const double* src = g.dNdX + e * (int64_t)(NQ * TD);
-    for (int idx = t; idx < NQ * TD; idx += NT) {
-      const int row = idx / ND, i = idx - row * ND;  // row = q*DIM + k
-      sdN[row * NDP + i] = __ldg(src + idx);
-    }
-  }
-  __syncthreads();
-  // ---- base F for every q: MultAtB(element_x_mat_, dN_dX, F_) + AddDiagonal(1.0) (integrator_utils.cpp:33-40)
-  for (int task = t; task < NQ * DD; task += NT) {
-    const int q = task / DD, n = task - q * DD;
-    const int i = n % DIM, j = n / DIM;
-    const double* dN = sdN + (q * DIM + j) * NDP;
-    const double* ui = sue + i * NDP;
-    double d = 0.0;
-#pragma unroll
-    for (int k = 0; k < ND; k++) d += ui[k] * dN[k];
-    if (i == j) d += 1.0;
-    sFb[task] = d;
-  }
-  // phase-1 identity of this thread
-  const bool producer = NPW ? (warp >= Cfg::NCW) : true;
-  const int pt = NPW ? t - NCT : t;  // index among the phase-1 threads
-  if (producer) {
-#pragma unroll
-    for (int r = 0; r < NRND; r++) fd4_products<Cfg, DIM, NQ>(r * NPT + pt, 0, sdN, sue, sP);
-  }
-  __syncthreads();
-
-  // warp-uniform range of k-pairs in which some lane of this warp replaces a term (per round)
-  int xlo[NRND], xhi[NRND];
-#pragma unroll
-  for (int r = 0; r < NRND; r++) {
-    const int t0 = r * NPT + (pt & ~31);
-    int t1 = t0 + 31;
-    if (t1 > Cfg::NPERT - 1) t1 = Cfg::NPERT - 1;
-    xlo[r] = (t0 / (DIM * QC)) / 2;
-    xhi[r] = (t1 / (DIM * QC)) / 2;
-  }
-
-  // phase-2 identity
-  const int li = lane % LI;
-  constexpr int NP = TI / 2;
-#define MB2_ROW4(x) (((x) < 2 * NP) ? (2 * LI * ((x) / 2) + 2 * li + (x) % 2) : (2 * LI * NP + li))
-  const int col0 = (warp * LC + lane / LI) * TC;
-  const bool consumer = warp < Cfg::NCW;
-  const bool act2 = consumer && col0 < NB;
-  double R[TI][TC];
-#pragma unroll
-  for (int x = 0; x < TI; x++)
-#pragma unroll
-    for (int y = 0; y < TC; y++) R[x][y] = 0.0;
-
-  auto phase2 = [&](int ch) {
-    const double* sbc = sb + (ch & 1) * Cfg::SBBUF;
-#pragma unroll
-    for (int qs = 0; qs < QC; qs++) {
-      const int q = ch * QC + qs;
-      if (q < NQ) {
-#pragma unroll
-        for (int k = 0; k < DIM; k++) {
-          double bv[TC], dv[TI];
-          const double2* b2 = reinterpret_cast<const double2*>(sbc + (qs * DIM + k) * NBP + col0);
-#pragma unroll
-          for (int y = 0; y < TC / 2; y++) {
-            const double2 v = b2[y];
-            bv[2 * y] = v.x;
-            bv[2 * y + 1] = v.y;
-          }
-          const double* dN = sdN + (q * DIM + k) * NDP;
-#pragma unroll
-          for (int p = 0; p < NP; p++) {
-            const double2 v = *reinterpret_cast<const double2*>(dN + 2 * LI * p + 2 * li);
-            dv[2 * p] = v.x;
-            dv[2 * p + 1] = v.y;
-          }
-          if (TI % 2) dv[TI - 1] = dN[2 * LI * NP + li];
-#pragma unroll
-          for (int x = 0; x < TI; x++)
-#pragma unroll
-            for (int y = 0; y < TC; y++) R[x][y] += dv[x] * bv[y];
-        }
-      }
-    }
-  };
-
-  if (NPW == 0) {
-#pragma unroll 1
-    for (int ch = 0; ch < NCH; ch++) {
-      fd4_phase1<Cfg, DIM, ND, NQ, MAT>(t, ch, xlo[0], xhi[0], g, e, sdN, sFb, sue, sup, swd, sP, sb);
-      __syncthreads();
-      // AddMult_a_ABt order: q then k ascending per accumulator (densemat.cpp:3002-3015)
-      if (act2) phase2(ch);
-    }
-  } else if (!consumer) {
-    // named barriers: 1 + b = "b tile b full", 3 + b = "b tile b free", 5 = producers only
-#pragma unroll 1
-    for (int ch = 0; ch < NCH; ch++) {
-      if (ch >= 2) named_bar_sync(3 + (ch & 1), NT);
-#pragma unroll
-      for (int r = 0; r < NRND; r++)
-        fd4_phase1<Cfg, DIM, ND, NQ, MAT>(r * NPT + pt, ch, xlo[r], xhi[r], g, e, sdN, sFb, sue, sup, swd, sP, sb);
-      __threadfence_block();
-      named_bar_arrive(1 + (ch & 1), NT);
-      named_bar_sync(5, NPT);  // products of chunk ch+1 complete; everyone has read those of chunk ch
-    }
-    return;
-  } else {
-#pragma unroll 1
-    for (int ch = 0; ch < NCH; ch++) {
-      named_bar_sync(1 + (ch & 1), NT);
-      if (act2) phase2(ch);
-      if (ch + 2 < NCH) named_bar_arrive(3 + (ch & 1), NT);
-    }
-  }
-
-  // ---- base residual -> smem + global; then forward differences (nonlinear_solid.cpp:69-74)
-  if (act2) {
-#pragma unroll
-    for (int y = 0; y < TC; y++) {
-      const int col = col0 + y;
-      if (col >= TD * DIM && col < NB) {
-        const int j = col - TD * DIM;
-#pragma unroll
-        for (int x = 0; x < TI; x++)
-          if (MB2_ROW4(x) < ND) {
-            sRb[MB2_ROW4(x) + j * ND] = R[x][y];
-            g.Re[e * TD + MB2_ROW4(x) + j * ND] = R[x][y];
-          }
-      }
-    }
-  }
-  if (NPW == 0) __syncthreads();
-  else named_bar_sync(6, NCT);
-  if (act2) {
-    // K_e block layout: [row node i][KP]: column = perturbed dof m * DIM + row component j
-    double hinv[TC];
-    int jj[TC];
-#pragma unroll
-    for (int y = 0; y < TC; y++) {
-      const int col = col0 + y;
-      const int m = (col < TD * DIM) ? col / DIM : 0;
-      jj[y] = col % DIM;
-      const double orig = sue[(m / ND) * NDP + m % ND];
-      const double h = (orig != 0.0) ? fabs(orig) * 1.0e-8 : 1.0e-10;
-      hinv[y] = 1. / h;
-    }
-    double* out = g.KeT + (e - g.e0) * (int64_t)(ND * KP) + col0;
-#pragma unroll
-    for (int x = 0; x < TI; x++) {
-      const int i = MB2_ROW4(x);
-      if (i < ND) {
-        double v[TC];
-#pragma unroll
-        for (int y = 0; y < TC; y++) v[y] = (R[x][y] - sRb[i + jj[y] * ND]) * hinv[y];
-        if (col0 + TC <= KP) {
-          double2* o2 = reinterpret_cast<double2*>(out + (int64_t)i * KP);
-#pragma unroll
-          for (int y = 0; y < TC / 2; y++) o2[y] = make_double2(v[2 * y], v[2 * y + 1]);
-        }
-      }
-    }
-  }
-#undef MB2_ROW4
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1321,17 +979,6 @@ static int launch_element_fd(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   return MB2_OK;
 }
 
-template <int DIM, int ND, int NQ, int MAT, int NPW>
-static int launch_element_fd4(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
-  using Cfg = Elem4Cfg<DIM, ND, NQ, NPW>;
-  auto kern = element_fd4_kernel<DIM, ND, NQ, MAT, NPW>;
-  MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
-  const int64_t grid = a.e1 - a.e0;  // one CTA per element, as launch_element_fd
-  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, st>>>(a);
-  MB2_CUDA(cudaGetLastError());
-  return MB2_OK;
-}
-
 template <int DIM, int ND, int NQ, int MAT, int KS>
 static int launch_element_fd_split(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   using Cfg = Elem3Cfg<DIM, ND, NQ, KS>;
@@ -1363,21 +1010,6 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   if (c->mass_tab) {  // mb2_assemble_mass_device / mb2_assemble_body_force_device: same pipelines, M_e / b_e instead of K_e / R_e
     if (GRAD != (form_mode(c) != 1)) { c->err = "bilinear forms use the Jacobian pipeline, linear forms the residual one"; return MB2_ERR_ARG; }
     return GRAD ? launch_mass_element(c, a.e0, a.e1, a.KeT, a.Re, st) : launch_lform_element(c, a.e0, a.e1, a.Re, st);
-  }
-  if (GRAD && dim == 3 && nd == 27 && nq == 64 && c->elem_variant >= 3 && c->elem_variant <= 6 &&
-      (c->mat_kind == MAT_NEOHOOKEAN || c->mat_kind == MAT_STVK)) {
-    // A/B: 3 = product re-use, all warps alternate; 4 / 5 / 6 = + 3 / 4 / 2 producer warps (warp-specialised)
-    const int v = c->elem_variant;
-    if (c->mat_kind == MAT_NEOHOOKEAN) {
-      if (v == 3) return launch_element_fd4<3, 27, 64, MAT_NEOHOOKEAN, 0>(c, a, st);
-      if (v == 4) return launch_element_fd4<3, 27, 64, MAT_NEOHOOKEAN, 3>(c, a, st);
-      if (v == 6) return launch_element_fd4<3, 27, 64, MAT_NEOHOOKEAN, 2>(c, a, st);
-      return launch_element_fd4<3, 27, 64, MAT_NEOHOOKEAN, 4>(c, a, st);
-    }
-    if (v == 3) return launch_element_fd4<3, 27, 64, MAT_STVK, 0>(c, a, st);
-    if (v == 4) return launch_element_fd4<3, 27, 64, MAT_STVK, 3>(c, a, st);
-    if (v == 6) return launch_element_fd4<3, 27, 64, MAT_STVK, 2>(c, a, st);
-    return launch_element_fd4<3, 27, 64, MAT_STVK, 4>(c, a, st);
   }
   if (GRAD && dim == 3 && nd == 27 && nq == 64 && c->elem_variant != 1) {
     switch (c->mat_kind) {
