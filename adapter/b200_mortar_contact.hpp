@@ -32,6 +32,52 @@ struct B200RigidBody {
   virtual std::vector<double> B200Params() const = 0;   // layout of mb2_contact_set_rigid_body for that kind
 };
 
+/// The reference's own scene class (coefficients/nearest_distance.hpp:214-281) describing itself to the device: the
+/// control net / knots / weights are read from the splinepy core it holds (SplinepyCurrentProperties), so a script keeps
+/// calling scene.add_spline(curv); scene.plant_kd_tree(resolution, nthreads) and moving curv.cps between steps.
+/// Kind by spline type: Bezier -> MB2_RIGID_BEZIER, RationalBezier -> MB2_RIGID_RATIONAL_BEZIER, BSpline ->
+/// MB2_RIGID_BSPLINE, NURBS -> MB2_RIGID_NURBS. The kd-tree resolution becomes the device's seed sampling (capped: the
+/// device samples every Bezier patch per query instead of planting a tree once).
+class B200NearestDistanceToSplines : public mimi::coefficients::NearestDistanceToSplines, public B200RigidBody {
+  int resolution_{65};
+
+public:
+  int max_seed_curve_{256}, max_seed_surface_{32};
+  void PlantKdTree(const int resolution, const int nthreads) {  // hides the base's: also remembers the sampling
+    resolution_ = resolution;
+    mimi::coefficients::NearestDistanceToSplines::PlantKdTree(resolution, nthreads);
+  }
+  int B200Kind() const override {
+    const auto& core = splines_.at(0)->Core();
+    const bool knots = core->SplinepyHasKnotVectors(), rational = core->SplinepyIsRational();
+    return knots ? (rational ? MB2_RIGID_NURBS : MB2_RIGID_BSPLINE) : (rational ? MB2_RIGID_RATIONAL_BEZIER : MB2_RIGID_BEZIER);
+  }
+  std::vector<double> B200Params() const override {
+    if (splines_.size() != 1) mimi::utils::PrintAndThrowError("mimi_b200: one spline per contact scene (as the reference asserts)");
+    const auto& core = splines_[0]->Core();
+    const int pd = core->SplinepyParaDim(), dim = core->SplinepyDim(), n = core->SplinepyNumberOfControlPoints();
+    const bool knots = core->SplinepyHasKnotVectors(), rational = core->SplinepyIsRational();
+    int deg[3] = {0, 0, 0}, res[3] = {1, 1, 1};
+    std::vector<std::vector<double>> kv;
+    std::vector<double> cps(size_t(n) * dim), w(rational ? n : 0);
+    core->SplinepyCurrentProperties(deg, knots ? &kv : nullptr, cps.data(), rational ? w.data() : nullptr);
+    core->SplinepyControlMeshResolutions(res);
+    const int cap = pd == 1 ? max_seed_curve_ : max_seed_surface_;
+    const int n_seed = std::max(1, std::min(resolution_ - 1, cap));
+    std::vector<double> p = {double(deg[0]), pd > 1 ? double(deg[1]) : 0.0, double(n_seed)};
+    if (knots) {
+      p.push_back(res[0]);
+      p.push_back(pd > 1 ? res[1] : 1);
+      for (int d = 0; d < pd; ++d) p.insert(p.end(), kv[d].begin(), kv[d].end());
+    }
+    for (int i = 0; i < n; ++i) {  // splinepy: first parametric direction fastest = the library's [v][u] layout
+      for (int c = 0; c < dim; ++c) p.push_back(cps[size_t(i) * dim + c]);
+      if (rational) p.push_back(w[i]);
+    }
+    return p;
+  }
+};
+
 class B200MortarContact : public NonlinearBase {
   mb2_ctx* ctx_;
   std::shared_ptr<mimi::coefficients::NearestDistanceBase> scene_;

@@ -94,6 +94,29 @@ def write_box_p1(path: str, lengths=(1.0, 1.0, 1.0)) -> None:
             f.write(" ".join(repr(float(c)) for c in v) + "\n")
 
 
+def write_cell_p1(path: str, verts, weights=None) -> None:
+    """Degree-1, one-element NURBS mesh with the given vertices (4 in 2D / 8 in 3D, MFEM's vertex order): a general
+    (non-affine) quadrilateral / hexahedron, e.g. the reference's tests/data/square-nurbs.mesh = [(0,0),(2,0),(1,1),(-1,2)];
+    optional NURBS weights per vertex make the patch rational."""
+    verts = [tuple(float(c) for c in v) for v in verts]
+    dim = len(verts[0])
+    if (dim, len(verts)) not in ((2, 4), (3, 8)):
+        raise ValueError("4 vertices in 2D, 8 in 3D")
+    topo = _QUAD_TOPOLOGY if dim == 2 else _HEX_TOPOLOGY
+    w = [1.0] * len(verts) if weights is None else [float(x) for x in weights]
+    with open(path, "w") as f:
+        f.write("MFEM NURBS mesh v1.0\n\n" + topo + "\nknotvectors\n%d\n" % dim)
+        for _ in range(dim):
+            f.write("1 2 0 0 1 1\n")
+        f.write("\nweights\n" + "".join(repr(x) + "\n" for x in w))
+        f.write("\nFiniteElementSpace\nFiniteElementCollection: NURBS1\nVDim: %d\nOrdering: 1\n\n" % dim)
+        for v in verts:
+            f.write(" ".join(repr(c) for c in v) + "\n")
+
+
+SQUARE_NURBS_VERTS = [(0.0, 0.0), (2.0, 0.0), (1.0, 1.0), (-1.0, 2.0)]   # the reference's tests/data/square-nurbs.mesh
+
+
 def open_uniform_knots(p: int, n: int) -> np.ndarray:
     """Open uniform knot vector of degree p with n spans on [0, 1] (n + 2p + 1 knots)."""
     inner = np.arange(0, n + 1, dtype=np.float64) / n

@@ -41,8 +41,38 @@ CONTACT_CASES = {
 }
 
 
+# Rigid bodies as the reference's own scenes hold them: NearestDistanceToSplines on REAL splinepy splines (closest point =
+# splinepy's kd-tree seed + Newton -> SLSQP -> LM, third_party/splinepy/src/proximity/proximity.cpp:643-733).
+def _spline_bodies():
+    s2 = np.sqrt(0.5)
+    # the cubic Bezier curve of examples/nl_contact.py:20-29 (control polygon shape), lowered onto the top of the 2 x 1 block
+    curve = np.array([[-0.5, 1.3], [0.6, 0.9], [1.4, 0.9], [2.5, 1.3]]) + [0.0, -0.0003]
+    # biquadratic Bezier surface bulging down onto the face z = 1 of the unit cube; rows reversed: normal = S_u x S_v points down
+    g = np.array([-0.5, 0.5, 1.5])
+    surf = np.array([[[g[i], g[j], 1.2 - 0.8012 * (i == 1) * (j == 1)] for i in range(3)] for j in range(3)])[::-1].copy()
+    # rational quadratic arc = the bottom quarter of the circle of contact_quad_p3_n4_sphere (c = (1, 1.9995), R = 1)
+    c, R = np.array([1.0, 1.9995]), 1.0
+    arc = np.array([c + R * np.array([-s2, -s2]), c + np.array([0.0, -R / s2]), c + R * np.array([s2, -s2])])
+    arc_w = np.array([1.0, s2, 1.0])
+    # cubic B-spline curve with two interior knots (what toy_problem.py's extracted boundaries look like)
+    bs = np.array([[-0.4, 1.25], [0.3, 1.05], [0.8, 0.9985], [1.2, 0.9985], [1.7, 1.05], [2.4, 1.25]]) - [0.0, 0.002]
+    bs_k = [0, 0, 0, 0, 1 / 3, 2 / 3, 1, 1, 1, 1]
+    return {
+        "contact_quad_p2_n4_bezier": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 1, 2, 0.3, 2, 1e5,
+                                      ("spline", O.spline_desc(200, curve))),
+        "contact_cube_p2_n4_bezier": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 1, 2, 0.7, 2, 1e5,
+                                      ("spline", O.spline_desc(64, surf))),
+        "contact_quad_p3_n4_rational_arc": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 2, 2, 0.3, 2, 1e5,
+                                            ("spline", O.spline_desc(200, arc, weights=arc_w))),
+        "contact_quad_p2_n4_bspline": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 1, 2, 0.3, 2, 1e5,
+                                       ("spline", O.spline_desc(150, bs, knots=[bs_k], degrees=(3, 0)))),
+    }
+
+
 def contact_main():
-    for name, (writer, elevate, refine, gf, attr, penalty, spec) in CONTACT_CASES.items():
+    cases = dict(CONTACT_CASES)
+    cases.update(_spline_bodies())
+    for name, (writer, elevate, refine, gf, attr, penalty, spec) in cases.items():
         with tempfile.TemporaryDirectory() as tmp:
             mesh = os.path.join(tmp, "m.mesh")
             writer(mesh)
@@ -55,6 +85,16 @@ def contact_main():
             out["body_params"] = np.array(spec[1], np.float64)
             np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
             print(name, out["meta"])
+
+
+def contact_steps_main(nsteps=12):
+    """examples/nl_contact.py's time loop (harness mode steps_contact) on the CPU reference with real splinepy."""
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        meshgen.write_cell_p1(mesh, O.NL_CONTACT["verts"])
+        x, its, ch = O.run_ref_steps_contact(mesh, os.path.join(tmp, "o"), nsteps)
+    np.savez_compressed(os.path.join(OUT, "contact_steps_square.npz"), x=x, its=its, contact_hist=ch)
+    print("contact_steps_square: Newton iterations", its.tolist(), "max |u|", float(np.abs(x).max()))
 
 
 # J2 + hardening laws: results only (tables / connectivity are those of the named base fixture)
@@ -225,7 +265,9 @@ def main(only=None):
 
 
 if __name__ == "__main__":
-    if "contact" in sys.argv[1:]:
+    if "contact_steps" in sys.argv[1:]:
+        contact_steps_main()
+    elif "contact" in sys.argv[1:]:
         contact_main()
     elif "bodyforce" in sys.argv[1:]:
         bodyforce_main()
@@ -246,3 +288,4 @@ if __name__ == "__main__":
         sweeps_main()
         eig_main()
         histories_main()
+        contact_steps_main()

@@ -417,6 +417,108 @@ def bezier_params(dim, cps, n_seed=None):
     return np.concatenate([[b.deg_u, b.deg_v, b.n_seed], b._keep.ravel()])
 
 
+# ---- splinepy scenes of the reference harness (body "spline", oracle/ref_harness.cpp struct SplineDesc) -----------------
+def spline_desc(resolution, cps, weights=None, knots=None, degrees=None):
+    """Flat description the harness parses: resolution (kd-tree sampling per direction, nl_contact.py plant_kd_tree),
+    rational, has_knots, deg_u, deg_v, ncp_u, ncp_v, [knots], control points [ncp_v][ncp_u][dim (+ weight)].
+    cps: curve [ncp_u, 2] or surface [ncp_v, ncp_u, 3]."""
+    cps = np.asarray(cps, np.float64)
+    dim = cps.shape[-1]
+    ncp = (cps.shape[0], 1) if dim == 2 else (cps.shape[1], cps.shape[0])
+    if degrees is None:
+        degrees = (ncp[0] - 1, ncp[1] - 1 if dim == 3 else 0)
+    out = [resolution, int(weights is not None), int(knots is not None), degrees[0], degrees[1], ncp[0], ncp[1]]
+    if knots is not None:
+        for k in knots:
+            out += [float(x) for x in k]
+    pts = cps.reshape(-1, dim)
+    w = None if weights is None else np.asarray(weights, np.float64).ravel()
+    for i in range(pts.shape[0]):
+        out += [float(x) for x in pts[i]]
+        if w is not None:
+            out.append(float(w[i]))
+    return np.array(out, np.float64)
+
+
+def parse_spline_desc(dim, desc):
+    d = [float(x) for x in desc]
+    res, rational, has_knots, du, dv, nu, nv = (int(x) for x in d[:7])
+    k = 7
+    knots = []
+    if has_knots:
+        for deg, n in ((du, nu), (dv, nv))[:dim - 1]:
+            knots.append(np.array(d[k:k + n + deg + 1]))
+            k += n + deg + 1
+    n = nu * (nv if dim == 3 else 1)
+    stride = dim + (1 if rational else 0)
+    pts = np.array(d[k:k + n * stride]).reshape(n, stride)
+    cps = pts[:, :dim].reshape((nu, dim) if dim == 2 else (nv, nu, dim))
+    w = pts[:, dim].reshape(cps.shape[:-1]) if rational else None
+    return dict(resolution=res, rational=bool(rational), knots=knots if has_knots else None, deg=(du, dv), ncp=(nu, nv), cps=cps,
+                weights=w)
+
+
+SEED_CAP = {2: 256, 3: 32}   # adapter/b200_mortar_contact.hpp B200NearestDistanceToSplines: max_seed_curve_ / _surface_
+
+
+def _n_seed(dim, S):
+    return max(1, min(S["resolution"] - 1, SEED_CAP[dim]))
+
+
+def rigid_from_desc(dim, desc):
+    """Oracle Rigid for a harness spline scene (Bezier extraction for splines with knots), seed sampling as the adapter
+    derives it from the kd-tree resolution."""
+    S = parse_spline_desc(dim, desc)
+    ns = _n_seed(dim, S)
+    cps = homogeneous(S["cps"], S["weights"]) if S["rational"] else S["cps"]
+    if S["knots"] is None:
+        patches = cps[None]
+    elif dim == 2:
+        patches = bspline_to_bezier(S["deg"][0], S["knots"][0], cps)
+    else:
+        patches = bspline_surface_to_bezier(S["deg"][0], S["deg"][1], S["knots"][0], S["knots"][1], cps)
+    return rigid_rational_patches(dim, patches, ns) if S["rational"] else rigid_bezier_patches(dim, patches, ns)
+
+
+def mb2_body_from_desc(dim, desc):
+    """(kind, params) of mb2_contact_set_rigid_body for a harness spline scene: what B200NearestDistanceToSplines builds."""
+    S = parse_spline_desc(dim, desc)
+    ns = _n_seed(dim, S)
+    pu, pv = S["deg"]
+    if S["knots"] is None:
+        if S["rational"]:
+            return 4, rational_bezier_params(dim, S["cps"][None], S["weights"][None], ns)
+        return 2, bezier_patches_params(dim, S["cps"][None], ns)
+    ku = S["knots"][0]
+    kv = S["knots"][1] if dim == 3 else []
+    if S["rational"]:
+        return 5, nurbs_params(dim, pu, pv, ku, kv, S["cps"], S["weights"], ns)
+    return 3, bspline_params(dim, pu, pv, ku, kv, S["cps"], ns)
+
+
+def run_ref_proximity(points, desc, nthreads=1):
+    """NearestDistanceToSplines::NearestDistance (the reference's class on real splinepy, harness mode "proximity") on
+    points [n, dim] -> dict of parametric, physical, pmq, distance, convergence, first_derivatives, normal, normal_gap."""
+    import tempfile
+    pts = np.ascontiguousarray(points, np.float64)
+    n, dim = pts.shape
+    pd = dim - 1
+    with tempfile.TemporaryDirectory() as tmp:
+        pts.tofile(os.path.join(tmp, "p.f64"))
+        cmd = [REF_BIN, "proximity", os.path.join(tmp, "p.f64"), str(dim), str(n), "-", str(nthreads), tmp] + [repr(float(x)) for x in desc]
+        subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+        rec = pd + 2 * dim + 2 + pd * dim + dim + 1
+        R = np.fromfile(os.path.join(tmp, "prox.f64")).reshape(n, rec)
+    o = 0
+    out = {}
+    for name, w in (("parametric", pd), ("physical", dim), ("pmq", dim), ("distance", 1), ("convergence", 1),
+                    ("first_derivatives", pd * dim), ("normal", dim), ("normal_gap", 1)):
+        out[name] = R[:, o:o + w] if w > 1 else R[:, o]
+        o += w
+    out["first_derivatives"] = R[:, pd + 2 * dim + 2:pd + 2 * dim + 2 + pd * dim].reshape(n, pd, dim)
+    return out
+
+
 def rigid_query(body, q):
     q = np.ascontiguousarray(q, np.float64)
     xi, pmq, fd = np.zeros(2), np.zeros(3), np.zeros(6)
@@ -447,6 +549,8 @@ def rigid_from_spec(dim, spec):
     """spec = ("plane", [o..., t0..., (t1...), lo, hi]) or ("sphere", [c..., R]) -- the harness' command line."""
     kind, v = spec
     v = list(v)
+    if kind == "spline":
+        return rigid_from_desc(dim, v)
     if kind == "plane":
         o, t0 = v[0:dim], v[dim:2 * dim]
         t1 = v[2 * dim:3 * dim] if dim == 3 else None
@@ -536,12 +640,36 @@ def load_contact_dump(d):
 
 def run_ref_contact(mesh, elevate, refine, outdir, bdr_attr, penalty, body, gf=1.0, material="neohookean", u_file="-",
                     nthreads=1, binary=None):
-    """body = ("plane", [...]) / ("sphere", [...])."""
+    """body = ("plane", [...]) / ("sphere", [...]) / ("spline", spline_desc(...))."""
     os.makedirs(outdir, exist_ok=True)
     cmd = [binary or REF_BIN, "contact", mesh, str(elevate), str(refine), material, str(nthreads), repr(gf), u_file, outdir,
            str(bdr_attr), repr(float(penalty)), body[0]] + [repr(float(x)) for x in body[1]]
     subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
     return load_contact_dump(outdir)
+
+
+# The contact time loop of examples/nl_contact.py as the harness restates it (mode "steps_contact"): its configuration
+NL_CONTACT = dict(verts=[(0.0, 0.0), (2.0, 0.0), (1.0, 1.0), (-1.0, 2.0)],       # tests/data/square-nurbs.mesh
+                  elevate=1, refine=3, density=7e4, young=1e10, dt=0.001, penalty=1e11, resolution=10000,
+                  cps=[[-2.45, 2.3], [0.35, 1.7], [0.75, 1.7], [1.55, 2.3]],      # sp.Bezier([3], ...) + [0.05, 1]
+                  shift=(0.0, 0.005), bdr_contact=2, bdr_clamp=1)
+
+
+def run_ref_steps_contact(mesh, outdir, nsteps, cfg=None, nthreads=1, binary=None):
+    """-> x [steps, NV], Newton iterations [steps], contact history [steps, 6] (area, pressure, force xyz, gap norm)."""
+    c = dict(NL_CONTACT)
+    c.update(cfg or {})
+    os.makedirs(outdir, exist_ok=True)
+    desc = spline_desc(c["resolution"], np.array(c["cps"], np.float64))
+    env = {**os.environ, "MIMI_REF_DENSITY": repr(float(c["density"])), "MIMI_REF_YOUNG": repr(float(c["young"]))}
+    cmd = [binary or REF_BIN, "steps_contact", mesh, str(c["elevate"]), str(c["refine"]), "neohookean", str(nthreads),
+           repr(float(c["dt"])), str(nsteps), outdir, str(c["bdr_contact"]), str(c["bdr_clamp"]), repr(float(c["penalty"]))]
+    cmd += [repr(float(v)) for v in c["shift"]] + [repr(float(v)) for v in desc]
+    subprocess.check_call(cmd, stdout=subprocess.DEVNULL, env=env)
+    its = np.fromfile(os.path.join(outdir, "newton_its.i32"), np.int32)
+    x = np.fromfile(os.path.join(outdir, "x_hist.f64")).reshape(nsteps, -1)
+    ch = np.fromfile(os.path.join(outdir, "contact_hist.f64")).reshape(nsteps, 6)
+    return x, its, ch
 
 
 # ---------------------------------------------------------------- Newton-iteration sweeps (SURVEY section 8(f) rank 1)

@@ -9,7 +9,10 @@
 //            <body> <p0> <p1> ...      rigid body = analytic NearestDistanceBase subclass (below):
 //            plane  o[dim] t0[dim] (t1[dim] in 3D) lo hi   closest point on the (clamped) affine patch o + s t0 + t t1
 //            sphere c[dim] R                                  closest point on the circle / sphere
+//            spline <description>  the reference's own NearestDistanceToSplines on a real splinepy Bezier / BSpline / NURBS
+//                                  (the flat description is documented at struct SplineDesc below)
 //   Dumps the marked faces' tables and what MortarContact (mortar_contact.cpp) computes on them.
+//   mimi_ref proximity ... / steps_contact ...: see the mode blocks in main().
 // material: neohookean | stvk | j2linear  (E=2100, nu=0.3, rho=1: tests/test_nonlinear_solid.py:59-62;
 //           j2linear adds isotropic_hardening=80, kinematic_hardening=40, sigma_y=<MIMI_REF_SIGMA_Y or 2.0>)
 // For materials with history the dump continues: DomainPostTimeAdvance(u) -> state.f64 [NE][nq][19]
@@ -25,6 +28,9 @@
 
 #include <mfem.hpp>
 #include <omp.h>
+#include <Python.h>
+
+#include <splinepy/splines/splinepy_base.hpp>
 
 #include "mimi/coefficients/nearest_distance.hpp"
 #include "mimi/integrators/mortar_contact.hpp"
@@ -49,11 +55,17 @@ using DomainIntegrator = mimi::integrators::NonlinearSolid;
 #define MIMI_REF_B200_BODY
 #endif
 
-// The only splinepy *library* symbol the reference's contact integrator pulls in
-// (coefficients/nearest_distance.hpp:259-281, NearestDistanceToSplines). The harness never builds a
-// NearestDistanceToSplines (rigid bodies are analytic NearestDistanceBase subclasses), so it must never run.
+// splinepy::py::PySpline::Core() is the one symbol of splinepy's *Python binding* (src/py/py_spline.cpp, a pybind11
+// module this harness does not build) that the reference's contact scene calls
+// (coefficients/nearest_distance.hpp:225-281, NearestDistanceToSplines). Everything behind it -- the spline classes and
+// the closest-point search splinepy::proximity::Proximity::VerboseQuery (kd-tree seed, Newton -> SLSQP -> LM,
+// third_party/splinepy/src/proximity/proximity.cpp:643-733) -- is the vendored splinepy core, compiled unmodified into
+// oracle/_ref/libsplinepy_ref.a by oracle/Makefile.ref.
 namespace splinepy::py {
-PySpline::CoreSpline_& PySpline::Core() { throw std::runtime_error("splinepy core is not linked into oracle/_ref"); }
+PySpline::CoreSpline_& PySpline::Core() {
+  if (!c_spline_) throw std::runtime_error("PySpline: core spline is not initialised");
+  return c_spline_;
+}
 }  // namespace splinepy::py
 
 namespace {
@@ -153,9 +165,14 @@ Setup build(const char* mesh_file, int elevate, int refine, const std::string& m
     } else { std::fprintf(stderr, "unknown hardening %s\n", h.c_str()); std::exit(2); }
   }
   else { std::fprintf(stderr, "unknown material %s\n", material.c_str()); std::exit(2); }
-  s.mat->density_ = 1.0;
+  // defaults = the reference's test values (tests/test_nonlinear_solid.py:59-62); the examples use others
+  // (examples/nl_contact.py:15-19: density 7e4, E = 1e10): MIMI_REF_DENSITY / MIMI_REF_YOUNG / MIMI_REF_POISSON override
+  const char* env_rho = std::getenv("MIMI_REF_DENSITY");
+  const char* env_E = std::getenv("MIMI_REF_YOUNG");
+  const char* env_nu = std::getenv("MIMI_REF_POISSON");
+  s.mat->density_ = env_rho ? std::atof(env_rho) : 1.0;
   s.mat->viscosity_ = -1.0;
-  s.mat->SetYoungPoisson(2100.0, 0.3);
+  s.mat->SetYoungPoisson(env_E ? std::atof(env_E) : 2100.0, env_nu ? std::atof(env_nu) : 0.3);
 
   auto t0 = std::chrono::steady_clock::now();
   s.pre = std::make_shared<mimi::utils::PrecomputedData>();
@@ -269,6 +286,59 @@ struct RigidSphere : mimi::coefficients::NearestDistanceBase MIMI_REF_B200_BODY 
 #endif
 };
 
+// ---- the reference's own scene: NearestDistanceToSplines holding a real splinepy spline, planted exactly as
+// examples/nl_contact.py:31-33 does (scene.add_spline(curv); scene.plant_kd_tree(resolution, nthreads)).
+// Flat description (all numbers, the harness' command line): resolution, rational, has_knots, deg_u, deg_v, ncp_u, ncp_v,
+// [knots_u (ncp_u + deg_u + 1), knots_v (3D only)] when has_knots, control points [ncp_v][ncp_u][dim (+ weight when rational)]
+// (u fastest: splinepy's and BSplineLib's control-point order). 2D scenes: deg_v = 0, ncp_v = 1.
+#ifdef MIMI_REF_USE_B200
+using SplineScene = mimi::integrators::B200NearestDistanceToSplines;
+#else
+using SplineScene = mimi::coefficients::NearestDistanceToSplines;
+#endif
+struct SplineDesc {
+  int resolution = 0, rational = 0, has_knots = 0, deg[2] = {0, 0}, ncp[2] = {1, 1}, para_dim = 1, dim = 2;
+  std::vector<std::vector<double>> knots;
+  std::vector<double> cps, weights;
+  // parses bp[k...]; returns the index after the description
+  size_t Parse(const std::vector<double>& bp, size_t k, int dim_) {
+    dim = dim_;
+    para_dim = dim - 1;
+    resolution = (int)bp.at(k++);
+    rational = (int)bp.at(k++);
+    has_knots = (int)bp.at(k++);
+    deg[0] = (int)bp.at(k++); deg[1] = (int)bp.at(k++);
+    ncp[0] = (int)bp.at(k++); ncp[1] = (int)bp.at(k++);
+    knots.clear();
+    if (has_knots)
+      for (int d = 0; d < para_dim; ++d) {
+        knots.emplace_back();
+        for (int i = 0; i < ncp[d] + deg[d] + 1; ++i) knots.back().push_back(bp.at(k++));
+      }
+    const int n = ncp[0] * (para_dim > 1 ? ncp[1] : 1);
+    cps.assign((size_t)n * dim, 0.0);
+    weights.assign(rational ? n : 0, 1.0);
+    for (int i = 0; i < n; ++i) {
+      for (int c = 0; c < dim; ++c) cps[(size_t)i * dim + c] = bp.at(k++);
+      if (rational) weights[i] = bp.at(k++);
+    }
+    return k;
+  }
+  std::shared_ptr<splinepy::splines::SplinepyBase> Core() {
+    // what PySpline::NewCore does with the kwargs of sp.Bezier / sp.RationalBezier / sp.BSpline / sp.NURBS
+    return splinepy::splines::SplinepyBase::SplinepyCreate(para_dim, dim, deg, has_knots ? &knots : nullptr, cps.data(),
+                                                           rational ? weights.data() : nullptr);
+  }
+};
+std::shared_ptr<SplineScene> make_spline_scene(SplineDesc& d, int nthreads) {
+  if (!Py_IsInitialized()) Py_Initialize();  // PySpline carries a py::dict member
+  auto spline = std::make_shared<splinepy::py::PySpline>(d.Core());
+  auto scene = std::make_shared<SplineScene>();
+  scene->AddSpline(spline);
+  scene->PlantKdTree(d.resolution, nthreads);
+  return scene;
+}
+
 // exposes MortarContact's protected nodal vectors for the dump
 struct ContactProbe : mimi::integrators::MortarContact {
   using mimi::integrators::MortarContact::MortarContact;
@@ -355,6 +425,46 @@ int main(int argc, char** argv) {
     double info[3] = {(double)lin.GetNumIterations(), lin.GetFinalNorm(), lin.GetConverged() ? 1.0 : 0.0};
     dump(out, "x.f64", x.GetData(), (size_t)n);
     dump(out, "info.f64", info, 3);
+    return 0;
+  }
+
+  if (mode == "proximity") {
+    // proximity <points.f64> <dim> <npoints> - <nthreads> <out dir> <spline description ...>: the reference's closest-point
+    // query NearestDistanceToSplines::NearestDistance (coefficients/nearest_distance.hpp:259-281 -> splinepy
+    // VerboseProximity) on the given points, exactly as MortarContact::ElementGapAndArea drives it
+    // (mortar_contact.cpp:157-181): -> prox.f64 [npoints][para_dim + 2 dim + 2 + para_dim*dim + dim + 1]
+    // = parametric, physical, physical - query, distance, convergence, first derivatives, unit normal, normal gap
+    const int dim = elevate, np = refine;
+    const std::string out = argv[7];
+    std::vector<double> bp, pts((size_t)np * dim);
+    for (int i = 8; i < argc; ++i) bp.push_back(std::atof(argv[i]));
+    FILE* f = std::fopen(mesh_file, "rb");
+    if (!f || std::fread(pts.data(), sizeof(double), pts.size(), f) != pts.size()) { std::fprintf(stderr, "proximity: bad input\n"); return 2; }
+    std::fclose(f);
+    SplineDesc d;
+    d.Parse(bp, 0, dim);
+    auto scene = make_spline_scene(d, nthreads);
+    const int pd = dim - 1, rec = pd + 2 * dim + 2 + pd * dim + dim + 1;
+    std::vector<double> res((size_t)np * rec);
+    mimi::coefficients::NearestDistanceBase::Query q;
+    mimi::coefficients::NearestDistanceBase::Results r;
+    q.SetSize(dim);
+    r.SetSize(pd, dim);
+    for (int i = 0; i < np; ++i) {
+      for (int c = 0; c < dim; ++c) q.query[c] = pts[(size_t)i * dim + c];
+      scene->NearestDistance(q, r);
+      r.ComputeNormal<true>();
+      double* o = &res[(size_t)i * rec];
+      for (int k = 0; k < pd; ++k) *o++ = r.parametric_[k];
+      for (int c = 0; c < dim; ++c) *o++ = r.physical_[c];
+      for (int c = 0; c < dim; ++c) *o++ = r.physical_minus_query_[c];
+      *o++ = r.distance_;
+      *o++ = r.convergence_;
+      for (int k = 0; k < pd * dim; ++k) *o++ = r.first_derivatives_[k];
+      for (int c = 0; c < dim; ++c) *o++ = r.normal_[c];
+      *o++ = r.NormalGap();
+    }
+    dump(out, "prox.f64", res.data(), res.size());
     return 0;
   }
 
@@ -567,6 +677,10 @@ int main(int argc, char** argv) {
       for (int d = 0; d < dim; ++d) b->c[d] = bp.at(k++);
       b->R = bp.at(k++);
       nd = b;
+    } else if (body == "spline") {
+      SplineDesc& d = *new SplineDesc();  // outlives the scene: splinepy's BSpline / NURBS only VIEW the control points
+      d.Parse(bp, 0, dim);
+      nd = make_spline_scene(d, nthreads);
     } else { std::fprintf(stderr, "unknown rigid body %s\n", body.c_str()); return 2; }
     nd->coefficient_ = penalty;
     nd->dim_ = dim;
@@ -745,6 +859,128 @@ int main(int argc, char** argv) {
     }
     dump(out, "x_hist.f64", hist.data(), hist.size());
     dump(out, "newton_its.i32", its.data(), its.size());
+    return 0;
+  }
+
+  if (mode == "steps_contact") {
+    // steps_contact <mesh> <elevate> <refine> <material> <nthreads> <dt> <n steps> <out dir> <bdr attr of the contact
+    //   boundary> <bdr attr of the clamped boundary> <penalty> <dx per step> <dy per step> [<dz per step>] <spline description ...>
+    // The contact time loop of examples/nl_contact.py: PyNonlinearSolid::Setup (py_nonlinear_solid.cpp:155-386) restated on
+    // the reference's own classes -- forms::Nonlinear for the stiffness and for "contact" with MortarContact registered as in
+    // py_nonlinear_solid.cpp:286-326, operators::NonlinearSolid, LineSearchNewton (nl_contact.py: 1e-10, 1e-8, 100
+    // iterations), GeneralizedAlpha2(0.25) -- with the rigid spline moved before every step and its kd-tree re-planted
+    // (nl_contact.py:58-64). UMFPACK is absent from this image: a dense LU solves the linear systems.
+    // -> x_hist.f64 [steps][NV], newton_its.i32 [steps], contact_hist.f64 [steps][6] = area, pressure, force x/y/z, gap norm
+    double dt = std::atof(argv[7]);
+    const int nsteps = std::atoi(argv[8]);
+    const std::string out = argv[9];
+    const int bdr_contact = std::atoi(argv[10]), bdr_clamp = std::atoi(argv[11]);
+    const double penalty = std::atof(argv[12]);
+    Setup s = build(mesh_file, elevate, refine, material, nthreads, false);
+    auto& fes = *s.fes;
+    auto& pre = *s.pre;
+    const int dim = pre.dim_, NV = pre.n_v_dofs_;
+    double shift[3] = {0, 0, 0};
+    int k0 = 13;
+    for (int c = 0; c < dim; ++c) shift[c] = std::atof(argv[k0++]);
+    std::vector<double> bp;
+    for (int i = k0; i < argc; ++i) bp.push_back(std::atof(argv[i]));
+    SplineDesc d;
+    d.Parse(bp, 0, dim);
+    auto scene = make_spline_scene(d, nthreads);
+    scene->coefficient_ = penalty;
+    scene->dim_ = dim;
+    scene->para_dim_ = dim - 1;
+
+    mfem::Array<int> zero_dofs;
+    for (int c = 0; c < dim; ++c) {
+      mfem::Array<int> marker(s.mesh->bdr_attributes.Max()), list;
+      marker = 0;
+      marker[bdr_clamp - 1] = 1;   // bc.initial.dirichlet(bid, c): boundary ids are 0-based there, attributes 1-based
+      fes.GetEssentialTrueDofs(marker, list, c);
+      zero_dofs.Append(list);
+    }
+    zero_dofs.Sort();
+    zero_dofs.Unique();
+    auto nl_oper = std::make_unique<mimi::operators::NonlinearSolid>(fes);
+    mfem::SparseMatrix tmp;
+    auto mass = std::make_shared<mfem::BilinearForm>(&fes);
+    nl_oper->AddBilinearForm("mass", mass);
+    mfem::ConstantCoefficient rho(s.mat->density_);
+    mass->AddDomainIntegrator(new mfem::VectorMassIntegrator(rho));
+    mass->Assemble(0);
+    mass->FormSystemMatrix(zero_dofs, tmp);
+    auto stiffness = std::make_shared<mimi::forms::Nonlinear>(&fes);
+    nl_oper->AddNonlinearForm("nonlinear_stiffness", stiffness);
+    stiffness->AddDomainIntegrator(s.integ);
+    stiffness->SetEssentialTrueDofs(zero_dofs);
+    // contact form (py_nonlinear_solid.cpp:286-326)
+    mfem::Array<int> cmarker(s.mesh->bdr_attributes.Max());
+    cmarker = 0;
+    cmarker[bdr_contact - 1] = 1;
+    auto contact_form = std::make_shared<mimi::forms::Nonlinear>(&fes);
+    nl_oper->AddNonlinearForm("contact", contact_form);
+#ifdef MIMI_REF_USE_B200
+    auto cinteg = std::make_shared<ContactIntegrator>(scene, "contact" + std::to_string(bdr_contact), s.pre, s.integ->Context());
+#else
+    auto cinteg = std::make_shared<ContactIntegrator>(scene, "contact" + std::to_string(bdr_contact), s.pre);
+#endif
+    cinteg->runtime_communication_ = std::make_shared<mimi::utils::RuntimeCommunication>();
+    cinteg->SetBoundaryMarker(&cmarker);
+    auto& marked = cinteg->MarkedBoundaryElements();
+    pre.CreateBoundaryElementQuadData(cinteg->Name(), marked.data(), (int)marked.size());
+    pre.PrecomputeElementQuadData(cinteg->Name(), -1, false);
+    cinteg->Prepare();
+    contact_form->AddBdrFaceIntegrator(cinteg, &cmarker);
+
+    struct DenseLU : mfem::Solver {
+      std::unique_ptr<mfem::DenseMatrix> d;
+      std::unique_ptr<mfem::DenseMatrixInverse> inv;
+      void SetOperator(const mfem::Operator& op) override {
+        d.reset(dynamic_cast<const mfem::SparseMatrix&>(op).ToDenseMatrix());
+        inv = std::make_unique<mfem::DenseMatrixInverse>(*d);
+        height = width = d->Height();
+      }
+      void Mult(const mfem::Vector& b, mfem::Vector& x) const override { inv->Mult(b, x); }
+    } lin;
+    auto newton = std::make_shared<mimi::solvers::LineSearchNewton>();
+    newton->nl_oper_ = nl_oper.get();
+    newton->iterative_mode = false;
+    newton->SetOperator(*nl_oper);
+    newton->SetSolver(lin);
+    newton->SetPrintLevel(-1);
+    newton->SetRelTol(1e-10);   // nl.configure_newton("nonlinear_solid", 1e-10, 1e-8, 100, False)
+    newton->SetAbsTol(1e-8);
+    newton->SetMaxIter(100);
+    nl_oper->SetNewtonSolver(newton);
+    mimi::solvers::GeneralizedAlpha2 ode(*nl_oper, 0.25);
+    nl_oper->Setup();
+    ode.SetupDirichletDofs(nl_oper->dirichlet_dofs_);
+    mfem::Vector x(NV), v(NV);
+    x = 0.0;
+    v = 0.0;
+    double t = 0.0;
+    std::vector<double> hist, chist;
+    std::vector<int> its;
+    for (int i = 0; i < nsteps; ++i) {
+      // move(): curv.cps[:] -= shift; scene.plant_kd_tree(resolution, nthreads)   (nl_contact.py:58-64)
+      const int n = (int)d.cps.size() / dim;
+      for (int a = 0; a < n; ++a)
+        for (int c = 0; c < dim; ++c) d.cps[(size_t)a * dim + c] -= shift[c];
+      scene->Clear();
+      auto spline = std::make_shared<splinepy::py::PySpline>(d.Core());
+      scene->AddSpline(spline);
+      scene->PlantKdTree(d.resolution, nthreads);
+      ode.StepTime2(x, v, t, dt);
+      hist.insert(hist.end(), x.GetData(), x.GetData() + NV);
+      its.push_back(newton->GetNumIterations());
+      const double gn = cinteg->GapNorm(x, nthreads);
+      chist.insert(chist.end(), {cinteg->last_area_, cinteg->last_pressure_, cinteg->last_force_[0], cinteg->last_force_[1],
+                                 dim > 2 ? cinteg->last_force_[2] : 0.0, gn});
+    }
+    dump(out, "x_hist.f64", hist.data(), hist.size());
+    dump(out, "newton_its.i32", its.data(), its.size());
+    dump(out, "contact_hist.f64", chist.data(), chist.size());
     return 0;
   }
 

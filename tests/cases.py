@@ -25,6 +25,11 @@ CONTACT_CASES = ["contact_cube_p2_n2_plane", "contact_cube_p2_n4_sphere", "conta
                  "contact_quad_p2_n4_plane_clamped"]
 
 
+# rigid bodies = the reference's NearestDistanceToSplines on REAL splinepy splines (closest point by splinepy's own search)
+SPLINE_CONTACT_CASES = ["contact_quad_p2_n4_bezier", "contact_cube_p2_n4_bezier", "contact_quad_p3_n4_rational_arc",
+                        "contact_quad_p2_n4_bspline"]
+
+
 def load_contact_golden(name):
     z = np.load(os.path.join(GOLDEN, name + ".npz"))
     D = {k: z[k] for k in z.files}

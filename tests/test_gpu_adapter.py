@@ -142,3 +142,55 @@ def test_reference_contact_chain_through_the_adapter(name):
         assert np.array_equal(D[k], G[k]), k
     assert np.any(G["c_pressure"] != 0)
     assert np.allclose(D["c_scalars"], G["c_scalars"], rtol=1e-12, atol=0)      # whole-boundary sums: DESIGN.md section 2
+
+
+from tests.cases import SPLINE_CONTACT_CASES  # noqa: E402
+
+
+@pytest.mark.parametrize("name", SPLINE_CONTACT_CASES)
+def test_reference_splinepy_scene_through_the_adapter(name):
+    """The reference's OWN contact scene -- NearestDistanceToSplines holding a real splinepy spline, add_spline +
+    plant_kd_tree as examples/nl_contact.py:31-33 -- handed to B200MortarContact: the adapter's
+    B200NearestDistanceToSplines reads degrees / knots / control points / weights from the splinepy core and describes
+    them to the device (MB2_RIGID_BEZIER / RATIONAL_BEZIER / BSPLINE). Golden = the unmodified MortarContact with
+    splinepy's own closest-point search; tolerances as in tests/test_gpu_contact.py (projection: 1e-12; FD tangent 1e-4)."""
+    if not O.have_ref_b200():
+        pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
+    from oracle.make_golden import _spline_bodies
+    writer, elevate, refine, gf, attr, penalty, spec = _spline_bodies()[name]
+    G = load_contact_golden(name)
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        writer(mesh)
+        D = O.run_ref_contact(mesh, elevate, refine, os.path.join(tmp, "c"), attr, penalty, spec, gf=gf, binary=O.REF_B200_BIN)
+    assert np.array_equal(D["c_marked_v_dofs"], G["c_marked_v_dofs"]) and np.array_equal(D["c_area"], G["c_area"])
+    assert np.array_equal(D["c_pressure"] != 0, G["c_pressure"] != 0) and np.any(G["c_pressure"] != 0)
+    for k in ("c_gap", "c_pressure", "c_r2"):
+        assert _rel(D[k], G[k]) <= 1e-12, k
+    assert _rel(D["c_r"] - D["c_r0"], G["c_r"] - G["c_r0"]) <= 1e-12
+    assert _rel(D["c_A"] - D["mass"], G["c_A"] - G["mass"]) <= 1e-4
+    assert np.allclose(D["c_scalars"], G["c_scalars"], rtol=1e-11, atol=0)
+
+
+def test_nl_contact_time_loop_through_the_adapter():
+    """Config 2 of BASELINE.json: examples/nl_contact.py's time loop (square-nurbs mesh, elevate 1, subdivide 3,
+    NeoHookean E = 1e10 / rho = 7e4, cubic Bezier rigid curve moved 0.005 down per step with its kd-tree re-planted,
+    penalty 1e11, dt = 1e-3, Newton 1e-10 / 1e-8 / 100) on the reference's own classes with B200NonlinearSolid and
+    B200MortarContact registered instead of NonlinearSolid and MortarContact. Golden = the same harness mode on the CPU
+    reference with real splinepy (tests/golden/contact_steps_square.npz). Per-step Newton iteration counts must be
+    identical; the trajectory within 1e-9 relative (the projections agree to 1e-15, the Newton iterates inherit it)."""
+    if not O.have_ref_b200():
+        pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "contact_steps_square.npz"))
+    n = z["x"].shape[0]
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        meshgen.write_cell_p1(mesh, O.NL_CONTACT["verts"])
+        x, its, ch = O.run_ref_steps_contact(mesh, os.path.join(tmp, "o"), n, binary=O.REF_B200_BIN)
+    diff = [int(i) for i in np.nonzero(its != z["its"])[0]]
+    print("\n[nl_contact] adapter Newton iterations %s\n             CPU reference      %s\n             steps that differ: %s; max |x - x_ref| / max |x_ref| = %.2e" % (
+        its.tolist(), z["its"].tolist(), diff, _rel(x, z["x"])))
+    assert (z["contact_hist"][:, 1] != 0).sum() >= 8               # the body is in contact for most of the steps
+    assert its.tolist() == z["its"].tolist()
+    assert _rel(x, z["x"]) <= 1e-9
+    assert np.allclose(ch[:, :5], z["contact_hist"][:, :5], rtol=1e-7, atol=1e-9 * np.abs(z["contact_hist"][:, :5]).max())

@@ -8,7 +8,7 @@ import pytest
 
 from mimi_b200 import capi
 from oracle import oracle_py as O
-from tests.cases import CONTACT_CASES, load_contact_golden
+from tests.cases import CONTACT_CASES, SPLINE_CONTACT_CASES, load_contact_golden
 
 pytestmark = pytest.mark.gpu
 
@@ -57,6 +57,47 @@ def test_contact_golden(ctx_factory, name):
     assert np.abs(A - D["mass"]).max() > 0
     # A14 GapNorm
     assert close(ctx.contact_gap_norm(D["u"]), D["c_scalars"][5])
+
+
+@pytest.mark.parametrize("name", SPLINE_CONTACT_CASES)
+def test_spline_contact_against_the_reference_on_real_splinepy(ctx_factory, name):
+    """A12 pinned on the device: golden vectors = the unmodified MortarContact driven by the reference's own
+    NearestDistanceToSplines on real splinepy splines (Bezier curve of examples/nl_contact.py, Bezier surface, rational
+    arc, B-spline with interior knots). The device's closest-point search converges to the same points: nodal gap /
+    pressure / residual within 1e-12 relative, FD tangent within 1e-4 of its largest entry (it divides the pressures'
+    1e-13 by h; fed the reference's pressures the oracle's tangent is bit-exact, tests/test_oracle_contact.py), and the
+    device equals the C oracle of the same search bit for bit."""
+    D = load_contact_golden(name)
+    dim = D["dim"]
+    kind, params = O.mb2_body_from_desc(dim, D["body"][1])
+    ctx = ctx_factory()
+    ctx.set_connectivity(dim, D["nd"], D["nq"], D["NV"], D["v_dofs"])
+    ctx.set_nodes(D["x_ref"])
+    ctx.build_pattern()
+    ctx.contact_set_faces(D["c_v_dofs"], D["c_N"], D["c_dN_dxi"], D["c_w"])
+    ctx.contact_set_rigid_body(kind, params, D["penalty"])
+    assert np.array_equal(ctx.contact_A_ids(), D["c_A_ids"])
+    r = D["c_r0"].copy()
+    ctx.add_boundary_residual(D["u"], r)
+    gap, area, pr = ctx.contact_nodal()
+    assert np.array_equal(area, D["c_area"]) and np.array_equal(pr != 0, D["c_pressure"] != 0) and (pr != 0).sum() >= 4
+    assert close(gap, D["c_gap"]) and close(pr, D["c_pressure"])
+    assert close(r - D["c_r0"], D["c_r"] - D["c_r0"])
+    r2 = np.zeros(D["NV"])
+    A = D["mass"].copy()
+    ctx.add_boundary_residual_and_grad(D["u"], D["gf"], r2, A)
+    assert close(r2, D["c_r2"])
+    assert close(A - D["mass"], D["c_A"] - D["mass"], 1e-4)
+    assert close(ctx.contact_gap_norm(D["u"]), D["c_scalars"][5])
+    # device == oracle of the same search, bit for bit
+    body = O.rigid_from_desc(dim, D["body"][1])
+    local, nm, _ = O.contact_prepare(dim, D["c_v_dofs"])
+    g_o, a_o, p_o, _ = O.contact_pressure(dim, D["c_v_dofs"], local, nm, D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"],
+                                          D["u"], body, D["penalty"])
+    r_o, A_o = np.zeros(D["NV"]), D["mass"].copy()
+    O.contact_assemble(dim, D["c_v_dofs"], local, D["c_A_ids"], D["c_N"], D["c_dN_dxi"], D["c_w"], D["c_x_ref"], D["u"], p_o,
+                       True, D["gf"], r_o, A_o)
+    assert np.array_equal(gap, g_o) and np.array_equal(pr, p_o) and np.array_equal(r2, r_o) and np.array_equal(A, A_o)
 
 
 def test_contact_moving_body_vs_oracle(ctx_factory):
