@@ -88,13 +88,27 @@ def contact_main():
 
 
 def contact_steps_main(nsteps=12):
-    """examples/nl_contact.py's time loop (harness mode steps_contact) on the CPU reference with real splinepy."""
+    """examples/nl_contact.py's time loop (harness mode steps_contact) on the CPU reference with real splinepy, plus the
+    reference's OWN spread: the same loop at nthreads = 2, 3, 4 (the thread-ordered reduction changes the last bits,
+    nonlinear_base.hpp:111-151) and with kd-tree resolutions 5000 / 20000 (another seed for the same closest point)."""
     with tempfile.TemporaryDirectory() as tmp:
         mesh = os.path.join(tmp, "m.mesh")
         meshgen.write_cell_p1(mesh, O.NL_CONTACT["verts"])
         x, its, ch = O.run_ref_steps_contact(mesh, os.path.join(tmp, "o"), nsteps)
-    np.savez_compressed(os.path.join(OUT, "contact_steps_square.npz"), x=x, its=its, contact_hist=ch)
+        variants, labels, spread = [its], ["nthreads=1"], [0.0]
+        for nt in (2, 3, 4):
+            xv, iv, _ = O.run_ref_steps_contact(mesh, os.path.join(tmp, "t%d" % nt), nsteps, nthreads=nt)
+            variants.append(iv); labels.append("nthreads=%d" % nt)
+            spread.append(float(np.abs(xv - x).max() / np.abs(x).max()))
+        for res in (5000, 20000):
+            xv, iv, _ = O.run_ref_steps_contact(mesh, os.path.join(tmp, "r%d" % res), nsteps, cfg=dict(resolution=res))
+            variants.append(iv); labels.append("resolution=%d" % res)
+            spread.append(float(np.abs(xv - x).max() / np.abs(x).max()))
+    np.savez_compressed(os.path.join(OUT, "contact_steps_square.npz"), x=x, its=its, contact_hist=ch,
+                        its_variants=np.array(variants), variant_labels=np.array(labels), x_rel_spread=np.array(spread))
     print("contact_steps_square: Newton iterations", its.tolist(), "max |u|", float(np.abs(x).max()))
+    for lab, iv, sp in zip(labels, variants, spread):
+        print("   %-18s %s  rel dx %.2e" % (lab, iv.tolist(), sp))
 
 
 # J2 + hardening laws: results only (tables / connectivity are those of the named base fixture)
