@@ -198,6 +198,12 @@ def source_md5(kernel_key=""):
     """md5 of the kernel's source text: a committed ncu capture only speaks for a binary built from the same kernel
     source. p=2: the text of element_fd_kernel (Elem2Cfg .. the next section) + mb2_math.cuh; p=3: element_fd_split_kernel."""
     import hashlib
+    if "fast" in kernel_key:
+        h = hashlib.md5()
+        for f in ("mb2_fast.cu", "mb2_math.cuh"):
+            with open(os.path.join(ROOT, "mimi_b200", "csrc", f), "rb") as fh:
+                h.update(fh.read())
+        return h.hexdigest()
     src = open(os.path.join(ROOT, "mimi_b200", "csrc", "mb2_assembly.cu")).read()
     a, b = ("struct Elem3Cfg", "// History commit:") if "split" in kernel_key else ("struct Elem2Cfg", "// FD-tangent element kernel, column-split")
     i = src.find(a)
@@ -339,6 +345,10 @@ def gpu_arm(args):
     stream = torch.cuda.Stream()            # the library launches on this stream, so torch events see its work
     ctx = capi.Context(local, stream=stream.cuda_stream)
     ctx.set_option("elem_variant", args.variant)
+    fast = args.tangent == "analytic"
+    if fast:
+        ctx.set_option("tangent_mode", 1)          # MB2_TANGENT_ANALYTIC (secondary line: the headline stays the parity mode)
+        ctx.set_option("fast_gemm", args.fast_gemm)
     uid = [None]
     if world > 1:
         uid = [capi.mg_unique_id() if rank == 0 else None]
@@ -354,6 +364,7 @@ def gpu_arm(args):
     # instruction mix a bit-exact (non-FMA) kernel is allowed to issue.
     peak_nofma = ctx.measure_fp64_peak(0)
     peak_fma = ctx.measure_fp64_peak(1)
+    ctx_peaks = {"dmma": ctx.measure_fp64_peak(2)}
 
     # ---- device-resident steps (weak scaling: n^3 elements per GPU) ----
     T = timed_steps(ctx, stream, args.steps, args.warmup, barrier, world, dist, ClockSampler(local))
@@ -476,6 +487,21 @@ def gpu_arm(args):
         tdof = 3 * M["nd"]
         bytes_el = NE * (8.0 * nq * (tdof + 1) + 4 * tdof + 8 * tdof + 8 * tdof * tdof + 8 * tdof)
         kern = ("element_fd_kernel<3,27,64,%s>" if p == 2 else "element_fd_split_kernel<3,64,125,%s,4>") % args.material
+        peak_src = ("mb2_measure_fp64_peak(fma=0) on this GPU in this run: DMUL+DADD pairs = the only "
+                    "mix a bit-exact non-FMA kernel may issue; peak_fma = the same with DFMA (MEASURED_PEAKS.json has no FP64 entry)")
+        if fast:
+            # closed-form tangent: flops the kernel executes per element = the 162 x 192 x 27 contraction (6 component pairs,
+            # K^{mj} mirrored) + T (162 x 192 x 3) + per point F (27 x 9 FMA), stress + dP/dF (~ 600) + residual (81 x 192 FMA)
+            kern = "element_fast_p2_kernel<%s,%s>" % (args.material, "dmma" if args.fast_gemm == 0 else "dfma")
+            per_el = 2.0 * 162 * 192 * 27 + 2.0 * 162 * 192 * 3 + nq * (2.0 * 27 * 9 + 600.0) + 2.0 * 81 * 192
+            exe = alg = per_el / nq
+            fd = 0.0
+            exe_qp = exe
+            achieved = qp_rate_kernel * exe_qp / 1e12
+            peak_dmma = ctx_peaks["dmma"]
+            peak_nofma = peak_dmma if args.fast_gemm == 0 else peak_fma
+            peak_src = ("fast mode (FMA allowed): mb2_measure_fp64_peak(%s) on this GPU in this run; DFMA %.2f, tensor-core "
+                        "m8n8k4 %.2f TFLOP/s" % ("fma=2: FP64 tensor cores" if args.fast_gemm == 0 else "fma=1: DFMA", peak_fma, peak_dmma))
         traffic, traffic_note = ncu_traffic(kern, min(chunk_elems, NE))
         roofline = {"bound": "fp64", "kernel": kern, "achieved": achieved, "peak": peak_nofma,
                     "unit": "TFLOP/s", "frac": achieved / peak_nofma,
@@ -483,8 +509,7 @@ def gpu_arm(args):
                     "frac_algorithmic": qp_rate_kernel * (alg + fd / nq) / 1e12 / peak_nofma,
                     "traffic": traffic, "traffic_note": traffic_note,
                     "algorithmic_bytes_per_launch": bytes_el / NE * min(chunk_elems, NE), "launches_per_step": n_chunks,
-                    "peak_source": "mb2_measure_fp64_peak(fma=0) on this GPU in this run: DMUL+DADD pairs = the only "
-                                   "mix a bit-exact non-FMA kernel may issue; peak_fma = the same with DFMA (MEASURED_PEAKS.json has no FP64 entry)",
+                    "peak_source": peak_src,
                     "flop_per_qp_executed": exe_qp, "flop_per_qp_algorithmic": alg + fd / nq,
                     "achieved_algorithmic": qp_rate_kernel * (alg + fd / nq) / 1e12,
                     "kernel_ms": el_ms, "scatter_ms": float(np.mean(t_sc)),
@@ -509,7 +534,7 @@ def gpu_arm(args):
                 "config": {"workload": "%s: 3D unit-cube B-spline patch p=%d, %d^3 = %d elements x %d qp per GPU, %s, "
                                        "one residual+tangent assembly into CSR (nnz=%d per GPU), MFEM dof numbering" % (
                                            "C3" if (p == 2 and args.material == "neohookean") else "C4-style block", p, n, NE, nq, args.material, nnz),
-                           "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "nnz_per_gpu": nnz, "tangent": "FD parity (bit-exact vs reference)",
+                           "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "nnz_per_gpu": nnz, "tangent": "FD parity (bit-exact vs reference)" if not fast else "MB2_TANGENT_ANALYTIC: closed-form tangent, %s contraction (NOT the headline mode: agrees with the reference's FD Jacobian to its 1e-4 noise, same Newton iteration counts)" % ("FP64 tensor-core (DMMA)" if args.fast_gemm == 0 else "CUDA-core DFMA"),
                            "l2": "inputs larger than L2 (tables %.1f GB, K_e %.1f GB per step)" % (8e-9 * NE * nq * (tdof + 1), 8e-9 * NE * tdof * tdof),
                            "parallelism": "1 GPU" if world == 1 else "z-slabs of %d^3 elements per GPU of one %dx%dx%d patch; raw K_e/R_e of the p interface layers sent to the owner rank by NCCL send/recv inside the step (bit-identical to the 1-thread reference order)" % (n, n, n, n * world),
                            "setup_s": M["setup_s"]},
@@ -708,6 +733,9 @@ def main():
     ap.add_argument("--material", default="neohookean", choices=["neohookean", "stvk"])
     ap.add_argument("--workload", default="c3", choices=["c3", "c5"], help="c5: J2 + contact secondary workload (1 GPU)")
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
+    ap.add_argument("--tangent", default="parity", choices=["parity", "analytic"],
+                    help="analytic = MB2_TANGENT_ANALYTIC fast mode (secondary line; p=2, neohookean / stvk)")
+    ap.add_argument("--fast-gemm", type=int, default=0, help="analytic mode: 0 = FP64 tensor cores (DMMA), 1 = CUDA-core DFMA")
     args = ap.parse_args()
     # The contract is ONE JSON line on stdout: libraries that write to fd 1 (NCCL prints its version banner there)
     # are sent to stderr; the JSON line goes to the original stdout.

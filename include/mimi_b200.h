@@ -59,8 +59,16 @@ enum {
 
 /* tangent modes */
 enum {
-  MB2_TANGENT_FD_PARITY = 0 /* forward finite difference in the reference's exact operation order
-                               (src/mimi/integrators/nonlinear_solid.cpp:48-76), no FMA */
+  MB2_TANGENT_FD_PARITY = 0, /* forward finite difference in the reference's exact operation order
+                                (src/mimi/integrators/nonlinear_solid.cpp:48-76), no FMA: bit-identical to the reference */
+  MB2_TANGENT_ANALYTIC = 1   /* "fast mode" (mb2_set_option(ctx, "tangent_mode", MB2_TANGENT_ANALYTIC)): the closed-form
+                                tangent the reference's difference quotient approximates, K_e = sum_q B^T (w detJ dP/dF) B,
+                                FMA allowed; CompressibleOgdenNeoHookean and StVenantKirchhoff only (MB2_ERR_UNSUPPORTED
+                                otherwise). Not bit-comparable: agrees with the reference's K to its finite-difference
+                                noise (1e-6 .. 1e-4 relative) and keeps its Newton iteration counts (tests/test_gpu_fast.py).
+                                The residual is the same quadrature with contracted FMAs (1e-15 relative).
+                                p = 2 hexahedra run the contraction on the FP64 tensor cores ("fast_gemm" 0, default) or
+                                on the CUDA cores ("fast_gemm" 1). */
 };
 
 /* ---- lifetime ------------------------------------------------------------------------------- */
@@ -354,7 +362,8 @@ int64_t mb2_mg_ke_doubles(mb2_ctx* ctx);
 int mb2_set_option(mb2_ctx* ctx, const char* name, int value);
 
 /* FP64 pipe micro-benchmark used for the roofline denominator: runs `iters` dependent-chain-free
- * DMUL+DADD pairs (fma = 0) or DFMA (fma = 1) per thread on a full grid; returns TFLOP/s. */
+ * DMUL+DADD pairs (fma = 0), DFMA (fma = 1) or FP64 tensor-core mma.sync.m8n8k4 (fma = 2) per thread on a full grid;
+ * returns TFLOP/s. */
 int mb2_measure_fp64_peak(mb2_ctx* ctx, int fma, double* tflops);
 
 #ifdef __cplusplus

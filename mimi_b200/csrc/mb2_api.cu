@@ -482,6 +482,7 @@ int mb2_measure_fp64_peak(mb2_ctx* c, int fma, double* tflops) {
   CHECK_CTX(c);
   REQUIRE(tflops, "null");
   MB2_CUDA(cudaSetDevice(c->device));
+  if (fma == 2) return mb2::launch_dmma_peak(c, tflops);
   return mb2::launch_fp64_peak(c, fma, tflops);
 }
 
@@ -489,6 +490,12 @@ int mb2_set_option(mb2_ctx* c, const char* name, int value) {
   CHECK_CTX(c);
   REQUIRE(name, "null option name");
   if (!std::strcmp(name, "elem_variant")) { c->elem_variant = value; return MB2_OK; }
+  if (!std::strcmp(name, "tangent_mode")) {
+    if (value != MB2_TANGENT_FD_PARITY && value != MB2_TANGENT_ANALYTIC) { c->err = "unknown tangent mode"; return MB2_ERR_ARG; }
+    c->tangent_mode = value;
+    return MB2_OK;
+  }
+  if (!std::strcmp(name, "fast_gemm")) { c->fast_gemm = value; return MB2_OK; }
   if (!std::strcmp(name, "chunk_elems")) { c->chunk_elems = value; mb2::free_plan(c); return MB2_OK; }
   if (!std::strcmp(name, "chunk_mb")) { c->chunk_mb = value > 0 ? value : 2048; mb2::free_plan(c); return MB2_OK; }
   c->err = std::string("unknown option ") + name;

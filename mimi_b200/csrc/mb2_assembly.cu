@@ -15,18 +15,6 @@
 
 namespace mb2 {
 
-struct ElemArgs {
-  int64_t e0, e1;  // element range of this launch; K_e is stored relative to e0
-  const int32_t* __restrict__ vdofs;
-  const double* __restrict__ dNdX;
-  const double* __restrict__ wdetJ;
-  const double* __restrict__ u;
-  double* __restrict__ Re;
-  double* __restrict__ KeT;
-  MatP mp;
-  const double* __restrict__ state;  // [NE][nq][NS] history variables (nullptr for stateless materials)
-};
-
 template <int DIM, int ND, int NQ>
 struct ElemCfg {
   static constexpr int TD = DIM * ND;
@@ -1011,6 +999,7 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
     if (GRAD != (form_mode(c) != 1)) { c->err = "bilinear forms use the Jacobian pipeline, linear forms the residual one"; return MB2_ERR_ARG; }
     return GRAD ? launch_mass_element(c, a.e0, a.e1, a.KeT, a.Re, st) : launch_lform_element(c, a.e0, a.e1, a.Re, st);
   }
+  if (GRAD && c->tangent_mode == MB2_TANGENT_ANALYTIC) return launch_element_analytic(c, a, st);  // mb2_fast.cu
   if (GRAD && dim == 3 && nd == 27 && nq == 64 && c->elem_variant != 1) {
     switch (c->mat_kind) {
       case MAT_NEOHOOKEAN: return launch_element_fd<3, 27, 64, MAT_NEOHOOKEAN>(c, a, st);

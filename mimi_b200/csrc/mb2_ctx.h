@@ -46,6 +46,8 @@ struct mb2_ctx {
   void* plan = nullptr;     // chunk pipeline state (mb2_assembly.cu)
   bool last_grad = false;
   int elem_variant = 0;  // 0 = default kernels, 1 = force the one-thread-per-dof FD kernel (A/B tests)
+  int tangent_mode = 0;  // MB2_TANGENT_FD_PARITY | MB2_TANGENT_ANALYTIC (mb2_fast.cu)
+  int fast_gemm = 0;     // analytic mode, p = 2 hexahedra: 0 = FP64 tensor cores (DMMA), 1 = CUDA-core DFMA tiles
   int mat_kind = -1;
   mb2::MatP mp;
   int ns = 0;                // history doubles per quadrature point (0 = stateless material)
@@ -99,6 +101,21 @@ struct mb2_ctx {
 };
 
 namespace mb2 {
+// arguments of every element kernel (mb2_assembly.cu, mb2_fast.cu)
+struct ElemArgs {
+  int64_t e0, e1;  // element range of this launch; K_e is stored relative to e0
+  const int32_t* __restrict__ vdofs;
+  const double* __restrict__ dNdX;
+  const double* __restrict__ wdetJ;
+  const double* __restrict__ u;
+  double* __restrict__ Re;
+  double* __restrict__ KeT;
+  MatP mp;
+  const double* __restrict__ state;  // [NE][nq][NS] history variables (nullptr for stateless materials)
+};
+// mb2_fast.cu: MB2_TANGENT_ANALYTIC element kernels (closed-form tangent, FMA allowed), FP64 tensor-core peak
+int launch_element_analytic(mb2_ctx* c, const ElemArgs& a, cudaStream_t st);
+int launch_dmma_peak(mb2_ctx* c, double* tflops);
 // mb2_pattern.cu
 int build_pattern(mb2_ctx* c);
 int expand_A_ids(mb2_ctx* c, int32_t* d_out);
