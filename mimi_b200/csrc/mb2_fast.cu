@@ -273,38 +273,129 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
     }
     for (int row = t; row < NQ * DIM; row += 256) sdN[row * NDP + ND] = 0.0;
     if (t < 4) sdN[NQ * DIM * NDP + t] = 0.0;
-    for (int idx = t; idx < 2 * Cfg::TBUF; idx += 256) sT[idx] = 0.0;   // rows 162..171 stay zero
   }
   __syncthreads();
-  // ---- per quadrature point: F, P and the material tangent; C kept for the 6 pairs j <= m as [jm][k][n]
+  // ---- per quadrature point, in three stages that keep all 256 threads busy (the stress + tangent of one point is
+  // ~1 kflop: one thread per point left 6 of 8 warps waiting at a barrier, ncu profiles/r02_fast_dmma_v1_summary.txt):
+  //  (1) F entries, one per thread:  F(a, b) = delta_ab + sum_k u_a[k] dN(q; k, b)
+  //  (2) one thread per point: P and the point's ingredients of dP/dF in the unified form
+  //        (w detJ) dP_jk/dF_mn = alpha X_jk X_mn + beta X_jn X_mk + delta_jm Y_nk + Z_jm delta_kn
+  //      NeoHookean: X = F^-T, alpha = w lambda (2J-1) J, beta = -w g, Y = w mu I, Z = 0;  StVK: X = F, alpha = w lambda,
+  //      beta = w mu, Y = w S, Z = w mu F F^T   (w = w detJ; the stages' scratch aliases the T buffers)
+  //  (3) one thread per (point, component pair j <= m): the 9 entries C^{jm}[k][n]
+  double* sF = sT;                       // [NQ][9]
+  double* sX = sT + NQ * 9;              // [NQ][9]
+  double* sY = sT + 2 * NQ * 9;          // [NQ][9]
+  double* sZ = sT + 3 * NQ * 9;          // [NQ][9]
+  double* sab = sT + 4 * NQ * 9;         // [NQ][2]
+  static_assert(4 * NQ * 9 + 2 * NQ <= 2 * Cfg::TBUF, "stage scratch fits the T buffers");
+  for (int task = t; task < NQ * DD; task += 256) {
+    const int q = task / DD, x = task - q * DD;
+    const int a = x % DIM, b = x / DIM;
+    double d = (a == b) ? 1.0 : 0.0;
+    const double* dN = sdN + (q * DIM + b) * NDP;
+    const double* ua = sue + a * ND;
+#pragma unroll
+    for (int k = 0; k < ND; k++) d += ua[k] * dN[k];
+    sF[task] = d;
+  }
+  __syncthreads();
   if (t < NQ) {
-    double F[DD], P[DD], C[DD * DD];
-#pragma unroll
-    for (int b = 0; b < DIM; b++)
-#pragma unroll
-      for (int a = 0; a < DIM; a++) {
-        double d = (a == b) ? 1.0 : 0.0;
-        const double* dN = sdN + (t * DIM + b) * NDP;
-        const double* ua = sue + a * ND;
-#pragma unroll
-        for (int k = 0; k < ND; k++) d += ua[k] * dN[k];
-        F[a + DIM * b] = d;
-      }
-    pk1_and_tangent<DIM, MAT>(g.mp, F, P, C);
+    const double lambda = g.mp.lambda, mu = g.mp.mu;
     const double aq = g.wdetJ[e * NQ + t];
+    double F[DD], P[DD];
+#pragma unroll
+    for (int x = 0; x < DD; x++) F[x] = sF[t * DD + x];
+    if (MAT == MAT_STVK) {
+      double S[DD], B[DD];
+      double tr = 0.0;
+#pragma unroll
+      for (int a = 0; a < DIM; a++)
+#pragma unroll
+        for (int b = 0; b < DIM; b++) {
+          double cab = 0.0, bab = 0.0;
+#pragma unroll
+          for (int pp = 0; pp < DIM; pp++) {
+            cab += F[pp + DIM * a] * F[pp + DIM * b];
+            bab += F[a + DIM * pp] * F[b + DIM * pp];
+          }
+          const double eab = 0.5 * (cab - (a == b ? 1.0 : 0.0));
+          S[a + DIM * b] = 2.0 * mu * eab;
+          B[a + DIM * b] = bab;
+          if (a == b) tr += eab;
+        }
+#pragma unroll
+      for (int a = 0; a < DIM; a++) S[a + DIM * a] += lambda * tr;
+#pragma unroll
+      for (int j = 0; j < DIM; j++)
+#pragma unroll
+        for (int k = 0; k < DIM; k++) {
+          double pv = 0.0;
+#pragma unroll
+          for (int a = 0; a < DIM; a++) pv += F[j + DIM * a] * S[a + DIM * k];
+          P[j + DIM * k] = pv;
+        }
+#pragma unroll
+      for (int x = 0; x < DD; x++) {
+        sX[t * DD + x] = F[x];
+        sY[t * DD + x] = aq * S[x];
+        sZ[t * DD + x] = aq * mu * B[x];
+      }
+      sab[2 * t] = aq * lambda;
+      sab[2 * t + 1] = aq * mu;
+    } else {
+      double Finv[DD];
+      const double J = det_small<DIM>(F);
+      inverse_small<DIM>(F, Finv);
+      const double gg = -mu + lambda * J * (J - 1.0);
+#pragma unroll
+      for (int j = 0; j < DIM; j++)
+#pragma unroll
+        for (int k = 0; k < DIM; k++) {
+          const double G = Finv[k + DIM * j];
+          P[j + DIM * k] = mu * F[j + DIM * k] + gg * G;
+          sX[t * DD + j + DIM * k] = G;
+          sY[t * DD + j + DIM * k] = (j == k) ? aq * mu : 0.0;
+          sZ[t * DD + j + DIM * k] = 0.0;
+        }
+      sab[2 * t] = aq * lambda * (2.0 * J - 1.0) * J;
+      sab[2 * t + 1] = -aq * gg;
+    }
 #pragma unroll
     for (int x = 0; x < DD; x++) sb[t * DD + x] = aq * P[x];
-#pragma unroll
-    for (int p = 0; p < Cfg::NJM; p++) {
-      const int j = (p < 3) ? 0 : (p < 5 ? 1 : 2);
-      const int m = (p < 3) ? p : (p < 5 ? p - 2 : 2);
-#pragma unroll
-      for (int k = 0; k < DIM; k++)
-#pragma unroll
-        for (int n = 0; n < DIM; n++) sC[(t * Cfg::NJM + p) * 9 + k * 3 + n] = aq * C[(j + DIM * k) + DD * (m + DIM * n)];
-    }
   }
   __syncthreads();
+  for (int task = t; task < NQ * Cfg::NJM; task += 256) {
+    const int q = task / Cfg::NJM, p = task - q * Cfg::NJM;
+    int j, m;
+    jm_of(p, j, m);
+    const double* X = sX + q * DD;
+    const double* Y = sY + q * DD;
+    const double alpha = sab[2 * q], beta = sab[2 * q + 1];
+    const double zjm = sZ[q * DD + j + DIM * m];
+    double xj[DIM], xm[DIM];
+#pragma unroll
+    for (int k = 0; k < DIM; k++) {
+      xj[k] = X[j + DIM * k];
+      xm[k] = X[m + DIM * k];
+    }
+    double* o = sC + task * 9;
+#pragma unroll
+    for (int k = 0; k < DIM; k++)
+#pragma unroll
+      for (int n = 0; n < DIM; n++) {
+        double c = alpha * xj[k] * xm[n] + beta * xj[n] * xm[k];
+        if (j == m) c += Y[n + DIM * k];
+        if (k == n) c += zjm;
+        o[k * 3 + n] = c;
+      }
+  }
+  __syncthreads();
+  // the rows 162 .. LDR-1 of both T buffers feed the padding rows of the last row tiles: zero once
+  for (int idx = t; idx < 2 * Cfg::KC * (Cfg::LDR - Cfg::MR); idx += 256) {
+    const int kk = idx / (Cfg::LDR - Cfg::MR), x = idx - kk * (Cfg::LDR - Cfg::MR);
+    sT[kk * Cfg::LDR + Cfg::MR + x] = 0.0;
+  }
   // ---- residual R(i, j) = sum_q sum_k dN(q; i, k) (w detJ P)(j, k)
   if (t < TD) {
     const int i = t % ND, j = t / ND;
@@ -316,15 +407,17 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
     g.Re[e * TD + t] = r;
   }
 
-  // T phase of chunk ch: T[(qs, n)][(p, i)] = sum_k dN(q; i, k) C_q^{p}[k][n]; task = (p, qs, node i), lanes over i
+  // T phase of chunk ch: T[(qs, n)][(p, i)] = sum_k dN(q; i, k) C_q^{p}[k][n]; task = (p, qs) per warp, lanes over the node i
   auto t_phase = [&](int ch) {
     double* Tb = sT + (ch & 1) * Cfg::TBUF;
-    for (int task = t; task < Cfg::NJM * QC * 32; task += 256) {
-      const int i = task & 31, pq = task >> 5;
+    const int i = lane;
+#pragma unroll
+    for (int r = 0; r < Cfg::NJM * QC / 8; r++) {
+      const int pq = warp + 8 * r;
       const int p = pq / QC, qs = pq - p * QC;
+      const int q = ch * QC + qs;
+      const double* c = sC + (q * Cfg::NJM + p) * 9;
       if (i < ND) {
-        const int q = ch * QC + qs;
-        const double* c = sC + (q * Cfg::NJM + p) * 9;
         const double d0 = sdN[(q * DIM + 0) * NDP + i], d1 = sdN[(q * DIM + 1) * NDP + i], d2 = sdN[(q * DIM + 2) * NDP + i];
         double* o = Tb + (qs * DIM) * LDR + p * ND + i;
 #pragma unroll
@@ -332,6 +425,7 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
       }
     }
   };
+  static_assert((Cfg::NJM * QC) % 8 == 0, "T-phase tasks per warp");
 
   if (GEMM == 0) {
     // ---- DMMA: warp w owns row tiles w, w + 8, w + 16 (the last only for w < 5) x all 4 column tiles
@@ -342,7 +436,8 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
     for (int a = 0; a < NMT; a++)
 #pragma unroll
       for (int b = 0; b < Cfg::NTL; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
-    const bool has3 = warp + 16 < Cfg::MT;
+    const bool has3 = warp + 16 < Cfg::MT;   // the third tile of warps 5..7 is padding: computed (keeps the MMA loop
+                                             // branch-free and the sub-partitions balanced), never stored
     t_phase(0);
     __syncthreads();
 #pragma unroll 1
@@ -357,14 +452,11 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
 #pragma unroll
         for (int nt = 0; nt < Cfg::NTL; nt++) bf[nt] = brow[nt * 8];
 #pragma unroll
-        for (int a = 0; a < NMT; a++) af[a] = (a < 2 || has3) ? Tb[(ks * 4 + tig) * LDR + (warp + 8 * a) * 8 + gid] : 0.0;
+        for (int a = 0; a < NMT; a++) af[a] = Tb[(ks * 4 + tig) * LDR + (warp + 8 * a) * 8 + gid];
 #pragma unroll
-        for (int a = 0; a < NMT; a++) {
-          if (a < 2 || has3) {
+        for (int a = 0; a < NMT; a++)
 #pragma unroll
-            for (int nt = 0; nt < Cfg::NTL; nt++) dmma_m8n8k4(acc[a][nt][0], acc[a][nt][1], af[a], bf[nt]);
-          }
-        }
+          for (int nt = 0; nt < Cfg::NTL; nt++) dmma_m8n8k4(acc[a][nt][0], acc[a][nt][1], af[a], bf[nt]);
       }
       __syncthreads();
     }

@@ -151,6 +151,42 @@ def write_box_patch(path: str, p: int, spans, lengths=None) -> None:
                     f.write("%r %r 1\n" % (float(x), float(y)))
 
 
+def write_patch(path: str, p: int, knots, cps, weights) -> None:
+    """Single NURBS patch of degree p in MFEM's 'patches' format: knots[d] per direction, control points
+    cps[k][j][i][dim] (3D) / cps[j][i][dim] (2D) with direction 0 fastest, weights of the same shape (Cartesian
+    coordinates, not pre-multiplied)."""
+    cps = np.asarray(cps, np.float64)
+    w = np.asarray(weights, np.float64)
+    dim = cps.shape[-1]
+    topo = _HEX_TOPOLOGY if dim == 3 else _QUAD_TOPOLOGY
+    with open(path, "w") as f:
+        f.write("MFEM NURBS mesh v1.0\n\n" + topo + "\npatches\n\nknotvectors\n%d\n" % dim)
+        for kv in knots:
+            f.write("%d %d " % (p, len(kv) - p - 1) + " ".join(repr(float(k)) for k in kv) + "\n")
+        f.write("\ndimension\n%d\n\ncontrolpoints_cartesian\n" % dim)
+        for x, ww in zip(cps.reshape(-1, dim), w.reshape(-1)):
+            f.write(" ".join(repr(float(c)) for c in x) + " %r\n" % float(ww))
+
+
+def write_quarter_annulus(path: str, r0=1.0, r1=2.0, height=None) -> None:
+    """Rational, curved geometry: the exact quarter annulus r0 <= r <= r1 (2D), or the thick quarter cylinder of the given
+    height (3D), p = 2 in every direction, one knot span each (refine with Mesh::UniformRefinement). Direction 0 = radial,
+    direction 1 = angular (rational quadratic arc, weights 1, sqrt(1/2), 1), direction 2 = axial."""
+    s = np.sqrt(0.5)
+    kv = [0.0, 0.0, 0.0, 1.0, 1.0, 1.0]
+    rs = [r0, 0.5 * (r0 + r1), r1]
+    ang = [((1.0, 0.0), 1.0), ((1.0, 1.0), s), ((0.0, 1.0), 1.0)]
+    if height is None:
+        cps = [[[r * a[0], r * a[1]] for r in rs] for a, _ in ang]
+        w = [[ww for _ in rs] for _, ww in ang]
+        write_patch(path, 2, [kv, kv], cps, w)
+    else:
+        zs = [0.0, 0.5 * height, height]
+        cps = [[[[r * a[0], r * a[1], z] for r in rs] for a, _ in ang] for z in zs]
+        w = [[[ww for _ in rs] for _, ww in ang] for _ in zs]
+        write_patch(path, 2, [kv, kv, kv], cps, w)
+
+
 # ---------------------------------------------------------------------------------------------------
 # Synthetic connectivity of a single 3D patch in MFEM's own numbering, so that large meshes (which the
 # reference cannot precompute on a host) get the same DOF indexing the reference would produce.

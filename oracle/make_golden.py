@@ -248,6 +248,42 @@ def bodyforce_main():
     print("bodyforce", {k: v.shape for k, v in out.items()})
 
 
+# Rational / curved / non-affine geometry: exact quarter annulus (weights 1, sqrt(1/2), 1), thick
+# quarter cylinder, and the reference's own non-affine tests/data/square-nurbs.mesh. Each file carries the patch as MFEM
+# holds it after refinement (knots, el_ijk, node weights) and MFEM's setup forms, so the device generators can be pinned.
+CURVED_CASES = {
+    "annulus_p2_n2": (lambda f: meshgen.write_quarter_annulus(f), 0, 1, 0.8),
+    "cylinder_p2_n2": (lambda f: meshgen.write_quarter_annulus(f, height=1.0), 0, 1, 0.8),
+    "square_nurbs_p2_n4": (lambda f: meshgen.write_cell_p1(f, meshgen.SQUARE_NURBS_VERTS), 1, 2, 0.5),
+}
+
+
+def curved_main():
+    for name, (writer, elevate, refine, gf) in CURVED_CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            mesh = os.path.join(tmp, "m.mesh")
+            writer(mesh)
+            out = {}
+            for mat in ("neohookean", "stvk", "j2linear"):
+                D = O.run_ref_dump(mesh, elevate, refine, mat, os.path.join(tmp, mat), gf=gf)
+                if not out:
+                    for k in ("I", "J", "v_dofs", "A_ids", "w", "detJ", "dN_dX", "N", "x_ref", "u", "mass", "ncp", "el_ijk",
+                              "node_w", "bodyforce", "viscform", "rhs_bf_traction", "t_meta", "t_v_dofs", "t_N", "t_w", "t_detW"):
+                        out[k] = D[k]
+                    for d, kv in enumerate(D["knots"]):
+                        out["knots%d" % d] = kv
+                    out["p"] = np.int64(D["p"])
+                    out["meta"] = np.array([D["dim"], D["nd"], D["nq"], D["NE"], D["NV"], D["nnz"]], np.int64)
+                    out["gf"] = np.float64(gf)
+                    out["lambda_mu"] = np.array([float.fromhex(D["lambda"]), float.fromhex(D["mu"])])
+                out["r_" + mat], out["r2_" + mat], out["A_" + mat] = D["r"], D["r2"], D["A"]
+                if mat == "j2linear":
+                    out["state_j2linear"], out["rb_j2linear"], out["Ab_j2linear"] = D["state"], D["r_b"], D["A_b"]
+            np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+            print(name, {k: int(v) for k, v in zip(("dim", "nd", "nq", "NE", "NV", "nnz"), out["meta"])},
+                  "weights in [%.4f, %.4f]" % (out["node_w"].min(), out["node_w"].max()))
+
+
 def main(only=None):
     assert O.have_ref(), "build oracle/_ref first: make -f oracle/Makefile.ref -j8"
     os.makedirs(OUT, exist_ok=True)
@@ -279,7 +315,9 @@ def main(only=None):
 
 
 if __name__ == "__main__":
-    if "contact_steps" in sys.argv[1:]:
+    if "curved" in sys.argv[1:]:
+        curved_main()
+    elif "contact_steps" in sys.argv[1:]:
         contact_steps_main()
     elif "contact" in sys.argv[1:]:
         contact_main()
@@ -303,3 +341,4 @@ if __name__ == "__main__":
         eig_main()
         histories_main()
         contact_steps_main()
+        curved_main()

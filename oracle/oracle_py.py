@@ -236,6 +236,15 @@ def load_dump(d):
     out["state"] = rd("state.f64", np.float64)
     if out["state"] is not None:
         out["state"] = out["state"].reshape(NE, nq, -1)
+    pm = rd("p_meta.i32", np.int32)     # single-patch meshes: the patch as MFEM holds it (degree, ncp, knots, el_ijk, weights)
+    if pm is not None:
+        kn = rd("p_knots.f64", np.float64)
+        out["p"], out["ncp"] = int(pm[0]), pm[2:2 + dim].astype(np.int32)
+        sizes = pm[2 + dim:2 + 2 * dim]
+        offs = np.concatenate([[0], np.cumsum(sizes)])
+        out["knots"] = [kn[offs[d]:offs[d + 1]].copy() for d in range(dim)]
+        out["el_ijk"] = rd("el_ijk.i32", np.int32, (NE, dim))
+        out["node_w"] = rd("node_w.f64", np.float64)
     out["t_meta"] = rd("t_meta.i32", np.int32)
     out["t_v_dofs"] = rd("t_v_dofs.i32", np.int32)
     for k in ("x_ref", "u", "r", "r2", "mass", "bodyforce", "viscform", "mass_b200", "viscform_b200", "bodyforce_b200", "rhs_b200", "rhs_bf_traction", "t_w", "t_detW", "t_N", "A", "r_b", "A_b"):

@@ -513,6 +513,30 @@ int main(int argc, char** argv) {
     // nodes (x_ref) in the FE space's byVDIM ordering
     mfem::GridFunction& nodes = *s.mesh->GetNodes();
     dump(out, "x_ref.f64", nodes.GetData(), (size_t)nodes.Size());
+    // the patch as MFEM's NURBSExtension holds it after elevation / refinement (single-patch meshes): degree, control
+    // points per direction, knot vectors, knot-span index of every element, NURBS weight of every node
+    if (s.mesh->NURBSext && s.mesh->NURBSext->GetNP() == 1) {
+      mfem::NURBSExtension* ext = s.mesh->NURBSext;
+      mfem::Array<const mfem::KnotVector*> kvs;
+      ext->GetPatchKnotVectors(0, kvs);
+      std::vector<int> pm = {kvs[0]->GetOrder(), dim};
+      std::vector<double> kn;
+      for (int d = 0; d < dim; ++d) pm.push_back(kvs[d]->GetNCP());
+      for (int d = 0; d < dim; ++d) {
+        pm.push_back(kvs[d]->Size());
+        for (int i = 0; i < kvs[d]->Size(); ++i) kn.push_back((*kvs[d])[i]);
+      }
+      std::vector<int> ijk;
+      mfem::Array<int> e_ijk(dim);
+      for (int e = 0; e < NE; ++e) {
+        ext->GetElementIJK(e, e_ijk);
+        for (int d = 0; d < dim; ++d) ijk.push_back(e_ijk[d]);
+      }
+      dump(out, "p_meta.i32", pm.data(), pm.size());
+      dump(out, "p_knots.f64", kn.data(), kn.size());
+      dump(out, "el_ijk.i32", ijk.data(), ijk.size());
+      dump(out, "node_w.f64", ext->GetWeights().GetData(), (size_t)ext->GetWeights().Size());
+    }
 
     mfem::Vector u(NV), r(NV), r2(NV);
     fill_u(u, u_file);

@@ -9,7 +9,16 @@ from mimi_b200 import meshgen
 from oracle import oracle_py as O
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "balken_p3_n2", "quad_p2_n4", "cube_p2_n3_patch", "cube_p3_n2"]
+# rational / curved / non-affine NURBS geometry (quarter annulus and thick quarter cylinder with weights 1, sqrt(1/2), 1; the
+# reference's own non-affine tests/data/square-nurbs.mesh): oracle/make_golden.py curved_main. They also carry the patch as
+# MFEM holds it (p, ncp, knots0.., el_ijk, node_w) and MFEM's setup forms (bodyforce, viscform, rhs_bf_traction, t_*).
+CURVED_CASES = ["annulus_p2_n2", "cylinder_p2_n2", "square_nurbs_p2_n4"]
+GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "balken_p3_n2", "quad_p2_n4", "cube_p2_n3_patch", "cube_p3_n2"] + CURVED_CASES
+
+
+def patch_description(D):
+    """(p, ncp, knots, el_ijk, node weights) of a curved fixture."""
+    return int(D["p"]), D["ncp"], [D["knots%d" % d] for d in range(D["dim"])], D["el_ijk"], D["node_w"]
 MATS = {"neohookean": 0, "stvk": 1, "j2linear": 2}
 
 

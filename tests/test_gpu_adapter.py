@@ -24,6 +24,10 @@ RECIPES = {
     "beam2d_p3_n2": (lambda f: meshgen.write_box_p1(f, (5.0, 1.0)), 2, 1),
     "quad_p2_n4": (lambda f: meshgen.write_box_p1(f, (2.0, 1.0)), 1, 2),
     "cube_p3_n2": (lambda f: meshgen.write_box_p1(f, (1.0, 1.0, 1.0)), 2, 1),
+    # rational / curved / non-affine geometry (oracle/make_golden.py CURVED_CASES)
+    "annulus_p2_n2": (lambda f: meshgen.write_quarter_annulus(f), 0, 1),
+    "cylinder_p2_n2": (lambda f: meshgen.write_quarter_annulus(f, height=1.0), 0, 1),
+    "square_nurbs_p2_n4": (lambda f: meshgen.write_cell_p1(f, meshgen.SQUARE_NURBS_VERTS), 1, 2),
 }
 
 

@@ -66,3 +66,35 @@ def test_oracle_forms_properties():
     w = np.full(D["NV"] // 3, 0.5)
     Mw = O.form_element_matrices(0, 3, p, D["v_dofs"], ijk, knots, D["x_ref"], coef=2.0, weights=w)
     assert np.allclose(Mw, Me, rtol=1e-13, atol=0)
+
+
+from tests.cases import CURVED_CASES, patch_description  # noqa: E402
+
+
+@pytest.mark.parametrize("name", CURVED_CASES)
+def test_oracle_forms_on_rational_and_curved_geometry_bit_exact_vs_reference(name):
+    """Rows A2 / f3 on NURBS geometry proper: exact quarter annulus / thick quarter cylinder (weights 1, sqrt(1/2), 1:
+    the rational branch of fe_nurbs.cpp:243-311, non-constant Jacobian) and the reference's own non-affine
+    square-nurbs.mesh. Mass, viscosity, body force and body force + traction equal MFEM's integrators inside the compiled
+    reference bit for bit, with the patch description MFEM itself holds after refinement."""
+    D = load_golden(name)
+    dim, nd = D["dim"], D["nd"]
+    p, ncp, knots, ijk, w = patch_description(D)
+    Me = O.form_element_matrices(0, dim, p, D["v_dofs"], ijk, knots, D["x_ref"], weights=w)
+    M = O.assemble_bilinear_form(dim, nd, D["v_dofs"], D["I"], D["J"], Me)
+    assert np.array_equal(M, D["mass"]), np.abs(M - D["mass"]).max()
+    Se = O.form_element_matrices(2, dim, p, D["v_dofs"], ijk, knots, D["x_ref"], coef=0.37, weights=w)
+    S = O.assemble_bilinear_form(dim, nd, D["v_dofs"], D["I"], D["J"], Se)
+    assert np.array_equal(S, D["viscform"]), np.abs(S - D["viscform"]).max()
+    f = np.array([0.3, -1.7, 0.9])[:dim]
+    be = O.form_element_vectors(dim, p, D["v_dofs"], ijk, knots, D["x_ref"], f, weights=w)
+    b = O.assemble_linear_form(D["NV"], D["v_dofs"], be)
+    assert np.array_equal(b, D["bodyforce"]), np.abs(b - D["bodyforce"]).max()
+    NF, ndf, nqf = (int(x) for x in D["t_meta"])
+    rhs = O.add_traction_form(b.copy(), dim, D["t_v_dofs"].reshape(NF, -1), D["t_N"].reshape(NF, nqf, ndf),
+                              D["t_w"].reshape(NF, nqf), D["t_detW"].reshape(NF, nqf), np.array([0.5, -0.25, 1.5])[:dim])
+    assert np.array_equal(rhs, D["rhs_bf_traction"])
+    if name != "square_nurbs_p2_n4":
+        assert w.min() < 0.9        # genuinely rational
+        r = np.hypot(D["x_ref"].reshape(-1, dim)[:, 0], D["x_ref"].reshape(-1, dim)[:, 1])
+        assert r.max() > 2.0        # control points off the arc: the geometry is curved, not interpolated
