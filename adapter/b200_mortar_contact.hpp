@@ -38,23 +38,24 @@ struct B200RigidBody {
 /// Kind by spline type: Bezier -> MB2_RIGID_BEZIER, RationalBezier -> MB2_RIGID_RATIONAL_BEZIER, BSpline ->
 /// MB2_RIGID_BSPLINE, NURBS -> MB2_RIGID_NURBS. The kd-tree resolution becomes the device's seed sampling (capped: the
 /// device samples every Bezier patch per query instead of planting a tree once).
-class B200NearestDistanceToSplines : public mimi::coefficients::NearestDistanceToSplines, public B200RigidBody {
-  int resolution_{65};
-
-public:
-  int max_seed_curve_{256}, max_seed_surface_{32};
-  void PlantKdTree(const int resolution, const int nthreads) {  // hides the base's: also remembers the sampling
-    resolution_ = resolution;
-    mimi::coefficients::NearestDistanceToSplines::PlantKdTree(resolution, nthreads);
+/// Describes the spline a NearestDistanceToSplines scene holds in the layout of mb2_contact_set_rigid_body.
+/// n_seed: sampling of the device's initial guess per Bezier patch and direction.
+struct B200SplineScene : mimi::coefficients::NearestDistanceToSplines {
+  // the scene keeps its splines protected: reach them through a derived class, read-only
+  static const std::vector<std::shared_ptr<splinepy::py::PySpline>>& Splines(
+      const mimi::coefficients::NearestDistanceToSplines& s) {
+    return s.*(&B200SplineScene::splines_);
   }
-  int B200Kind() const override {
-    const auto& core = splines_.at(0)->Core();
+  static int Kind(const mimi::coefficients::NearestDistanceToSplines& s) {
+    const auto& core = Splines(s).at(0)->Core();
     const bool knots = core->SplinepyHasKnotVectors(), rational = core->SplinepyIsRational();
     return knots ? (rational ? MB2_RIGID_NURBS : MB2_RIGID_BSPLINE) : (rational ? MB2_RIGID_RATIONAL_BEZIER : MB2_RIGID_BEZIER);
   }
-  std::vector<double> B200Params() const override {
-    if (splines_.size() != 1) mimi::utils::PrintAndThrowError("mimi_b200: one spline per contact scene (as the reference asserts)");
-    const auto& core = splines_[0]->Core();
+  static std::vector<double> Params(const mimi::coefficients::NearestDistanceToSplines& s, const int resolution,
+                                    const int max_seed_curve = 256, const int max_seed_surface = 32) {
+    const auto& splines = Splines(s);
+    if (splines.size() != 1) mimi::utils::PrintAndThrowError("mimi_b200: one spline per contact scene (as the reference asserts)");
+    const auto& core = splines[0]->Core();
     const int pd = core->SplinepyParaDim(), dim = core->SplinepyDim(), n = core->SplinepyNumberOfControlPoints();
     const bool knots = core->SplinepyHasKnotVectors(), rational = core->SplinepyIsRational();
     int deg[3] = {0, 0, 0}, res[3] = {1, 1, 1};
@@ -62,8 +63,8 @@ public:
     std::vector<double> cps(size_t(n) * dim), w(rational ? n : 0);
     core->SplinepyCurrentProperties(deg, knots ? &kv : nullptr, cps.data(), rational ? w.data() : nullptr);
     core->SplinepyControlMeshResolutions(res);
-    const int cap = pd == 1 ? max_seed_curve_ : max_seed_surface_;
-    const int n_seed = std::max(1, std::min(resolution_ - 1, cap));
+    const int cap = pd == 1 ? max_seed_curve : max_seed_surface;
+    const int n_seed = std::max(1, std::min(resolution - 1, cap));
     std::vector<double> p = {double(deg[0]), pd > 1 ? double(deg[1]) : 0.0, double(n_seed)};
     if (knots) {
       p.push_back(res[0]);
@@ -78,6 +79,25 @@ public:
   }
 };
 
+/// The reference's own scene class (coefficients/nearest_distance.hpp:214-281) that also remembers the kd-tree resolution
+/// of plant_kd_tree, which becomes the device's seed sampling (capped: the device samples every Bezier patch per query
+/// instead of planting a tree once). A plain NearestDistanceToSplines (what the pybind11 module constructs) works too:
+/// B200MortarContact describes it with the default sampling.
+class B200NearestDistanceToSplines : public mimi::coefficients::NearestDistanceToSplines, public B200RigidBody {
+  int resolution_{65};
+
+public:
+  int max_seed_curve_{256}, max_seed_surface_{32};
+  void PlantKdTree(const int resolution, const int nthreads) {  // hides the base's: also remembers the sampling
+    resolution_ = resolution;
+    mimi::coefficients::NearestDistanceToSplines::PlantKdTree(resolution, nthreads);
+  }
+  int B200Kind() const override { return B200SplineScene::Kind(*this); }
+  std::vector<double> B200Params() const override {
+    return B200SplineScene::Params(*this, resolution_, max_seed_curve_, max_seed_surface_);
+  }
+};
+
 class B200MortarContact : public NonlinearBase {
   mb2_ctx* ctx_;
   std::shared_ptr<mimi::coefficients::NearestDistanceBase> scene_;
@@ -89,10 +109,16 @@ class B200MortarContact : public NonlinearBase {
     if (rc) mimi::utils::PrintAndThrowError("mimi_b200:", mb2_last_error(ctx_));
   }
   void PushBody() const {  // every call: examples/nl_contact.py moves the body between steps
-    const auto* body = dynamic_cast<const B200RigidBody*>(scene_.get());
-    if (!body) mimi::utils::PrintAndThrowError("mimi_b200: the contact scene does not describe itself (B200RigidBody)");
-    const std::vector<double> p = body->B200Params();
-    Check(mb2_contact_set_rigid_body(ctx_, body->B200Kind(), p.data(), (int)p.size(), scene_->coefficient_));
+    if (const auto* body = dynamic_cast<const B200RigidBody*>(scene_.get())) {
+      const std::vector<double> p = body->B200Params();
+      Check(mb2_contact_set_rigid_body(ctx_, body->B200Kind(), p.data(), (int)p.size(), scene_->coefficient_));
+    } else if (const auto* sp = dynamic_cast<const mimi::coefficients::NearestDistanceToSplines*>(scene_.get())) {
+      // the reference's own scene as the pybind11 module builds it (py_nearest_distance.cpp:24-32)
+      const std::vector<double> p = B200SplineScene::Params(*sp, 257);
+      Check(mb2_contact_set_rigid_body(ctx_, B200SplineScene::Kind(*sp), p.data(), (int)p.size(), scene_->coefficient_));
+    } else {
+      mimi::utils::PrintAndThrowError("mimi_b200: the contact scene does not describe itself (B200RigidBody)");
+    }
   }
   void Fetch() {
     Check(mb2_contact_get_nodal(ctx_, average_gap_.GetData(), area_.GetData(), average_pressure_.GetData()));
