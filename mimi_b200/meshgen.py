@@ -168,6 +168,50 @@ def write_patch(path: str, p: int, knots, cps, weights) -> None:
             f.write(" ".join(repr(float(c)) for c in x) + " %r\n" % float(ww))
 
 
+def write_beam_patches(path: str, p: int, spans, n_patches: int, lengths=(1.0, 1.0, 1.0)) -> None:
+    """Multi-patch beam (BASELINE config 4): n_patches hexahedral patches of degree p glued along x, each with spans =
+    (nx, ny, nz) knot spans and size lengths (per patch), open uniform knots, control points at the Greville abscissae.
+    Vertices: cross-section s holds 4 s + {0: (y0, z0), 1: (y1, z0), 2: (y1, z1), 3: (y0, z1)}; knot vector s belongs to
+    the x edges of patch s, n_patches / n_patches + 1 to all y / z edges."""
+    M = int(n_patches)
+    kvs = [open_uniform_knots(p, n) for n in spans]
+    grev = [greville(p, kv) * L for kv, L in zip(kvs, lengths)]
+    with open(path, "w") as f:
+        f.write("MFEM NURBS mesh v1.0\n\ndimension\n3\n\nelements\n%d\n" % M)
+        for s_ in range(M):
+            a, b = 4 * s_, 4 * (s_ + 1)
+            f.write("1 5 %d %d %d %d %d %d %d %d\n" % (a, b, b + 1, a + 1, a + 3, b + 3, b + 2, a + 2))
+        f.write("\nboundary\n%d\n" % (4 * M + 2))
+        for s_ in range(M):
+            a, b = 4 * s_, 4 * (s_ + 1)
+            f.write("1 3 %d %d %d %d\n" % (a + 1, b + 1, b, a))          # z = 0
+            f.write("2 3 %d %d %d %d\n" % (a + 3, b + 3, b + 2, a + 2))  # z = 1
+            f.write("3 3 %d %d %d %d\n" % (a, b, b + 3, a + 3))          # y = 0
+            f.write("5 3 %d %d %d %d\n" % (b + 1, a + 1, a + 2, b + 2))  # y = 1
+        f.write("6 3 %d %d %d %d\n" % (1, 0, 3, 2))                       # x = 0
+        e = 4 * M
+        f.write("4 3 %d %d %d %d\n" % (e, e + 1, e + 2, e + 3))           # x = L
+        f.write("\nedges\n%d\n" % (4 * M + 4 * (M + 1)))
+        for s_ in range(M):
+            for i in range(4):
+                f.write("%d %d %d\n" % (s_, 4 * s_ + i, 4 * (s_ + 1) + i))
+        for s_ in range(M + 1):
+            a = 4 * s_
+            f.write("%d %d %d\n%d %d %d\n" % (M, a, a + 1, M, a + 3, a + 2))
+            f.write("%d %d %d\n%d %d %d\n" % (M + 1, a, a + 3, M + 1, a + 1, a + 2))
+        f.write("\nvertices\n%d\n\npatches\n\n" % (4 * (M + 1)))
+        for s_ in range(M):
+            f.write("knotvectors\n3\n")
+            for kv in kvs:
+                f.write("%d %d " % (p, len(kv) - p - 1) + " ".join(repr(float(k)) for k in kv) + "\n")
+            f.write("\ndimension\n3\n\ncontrolpoints_cartesian\n")
+            for z in grev[2]:
+                for y in grev[1]:
+                    for x in grev[0]:
+                        f.write("%r %r %r 1\n" % (float(x + s_ * lengths[0]), float(y), float(z)))
+            f.write("\n")
+
+
 def write_quarter_annulus(path: str, r0=1.0, r1=2.0, height=None) -> None:
     """Rational, curved geometry: the exact quarter annulus r0 <= r <= r1 (2D), or the thick quarter cylinder of the given
     height (3D), p = 2 in every direction, one knot span each (refine with Mesh::UniformRefinement). Direction 0 = radial,

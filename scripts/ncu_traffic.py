@@ -28,7 +28,7 @@ ctas_per_element = 4 if "split" in key else 1
 path = os.path.join(ROOT, "profiles", "traffic.json")
 T = json.load(open(path)) if os.path.exists(path) else {}
 T[key] = {"launch_elements": grid // ctas_per_element, "dram_read_bytes": val("dram__bytes_read.sum"),
-          "dram_write_bytes": val("dram__bytes_write.sum"), "kernel_ms": float(v[h.index("gpu__time_duration.sum")]),
+          "dram_write_bytes": val("dram__bytes_write.sum"), "kernel_ms": float(v[h.index("gpu__time_duration.sum")]) * {"us": 1e-3, "ns": 1e-6, "ms": 1.0, "s": 1e3}.get(units[h.index("gpu__time_duration.sum")], 1.0),
           "source_md5": bench.source_md5(key), "capture": capture}
 json.dump(T, open(path, "w"), indent=1, sort_keys=True)
 print(json.dumps(T[key]))
