@@ -194,6 +194,37 @@ def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean", s
     return M
 
 
+def build_problem_c4(ctx, n, rank=0, world=1, uid=None):
+    """BASELINE config 4: multi-patch p = 3 StVenantKirchhoff beam, patches of n^3 knot spans glued along x, element-partitioned:
+    every rank computes n x n x n/2 elements (N = 1: half a patch; N = 2: one patch; N = 4: two; N = 8: the four patches =
+    4e6 elements at n = 100). Lexicographic numbering over the glued control grid (mimi_b200/partition.py beam_rank_problem);
+    the parity fixtures with MFEM's own multi-patch numbering are tests/golden/beam4_p3.npz / beam3_p2.npz."""
+    from mimi_b200 import capi, meshgen, partition
+    t0 = time.time()
+    p = 3
+    M_patches = max(1, world // 2)
+    spans = (n, n, n if world >= 2 else n // 2)
+    M = partition.beam_rank_problem(p, spans, M_patches, world, rank)
+    nq1 = (2 * p + 3) // 2 + 1
+    ctx.set_connectivity(3, M["nd"], nq1 ** 3, M["NV"], M["v_dofs"])
+    if world > 1:
+        ctx.mg_setup(M)
+        ctx.mg_init_nccl(rank, world, uid)
+    ctx.set_nodes(M["x_ref"], None)
+    for (e0, cnt, q) in M["patch_segments"]:
+        ctx.generate_patch_tables(p, M["ncp"], M["knots"], M["el_ijk"][e0:e0 + cnt], e0=e0)
+    nnz = ctx.build_pattern()
+    young, poisson = 2100.0, 0.3
+    lam = young * poisson / ((1 + poisson) * (1 - 2 * poisson))
+    mu = young / (2.0 * (1.0 + poisson))
+    ctx.set_material(capi.MB2_MAT_STVK, [lam, mu])
+    u = meshgen.synth_u(M["NV"])
+    x = M["x_ref"].reshape(-1, 3)
+    u.reshape(-1, 3)[x[:, 0] == 0.0, :] = 0.0
+    M.update(u=u, nnz=nnz, nq=nq1 ** 3, setup_s=time.time() - t0, n_patches=M_patches, spans=spans)
+    return M
+
+
 def source_md5(kernel_key=""):
     """md5 of the kernel's source text: a committed ncu capture only speaks for a binary built from the same kernel
     source. p=2: the text of element_fd_kernel (Elem2Cfg .. the next section) + mb2_math.cuh; p=3: element_fd_split_kernel."""
@@ -341,6 +372,9 @@ def gpu_arm(args):
         if not parity["ok"]:
             raise RuntimeError("partitioned assembly over NCCL differs from the reference's golden vectors: not timing a wrong result")
 
+    c4 = args.workload == "c4"
+    if c4:
+        args.p, args.material = 3, "stvk"
     n, p = args.n, args.p
     stream = torch.cuda.Stream()            # the library launches on this stream, so torch events see its work
     ctx = capi.Context(local, stream=stream.cuda_stream)
@@ -353,7 +387,7 @@ def gpu_arm(args):
     if world > 1:
         uid = [capi.mg_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
-    M = build_problem(ctx, n, p, rank, world, uid[0], args.material)
+    M = build_problem_c4(ctx, n, rank, world, uid[0]) if c4 else build_problem(ctx, n, p, rank, world, uid[0], args.material)
     NE, nq, NV, nnz = M["n_compute"], M["nq"], M["NV"], M["nnz"]     # NE = elements this rank computes
     ctx.set_u(M["u"])
     ctx.set_r(None)
@@ -410,7 +444,8 @@ def gpu_arm(args):
         up, ap_, rp, Ap = (C_void(t) for t in (u_h, a_h, r_h, A_h))
         # mass, resident: assembled on the device (VectorMassIntegrator, rho = 1), never leaves it
         ctx.set_A(None)
-        ctx.assemble_mass_device(p, M["ncp"], M["knots"], M["el_ijk"][:M["n_compute"]])
+        if not c4:       # c4: the device forms take one patch per call -- a zero mass keeps the same kernels in the timed call
+            ctx.assemble_mass_device(p, M["ncp"], M["knots"], M["el_ijk"][:M["n_compute"]])
         ctx.newton_mass_from_A(False)
         ctx.sync()
 
@@ -455,7 +490,7 @@ def gpu_arm(args):
 
     # ---- strong scaling: the SAME 1e6-element block (n^3) cut into N z-slabs ----
     strong = None
-    if world > 1 and args.scaling in ("strong", "both") and n % world == 0:
+    if world > 1 and args.scaling in ("strong", "both") and n % world == 0 and not c4:
         ctx2 = capi.Context(local, stream=stream.cuda_stream)
         ctx2.set_option("elem_variant", args.variant)
         uid2 = [capi.mg_unique_id() if rank == 0 else None]
@@ -531,12 +566,16 @@ def gpu_arm(args):
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
-                "config": {"workload": "%s: 3D unit-cube B-spline patch p=%d, %d^3 = %d elements x %d qp per GPU, %s, "
+                "config": {"workload": ("C4: multi-patch beam, %d patch(es) of %dx%dx%d knot spans glued along x, p=3, %d elements x %d qp per GPU "
+                                        "(%d elements in all), stvk, one residual+tangent assembly into CSR (nnz=%d per GPU), lexicographic "
+                                        "numbering over the glued control grid" % (M["n_patches"], M["spans"][0], M["spans"][1], M["spans"][2], NE, nq,
+                                                                                    M["NE_global"], nnz)) if c4 else
+                                       "%s: 3D unit-cube B-spline patch p=%d, %d^3 = %d elements x %d qp per GPU, %s, "
                                        "one residual+tangent assembly into CSR (nnz=%d per GPU), MFEM dof numbering" % (
                                            "C3" if (p == 2 and args.material == "neohookean") else "C4-style block", p, n, NE, nq, args.material, nnz),
                            "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "nnz_per_gpu": nnz, "tangent": "FD parity (bit-exact vs reference)" if not fast else "MB2_TANGENT_ANALYTIC: closed-form tangent, %s contraction (NOT the headline mode: agrees with the reference's FD Jacobian to its 1e-4 noise, same Newton iteration counts)" % ("FP64 tensor-core (DMMA)" if args.fast_gemm == 0 else "CUDA-core DFMA"),
                            "l2": "inputs larger than L2 (tables %.1f GB, K_e %.1f GB per step)" % (8e-9 * NE * nq * (tdof + 1), 8e-9 * NE * tdof * tdof),
-                           "parallelism": "1 GPU" if world == 1 else "z-slabs of %d^3 elements per GPU of one %dx%dx%d patch; raw K_e/R_e of the p interface layers sent to the owner rank by NCCL send/recv inside the step (bit-identical to the 1-thread reference order)" % (n, n, n, n * world),
+                           "parallelism": "1 GPU" if world == 1 else ("element ranges of %d elements per rank: every patch cut into 2 z-slabs, raw K_e/R_e of the p layers under every cut and of the first element column behind every patch interface sent to the owner rank by NCCL inside the step" % NE) if c4 else "z-slabs of %d^3 elements per GPU of one %dx%dx%d patch; raw K_e/R_e of the p interface layers sent to the owner rank by NCCL send/recv inside the step (bit-identical to the 1-thread reference order)" % (n, n, n, n * world),
                            "setup_s": M["setup_s"]},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_host_csr": e2e_host, "e2e_roundtrip": e2e_rt,
                 "strong_scaling": strong, "gpu_launches": launches, "clocks": clocks, "wall_s_timed_region": wall}
@@ -731,7 +770,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--p", type=int, default=2, help="degree (2 = C3 headline; 3 = the C4 element type)")
     ap.add_argument("--material", default="neohookean", choices=["neohookean", "stvk"])
-    ap.add_argument("--workload", default="c3", choices=["c3", "c5"], help="c5: J2 + contact secondary workload (1 GPU)")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
+                    help="c4: multi-patch p=3 StVK beam, 5e5 elements per GPU (config 4); c5: J2 + contact secondary workload (1 GPU)")
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     ap.add_argument("--tangent", default="parity", choices=["parity", "analytic"],
                     help="analytic = MB2_TANGENT_ANALYTIC fast mode (secondary line; p=2, neohookean / stvk)")

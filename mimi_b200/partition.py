@@ -107,3 +107,117 @@ def slab_rank_problem(p: int, spans, world: int, rank: int, lengths=None) -> dic
                 local_elems=np.arange(e0, e0 + len(el_ijk)), v_dofs=v_dofs, owned=owned, send=send, recv=recv,
                 el_ijk=el_ijk, knots=kvs, ncp=np.array(ncp, np.int32), x_ref=x.ravel(), NV=3 * Nn, Nn=Nn, nd=nd, p=p,
                 NE=len(el_ijk), NE_global=n_layer * n2)
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE config 4: multi-patch beam, M patches glued along x, element-partitioned across the ranks.
+# Numbering used by the throughput bench (NOT MFEM's multi-patch numbering, which the parity fixtures carry):
+# nodes lexicographic over the glued control grid, ix fastest; elements patch by patch, i fastest, then j, then k.
+# ---------------------------------------------------------------------------------------------------
+def _beam_dims(p, spans, M):
+    nx, ny, nz = (int(s) for s in spans)
+    cx = nx + p
+    return nx, ny, nz, cx, M * (cx - 1) + 1, ny + p, nz + p
+
+
+def beam_connectivity(p: int, spans, n_patches: int):
+    """Global connectivity of the glued beam (small sizes: tests): v_dofs [NE, 3 (p+1)^3], NV."""
+    M = int(n_patches)
+    nx, ny, nz, cx, NX, NY, NZ = _beam_dims(p, spans, M)
+    s, k, j, i = np.meshgrid(np.arange(M), np.arange(nz), np.arange(ny), np.arange(nx), indexing="ij")
+    return _beam_vdofs(p, spans, M, s.ravel(), i.ravel(), j.ravel(), k.ravel()), 3 * NX * NY * NZ
+
+
+def _beam_vdofs(p, spans, M, s, i, j, k):
+    nx, ny, nz, cx, NX, NY, NZ = _beam_dims(p, spans, M)
+    nd = (p + 1) ** 3
+    nodes = np.empty((len(s), nd), np.int64)
+    a = 0
+    for c in range(p + 1):
+        for b in range(p + 1):
+            for a_ in range(p + 1):
+                nodes[:, a] = (s * (cx - 1) + i + a_) + NX * ((j + b) + NY * (k + c))
+                a += 1
+    return np.concatenate([3 * nodes + c for c in range(3)], 1).astype(np.int32)
+
+
+def beam_rank_problem(p: int, spans, n_patches: int, world: int, rank: int, lengths=(1.0, 1.0, 1.0)) -> dict:
+    """rank_problem for the glued beam WITHOUT the global connectivity (config 4 has 4e6 p = 3 elements). world >= M: every
+    patch is cut into world / M z-slabs of whole element layers; world < M: every rank takes M / world whole patches.
+    Same rules as rank_problem (node owner = rank of its lowest element; raw element matrices of higher ranks that touch
+    an owned node arrive as ghosts); equality with rank_problem on beam_connectivity is checked in tests/test_partition.py."""
+    from . import meshgen
+    M = int(n_patches)
+    nx, ny, nz, cx, NX, NY, NZ = _beam_dims(p, spans, M)
+    if world >= M:
+        assert world % M == 0 and nz % (world // M) == 0 and nz // (world // M) >= p, "slabs of >= p whole layers per rank"
+        R, lz = world // M, nz // (world // M)
+        rank_of = lambda s_, k_: s_ * R + k_ // lz                      # noqa: E731
+    else:
+        assert M % world == 0
+        G = M // world
+        rank_of = lambda s_, k_: s_ // G + 0 * k_                       # noqa: E731
+    npe, nlay = nx * ny * nz, nx * ny
+    ks = np.arange(nz)
+    own_blocks, ghost_parts, send_parts = [], [], {}
+    lay = np.arange(nlay)
+    lay_i0 = np.arange(ny) * nx                                          # elements with i == 0 inside a layer
+    for s_ in range(M):
+        for k_ in range(nz):
+            re = int(rank_of(s_, k_))
+            kk = np.arange(max(0, k_ - p), k_ + 1)
+            set_s = set(int(x) for x in rank_of(s_, kk))
+            set_sm = set(int(x) for x in rank_of(s_ - 1, kk)) if s_ > 0 else set()
+            base = s_ * npe + k_ * nlay
+            if re == rank:
+                own_blocks.append(base + lay)
+                for r2 in sorted((set_s | set_sm) - {rank}):
+                    assert r2 < rank
+                    send_parts.setdefault(r2, []).append(base + (lay if r2 in set_s else lay_i0))
+            elif re > rank:
+                if rank in set_s:
+                    ghost_parts.append((re, base + lay))
+                elif rank in set_sm:
+                    ghost_parts.append((re, base + lay_i0))
+    own = np.concatenate(own_blocks)
+    e0, n_compute = int(own[0]), len(own)
+    assert np.array_equal(own, np.arange(e0, e0 + n_compute))
+    ghosts = np.concatenate([g for _, g in ghost_parts]) if ghost_parts else np.zeros(0, np.int64)
+    gsrc = np.concatenate([np.full(len(g), r2) for r2, g in ghost_parts]) if ghost_parts else np.zeros(0, np.int64)
+    order = np.argsort(ghosts, kind="stable")
+    ghosts, gsrc = ghosts[order], gsrc[order]
+    local = np.concatenate([own, ghosts])
+    recv = {int(r2): np.nonzero(gsrc == r2)[0] + n_compute for r2 in np.unique(gsrc)}
+    send = {int(r2): np.sort(np.concatenate(v)) - e0 for r2, v in send_parts.items()}
+    s_ = local // npe
+    rem = local - s_ * npe
+    k_, rem = rem // nlay, rem % nlay
+    j_, i_ = rem // nx, rem % nx
+    v_dofs = _beam_vdofs(p, spans, M, s_, i_, j_, k_)
+    # node owners
+    ix, iz = np.arange(NX), np.arange(NZ)
+    smin = np.where(ix == 0, 0, np.minimum((ix - 1) // (cx - 1), M - 1))
+    kmin = np.maximum(iz - p, 0)
+    owner_xz = rank_of(smin[:, None], kmin[None, :])                     # [NX, NZ]
+    owned = np.zeros((NZ, NY, NX), bool)
+    owned[:] = (owner_xz.T == rank)[:, None, :]
+    kvs = [meshgen.open_uniform_knots(p, n) for n in (nx, ny, nz)]
+    grev = [meshgen.greville(p, kv) * L for kv, L in zip(kvs, lengths)]
+    sx = np.minimum(ix // (cx - 1), M - 1)
+    X = sx * lengths[0] + grev[0][ix - sx * (cx - 1)]
+    x = np.empty((NZ, NY, NX, 3))
+    x[..., 0] = X[None, None, :]
+    x[..., 1] = grev[1][None, :, None]
+    x[..., 2] = grev[2][:, None, None]
+    # own elements patch by patch (mb2_generate_patch_tables is called once per segment)
+    segs = []
+    so = s_[:n_compute]
+    for q in np.unique(so):
+        idx = np.nonzero(so == q)[0]
+        segs.append((int(idx[0]), int(len(idx)), int(q)))
+    el_ijk = np.stack([i_, j_, k_], 1).astype(np.int32)
+    Nn = NX * NY * NZ
+    return dict(rank=rank, world=world, e0=e0, e1=e0 + n_compute, n_compute=n_compute, local_elems=local, v_dofs=v_dofs,
+                owned=owned.ravel(), send=send, recv=recv, el_ijk=el_ijk, knots=kvs,
+                ncp=np.array([cx, NY, NZ], np.int32), x_ref=x.reshape(-1), NV=3 * Nn, Nn=Nn, nd=(p + 1) ** 3, p=p,
+                NE=len(local), NE_global=M * npe, patch_segments=segs)

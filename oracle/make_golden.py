@@ -284,6 +284,57 @@ def curved_main():
                   "weights in [%.4f, %.4f]" % (out["node_w"].min(), out["node_w"].max()))
 
 
+def config1_main(nsteps=20):
+    """BASELINE config 1: examples/nonlinear_solid.py as shipped -- balken.mesh (= the 5 x 1 one-element box), elevate 1,
+    subdivide 2, NeoHookean (2100, 0.3, rho 1), clamped boundary 2, body force -5 on component 1, dt 0.05, Newton
+    (1e-12, 1e-8, 10), generalized-alpha with the default ode_coefficient 0.25, nl.setup(2) -- through harness mode `steps`
+    on the CPU reference at nthreads = 2 (as shipped) and 1."""
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        meshgen.write_box_p1(mesh, (5.0, 1.0))
+        out = {}
+        for nt in (1, 2):
+            x, its = O.run_ref_steps(mesh, 1, 2, "neohookean", -5.0, 0.05, nsteps, os.path.join(tmp, "o%d" % nt), nthreads=nt, rho_inf=0.25)
+            out["x_nt%d" % nt], out["its_nt%d" % nt] = x, its
+            print("config1 nthreads=%d Newton iterations %s max|u| %.4f" % (nt, its.tolist(), np.abs(x).max()))
+    np.savez_compressed(os.path.join(OUT, "config1_steps.npz"), **out)
+
+
+# Multi-patch meshes (BASELINE config 4: patches glued along x, shared interface nodes numbered by MFEM's NURBSExtension,
+# precomputed.cpp:39-218 run across the patch interfaces): 4 x (2 x 1 x 1) p = 3 and 3 x (2 x 2 x 2) p = 2.
+MULTIPATCH_CASES = {
+    "beam4_p3": (lambda f: meshgen.write_beam_patches(f, 3, (2, 1, 1), 4, (1.0, 0.5, 0.5)), 0.7),
+    "beam3_p2": (lambda f: meshgen.write_beam_patches(f, 2, (2, 2, 2), 3, (1.0, 1.0, 1.0)), 0.9),
+}
+
+
+def multipatch_main():
+    for name, (writer, gf) in MULTIPATCH_CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            mesh = os.path.join(tmp, "m.mesh")
+            writer(mesh)
+            out = {}
+            for mat in ("neohookean", "stvk"):
+                D = O.run_ref_dump(mesh, 0, 0, mat, os.path.join(tmp, mat), gf=gf)
+                if not out:
+                    for k in ("I", "J", "v_dofs", "A_ids", "w", "detJ", "dN_dX", "N", "x_ref", "u", "mass", "el_ijk", "el_patch", "node_w"):
+                        out[k] = D[k]
+                    out["p"], out["n_patches"] = np.int64(D["p"]), np.int64(D["n_patches"])
+                    for q, (ncp, kv) in enumerate(zip(D["patch_ncp"], D["patch_knots"])):
+                        out["ncp_%d" % q] = ncp
+                        for d, k in enumerate(kv):
+                            out["knots_%d_%d" % (q, d)] = k
+                    out["meta"] = np.array([D["dim"], D["nd"], D["nq"], D["NE"], D["NV"], D["nnz"]], np.int64)
+                    out["gf"] = np.float64(gf)
+                    out["lambda_mu"] = np.array([float.fromhex(D["lambda"]), float.fromhex(D["mu"])])
+                out["r_" + mat], out["r2_" + mat], out["A_" + mat] = D["r"], D["r2"], D["A"]
+            D = O.run_ref_dump(mesh, 0, 0, "j2linear", os.path.join(tmp, "j2linear"), gf=gf)
+            out["r_j2linear"], out["r2_j2linear"], out["A_j2linear"] = D["r"], D["r2"], D["A"]
+            out["state_j2linear"], out["rb_j2linear"], out["Ab_j2linear"] = D["state"], D["r_b"], D["A_b"]
+            np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+            print(name, {k: int(v) for k, v in zip(("dim", "nd", "nq", "NE", "NV", "nnz"), out["meta"])}, "patches", int(out["n_patches"]))
+
+
 def main(only=None):
     assert O.have_ref(), "build oracle/_ref first: make -f oracle/Makefile.ref -j8"
     os.makedirs(OUT, exist_ok=True)
@@ -315,7 +366,11 @@ def main(only=None):
 
 
 if __name__ == "__main__":
-    if "curved" in sys.argv[1:]:
+    if "config1" in sys.argv[1:]:
+        config1_main()
+    elif "multipatch" in sys.argv[1:]:
+        multipatch_main()
+    elif "curved" in sys.argv[1:]:
         curved_main()
     elif "contact_steps" in sys.argv[1:]:
         contact_steps_main()
@@ -342,3 +397,5 @@ if __name__ == "__main__":
         histories_main()
         contact_steps_main()
         curved_main()
+        multipatch_main()
+        config1_main()

@@ -236,14 +236,22 @@ def load_dump(d):
     out["state"] = rd("state.f64", np.float64)
     if out["state"] is not None:
         out["state"] = out["state"].reshape(NE, nq, -1)
-    pm = rd("p_meta.i32", np.int32)     # single-patch meshes: the patch as MFEM holds it (degree, ncp, knots, el_ijk, weights)
+    pm = rd("p_meta.i32", np.int32)     # the patches as MFEM holds them (degree, ncp, knots per patch; el_patch, el_ijk, weights)
     if pm is not None:
         kn = rd("p_knots.f64", np.float64)
-        out["p"], out["ncp"] = int(pm[0]), pm[2:2 + dim].astype(np.int32)
-        sizes = pm[2 + dim:2 + 2 * dim]
-        offs = np.concatenate([[0], np.cumsum(sizes)])
-        out["knots"] = [kn[offs[d]:offs[d + 1]].copy() for d in range(dim)]
+        NP = int(pm[2])
+        out["p"], out["n_patches"] = int(pm[0]), NP
+        out["patch_ncp"], out["patch_knots"] = [], []
+        o, k = 3, 0
+        for _ in range(NP):
+            out["patch_ncp"].append(pm[o:o + dim].astype(np.int32))
+            sizes = pm[o + dim:o + 2 * dim]
+            out["patch_knots"].append([kn[k + int(sizes[:d].sum()):k + int(sizes[:d + 1].sum())].copy() for d in range(dim)])
+            k += int(sizes.sum())
+            o += 2 * dim
+        out["ncp"], out["knots"] = out["patch_ncp"][0], out["patch_knots"][0]      # single-patch shorthand
         out["el_ijk"] = rd("el_ijk.i32", np.int32, (NE, dim))
+        out["el_patch"] = rd("el_patch.i32", np.int32)
         out["node_w"] = rd("node_w.f64", np.float64)
     out["t_meta"] = rd("t_meta.i32", np.int32)
     out["t_v_dofs"] = rd("t_v_dofs.i32", np.int32)
@@ -765,12 +773,13 @@ def run_ref_eig(mats, outdir):
     return lam, vec
 
 
-def run_ref_steps(mesh, elevate, refine, material, force, dt, nsteps, outdir, binary=None, nthreads=1):
+def run_ref_steps(mesh, elevate, refine, material, force, dt, nsteps, outdir, binary=None, nthreads=1, rho_inf=None):
     """Harness mode 'steps': the reference's own time loop (forms::Nonlinear + operators::NonlinearSolid + LineSearchNewton
     + GeneralizedAlpha2) on the clamped-beam set-up of its tests -> (x history [nsteps][NV], Newton iterations)."""
     os.makedirs(outdir, exist_ok=True)
+    env = dict(os.environ) if rho_inf is None else {**os.environ, "MIMI_REF_RHO_INF": repr(float(rho_inf))}
     subprocess.check_call([binary or REF_BIN, "steps", mesh, str(elevate), str(refine), material, str(nthreads), repr(force),
-                           repr(dt), str(nsteps), outdir], stdout=subprocess.DEVNULL)
+                           repr(dt), str(nsteps), outdir], stdout=subprocess.DEVNULL, env=env)
     its = np.fromfile(os.path.join(outdir, "newton_its.i32"), np.int32)
     return np.fromfile(os.path.join(outdir, "x_hist.f64")).reshape(nsteps, -1), its
 

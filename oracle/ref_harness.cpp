@@ -515,26 +515,34 @@ int main(int argc, char** argv) {
     dump(out, "x_ref.f64", nodes.GetData(), (size_t)nodes.Size());
     // the patch as MFEM's NURBSExtension holds it after elevation / refinement (single-patch meshes): degree, control
     // points per direction, knot vectors, knot-span index of every element, NURBS weight of every node
-    if (s.mesh->NURBSext && s.mesh->NURBSext->GetNP() == 1) {
+    if (s.mesh->NURBSext) {
+      // p_meta = {degree, dim, number of patches, then per patch: ncp[dim], knot counts[dim]}; knots patch by patch;
+      // per element: its patch (el_patch) and its knot-span index inside that patch (el_ijk)
       mfem::NURBSExtension* ext = s.mesh->NURBSext;
+      const int NP = ext->GetNP();
       mfem::Array<const mfem::KnotVector*> kvs;
       ext->GetPatchKnotVectors(0, kvs);
-      std::vector<int> pm = {kvs[0]->GetOrder(), dim};
+      std::vector<int> pm = {kvs[0]->GetOrder(), dim, NP};
       std::vector<double> kn;
-      for (int d = 0; d < dim; ++d) pm.push_back(kvs[d]->GetNCP());
-      for (int d = 0; d < dim; ++d) {
-        pm.push_back(kvs[d]->Size());
-        for (int i = 0; i < kvs[d]->Size(); ++i) kn.push_back((*kvs[d])[i]);
+      for (int pch = 0; pch < NP; ++pch) {
+        ext->GetPatchKnotVectors(pch, kvs);
+        for (int d = 0; d < dim; ++d) pm.push_back(kvs[d]->GetNCP());
+        for (int d = 0; d < dim; ++d) {
+          pm.push_back(kvs[d]->Size());
+          for (int i = 0; i < kvs[d]->Size(); ++i) kn.push_back((*kvs[d])[i]);
+        }
       }
-      std::vector<int> ijk;
+      std::vector<int> ijk, epatch;
       mfem::Array<int> e_ijk(dim);
       for (int e = 0; e < NE; ++e) {
         ext->GetElementIJK(e, e_ijk);
         for (int d = 0; d < dim; ++d) ijk.push_back(e_ijk[d]);
+        epatch.push_back(ext->GetElementPatch(e));
       }
       dump(out, "p_meta.i32", pm.data(), pm.size());
       dump(out, "p_knots.f64", kn.data(), kn.size());
       dump(out, "el_ijk.i32", ijk.data(), ijk.size());
+      dump(out, "el_patch.i32", epatch.data(), epatch.size());
       dump(out, "node_w.f64", ext->GetWeights().GetData(), (size_t)ext->GetWeights().Size());
     }
 
@@ -611,7 +619,7 @@ int main(int argc, char** argv) {
       dump(out, "t_N.f64", tN.data(), tN.size());
     }
 #ifdef MIMI_REF_USE_B200  // the same three forms through the adapter (device assembly), dumped beside MFEM's
-    {
+    if (s.mesh->NURBSext->GetNP() == 1) {  // the device forms take one tensor-product patch per call
       mfem::SparseMatrix Mb(sp), Sb(sp);
       s.integ->AssembleMass(*s.mesh, s.mat->density_, Mb);
       dump(out, "mass_b200.f64", Mb.GetData(), (size_t)nnz);
@@ -867,7 +875,10 @@ int main(int argc, char** argv) {
     newton->SetAbsTol(1e-8);
     newton->SetMaxIter(10);
     nl_oper->SetNewtonSolver(newton);
-    mimi::solvers::GeneralizedAlpha2 ode(*nl_oper, 0.5);
+    // rho_inf: the reference's tests set ode_coefficient = 0.5; PyNonlinearSolid::Setup's default, which examples/*.py run
+    // with, is 0.25 (py_nonlinear_solid.cpp:367-368): MIMI_REF_RHO_INF overrides
+    const char* env_rho_inf = std::getenv("MIMI_REF_RHO_INF");
+    mimi::solvers::GeneralizedAlpha2 ode(*nl_oper, env_rho_inf ? std::atof(env_rho_inf) : 0.5);
     nl_oper->Setup();
     ode.SetupDirichletDofs(nl_oper->dirichlet_dofs_);
     mfem::Vector x(NV), v(NV);

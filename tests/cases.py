@@ -13,7 +13,21 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 # reference's own non-affine tests/data/square-nurbs.mesh): oracle/make_golden.py curved_main. They also carry the patch as
 # MFEM holds it (p, ncp, knots0.., el_ijk, node_w) and MFEM's setup forms (bodyforce, viscform, rhs_bf_traction, t_*).
 CURVED_CASES = ["annulus_p2_n2", "cylinder_p2_n2", "square_nurbs_p2_n4"]
-GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "balken_p3_n2", "quad_p2_n4", "cube_p2_n3_patch", "cube_p3_n2"] + CURVED_CASES
+GOLDEN_CASES = ["cube_p2_n2", "cube_p1_n2", "beam2d_p3_n2", "balken_p3_n2", "quad_p2_n4", "cube_p2_n3_patch", "cube_p3_n2"] + CURVED_CASES + ["beam4_p3", "beam3_p2"]
+
+
+# multi-patch beams dumped from the reference (oracle/make_golden.py multipatch_main): MFEM's numbering across patch interfaces
+MULTIPATCH_CASES = ["beam4_p3", "beam3_p2"]
+
+
+def patches_of(D):
+    """[(element range e0, e1), ncp, knots] per patch of a multi-patch fixture (elements are ordered patch by patch)."""
+    out = []
+    for q in range(int(D["n_patches"])):
+        idx = np.nonzero(D["el_patch"] == q)[0]
+        assert idx.size and np.array_equal(idx, np.arange(idx[0], idx[0] + idx.size))
+        out.append(((int(idx[0]), int(idx[-1]) + 1), D["ncp_%d" % q], [D["knots_%d_%d" % (q, d)] for d in range(D["dim"])]))
+    return out
 
 
 def patch_description(D):

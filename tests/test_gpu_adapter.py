@@ -31,10 +31,17 @@ RECIPES = {
 }
 
 
+# multi-patch beams (oracle/make_golden.py MULTIPATCH_CASES): only the integrator chain (the device forms are per patch)
+MP_RECIPES = {
+    "beam4_p3": (lambda f: meshgen.write_beam_patches(f, 3, (2, 1, 1), 4, (1.0, 0.5, 0.5)), 0, 0),
+    "beam3_p2": (lambda f: meshgen.write_beam_patches(f, 2, (2, 2, 2), 3, (1.0, 1.0, 1.0)), 0, 0),
+}
+
+
 def run_adapter(name, material, gf):
     if not O.have_ref_b200():
         pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
-    writer, elevate, refine = RECIPES[name]
+    writer, elevate, refine = RECIPES[name] if name in RECIPES else MP_RECIPES[name]
     with tempfile.TemporaryDirectory() as tmp:
         mesh = os.path.join(tmp, "m.mesh")
         writer(mesh)
@@ -42,7 +49,7 @@ def run_adapter(name, material, gf):
 
 
 @pytest.mark.parametrize("material", ["neohookean", "stvk", "j2linear"])
-@pytest.mark.parametrize("name", list(RECIPES))
+@pytest.mark.parametrize("name", list(RECIPES) + list(MP_RECIPES))
 def test_reference_chain_through_the_adapter_bit_exact(name, material):
     G = load_golden(name)
     D = run_adapter(name, material, G["gf"])
@@ -210,3 +217,23 @@ def test_nl_contact_time_loop_through_the_adapter():
     # the converged trajectory (each step solved to 1e-10 relative): the reference's own spread is 3e-12 .. 2e-11
     assert _rel(x, z["x"]) <= 1e-9
     assert np.allclose(ch[:, :5], z["contact_hist"][:, :5], rtol=1e-7, atol=1e-9 * np.abs(z["contact_hist"][:, :5]).max())
+
+
+def test_config1_example_as_shipped_through_the_adapter():
+    """BASELINE config 1 = examples/nonlinear_solid.py as shipped (balken.mesh, elevate 1, subdivide 2, NeoHookean, body
+    force -5, dt 0.05, Newton 1e-12 / 1e-8 / 10, default ode_coefficient 0.25): 20 generalized-alpha steps on the reference's
+    own classes with B200NonlinearSolid as the domain integrator. Identical Newton iteration counts and a bit-identical
+    trajectory against the compiled CPU reference (tests/golden/config1_steps.npz, nthreads 1 and 2 agree there)."""
+    if not O.have_ref_b200():
+        pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "config1_steps.npz"))
+    n = z["x_nt1"].shape[0]
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        meshgen.write_box_p1(mesh, (5.0, 1.0))
+        x, its = O.run_ref_steps(mesh, 1, 2, "neohookean", -5.0, 0.05, n, os.path.join(tmp, "o"), binary=O.REF_B200_BIN, rho_inf=0.25)
+    print("\n[config 1] adapter Newton iterations %s; CPU reference %s; max |x - x_ref| = %.2e" % (
+        its.tolist(), z["its_nt1"].tolist(), float(np.abs(x - z["x_nt1"]).max())))
+    assert np.array_equal(z["its_nt1"], z["its_nt2"])
+    assert its.tolist() == z["its_nt1"].tolist()
+    assert np.array_equal(x, z["x_nt1"])          # bit-exact integrator => bit-identical nonlinear trajectory

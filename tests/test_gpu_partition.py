@@ -25,14 +25,18 @@ def _rank_ctx(ctx, D, R, material, chunk):
 
 
 @pytest.mark.parametrize("name,world,chunk", [("cube_p2_n3_patch", 2, 0), ("cube_p2_n3_patch", 3, 2), ("cube_p2_n2", 2, 1),
-                                              ("beam2d_p3_n2", 2, 0)])
+                                              ("beam2d_p3_n2", 2, 0),
+                                              # multi-patch beams: the cuts fall ON patch interfaces (4 ranks / 4 patches), INSIDE
+                                              # patches (2 and 3 ranks over 3 patches of 8 elements) -- ghosts cross both
+                                              ("beam4_p3", 4, 0), ("beam4_p3", 2, 0), ("beam3_p2", 2, 0), ("beam3_p2", 4, 5),
+                                              ("beam3_p2", 3, 0)])
 @pytest.mark.parametrize("grad", [True, False])
-def test_emulated_ranks_reproduce_reference(ctx_factory, name, world, chunk, grad):
+def test_emulated_ranks_reproduce_reference(ctx_factory, name, world, chunk, grad, material="neohookean"):
     D = load_golden(name)
     dim = D["dim"]
     ranges = P.element_ranges(D["NE"], world)
     ranks = [P.rank_problem(D["v_dofs"], dim, D["NV"], ranges, r) for r in range(world)]
-    ctxs = [_rank_ctx(ctx_factory(), D, R, "neohookean", chunk) for R in ranks]
+    ctxs = [_rank_ctx(ctx_factory(), D, R, material, chunk) for R in ranks]
     gf = D["gf"]
     # global CSR offsets of every rank's (compact) row block
     for ctx, R in zip(ctxs, ranks):
@@ -61,9 +65,17 @@ def test_emulated_ranks_reproduce_reference(ctx_factory, name, world, chunk, gra
         if grad:
             A_glob[R["_gidx"]] = ctx.get_A()
     if grad:
-        assert np.array_equal(r_glob, D["r2_neohookean"]) and np.array_equal(A_glob, D["A_neohookean"])
+        assert np.array_equal(r_glob, D["r2_" + material]) and np.array_equal(A_glob, D["A_" + material])
     else:
-        assert np.array_equal(r_glob, D["r_neohookean"])
+        assert np.array_equal(r_glob, D["r_" + material])
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_config4_element_type_partitioned_across_patches(ctx_factory, world):
+    """BASELINE config 4 in small: 4-patch p = 3 StVenantKirchhoff beam, element-partitioned over 2 / 4 / 8 emulated ranks
+    (8 ranks = one element each: every patch interface and every in-patch cut carries ghosts), bit-identical to the
+    reference's single-thread assembly."""
+    test_emulated_ranks_reproduce_reference(ctx_factory, "beam4_p3", world, 0, True, material="stvk")
 
 
 def test_partition_call_order_is_checked(ctx_factory):

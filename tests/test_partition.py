@@ -115,3 +115,27 @@ def test_slab_problem_equals_generic(p, spans, world):
         for k in S["recv"]:
             assert np.array_equal(S["recv"][k], G["recv"][k])
         assert np.array_equal(S["x_ref"], M["x_ref"]) and np.array_equal(S["el_ijk"], M["el_ijk"][G["local_elems"]])
+
+
+@pytest.mark.parametrize("p,spans,M,world", [(2, (2, 2, 4), 2, 4), (3, (2, 1, 6), 2, 4), (2, (3, 2, 2), 4, 2), (2, (2, 2, 2), 4, 4),
+                                             (1, (2, 3, 4), 2, 8), (2, (2, 2, 4), 1, 2)])
+def test_beam_rank_problem_equals_the_generic_planner(p, spans, M, world):
+    """Config 4's analytic planner (glued multi-patch beam, no global connectivity) against rank_problem on the full
+    connectivity: same own range, ghosts, owned nodes, send / receive lists, local connectivity."""
+    from mimi_b200 import partition as P
+    v_dofs, NV = P.beam_connectivity(p, spans, M)
+    ranges = P.element_ranges(len(v_dofs), world)
+    for rank in range(world):
+        A = P.rank_problem(v_dofs, 3, NV, ranges, rank)
+        B = P.beam_rank_problem(p, spans, M, world, rank)
+        assert (A["e0"], A["e1"], A["n_compute"]) == (B["e0"], B["e1"], B["n_compute"])
+        assert np.array_equal(A["local_elems"], B["local_elems"]) and np.array_equal(A["v_dofs"], B["v_dofs"])
+        touched = A["owner"] >= 0
+        assert np.array_equal(A["owned"][touched], B["owned"][touched]) and B["NV"] == NV
+        assert sorted(A["send"]) == sorted(B["send"]) and sorted(A["recv"]) == sorted(B["recv"])
+        for k in A["send"]:
+            assert np.array_equal(A["send"][k], B["send"][k])
+        for k in A["recv"]:
+            assert np.array_equal(A["recv"][k], B["recv"][k])
+        segs = B["patch_segments"]
+        assert sum(n for _, n, _ in segs) == B["n_compute"] and segs[0][0] == 0
