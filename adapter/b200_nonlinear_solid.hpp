@@ -81,9 +81,12 @@ public:
   }
 
   /// Dispatch on MaterialBase::Name() (materials.hpp); user subclasses the library does not know throw.
-  void SetMaterial() {
+  void SetMaterial() { SetMaterialOn(ctx_, *material_, dt_); }
+  static void SetMaterialOn(mb2_ctx* ctx_, mimi::materials::MaterialBase& m, const double dt_) {
     namespace mm = mimi::materials;
-    auto& m = *material_;
+    auto Check = [ctx_](int rc) {
+      if (rc) mimi::utils::PrintAndThrowError("mimi_b200:", mb2_last_error(ctx_));
+    };
     const std::string n = m.Name();
     if (n == "StVenantKirchhoff" || n.find("NeoHookean") != std::string::npos) {
       const double par[2] = {m.lambda_, m.mu_};

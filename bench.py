@@ -599,20 +599,55 @@ def gpu_arm(args):
 # ----------------------------------------------------------------------------------------------------
 def c5_arm(args):
     import torch
-    from mimi_b200 import capi, meshgen
+    import torch.distributed as dist
+    from mimi_b200 import capi, meshgen, partition
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: libmimi_b200 has no CPU fallback")
-    torch.cuda.set_device(0)
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def maxr(x):
+        if world > 1:
+            tt = torch.tensor([x], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt[0])
+        return x
+
+    parity = None
+    if world > 1:
+        parity = nccl_parity_check(rank, world, local, dist)
+        if not parity["ok"]:
+            raise RuntimeError("partitioned assembly over NCCL differs from the reference's golden vectors")
     n, p = args.n, 2
-    spans = (n, n, n)
     stream = torch.cuda.Stream()
-    ctx = capi.Context(0, stream=stream.cuda_stream)
+    ctx = capi.Context(local, stream=stream.cuda_stream)
     t0 = time.time()
-    M = meshgen.patch_connectivity(p, spans)
     nq1 = p + 2
+    spans = (n, n, n * world)          # weak scaling: n^3 elements (and their history variables) per GPU, z-slabs
+    if world == 1:
+        M = meshgen.patch_connectivity(p, spans)
+        M["n_compute"] = M["NE"]
+        gtop = meshgen.patch_node_grid(M["ncp"])[:, :, -1]
+    else:
+        M = partition.slab_rank_problem(p, spans, world, rank)
+        gtop = M["node_grid_top"]
     ctx.set_connectivity(3, M["nd"], nq1 ** 3, M["NV"], M["v_dofs"])
+    if world > 1:
+        uid = [capi.mg_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.mg_setup(M)
+        ctx.mg_init_nccl(rank, world, uid[0])
     ctx.set_nodes(M["x_ref"], None)
-    ctx.generate_patch_tables(p, M["ncp"], M["knots"], M["el_ijk"])
+    ctx.generate_patch_tables(p, M["ncp"], M["knots"], M["el_ijk"][:M["n_compute"]])
     nnz = ctx.build_pattern()
     young, poisson = 2100.0, 0.3
     lam = young * poisson / ((1 + poisson) * (1 - 2 * poisson))
@@ -622,16 +657,19 @@ def c5_arm(args):
     # that the synthetic 1e-3 displacement field yields at about half of the quadrature points
     hp = [2.0, 4.0, 0.2835, 0.015, 1.0e-5, 20.0, 0.0, 1.3558, 0.0, 0.0]
     ctx.set_material(capi.MB2_MAT_J2, [lam, mu, K, mu, 4] + hp + [0.05, 0.9, 1.0, 450.0, 20.0, 1500.0])
-    F = meshgen.top_face_tables(M, spans)
+    # rigid contact on the global top face: every rank evaluates all marked faces (faces << elements), gathers its own rows
+    F = meshgen.top_face_tables_from_grid(p, spans[:2], M["knots"], gtop)
     ctx.contact_set_faces(F["v_dofs"], F["N"], F["dN_dxi"], F["w"])
+    ztop = float(M["x_ref"].reshape(-1, 3)[:, 2].max())
     body = np.zeros(16)
-    body[:4] = [0.5, 0.5, 1.9998, 1.0]              # rigid sphere pressed 2e-4 into the face z = 1
+    body[:4] = [0.5, 0.5, ztop + 1.0 - 2e-4, 1.0]     # rigid sphere pressed 2e-4 into the top face
     ctx.contact_set_rigid_body(capi.MB2_RIGID_SPHERE, body, 1.0e4 * young)
     u = meshgen.synth_u(M["NV"])
     x = M["x_ref"].reshape(-1, 3)
     u.reshape(-1, 3)[x[:, 2] == 0.0, :] = 0.0       # clamped bottom
     setup_s = time.time() - t0
-    NE, nq = M["NE"], nq1 ** 3
+    NE, nq = M["n_compute"], nq1 ** 3
+    tdof = 3 * M["nd"]
     ctx.set_u(u); ctx.set_r(None); ctx.set_A(None)
     # commit a first history so that the timed assemblies run on a non-virgin state
     ctx._ck(ctx.lib.mb2_post_time_advance_device(ctx.h))
@@ -648,11 +686,11 @@ def c5_arm(args):
     for _ in range(args.warmup):
         step()
     ctx.sync()
-    sampler = ClockSampler(0)
-    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    barrier()
     sampler.start()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 2)]
-    t_el, launches, t_contact = [], 0, []
+    t_el, launches = [], 0
     ev[0].record(stream)
     for k in range(args.steps):
         ctx.assemble_residual_and_grad_device(1.0)
@@ -663,23 +701,50 @@ def c5_arm(args):
         ctx.contact_residual_and_grad_device(1.0)
         launches += ctx.last_launch_count()
         ev[2 + 2 * k].record(stream)
-    torch.cuda.synchronize()
+    barrier()
     clocks = sampler.stop()
-    dev_ms = float(ev[0].elapsed_time(ev[2 * args.steps]))
+    dev_ms = maxr(float(ev[0].elapsed_time(ev[2 * args.steps])))
     contact_ms = float(np.mean([ev[1 + 2 * k].elapsed_time(ev[2 + 2 * k]) for k in range(args.steps)]))
     ctx.check_numeric()
-    # history commit, timed on its own
+    # ---- what the return mapping really did in one such assembly (measurement pass, atomics on, outside the timing)
+    ctx.set_option("j2_counters", 1)
+    ctx.j2_counters(reset=True)
+    ctx.assemble_residual_and_grad_device(1.0)
+    n_yield, n_hard = ctx.j2_counters(reset=True)
+    ctx.set_option("j2_counters", 0)
+    n_eval = float(NE) * nq * (tdof + 1)
+    yielded_fraction = n_yield / n_eval
+    hard_per_yield = n_hard / max(n_yield, 1)
+    # ---- implicit-dynamics time steps: 2 Newton iterations (assembly + contact, two line-search residuals each) and the
+    # history commit per step, the displacement growing from step to step (assembly share of a generalized-alpha step)
+    n_ts = max(2, min(args.steps, 4))
+    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_hist = 0.0
     e0.record(stream)
-    ctx._ck(ctx.lib.mb2_post_time_advance_device(ctx.h))
+    for ts in range(n_ts):
+        ctx.set_u(np.ascontiguousarray((1.5 + 0.1 * (ts + 1)) * u))
+        for it in range(2):
+            ctx.assemble_residual_and_grad_device(1.0)
+            ctx.contact_residual_and_grad_device(1.0)
+            for ls in range(2):
+                ctx.assemble_residual_device()
+                ctx._ck(ctx.lib.mb2_contact_residual_device(ctx.h))
+        ctx._ck(ctx.lib.mb2_post_time_advance_device(ctx.h))
     e1.record(stream)
+    barrier()
+    ts_ms = maxr(float(e0.elapsed_time(e1)) / n_ts)
+    ctx.check_numeric()
+    ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ea.record(stream)
+    ctx._ck(ctx.lib.mb2_post_time_advance_device(ctx.h))
+    eb.record(stream)
     torch.cuda.synchronize()
-    pta_ms = float(e0.elapsed_time(e1))
+    pta_ms = float(ea.elapsed_time(eb))
     gap, area, pr = ctx.contact_nodal()
-    S = None
     face_qp = F["NF"] * F["nqf"]
     ms_per_step = dev_ms / args.steps
-    total_qp = float(NE) * nq + face_qp
+    total_qp = float(NE) * nq * world + face_qp
     value = total_qp / (ms_per_step * 1e-3)
     # end to end: host-buffer entries (domain + contact) with pinned buffers
     e2e = None
@@ -695,48 +760,74 @@ def c5_arm(args):
             ctx._ck(ctx.lib.mb2_add_boundary_residual_and_grad(ctx.h, up, one, rp, Ap))
 
         host_step()
-        torch.cuda.synchronize()
+        barrier()
         t1 = time.perf_counter()
-        k2 = max(1, min(args.steps, args.e2e_steps))
+        k2 = max(1, min(args.steps, 3))
         for _ in range(k2):
             host_step()
-        torch.cuda.synchronize()
-        e2e_s = (time.perf_counter() - t1) / k2
+        barrier()
+        e2e_s = maxr((time.perf_counter() - t1) / k2)
         e2e = {"value": total_qp / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * (4 * M["NV"] + nnz),
                "d2h_bytes_per_step": 8 * (2 * M["NV"] + nnz), "ms_per_step": e2e_s * 1e3, "steps": k2,
                "call": "mb2_add_domain_residual_and_grad + mb2_add_boundary_residual_and_grad with pinned host buffers"}
     peak_nofma = ctx.measure_fp64_peak(0)
+    peak_fma = ctx.measure_fp64_peak(1)
     el_ms = float(np.mean(t_el))
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
-            "config": {"workload": "C5-style (secondary workload, not the headline): 3D unit-cube B-spline patch p=2, %d^3 = %d "
-                                   "elements x %d qp, J2 + JohnsonCookTemperatureAndRateDependent hardening with %d history "
-                                   "doubles per qp, rigid sphere on the %d faces (x %d qp) of z = 1; one step = domain "
-                                   "residual+tangent + contact residual+tangent into the same CSR (nnz=%d)" % (
-                                       n, NE, nq, ctx.state_size(), F["NF"], F["nqf"], nnz),
-                       "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "face_qp": face_qp, "nnz_per_gpu": nnz,
-                       "active_contact_nodes": int((pr != 0).sum()), "marked_nodes": int(pr.size),
-                       "l2": "inputs larger than L2", "parallelism": "1 GPU", "setup_s": setup_s},
-            "roofline": {"bound": "fp64", "kernel": "element_fd_kernel<3,27,64,J2>", "achieved": None, "peak": peak_nofma,
-                         "unit": "TFLOP/s", "frac": None, "traffic": None,
-                         "note": "data-dependent flop count (return mapping: bracketed Newton per yielded qp); kernel time "
-                                 "reported instead", "kernel_ms": el_ms},
-            "extra": {"domain_element_kernel_ms": el_ms, "contact_ms": contact_ms, "post_time_advance_ms": pta_ms,
-                      "contact_share": contact_ms / ms_per_step},
-            "cpu_baseline": None, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
-    if not args.no_cpu:
-        try:
-            cores = host_cores()
-            S = run_reference_sample(args.ref_n, 2, cores, warmup=1, p=2, material="j2_jcthermo")
-            line["cpu_baseline"] = {"value": S["value_mean"], "unit": UNIT, "cores": cores, "kind": "reference",
-                                    "sample": "unmodified reference, domain integrator only (J2 + JC thermo-rate hardening), "
-                                              "p=2 cube %d^3 = %d el, virgin state, %d threads" % (args.ref_n, S["NE"], cores)}
-        except Exception as ex:
-            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": host_cores(), "kind": "reference",
-                                    "sample": "unavailable: %s" % ex}
-    emit(line)
+    # ---- executed flops of the J2 element kernel: FP64 thread instructions per quadrature point from the committed ncu capture
+    # (profiles/j2_flops.json: DADD + DMUL + 2 DFMA of one launch, with the yielded fraction and hardening evaluations per return
+    # mapping it was taken at); valid for this run if the live counters agree with the capture's
+    roof = {"bound": "fp64", "kernel": "element_fd_kernel<3,27,64,J2>", "achieved": None, "peak": None, "unit": "TFLOP/s", "frac": None,
+            "traffic": None, "kernel_ms": el_ms, "yielded_fraction": yielded_fraction, "hardening_evals_per_return_mapping": hard_per_yield,
+            "stress_evaluations_per_assembly": n_eval}
+    try:
+        Jf = json.load(open(os.path.join(ROOT, "profiles", "j2_flops.json")))
+        ok = abs(Jf["yielded_fraction"] - yielded_fraction) <= 0.02 and abs(Jf["hardening_evals_per_return_mapping"] - hard_per_yield) <= 0.05 * hard_per_yield
+        flop_qp = Jf["flop_per_qp"]
+        mix = Jf["fused_flop_share"]          # share of the flops issued as DFMA (libdevice pow / log / divisions)
+        peak_mix = 1.0 / ((1.0 - mix) / peak_nofma + mix / peak_fma)
+        achieved = float(NE) * nq / (el_ms * 1e-3) * flop_qp / 1e12
+        roof.update(achieved=achieved if ok else None, peak=peak_mix, frac=(achieved / peak_mix) if ok else None,
+                    flop_per_qp_executed=flop_qp, peak_nofma=peak_nofma, peak_fma=peak_fma,
+                    peak_source="harmonic mix of the measured DMUL+DADD and DFMA peaks at the capture's fused share %.3f" % mix,
+                    flop_source=Jf.get("capture"), capture_matches_run=bool(ok))
+    except (OSError, KeyError, ValueError):
+        roof["note"] = "no profiles/j2_flops.json: data-dependent flop count not calibrated"
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic",
+                "config": {"workload": "C5-style (secondary workload, not the headline): 3D B-spline block p=2, %d x %d x %d = %d "
+                                       "elements x %d qp per GPU (%d GPUs: %d elements), J2 + JohnsonCookTemperatureAndRateDependent hardening with %d history "
+                                       "doubles per qp (partitioned with the elements), rigid sphere on the %d faces (x %d qp) of the top face (evaluated by every rank); one step = domain "
+                                       "residual+tangent + contact residual+tangent into the same CSR (nnz=%d per GPU)" % (
+                                           n, n, n, NE, nq, world, NE * world, ctx.state_size(), F["NF"], F["nqf"], nnz),
+                           "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "face_qp": face_qp, "nnz_per_gpu": nnz,
+                           "active_contact_nodes": int((pr != 0).sum()), "marked_nodes": int(pr.size),
+                           "l2": "inputs larger than L2", "parallelism": "1 GPU" if world == 1 else "z-slabs, NCCL exchange of raw K_e / R_e; history local; contact replicated",
+                           "setup_s": setup_s},
+                "roofline": roof,
+                "extra": {"domain_element_kernel_ms": el_ms, "contact_ms": contact_ms, "post_time_advance_ms": pta_ms,
+                          "contact_share": contact_ms / ms_per_step,
+                          "time_step": {"steps": n_ts, "newton_iterations_per_step": 2, "line_search_residuals_per_iteration": 2,
+                                        "ms_per_time_step": ts_ms, "note": "assembly share of an implicit generalized-alpha step: 2 x (residual + tangent + contact), "
+                                        "4 x (residual + contact), 1 history commit; the displacement grows every step"}},
+                "cpu_baseline": None, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
+        if parity:
+            line["parity_check"] = parity
+        if not args.no_cpu:
+            try:
+                cores = host_cores()
+                S = run_reference_sample(min(args.ref_n, 24), 2, cores, warmup=1, p=2, material="j2_jcthermo")
+                line["cpu_baseline"] = {"value": S["value_mean"], "unit": UNIT, "cores": S["omp_team"], "kind": "reference",
+                                        "sample": "unmodified reference, domain integrator only (J2 + JC thermo-rate hardening), "
+                                                  "p=2 cube %d^3 = %d el, virgin state, %d threads" % (min(args.ref_n, 24), S["NE"], S["omp_team"])}
+            except Exception as ex:
+                line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": host_cores(), "kind": "reference",
+                                        "sample": "unavailable: %s" % ex}
+        emit(line)
     ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
     return 0
 
 

@@ -175,6 +175,11 @@ int mb2_set_time_step(mb2_ctx* ctx, double dt);
  * mb2_newton_residual_and_grad_device) do NOT: a caller that consumes their output without going through the solve
  * must call mb2_check_numeric once per iteration. */
 int mb2_check_numeric(mb2_ctx* ctx);
+/* Measurement counters of the J2 family (on with mb2_set_option(ctx, "j2_counters", 1); they cost atomics, keep them off
+ * in timed runs): out2[0] = return mappings run since the last reset (yielded stress evaluations; an assembly makes
+ * NE * nq * (tdof + 1) stress evaluations in all), out2[1] = hardening-law evaluations inside their ScalarSolve calls
+ * (src/mimi/solvers/newton.hpp:53-169). bench.py uses them to turn the data-dependent J2 work into executed flops. */
+int mb2_get_j2_counters(mb2_ctx* ctx, uint64_t* out2, int reset);
 int mb2_get_state(mb2_ctx* ctx, double* state);
 int mb2_set_state(mb2_ctx* ctx, const double* state);
 /* Commits the history variables at the converged u. Replaces NonlinearSolid::DomainPostTimeAdvance
@@ -356,6 +361,29 @@ int mb2_mg_export_send(mb2_ctx* ctx, int peer, double* Ke_host, double* Re_host)
 int mb2_mg_import_recv(mb2_ctx* ctx, int peer, const double* Ke_host, const double* Re_host);
 int mb2_mg_finish(mb2_ctx* ctx, double grad_factor, int grad);
 int64_t mb2_mg_ke_doubles(mb2_ctx* ctx);
+
+/* ---- partition planner (pure host code; mimi_b200/partition.py is its test oracle) --------------------------------
+ * Plans rank `rank` of `world` for a GLOBAL connectivity (v_dofs NE x dim*nd as in mb2_set_connectivity): balanced
+ * contiguous element ranges, node owner = rank of the node's lowest element, ghosts = elements of higher ranks touching an
+ * owned node, send lists = own elements touching a lower rank's node. Replaces the reference's thread chunks
+ * (src/mimi/utils/n_thread_exe.hpp:36-97) across devices. */
+typedef struct mb2_plan mb2_plan;
+int mb2_plan_partition(const int32_t* v_dofs, int dim, int nd, int64_t NE, int64_t NV, int world, int rank, mb2_plan** out);
+void mb2_plan_free(mb2_plan* plan);
+/* what: 0 elements computed here, 1 local elements (own + ghosts), 2 global id of the first own element, 3 peers, 4 nodes */
+int64_t mb2_plan_size(const mb2_plan* plan, int what);
+int mb2_plan_local_elems(const mb2_plan* plan, int64_t* global_ids);          /* own elements, then ghosts */
+int mb2_plan_owned_nodes(const mb2_plan* plan, uint8_t* owned);               /* one byte per node */
+int mb2_plan_peer(const mb2_plan* plan, int k, int* peer, int64_t* n_send, int64_t* recv_first, int64_t* n_recv);
+int mb2_plan_peer_send(const mb2_plan* plan, int k, int64_t* send_local_elems);
+/* mb2_set_connectivity (the plan's local elements, global node ids) + mb2_set_partition + mb2_mg_set_send / _recv. */
+int mb2_plan_apply(mb2_ctx* ctx, const mb2_plan* plan, const int32_t* v_dofs_global, int nq);
+/* One process driving several GPUs (ctxs[r] = rank r's context, each after mb2_plan_apply ... mb2_build_pattern): the
+ * packed element matrices travel by cudaMemcpyPeerAsync (NVLink peer-to-peer where available). The C++ route to more than
+ * one GPU for a caller without MPI / torchrun (adapter/b200_multigpu.hpp). grad != 0: r += R(u), A += grad_factor K(u) on
+ * every rank's resident arrays (mb2_set_u / _r / _A per context before, mb2_get_r / _A after); 0: residual only. */
+int mb2_mg_group_init(mb2_ctx** ctxs, int n);
+int mb2_mg_group_assemble(mb2_ctx** ctxs, int n, double grad_factor, int grad);
 
 /* Tuning / A-B switches (never change results): "elem_variant" 0 = default kernels, 1 = one-thread-per-dof FD
  * kernel; "chunk_elems" = elements per pipeline chunk (0 = derive from "chunk_mb", the K_e buffer budget in MiB). */

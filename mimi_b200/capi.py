@@ -32,7 +32,9 @@ SYMBOLS = [
     "mb2_add_boundary_residual_and_grad", "mb2_contact_residual_device", "mb2_contact_residual_and_grad_device",
     "mb2_contact_get_nodal", "mb2_contact_last_scalars", "mb2_contact_gap_norm", "mb2_set_mass", "mb2_set_viscosity",
     "mb2_set_rhs", "mb2_set_essential_dofs", "mb2_newton_residual_and_grad_device", "mb2_newton_residual_device", "mb2_newton_solve_gmres_device", "mb2_newton_get_solution",
-    "mb2_domain_residual_and_grad_on_mass",
+    "mb2_domain_residual_and_grad_on_mass", "mb2_get_j2_counters", "mb2_plan_partition", "mb2_plan_free", "mb2_plan_size",
+    "mb2_plan_local_elems", "mb2_plan_owned_nodes", "mb2_plan_peer", "mb2_plan_peer_send", "mb2_plan_apply", "mb2_mg_group_init",
+    "mb2_mg_group_assemble",
 ]
 
 
@@ -331,6 +333,11 @@ class Context:
     def add_domain_residual_and_grad(self, u, gf, r, A):
         self._ck(self.lib.mb2_add_domain_residual_and_grad(self.h, _dp(u), C.c_double(gf), _dp(r), _dp(A)))
 
+    def j2_counters(self, reset=True):
+        out = (C.c_uint64 * 2)()
+        self._ck(self.lib.mb2_get_j2_counters(self.h, out, int(reset)))
+        return int(out[0]), int(out[1])
+
     def domain_residual_and_grad_on_mass(self, u, gf, r, A_out):
         """r += R(u); A_out = M + gf K(u) with the mass resident on the device (mb2_set_mass): no CSR upload."""
         self._ck(self.lib.mb2_domain_residual_and_grad_on_mass(self.h, _dp(u), C.c_double(gf), _dp(r), _dp(A_out)))
@@ -431,3 +438,55 @@ class Context:
         t = C.c_double()
         self._ck(self.lib.mb2_measure_fp64_peak(self.h, int(fma), C.byref(t)))
         return t.value
+
+
+class Plan:
+    """mb2_plan_partition: the library's planner for rank `rank` of `world` (the C++ twin of partition.rank_problem)."""
+
+    def __init__(self, v_dofs, dim, NV, world, rank):
+        self.lib = load()
+        self.lib.mb2_plan_size.restype = C.c_int64
+        self.lib.mb2_plan_size.argtypes = [C.c_void_p, C.c_int]
+        v = np.ascontiguousarray(v_dofs, np.int32)
+        self.v_dofs, self.dim, self.nd = v, dim, v.shape[1] // dim
+        self.h = C.c_void_p()
+        rc = self.lib.mb2_plan_partition(_dp(v), C.c_int(dim), C.c_int(self.nd), C.c_int64(v.shape[0]), C.c_int64(NV),
+                                         C.c_int(world), C.c_int(rank), C.byref(self.h))
+        if rc:
+            raise Mb2Error("mb2_plan_partition failed (%d)" % rc)
+        self.n_compute, self.n_local, self.e0, self.n_peers, self.Nn = (int(self.lib.mb2_plan_size(self.h, k)) for k in range(5))
+        self.local_elems = np.zeros(self.n_local, np.int64)
+        self.lib.mb2_plan_local_elems(self.h, _dp(self.local_elems))
+        self.owned = np.zeros(self.Nn, np.uint8)
+        self.lib.mb2_plan_owned_nodes(self.h, _dp(self.owned))
+        self.send, self.recv = {}, {}
+        for k in range(self.n_peers):
+            peer, ns, rf, nr = C.c_int(), C.c_int64(), C.c_int64(), C.c_int64()
+            self.lib.mb2_plan_peer(self.h, k, C.byref(peer), C.byref(ns), C.byref(rf), C.byref(nr))
+            if ns.value:
+                a = np.zeros(ns.value, np.int64)
+                self.lib.mb2_plan_peer_send(self.h, k, _dp(a))
+                self.send[peer.value] = a
+            if nr.value:
+                self.recv[peer.value] = np.arange(rf.value, rf.value + nr.value)
+
+    def apply(self, ctx, nq):
+        ctx._ck(self.lib.mb2_plan_apply(ctx.h, self.h, _dp(self.v_dofs), C.c_int(nq)))
+        ctx.dim, ctx.nd, ctx.nq, ctx.tdof, ctx.NE, ctx.NV = self.dim, self.nd, nq, self.dim * self.nd, self.n_local, self.Nn * self.dim
+
+    def close(self):
+        if self.h:
+            self.lib.mb2_plan_free(self.h)
+            self.h = C.c_void_p()
+
+
+def group_init(ctxs):
+    arr = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+    ctxs[0]._ck(load().mb2_mg_group_init(arr, len(ctxs)))
+    return arr
+
+
+def group_assemble(ctxs, arr, gf, grad=True):
+    rc = load().mb2_mg_group_assemble(arr, len(ctxs), C.c_double(gf), int(grad))
+    if rc:
+        raise Mb2Error("mb2_mg_group_assemble: " + "; ".join(load().mb2_last_error(c.h).decode() for c in ctxs))

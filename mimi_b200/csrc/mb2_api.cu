@@ -85,6 +85,7 @@ int mb2_destroy(mb2_ctx* c) {
   cudaStreamSynchronize(c->stream);
   free_problem(c);
   dfree(c->d_flag);
+  dfree(c->d_cnt);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
   if (c->own_stream) cudaStreamDestroy(c->stream);
   delete c;
@@ -222,7 +223,7 @@ int mb2_set_material(mb2_ctx* c, int kind, const double* params, int nparams) {
   }
   const bool realloc_state = (kind != c->mat_kind) || (mb2::mat_state_size(kind) && !c->d_state);
   c->mat_kind = kind;
-  c->mp = m;
+  { unsigned long long* keep = c->mp.cnt; c->mp = m; c->mp.cnt = keep; }
   if (realloc_state) {
     MB2_CUDA(cudaSetDevice(c->device));
     return alloc_state(c);
@@ -264,6 +265,14 @@ int mb2_check_numeric(mb2_ctx* c) {
   return mb2::consume_flag(c);
 }
 
+int mb2_get_j2_counters(mb2_ctx* c, uint64_t* out2, int reset) {
+  CHECK_CTX(c);
+  REQUIRE(out2 && c->d_cnt, "counters are off: mb2_set_option(ctx, \"j2_counters\", 1)");
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  MB2_CUDA(cudaMemcpy(out2, c->d_cnt, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  if (reset) MB2_CUDA(cudaMemset(c->d_cnt, 0, 2 * sizeof(unsigned long long)));
+  return MB2_OK;
+}
 int mb2_state_size(mb2_ctx* c) { return c ? c->ns : 0; }
 int mb2_get_state(mb2_ctx* c, double* state) {
   CHECK_CTX(c);
@@ -496,6 +505,14 @@ int mb2_set_option(mb2_ctx* c, const char* name, int value) {
     return MB2_OK;
   }
   if (!std::strcmp(name, "fast_gemm")) { c->fast_gemm = value; return MB2_OK; }
+  if (!std::strcmp(name, "j2_counters")) {  // measurement only: atomics in the return mapping, never on in timed runs
+    if (value && !c->d_cnt) {
+      MB2_CUDA(cudaMalloc(&c->d_cnt, 2 * sizeof(unsigned long long)));
+      MB2_CUDA(cudaMemset(c->d_cnt, 0, 2 * sizeof(unsigned long long)));
+    }
+    c->mp.cnt = value ? c->d_cnt : nullptr;
+    return MB2_OK;
+  }
   if (!std::strcmp(name, "chunk_elems")) { c->chunk_elems = value; mb2::free_plan(c); return MB2_OK; }
   if (!std::strcmp(name, "chunk_mb")) { c->chunk_mb = value > 0 ? value : 2048; mb2::free_plan(c); return MB2_OK; }
   c->err = std::string("unknown option ") + name;

@@ -25,7 +25,7 @@ struct MgState {
   void* nccl_lib = nullptr;   // dlopen handle
   void* comm = nullptr;       // ncclComm_t
   cudaStream_t s_comm = nullptr;
-  cudaEvent_t ev_pack = nullptr, ev_comm = nullptr;
+  cudaEvent_t ev_pack = nullptr, ev_comm = nullptr, ev_sent = nullptr;
   bool manual = false;        // exchange driven by the host through mb2_mg_export/import (tests, foreign transports)
 };
 
@@ -94,6 +94,7 @@ struct mb2_ctx {
   double* d_Re = nullptr;  // NE x tdof
   double* d_KeT = nullptr; // NE x [row node][perturbed dof][row component]  = K_e(node + comp*nd, dof)
   int* d_flag = nullptr;   // device failure flag
+  unsigned long long* d_cnt = nullptr;  // J2 measurement counters (2), allocated by mb2_set_option("j2_counters", 1)
 
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   float last_ms[3] = {0, 0, 0};

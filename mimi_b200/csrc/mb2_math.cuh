@@ -24,6 +24,9 @@ struct MatP {
   double hp[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   double dt = 0, heat_fraction = 0, density = 0, specific_heat = 0, T0 = 0;
   int* flag = nullptr;  // device failure flag: 1 = root not bracketed, 2 = scalar solve did not converge
+  // optional measurement counters (mb2_set_option "j2_counters"): [0] return mappings run (= yielded stress evaluations),
+  // [1] hardening-law evaluations inside their bracketed Newton solves (ScalarSolve residual calls)
+  unsigned long long* cnt = nullptr;
 };
 
 // per-quadrature-point history doubles: J2Linear = plastic_strain[9], beta[9], accumulated_plastic_strain
@@ -335,6 +338,10 @@ static __device__ __noinline__ double j2_scalar_solve(const MatP& m, const RC& c
     converged = (fabs(delta_x) < xtol) || (fabs(fval) < rtol);
     if (fval < 0) xl = x; else xh = x;
     ++it;
+  }
+  if (m.cnt) {
+    atomicAdd(&m.cnt[0], 1ULL);
+    atomicAdd(&m.cnt[1], (unsigned long long)(it + 3));  // two bracket residuals, the first AD residual, one per iteration
   }
   return x;
 }

@@ -75,6 +75,7 @@ static MgState* state(mb2_ctx* c) {
     cudaStreamCreateWithPriority(&c->mg->s_comm, cudaStreamNonBlocking, hi);
     cudaEventCreateWithFlags(&c->mg->ev_pack, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->mg->ev_comm, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->mg->ev_sent, cudaEventDisableTiming);
   }
   return c->mg;
 }
@@ -98,6 +99,7 @@ void free_mg(mb2_ctx* c) {
   if (mg->s_comm) cudaStreamDestroy(mg->s_comm);
   if (mg->ev_pack) cudaEventDestroy(mg->ev_pack);
   if (mg->ev_comm) cudaEventDestroy(mg->ev_comm);
+  if (mg->ev_sent) cudaEventDestroy(mg->ev_sent);
   delete mg;
   c->mg = nullptr;
 }
@@ -304,6 +306,89 @@ int mb2_mg_finish(mb2_ctx* c, double grad_factor, int grad) {
   if (rc) return rc;
   MB2_CUDA(cudaSetDevice(c->device));
   return assemble_finish(c, grad_factor, grad != 0, nullptr);
+}
+
+/* ---- one process, several GPUs: the contexts of all ranks are driven together and the packed element matrices travel by
+ * cudaMemcpyPeerAsync (NVLink peer-to-peer when the devices allow it; the same device works too, which is how the
+ * single-GPU test suite covers this path). ctxs[r] = the context of rank r, set up with mb2_plan_apply / mb2_set_partition.
+ * grad != 0: r += R(u), A += gf K(u) on every rank's resident arrays; 0: residual only. */
+int mb2_mg_group_init(mb2_ctx** ctxs, int n) {
+  if (!ctxs || n < 1) return MB2_ERR_ARG;
+  for (int a = 0; a < n; a++) {
+    mb2_ctx* c = ctxs[a];
+    MG_CHECK_CTX(c);
+    MG_REQUIRE(n == 1 || c->mg, "call mb2_set_partition (mb2_plan_apply) on every context first");
+    if (c->mg) { c->mg->manual = false; c->mg->rank = a; c->mg->world = n; }
+    for (int b = 0; b < n; b++) {
+      if (ctxs[b]->device == c->device) continue;
+      int can = 0;
+      MB2_CUDA(cudaDeviceCanAccessPeer(&can, c->device, ctxs[b]->device));
+      if (!can) continue;                      // cudaMemcpyPeerAsync then stages through the host
+      MB2_CUDA(cudaSetDevice(c->device));
+      cudaError_t e = cudaDeviceEnablePeerAccess(ctxs[b]->device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) MB2_CUDA(e);
+      (void)cudaGetLastError();
+    }
+  }
+  return MB2_OK;
+}
+
+int mb2_mg_group_assemble(mb2_ctx** ctxs, int n, double grad_factor, int grad) {
+  if (!ctxs || n < 1) return MB2_ERR_ARG;
+  const bool g = grad != 0;
+  for (int a = 0; a < n; a++) {  // stage 1 on every rank: own elements, packs
+    mb2_ctx* c = ctxs[a];
+    MG_CHECK_CTX(c);
+    MB2_CUDA(cudaSetDevice(c->device));
+    int rc = assemble_begin(c, grad_factor, g, nullptr, nullptr);
+    if (rc) return rc;
+  }
+  if (n > 1) {
+    // sends, issued on the sender's communication stream after its packs
+    for (int a = 0; a < n; a++) {
+      mb2_ctx* c = ctxs[a];
+      MgState* mg = c->mg;
+      MB2_CUDA(cudaSetDevice(c->device));
+      MB2_CUDA(cudaStreamWaitEvent(mg->s_comm, mg->ev_pack, 0));
+      const size_t ked = ke_doubles(c);
+      for (auto& p : mg->peers) {
+        const size_t ns = p.send_elems.size();
+        if (!ns) continue;
+        if (p.peer < 0 || p.peer >= n) { c->err = "send peer outside the group"; return MB2_ERR_ARG; }
+        mb2_ctx* d = ctxs[p.peer];
+        const MgPeer* q = nullptr;
+        for (auto& x : d->mg->peers)
+          if (x.peer == a) q = &x;
+        if (!q || (size_t)q->n_recv != ns) { c->err = "send / receive lists of the group do not match"; return MB2_ERR_ARG; }
+        // the receiver's buffers are free once ITS packs of this step are queued (its previous ghost gather precedes them)
+        MB2_CUDA(cudaStreamWaitEvent(mg->s_comm, d->mg->ev_pack, 0));
+        if (g) {
+          double* ghost = ghost_ke_buffer(d);
+          if (!ghost) { c->err = "receiver has no ghost buffer"; return MB2_ERR_ARG; }
+          MB2_CUDA(cudaMemcpyPeerAsync(ghost + (size_t)(q->recv_first - d->n_compute) * ked, d->device, p.d_send, c->device,
+                                       sizeof(double) * ns * ked, mg->s_comm));
+        }
+        MB2_CUDA(cudaMemcpyPeerAsync(d->d_Re + (size_t)q->recv_first * d->tdof, d->device, p.d_send + ns * ked, c->device,
+                                     sizeof(double) * ns * c->tdof, mg->s_comm));
+      }
+      MB2_CUDA(cudaEventRecord(mg->ev_sent, mg->s_comm));  // everything this rank sends has left
+    }
+    // every rank: wait for what it receives, then (ev_comm) both its sends and its receives are complete
+    for (int a = 0; a < n; a++) {
+      mb2_ctx* c = ctxs[a];
+      MB2_CUDA(cudaSetDevice(c->device));
+      for (auto& p : c->mg->peers)
+        if (p.n_recv) MB2_CUDA(cudaStreamWaitEvent(c->mg->s_comm, ctxs[p.peer]->mg->ev_sent, 0));
+      MB2_CUDA(cudaEventRecord(c->mg->ev_comm, c->mg->s_comm));
+    }
+  }
+  for (int a = 0; a < n; a++) {  // stage 2: ghost gather, residual gather, join
+    mb2_ctx* c = ctxs[a];
+    MB2_CUDA(cudaSetDevice(c->device));
+    int rc = assemble_finish(c, grad_factor, g, nullptr);
+    if (rc) return rc;
+  }
+  return MB2_OK;
 }
 
 /* doubles per packed element matrix (nd * KP) */

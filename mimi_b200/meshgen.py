@@ -396,3 +396,36 @@ def top_face_tables(M, spans, quad_points=None):
         dN[f, :, 1] = np.einsum("xi,yj->yxji", Nx, dNy).reshape(nq, ndf)
     w = np.tile(np.outer(gw, gw).reshape(1, nq), (NF, 1))
     return dict(v_dofs=fv, N=N, dN_dxi=dN, w=w, NF=NF, ndf=ndf, nqf=nq)
+
+
+def top_face_tables_from_grid(p, spans_xy, knots, gtop, quad_points=None):
+    """top_face_tables for a box whose connectivity is not held as a whole (partitioned runs: every rank evaluates all
+    contact faces): gtop[i, j] = node id of control point (i, j) of the top control layer (patch_node_grid(ncp)[:, :, -1]).
+    Same layout, face order (i fastest) and values as top_face_tables."""
+    n0, n1 = spans_xy
+    nq1 = quad_points or (p + 2)
+    gx, gw = np.polynomial.legendre.leggauss(nq1)
+    gx, gw = 0.5 * (gx + 1.0), 0.5 * gw
+    nd1 = p + 1
+    ej, ei = np.meshgrid(np.arange(n1), np.arange(n0), indexing="ij")
+    ei, ej = ei.ravel(), ej.ravel()                     # i fastest
+    NF, ndf, nq = len(ei), nd1 * nd1, nq1 * nq1
+    nodes = np.empty((NF, ndf), np.int64)
+    a = 0
+    for jj in range(nd1):
+        for ii in range(nd1):
+            nodes[:, a] = gtop[ei + ii, ej + jj]
+            a += 1
+    fv = np.concatenate([3 * nodes + c for c in range(3)], 1).astype(np.int32)
+    bx = [bspline_basis_1d(p, knots[0], s_, gx) for s_ in range(n0)]
+    by = [bspline_basis_1d(p, knots[1], s_, gx) for s_ in range(n1)]
+    N = np.empty((NF, nq, ndf))
+    dN = np.empty((NF, nq, 2, ndf))
+    for f in range(NF):
+        Nx, dNx = bx[ei[f]]
+        Ny, dNy = by[ej[f]]
+        N[f] = np.einsum("xi,yj->yxji", Nx, Ny).reshape(nq, ndf)
+        dN[f, :, 0] = np.einsum("xi,yj->yxji", dNx, Ny).reshape(nq, ndf)
+        dN[f, :, 1] = np.einsum("xi,yj->yxji", Nx, dNy).reshape(nq, ndf)
+    w = np.tile(np.outer(gw, gw).reshape(1, nq), (NF, 1))
+    return dict(v_dofs=fv, N=N, dN_dxi=dN, w=w, NF=NF, ndf=ndf, nqf=nq)

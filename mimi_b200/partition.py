@@ -106,7 +106,7 @@ def slab_rank_problem(p: int, spans, world: int, rank: int, lengths=None) -> dic
     return dict(rank=rank, world=world, e0=e0, e1=e0 + n_compute, n_compute=n_compute,
                 local_elems=np.arange(e0, e0 + len(el_ijk)), v_dofs=v_dofs, owned=owned, send=send, recv=recv,
                 el_ijk=el_ijk, knots=kvs, ncp=np.array(ncp, np.int32), x_ref=x.ravel(), NV=3 * Nn, Nn=Nn, nd=nd, p=p,
-                NE=len(el_ijk), NE_global=n_layer * n2)
+                NE=len(el_ijk), NE_global=n_layer * n2, node_grid_top=g[:, :, -1].copy())
 
 
 # ---------------------------------------------------------------------------------------------------

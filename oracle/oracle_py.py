@@ -255,7 +255,7 @@ def load_dump(d):
         out["node_w"] = rd("node_w.f64", np.float64)
     out["t_meta"] = rd("t_meta.i32", np.int32)
     out["t_v_dofs"] = rd("t_v_dofs.i32", np.int32)
-    for k in ("x_ref", "u", "r", "r2", "mass", "bodyforce", "viscform", "mass_b200", "viscform_b200", "bodyforce_b200", "rhs_b200", "rhs_bf_traction", "t_w", "t_detW", "t_N", "A", "r_b", "A_b"):
+    for k in ("x_ref", "u", "r", "r2", "mass", "bodyforce", "viscform", "mass_b200", "viscform_b200", "bodyforce_b200", "rhs_b200", "rhs_bf_traction", "t_w", "t_detW", "t_N", "A", "r_b", "A_b", "r_mg", "r2_mg", "A_mg"):
         out[k] = rd(k + ".f64", np.float64)
     return out
 
@@ -267,12 +267,12 @@ def have_ref_b200():
     return os.path.exists(REF_B200_BIN) and os.access(REF_B200_BIN, os.X_OK)
 
 
-def run_ref_dump(mesh, elevate, refine, material, outdir, gf=1.0, nthreads=1, u_file="-", lite=False, binary=None):
+def run_ref_dump(mesh, elevate, refine, material, outdir, gf=1.0, nthreads=1, u_file="-", lite=False, binary=None, env=None):
     os.makedirs(outdir, exist_ok=True)
     cmd = [binary or REF_BIN, "dump", mesh, str(elevate), str(refine), material, str(nthreads), repr(gf), u_file, outdir]
     if lite:
         cmd.append("lite")
-    subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+    subprocess.check_call(cmd, stdout=subprocess.DEVNULL, env=None if env is None else {**os.environ, **env})
     return load_dump(outdir)
 
 

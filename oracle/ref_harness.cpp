@@ -46,7 +46,9 @@
 // by the adapter a maintainer would add (adapter/b200_nonlinear_solid.hpp -> C ABI of libmimi_b200.so). Everything
 // else in this file -- mesh, FE space, PrecomputedData, materials, mass form, the dumps -- stays the reference's.
 #ifdef MIMI_REF_USE_B200
+#include "b200_gmres_solver.hpp"
 #include "b200_mortar_contact.hpp"
+#include "b200_multigpu.hpp"
 #include "b200_nonlinear_solid.hpp"
 using DomainIntegrator = mimi::integrators::B200NonlinearSolid;
 #define MIMI_REF_B200_BODY , mimi::integrators::B200RigidBody
@@ -641,6 +643,29 @@ int main(int argc, char** argv) {
     s.integ->AddDomainResidualAndGrad(u, gf, r2, A);
     dump(out, "r2.f64", r2.GetData(), (size_t)NV);
     dump(out, "A.f64", A.GetData(), (size_t)nnz);
+#ifdef MIMI_REF_USE_B200
+    if (const char* ng = std::getenv("MIMI_REF_B200_GPUS")) {
+      // the same two calls through adapter/b200_multigpu.hpp: N contexts in this process (devices round-robin over the
+      // visible GPUs), partition planned by the library, element matrices exchanged GPU to GPU
+      const char* nd_env = std::getenv("MIMI_REF_B200_NDEV");   // visible GPUs (the harness does not link the CUDA runtime)
+      const int ndev = nd_env ? std::atoi(nd_env) : 1;
+      std::vector<int> devs;
+      for (int i = 0; i < std::atoi(ng); ++i) devs.push_back(i % std::max(ndev, 1));
+      auto mg = std::make_shared<mimi::integrators::B200MultiGpuNonlinearSolid>("mg", s.mat, s.pre, devs);
+      mg->dt_ = s.integ->dt_;
+      mg->Prepare();
+      mfem::Vector rm(NV), rm2(NV);
+      rm = 0.0;
+      mg->AddDomainResidual(u, rm);
+      dump(out, "r_mg.f64", rm.GetData(), (size_t)NV);
+      mfem::SparseMatrix Am(s.mass->SpMat());
+      rm2 = 0.0;
+      mg->AddDomainResidualAndGrad(u, gf, rm2, Am);
+      mg->AddDomainResidualAndGrad(u, gf, rm2, Am);   // adds into: twice
+      dump(out, "r2_mg.f64", rm2.GetData(), (size_t)NV);
+      dump(out, "A_mg.f64", Am.GetData(), (size_t)nnz);
+    }
+#endif
     if (material == "j2linear" || material.rfind("j2", 0) == 0) {
       s.integ->DomainPostTimeAdvance(u);
       // history layout: every state matrix in a 9-double slot (column-major dim x dim in front), then the scalars;

