@@ -379,6 +379,7 @@ def gpu_arm(args):
     stream = torch.cuda.Stream()            # the library launches on this stream, so torch events see its work
     ctx = capi.Context(local, stream=stream.cuda_stream)
     ctx.set_option("elem_variant", args.variant)
+    ctx.set_option("park_acc", args.park)
     fast = args.tangent == "analytic"
     if fast:
         ctx.set_option("tangent_mode", 1)          # MB2_TANGENT_ANALYTIC (secondary line: the headline stays the parity mode)
@@ -630,6 +631,7 @@ def c5_arm(args):
     n, p = args.n, 2
     stream = torch.cuda.Stream()
     ctx = capi.Context(local, stream=stream.cuda_stream)
+    ctx.set_option("park_acc", args.park)
     t0 = time.time()
     nq1 = p + 2
     spans = (n, n, n * world)          # weak scaling: n^3 elements (and their history variables) per GPU, z-slabs
@@ -715,6 +717,34 @@ def c5_arm(args):
     n_eval = float(NE) * nq * (tdof + 1)
     yielded_fraction = n_yield / n_eval
     hard_per_yield = n_hard / max(n_yield, 1)
+    face_qp = F["NF"] * F["nqf"]
+    ms_per_step = dev_ms / args.steps
+    total_qp = float(NE) * nq * world + face_qp
+    # end to end: host-buffer entries (domain + contact) with pinned buffers, on the same displacement and history as the timed steps
+    # (before the time-step loop below moves the history on)
+    e2e = None
+    if not args.no_e2e:
+        u_h = torch.from_numpy(np.ascontiguousarray(1.5 * u)).pin_memory()
+        r_h = torch.zeros(M["NV"], dtype=torch.float64).pin_memory()
+        A_h = torch.zeros(nnz, dtype=torch.float64).pin_memory()
+        up, rp, Ap = (C_void(t) for t in (u_h, r_h, A_h))
+        one = capi.C.c_double(1.0)
+
+        def host_step():
+            ctx._ck(ctx.lib.mb2_add_domain_residual_and_grad(ctx.h, up, one, rp, Ap))
+            ctx._ck(ctx.lib.mb2_add_boundary_residual_and_grad(ctx.h, up, one, rp, Ap))
+
+        host_step()
+        barrier()
+        t1 = time.perf_counter()
+        k2 = max(1, min(args.steps, 3))
+        for _ in range(k2):
+            host_step()
+        barrier()
+        e2e_s = maxr((time.perf_counter() - t1) / k2)
+        e2e = {"value": total_qp / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * (4 * M["NV"] + nnz),
+               "d2h_bytes_per_step": 8 * (2 * M["NV"] + nnz), "ms_per_step": e2e_s * 1e3, "steps": k2,
+               "call": "mb2_add_domain_residual_and_grad + mb2_add_boundary_residual_and_grad with pinned host buffers"}
     # ---- implicit-dynamics time steps: 2 Newton iterations (assembly + contact, two line-search residuals each) and the
     # history commit per step, the displacement growing from step to step (assembly share of a generalized-alpha step)
     n_ts = max(2, min(args.steps, 4))
@@ -742,54 +772,33 @@ def c5_arm(args):
     torch.cuda.synchronize()
     pta_ms = float(ea.elapsed_time(eb))
     gap, area, pr = ctx.contact_nodal()
-    face_qp = F["NF"] * F["nqf"]
-    ms_per_step = dev_ms / args.steps
-    total_qp = float(NE) * nq * world + face_qp
     value = total_qp / (ms_per_step * 1e-3)
-    # end to end: host-buffer entries (domain + contact) with pinned buffers
-    e2e = None
-    if not args.no_e2e:
-        u_h = torch.from_numpy(np.ascontiguousarray(1.5 * u)).pin_memory()
-        r_h = torch.zeros(M["NV"], dtype=torch.float64).pin_memory()
-        A_h = torch.zeros(nnz, dtype=torch.float64).pin_memory()
-        up, rp, Ap = (C_void(t) for t in (u_h, r_h, A_h))
-        one = capi.C.c_double(1.0)
-
-        def host_step():
-            ctx._ck(ctx.lib.mb2_add_domain_residual_and_grad(ctx.h, up, one, rp, Ap))
-            ctx._ck(ctx.lib.mb2_add_boundary_residual_and_grad(ctx.h, up, one, rp, Ap))
-
-        host_step()
-        barrier()
-        t1 = time.perf_counter()
-        k2 = max(1, min(args.steps, 3))
-        for _ in range(k2):
-            host_step()
-        barrier()
-        e2e_s = maxr((time.perf_counter() - t1) / k2)
-        e2e = {"value": total_qp / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * (4 * M["NV"] + nnz),
-               "d2h_bytes_per_step": 8 * (2 * M["NV"] + nnz), "ms_per_step": e2e_s * 1e3, "steps": k2,
-               "call": "mb2_add_domain_residual_and_grad + mb2_add_boundary_residual_and_grad with pinned host buffers"}
     peak_nofma = ctx.measure_fp64_peak(0)
     peak_fma = ctx.measure_fp64_peak(1)
     el_ms = float(np.mean(t_el))
-    # ---- executed flops of the J2 element kernel: FP64 thread instructions per quadrature point from the committed ncu capture
-    # (profiles/j2_flops.json: DADD + DMUL + 2 DFMA of one launch, with the yielded fraction and hardening evaluations per return
-    # mapping it was taken at); valid for this run if the live counters agree with the capture's
+    # ---- executed flops of the J2 element kernel. The return mapping runs a data-dependent number of hardening-law evaluations,
+    # so the count is a calibrated linear model (profiles/j2_flops.json, written by scripts/ncu_j2_flops.py from an ncu capture:
+    # FP64 thread instructions DADD + DMUL + 2 DFMA, split by source line into a fixed part per qp and a part per hardening
+    # evaluation) evaluated at THIS run's device counters (return mappings, hardening evaluations of one assembly)
     roof = {"bound": "fp64", "kernel": "element_fd_kernel<3,27,64,J2>", "achieved": None, "peak": None, "unit": "TFLOP/s", "frac": None,
             "traffic": None, "kernel_ms": el_ms, "yielded_fraction": yielded_fraction, "hardening_evals_per_return_mapping": hard_per_yield,
-            "stress_evaluations_per_assembly": n_eval}
+            "stress_evaluations_per_assembly": n_eval, "park_acc": args.park}
     try:
         Jf = json.load(open(os.path.join(ROOT, "profiles", "j2_flops.json")))
-        ok = abs(Jf["yielded_fraction"] - yielded_fraction) <= 0.02 and abs(Jf["hardening_evals_per_return_mapping"] - hard_per_yield) <= 0.05 * hard_per_yield
-        flop_qp = Jf["flop_per_qp"]
-        mix = Jf["fused_flop_share"]          # share of the flops issued as DFMA (libdevice pow / log / divisions)
+        evals_qp = n_eval * yielded_fraction * hard_per_yield / (float(NE) * nq)
+        f_fix, f_var = Jf["flop_fixed_per_qp"], Jf["flop_per_hardening_eval"] * evals_qp
+        flop_qp = f_fix + f_var
+        # share of the flops issued as DFMA (libdevice pow / log / divisions are fused whatever -fmad says)
+        mix = (f_fix * Jf["fused_share_fixed"] + f_var * Jf["fused_share_variable"]) / flop_qp
         peak_mix = 1.0 / ((1.0 - mix) / peak_nofma + mix / peak_fma)
         achieved = float(NE) * nq / (el_ms * 1e-3) * flop_qp / 1e12
-        roof.update(achieved=achieved if ok else None, peak=peak_mix, frac=(achieved / peak_mix) if ok else None,
-                    flop_per_qp_executed=flop_qp, peak_nofma=peak_nofma, peak_fma=peak_fma,
-                    peak_source="harmonic mix of the measured DMUL+DADD and DFMA peaks at the capture's fused share %.3f" % mix,
-                    flop_source=Jf.get("capture"), capture_matches_run=bool(ok))
+        roof.update(achieved=achieved, peak=peak_mix, frac=achieved / peak_mix,
+                    flop_per_qp_executed=flop_qp, hardening_evals_per_qp=evals_qp, fused_flop_share=mix,
+                    peak_nofma=peak_nofma, peak_fma=peak_fma,
+                    peak_source="harmonic mix of the DMUL+DADD and DFMA peaks measured in this run (mb2_measure_fp64_peak) at the "
+                                "kernel's fused flop share %.3f" % mix,
+                    flop_source="profiles/j2_flops.json: %.0f flop/qp fixed + %.1f flop per hardening evaluation x %.1f evaluations/qp "
+                                "counted by this run; calibrated on %s" % (f_fix, Jf["flop_per_hardening_eval"], evals_qp, Jf.get("capture")))
     except (OSError, KeyError, ValueError):
         roof["note"] = "no profiles/j2_flops.json: data-dependent flop count not calibrated"
     if rank == 0:
@@ -863,6 +872,7 @@ def main():
     ap.add_argument("--material", default="neohookean", choices=["neohookean", "stvk"])
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
                     help="c4: multi-patch p=3 StVK beam, 5e5 elements per GPU (config 4); c5: J2 + contact secondary workload (1 GPU)")
+    ap.add_argument("--park", type=int, default=1, help="A/B: FD kernels park their accumulators in tensor memory during phase 1 (mb2_set_option park_acc; p=2: plastic materials, p=3: all)")
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     ap.add_argument("--tangent", default="parity", choices=["parity", "analytic"],
                     help="analytic = MB2_TANGENT_ANALYTIC fast mode (secondary line; p=2, neohookean / stvk)")

@@ -171,6 +171,58 @@ __global__ void __launch_bounds__(ElemCfg<DIM, ND, NQ>::NT, MINB) element_kernel
 // but needed more wavefronts, with and without warp-specialised producer / consumer warps, measured 7 - 9 % SLOWER
 // and were removed again.
 // ---------------------------------------------------------------------------------------------
+// Tensor memory as a parking place for the phase-2 accumulators (plastic materials): their return mapping needs the
+// registers the 28 FP64 accumulators of a thread occupy, and a spill goes to local memory = through an L1 that the 2 x 85 KB
+// of shared memory leave 56 KB of. TMEM (256 KB per SM, unused by a kernel without tcgen05.mma) takes them instead:
+// tcgen05.st before phase 1, tcgen05.ld after it, 32 lanes x N columns per warp (shape 32x32b: lane = thread).
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, int ncols) {  // one whole warp
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_slot)),
+               "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, int ncols) {  // the same warp
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]),
+               "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t* r) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+// N doubles of a thread <-> 2 N consecutive columns of its TMEM lane, 8 columns per instruction
+template <int N>
+__device__ __forceinline__ void tmem_park(uint32_t taddr, const double* v) {
+  static_assert(N % 4 == 0, "whole x8 groups");
+#pragma unroll
+  for (int g = 0; g < N / 4; g++) {
+    uint32_t r[8];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      r[2 * i] = (uint32_t)__double2loint(v[4 * g + i]);
+      r[2 * i + 1] = (uint32_t)__double2hiint(v[4 * g + i]);
+    }
+    tmem_st8(taddr + 8 * g, r);
+  }
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void tmem_unpark(uint32_t taddr, double* v) {
+  uint32_t r[N / 4][8];
+#pragma unroll
+  for (int g = 0; g < N / 4; g++) tmem_ld8(taddr + 8 * g, r[g]);
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int g = 0; g < N / 4; g++)
+#pragma unroll
+    for (int i = 0; i < 4; i++) v[4 * g + i] = __hiloint2double((int)r[g][2 * i + 1], (int)r[g][2 * i]);
+}
+
 template <int DIM, int ND, int NQ>
 struct Elem2Cfg {
   static constexpr int TD = DIM * ND;
@@ -200,8 +252,8 @@ struct Elem2Cfg {
   static_assert(NBP % 4 == 0 && OFF_SB % 2 == 0 && (QC * DIM * NBP) % 2 == 0, "b buffer alignment");
 };
 
-template <int DIM, int ND, int NQ, int MAT>
-__global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
+template <int DIM, int ND, int NQ, int MAT, bool PARK>
+__global__ void __launch_bounds__(256, 2) element_fd_kernel(const __grid_constant__ ElemArgs g) {
   using Cfg = Elem2Cfg<DIM, ND, NQ>;
   constexpr int TD = Cfg::TD, DD = Cfg::DD, NM = Cfg::NM, NT = Cfg::NT, QC = Cfg::QC, NCH = Cfg::NCH, NDP = Cfg::NDP,
                 NB = Cfg::NB, NBP = Cfg::NBP, TI = Cfg::TI, TC = Cfg::TC, LI = Cfg::LI, LC = Cfg::LC, KP = Cfg::KP,
@@ -235,6 +287,19 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
   for (int idx = t; idx < 2 * QC * DIM * NBP; idx += NT) sb[idx] = 0.0;
   if (t < DIM)
     for (int i = ND; i < NDP; i++) sue[t * NDP + i] = 0.0;
+  // PARK: 2 TI TC columns per warp; warps w and w + 4 share the 32 TMEM lanes of sub-partition w % 4
+  constexpr int PCOLS = 2 * TI * TC;
+  constexpr int TMEM_COLS = (NT / 128) * PCOLS <= 32 ? 32 : ((NT / 128) * PCOLS <= 64 ? 64 : ((NT / 128) * PCOLS <= 128 ? 128 : 256));
+  static_assert(!PARK || ((TI * TC) % 4 == 0 && (NT / 128) * PCOLS <= 256 && NT % 128 == 0), "accumulator tile does not map to TMEM");
+  __shared__ uint32_t s_tmem;
+  uint32_t tpark = 0;
+  if (PARK) {
+    if (warp == 0) tmem_alloc(&s_tmem, TMEM_COLS);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    tpark = s_tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * PCOLS);
+  }
 
   for (int64_t e = g.e0 + blockIdx.x; e < g.e1; e += gridDim.x) {
     // ---- stage: gathered dofs (Vector::GetSubVector), weights, dN_dX rows padded to NDP
@@ -268,15 +333,19 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
       up1 = orig + h;
     }
     double R[TI][TC];
+    if (!PARK) {
 #pragma unroll
-    for (int x = 0; x < TI; x++)
+      for (int x = 0; x < TI; x++)
 #pragma unroll
-      for (int y = 0; y < TC; y++) R[x][y] = 0.0;
+        for (int y = 0; y < TC; y++) R[x][y] = 0.0;
+    }
     __syncthreads();
 
 #pragma unroll 1
     for (int ch = 0; ch < NCH; ch++) {
       double* sbc = sb + (ch & 1) * (QC * DIM * NBP);
+      // PARK: the accumulators sit in tensor memory while phase 1 runs (whole warps: the instructions are .aligned)
+      if (PARK && ch > 0) tmem_park<TI * TC>(tpark, &R[0][0]);
       // ---- phase 1: stress of (m1, q1)
       const int q1 = ch * QC + qs1;
       if (act1 && q1 < NQ) {
@@ -320,6 +389,16 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
           for (int j = 0; j < DIM; j++) o[k * NBP + j] = aq * P[j + DIM * k];
       }
       __syncthreads();
+      if (PARK) {
+        if (ch > 0) {
+          tmem_unpark<TI * TC>(tpark, &R[0][0]);
+        } else {
+#pragma unroll
+          for (int x = 0; x < TI; x++)
+#pragma unroll
+            for (int y = 0; y < TC; y++) R[x][y] = 0.0;
+        }
+      }
       // ---- phase 2: R(i, col) += dN(q; i, k) * b(q; col, k), q then k ascending (AddMult_a_ABt, densemat.cpp:3002-3015)
       if (act2) {
 #pragma unroll
@@ -401,6 +480,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_kernel(const ElemArgs g) {
     }
     __syncthreads();
   }
+  if (PARK && warp == 0) tmem_dealloc(s_tmem, TMEM_COLS);
 #undef MB2_ROW2
 }
 
@@ -467,8 +547,8 @@ struct Elem3Cfg {
   static_assert((QC * DIM * ND) % 2 == 0 && (NQ * DD) % 2 == 1 || true, "alignment");
 };
 
-template <int DIM, int ND, int NQ, int MAT, int KS>
-__global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs g) {
+template <int DIM, int ND, int NQ, int MAT, int KS, bool PARK>
+__global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const __grid_constant__ ElemArgs g) {
   using Cfg = Elem3Cfg<DIM, ND, NQ, KS>;
   constexpr int TD = Cfg::TD, DD = Cfg::DD, MP = Cfg::MP, NM = Cfg::NM, NT = Cfg::NT, QC = Cfg::QC, NCH = Cfg::NCH,
                 NB = Cfg::NB, NBP = Cfg::NBP, TI = Cfg::TI, TC = Cfg::TC, LI = Cfg::LI, KP = Cfg::KP,
@@ -508,7 +588,24 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
   for (int idx = t; idx < 2 * QC * DIM * NBP; idx += NT) sb[idx] = 0.0;
   if (t < TD) sue[t] = g.u[g.vdofs[e * TD + t]];  // [c][a] = component-major gather (Vector::GetSubVector)
   for (int q = t; q < NQ; q += NT) swd[q] = g.wdetJ[e * NQ + q];
+  // PARK: the TI x TC accumulators of a thread sit in tensor memory while phase 1 runs (see tmem_park above): phase 1 then
+  // has the registers to keep a batch of shared-memory loads in flight (its F-row product waited on them one by one,
+  // profiles/r01_elem_p3_split_v2_summary.txt). 2 TI TC = 80 columns per warp, two warps per TMEM sub-partition, 256 columns
+  // per CTA: the two resident CTAs take the SM's 512 columns.
+  constexpr int PCOLS = 2 * TI * TC;
+  constexpr int TMEM_COLS = (NT / 128) * PCOLS <= 32 ? 32 : ((NT / 128) * PCOLS <= 64 ? 64 : ((NT / 128) * PCOLS <= 128 ? 128 : 256));
+  static_assert(!PARK || ((TI * TC) % 4 == 0 && (NT / 128) * PCOLS <= 256 && NT % 128 == 0), "accumulator tile does not map to TMEM");
+  __shared__ uint32_t s_tmem;
+  uint32_t tpark = 0;
+  if (PARK) {
+    if (warp == 0) tmem_alloc(&s_tmem, TMEM_COLS);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
   __syncthreads();
+  if (PARK) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    tpark = s_tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * PCOLS);
+  }
   constexpr uint32_t CHUNK_BYTES = QC * TD * sizeof(double);
   if (t == 0) {
     const int nq0 = (NQ < QC) ? NQ : QC;
@@ -550,16 +647,19 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
     up1 = orig + h;
   }
   double R[TI][TC];
+  if (!PARK) {
 #pragma unroll
-  for (int x = 0; x < TI; x++)
+    for (int x = 0; x < TI; x++)
 #pragma unroll
-    for (int y = 0; y < TC; y++) R[x][y] = 0.0;
+      for (int y = 0; y < TC; y++) R[x][y] = 0.0;
+  }
   __syncthreads();
 
 #pragma unroll 1
   for (int ch = 0; ch < NCH; ch++) {
     const double* dNc = sdN + (ch & 1) * (QC * DIM * ND);
     double* sbc = sb + (ch & 1) * (QC * DIM * NBP);
+    if (PARK && ch > 0) tmem_park<TI * TC>(tpark, &R[0][0]);
     mbar_wait(&bar[ch & 1], (uint32_t)((ch >> 1) & 1));
     // ---- phase 1
     const int q1 = ch * QC + qs1;
@@ -609,6 +709,16 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
                   (uint32_t)(nqn * TD * sizeof(double)), &bar[(ch + 1) & 1]);
     }
     (void)CHUNK_BYTES;
+    if (PARK) {
+      if (ch > 0) {
+        tmem_unpark<TI * TC>(tpark, &R[0][0]);
+      } else {
+#pragma unroll
+        for (int x = 0; x < TI; x++)
+#pragma unroll
+          for (int y = 0; y < TC; y++) R[x][y] = 0.0;
+      }
+    }
     // ---- phase 2
 #pragma unroll
     for (int qs = 0; qs < QC; qs++) {
@@ -662,6 +772,7 @@ __global__ void __launch_bounds__(256, 2) element_fd_split_kernel(const ElemArgs
         out[(int64_t)MB2_ROW(x) * KP + mg * DIM + j] = (R[x][y] - sRb[MB2_ROW(x) + j * ND]) * hinv;
     }
   }
+  if (PARK && warp == 0) tmem_dealloc(s_tmem, TMEM_COLS);  // every warp's last tcgen05.ld precedes the __syncthreads above
 #undef MB2_ROW
 }
 
@@ -953,7 +1064,9 @@ static int launch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
 template <int DIM, int ND, int NQ, int MAT>
 static int launch_element_fd(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   using Cfg = Elem2Cfg<DIM, ND, NQ>;
-  auto kern = element_fd_kernel<DIM, ND, NQ, MAT>;
+  // plastic materials park the accumulators in tensor memory during the return mapping (option park_acc, default on)
+  auto kern = (MAT >= MAT_J2LINEAR && c->park_acc) ? element_fd_kernel<DIM, ND, NQ, MAT, (MAT >= MAT_J2LINEAR)>
+                                                   : element_fd_kernel<DIM, ND, NQ, MAT, false>;
   MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
   int per_sm = 0;
   MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::NT, Cfg::SMEM_BYTES));
@@ -970,7 +1083,7 @@ static int launch_element_fd(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
 template <int DIM, int ND, int NQ, int MAT, int KS>
 static int launch_element_fd_split(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   using Cfg = Elem3Cfg<DIM, ND, NQ, KS>;
-  auto kern = element_fd_split_kernel<DIM, ND, NQ, MAT, KS>;
+  auto kern = c->park_acc ? element_fd_split_kernel<DIM, ND, NQ, MAT, KS, true> : element_fd_split_kernel<DIM, ND, NQ, MAT, KS, false>;
   MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
   const int64_t grid = (a.e1 - a.e0) * KS;  // the KS parts of an element are adjacent: they share its table in L2
   kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, st>>>(a);

@@ -46,6 +46,7 @@ struct mb2_ctx {
   void* plan = nullptr;     // chunk pipeline state (mb2_assembly.cu)
   bool last_grad = false;
   int elem_variant = 0;  // 0 = default kernels, 1 = force the one-thread-per-dof FD kernel (A/B tests)
+  int park_acc = 1;      // plastic materials: FD kernel parks its accumulators in tensor memory during phase 1 (0 = spill, A/B)
   int tangent_mode = 0;  // MB2_TANGENT_FD_PARITY | MB2_TANGENT_ANALYTIC (mb2_fast.cu)
   int fast_gemm = 0;     // analytic mode, p = 2 hexahedra: 0 = FP64 tensor cores (DMMA), 1 = CUDA-core DFMA tiles
   int mat_kind = -1;

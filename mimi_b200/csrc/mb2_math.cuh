@@ -297,7 +297,7 @@ __device__ __forceinline__ AD1 j2_residual_ad(const MatP& m, const RC& c, double
   return a;
 }
 // mimi::solvers::ScalarSolve (src/mimi/solvers/newton.hpp:53-169), x0 = 0; failures raise the device flag
-static __device__ __noinline__ double j2_scalar_solve(const MatP& m, const RC& c, double lower, double upper, double xtol,
+static __device__ __forceinline__ double j2_scalar_solve(const MatP& m, const RC& c, double lower, double upper, double xtol,
                                                double rtol, int max_iter) {
   const double fl = j2_residual_d(m, c, lower), fh = j2_residual_d(m, c, upper);
   if (fabs(fl) < xtol) return lower;
@@ -347,7 +347,7 @@ static __device__ __noinline__ double j2_scalar_solve(const MatP& m, const RC& c
 }
 // J2::PlasticStress<ACC> (materials.hpp:311-391) on st = {plastic_strain[9], accumulated_plastic_strain, temperature}
 template <int DIM, bool ACC>
-__device__ __noinline__ void j2_plastic_stress(const MatP& m, const double* F, double* st, double* sigma) {
+__device__ __forceinline__ void j2_plastic_stress(const MatP& m, const double* F, double* st, double* sigma) {
   constexpr int DD = DIM * DIM;
   double eps[DD], s[DD];
 #pragma unroll
@@ -419,7 +419,7 @@ __device__ __forceinline__ void dev_mat(const double* A, double factor, double* 
 // J2Simo::PlasticStress<ACC> (materials.hpp:455-562) on st = {be_old[9], F_old[9], eqps, temperature}; Finv / det_F
 // are NonlinearSolidWorkData::FInv / DetF. ACC == false: P out (EvaluatePK1, materials.hpp:564-570). cbrt: libdevice.
 template <int DIM, bool ACC>
-__device__ __noinline__ void j2simo_plastic_stress(const MatP& m, const double* F, const double* Finv, double det_F,
+__device__ __forceinline__ void j2simo_plastic_stress(const MatP& m, const double* F, const double* Finv, double det_F,
                                                    double* st, double* P) {
   constexpr int DD = DIM * DIM;
   double w0[DD], w1[DD], w2[DD];
@@ -490,7 +490,7 @@ __device__ __noinline__ void j2simo_plastic_stress(const MatP& m, const double* 
 // tmp.stress_ (materials.hpp:728-734) is overwritten by that call and the exponential map only feeds it when
 // ACC == false, so neither is executed here. log / exp / hypot / acos / cos: libdevice.
 template <int DIM, bool ACC>
-__device__ __noinline__ void j2log_plastic_stress(const MatP& m, const double* F, const double* Finv, double det_F,
+__device__ __forceinline__ void j2log_plastic_stress(const MatP& m, const double* F, const double* Finv, double det_F,
                                                   double* st, double* P) {
   constexpr int DD = DIM * DIM;
   double w0[DD], w1[DD], V[DD], lam[DIM];

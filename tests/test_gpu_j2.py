@@ -215,3 +215,48 @@ def test_j2log_golden(ctx_factory, name, law):
     assert np.array_equal(r2, r) and _rel(A, D["A" + k]) <= 1e-2
     assert _rel(S, D["state" + k]) <= 1e-12
     assert _rel(rb, D["rb" + k]) <= 1e-12 and _rel(Ab, D["Ab" + k]) <= 1e-2
+
+
+@pytest.mark.parametrize("mat,law", [(2, None), (3, "jcthermo"), (3, "powerlaw"), (4, "jcthermo"), (5, "jcthermo")])
+def test_accumulators_parked_in_tensor_memory_give_the_same_bits(ctx_factory, mat, law):
+    """element_fd_kernel parks its 28 FP64 accumulators per thread in tensor memory (tcgen05.st / tcgen05.ld) while the
+    return mapping runs (option park_acc, default 1) instead of letting them spill to local memory: a move, no
+    arithmetic -- residual and Jacobian are bit-equal with the option off, on a yielded state (after one commit)."""
+    name = "cube_p2_n2"
+    D = load_golden(name) if mat == 2 else load_j2_golden(J2_CASES[0])
+    assert (D["dim"], D["nd"], D["nq"]) == (3, 27, 64)       # the two-phase kernel's element type
+    out = []
+    for park in (1, 0):
+        ctx = ctx_factory()
+        ctx.set_option("park_acc", park)
+        if mat == 2:
+            setup_ctx(ctx, D, "j2linear")
+        else:
+            ctx.set_connectivity(D["dim"], D["nd"], D["nq"], D["NV"], D["v_dofs"])
+            ctx.upload_quad_tables(D["dN_dX"], D["w"], D["detJ"])
+            ctx.build_pattern()
+            ctx.set_material(mat, j2_params(law))
+        ctx.post_time_advance(D["u"])
+        r = np.zeros(D["NV"])
+        A = D["mass"].copy()
+        ctx.add_domain_residual_and_grad(np.ascontiguousarray(1.5 * D["u"]), D["gf"], r, A)
+        out.append((r, A, ctx.get_state()))
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+    assert np.array_equal(out[0][2], out[1][2]) and np.abs(out[0][1] - D["mass"]).max() > 0
+
+
+@pytest.mark.parametrize("material", ["neohookean", "stvk", "j2linear"])
+def test_split_kernel_parks_its_accumulators_with_the_same_bits(ctx_factory, material):
+    """p = 3 (element_fd_split_kernel): the 40 accumulators per thread are parked in tensor memory for every material
+    (2 x 256 columns = the whole TMEM of an SM with two resident CTAs); bit-equal to the reference's dump with the option
+    on (default) and off."""
+    D = load_golden("beam4_p3")
+    assert (D["dim"], D["nd"], D["nq"]) == (3, 64, 125)
+    for park in (1, 0):
+        ctx = ctx_factory()
+        ctx.set_option("park_acc", park)
+        setup_ctx(ctx, D, material)
+        r = np.zeros(D["NV"])
+        A = D["mass"].copy()
+        ctx.add_domain_residual_and_grad(D["u"], D["gf"], r, A)
+        assert np.array_equal(r, D["r2_" + material]) and np.array_equal(A, D["A_" + material])
