@@ -380,6 +380,7 @@ def gpu_arm(args):
     ctx = capi.Context(local, stream=stream.cuda_stream)
     ctx.set_option("elem_variant", args.variant)
     ctx.set_option("park_acc", args.park)
+    ctx.set_option("res_variant", args.res_variant)
     fast = args.tangent == "analytic"
     if fast:
         ctx.set_option("tangent_mode", 1)          # MB2_TANGENT_ANALYTIC (secondary line: the headline stays the parity mode)
@@ -873,6 +874,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
                     help="c4: multi-patch p=3 StVK beam, 5e5 elements per GPU (config 4); c5: J2 + contact secondary workload (1 GPU)")
     ap.add_argument("--park", type=int, default=1, help="A/B: FD kernels park their accumulators in tensor memory during phase 1 (mb2_set_option park_acc; p=2: plastic materials, p=3: all)")
+    ap.add_argument("--res-variant", type=int, default=0, help="A/B: residual-only kernel (0 = element_res2_kernel, 1 = first form)")
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     ap.add_argument("--tangent", default="parity", choices=["parity", "analytic"],
                     help="analytic = MB2_TANGENT_ANALYTIC fast mode (secondary line; p=2, neohookean / stvk)")

@@ -1027,8 +1027,125 @@ __global__ void __launch_bounds__(192) element_res_kernel(const ElemArgs g) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Residual-only element kernel, second form. ncu of the first form (profiles/r02_elem_res_summary.txt): shared-memory
+// wavefronts at 85 % of peak (3 235 per element against a budget of 1 965 cycles per element and SM at the HBM peak) and
+// 49 % of the stall samples on barriers: the R phase read two shared-memory words per product. Here
+//   * the thread of quadrature point q computes all of F(q) (nine accumulators, u read as one LDS.128 + one LDS.64
+//     broadcast per node) and goes straight on to the stress: no F buffer, one barrier less;
+//   * one warp owns the R phase: lane = node a, three accumulators (j = 0..2) per lane, so a dN value is read once for
+//     three products and b(q; :, k) arrives as one LDS.128 + one LDS.64 broadcast: 4 wavefronts per (q, k) instead of 12.
+// Three warps per CTA, four CTAs per SM (49 KB each). Operation order of every accumulator as before.
+// ---------------------------------------------------------------------------------------------
+template <int DIM, int ND, int NQ>
+struct ElemRes2Cfg {
+  static constexpr int TD = DIM * ND;
+  static constexpr int DD = DIM * DIM;
+  static constexpr int NWQ = (NQ + 31) / 32;             // warps of the F + stress phase
+  static constexpr int NT = 32 * (NWQ + 1);
+  static constexpr int OFF_DN = 0;                       // [NQ][DIM][ND] (the global layout), 16-byte aligned
+  static constexpr int OFF_BQ = (OFF_DN + NQ * TD + 1) / 2 * 2;  // [NQ][DIM k][4]: b(q; j, k), j padded to 4
+  static constexpr int OFF_UT = OFF_BQ + NQ * DIM * 4;   // [ND][4]: u(i, a), i padded to 4
+  static constexpr int OFF_BAR = OFF_UT + ND * 4;
+  static constexpr int SMEM_DOUBLES = OFF_BAR + 2;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
+  static_assert(DIM == 3 && ND <= 32, "one lane per node, three components");
+  static_assert((NQ * TD * sizeof(double)) % 16 == 0, "bulk copy size must be a multiple of 16 bytes");
+  static_assert(NT >= TD, "CTA too small for the gather");
+};
+
+template <int DIM, int ND, int NQ, int MAT>
+__global__ void __launch_bounds__(ElemRes2Cfg<DIM, ND, NQ>::NT) element_res2_kernel(const __grid_constant__ ElemArgs g) {
+  using Cfg = ElemRes2Cfg<DIM, ND, NQ>;
+  constexpr int TD = Cfg::TD, DD = Cfg::DD, NS = mat_state_size(MAT);
+  extern __shared__ __align__(128) double smem[];
+  double* sdN = smem + Cfg::OFF_DN;
+  double* sbq = smem + Cfg::OFF_BQ;
+  double* sut = smem + Cfg::OFF_UT;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (t == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t phase = 0;
+  for (int64_t e = g.e0 + blockIdx.x; e < g.e1; e += gridDim.x) {
+    if (t == 0) tma_load_1d(sdN, g.dNdX + e * (int64_t)(NQ * TD), (uint32_t)(NQ * TD * sizeof(double)), bar);
+    if (t < TD) sut[(t % ND) * 4 + t / ND] = g.u[g.vdofs[e * TD + t]];  // component-major gather (Vector::GetSubVector)
+    double aq = 0.0;
+    if (t < NQ) aq = g.wdetJ[e * NQ + t];
+    __syncthreads();
+    mbar_wait(bar, phase);
+    phase ^= 1u;
+    if (t < NQ) {
+      // ---- F(q): MultAtB(element_x_mat_, dN_dX, F_) + AddDiagonal(1.0) (integrator_utils.cpp:33-40), nodes ascending
+      const double* dN = sdN + t * TD;
+      double F[DD], P[DD];
+#pragma unroll
+      for (int n = 0; n < DD; n++) F[n] = 0.0;
+#pragma unroll
+      for (int a = 0; a < ND; a++) {
+        const double2 u01 = *reinterpret_cast<const double2*>(sut + 4 * a);
+        const double u2 = sut[4 * a + 2];
+#pragma unroll
+        for (int j = 0; j < DIM; j++) {
+          const double v = dN[j * ND + a];
+          F[0 + DIM * j] += u01.x * v;
+          F[1 + DIM * j] += u01.y * v;
+          F[2 + DIM * j] += u2 * v;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < DIM; i++) F[i + DIM * i] += 1.0;
+      // ---- stress: b = (w detJ) P, bjk = a * P(j,k) (densemat.cpp:3008)
+      material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + t) * NS : nullptr, P);
+#pragma unroll
+      for (int k = 0; k < DIM; k++) {
+        *reinterpret_cast<double2*>(sbq + (t * DIM + k) * 4) = make_double2(aq * P[0 + DIM * k], aq * P[1 + DIM * k]);
+        sbq[(t * DIM + k) * 4 + 2] = aq * P[2 + DIM * k];
+      }
+    }
+    __syncthreads();
+    // ---- R(a, j) = sum_q sum_k dN(q; a, k) * b(q; j, k), q then k ascending (AddMult_a_ABt order, densemat.cpp:3002-3015)
+    if (warp == Cfg::NWQ && lane < ND) {
+      double r[DIM];
+#pragma unroll
+      for (int j = 0; j < DIM; j++) r[j] = 0.0;
+#pragma unroll 4
+      for (int q = 0; q < NQ; q++) {
+#pragma unroll
+        for (int k = 0; k < DIM; k++) {
+          const double v = sdN[q * TD + k * ND + lane];
+          const double2 b01 = *reinterpret_cast<const double2*>(sbq + (q * DIM + k) * 4);
+          const double b2 = sbq[(q * DIM + k) * 4 + 2];
+          r[0] += v * b01.x;
+          r[1] += v * b01.y;
+          r[2] += v * b2;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < DIM; j++) g.Re[e * TD + lane + j * ND] = r[j];
+    }
+    __syncthreads();  // smem is reused by the next element's copy
+  }
+}
+
 template <int DIM, int ND, int NQ, int MAT>
 static int launch_element_res(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
+  if (c->res_variant == 0) {
+    using Cfg2 = ElemRes2Cfg<DIM, ND, NQ>;
+    auto kern2 = element_res2_kernel<DIM, ND, NQ, MAT>;
+    MB2_CUDA(cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM_BYTES));
+    int per_sm2 = 0;
+    MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, kern2, Cfg2::NT, Cfg2::SMEM_BYTES));
+    if (per_sm2 < 1) per_sm2 = 1;
+    int64_t grid2 = (int64_t)c->sm_count * per_sm2;  // persistent: a whole number of resident CTAs per SM
+    if (grid2 > a.e1 - a.e0) grid2 = a.e1 - a.e0;
+    kern2<<<(unsigned)grid2, Cfg2::NT, Cfg2::SMEM_BYTES, st>>>(a);
+    MB2_CUDA(cudaGetLastError());
+    return MB2_OK;
+  }
   using Cfg = ElemResCfg<DIM, ND, NQ>;
   auto kern = element_res_kernel<DIM, ND, NQ, MAT>;
   MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
@@ -1065,8 +1182,8 @@ template <int DIM, int ND, int NQ, int MAT>
 static int launch_element_fd(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   using Cfg = Elem2Cfg<DIM, ND, NQ>;
   // plastic materials park the accumulators in tensor memory during the return mapping (option park_acc, default on)
-  auto kern = (MAT >= MAT_J2LINEAR && c->park_acc) ? element_fd_kernel<DIM, ND, NQ, MAT, (MAT >= MAT_J2LINEAR)>
-                                                   : element_fd_kernel<DIM, ND, NQ, MAT, false>;
+  auto kern = ((MAT >= MAT_J2LINEAR && c->park_acc) || c->park_acc == 2) ? element_fd_kernel<DIM, ND, NQ, MAT, true>
+                                                                         : element_fd_kernel<DIM, ND, NQ, MAT, false>;
   MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
   int per_sm = 0;
   MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::NT, Cfg::SMEM_BYTES));

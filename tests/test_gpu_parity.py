@@ -154,3 +154,32 @@ def test_mass_resident_entry_equals_the_adds_into_entry(ctx_factory):
         A = np.full(D["nnz"], np.nan)   # every entry must be overwritten
         ctx.domain_residual_and_grad_on_mass(D["u"], D["gf"], r, A)
         assert np.array_equal(r, D["r2_neohookean"]) and np.array_equal(A, D["A_neohookean"])
+
+
+@pytest.mark.parametrize("material", ["neohookean", "stvk", "j2linear"])
+@pytest.mark.parametrize("name", ["cube_p2_n3_patch", "beam3_p2", "cylinder_p2_n2"])
+def test_both_residual_only_kernels_are_bit_exact(ctx_factory, name, material):
+    """mb2_set_option("res_variant"): 0 = element_res2_kernel (one thread per quadrature point for F + stress, one warp
+    with three accumulators per lane for R), 1 = the first form. Same bits from both = the reference's residual."""
+    D = load_golden(name)
+    for variant in (0, 1):
+        ctx = ctx_factory()
+        ctx.set_option("res_variant", variant)
+        setup_ctx(ctx, D, material)
+        r = np.zeros(D["NV"])
+        ctx.add_domain_residual(D["u"], r)
+        assert np.array_equal(r, D["r_" + material])
+
+
+@pytest.mark.parametrize("material", ["neohookean", "stvk"])
+def test_parking_the_accumulators_of_the_hyperelastic_p2_kernel_changes_no_bit(ctx_factory, material):
+    """park_acc = 2: element_fd_kernel<3,27,64> parks its accumulators in tensor memory for the hyperelastic materials too
+    (an A/B option: they do not spill without it)."""
+    D = load_golden("cube_p2_n3_patch")
+    ctx = ctx_factory()
+    ctx.set_option("park_acc", 2)
+    setup_ctx(ctx, D, material)
+    r = np.zeros(D["NV"])
+    A = D["mass"].copy()
+    ctx.add_domain_residual_and_grad(D["u"], D["gf"], r, A)
+    assert np.array_equal(r, D["r2_" + material]) and np.array_equal(A, D["A_" + material])
