@@ -1035,7 +1035,10 @@ __global__ void __launch_bounds__(192) element_res_kernel(const ElemArgs g) {
 //     broadcast per node) and goes straight on to the stress: no F buffer, one barrier less;
 //   * one warp owns the R phase: lane = node a, three accumulators (j = 0..2) per lane, so a dN value is read once for
 //     three products and b(q; :, k) arrives as one LDS.128 + one LDS.64 broadcast: 4 wavefronts per (q, k) instead of 12.
+//   * the next element's v_dofs / wdetJ loads go out before the R loop and the dependent u load after it: the gather
+//     overlaps the R phase and the bulk copy.
 // Three warps per CTA, four CTAs per SM (49 KB each). Operation order of every accumulator as before.
+// Measured: 0.494 -> 0.695 of the HBM peak (bench.py --n 48, profiles/r02_bench_c3_n48_res*.json).
 // ---------------------------------------------------------------------------------------------
 template <int DIM, int ND, int NQ>
 struct ElemRes2Cfg {
@@ -1064,23 +1067,34 @@ __global__ void __launch_bounds__(ElemRes2Cfg<DIM, ND, NQ>::NT) element_res2_ker
   double* sut = smem + Cfg::OFF_UT;
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  // (rotating the R-warp role with the block id, to spread the R warps of an SM's CTAs over the schedulers, measured 4 % slower)
+  const int tq = t;  // quadrature point in the F + stress phase
   if (t == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
   uint32_t phase = 0;
+  // the gathered dof and the weight of the NEXT element travel in registers: the dependent loads v_dofs -> u are issued
+  // while this element's R phase runs (they were 17 % of the stall samples at the top of the loop)
+  double un = 0.0, aqn = 0.0;
+  {
+    const int64_t e = g.e0 + blockIdx.x;
+    if (e < g.e1) {
+      if (t < TD) un = g.u[g.vdofs[e * TD + t]];
+      if (tq < NQ) aqn = g.wdetJ[e * NQ + tq];
+    }
+  }
   for (int64_t e = g.e0 + blockIdx.x; e < g.e1; e += gridDim.x) {
     if (t == 0) tma_load_1d(sdN, g.dNdX + e * (int64_t)(NQ * TD), (uint32_t)(NQ * TD * sizeof(double)), bar);
-    if (t < TD) sut[(t % ND) * 4 + t / ND] = g.u[g.vdofs[e * TD + t]];  // component-major gather (Vector::GetSubVector)
-    double aq = 0.0;
-    if (t < NQ) aq = g.wdetJ[e * NQ + t];
+    if (t < TD) sut[(t % ND) * 4 + t / ND] = un;  // component-major gather (Vector::GetSubVector)
+    const double aq = aqn;
     __syncthreads();
     mbar_wait(bar, phase);
     phase ^= 1u;
-    if (t < NQ) {
+    if (tq < NQ) {
       // ---- F(q): MultAtB(element_x_mat_, dN_dX, F_) + AddDiagonal(1.0) (integrator_utils.cpp:33-40), nodes ascending
-      const double* dN = sdN + t * TD;
+      const double* dN = sdN + tq * TD;
       double F[DD], P[DD];
 #pragma unroll
       for (int n = 0; n < DD; n++) F[n] = 0.0;
@@ -1099,14 +1113,22 @@ __global__ void __launch_bounds__(ElemRes2Cfg<DIM, ND, NQ>::NT) element_res2_ker
 #pragma unroll
       for (int i = 0; i < DIM; i++) F[i + DIM * i] += 1.0;
       // ---- stress: b = (w detJ) P, bjk = a * P(j,k) (densemat.cpp:3008)
-      material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + t) * NS : nullptr, P);
+      material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + (e * NQ + tq) * NS : nullptr, P);
 #pragma unroll
       for (int k = 0; k < DIM; k++) {
-        *reinterpret_cast<double2*>(sbq + (t * DIM + k) * 4) = make_double2(aq * P[0 + DIM * k], aq * P[1 + DIM * k]);
-        sbq[(t * DIM + k) * 4 + 2] = aq * P[2 + DIM * k];
+        *reinterpret_cast<double2*>(sbq + (tq * DIM + k) * 4) = make_double2(aq * P[0 + DIM * k], aq * P[1 + DIM * k]);
+        sbq[(tq * DIM + k) * 4 + 2] = aq * P[2 + DIM * k];
       }
     }
     __syncthreads();
+    // next element: the index load goes out before the R loop, the dependent load of u after it (the R warp must not
+    // wait for the index at its loop head)
+    const int64_t en = e + gridDim.x;
+    int vdn = 0;
+    if (en < g.e1) {
+      if (t < TD) vdn = g.vdofs[en * TD + t];
+      if (tq < NQ) aqn = g.wdetJ[en * NQ + tq];
+    }
     // ---- R(a, j) = sum_q sum_k dN(q; a, k) * b(q; j, k), q then k ascending (AddMult_a_ABt order, densemat.cpp:3002-3015)
     if (warp == Cfg::NWQ && lane < ND) {
       double r[DIM];
@@ -1127,13 +1149,14 @@ __global__ void __launch_bounds__(ElemRes2Cfg<DIM, ND, NQ>::NT) element_res2_ker
 #pragma unroll
       for (int j = 0; j < DIM; j++) g.Re[e * TD + lane + j * ND] = r[j];
     }
+    if (en < g.e1 && t < TD) un = g.u[vdn];
     __syncthreads();  // smem is reused by the next element's copy
   }
 }
 
 template <int DIM, int ND, int NQ, int MAT>
 static int launch_element_res(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
-  if (c->res_variant == 0) {
+  if (c->res_variant != 1) {
     using Cfg2 = ElemRes2Cfg<DIM, ND, NQ>;
     auto kern2 = element_res2_kernel<DIM, ND, NQ, MAT>;
     MB2_CUDA(cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM_BYTES));
@@ -1181,9 +1204,11 @@ static int launch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
 template <int DIM, int ND, int NQ, int MAT>
 static int launch_element_fd(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   using Cfg = Elem2Cfg<DIM, ND, NQ>;
-  // plastic materials park the accumulators in tensor memory during the return mapping (option park_acc, default on)
-  auto kern = ((MAT >= MAT_J2LINEAR && c->park_acc) || c->park_acc == 2) ? element_fd_kernel<DIM, ND, NQ, MAT, true>
-                                                                         : element_fd_kernel<DIM, ND, NQ, MAT, false>;
+  // plastic materials park the accumulators in tensor memory during the return mapping (option park_acc, default on);
+  // for NeoHookean / StVK, which do not spill, parking measured 4 % SLOWER (38.05 -> 39.58 ms per 110 592 elements,
+  // profiles/r02_bench_c3_n48_park2.json): not instantiated
+  auto kern = (MAT >= MAT_J2LINEAR && c->park_acc) ? element_fd_kernel<DIM, ND, NQ, MAT, (MAT >= MAT_J2LINEAR)>
+                                                   : element_fd_kernel<DIM, ND, NQ, MAT, false>;
   MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
   int per_sm = 0;
   MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::NT, Cfg::SMEM_BYTES));

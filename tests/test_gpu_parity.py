@@ -169,17 +169,3 @@ def test_both_residual_only_kernels_are_bit_exact(ctx_factory, name, material):
         r = np.zeros(D["NV"])
         ctx.add_domain_residual(D["u"], r)
         assert np.array_equal(r, D["r_" + material])
-
-
-@pytest.mark.parametrize("material", ["neohookean", "stvk"])
-def test_parking_the_accumulators_of_the_hyperelastic_p2_kernel_changes_no_bit(ctx_factory, material):
-    """park_acc = 2: element_fd_kernel<3,27,64> parks its accumulators in tensor memory for the hyperelastic materials too
-    (an A/B option: they do not spill without it)."""
-    D = load_golden("cube_p2_n3_patch")
-    ctx = ctx_factory()
-    ctx.set_option("park_acc", 2)
-    setup_ctx(ctx, D, material)
-    r = np.zeros(D["NV"])
-    A = D["mass"].copy()
-    ctx.add_domain_residual_and_grad(D["u"], D["gf"], r, A)
-    assert np.array_equal(r, D["r2_" + material]) and np.array_equal(A, D["A_" + material])
