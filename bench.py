@@ -160,7 +160,7 @@ def reference_arm(args):
 # ----------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------
-def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean", slab=None):
+def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean", slab=None, nz_total=None):
     """Synthetic C3-style block in MFEM's numbering; tables regenerated on the device. world > 1: the global mesh
     is n x n x (n*world) spans (weak scaling), cut into z-slabs of n layers; rank g computes slab g, owns the nodes
     whose lowest element it computes, and receives the raw element matrices of the next slab's first p layers."""
@@ -173,7 +173,8 @@ def build_problem(ctx, n, p, rank=0, world=1, uid=None, material="neohookean", s
         owned_rows = None
     else:
         # weak scaling: n layers per rank of an n x n x (n world) patch; strong (slab given): slab layers of n x n x n
-        M = partition.slab_rank_problem(p, (n, n, (slab or n) * world), world, rank)
+        # (nz_total given: that many layers in all, cut into balanced, possibly uneven slabs)
+        M = partition.slab_rank_problem(p, (n, n, nz_total or (slab or n) * world), world, rank)
         owned_rows = np.repeat(M["owned"], 3)
     ctx.set_connectivity(3, M["nd"], nq1 ** 3, M["NV"], M["v_dofs"])
     if world > 1:
@@ -492,18 +493,19 @@ def gpu_arm(args):
 
     # ---- strong scaling: the SAME 1e6-element block (n^3) cut into N z-slabs ----
     strong = None
-    if world > 1 and args.scaling in ("strong", "both") and n % world == 0 and not c4:
+    if world > 1 and args.scaling in ("strong", "both") and n // world >= p and not c4:
         ctx2 = capi.Context(local, stream=stream.cuda_stream)
         ctx2.set_option("elem_variant", args.variant)
         uid2 = [capi.mg_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid2, src=0)
-        M2 = build_problem(ctx2, n, p, rank, world, uid2[0], args.material, slab=n // world)
+        M2 = build_problem(ctx2, n, p, rank, world, uid2[0], args.material, nz_total=n)
         ctx2.set_u(M2["u"]); ctx2.set_r(None); ctx2.set_A(None); ctx2.sync()
         T2 = timed_steps(ctx2, stream, args.steps, args.warmup, barrier, world, dist)
         qp2 = float(n) ** 3 * M2["nq"]
         strong = {"value": qp2 / (T2["ms_per_step"] * 1e-3), "unit": UNIT, "ms_per_step": T2["ms_per_step"],
                   "elements_total": n ** 3, "elements_per_gpu": M2["n_compute"],
-                  "workload": "the one %d^3-element block cut into %d z-slabs of %d layers" % (n, world, n // world)}
+                  "workload": "the one %d^3-element block cut into %d z-slabs of %s layers" % (
+                      n, world, "%d" % (n // world) if n % world == 0 else "%d or %d" % (n // world + 1, n // world))}
         ctx2.close()
     elif world == 1:
         strong = {"value": value, "unit": UNIT, "ms_per_step": ms_per_step, "elements_total": NE, "elements_per_gpu": NE,

@@ -60,15 +60,22 @@ def rank_problem(v_dofs: np.ndarray, dim: int, NV: int, ranges: np.ndarray, rank
                 send=send, recv=recv, el_owner_min=el_owner_min)
 
 
+def slab_bounds(n_layers: int, world: int) -> np.ndarray:
+    """Balanced cut of n_layers element layers into `world` slabs: the first n_layers % world ranks get one layer more."""
+    base, rem = divmod(int(n_layers), int(world))
+    return np.concatenate([[0], np.cumsum([base + (1 if r < rem else 0) for r in range(world)])]).astype(np.int64)
+
+
 def slab_rank_problem(p: int, spans, world: int, rank: int, lengths=None) -> dict:
     """rank_problem for a single-patch box cut into z-slabs of whole element layers, built WITHOUT the global
     connectivity (the 8-GPU weak-scaling mesh has 8e6 elements). Same rules as rank_problem; equality with it is
     checked in tests/test_partition.py. Returns the rank_problem dict plus the mesh pieces bench.py needs."""
     from . import meshgen
     n0, n1, n2 = (int(s) for s in spans)
-    assert n2 % world == 0 and n2 // world >= p, "z spans must split into slabs of at least p layers"
-    lz = n2 // world
-    k0, k1 = rank * lz, (rank + 1) * lz
+    kb = slab_bounds(n2, world)                            # layers [kb[r], kb[r+1]) belong to rank r (balanced, may be uneven)
+    assert min(np.diff(kb)) >= p, "z spans must split into slabs of at least p layers"
+    k0, k1 = int(kb[rank]), int(kb[rank + 1])
+    lz = k1 - k0
     kg = min(k1 + p, n2)                                   # ghost layers [k1, kg)
     kvs = [meshgen.open_uniform_knots(p, n) for n in spans]
     ncp = [len(kv) - p - 1 for kv in kvs]
@@ -89,7 +96,7 @@ def slab_rank_problem(p: int, spans, world: int, rank: int, lengths=None) -> dic
     Nn = g.size
     # owner of a node = rank of the layer of its lowest element = max(0, k_node - p)
     knode = np.arange(ncp[2])
-    owner_k = np.maximum(knode - p, 0) // lz
+    owner_k = np.searchsorted(kb[1:], np.maximum(knode - p, 0), side="right")
     owned = np.zeros(Nn, bool)
     owned[g[:, :, owner_k == rank].ravel()] = True
     n_layer = n0 * n1

@@ -297,6 +297,11 @@ def config1_main(nsteps=20):
             x, its = O.run_ref_steps(mesh, 1, 2, "neohookean", -5.0, 0.05, nsteps, os.path.join(tmp, "o%d" % nt), nthreads=nt, rho_inf=0.25)
             out["x_nt%d" % nt], out["its_nt%d" % nt] = x, its
             print("config1 nthreads=%d Newton iterations %s max|u| %.4f" % (nt, its.tolist(), np.abs(x).max()))
+        # the same run with the reference's iterative linear solver (use_iterative_solver: GMRESSolver + DSmoother,
+        # py_nonlinear_solid.cpp:330-339) and the GMRES iteration count of every Newton iteration
+        x, its, lin = O.run_ref_steps(mesh, 1, 2, "neohookean", -5.0, 0.05, nsteps, os.path.join(tmp, "og"), nthreads=1, rho_inf=0.25, lin="gmres")
+        out["x_gmres"], out["its_gmres"], out["lin_its_gmres"] = x, its, lin
+        print("config1 GMRES: Newton iterations %s, linear iterations %s" % (its.tolist(), lin.tolist()))
     np.savez_compressed(os.path.join(OUT, "config1_steps.npz"), **out)
 
 

@@ -773,15 +773,23 @@ def run_ref_eig(mats, outdir):
     return lam, vec
 
 
-def run_ref_steps(mesh, elevate, refine, material, force, dt, nsteps, outdir, binary=None, nthreads=1, rho_inf=None):
+def run_ref_steps(mesh, elevate, refine, material, force, dt, nsteps, outdir, binary=None, nthreads=1, rho_inf=None, lin=None):
     """Harness mode 'steps': the reference's own time loop (forms::Nonlinear + operators::NonlinearSolid + LineSearchNewton
-    + GeneralizedAlpha2) on the clamped-beam set-up of its tests -> (x history [nsteps][NV], Newton iterations)."""
+    + GeneralizedAlpha2) on the clamped-beam set-up of its tests -> (x history [nsteps][NV], Newton iterations).
+    lin="gmres": the reference's `use_iterative_solver` option (GMRESSolver + DSmoother on the CPU binary,
+    adapter/b200_gmres_solver.hpp on the B200 binary) instead of the dense LU -> additionally the linear iteration count of
+    every Newton iteration."""
     os.makedirs(outdir, exist_ok=True)
     env = dict(os.environ) if rho_inf is None else {**os.environ, "MIMI_REF_RHO_INF": repr(float(rho_inf))}
+    if lin:
+        env["MIMI_REF_LIN"] = lin
     subprocess.check_call([binary or REF_BIN, "steps", mesh, str(elevate), str(refine), material, str(nthreads), repr(force),
                            repr(dt), str(nsteps), outdir], stdout=subprocess.DEVNULL, env=env)
     its = np.fromfile(os.path.join(outdir, "newton_its.i32"), np.int32)
-    return np.fromfile(os.path.join(outdir, "x_hist.f64")).reshape(nsteps, -1), its
+    x = np.fromfile(os.path.join(outdir, "x_hist.f64")).reshape(nsteps, -1)
+    if lin:
+        return x, its, np.fromfile(os.path.join(outdir, "lin_its.i32"), np.int32)
+    return x, its
 
 
 def gmres_jacobi(I, J, A, b, rel_tol=1e-8, abs_tol=1e-12, max_iter=300, m=50):

@@ -22,6 +22,7 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <functional>
 #include <memory>
 #include <string>
 #include <vector>
@@ -890,11 +891,51 @@ int main(int argc, char** argv) {
       }
       void Mult(const mfem::Vector& b, mfem::Vector& x) const override { inv->Mult(b, x); }
     } lin;
+    // MIMI_REF_LIN=gmres: the reference's iterative option (`use_iterative_solver`, py_nonlinear_solid.cpp:330-339) -- the
+    // CPU binary builds mfem::GMRESSolver + mfem::DSmoother with the reference's constants, the B200 binary puts
+    // adapter/b200_gmres_solver.hpp in their place (device GMRES on the library's resident CSR). Either way the linear
+    // iteration count of every Newton iteration is recorded -> lin_its.i32.
+    struct Counting : mfem::Solver {
+      mfem::Solver* inner = nullptr;
+      std::function<int()> its;
+      mutable std::vector<int> log;
+      void SetOperator(const mfem::Operator& op) override {
+        inner->SetOperator(op);
+        height = width = op.Height();
+      }
+      void Mult(const mfem::Vector& b, mfem::Vector& x) const override {
+        inner->Mult(b, x);
+        log.push_back(its());
+      }
+    } counting;
+    mfem::GMRESSolver gm;
+    mfem::DSmoother dprec;
+    const char* env_lin = std::getenv("MIMI_REF_LIN");
+    const bool use_gmres = env_lin && std::string(env_lin) == "gmres";
+#ifdef MIMI_REF_USE_B200
+    std::unique_ptr<mimi::solvers::B200GMRESSolver> bg;
+#endif
+    if (use_gmres) {
+#ifdef MIMI_REF_USE_B200
+      bg = std::make_unique<mimi::solvers::B200GMRESSolver>(s.integ->Context());
+      counting.inner = bg.get();
+      counting.its = [&bg]() { return bg->GetNumIterations(); };
+#else
+      gm.SetRelTol(1e-8);
+      gm.SetAbsTol(1e-12);
+      gm.SetMaxIter(300);
+      gm.SetPrintLevel(-1);
+      gm.SetPreconditioner(dprec);
+      counting.inner = &gm;
+      counting.its = [&gm]() { return gm.GetNumIterations(); };
+#endif
+    }
     auto newton = std::make_shared<mimi::solvers::LineSearchNewton>();
     newton->nl_oper_ = nl_oper.get();
     newton->iterative_mode = false;
     newton->SetOperator(*nl_oper);
-    newton->SetSolver(lin);
+    if (use_gmres) newton->SetSolver(counting);
+    else newton->SetSolver(lin);
     newton->SetPrintLevel(-1);
     newton->SetRelTol(1e-12);
     newton->SetAbsTol(1e-8);
@@ -919,6 +960,7 @@ int main(int argc, char** argv) {
     }
     dump(out, "x_hist.f64", hist.data(), hist.size());
     dump(out, "newton_its.i32", its.data(), its.size());
+    if (use_gmres) dump(out, "lin_its.i32", counting.log.data(), counting.log.size());
     return 0;
   }
 

@@ -249,6 +249,30 @@ def test_config1_example_as_shipped_through_the_adapter():
     assert np.array_equal(x, z["x_nt1"])          # bit-exact integrator => bit-identical nonlinear trajectory
 
 
+def test_config1_with_the_iterative_solver_adapter():
+    """`use_iterative_solver` (py_nonlinear_solid.cpp:330-339) through the adapter: the same 20 steps of config 1 with
+    adapter/b200_gmres_solver.hpp (device GMRES(50) + Jacobi on the CSR the integrator adapter filled) driven by the
+    reference's LineSearchNewton in place of mfem::GMRESSolver + mfem::DSmoother. Golden = the CPU reference with its own
+    GMRES (61 Newton iterations, 57 .. 97 linear iterations each). The device solve sums its dot products in a tree, so its
+    iterates agree to rounding, not bitwise: Newton counts must be equal, the linear counts within 2 of the reference's
+    per solve, the trajectory within the linear tolerance's reach (1e-8 relative residual per solve)."""
+    if not O.have_ref_b200():
+        pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "config1_steps.npz"))
+    n = z["x_gmres"].shape[0]
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        meshgen.write_box_p1(mesh, (5.0, 1.0))
+        x, its, lin = O.run_ref_steps(mesh, 1, 2, "neohookean", -5.0, 0.05, n, os.path.join(tmp, "o"), binary=O.REF_B200_BIN,
+                                      rho_inf=0.25, lin="gmres")
+    dev = float(np.abs(x - z["x_gmres"]).max() / np.abs(z["x_gmres"]).max())
+    print("\n[config 1, GMRES adapter] Newton iterations %s (reference %s)\n linear iterations %s\n reference         %s\n"
+          " max |x - x_ref| / max |x_ref| = %.2e" % (its.tolist(), z["its_gmres"].tolist(), lin.tolist(), z["lin_its_gmres"].tolist(), dev))
+    assert its.tolist() == z["its_gmres"].tolist()
+    assert lin.size == z["lin_its_gmres"].size and np.abs(lin - z["lin_its_gmres"]).max() <= 2
+    assert dev <= 1e-8
+
+
 @pytest.mark.parametrize("name,material,ngpu", [("cube_p2_n2", "neohookean", 2), ("cube_p2_n2", "j2linear", 3), ("beam4_p3", "stvk", 4),
                                                 ("quad_p2_n4", "neohookean", 2)])
 def test_multi_gpu_adapter_in_one_process(name, material, ngpu):

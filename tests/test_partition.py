@@ -99,11 +99,15 @@ def test_ranges_and_ownership():
     assert (owned == 1).all()
 
 
-@pytest.mark.parametrize("p,spans,world", [(2, (3, 2, 8), 2), (2, (2, 3, 12), 4), (1, (2, 2, 6), 3), (3, (2, 2, 6), 2)])
+@pytest.mark.parametrize("p,spans,world", [(2, (3, 2, 8), 2), (2, (2, 3, 12), 4), (1, (2, 2, 6), 3), (3, (2, 2, 6), 2),
+                                           # uneven slabs (strong scaling of a 100-layer block over 8 ranks: 13,13,13,13,12,12,12,12)
+                                           (2, (2, 2, 11), 4), (2, (2, 3, 7), 3), (1, (3, 2, 13), 8)])
 def test_slab_problem_equals_generic(p, spans, world):
     from mimi_b200 import meshgen
     M = meshgen.patch_connectivity(p, spans)
-    rg = P.element_ranges(M["NE"], world)
+    rg = P.slab_bounds(spans[2], world) * (spans[0] * spans[1])       # whole layers per rank
+    if spans[2] % world == 0:
+        assert np.array_equal(rg, P.element_ranges(M["NE"], world))
     for r in range(world):
         G = P.rank_problem(M["v_dofs"], 3, M["NV"], rg, r)
         S = P.slab_rank_problem(p, spans, world, r)
