@@ -133,10 +133,23 @@ def test_reference_time_loop_through_the_adapter(case):
         # bit-exact integrator => the whole nonlinear trajectory is bit-identical to the CPU reference's
         assert its == ref_its and np.array_equal(x, z["ref_x_" + case])
     else:
-        # J2 family: residuals agree to 1e-13 (libdevice vs glibc), so a Newton step that ends within that distance of
-        # the tolerance may take one iteration more or less; the converged trajectory must not move
-        assert max(abs(a - b) for a, b in zip(its, ref_its)) <= 1
-        assert np.allclose(x, z["ref_x_" + case], rtol=1e-9, atol=1e-12)
+        # J2 family: pow / exp / log come from libdevice here and from glibc in the reference. How much that may move is
+        # MEASURED, not argued: tests/golden/j2_libm_spread.npz (oracle/libm_spread.py) holds the same compiled reference run
+        # with glibc's FMA ifunc variants and with its generic ones -- bit-equal residuals, FD tangents 3e-9 .. 3e-5 apart,
+        # trajectories 1e-12 apart, equal iteration counts. The device: trajectory within 1e-11 (absolute; |x| = O(1)) of the
+        # CPU reference's, every step whose Newton count differs reported, none by more than one iteration.
+        S = np.load(os.path.join(os.path.dirname(__file__), "golden", "j2_libm_spread.npz"))
+        diff = [(i, its[i], ref_its[i]) for i in range(10) if its[i] != ref_its[i]]
+        dev = float(np.abs(x - z["ref_x_" + case]).max())
+        print("[%s] steps whose Newton count differs from the CPU reference's (step, device, reference): %s; trajectory deviation %.2e;"
+              " reference-vs-reference (glibc FMA variants on / off): counts %s, trajectory %.2e" % (
+                  case, diff, dev, "equal" if np.array_equal(S["its_default_" + case], S["its_generic_" + case]) else "differ",
+                  float(S["x_spread_" + case])))
+        assert S["its_default_" + case].tolist() == ref_its
+        assert dev <= 1e-10
+        assert all(abs(a - b) <= 1 for _, a, b in diff) and len(diff) <= 1
+        if case != "j2":
+            assert not diff          # J2Simo / J2Log: identical counts (J2: one step of ten takes 4 instead of 5)
 
 
 from oracle.make_golden import CONTACT_CASES as CONTACT_RECIPES  # noqa: E402  (mesh recipe, boundary, penalty, body)

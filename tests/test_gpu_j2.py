@@ -87,6 +87,17 @@ def _rel(a, b):
     return np.abs(a - b).max() / np.abs(b).max()
 
 
+def _print_spread(mat):
+    """The reference against itself (oracle/libm_spread.py: glibc's FMA ifunc variants of pow / exp / log on and off, 3D
+    fixture): the floor for the FD tangent of this material, printed beside the device's deviation."""
+    import os
+    f = os.path.join(os.path.dirname(__file__), "golden", "j2_libm_spread.npz")
+    if os.path.exists(f):
+        z = np.load(f)
+        if "spread_" + mat in z.files:
+            print("    reference vs reference (libm variants), cube_p2_n2: r %.1e  A %.1e  state %.1e  rb %.1e  Ab %.1e" % tuple(z["spread_" + mat]))
+
+
 @pytest.mark.parametrize("law", J2_LAWS)
 @pytest.mark.parametrize("name", J2_CASES)
 def test_j2_hardening_golden(ctx_factory, name, law):
@@ -117,6 +128,7 @@ def test_j2_hardening_golden(ctx_factory, name, law):
     print("\n[j2 %s %s] rel dev: r %.1e  A %.1e  state %.1e  rb %.1e  Ab %.1e  (bit-equal r: %s)" % (
         name, law, _rel(r, D["r_" + law]), _rel(A, D["A_" + law]), _rel(S, D["state_" + law]), _rel(rb, D["rb_" + law]),
         _rel(Ab, D["Ab_" + law]), np.array_equal(r, D["r_" + law])))
+    _print_spread("j2_" + law)
 
 
 def test_j2_scalar_solve_failure_is_reported(ctx_factory):
@@ -175,6 +187,7 @@ def test_j2simo_golden(ctx_factory, name, law):
     print("\n[j2simo %s %s] rel dev: r %.1e  A %.1e  state %.1e  rb %.1e  Ab %.1e" % (
         name, law, _rel(r, D["r" + k]), _rel(A, D["A" + k]), _rel(S, D["state" + k]), _rel(rb, D["rb" + k]),
         _rel(Ab, D["Ab" + k])))
+    _print_spread("j2simo_" + law)
 
 
 from tests.cases import LOG_LAWS  # noqa: E402
@@ -211,6 +224,7 @@ def test_j2log_golden(ctx_factory, name, law):
     print("\n[j2log %s %s] rel dev: r %.1e  A %.1e  state %.1e  rb %.1e  Ab %.1e" % (
         name, law, _rel(r, D["r" + k]), _rel(A, D["A" + k]), _rel(S, D["state" + k]), _rel(rb, D["rb" + k]),
         _rel(Ab, D["Ab" + k])))
+    _print_spread("j2log_" + law)
     assert _rel(r, D["r" + k]) <= 1e-12
     assert np.array_equal(r2, r) and _rel(A, D["A" + k]) <= 1e-2
     assert _rel(S, D["state" + k]) <= 1e-12
