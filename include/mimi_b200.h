@@ -385,6 +385,20 @@ int mb2_plan_apply(mb2_ctx* ctx, const mb2_plan* plan, const int32_t* v_dofs_glo
 int mb2_mg_group_init(mb2_ctx** ctxs, int n);
 int mb2_mg_group_assemble(mb2_ctx** ctxs, int n, double grad_factor, int grad);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation). d_out[0] = sum_i d_a[i] d_b[i]
+ * over n doubles, all three DEVICE pointers of the context's device, with the deterministic reduction the library's own
+ * Newton norm (mb2_newton_residual_device) and GMRES inner products use -- the same bits as those. The call allocates
+ * nothing (no cudaMalloc / cudaFree, no allocating library routine): the block partials live in a file-scope device array
+ * of MB2_NOALLOC_MAX_N / 4096 = 16384 doubles (128 KiB held by every GPU that loads the library until exit), so
+ * n > MB2_NOALLOC_MAX_N is rejected with MB2_ERR_ARG and a message. It only enqueues two kernels on the context's stream
+ * and does not synchronise; the first call on a device also resolves the array's device address (cudaGetSymbolAddress: no
+ * allocation, but make that first call outside a graph capture). All calls share the array: nothing has to be cleared
+ * between calls (every partial that is read has been rewritten), but calls that overlap on one GPU (two streams, two
+ * contexts) race on it -- serialise them. */
+#define MB2_NOALLOC_MAX_N (64 * 1024 * 1024)
+int mb2_dot_noalloc(mb2_ctx* ctx, const double* d_a, const double* d_b, int64_t n, double* d_out);
+
 /* Tuning / A-B switches (never change results): "elem_variant" 0 = default kernels, 1 = one-thread-per-dof FD
  * kernel; "chunk_elems" = elements per pipeline chunk (0 = derive from "chunk_mb", the K_e buffer budget in MiB). */
 int mb2_set_option(mb2_ctx* ctx, const char* name, int value);

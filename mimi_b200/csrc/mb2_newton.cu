@@ -14,6 +14,7 @@
 //   y -= rhs; y[ess] = 0                      Vector::Add(-1.0, rhs)
 // Every kernel keeps the reference's per-entry expression (row sums sequential in column order), so y and J are
 // bit-identical to the reference's (tests/test_gpu_newton.py against dumps of the compiled reference).
+#include <mutex>
 #include <algorithm>
 #include <cmath>
 #include <vector>
@@ -605,6 +606,51 @@ int mb2_newton_residual_device(mb2_ctx* c, const double* x, const double* v, con
   if (!c->d_dNdX || c->mat_kind < 0) { c->err = "tables / material missing"; return MB2_ERR_ARG; }
   MB2_CUDA(cudaSetDevice(c->device));
   return mb2::newton_residual(c, x, v, a, fac0, fac1, norm_out);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free dot product (no counterpart in the reference; added for callers
+// that cannot call cudaMalloc: CUDA graph capture, tight serving loops). The same two kernels as dev_dot above -- the
+// deterministic reduction behind the Newton norm and the GMRES inner products -- with the block partials in a file-scope
+// device array instead of NewtonState::d_part. Every GPU that loads the library holds the 128 KiB until exit.
+// In host code `g_noalloc_part` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+// resolved once per device with that device current (first call on the device), and is what the kernels receive.
+// All calls share the array and it keeps the last call's partials: nothing needs clearing (k_dot_partial overwrites the
+// nparts entries k_dot_final reads), but two calls that overlap on the GPU (different streams / contexts on one device)
+// race on it.
+// ---------------------------------------------------------------------------------------------
+static_assert(MB2_NOALLOC_MAX_N % mb2::DOT_CHUNK == 0, "whole reduction blocks");
+constexpr int64_t NOALLOC_MAX_PARTS = MB2_NOALLOC_MAX_N / mb2::DOT_CHUNK;  // 16384 doubles
+static __device__ __align__(256) double g_noalloc_part[NOALLOC_MAX_PARTS];
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static double* g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of g_noalloc_part per device, 0 = not resolved yet
+static std::mutex g_noalloc_mutex;
+
+int mb2_dot_noalloc(mb2_ctx* c, const double* d_a, const double* d_b, int64_t n, double* d_out) {
+  if (!c) return MB2_ERR_ARG;
+  if (!d_a || !d_b || !d_out || n < 0) { c->err = "mb2_dot_noalloc: null pointer or negative length"; return MB2_ERR_ARG; }
+  if (n > (int64_t)MB2_NOALLOC_MAX_N) {
+    c->err = "mb2_dot_noalloc: n = " + std::to_string(n) + " exceeds MB2_NOALLOC_MAX_N = " + std::to_string((int64_t)MB2_NOALLOC_MAX_N) +
+             " (the static scratch holds " + std::to_string(NOALLOC_MAX_PARTS) + " block partials); use the allocating entries";
+    return MB2_ERR_ARG;
+  }
+  if (c->device < 0 || c->device >= NOALLOC_MAX_DEVICES) { c->err = "mb2_dot_noalloc: device index out of range"; return MB2_ERR_ARG; }
+  MB2_CUDA(cudaSetDevice(c->device));
+  double* part = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[c->device]) {
+      double* p = nullptr;
+      MB2_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_part));  // this device's instance of the array
+      g_noalloc_ptr[c->device] = p;
+    }
+    part = g_noalloc_ptr[c->device];
+  }
+  const int64_t nparts = (n + mb2::DOT_CHUNK - 1) / mb2::DOT_CHUNK;
+  if (nparts) mb2::k_dot_partial<<<(unsigned)nparts, 256, 0, c->stream>>>(n, d_a, d_b, part);
+  mb2::k_dot_final<<<1, 256, 0, c->stream>>>(nparts, part, d_out);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
 }
 
 }  // extern "C"
