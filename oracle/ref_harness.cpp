@@ -904,6 +904,9 @@ int main(int argc, char** argv) {
         height = width = op.Height();
       }
       void Mult(const mfem::Vector& b, mfem::Vector& x) const override {
+        // LineSearchNewton::Mult sets prec->iterative_mode = false (solvers/newton.cpp:74) on the solver it was given: hand
+        // that on, as if the inner solver had been registered directly (an IterativeSolver defaults to true)
+        inner->iterative_mode = iterative_mode;
         inner->Mult(b, x);
         log.push_back(its());
       }
