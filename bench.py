@@ -27,6 +27,7 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+MG_LATE = -1   # --mg-late
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
@@ -211,6 +212,9 @@ def build_problem_c4(ctx, n, rank=0, world=1, uid=None):
     if world > 1:
         ctx.mg_setup(M)
         ctx.mg_init_nccl(rank, world, uid)
+        # the x-interfaces between patches put outgoing elements (every i < p column) all through a rank's element range:
+        # hold the NCCL exchange back until the element kernels are done (see mb2_set_option "mg_exchange_late")
+        ctx.set_option("mg_exchange_late", MG_LATE if MG_LATE >= 0 else (1 if world > 2 else 0))
     ctx.set_nodes(M["x_ref"], None)
     for (e0, cnt, q) in M["patch_segments"]:
         ctx.generate_patch_tables(p, M["ncp"], M["knots"], M["el_ijk"][e0:e0 + cnt], e0=e0)
@@ -863,7 +867,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=100, help="knot spans per direction (per GPU)")
+    ap.add_argument("--n", "--size", dest="n", type=int, default=100, help="knot spans per direction (per GPU)")
     ap.add_argument("--ref-n", type=int, default=32, help="spans per direction of the CPU reference sample")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed e2e steps (0 = --steps)")
     ap.add_argument("--scaling", default="both", choices=["weak", "strong", "both"],
@@ -876,12 +880,15 @@ def main():
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
                     help="c4: multi-patch p=3 StVK beam, 5e5 elements per GPU (config 4); c5: J2 + contact secondary workload (1 GPU)")
     ap.add_argument("--park", type=int, default=1, help="A/B: FD kernels park their accumulators in tensor memory during phase 1 (mb2_set_option park_acc; p=2: plastic materials, p=3: all)")
+    ap.add_argument("--mg-late", type=int, default=-1, help="A/B (c4, N > 1): mb2_set_option mg_exchange_late (-1 = 1 when patches are split over ranks in x)")
     ap.add_argument("--res-variant", type=int, default=0, help="A/B: residual-only kernel (0 = element_res2_kernel, 1 = first form)")
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     ap.add_argument("--tangent", default="parity", choices=["parity", "analytic"],
                     help="analytic = MB2_TANGENT_ANALYTIC fast mode (secondary line; p=2, neohookean / stvk)")
     ap.add_argument("--fast-gemm", type=int, default=0, help="analytic mode: 0 = FP64 tensor cores (DMMA), 1 = CUDA-core DFMA")
     args = ap.parse_args()
+    global MG_LATE
+    MG_LATE = args.mg_late
     # The contract is ONE JSON line on stdout: libraries that write to fd 1 (NCCL prints its version banner there)
     # are sent to stderr; the JSON line goes to the original stdout.
     global _JSON_OUT

@@ -370,7 +370,8 @@ int64_t mb2_mg_ke_doubles(mb2_ctx* ctx);
 typedef struct mb2_plan mb2_plan;
 int mb2_plan_partition(const int32_t* v_dofs, int dim, int nd, int64_t NE, int64_t NV, int world, int rank, mb2_plan** out);
 void mb2_plan_free(mb2_plan* plan);
-/* what: 0 elements computed here, 1 local elements (own + ghosts), 2 global id of the first own element, 3 peers, 4 nodes */
+/* what: 0 elements computed here, 1 local elements (own + ghosts), 2 global id of the first own element, 3 peers, 4 nodes,
+ * 5 = 1 if some rank's outgoing elements lie in the second half of its range (mb2_plan_apply then sets "mg_exchange_late") */
 int64_t mb2_plan_size(const mb2_plan* plan, int what);
 int mb2_plan_local_elems(const mb2_plan* plan, int64_t* global_ids);          /* own elements, then ghosts */
 int mb2_plan_owned_nodes(const mb2_plan* plan, uint8_t* owned);               /* one byte per node */
@@ -400,7 +401,12 @@ int mb2_mg_group_assemble(mb2_ctx** ctxs, int n, double grad_factor, int grad);
 int mb2_dot_noalloc(mb2_ctx* ctx, const double* d_a, const double* d_b, int64_t n, double* d_out);
 
 /* Tuning / A-B switches (never change results): "elem_variant" 0 = default kernels, 1 = one-thread-per-dof FD
- * kernel; "chunk_elems" = elements per pipeline chunk (0 = derive from "chunk_mb", the K_e buffer budget in MiB). */
+ * kernel; "chunk_elems" = elements per pipeline chunk (0 = derive from "chunk_mb", the K_e buffer budget in MiB);
+ * "park_acc" 0 = FD kernels keep their accumulators in registers / local memory instead of tensor memory; "res_variant"
+ * 1 = first form of the residual-only kernel; "mg_exchange_late" 1 = the NCCL exchange of a partitioned assembly is
+ * enqueued behind the rank's last element kernel instead of behind its pack kernels (set it on EVERY rank when interface
+ * elements are spread through the element ranges: NCCL's kernels hold SMs while they wait for a peer);
+ * "tangent_mode", "fast_gemm", "j2_counters": see MB2_TANGENT_ANALYTIC and mb2_get_j2_counters. */
 int mb2_set_option(mb2_ctx* ctx, const char* name, int value);
 
 /* FP64 pipe micro-benchmark used for the roofline denominator: runs `iters` dependent-chain-free

@@ -460,6 +460,7 @@ class Plan:
         if rc:
             raise Mb2Error("mb2_plan_partition failed (%d)" % rc)
         self.n_compute, self.n_local, self.e0, self.n_peers, self.Nn = (int(self.lib.mb2_plan_size(self.h, k)) for k in range(5))
+        self.late_exchange = bool(self.lib.mb2_plan_size(self.h, 5))
         self.local_elems = np.zeros(self.n_local, np.int64)
         self.lib.mb2_plan_local_elems(self.h, _dp(self.local_elems))
         self.owned = np.zeros(self.Nn, np.uint8)

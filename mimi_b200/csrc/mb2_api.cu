@@ -501,6 +501,7 @@ int mb2_set_option(mb2_ctx* c, const char* name, int value) {
   if (!std::strcmp(name, "elem_variant")) { c->elem_variant = value; return MB2_OK; }
   if (!std::strcmp(name, "park_acc")) { c->park_acc = value; return MB2_OK; }
   if (!std::strcmp(name, "res_variant")) { c->res_variant = value; return MB2_OK; }
+  if (!std::strcmp(name, "mg_exchange_late")) { c->mg_late = value; return MB2_OK; }
   if (!std::strcmp(name, "tangent_mode")) {
     if (value != MB2_TANGENT_FD_PARITY && value != MB2_TANGENT_ANALYTIC) { c->err = "unknown tangent mode"; return MB2_ERR_ARG; }
     c->tangent_mode = value;

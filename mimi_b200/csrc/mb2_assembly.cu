@@ -1601,6 +1601,12 @@ static int assemble(mb2_ctx* c, double gf, bool grad, const double* A_in, double
       return MB2_ERR_ARG;
     }
     Plan* P = static_cast<Plan*>(c->plan);
+    // NCCL's send / receive kernels occupy SMs from their launch until their peer is ready. With interface elements spread
+    // through the element range (multi-patch beams: every i < p column of a patch) a peer packs until the end of its
+    // step, and a receiver launched early would spin beside its own element kernels for the whole step (config 4 on
+    // 8 GPUs: 1 983 ms of element kernels against 1 734 ms on one GPU). mg_exchange_late holds the exchange back until this
+    // rank's last element kernel has finished; z-slab partitions (interface = the first p layers) keep the early launch.
+    if (c->mg_late) MB2_CUDA(cudaStreamWaitEvent(c->mg->s_comm, grad ? P->el1[P->nch_own - 1] : P->el1[0], 0));
     if ((rc = mg_exchange(c, grad, P->s_ga, P->s_ga))) return rc;
   }
   return assemble_finish(c, gf, grad, A_out);

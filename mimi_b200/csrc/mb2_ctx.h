@@ -47,6 +47,7 @@ struct mb2_ctx {
   bool last_grad = false;
   int elem_variant = 0;  // 0 = default kernels, 1 = force the one-thread-per-dof FD kernel (A/B tests)
   int park_acc = 1;      // FD kernels park their accumulators in tensor memory during phase 1 (p=2: plastic materials, p=3: all); 0 = never (A/B)
+  int mg_late = 0;       // NCCL exchange enqueued behind the rank's last element kernel instead of behind its pack (see mb2_set_option)
   int res_variant = 0;   // residual-only kernel: 0 = element_res2_kernel, 1 = the first form (A/B)
   int tangent_mode = 0;  // MB2_TANGENT_FD_PARITY | MB2_TANGENT_ANALYTIC (mb2_fast.cu)
   int fast_gemm = 0;     // analytic mode, p = 2 hexahedra: 0 = FP64 tensor cores (DMMA), 1 = CUDA-core DFMA tiles

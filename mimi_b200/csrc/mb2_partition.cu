@@ -25,6 +25,9 @@ struct mb2_plan {
     int64_t recv_first = 0, n_recv = 0;
   };
   std::vector<Peer> peers;
+  // some rank's outgoing elements lie in the second half of its element range: a receiver's NCCL kernel launched at the start
+  // of the step would spin on SMs until that rank has packed them (option "mg_exchange_late", mb2_assembly.cu)
+  bool late_exchange = false;
   Peer& peer_of(int r) {
     for (auto& p : peers)
       if (p.peer == r) return p;
@@ -61,6 +64,14 @@ int mb2_plan_partition(const int32_t* v_dofs, int dim, int nd, int64_t NE, int64
       owner[(size_t)n] = rank_of_elem(first[(size_t)n]);
       P->owned[(size_t)n] = owner[(size_t)n] == rank;
     }
+  for (int64_t e = 0; e < NE && !P->late_exchange; ++e) {
+    const int re = rank_of_elem(e);
+    if (2 * (e - range(re)) < range(re + 1) - range(re)) continue;  // first half of its rank's range
+    for (int a = 0; a < nd; ++a) {
+      const int r = owner[(size_t)(v_dofs[e * tdof + a] / dim)];
+      if (r >= 0 && r < re) { P->late_exchange = true; break; }
+    }
+  }
   for (int64_t e = P->e0; e < P->e1; ++e) P->local.push_back(e);
   // sends: own elements touching a node of a lower rank (one ascending list per such rank)
   for (int64_t e = P->e0; e < P->e1; ++e) {
@@ -98,6 +109,7 @@ int64_t mb2_plan_size(const mb2_plan* p, int what) {
     case 2: return p->e0;                       // global id of the first own element
     case 3: return (int64_t)p->peers.size();
     case 4: return p->NV / p->dim;              // nodes
+    case 5: return p->late_exchange ? 1 : 0;    // the NCCL exchange should wait for the element kernels (see mb2_set_option)
   }
   return -1;
 }
@@ -138,6 +150,7 @@ int mb2_plan_apply(mb2_ctx* c, const mb2_plan* p, const int32_t* v_dofs_global, 
   if (rc) return rc;
   if (p->world == 1) return MB2_OK;
   if ((rc = mb2_set_partition(c, p->e1 - p->e0, p->owned.data()))) return rc;
+  if ((rc = mb2_set_option(c, "mg_exchange_late", p->late_exchange ? 1 : 0))) return rc;
   for (const auto& q : p->peers) {
     if (!q.send.empty() && (rc = mb2_mg_set_send(c, q.peer, q.send.data(), (int64_t)q.send.size()))) return rc;
     if (q.n_recv && (rc = mb2_mg_set_recv(c, q.peer, q.recv_first, q.n_recv))) return rc;

@@ -165,3 +165,14 @@ def test_library_planner_equals_the_python_oracle(name, world):
         for k in A["recv"]:
             assert np.array_equal(B.recv[k], A["recv"][k])
         B.close()
+
+
+def test_planner_flags_partitions_whose_interface_elements_come_late():
+    """mb2_plan_size(plan, 5): z-slabs of one patch send their first p layers (early: the NCCL exchange may start behind the
+    pack); a beam whose patches are split over ranks in x sends every i < p column of a patch, all through the element
+    range (late: mb2_plan_apply sets "mg_exchange_late")."""
+    from mimi_b200 import capi, meshgen
+    M = meshgen.patch_connectivity(2, (2, 2, 24))       # 6 layers per rank, the first 2 of them go to the rank below
+    assert not any(capi.Plan(M["v_dofs"], 3, M["NV"], 4, r).late_exchange for r in range(4))
+    v_dofs, NV = P.beam_connectivity(2, (3, 2, 2), 4)
+    assert all(capi.Plan(v_dofs, 3, NV, 4, r).late_exchange for r in range(4))
