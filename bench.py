@@ -535,16 +535,17 @@ def gpu_arm(args):
         if fast:
             # closed-form tangent: flops the kernel executes per element = the 162 x 192 x 27 contraction (6 component pairs,
             # K^{mj} mirrored) + T (162 x 192 x 3) + per point F (27 x 9 FMA), stress + dP/dF (~ 600) + residual (81 x 192 FMA)
-            kern = "element_fast_p2_kernel<%s,%s>" % (args.material, "dmma" if args.fast_gemm == 0 else "dfma")
+            kern = ("element_fast_p2v3_kernel<%s>" % args.material if args.fast_gemm == 0 else
+                    "element_fast_p2_kernel<%s,%s>" % (args.material, "dmma" if args.fast_gemm == 2 else "dfma"))
             per_el = 2.0 * 162 * 192 * 27 + 2.0 * 162 * 192 * 3 + nq * (2.0 * 27 * 9 + 600.0) + 2.0 * 81 * 192
             exe = alg = per_el / nq
             fd = 0.0
             exe_qp = exe
             achieved = qp_rate_kernel * exe_qp / 1e12
             peak_dmma = ctx_peaks["dmma"]
-            peak_nofma = peak_dmma if args.fast_gemm == 0 else peak_fma
+            peak_nofma = peak_dmma if args.fast_gemm != 1 else peak_fma
             peak_src = ("fast mode (FMA allowed): mb2_measure_fp64_peak(%s) on this GPU in this run; DFMA %.2f, tensor-core "
-                        "m8n8k4 %.2f TFLOP/s" % ("fma=2: FP64 tensor cores" if args.fast_gemm == 0 else "fma=1: DFMA", peak_fma, peak_dmma))
+                        "m8n8k4 %.2f TFLOP/s" % ("fma=2: FP64 tensor cores" if args.fast_gemm != 1 else "fma=1: DFMA", peak_fma, peak_dmma))
         traffic, traffic_note = ncu_traffic(kern, min(chunk_elems, NE))
         roofline = {"bound": "fp64", "kernel": kern, "achieved": achieved, "peak": peak_nofma,
                     "unit": "TFLOP/s", "frac": achieved / peak_nofma,
@@ -581,7 +582,7 @@ def gpu_arm(args):
                                        "%s: 3D unit-cube B-spline patch p=%d, %d^3 = %d elements x %d qp per GPU, %s, "
                                        "one residual+tangent assembly into CSR (nnz=%d per GPU), MFEM dof numbering" % (
                                            "C3" if (p == 2 and args.material == "neohookean") else "C4-style block", p, n, NE, nq, args.material, nnz),
-                           "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "nnz_per_gpu": nnz, "tangent": "FD parity (bit-exact vs reference)" if not fast else "MB2_TANGENT_ANALYTIC: closed-form tangent, %s contraction (NOT the headline mode: agrees with the reference's FD Jacobian to its 1e-4 noise, same Newton iteration counts)" % ("FP64 tensor-core (DMMA)" if args.fast_gemm == 0 else "CUDA-core DFMA"),
+                           "elements_per_gpu": NE, "qp_per_gpu": NE * nq, "nnz_per_gpu": nnz, "tangent": "FD parity (bit-exact vs reference)" if not fast else "MB2_TANGENT_ANALYTIC: closed-form tangent, %s contraction (NOT the headline mode: agrees with the reference's FD Jacobian to its 1e-4 noise, same Newton iteration counts)" % ("FP64 tensor-core (DMMA)" if args.fast_gemm != 1 else "CUDA-core DFMA"),
                            "l2": "inputs larger than L2 (tables %.1f GB, K_e %.1f GB per step)" % (8e-9 * NE * nq * (tdof + 1), 8e-9 * NE * tdof * tdof),
                            "parallelism": "1 GPU" if world == 1 else ("element ranges of %d elements per rank: every patch cut into 2 z-slabs, raw K_e/R_e of the p layers under every cut and of the first element column behind every patch interface sent to the owner rank by NCCL inside the step" % NE) if c4 else "z-slabs of %d^3 elements per GPU of one %dx%dx%d patch; raw K_e/R_e of the p interface layers sent to the owner rank by NCCL send/recv inside the step (bit-identical to the 1-thread reference order)" % (n, n, n, n * world),
                            "setup_s": M["setup_s"]},
@@ -885,7 +886,7 @@ def main():
     ap.add_argument("--variant", type=int, default=0, help="A/B: element kernel variant (mb2_set_option elem_variant)")
     ap.add_argument("--tangent", default="parity", choices=["parity", "analytic"],
                     help="analytic = MB2_TANGENT_ANALYTIC fast mode (secondary line; p=2, neohookean / stvk)")
-    ap.add_argument("--fast-gemm", type=int, default=0, help="analytic mode: 0 = FP64 tensor cores (DMMA), 1 = CUDA-core DFMA")
+    ap.add_argument("--fast-gemm", type=int, default=0, help="analytic mode: 0 = FP64 tensor cores, A fragments in registers (default), 1 = CUDA-core DFMA, 2 = tensor cores fed from T buffers")
     args = ap.parse_args()
     global MG_LATE
     MG_LATE = args.mg_late

@@ -67,8 +67,9 @@ enum {
                                 otherwise). Not bit-comparable: agrees with the reference's K to its finite-difference
                                 noise (1e-6 .. 1e-4 relative) and keeps its Newton iteration counts (tests/test_gpu_fast.py).
                                 The residual is the same quadrature with contracted FMAs (1e-15 relative).
-                                p = 2 hexahedra run the contraction on the FP64 tensor cores ("fast_gemm" 0, default) or
-                                on the CUDA cores ("fast_gemm" 1). */
+                                p = 2 hexahedra run the contraction on the FP64 tensor cores ("fast_gemm" 0, default:
+                                A fragments built in registers; 2: fed from shared-memory T buffers) or on the CUDA
+                                cores ("fast_gemm" 1; same bits as 2). */
 };
 
 /* ---- lifetime ------------------------------------------------------------------------------- */

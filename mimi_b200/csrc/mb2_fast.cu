@@ -250,19 +250,36 @@ __device__ __forceinline__ void jm_of(int p, int& j, int& m) {
   m = (p < 3) ? p : (p < 5 ? p - 2 : 2);
 }
 
-template <int MAT, int GEMM>  // GEMM: 0 = FP64 tensor cores (DMMA), 1 = CUDA-core DFMA register tiles
-__global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs g) {
-  using Cfg = FastP2;
-  constexpr int DIM = 3, ND = 27, NQ = 64, TD = 81, DD = 9, NDP = Cfg::NDP, LDR = Cfg::LDR, QC = Cfg::QC, KP = Cfg::KP;
-  extern __shared__ __align__(16) double smem[];
-  double* sdN = smem + Cfg::OFF_DN;
-  double* sC = smem + Cfg::OFF_C;
-  double* sT = smem + Cfg::OFF_T;
-  double* sb = smem + Cfg::OFF_B;
-  double* sue = smem + Cfg::OFF_UE;
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const int64_t e = g.e0 + blockIdx.x;
+// Third form of the p = 2 contraction (the library's default): the A fragments of the tensor-core GEMM are built in
+// REGISTERS. ncu of the second form (profiles/r02_fast_dmma_vs_dfma_summary.txt): 36 % of the DMMA peak, the T = dN C stage
+// between the MMA bursts 28 % of the stall samples, the CTA barrier per chunk 19 %, shared memory the busiest pipe (22
+// LDS / STS per k-step). With the GEMM depth ordered (n, q) -- a k-step = one n, four consecutive points -- a thread's A
+// element T[(p,i),(q,n)] = sum_k dN(q;i,k) C_q^p[k][n] needs the three dN(q;i,:) it keeps for all three n and three C
+// values: no T buffers, no barrier inside the loop (warps run through the 64 points independently), 12 LDS per k-step.
+struct FastP2V3 {
+  static constexpr int DIM = 3, ND = 27, NQ = 64, TD = 81, NDP = 28, NJM = 6, MR = NJM * ND, MT = (MR + 7) / 8, NTL = 4;
+  static constexpr int CQP = 74;  // pitch of one point's C block [p][n][4]: 72 + 2, so that the LDS.128 of the four points
+                                  // of a k-step fall into four different bank groups
+  static constexpr int KP = (TD * DIM + 3) / 4 * 4;
+  static constexpr int OFF_DN = 0;                               // [NQ*DIM][NDP] + 4 pad
+  static constexpr int OFF_C = OFF_DN + NQ * DIM * NDP + 4;      // [NQ][CQP]
+  static constexpr int OFF_B = OFF_C + NQ * CQP;                 // [NQ][9]  (w detJ) P
+  static constexpr int OFF_UE = OFF_B + NQ * 9;                  // [81]
+  static constexpr int OFF_SCR = OFF_UE + 84;                    // per-point stage scratch
+  static constexpr int SMEM_DOUBLES = OFF_SCR + 4 * NQ * 9 + 2 * NQ;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
+  static_assert(OFF_B >= ND * KP, "K_e staging aliases the dN and C buffers");
+  static_assert(OFF_C % 2 == 0 && CQP % 2 == 0, "16-byte aligned C rows");
+  static_assert(2 * (SMEM_BYTES + 1024) <= 227 * 1024, "two CTAs per SM");
+};
 
+// Everything before the contraction, shared by the p = 2 kernels: staging, the three per-point stages, the residual.
+// scr: 4 * 64 * 9 + 2 * 64 doubles of scratch. Ends without a barrier: sdN, sC, sb are complete (the last barrier follows
+// the C stage); the residual only reads them.
+template <int MAT, bool V3>
+__device__ __forceinline__ void fast_p2_prepare(const ElemArgs& g, const int64_t e, const int t, double* sdN, double* sC, double* sb,
+                                                double* sue, double* scr) {
+  constexpr int DIM = 3, ND = 27, NQ = 64, TD = 81, DD = 9, NDP = FastP2::NDP;
   // ---- stage the element
   if (t < TD) sue[t] = g.u[g.vdofs[e * TD + t]];
   {
@@ -283,12 +300,11 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
   //      NeoHookean: X = F^-T, alpha = w lambda (2J-1) J, beta = -w g, Y = w mu I, Z = 0;  StVK: X = F, alpha = w lambda,
   //      beta = w mu, Y = w S, Z = w mu F F^T   (w = w detJ; the stages' scratch aliases the T buffers)
   //  (3) one thread per (point, component pair j <= m): the 9 entries C^{jm}[k][n]
-  double* sF = sT;                       // [NQ][9]
-  double* sX = sT + NQ * 9;              // [NQ][9]
-  double* sY = sT + 2 * NQ * 9;          // [NQ][9]
-  double* sZ = sT + 3 * NQ * 9;          // [NQ][9]
-  double* sab = sT + 4 * NQ * 9;         // [NQ][2]
-  static_assert(4 * NQ * 9 + 2 * NQ <= 2 * Cfg::TBUF, "stage scratch fits the T buffers");
+  double* sF = scr;                      // [NQ][9]
+  double* sX = scr + NQ * 9;              // [NQ][9]
+  double* sY = scr + 2 * NQ * 9;          // [NQ][9]
+  double* sZ = scr + 3 * NQ * 9;          // [NQ][9]
+  double* sab = scr + 4 * NQ * 9;         // [NQ][2]
   for (int task = t; task < NQ * DD; task += 256) {
     const int q = task / DD, x = task - q * DD;
     const int a = x % DIM, b = x / DIM;
@@ -365,8 +381,8 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
     for (int x = 0; x < DD; x++) sb[t * DD + x] = aq * P[x];
   }
   __syncthreads();
-  for (int task = t; task < NQ * Cfg::NJM; task += 256) {
-    const int q = task / Cfg::NJM, p = task - q * Cfg::NJM;
+  for (int task = t; task < NQ * FastP2::NJM; task += 256) {
+    const int q = task / FastP2::NJM, p = task - q * FastP2::NJM;
     int j, m;
     jm_of(p, j, m);
     const double* X = sX + q * DD;
@@ -379,7 +395,9 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
       xj[k] = X[j + DIM * k];
       xm[k] = X[m + DIM * k];
     }
-    double* o = sC + task * 9;
+    // C layout: V3 = [q] pitch CQP, [(p, n)][4] (k contiguous: one LDS.128 + one LDS.64 per A-fragment element);
+    // otherwise [q][p][k][n]
+    double* o = V3 ? sC + q * FastP2V3::CQP + p * 12 : sC + task * 9;
 #pragma unroll
     for (int k = 0; k < DIM; k++)
 #pragma unroll
@@ -387,15 +405,10 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
         double c = alpha * xj[k] * xm[n] + beta * xj[n] * xm[k];
         if (j == m) c += Y[n + DIM * k];
         if (k == n) c += zjm;
-        o[k * 3 + n] = c;
+        o[V3 ? n * 4 + k : k * 3 + n] = c;
       }
   }
   __syncthreads();
-  // the rows 162 .. LDR-1 of both T buffers feed the padding rows of the last row tiles: zero once
-  for (int idx = t; idx < 2 * Cfg::KC * (Cfg::LDR - Cfg::MR); idx += 256) {
-    const int kk = idx / (Cfg::LDR - Cfg::MR), x = idx - kk * (Cfg::LDR - Cfg::MR);
-    sT[kk * Cfg::LDR + Cfg::MR + x] = 0.0;
-  }
   // ---- residual R(i, j) = sum_q sum_k dN(q; i, k) (w detJ P)(j, k)
   if (t < TD) {
     const int i = t % ND, j = t / ND;
@@ -407,6 +420,27 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
     g.Re[e * TD + t] = r;
   }
 
+}
+
+template <int MAT, int GEMM>  // GEMM: 0 = FP64 tensor cores (DMMA), 1 = CUDA-core DFMA register tiles
+__global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs g) {
+  using Cfg = FastP2;
+  constexpr int DIM = 3, ND = 27, NQ = 64, TD = 81, DD = 9, NDP = Cfg::NDP, LDR = Cfg::LDR, QC = Cfg::QC, KP = Cfg::KP;
+  extern __shared__ __align__(16) double smem[];
+  double* sdN = smem + Cfg::OFF_DN;
+  double* sC = smem + Cfg::OFF_C;
+  double* sT = smem + Cfg::OFF_T;
+  double* sb = smem + Cfg::OFF_B;
+  double* sue = smem + Cfg::OFF_UE;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int64_t e = g.e0 + blockIdx.x;
+
+  fast_p2_prepare<MAT, false>(g, e, t, sdN, sC, sb, sue, sT);   // the stages' scratch aliases the T buffers
+  // the rows 162 .. LDR-1 of both T buffers feed the padding rows of the last row tiles: zero once
+  for (int idx = t; idx < 2 * Cfg::KC * (Cfg::LDR - Cfg::MR); idx += 256) {
+    const int kk = idx / (Cfg::LDR - Cfg::MR), x = idx - kk * (Cfg::LDR - Cfg::MR);
+    sT[kk * Cfg::LDR + Cfg::MR + x] = 0.0;
+  }
   // T phase of chunk ch: T[(qs, n)][(p, i)] = sum_k dN(q; i, k) C_q^{p}[k][n]; task = (p, qs) per warp, lanes over the node i
   auto t_phase = [&](int ch) {
     double* Tb = sT + (ch & 1) * Cfg::TBUF;
@@ -547,6 +581,100 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2_kernel(const ElemArgs 
   }
 }
 
+template <int MAT>
+__global__ void __launch_bounds__(256, 2) element_fast_p2v3_kernel(const __grid_constant__ ElemArgs g) {
+  using Cfg = FastP2V3;
+  constexpr int DIM = 3, ND = 27, TD = 81, NDP = Cfg::NDP, KP = Cfg::KP;
+  extern __shared__ __align__(16) double smem[];
+  double* sdN = smem + Cfg::OFF_DN;
+  double* sC = smem + Cfg::OFF_C;
+  double* sb = smem + Cfg::OFF_B;
+  double* sue = smem + Cfg::OFF_UE;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int64_t e = g.e0 + blockIdx.x;
+  fast_p2_prepare<MAT, true>(g, e, t, sdN, sC, sb, sue, smem + Cfg::OFF_SCR);
+
+  // warp w owns row tiles w, w + 8, w + 16 x all 4 column tiles; row = (p, i), rows >= 162 read the zero pad column of dN
+  const int gid = lane >> 2, tig = lane & 3;
+  constexpr int NMT = 3;
+  int ia[NMT], pa12[NMT];
+#pragma unroll
+  for (int a = 0; a < NMT; a++) {
+    const int row = (warp + 8 * a) * 8 + gid;
+    const int p = row < Cfg::MR ? row / ND : 0;
+    ia[a] = row < Cfg::MR ? row - p * ND : ND;
+    pa12[a] = p * 12;
+  }
+  double acc[NMT][Cfg::NTL][2];
+#pragma unroll
+  for (int a = 0; a < NMT; a++)
+#pragma unroll
+    for (int b = 0; b < Cfg::NTL; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
+#pragma unroll 2
+  for (int qg = 0; qg < Cfg::NQ / 4; qg++) {
+    const int q = qg * 4 + tig;                 // the k index of a fragment element is the point
+    const double* dq = sdN + q * (DIM * NDP);
+    const double* cq = sC + q * Cfg::CQP;
+    double dn[NMT][DIM];
+#pragma unroll
+    for (int a = 0; a < NMT; a++)
+#pragma unroll
+      for (int k = 0; k < DIM; k++) dn[a][k] = dq[k * NDP + ia[a]];
+#pragma unroll
+    for (int n = 0; n < DIM; n++) {
+      double af[NMT], bf[Cfg::NTL];
+#pragma unroll
+      for (int a = 0; a < NMT; a++) {
+        const double2 c01 = *reinterpret_cast<const double2*>(cq + pa12[a] + n * 4);
+        const double c2 = cq[pa12[a] + n * 4 + 2];
+        af[a] = dn[a][0] * c01.x + dn[a][1] * c01.y + dn[a][2] * c2;
+      }
+      // B(k, col) = dN(q; l = 8 nt + gid, n)
+      const double* brow = dq + n * NDP + gid;
+#pragma unroll
+      for (int nt = 0; nt < Cfg::NTL; nt++) bf[nt] = brow[nt * 8];
+#pragma unroll
+      for (int a = 0; a < NMT; a++)
+#pragma unroll
+        for (int nt = 0; nt < Cfg::NTL; nt++) dmma_m8n8k4(acc[a][nt][0], acc[a][nt][1], af[a], bf[nt]);
+    }
+  }
+  __syncthreads();  // every warp has left the loop (and the residual): dN and C may be overwritten
+  // ---- K_e staged in shared memory (aliases dN and C), K^{mj} = (K^{jm})^T mirrored
+  double* sK = smem;
+#pragma unroll
+  for (int a = 0; a < NMT; a++) {
+    const int row = (warp + 8 * a) * 8 + gid;
+    if (row < Cfg::MR) {
+      const int p = row / ND, i = row - p * ND;
+      int j, m;
+      jm_of(p, j, m);
+#pragma unroll
+      for (int nt = 0; nt < Cfg::NTL; nt++)
+#pragma unroll
+        for (int x = 0; x < 2; x++) {
+          const int l = nt * 8 + tig * 2 + x;
+          if (l < ND) {
+            const double v = acc[a][nt][x];
+            sK[i * KP + (l + m * ND) * DIM + j] = v;
+            if (j != m) sK[l * KP + (i + j * ND) * DIM + m] = v;
+          }
+        }
+    }
+  }
+  __syncthreads();
+  // ---- coalesced 16-byte stores of the element matrix (pad column KP - 1 carries a zero)
+  {
+    double2* out = reinterpret_cast<double2*>(g.KeT + (e - g.e0) * (int64_t)(ND * KP));
+    for (int idx = t; idx < ND * KP / 2; idx += 256) {
+      const int col = (2 * idx) % KP;
+      double2 v = *reinterpret_cast<const double2*>(sK + 2 * idx);
+      if (col + 1 >= TD * DIM) v.y = 0.0;
+      out[idx] = v;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // launchers
 // ---------------------------------------------------------------------------------------------
@@ -569,6 +697,15 @@ static int launch_p2(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   return MB2_OK;
 }
 
+template <int MAT>
+static int launch_p2v3(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
+  auto kern = element_fast_p2v3_kernel<MAT>;
+  MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FastP2V3::SMEM_BYTES));
+  kern<<<(unsigned)(a.e1 - a.e0), 256, FastP2V3::SMEM_BYTES, st>>>(a);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
 int launch_element_analytic(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   if (c->mat_kind != MAT_NEOHOOKEAN && c->mat_kind != MAT_STVK) {
     c->err = "MB2_TANGENT_ANALYTIC: closed-form tangents exist for CompressibleOgdenNeoHookean and StVenantKirchhoff only";
@@ -577,8 +714,11 @@ int launch_element_analytic(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   const int dim = c->dim, nd = c->nd, nq = c->nq;
   if (dim == 3 && nd == 27 && nq == 64 && c->elem_variant != 1) {
     const bool nh = c->mat_kind == MAT_NEOHOOKEAN;
+    // fast_gemm: 0 = tensor cores, A fragments built in registers (default); 1 = CUDA-core DFMA tiles; 2 = tensor cores
+    // fed from T buffers in shared memory (the second form: same summation order as 1, hence the same bits)
     if (c->fast_gemm == 1) return nh ? launch_p2<MAT_NEOHOOKEAN, 1>(c, a, st) : launch_p2<MAT_STVK, 1>(c, a, st);
-    return nh ? launch_p2<MAT_NEOHOOKEAN, 0>(c, a, st) : launch_p2<MAT_STVK, 0>(c, a, st);
+    if (c->fast_gemm == 2) return nh ? launch_p2<MAT_NEOHOOKEAN, 0>(c, a, st) : launch_p2<MAT_STVK, 0>(c, a, st);
+    return nh ? launch_p2v3<MAT_NEOHOOKEAN>(c, a, st) : launch_p2v3<MAT_STVK>(c, a, st);
   }
   if (dim == 3 && nd == 27 && nq == 64) return launch_generic<3, 27, 64>(c, a, st);
   if (dim == 3 && nd == 64 && nq == 125) return launch_generic<3, 64, 125>(c, a, st);

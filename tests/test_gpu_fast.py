@@ -54,13 +54,14 @@ def test_fast_mode_equals_the_closed_form_and_tracks_the_reference(ctx_factory, 
 def test_tensor_core_and_cuda_core_contractions_agree(ctx_factory, material):
     D = load_golden("cube_p2_n3_patch")
     out = []
-    for gemm in (0, 1):
+    for gemm in (0, 1, 2):
         ctx = fast_ctx(ctx_factory(), D, material, gemm)
         r, A = np.zeros(D["NV"]), np.zeros(D["nnz"])
         ctx.add_domain_residual_and_grad(D["u"], 1.0, r, A)
         out.append((r, A))
-    assert np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][0], out[2][0])
     assert np.abs(out[0][1] - out[1][1]).max() <= 1e-13 * np.abs(out[1][1]).max()
+    assert np.array_equal(out[2][1], out[1][1])           # T-buffer tensor-core form == DFMA tiles, bit for bit
     # and the generic kernel (elem_variant 1) as a third opinion
     ctx = fast_ctx(ctx_factory(), D, material)
     ctx.set_option("elem_variant", 1)
@@ -93,12 +94,14 @@ def test_dmma_cannot_serve_the_parity_mode(ctx_factory):
     D = load_golden("cube_p2_n2")
     lam, mu = (float(x) for x in D["lambda_mu"])
     A = []
-    for gemm in (0, 1):
+    for gemm in (2, 1, 0):          # 2 = tensor cores fed from T buffers, 1 = DFMA tiles on the same buffers, 0 = default
         ctx = fast_ctx(ctx_factory(), D, "neohookean", gemm)
         a = np.zeros(D["nnz"])
         ctx.add_domain_residual_and_grad(D["u"], 1.0, np.zeros(D["NV"]), a)
         A.append(a)
-    assert np.array_equal(A[0], A[1])                     # DMMA == chained DFMA, bit for bit
+    assert np.array_equal(A[0], A[1])                     # DMMA == chained DFMA (same summation order), bit for bit
+    # the default form sums the same products in another order ((n, q) instead of (q, n)): rounding only
+    assert np.abs(A[2] - A[0]).max() <= 1e-13 * np.abs(A[0]).max()
     _, A_n = AR.assemble("neohookean", lam, mu, D, D["u"], 1.0, np.zeros(D["nnz"]))      # unfused float64 (numpy)
     d = np.abs(A[0] - A_n).max() / np.abs(A_n).max()
     print("\ntensor-core == CUDA-core DFMA bit for bit; fused vs unfused closed form: max relative difference %.2e, "
