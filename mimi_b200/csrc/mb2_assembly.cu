@@ -1403,6 +1403,9 @@ static int build_plan(mb2_ctx* c) {
   std::vector<int64_t> nodeptr((size_t)Nn + 1);
   {
     int32_t *d_f = nullptr, *d_l = nullptr;
+    DevTmp tmp;
+    tmp.own(&d_f);
+    tmp.own(&d_l);
     MB2_CUDA(cudaMalloc(&d_f, sizeof(int32_t) * Nn));
     MB2_CUDA(cudaMalloc(&d_l, sizeof(int32_t) * Nn));
     k_first_last<<<(unsigned)((Nn + 255) / 256), 256, 0, c->stream>>>(Nn, c->d_n2e_ptr, c->d_n2e_elem, d_f, d_l);
@@ -1412,8 +1415,6 @@ static int build_plan(mb2_ctx* c) {
     MB2_CUDA(cudaMemcpyAsync(nnbr.data(), c->d_nnbr, sizeof(int32_t) * Nn, cudaMemcpyDeviceToHost, c->stream));
     MB2_CUDA(cudaMemcpyAsync(nodeptr.data(), c->d_nodeptr, sizeof(int64_t) * (Nn + 1), cudaMemcpyDeviceToHost, c->stream));
     MB2_CUDA(cudaStreamSynchronize(c->stream));
-    cudaFree(d_f);
-    cudaFree(d_l);
   }
   const int64_t dd = (int64_t)c->dim * c->dim;
   // per-chunk node lists (a node appears in every chunk between its first and last element's chunk)

@@ -161,6 +161,19 @@ int assemble_traction(mb2_ctx* c, int64_t NF, int ndf, int nqf, const int32_t* f
 int form_mode(const mb2_ctx* c);  // 0 mass, 1 body force, 2 viscosity (valid while mass_tab is set)
 }  // namespace mb2
 
+// Device temporaries of a set-up routine: freed on scope exit, also on the early returns of MB2_CUDA.
+struct DevTmp {
+  std::vector<void**> slots;
+  template <class T>
+  void own(T** p) { slots.push_back(reinterpret_cast<void**>(p)); }
+  ~DevTmp() {
+    for (void** s : slots) {
+      if (*s) cudaFree(*s);
+      *s = nullptr;
+    }
+  }
+};
+
 #define MB2_CUDA(call)                                                                      \
   do {                                                                                      \
     cudaError_t e_ = (call);                                                                \

@@ -594,7 +594,11 @@ __global__ void __launch_bounds__(256, 2) element_fast_p2v3_kernel(const __grid_
   const int64_t e = g.e0 + blockIdx.x;
   fast_p2_prepare<MAT, true>(g, e, t, sdN, sC, sb, sue, smem + Cfg::OFF_SCR);
 
-  // warp w owns row tiles w, w + 8, w + 16 x all 4 column tiles; row = (p, i), rows >= 162 read the zero pad column of dN
+  // warp w owns row tiles w, w + 8, w + 16 x all 4 column tiles; row = (p, i), rows >= 162 read the zero pad column of dN.
+  // Measured and dropped (48^3 elements, this form 13.48 ms): rows grouped so that a warp serves one component pair and
+  // loads its C values once per k-step (-20 % shared-memory wavefronts) with the residual spread over 243 threads: 13.76 ms;
+  // the three pure-padding row tiles of warps 5 .. 7 skipped behind warp-uniform branches: 13.95 ms. The loop waits for the
+  // FP64 / tensor pipe ("math" is the top stall), not for shared memory; profiles/r02_fast_v3_summary.txt.
   const int gid = lane >> 2, tig = lane & 3;
   constexpr int NMT = 3;
   int ia[NMT], pa12[NMT];

@@ -273,6 +273,9 @@ int generate_patch_tables(mb2_ctx* c, int64_t e0, int64_t ne, int p, const int32
   double *d_gx = nullptr, *d_gw = nullptr, *d_knot[3] = {nullptr, nullptr, nullptr};
   double *d_B1[3] = {nullptr, nullptr, nullptr}, *d_D1[3] = {nullptr, nullptr, nullptr};
   int32_t* d_ijk = nullptr;
+  DevTmp tmp;
+  tmp.own(&d_gx); tmp.own(&d_gw); tmp.own(&d_ijk);
+  for (int d = 0; d < 3; d++) { tmp.own(&d_knot[d]); tmp.own(&d_B1[d]); tmp.own(&d_D1[d]); }
   MB2_CUDA(cudaMalloc(&d_gx, sizeof(double) * nq1));
   MB2_CUDA(cudaMalloc(&d_gw, sizeof(double) * nq1));
   MB2_CUDA(cudaMemcpyAsync(d_gx, gx.data(), sizeof(double) * nq1, cudaMemcpyHostToDevice, c->stream));
@@ -312,8 +315,6 @@ int generate_patch_tables(mb2_ctx* c, int64_t e0, int64_t ne, int p, const int32
   int flag = 0;
   MB2_CUDA(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   MB2_CUDA(cudaStreamSynchronize(c->stream));
-  cudaFree(d_gx); cudaFree(d_gw); cudaFree(d_ijk);
-  for (int d = 0; d < dim; d++) { cudaFree(d_knot[d]); cudaFree(d_B1[d]); cudaFree(d_D1[d]); }
   if (flag) { c->err = "non-positive geometry Jacobian determinant while generating tables"; return MB2_ERR_NUMERIC; }
   return MB2_OK;
 }
@@ -628,6 +629,8 @@ static int assemble_form(mb2_ctx* c, int mode, int p, const int32_t* ncp, const 
     MB2_CUDA(cudaMemcpyAsync(d_gx, gx.data(), sizeof(double) * T.nq1, cudaMemcpyHostToDevice, c->stream));
     MB2_CUDA(cudaMemcpyAsync(T.d_gw, gw.data(), sizeof(double) * T.nq1, cudaMemcpyHostToDevice, c->stream));
     std::vector<double*> d_knot(dim, nullptr);
+    DevTmp tmp;
+    for (int d = 0; d < dim; d++) tmp.own(&d_knot[d]);
     for (int d = 0; d < dim; d++) {
       const int nk = ncp[d] + p + 1, nspan = ncp[d] - p;
       MB2_CUDA(cudaMalloc(&d_knot[d], sizeof(double) * nk));
@@ -640,7 +643,6 @@ static int assemble_form(mb2_ctx* c, int mode, int p, const int32_t* ncp, const 
     MB2_CUDA(cudaMalloc(&T.d_ijk, sizeof(int32_t) * c->n_compute * dim));
     MB2_CUDA(cudaMemcpyAsync(T.d_ijk, el_ijk, sizeof(int32_t) * c->n_compute * dim, cudaMemcpyHostToDevice, c->stream));
     MB2_CUDA(cudaStreamSynchronize(c->stream));
-    for (int d = 0; d < dim; d++) cudaFree(d_knot[d]);
     c->mass_tab = &T;
     int r = mode != 1 ? launch_residual_and_grad(c, 1.0, nullptr, nullptr) : launch_residual(c);
     if (r) return r;
