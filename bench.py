@@ -493,6 +493,27 @@ def gpu_arm(args):
         del A_h, Ap
 
     chunk_elems, n_chunks = ctx.plan_info()
+
+    # ---- secondary: the same assembly in the fast tangent mode (MB2_TANGENT_ANALYTIC, NOT bit-comparable),
+    # so that the default line carries both modes. p = 2 NeoHookean / StVK only; its own executed-flop count and peak.
+    fast_mode = None
+    if not fast and not c4 and p == 2 and not args.no_fast:
+        ctx.set_option("tangent_mode", 1)
+        ctx.set_option("fast_gemm", 0)
+        ctx.set_r(None); ctx.set_A(None)
+        Tf = timed_steps(ctx, stream, max(2, min(args.steps, 5)), 2, barrier, world, dist)
+        ctx.set_option("tangent_mode", 0)
+        per_el = 2.0 * 162 * 192 * 27 + 2.0 * 162 * 192 * 3 + nq * (2.0 * 27 * 9 + 600.0) + 2.0 * 81 * 192
+        elf = float(np.mean(Tf["t_el"]))
+        ach = float(NE) * per_el / (elf * 1e-3) / 1e12
+        fast_mode = {"value": total_qp / (Tf["ms_per_step"] * 1e-3), "unit": UNIT, "ms_per_step": Tf["ms_per_step"],
+                     "speedup_vs_parity_mode": ms_per_step / Tf["ms_per_step"],
+                     "kernel": "element_fast_p2v3_kernel<%s>" % args.material, "kernel_ms": elf,
+                     "flop_per_qp_executed": per_el / nq, "achieved": ach, "peak": ctx_peaks["dmma"], "unit_roofline": "TFLOP/s",
+                     "frac": ach / ctx_peaks["dmma"],
+                     "note": "MB2_TANGENT_ANALYTIC: closed-form tangent, B^T C B on the FP64 tensor cores (mma.sync.m8n8k4.f64); opt-in, "
+                             "not bit-comparable: Jacobian within the reference's finite-difference noise, residual unchanged, Newton "
+                             "needs the same or fewer iterations (tests/test_gpu_fast.py); peak = mb2_measure_fp64_peak(2) in this run"}
     ctx.close()
 
     # ---- strong scaling: the SAME 1e6-element block (n^3) cut into N z-slabs ----
@@ -594,6 +615,8 @@ def gpu_arm(args):
             res_only["hbm_peak_gbs"] = hbm_peak
             res_only["frac_hbm"] = res_only["achieved_gbs_per_gpu"] / hbm_peak
             line["residual_only"] = res_only
+        if fast_mode:
+            line["fast_mode"] = fast_mode
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -875,6 +898,7 @@ def main():
                     help="N > 1: weak = n^3 elements per GPU (the headline value); strong = the one n^3 block cut into N slabs (key strong_scaling)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-res-only", action="store_true", help="skip the residual-only pass")
+    ap.add_argument("--no-fast", action="store_true", help="skip the secondary fast-tangent-mode measurement (key fast_mode)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--p", type=int, default=2, help="degree (2 = C3 headline; 3 = the C4 element type)")
     ap.add_argument("--material", default="neohookean", choices=["neohookean", "stvk"])
