@@ -55,4 +55,30 @@ public:
   }
 };
 
+/// The direct counterpart: takes the place of the mfem::UMFPackSolver PyNonlinearSolid::Setup builds by default
+/// (src/mimi/py/py_nonlinear_solid.cpp:340-343) -- mb2_newton_solve_direct_device (cuSOLVER sparse QR on the device CSR).
+class B200DirectSolver : public mfem::Solver {
+  mb2_ctx* ctx_;
+  bool resident_{false};
+
+  void Check(int rc) const {
+    if (rc) mimi::utils::PrintAndThrowError("mimi_b200:", mb2_last_error(ctx_));
+  }
+
+public:
+  explicit B200DirectSolver(mb2_ctx* ctx) : ctx_(ctx) {}
+  void SetResident(const bool on) { resident_ = on; }
+  void SetOperator(const mfem::Operator& op) override {
+    const auto* A = dynamic_cast<const mfem::SparseMatrix*>(&op);
+    if (!A) mimi::utils::PrintAndThrowError("B200DirectSolver: the operator must be the mfem::SparseMatrix Jacobian");
+    height = width = A->Height();
+    if (!resident_) Check(mb2_set_A(ctx_, A->GetData()));
+  }
+  void Mult(const mfem::Vector& b, mfem::Vector& x) const override {
+    if (!resident_) Check(mb2_set_r(ctx_, b.GetData()));
+    Check(mb2_newton_solve_direct_device(ctx_, nullptr));
+    Check(mb2_newton_get_solution(ctx_, x.GetData()));
+  }
+};
+
 }  // namespace mimi::solvers

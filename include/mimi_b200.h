@@ -334,6 +334,13 @@ int mb2_newton_residual_device(mb2_ctx* ctx, const double* x, const double* v, c
  * tolerance, iteration count within a few), not bitwise. */
 int mb2_newton_solve_gmres_device(mb2_ctx* ctx, double rel_tol, double abs_tol, int max_iter, int kdim, int* iterations,
                                   double* final_norm, int* converged);
+/* The reference's DEFAULT linear solver is mfem::UMFPackSolver (src/mimi/py/py_nonlinear_solid.cpp:340-343; Newton drives it
+ * as prec->SetOperator(J); prec->Mult(r, c), src/mimi/solvers/newton.cpp:125-132). Direct option on the resident arrays:
+ * J c = y by cuSOLVER's sparse QR (cusolverSpDcsrlsvqr with symrcm reordering, loaded with dlopen), solution resident like the
+ * iterative option's (mb2_newton_get_solution). A library call, not a kernel of this path: meant for the mesh sizes a direct
+ * solve is used at (cuSOLVER indexes with 32 bits); agrees with an LU solve to rounding (tests: 1e-10 relative). A singular
+ * Jacobian returns MB2_ERR_NUMERIC and, if singular_row != NULL, the row. */
+int mb2_newton_solve_direct_device(mb2_ctx* ctx, int* singular_row);
 int mb2_newton_get_solution(mb2_ctx* ctx, double* c_host);
 
 /* ---- multi-GPU: element partition with raw element-matrix exchange ------------------

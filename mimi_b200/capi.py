@@ -19,7 +19,7 @@ MB2_RIGID_RATIONAL_BEZIER, MB2_RIGID_NURBS = 4, 5
 
 # every symbol include/mimi_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
-    "mb2_create", "mb2_destroy", "mb2_last_error", "mb2_version", "mb2_set_connectivity", "mb2_dot_noalloc",
+    "mb2_create", "mb2_destroy", "mb2_last_error", "mb2_version", "mb2_set_connectivity", "mb2_dot_noalloc", "mb2_newton_solve_direct_device",
     "mb2_upload_quad_tables", "mb2_set_nodes", "mb2_generate_patch_tables", "mb2_assemble_mass_device", "mb2_assemble_body_force_device", "mb2_assemble_viscosity_device", "mb2_assemble_traction_device", "mb2_newton_viscosity_from_A", "mb2_newton_get_viscosity", "mb2_newton_rhs_from_r", "mb2_newton_mass_from_A", "mb2_newton_get_mass", "mb2_download_shape_values", "mb2_download_quad_tables", "mb2_build_pattern",
     "mb2_get_pattern_i32", "mb2_get_pattern_i64", "mb2_get_A_ids_i32", "mb2_set_material",
     "mb2_add_domain_residual", "mb2_add_domain_residual_and_grad", "mb2_set_u", "mb2_set_r", "mb2_set_A",
@@ -315,6 +315,12 @@ class Context:
         self._ck(self.lib.mb2_newton_residual_device(self.h, _dp(x), _dp(v), _dp(a), C.c_double(fac0), C.c_double(fac1),
                                                      C.byref(nrm) if want_norm else None))
         return nrm.value
+
+    def newton_solve_direct_device(self):
+        """J c = y on the resident arrays by cuSOLVER's sparse QR (the reference's default is UMFPACK); -> singular row (-1)."""
+        row = C.c_int(-1)
+        self._ck(self.lib.mb2_newton_solve_direct_device(self.h, C.byref(row)))
+        return row.value
 
     def dot_noalloc(self, d_a, d_b, n, d_out):
         """mb2_dot_noalloc: device addresses (ints) of a, b (n doubles) and of the one-double result; enqueued on the

@@ -14,7 +14,9 @@
 //   y -= rhs; y[ess] = 0                      Vector::Add(-1.0, rhs)
 // Every kernel keeps the reference's per-entry expression (row sums sequential in column order), so y and J are
 // bit-identical to the reference's (tests/test_gpu_newton.py against dumps of the compiled reference).
+#include <dlfcn.h>
 #include <mutex>
+#include <string>
 #include <algorithm>
 #include <cmath>
 #include <vector>
@@ -40,13 +42,20 @@ struct NewtonState {
   double* d_t = nullptr;      // NV work
   double* d_part = nullptr;   // block partials of the dot products
   std::vector<double*> d_vk;  // Krylov basis, m + 1 vectors
+  // direct option: cuSOLVER's sparse QR (mb2_newton_solve_direct_device)
+  int32_t* d_I32 = nullptr;   // row offsets as int32 (cuSOLVER's index type)
+  void* sp_handle = nullptr;  // cusolverSpHandle_t
+  void* sp_descr = nullptr;   // cusparseMatDescr_t
 };
 
 static NewtonState* NS(mb2_ctx* c) { return static_cast<NewtonState*>(c->newton); }
 
+static void free_direct(NewtonState* S);  // cuSOLVER handles of the direct option (defined with it below)
+
 void free_newton(mb2_ctx* c) {
   NewtonState* S = NS(c);
   if (!S) return;
+  free_direct(S);
   for (void* p : {(void*)S->d_M, (void*)S->d_S, (void*)S->d_rhs, (void*)S->d_a, (void*)S->d_tv, (void*)S->d_v, (void*)S->d_x,
                   (void*)S->d_ess, (void*)S->d_diag, (void*)S->d_c, (void*)S->d_w, (void*)S->d_t, (void*)S->d_part})
     if (p) cudaFree(p);
@@ -241,7 +250,8 @@ int newton_solve_gmres(mb2_ctx* c, double rel_tol, double abs_tol, int max_iter,
   if (!S->d_diag) {
     MB2_CUDA(cudaMalloc(&S->d_diag, sizeof(int64_t) * n));
     k_find_diag<<<nb(n), 256, 0, st>>>(n, c->d_I, c->d_J, S->d_diag, c->d_flag);
-    for (double** p : {&S->d_c, &S->d_w, &S->d_t}) MB2_CUDA(cudaMalloc(p, sizeof(double) * n));
+    for (double** p : {&S->d_c, &S->d_w, &S->d_t})
+      if (!*p) MB2_CUDA(cudaMalloc(p, sizeof(double) * n));   // d_c may exist already (direct option)
   }
   if (!S->d_part) MB2_CUDA(cudaMalloc(&S->d_part, sizeof(double) * (nparts + 1)));
   if ((int)S->d_vk.size() < m + 1) S->d_vk.resize(m + 1, nullptr);
@@ -400,6 +410,75 @@ int newton_residual(mb2_ctx* c, const double* x, const double* v, const double* 
     *norm_out = std::sqrt(dd);
     if ((rc = consume_flag(c))) return rc;  // the norm already synchronised: a failed return mapping surfaces here
   }
+  return MB2_OK;
+}
+
+// ---- direct option of the linear solve: the reference's default is mfem::UMFPackSolver (py_nonlinear_solid.cpp:340-343).
+// A sparse direct factorisation is library territory, not a kernel of this path: the resident CSR is handed to cuSOLVER's
+// sparse QR (cusolverSpDcsrlsvqr, device path, symrcm reordering), loaded with dlopen like NCCL so that the library keeps no
+// link-time dependency. For the mesh sizes a direct solve is used at; large meshes take the iterative option above.
+struct SpApi {
+  void *lib_solver = nullptr, *lib_sparse = nullptr;
+  int (*Create)(void**) = nullptr;
+  int (*Destroy)(void*) = nullptr;
+  int (*SetStream)(void*, cudaStream_t) = nullptr;
+  int (*CreateMatDescr)(void**) = nullptr;
+  int (*DestroyMatDescr)(void*) = nullptr;
+  int (*csrlsvqr)(void*, int, int, void*, const double*, const int*, const int*, const double*, double, int, double*, int*) = nullptr;
+};
+static SpApi g_sp;
+static int load_sp(std::string& err) {
+  if (g_sp.csrlsvqr) return MB2_OK;
+  for (const char* n : {"libcusolver.so.11", "libcusolver.so.12", "libcusolver.so"})
+    if ((g_sp.lib_solver = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
+  for (const char* n : {"libcusparse.so.12", "libcusparse.so.11", "libcusparse.so"})
+    if ((g_sp.lib_sparse = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
+  if (!g_sp.lib_solver || !g_sp.lib_sparse) { err = "direct solve: cannot load libcusolver / libcusparse"; return MB2_ERR_UNSUPPORTED; }
+#define MB2_SP(field, lib, name)                                                          \
+  g_sp.field = reinterpret_cast<decltype(g_sp.field)>(dlsym(g_sp.lib, name));            \
+  if (!g_sp.field) { err = std::string("direct solve: missing symbol ") + name; return MB2_ERR_UNSUPPORTED; }
+  MB2_SP(Create, lib_solver, "cusolverSpCreate")
+  MB2_SP(Destroy, lib_solver, "cusolverSpDestroy")
+  MB2_SP(SetStream, lib_solver, "cusolverSpSetStream")
+  MB2_SP(CreateMatDescr, lib_sparse, "cusparseCreateMatDescr")
+  MB2_SP(DestroyMatDescr, lib_sparse, "cusparseDestroyMatDescr")
+  MB2_SP(csrlsvqr, lib_solver, "cusolverSpDcsrlsvqr")
+#undef MB2_SP
+  return MB2_OK;
+}
+static void free_direct(NewtonState* S) {
+  if (S->d_I32) cudaFree(S->d_I32);
+  if (S->sp_descr && g_sp.DestroyMatDescr) g_sp.DestroyMatDescr(S->sp_descr);
+  if (S->sp_handle && g_sp.Destroy) g_sp.Destroy(S->sp_handle);
+  S->d_I32 = nullptr;
+  S->sp_descr = S->sp_handle = nullptr;
+}
+__global__ void k_i64_to_i32(int64_t n, const int64_t* __restrict__ a, int32_t* __restrict__ b) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) b[i] = (int32_t)a[i];
+}
+int newton_solve_direct(mb2_ctx* c, int* singular_row) {
+  NewtonState* S = NS(c);
+  const int64_t n = c->NV;
+  if (c->nnz > 2147483647LL || n > 2147483647LL) { c->err = "direct solve: cuSOLVER indexes with 32 bits (use the iterative option)"; return MB2_ERR_UNSUPPORTED; }
+  int rc = load_sp(c->err);
+  if (rc) return rc;
+  if (!S->sp_handle) {
+    if (g_sp.Create(&S->sp_handle) || g_sp.CreateMatDescr(&S->sp_descr)) { c->err = "direct solve: cusolverSpCreate / cusparseCreateMatDescr failed"; return MB2_ERR_CUDA; }
+  }
+  if (g_sp.SetStream(S->sp_handle, c->stream)) { c->err = "direct solve: cusolverSpSetStream failed"; return MB2_ERR_CUDA; }
+  if (!S->d_I32) {
+    MB2_CUDA(cudaMalloc(&S->d_I32, sizeof(int32_t) * (n + 1)));
+    k_i64_to_i32<<<nb(n + 1), 256, 0, c->stream>>>(n + 1, c->d_I, S->d_I32);
+    MB2_CUDA(cudaGetLastError());
+  }
+  if (!S->d_c) MB2_CUDA(cudaMalloc(&S->d_c, sizeof(double) * n));
+  int sing = -1;
+  const int st = g_sp.csrlsvqr(S->sp_handle, (int)n, (int)c->nnz, S->sp_descr, c->d_A, S->d_I32, c->d_J, c->d_r, 1e-300, 1, S->d_c, &sing);
+  MB2_CUDA(cudaStreamSynchronize(c->stream));
+  if (st) { c->err = "direct solve: cusolverSpDcsrlsvqr returned status " + std::to_string(st); return MB2_ERR_CUDA; }
+  if (singular_row) *singular_row = sing;
+  if (sing >= 0) { c->err = "direct solve: the Jacobian is singular (row " + std::to_string(sing) + ")"; return MB2_ERR_NUMERIC; }
   return MB2_OK;
 }
 
@@ -565,6 +644,15 @@ int mb2_newton_solve_gmres_device(mb2_ctx* c, double rel_tol, double abs_tol, in
   if (rc) return rc;
   // any latched device failure (a failed return mapping in the assembly that produced J, a bad elimination, a missing
   // diagonal) makes this solve meaningless: the reference would have thrown before reaching its linear solver
+  return mb2::consume_flag(c);
+}
+
+int mb2_newton_solve_direct_device(mb2_ctx* c, int* singular_row) {
+  if (!c) return MB2_ERR_ARG;
+  int rc = mb2::ensure(c);
+  if (rc) return rc;
+  MB2_CUDA(cudaSetDevice(c->device));
+  if ((rc = mb2::newton_solve_direct(c, singular_row))) return rc;
   return mb2::consume_flag(c);
 }
 

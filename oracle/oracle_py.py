@@ -787,7 +787,7 @@ def run_ref_steps(mesh, elevate, refine, material, force, dt, nsteps, outdir, bi
                            repr(dt), str(nsteps), outdir], stdout=subprocess.DEVNULL, env=env)
     its = np.fromfile(os.path.join(outdir, "newton_its.i32"), np.int32)
     x = np.fromfile(os.path.join(outdir, "x_hist.f64")).reshape(nsteps, -1)
-    if lin:
+    if lin == "gmres":
         return x, its, np.fromfile(os.path.join(outdir, "lin_its.i32"), np.int32)
     return x, its
 

@@ -917,6 +917,10 @@ int main(int argc, char** argv) {
     const bool use_gmres = env_lin && std::string(env_lin) == "gmres";
 #ifdef MIMI_REF_USE_B200
     std::unique_ptr<mimi::solvers::B200GMRESSolver> bg;
+    // MIMI_REF_LIN=direct (B200 binary only): adapter/b200_gmres_solver.hpp's B200DirectSolver (cuSOLVER sparse QR on the
+    // device CSR) in the place of the direct solver (UMFPACK in the reference, the dense LU above in this harness)
+    std::unique_ptr<mimi::solvers::B200DirectSolver> bd;
+    if (env_lin && std::string(env_lin) == "direct") bd = std::make_unique<mimi::solvers::B200DirectSolver>(s.integ->Context());
 #endif
     if (use_gmres) {
 #ifdef MIMI_REF_USE_B200
@@ -938,6 +942,9 @@ int main(int argc, char** argv) {
     newton->iterative_mode = false;
     newton->SetOperator(*nl_oper);
     if (use_gmres) newton->SetSolver(counting);
+#ifdef MIMI_REF_USE_B200
+    else if (bd) newton->SetSolver(*bd);
+#endif
     else newton->SetSolver(lin);
     newton->SetPrintLevel(-1);
     newton->SetRelTol(1e-12);

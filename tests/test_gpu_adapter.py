@@ -262,6 +262,28 @@ def test_config1_example_as_shipped_through_the_adapter():
     assert np.array_equal(x, z["x_nt1"])          # bit-exact integrator => bit-identical nonlinear trajectory
 
 
+def test_config1_with_the_direct_solver_adapter():
+    """adapter/b200_gmres_solver.hpp::B200DirectSolver (mb2_newton_solve_direct_device: cuSOLVER sparse QR on the device CSR)
+    in the place of the reference's default direct solver, driven by the reference's LineSearchNewton over the 20 steps of
+    config 1. Golden = the CPU reference with its direct solve (UMFPACK is absent here: the harness' dense LU). Equal
+    Newton iteration counts; trajectory within 1e-9 relative (two direct solvers agree to rounding, the Newton iterates
+    inherit it)."""
+    if not O.have_ref_b200():
+        pytest.skip("oracle/_ref/mimi_ref_b200 not built (make -f oracle/Makefile.ref b200, needs /root/reference)")
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "config1_steps.npz"))
+    n = z["x_nt1"].shape[0]
+    with tempfile.TemporaryDirectory() as tmp:
+        mesh = os.path.join(tmp, "m.mesh")
+        meshgen.write_box_p1(mesh, (5.0, 1.0))
+        x, its = O.run_ref_steps(mesh, 1, 2, "neohookean", -5.0, 0.05, n, os.path.join(tmp, "o"), binary=O.REF_B200_BIN,
+                                 rho_inf=0.25, lin="direct")
+    dev = float(np.abs(x - z["x_nt1"]).max() / np.abs(z["x_nt1"]).max())
+    print("\n[config 1, direct solver adapter] Newton iterations %s (reference %s), max |x - x_ref| / max |x_ref| = %.2e" % (
+        its.tolist(), z["its_nt1"].tolist(), dev))
+    assert its.tolist() == z["its_nt1"].tolist()
+    assert dev <= 1e-9
+
+
 def test_config1_with_the_iterative_solver_adapter():
     """`use_iterative_solver` (py_nonlinear_solid.cpp:330-339) through the adapter: the same 20 steps of config 1 with
     adapter/b200_gmres_solver.hpp (device GMRES(50) + Jacobi on the CSR the integrator adapter filled) driven by the

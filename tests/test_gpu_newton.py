@@ -90,6 +90,40 @@ def test_newton_linear_solve_gmres(ctx_factory, name):
 
 
 @pytest.mark.parametrize("name", SWEEP_CASES)
+def test_newton_linear_solve_direct(ctx_factory, name):
+    """The direct option (the reference's default is mfem::UMFPackSolver, py_nonlinear_solid.cpp:340-343; SuiteSparse is not in
+    this image, so the yardstick is LAPACK's dense LU on the same system): mb2_newton_solve_direct_device = cuSOLVER's sparse
+    QR on the resident CSR. Solution within 1e-10 relative of the dense solve, true residual at rounding level, y and J left
+    alone, second solve bit-identical; a singular matrix is reported, not solved."""
+    D, W = load_sweeps_golden(name)
+    ctx = setup_ctx(ctx_factory(), D, "neohookean")
+    ctx.set_mass(W["mass"]); ctx.set_viscosity(W["visc"]); ctx.set_rhs(W["rhs"]); ctx.set_essential_dofs(W["ess"])
+    ctx.newton_residual_and_grad_device(W["x"], W["v"], W["a"], W["fac0"], W["fac1"])
+    assert ctx.newton_solve_direct_device() == -1
+    c = ctx.newton_get_solution()
+    n = len(W["I"]) - 1
+    Jd = np.zeros((n, n))
+    for i in range(n):
+        Jd[i, W["J"][W["I"][i]:W["I"][i + 1]]] = W["Jac"][W["I"][i]:W["I"][i + 1]]
+    c_ref = np.linalg.solve(Jd, W["y"])
+    dev = np.abs(c - c_ref).max() / np.abs(c_ref).max()
+    res = np.linalg.norm(Jd @ c - W["y"]) / np.linalg.norm(W["y"])
+    print("\n[direct %s] max |c - c_LU| / max |c_LU| = %.2e, |J c - y| / |y| = %.2e; vs the reference's GMRES solution %.2e" % (
+        name, dev, res, np.abs(c - W["gmres_x"]).max() / np.abs(W["gmres_x"]).max()))
+    assert dev <= 1e-10 and res <= 1e-12
+    assert np.array_equal(ctx.get_r(), W["y"]) and np.array_equal(ctx.get_A(), W["Jac"])
+    ctx.newton_solve_direct_device()
+    assert np.array_equal(ctx.newton_get_solution(), c)
+    # the iterative option still works on the same context afterwards (shared solution vector)
+    it, fn, conv = ctx.newton_solve_gmres_device()
+    assert conv and np.abs(ctx.newton_get_solution() - c).max() <= 1e-6 * np.abs(c).max()
+    # singular Jacobian: reported
+    ctx.set_A(np.zeros(D["nnz"]))
+    with pytest.raises(Exception, match="singular|status"):
+        ctx.newton_solve_direct_device()
+
+
+@pytest.mark.parametrize("name", SWEEP_CASES)
 def test_newton_line_search_residual(ctx_factory, name):
     """mb2_newton_residual_device = NonlinearSolid::Mult(a, y) (operators/nonlinear_solid.cpp:172-205): y bit-identical to
     the oracle's composition of the same sequence (mass, stiffness + essential zeroing, viscosity, rhs); the l2 norm is a
