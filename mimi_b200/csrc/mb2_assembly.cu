@@ -1154,6 +1154,169 @@ __global__ void __launch_bounds__(ElemRes2Cfg<DIM, ND, NQ>::NT) element_res2_ker
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Residual-only element kernel for p = 3 (nd = 64, nq = 125: config 4's element; the generic kernel held the whole 192 KB
+// table of an element in shared memory, one CTA per SM, and reached 0.13 of the HBM peak). Streaming form: the table arrives
+// in chunks of QC quadrature points, row by row (one bulk copy per (q, k) row of 64 doubles into a row pitch of 66, which
+// keeps the per-thread 16-byte loads of the F phase conflict-free), double-buffered on two mbarriers; four 128-thread CTAs
+// per SM hide one another's serial phases. Per chunk:
+//   F      thread (q, j): the column F(:, j) of the point, 64 nodes ascending (MultAtB order), u as broadcast loads
+//   stress thread q: P, b = (w detJ) P
+//   R      lane = node (two warps), three accumulators R(a, 0..2) carried across the chunks, q then k ascending
+// ---------------------------------------------------------------------------------------------
+template <int DIM, int ND, int NQ>
+struct ElemRes3Cfg {
+  static constexpr int TD = DIM * ND;
+  static constexpr int DD = DIM * DIM;
+  static constexpr int NT = 128;
+  static constexpr int QC = 16;
+  static constexpr int NCH = (NQ + QC - 1) / QC;
+  static constexpr int NDP = ND + 2;                       // row pitch (16-byte aligned rows, 4-word bank shift per row)
+  static constexpr int CHD = QC * DIM * NDP;               // doubles per chunk buffer
+  static constexpr int OFF_DN = 0;                         // [2][QC * DIM][NDP]
+  static constexpr int OFF_F = 2 * CHD;                    // [QC][DIM j][4]: F(i, j), i padded to 4
+  static constexpr int OFF_BQ = OFF_F + QC * DIM * 4;      // [QC][DIM k][4]: b(q; j, k), j padded to 4
+  static constexpr int OFF_UT = OFF_BQ + QC * DIM * 4;     // [ND][4]: u(i, a), i padded to 4
+  static constexpr int OFF_BAR = OFF_UT + ND * 4;
+  static constexpr int SMEM_DOUBLES = OFF_BAR + 2;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * SMEM_DOUBLES;
+  static_assert(DIM == 3 && ND == 64 && ND % 2 == 0 && NDP % 2 == 0, "two warps of node lanes, 16-byte rows");
+  static_assert(QC * DIM <= NT && QC <= NT && ND <= NT, "CTA too small");
+};
+
+template <int DIM, int ND, int NQ, int MAT>
+__global__ void __launch_bounds__(ElemRes3Cfg<DIM, ND, NQ>::NT, 4) element_res3_kernel(const __grid_constant__ ElemArgs g) {
+  using Cfg = ElemRes3Cfg<DIM, ND, NQ>;
+  constexpr int TD = Cfg::TD, DD = Cfg::DD, NT = Cfg::NT, QC = Cfg::QC, NCH = Cfg::NCH, NDP = Cfg::NDP, CHD = Cfg::CHD,
+                NS = mat_state_size(MAT);
+  extern __shared__ __align__(128) double smem[];
+  double* sdN = smem + Cfg::OFF_DN;
+  double* sF = smem + Cfg::OFF_F;
+  double* sbq = smem + Cfg::OFF_BQ;
+  double* sut = smem + Cfg::OFF_UT;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  const int t = threadIdx.x;
+  if (t == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  // one thread issues the row copies of chunk ch of element e into buffer b
+  auto issue = [&](int64_t e, int ch, int b) {
+    const int nq = (NQ - ch * QC < QC) ? NQ - ch * QC : QC;
+    const double* src = g.dNdX + e * (int64_t)(NQ * TD) + (int64_t)ch * QC * TD;
+    double* dst = sdN + b * CHD;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bar[b])),
+                 "r"((uint32_t)(nq * DIM * ND * sizeof(double)))
+                 : "memory");
+    for (int r = 0; r < nq * DIM; r++)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst + r * NDP)),
+                   "l"(src + r * ND), "r"((uint32_t)(ND * sizeof(double))), "r"(smem_u32(&bar[b]))
+                   : "memory");
+  };
+  uint32_t it = 0;  // chunks consumed so far by this CTA: buffer it & 1, barrier phase (it >> 1) & 1
+  int64_t e = g.e0 + blockIdx.x;
+  if (t == 0 && e < g.e1) issue(e, 0, 0);
+  for (; e < g.e1; e += gridDim.x) {
+    if (t < TD) sut[(t % ND) * 4 + t / ND] = g.u[g.vdofs[e * TD + t]];     // NT < TD: two rounds
+    if (t + NT < TD) sut[((t + NT) % ND) * 4 + (t + NT) / ND] = g.u[g.vdofs[e * TD + t + NT]];
+    double r[DIM];
+#pragma unroll
+    for (int j = 0; j < DIM; j++) r[j] = 0.0;
+    __syncthreads();
+#pragma unroll 1
+    for (int ch = 0; ch < NCH; ch++, it++) {
+      const int b = it & 1;
+      // the other buffer was last read in the R phase of the previous chunk, which every thread has left (barrier below)
+      if (t == 0) {
+        if (ch + 1 < NCH) issue(e, ch + 1, b ^ 1);
+        else if (e + gridDim.x < g.e1) issue(e + gridDim.x, 0, b ^ 1);
+      }
+      mbar_wait(&bar[b], (it >> 1) & 1u);
+      const double* buf = sdN + b * CHD;
+      const int nq = (NQ - ch * QC < QC) ? NQ - ch * QC : QC;
+      // ---- F(:, j) of point q: MultAtB(element_x_mat_, dN_dX, F_) + AddDiagonal(1.0) (integrator_utils.cpp:33-40)
+      if (t < nq * DIM) {
+        const int q = t / DIM, j = t - q * DIM;
+        const double2* row = reinterpret_cast<const double2*>(buf + (q * DIM + j) * NDP);
+        double f0 = 0.0, f1 = 0.0, f2 = 0.0;
+#pragma unroll 8
+        for (int a2 = 0; a2 < ND / 2; a2++) {
+          const double2 v = row[a2];
+          const double2 ua = *reinterpret_cast<const double2*>(sut + 8 * a2);
+          const double ua2 = sut[8 * a2 + 2];
+          const double2 ub = *reinterpret_cast<const double2*>(sut + 8 * a2 + 4);
+          const double ub2 = sut[8 * a2 + 6];
+          f0 += ua.x * v.x;
+          f1 += ua.y * v.x;
+          f2 += ua2 * v.x;
+          f0 += ub.x * v.y;
+          f1 += ub.y * v.y;
+          f2 += ub2 * v.y;
+        }
+        if (j == 0) f0 += 1.0;
+        if (j == 1) f1 += 1.0;
+        if (j == 2) f2 += 1.0;
+        *reinterpret_cast<double2*>(sF + (q * DIM + j) * 4) = make_double2(f0, f1);
+        sF[(q * DIM + j) * 4 + 2] = f2;
+      }
+      __syncthreads();
+      // ---- stress: b = (w detJ) P, bjk = a * P(j,k) (densemat.cpp:3008)
+      if (t < nq) {
+        const int64_t qg = e * NQ + ch * QC + t;
+        double F[DD], P[DD];
+#pragma unroll
+        for (int j = 0; j < DIM; j++)
+#pragma unroll
+          for (int i = 0; i < DIM; i++) F[i + DIM * j] = sF[(t * DIM + j) * 4 + i];
+        material_pk1<DIM, MAT>(g.mp, F, NS ? g.state + qg * NS : nullptr, P);
+        const double aq = g.wdetJ[qg];
+#pragma unroll
+        for (int k = 0; k < DIM; k++) {
+          *reinterpret_cast<double2*>(sbq + (t * DIM + k) * 4) = make_double2(aq * P[0 + DIM * k], aq * P[1 + DIM * k]);
+          sbq[(t * DIM + k) * 4 + 2] = aq * P[2 + DIM * k];
+        }
+      }
+      __syncthreads();
+      // ---- R(a, j) += sum_k dN(q; a, k) * b(q; j, k), q then k ascending (AddMult_a_ABt order, densemat.cpp:3002-3015)
+      if (t < ND) {
+        for (int q = 0; q < nq; q++) {
+#pragma unroll
+          for (int k = 0; k < DIM; k++) {
+            const double v = buf[(q * DIM + k) * NDP + t];
+            const double2 b01 = *reinterpret_cast<const double2*>(sbq + (q * DIM + k) * 4);
+            const double b2 = sbq[(q * DIM + k) * 4 + 2];
+            r[0] += v * b01.x;
+            r[1] += v * b01.y;
+            r[2] += v * b2;
+          }
+        }
+      }
+      __syncthreads();  // this chunk's buffer, F and b may be overwritten
+    }
+    if (t < ND) {
+#pragma unroll
+      for (int j = 0; j < DIM; j++) g.Re[e * TD + t + j * ND] = r[j];
+    }
+  }
+}
+
+template <int DIM, int ND, int NQ, int MAT>
+static int launch_element_res3(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
+  using Cfg = ElemRes3Cfg<DIM, ND, NQ>;
+  auto kern = element_res3_kernel<DIM, ND, NQ, MAT>;
+  MB2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+  int per_sm = 0;
+  MB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Cfg::NT, Cfg::SMEM_BYTES));
+  if (per_sm < 1) per_sm = 1;
+  int64_t grid = (int64_t)c->sm_count * per_sm;  // persistent: a whole number of resident CTAs per SM
+  if (grid > a.e1 - a.e0) grid = a.e1 - a.e0;
+  kern<<<(unsigned)grid, Cfg::NT, Cfg::SMEM_BYTES, st>>>(a);
+  MB2_CUDA(cudaGetLastError());
+  return MB2_OK;
+}
+
 template <int DIM, int ND, int NQ, int MAT>
 static int launch_element_res(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
   if (c->res_variant != 1) {
@@ -1283,6 +1446,16 @@ static int dispatch_element(mb2_ctx* c, const ElemArgs& a, cudaStream_t st) {
       case MAT_J2: return launch_element_res<3, 27, 64, MAT_J2>(c, a, st);
       case MAT_J2SIMO: return launch_element_res<3, 27, 64, MAT_J2SIMO>(c, a, st);
       case MAT_J2LOG: return launch_element_res<3, 27, 64, MAT_J2LOG>(c, a, st);
+    }
+  }
+  if (!GRAD && dim == 3 && nd == 64 && nq == 125 && c->elem_variant != 1 && c->res_variant != 1) {
+    switch (c->mat_kind) {
+      case MAT_NEOHOOKEAN: return launch_element_res3<3, 64, 125, MAT_NEOHOOKEAN>(c, a, st);
+      case MAT_STVK: return launch_element_res3<3, 64, 125, MAT_STVK>(c, a, st);
+      case MAT_J2LINEAR: return launch_element_res3<3, 64, 125, MAT_J2LINEAR>(c, a, st);
+      case MAT_J2: return launch_element_res3<3, 64, 125, MAT_J2>(c, a, st);
+      case MAT_J2SIMO: return launch_element_res3<3, 64, 125, MAT_J2SIMO>(c, a, st);
+      case MAT_J2LOG: return launch_element_res3<3, 64, 125, MAT_J2LOG>(c, a, st);
     }
   }
   if (dim == 3 && nd == 27 && nq == 64) return launch_element_mat<3, 27, 64, GRAD, 2>(c, a, st);

@@ -157,10 +157,12 @@ def test_mass_resident_entry_equals_the_adds_into_entry(ctx_factory):
 
 
 @pytest.mark.parametrize("material", ["neohookean", "stvk", "j2linear"])
-@pytest.mark.parametrize("name", ["cube_p2_n3_patch", "beam3_p2", "cylinder_p2_n2"])
+@pytest.mark.parametrize("name", ["cube_p2_n3_patch", "beam3_p2", "cylinder_p2_n2", "cube_p3_n2", "beam4_p3"])
 def test_both_residual_only_kernels_are_bit_exact(ctx_factory, name, material):
-    """mb2_set_option("res_variant"): 0 = element_res2_kernel (one thread per quadrature point for F + stress, one warp
-    with three accumulators per lane for R), 1 = the first form. Same bits from both = the reference's residual."""
+    """mb2_set_option("res_variant"): 0 = element_res2_kernel (p = 2: one thread per quadrature point for F + stress, one warp
+    with three accumulators per lane for R) / element_res3_kernel (p = 3: the table streamed in chunks of 16 points by
+    row-wise bulk copies), 1 = the first form (p = 2) / the generic kernel (p = 3). Same bits from both = the reference's
+    residual."""
     D = load_golden(name)
     for variant in (0, 1):
         ctx = ctx_factory()
