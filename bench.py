@@ -230,24 +230,30 @@ def build_problem_c4(ctx, n, rank=0, world=1, uid=None):
     return M
 
 
+def _code_only(text):
+    """Source text without comments, blank lines and trailing blanks: a comment edit must not orphan an ncu capture."""
+    import re
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    text = re.sub(r"//[^\n]*", "", text)
+    return "\n".join(l.rstrip() for l in text.split("\n") if l.strip())
+
+
 def source_md5(kernel_key=""):
-    """md5 of the kernel's source text: a committed ncu capture only speaks for a binary built from the same kernel
-    source. p=2: the text of element_fd_kernel (Elem2Cfg .. the next section) + mb2_math.cuh; p=3: element_fd_split_kernel."""
+    """md5 of the kernel's source CODE (comments stripped): a committed ncu capture only speaks for a binary built from the
+    same kernel code. p=2: element_fd_kernel (Elem2Cfg .. the next section) + mb2_math.cuh; p=3: element_fd_split_kernel;
+    fast mode: mb2_fast.cu + mb2_math.cuh."""
     import hashlib
-    if "fast" in kernel_key:
-        h = hashlib.md5()
-        for f in ("mb2_fast.cu", "mb2_math.cuh"):
-            with open(os.path.join(ROOT, "mimi_b200", "csrc", f), "rb") as fh:
-                h.update(fh.read())
-        return h.hexdigest()
-    src = open(os.path.join(ROOT, "mimi_b200", "csrc", "mb2_assembly.cu")).read()
-    a, b = ("struct Elem3Cfg", "// History commit:") if "split" in kernel_key else ("struct Elem2Cfg", "// FD-tangent element kernel, column-split")
-    i = src.find(a)
-    j = src.find(b, i)
+    csrc = os.path.join(ROOT, "mimi_b200", "csrc")
     h = hashlib.md5()
-    h.update((src[i:j] if i >= 0 and j > i else src).encode())
-    with open(os.path.join(ROOT, "mimi_b200", "csrc", "mb2_math.cuh"), "rb") as fh:
-        h.update(fh.read())
+    if "fast" in kernel_key:
+        h.update(_code_only(open(os.path.join(csrc, "mb2_fast.cu")).read()).encode())
+    else:
+        src = open(os.path.join(csrc, "mb2_assembly.cu")).read()
+        a, b = ("struct Elem3Cfg", "// History commit:") if "split" in kernel_key else ("struct Elem2Cfg", "// FD-tangent element kernel, column-split")
+        i = src.find(a)
+        j = src.find(b, i)
+        h.update(_code_only(src[i:j] if i >= 0 and j > i else src).encode())
+    h.update(_code_only(open(os.path.join(csrc, "mb2_math.cuh")).read()).encode())
     return h.hexdigest()
 
 
